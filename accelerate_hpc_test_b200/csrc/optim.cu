@@ -1,0 +1,192 @@
+// Fused AdamW (fp32 master weights + moments, bf16/fp32 grads, bf16 shadow params out),
+// squared-gradient-norm reduction and the clip coefficient, all stream-ordered with no host sync.
+// the reference calls torch.optim.AdamW (multi-tensor ATen) and
+// torch.nn.utils.clip_grad_norm_ (reference src/accelerate/accelerator.py:2918-2979).
+#include "common.cuh"
+
+namespace b200 {
+int num_sms();
+
+struct AdamArgs {
+  float lr, beta1, beta2, eps, weight_decay;
+  float bias_c1, bias_c2;  // 1 - beta1^t, 1 - beta2^t
+  float grad_scale;        // multiplies every grad (1/GA, 1/loss_scale, ...)
+};
+
+template <typename GradT>
+__device__ __forceinline__ float load_grad(const GradT* g, long long i);
+template <>
+__device__ __forceinline__ float load_grad<float>(const float* g, long long i) { return g[i]; }
+template <>
+__device__ __forceinline__ float load_grad<__nv_bfloat16>(const __nv_bfloat16* g, long long i) {
+  return __bfloat162float(g[i]);
+}
+
+// flat AdamW over n elements.  clip_coef (device scalar, may be null) multiplies grads;
+// found_inf (device scalar, may be null) != 0 skips the whole update (GradScaler semantics).
+template <typename GradT>
+__global__ void __launch_bounds__(256)
+adamw_flat_kernel(float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
+                  const GradT* __restrict__ grad, __nv_bfloat16* __restrict__ shadow, long long n,
+                  AdamArgs a, const float* __restrict__ clip_coef, const float* __restrict__ found_inf) {
+  if (found_inf && *found_inf != 0.f) return;
+  const float gs = a.grad_scale * (clip_coef ? *clip_coef : 1.f);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float g = load_grad<GradT>(grad, i) * gs;
+    float p = master[i];
+    float mi = m[i] * a.beta1 + (1.f - a.beta1) * g;
+    float vi = v[i] * a.beta2 + (1.f - a.beta2) * g * g;
+    m[i] = mi;
+    v[i] = vi;
+    p *= (1.f - a.lr * a.weight_decay);
+    const float denom = sqrtf(vi / a.bias_c2) + a.eps;
+    p -= (a.lr / a.bias_c1) * (mi / denom);
+    master[i] = p;
+    if (shadow) shadow[i] = __float2bfloat16(p);
+  }
+}
+
+// multi-tensor variant: tensor table in device memory, one CTA per (tensor, 64K-element chunk)
+struct MTEntry {
+  float* master;
+  float* m;
+  float* v;
+  const void* grad;
+  __nv_bfloat16* shadow;
+  long long n;
+  long long chunk_begin;  // first global chunk index of this tensor
+};
+static constexpr int MT_CHUNK = 65536;
+
+template <typename GradT>
+__global__ void __launch_bounds__(256)
+adamw_mt_kernel(const MTEntry* __restrict__ table, int ntensors, AdamArgs a,
+                const float* __restrict__ clip_coef, const float* __restrict__ found_inf) {
+  if (found_inf && *found_inf != 0.f) return;
+  // binary search the tensor owning this chunk
+  const long long chunk = blockIdx.x;
+  int lo = 0, hi = ntensors - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (table[mid].chunk_begin <= chunk) lo = mid; else hi = mid - 1;
+  }
+  const MTEntry e = table[lo];
+  const long long begin = (chunk - e.chunk_begin) * MT_CHUNK;
+  const long long end = min(begin + (long long)MT_CHUNK, e.n);
+  const float gs = a.grad_scale * (clip_coef ? *clip_coef : 1.f);
+  const GradT* grad = reinterpret_cast<const GradT*>(e.grad);
+  for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
+    const float g = load_grad<GradT>(grad, i) * gs;
+    float p = e.master[i];
+    float mi = e.m[i] * a.beta1 + (1.f - a.beta1) * g;
+    float vi = e.v[i] * a.beta2 + (1.f - a.beta2) * g * g;
+    e.m[i] = mi;
+    e.v[i] = vi;
+    p *= (1.f - a.lr * a.weight_decay);
+    p -= (a.lr / a.bias_c1) * (mi / (sqrtf(vi / a.bias_c2) + a.eps));
+    e.master[i] = p;
+    if (e.shadow) e.shadow[i] = __float2bfloat16(p);
+  }
+}
+
+// out[0] += sum(g^2) ; also flags non-finite values in out[1]
+template <typename GradT>
+__global__ void __launch_bounds__(256)
+sumsq_kernel(const GradT* __restrict__ g, long long n, float* __restrict__ out) {
+  __shared__ float red[32];
+  float s = 0.f;
+  bool bad = false;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float x = load_grad<GradT>(g, i);
+    s += x * x;
+    bad |= !isfinite(x);
+  }
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) atomicAdd(out, s);
+  if (bad) out[1] = 1.f;
+}
+
+// norm_out[0] = sqrt(sumsq) ; coef_out[0] = min(1, max_norm / (norm + 1e-6))
+__global__ void clip_coef_kernel(const float* __restrict__ sumsq, float max_norm, float* __restrict__ norm_out,
+                                 float* __restrict__ coef_out) {
+  const float norm = sqrtf(sumsq[0]);
+  norm_out[0] = norm;
+  const float c = max_norm / (norm + 1e-6f);
+  coef_out[0] = c < 1.f ? c : 1.f;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+static inline int flat_grid(long long n) {
+  long long g = (n + 255) / 256;
+  long long cap = (long long)num_sms() * 8;
+  return (int)(g < cap ? (g > 0 ? g : 1) : cap);
+}
+
+B200_API int b200_adamw_flat(void* master, void* m, void* v, const void* grad, void* shadow_bf16,
+                             long long n, int grad_is_bf16, float lr, float beta1, float beta2, float eps,
+                             float weight_decay, int step, float grad_scale, const void* clip_coef,
+                             const void* found_inf, void* stream) {
+  if (n == 0) return 0;
+  AdamArgs a{lr, beta1, beta2, eps, weight_decay, 1.f - powf(beta1, (float)step),
+             1.f - powf(beta2, (float)step), grad_scale};
+  cudaStream_t st = (cudaStream_t)stream;
+  if (grad_is_bf16)
+    adamw_flat_kernel<__nv_bfloat16><<<flat_grid(n), 256, 0, st>>>(
+        (float*)master, (float*)m, (float*)v, (const __nv_bfloat16*)grad, (__nv_bfloat16*)shadow_bf16, n, a,
+        (const float*)clip_coef, (const float*)found_inf);
+  else
+    adamw_flat_kernel<float><<<flat_grid(n), 256, 0, st>>>((float*)master, (float*)m, (float*)v,
+                                                           (const float*)grad, (__nv_bfloat16*)shadow_bf16,
+                                                           n, a, (const float*)clip_coef,
+                                                           (const float*)found_inf);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// table: device array of ntensors MTEntry records (7 x 8 bytes each, see MTEntry); total_chunks =
+// sum(ceil(n_i / 65536)).  The Python side builds the table once per optimizer and re-uses it.
+B200_API int b200_adamw_multi(const void* table, int ntensors, long long total_chunks, int grad_is_bf16,
+                              float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                              float grad_scale, const void* clip_coef, const void* found_inf, void* stream) {
+  if (ntensors == 0 || total_chunks == 0) return 0;
+  AdamArgs a{lr, beta1, beta2, eps, weight_decay, 1.f - powf(beta1, (float)step),
+             1.f - powf(beta2, (float)step), grad_scale};
+  cudaStream_t st = (cudaStream_t)stream;
+  if (grad_is_bf16)
+    adamw_mt_kernel<__nv_bfloat16><<<(unsigned)total_chunks, 256, 0, st>>>(
+        (const MTEntry*)table, ntensors, a, (const float*)clip_coef, (const float*)found_inf);
+  else
+    adamw_mt_kernel<float><<<(unsigned)total_chunks, 256, 0, st>>>((const MTEntry*)table, ntensors, a,
+                                                                   (const float*)clip_coef,
+                                                                   (const float*)found_inf);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// out (2 floats, caller-zeroed before the first call of a step): out[0] += sum g^2, out[1] = inf flag
+B200_API int b200_sumsq(const void* g, long long n, int is_bf16, void* out2, void* stream) {
+  if (n == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_bf16)
+    sumsq_kernel<__nv_bfloat16><<<flat_grid(n), 256, 0, st>>>((const __nv_bfloat16*)g, n, (float*)out2);
+  else
+    sumsq_kernel<float><<<flat_grid(n), 256, 0, st>>>((const float*)g, n, (float*)out2);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+B200_API int b200_clip_coef(const void* sumsq, float max_norm, void* norm_out, void* coef_out, void* stream) {
+  clip_coef_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((const float*)sumsq, max_norm, (float*)norm_out,
+                                                      (float*)coef_out);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
