@@ -1,0 +1,1356 @@
+"""The ``Accelerator``: one object that adapts a user's model / optimizer / dataloaders / scheduler to
+whatever distributed regime the environment describes.
+
+Public surface parity with the reference (src/accelerate/accelerator.py:184-4324; inventory in
+SURVEY.md §2.2): same constructor arguments, properties, ``prepare`` / ``backward`` / ``accumulate``
+/ ``no_sync`` / ``clip_grad_norm_`` / ``gather*`` / ``reduce`` / ``save_state`` / ``load_state`` /
+tracker methods.  What is different is what ``prepare`` hands back on CUDA:
+
+* ``MULTI_GPU``  -> :class:`~.parallel.ddp.B200DataParallel`, a bucketed reducer whose buckets live in
+  peer-mapped memory and are reduced by a fused cast+scale+all-reduce kernel overlapped with backward
+  (the reference wraps ``torch.nn.parallel.DistributedDataParallel``, :1865-1869);
+* ``FSDP``       -> :class:`~.parallel.fsdp.B200ShardedModule`, flat per-unit shards, peer-pull
+  all-gather with prefetch, reduce-scatter fused with the sharded AdamW update
+  (the reference calls torch's ``fully_shard``, utils/fsdp_utils.py:621-737);
+* tp / cp / sp axes of ``ParallelismConfig`` -> the engines in :mod:`.parallel`.
+
+On CPU (gloo) the same classes run with c10d collectives, which is the oracle the tests use.
+"""
+
+from __future__ import annotations
+
+import contextlib
+import functools
+import json
+import math
+import os
+import re
+import shutil
+import sys
+import warnings
+from collections import OrderedDict
+from contextlib import contextmanager
+from functools import partial
+from types import MethodType
+from typing import Any, Callable, Optional, Union
+
+import torch
+
+from .checkpointing import load_accelerator_state, load_custom_state, save_accelerator_state, save_custom_state
+from .data_loader import DataLoaderDispatcher, prepare_data_loader, skip_first_batches
+from .logging import get_logger
+from .optimizer import AcceleratedOptimizer
+from .parallelism_config import ParallelismConfig
+from .scheduler import AcceleratedScheduler
+from .state import AcceleratorState, GradientState, PartialState
+from .utils.constants import FSDP_MODEL_NAME, OPTIMIZER_NAME, PROFILE_PATTERN_NAME, SAFE_WEIGHTS_INDEX_NAME, SAFE_WEIGHTS_NAME, SAFE_WEIGHTS_PATTERN_NAME, WEIGHTS_INDEX_NAME, WEIGHTS_NAME, WEIGHTS_PATTERN_NAME
+from .utils.dataclasses import (
+    AORecipeKwargs,
+    AutocastKwargs,
+    DataLoaderConfiguration,
+    DeepSpeedPlugin,
+    DistributedDataParallelKwargs,
+    DistributedType,
+    DynamoBackend,
+    FP8BackendType,
+    FP8RecipeKwargs,
+    FullyShardedDataParallelPlugin,
+    GradientAccumulationPlugin,
+    GradScalerKwargs,
+    InitProcessGroupKwargs,
+    KwargsHandler,
+    LoggerType,
+    MegatronLMPlugin,
+    MSAMPRecipeKwargs,
+    PrecisionType,
+    ProfileKwargs,
+    ProjectConfiguration,
+    RNGType,
+    TERecipeKwargs,
+    TorchDynamoPlugin,
+    TorchTensorParallelPlugin,
+)
+from .utils.environment import parse_choice_from_env, parse_flag_from_env, str_to_bool
+from .utils.memory import clear_device_cache, release_memory
+from .utils.operations import (
+    broadcast,
+    convert_outputs_to_fp32,
+    gather,
+    gather_object,
+    pad_across_processes,
+    recursively_apply,
+    reduce,
+    send_to_device,
+)
+from .utils.other import check_os_kernel, clean_state_dict_for_safetensors, compile_regions, extract_model_from_parallel, is_compiled_module, save, wait_for_everyone
+from .utils.random import set_seed
+
+logger = get_logger(__name__)
+
+_split_batches = object()
+_dispatch_batches = object()
+_even_batches = object()
+_use_seedable_sampler = object()
+
+
+def _is_module(x):
+    return isinstance(x, torch.nn.Module)
+
+
+def _is_optimizer(x):
+    return isinstance(x, torch.optim.Optimizer)
+
+
+def _is_dataloader(x):
+    return isinstance(x, torch.utils.data.DataLoader)
+
+
+def _is_scheduler(x):
+    try:
+        from torch.optim.lr_scheduler import LRScheduler
+    except ImportError:  # pragma: no cover
+        from torch.optim.lr_scheduler import _LRScheduler as LRScheduler
+    return isinstance(x, LRScheduler)
+
+
+class Accelerator:
+    """Creates the distributed state and wraps training objects.
+
+    Args mirror the reference: ``device_placement, split_batches, mixed_precision,
+    gradient_accumulation_steps, cpu, dataloader_config, deepspeed_plugin(s), fsdp_plugin,
+    torch_tp_plugin (deprecated), megatron_lm_plugin, rng_types, log_with, project_dir, project_config,
+    gradient_accumulation_plugin, step_scheduler_with_optimizer, kwargs_handlers, dynamo_backend,
+    dynamo_plugin, parallelism_config``.
+    """
+
+    def __init__(
+        self,
+        device_placement: bool = True,
+        split_batches: bool = _split_batches,
+        mixed_precision: Optional[str] = None,
+        gradient_accumulation_steps: int = 1,
+        cpu: bool = False,
+        dataloader_config: Optional[DataLoaderConfiguration] = None,
+        deepspeed_plugin: Union[DeepSpeedPlugin, dict, None] = None,
+        fsdp_plugin: Optional[FullyShardedDataParallelPlugin] = None,
+        torch_tp_plugin: Optional[TorchTensorParallelPlugin] = None,
+        megatron_lm_plugin: Optional[MegatronLMPlugin] = None,
+        rng_types: Optional[list] = None,
+        log_with=None,
+        project_dir: Optional[Union[str, os.PathLike]] = None,
+        project_config: Optional[ProjectConfiguration] = None,
+        gradient_accumulation_plugin: Optional[GradientAccumulationPlugin] = None,
+        step_scheduler_with_optimizer: bool = True,
+        kwargs_handlers: Optional[list[KwargsHandler]] = None,
+        dynamo_backend=None,
+        dynamo_plugin: Optional[TorchDynamoPlugin] = None,
+        deepspeed_plugins: Union[DeepSpeedPlugin, dict, None] = None,
+        parallelism_config: Optional[ParallelismConfig] = None,
+    ):
+        self.trackers = []
+        if project_config is not None:
+            self.project_configuration = project_config
+        else:
+            self.project_configuration = ProjectConfiguration(project_dir=project_dir)
+        if project_dir is not None and self.project_dir is None:
+            self.project_configuration.set_directories(project_dir)
+        if mixed_precision is not None:
+            mixed_precision = str(mixed_precision)
+            if mixed_precision not in PrecisionType:
+                raise ValueError(f"Unknown mixed_precision mode: {mixed_precision}. Choose between {PrecisionType.list()}")
+        if dynamo_plugin is not None and dynamo_backend is not None:
+            raise ValueError("You cannot pass in both `dynamo_plugin` and `dynamo_backend`, please only pass in one.")
+        if dynamo_backend is not None:
+            dynamo_plugin = TorchDynamoPlugin(backend=dynamo_backend)
+        elif dynamo_plugin is None:
+            dynamo_plugin = TorchDynamoPlugin()
+
+        if deepspeed_plugins is not None and deepspeed_plugin is not None:
+            raise ValueError("You cannot pass in both `deepspeed_plugins` and `deepspeed_plugin`.")
+        elif deepspeed_plugin is not None:
+            deepspeed_plugins = deepspeed_plugin
+        if deepspeed_plugins is None and PartialState._shared_state == {} and parse_flag_from_env("ACCELERATE_USE_DEEPSPEED"):
+            deepspeed_plugins = DeepSpeedPlugin()
+        if deepspeed_plugins is not None and not isinstance(deepspeed_plugins, dict):
+            if not isinstance(deepspeed_plugins, DeepSpeedPlugin):
+                raise TypeError("`deepspeed_plugin` must be a DeepSpeedPlugin or a dict of them")
+            deepspeed_plugins = {"default": deepspeed_plugins}
+        if deepspeed_plugins is not None:
+            for plugin in deepspeed_plugins.values():
+                if not isinstance(plugin, DeepSpeedPlugin):
+                    raise TypeError("`deepspeed_plugin` must be a DeepSpeedPlugin or a dict of them")
+            os.environ["ACCELERATE_USE_DEEPSPEED"] = "true"
+
+        if parse_flag_from_env("ACCELERATE_USE_FSDP") or isinstance(fsdp_plugin, FullyShardedDataParallelPlugin):
+            pass
+        if fsdp_plugin is None:
+            if parse_flag_from_env("ACCELERATE_USE_FSDP"):
+                fsdp_plugin = FullyShardedDataParallelPlugin()
+        elif not isinstance(fsdp_plugin, FullyShardedDataParallelPlugin):
+            raise TypeError("`fsdp_plugin` must be a FullyShardedDataParallelPlugin object.")
+        if megatron_lm_plugin is None:
+            if parse_flag_from_env("ACCELERATE_USE_MEGATRON_LM"):
+                megatron_lm_plugin = MegatronLMPlugin()
+        elif not isinstance(megatron_lm_plugin, MegatronLMPlugin):
+            raise TypeError("`megatron_lm_plugin` must be a MegatronLMPlugin object.")
+
+        # ---- kwargs handlers
+        self.ddp_handler = None
+        self.scaler_handler = None
+        self.init_handler = None
+        self.fp8_recipe_handler = None
+        self.ao_recipe_handler = None
+        self.te_recipe_handler = None
+        self.msamp_recipe_handler = None
+        self.autocast_handler = None
+        self.profile_handler = None
+        self.has_lomo_optimizer = False
+        found_handlers = set()
+        handler_slots = {
+            DistributedDataParallelKwargs: "ddp_handler", GradScalerKwargs: "scaler_handler", InitProcessGroupKwargs: "init_handler",
+            AORecipeKwargs: "ao_recipe_handler", TERecipeKwargs: "te_recipe_handler", MSAMPRecipeKwargs: "msamp_recipe_handler",
+            AutocastKwargs: "autocast_handler", ProfileKwargs: "profile_handler", FP8RecipeKwargs: "fp8_recipe_handler",
+        }
+        for handler in kwargs_handlers or []:
+            if not isinstance(handler, KwargsHandler):
+                raise TypeError(f"Unsupported kwargs handler passed: {handler}, must be one that inherits `accelerate.utils.KwargsHandler`.")
+            # exact class first so FP8RecipeKwargs (a TE+MSAMP subclass) lands in its own slot
+            slot = handler_slots.get(type(handler))
+            if slot is None:
+                for cls, name in handler_slots.items():
+                    if isinstance(handler, cls):
+                        slot = name
+                        break
+            if slot is None:
+                raise ValueError(f"Unsupported kwargs handler {handler.__class__}")
+            if type(handler) in found_handlers:
+                raise ValueError(f"You can only pass one {handler.__class__} in `kwargs_handlers`.")
+            found_handlers.add(type(handler))
+            setattr(self, slot, handler)
+
+        if parallelism_config is None and parse_flag_from_env("ACCELERATE_USE_PARALLELISM_CONFIG"):
+            parallelism_config = ParallelismConfig()
+        if torch_tp_plugin is not None and parallelism_config is None:
+            parallelism_config = ParallelismConfig(tp_size=torch_tp_plugin.tp_size)
+
+        kwargs = self.init_handler.to_kwargs() if self.init_handler is not None else {}
+        self.state = AcceleratorState(
+            mixed_precision=mixed_precision, cpu=cpu, dynamo_plugin=dynamo_plugin, deepspeed_plugin=deepspeed_plugins,
+            fsdp_plugin=fsdp_plugin, torch_tp_plugin=torch_tp_plugin, megatron_lm_plugin=megatron_lm_plugin,
+            parallelism_config=parallelism_config, _from_accelerator=True, **kwargs,
+        )
+        if self.parallelism_config is not None:
+            self.parallelism_config._validate_accelerator(self)
+            if self.parallelism_config.total_size > 1 and self.state.device_mesh is None:
+                self.state.device_mesh = self.parallelism_config.get_device_mesh(self.device.type)
+
+        # ---- fp8 back-end selection: native MXFP8 first, then library back-ends
+        self.fp8_enabled = self.state.mixed_precision == "fp8" or mixed_precision == "fp8"
+        self.has_fp8_handler = any(h is not None for h in (self.fp8_recipe_handler, self.ao_recipe_handler, self.te_recipe_handler, self.msamp_recipe_handler))
+        if self.fp8_enabled:
+            self._fp8_backend = self._select_fp8_backend()
+        else:
+            self._fp8_backend = None
+        self.delayed_fp8_autocast = False
+
+        trackers = log_with
+        from .tracking import filter_trackers
+
+        self.log_with = filter_trackers(trackers, self.logging_dir)
+
+        if (mixed_precision != "bf16") and getattr(self.state, "downcast_bfloat", False) and (self.state.distributed_type != DistributedType.XLA):
+            raise ValueError("Can only use `downcast_bf16` when using `mixed_precision='bf16'` and on a TPU")
+
+        # ---- gradient accumulation
+        if gradient_accumulation_plugin is not None:
+            if gradient_accumulation_steps != 1:
+                raise ValueError("You can only pass one of `gradient_accumulation_steps` and `gradient_accumulation_plugin`. Please only pass in the created `GradientAccumulationPlugin` object.")
+        else:
+            gradient_accumulation_steps = int(parse_choice_from_env("ACCELERATE_GRADIENT_ACCUMULATION_STEPS", gradient_accumulation_steps))
+            gradient_accumulation_plugin = GradientAccumulationPlugin(num_steps=gradient_accumulation_steps)
+        self.gradient_state = GradientState(gradient_accumulation_plugin=gradient_accumulation_plugin)
+
+        self.device_placement = device_placement
+        if dataloader_config is None:
+            dataloader_config = DataLoaderConfiguration()
+        self.dataloader_config = dataloader_config
+        if split_batches is not _split_batches:
+            warnings.warn("`split_batches` as an Accelerator argument is deprecated; pass `dataloader_config=DataLoaderConfiguration(split_batches=...)`.", FutureWarning)
+            self.dataloader_config.split_batches = split_batches
+        self.step_scheduler_with_optimizer = step_scheduler_with_optimizer
+
+        # ---- mixed precision: only fp16 needs a loss scaler
+        self.scaler = None
+        self.native_amp = False
+        if self.state.mixed_precision == "fp16" and self.device.type != "cpu":
+            self.native_amp = True
+            kwargs = self.scaler_handler.to_kwargs() if self.scaler_handler is not None else {}
+            self.scaler = torch.amp.GradScaler("cuda", **kwargs)
+        elif self.state.mixed_precision == "fp16":
+            self.native_amp = True
+            kwargs = self.scaler_handler.to_kwargs() if self.scaler_handler is not None else {}
+            self.scaler = torch.amp.GradScaler("cpu", **kwargs)
+        elif self.state.mixed_precision == "bf16":
+            self.native_amp = True
+        elif self.state.mixed_precision == "fp8":
+            self.native_amp = True
+
+        self.step = 0
+        self._optimizers = []
+        self._models = []
+        self._schedulers = []
+        self._dataloaders = []
+        self._custom_objects = []
+        self._load_model_state_pre_hook = OrderedDict()
+        self._save_model_state_pre_hook = OrderedDict()
+        self.rng_types = rng_types
+        if self.rng_types is None:
+            self.rng_types = ["generator"]
+        self.flag_tensor = None
+        self._cp_context = None
+        check_os_kernel()
+
+    def _select_fp8_backend(self) -> FP8BackendType:
+        from .utils.imports import is_b200_kernels_available, is_msamp_available, is_torchao_available, is_transformer_engine_available
+
+        env = os.environ.get("ACCELERATE_FP8_BACKEND", None)
+        if env is not None:
+            return FP8BackendType(env.upper())
+        if self.ao_recipe_handler is not None:
+            return FP8BackendType.AO
+        if self.msamp_recipe_handler is not None:
+            return FP8BackendType.MSAMP
+        if self.te_recipe_handler is not None and is_transformer_engine_available():
+            return FP8BackendType.TE
+        if self.device.type == "cuda" and is_b200_kernels_available():
+            return FP8BackendType.NATIVE
+        if is_torchao_available():
+            return FP8BackendType.AO
+        if is_transformer_engine_available():
+            return FP8BackendType.TE
+        if is_msamp_available():
+            return FP8BackendType.MSAMP
+        raise ImportError("fp8 mixed precision needs the native kernel library on a CUDA device, or torchao / transformer-engine / MS-AMP.")
+
+    # ================================================================== properties
+    @property
+    def deepspeed_plugin(self):
+        return self.state.deepspeed_plugin
+
+    @property
+    def use_distributed(self):
+        return self.state.use_distributed
+
+    @property
+    def multi_device(self):
+        return self.use_distributed and self.distributed_type in (DistributedType.MULTI_GPU, DistributedType.MULTI_CPU)
+
+    @property
+    def distributed_type(self):
+        return self.state.distributed_type
+
+    @property
+    def num_processes(self):
+        return self.state.num_processes
+
+    @property
+    def process_index(self):
+        return self.state.process_index
+
+    @property
+    def local_process_index(self):
+        return self.state.local_process_index
+
+    @property
+    def device(self):
+        return self.state.device
+
+    @property
+    def split_batches(self):
+        return self.dataloader_config.split_batches
+
+    @property
+    def dispatch_batches(self):
+        return self.dataloader_config.dispatch_batches
+
+    @property
+    def even_batches(self):
+        return self.dataloader_config.even_batches
+
+    @even_batches.setter
+    def even_batches(self, value: bool):
+        self.dataloader_config.even_batches = value
+
+    @property
+    def use_seedable_sampler(self):
+        return self.dataloader_config.use_seedable_sampler
+
+    @property
+    def non_blocking(self):
+        return self.dataloader_config.non_blocking
+
+    @property
+    def use_stateful_dataloader(self):
+        return getattr(self.dataloader_config, "use_stateful_dataloader", False)
+
+    @property
+    def project_dir(self):
+        return self.project_configuration.project_dir
+
+    @property
+    def logging_dir(self):
+        return self.project_configuration.logging_dir
+
+    @property
+    def save_iteration(self):
+        return self.project_configuration.iteration
+
+    @property
+    def is_main_process(self):
+        return self.state.is_main_process
+
+    @property
+    def is_local_main_process(self):
+        return self.state.is_local_main_process
+
+    @property
+    def is_last_process(self):
+        return self.process_index == self.num_processes - 1
+
+    @property
+    def mixed_precision(self):
+        return self.state.mixed_precision
+
+    @property
+    def is_fsdp2(self):
+        return self.state.is_fsdp2
+
+    @property
+    def is_composable_parallelism_enabled(self):
+        return self.is_fsdp2
+
+    @property
+    def parallelism_config(self) -> Optional[ParallelismConfig]:
+        return self.state.parallelism_config
+
+    @property
+    def torch_device_mesh(self):
+        return self.state.device_mesh
+
+    @property
+    def should_save_model(self):
+        """False on ranks that hold a replica another rank already saves (non-zero tp rank etc.)."""
+        if (pc := self.parallelism_config) is None or pc.total_size == 1:
+            return True
+        mesh = self.torch_device_mesh
+        names = tuple(mesh.mesh_dim_names or ()) if mesh is not None else ()
+        for axis in ("dp_replicate", "cp", "sp"):
+            if axis in names and mesh.get_local_rank(axis) != 0:
+                return False
+        return True
+
+    def _mesh_rank(self, axis: str, what: str) -> int:
+        mesh = self.torch_device_mesh
+        if mesh is None or axis not in (mesh.mesh_dim_names or ()):
+            raise RuntimeError(f"{what} is not enabled. Please check your configuration.")
+        return mesh.get_local_rank(axis)
+
+    @property
+    def tensor_parallel_rank(self) -> int:
+        return self._mesh_rank("tp", "Tensor parallelism")
+
+    @property
+    def pipeline_parallel_rank(self) -> int:
+        raise NotImplementedError("Pipeline parallelism is currently not supported in Accelerate.")
+
+    @property
+    def context_parallel_rank(self) -> int:
+        raise NotImplementedError("Context parallelism is currently not supported in Accelerate.")
+
+    @property
+    def data_parallel_rank(self) -> int:
+        return self._mesh_rank("dp_replicate", "Data parallelism")
+
+    @property
+    def data_parallel_shard_rank(self) -> int:
+        return self._mesh_rank("dp_shard", "Data parallelism")
+
+    @property
+    def sync_gradients(self):
+        return self.gradient_state.sync_gradients
+
+    @sync_gradients.setter
+    def sync_gradients(self, sync_gradients):
+        self.gradient_state.sync_gradients = sync_gradients
+
+    @property
+    def gradient_accumulation_steps(self):
+        return self.gradient_state.num_steps
+
+    @gradient_accumulation_steps.setter
+    def gradient_accumulation_steps(self, gradient_accumulation_steps):
+        self.gradient_state.plugin_kwargs.update({"num_steps": gradient_accumulation_steps})
+
+    @property
+    def optimizer_step_was_skipped(self):
+        """True if the last optimizer step was skipped (fp16 overflow)."""
+        return any(opt.step_was_skipped for opt in self._optimizers)
+
+    @property
+    def fp8_backend(self):
+        """The fp8 back-end in use (``NATIVE`` = own MXFP8 kernels), or None."""
+        return self._fp8_backend
+
+    # ================================================================== process control passthroughs
+    @contextmanager
+    def split_between_processes(self, inputs, apply_padding: bool = False):
+        with PartialState().split_between_processes(inputs, apply_padding=apply_padding) as inputs:
+            yield inputs
+
+    def _proc_decorator(self, state_method, function, **kw):
+        if function is None:
+            if "Accelerator." in getattr(self, "__qualname__", ""):
+                function = self
+            else:
+                raise ValueError("The decorator must wrap a function.")
+
+        def _inner(*args, **kwargs):
+            return state_method(function, **kw)(*args, **kwargs)
+
+        return functools.wraps(function)(_inner)
+
+    def on_main_process(self, function: Callable[..., Any] = None):
+        return self._proc_decorator(PartialState().on_main_process, function)
+
+    def on_local_main_process(self, function: Callable[..., Any] = None):
+        return self._proc_decorator(PartialState().on_local_main_process, function)
+
+    def on_last_process(self, function: Callable[..., Any]):
+        return self._proc_decorator(PartialState().on_last_process, function)
+
+    def on_process(self, function: Callable[..., Any] = None, process_index: int = None):
+        if (self is not None) and (process_index is not None) and (function is None):
+            return partial(self.on_process, process_index=process_index)
+        return self._proc_decorator(PartialState().on_process, function, process_index=process_index)
+
+    def on_local_process(self, function: Callable[..., Any] = None, local_process_index: int = None):
+        if (self is not None) and (local_process_index is not None) and (function is None):
+            return partial(self.on_local_process, local_process_index=local_process_index)
+        return self._proc_decorator(PartialState().on_local_process, function, local_process_index=local_process_index)
+
+    @contextmanager
+    def main_process_first(self):
+        with self.state.main_process_first():
+            yield
+
+    @contextmanager
+    def local_main_process_first(self):
+        with self.state.local_main_process_first():
+            yield
+
+    def wait_for_everyone(self):
+        wait_for_everyone()
+
+    def print(self, *args, **kwargs):
+        self.state.print(*args, **kwargs)
+
+    # ================================================================== gradient synchronisation
+    @contextmanager
+    def no_sync(self, model):
+        """Skip the gradient reduction of the wrapped ``model`` for the steps inside the block."""
+        if self.is_fsdp2 and hasattr(model, "set_requires_gradient_sync"):
+            model.set_requires_gradient_sync(False)
+            try:
+                yield
+            finally:
+                model.set_requires_gradient_sync(True)
+            return
+        context = contextlib.nullcontext
+        if self.use_distributed:
+            context = getattr(model, "no_sync", context)
+        with context():
+            yield
+
+    @staticmethod
+    @contextmanager
+    def trigger_sync_in_backward(model):
+        """Re-enable the reduction for a backward whose forward ran under ``no_sync``."""
+        if hasattr(model, "trigger_sync_in_backward"):
+            with model.trigger_sync_in_backward():
+                yield
+            return
+        if not isinstance(model, torch.nn.parallel.DistributedDataParallel):
+            yield
+            return
+        old_require_backward_grad_sync = model.require_backward_grad_sync
+        old_require_forward_param_sync = model.require_forward_param_sync
+        model.require_backward_grad_sync = True
+        model.require_forward_param_sync = True
+        model.reducer.prepare_for_backward([])
+        try:
+            yield
+        finally:
+            model.require_backward_grad_sync = old_require_backward_grad_sync
+            model.require_forward_param_sync = old_require_forward_param_sync
+
+    def _do_sync(self):
+        """Decide whether the current micro-step ends an accumulation window."""
+        if self.gradient_state.sync_with_dataloader and self.gradient_state.end_of_dataloader:
+            self.step = 0
+            self.gradient_state._set_sync_gradients(True)
+        else:
+            self.step += 1
+            self.gradient_state._set_sync_gradients((self.step % self.gradient_state.num_steps) == 0)
+
+    @contextmanager
+    def accumulate(self, *models):
+        """Gradient accumulation: inside the block ``sync_gradients`` says whether this is a real step."""
+        self._do_sync()
+        allow_gradient_sync = self.sync_gradients or (
+            self.use_distributed and self.gradient_state.plugin_kwargs.get("sync_each_batch", False)
+        )
+        with contextlib.ExitStack() as cm_stack:
+            for m in models:
+                cm_stack.enter_context(contextlib.nullcontext() if allow_gradient_sync else self.no_sync(m))
+            yield
+
+    @contextmanager
+    def join_uneven_inputs(self, joinables, even_batches=None):
+        """Train on uneven per-rank inputs (torch ``Join``); optionally override ``even_batches`` inside."""
+        if self.multi_device or self.distributed_type == DistributedType.FSDP:
+            from torch.distributed.algorithms.join import Join
+
+            dl_even_batches_values = []
+            if even_batches is not None:
+                iterable_dl_seen = False
+                for dl_idx, dl in enumerate(self._dataloaders):
+                    if isinstance(dl, DataLoaderDispatcher) or type(dl) is DataLoaderDispatcher:
+                        iterable_dl_seen = True
+                        continue
+                    if getattr(dl, "batch_sampler", None) is not None and hasattr(dl.batch_sampler, "even_batches"):
+                        dl_even_batches_values.append((dl_idx, dl.batch_sampler.even_batches))
+                        dl.batch_sampler.even_batches = even_batches
+                if iterable_dl_seen:
+                    warnings.warn("Overridding even_batches is only supported for map-style datasets, yet some dataloaders given were iterable")
+            joinables = [j for j in joinables if hasattr(j, "join_hook")]
+            try:
+                if joinables:
+                    with Join(joinables):
+                        yield
+                else:
+                    yield
+            finally:
+                for dl_idx, value in dl_even_batches_values:
+                    self._dataloaders[dl_idx].batch_sampler.even_batches = value
+        else:
+            if self.distributed_type != DistributedType.NO:
+                warnings.warn("Joining uneven inputs is only supported for multi-GPU training, as a result `join_uneven_inputs` will have no effect.")
+            with contextlib.nullcontext(joinables):
+                yield
+
+    # ================================================================== prepare
+    def _prepare_one(self, obj, first_pass: bool = False, device_placement=None):
+        if first_pass:
+            if _is_dataloader(obj):
+                return self.prepare_data_loader(obj, device_placement=device_placement)
+            if _is_module(obj):
+                return self.prepare_model(obj, device_placement=device_placement)
+            if _is_optimizer(obj):
+                optimizer = self.prepare_optimizer(obj, device_placement=device_placement)
+                return optimizer
+        elif _is_scheduler(obj):
+            return self.prepare_scheduler(obj)
+        return obj
+
+    def prepare(self, *args, device_placement=None):
+        """Prepare models, optimizers, dataloaders and schedulers; returns them in the order given."""
+        if device_placement is None:
+            device_placement = [None for _ in args]
+        elif self.distributed_type in (DistributedType.DEEPSPEED, DistributedType.MEGATRON_LM):
+            raise ValueError("You can't customize device placements with DeepSpeed or Megatron-LM.")
+        elif len(device_placement) != len(args):
+            raise ValueError(f"`device_placement` should be a list with {len(args)} elements (the number of objects passed).")
+
+        for obj in args:
+            if _is_module(obj) and self.verify_device_map(obj) and self.distributed_type != DistributedType.NO and os.environ.get("ACCELERATE_BYPASS_DEVICE_MAP", "false") != "true":
+                raise ValueError(
+                    "You can't train a model that has been loaded with `device_map='auto'` in any distributed mode."
+                    " Please rerun your script specifying `--num_processes=1` or by launching with `python {{myscript.py}}`."
+                )
+        if self.distributed_type in (DistributedType.FSDP,) or self.is_fsdp2:
+            n_models = sum(1 for o in args if _is_module(o))
+            n_opts = sum(1 for o in args if _is_optimizer(o))
+            if self.is_fsdp2 and n_opts > 0 and n_models == 0:
+                raise ValueError("When using FSDP2, a model and optimizer must be passed together to `Accelerator.prepare()` as the optimizer needs to have its parameters modified after the model is converted.")
+            if self.is_fsdp2 and n_models > 1:
+                raise ValueError("Only one model is supported when using FSDP2")
+
+        # already-prepared objects pass through untouched (idempotence)
+        result = []
+        models_this_call = []
+        optimizers_this_call = []
+        for obj, placement in zip(args, device_placement):
+            if getattr(obj, "_is_accelerate_prepared", False):
+                result.append(obj)
+                continue
+            if _is_module(obj):
+                new = self.prepare_model(obj, device_placement=placement)
+                models_this_call.append((obj, new))
+                result.append(new)
+            elif _is_dataloader(obj):
+                result.append(self.prepare_data_loader(obj, device_placement=placement))
+            elif _is_optimizer(obj):
+                new = self.prepare_optimizer(obj, device_placement=placement)
+                optimizers_this_call.append(new)
+                result.append(new)
+            else:
+                result.append(obj)
+        # optimizers learn about the engines that own their parameters (sharded update, fused clip)
+        for _, engine_model in models_this_call:
+            engine = engine_model if hasattr(engine_model, "bind_optimizer") else None
+            if engine is not None:
+                for opt in optimizers_this_call or self._optimizers:
+                    engine.bind_optimizer(opt)
+        # schedulers last: they need the prepared optimizers
+        result = [self.prepare_scheduler(o) if (_is_scheduler(o) and not getattr(o, "_is_accelerate_prepared", False)) else o for o in result]
+        for item in result:
+            if any(item in container for container in (self._dataloaders, self._models, self._optimizers, self._schedulers)):
+                try:
+                    item._is_accelerate_prepared = True
+                except Exception:
+                    pass
+        return tuple(result) if len(result) > 1 else result[0]
+
+    def _mixed_precision_dtype(self):
+        return {"fp16": torch.float16, "bf16": torch.bfloat16, "fp8": torch.bfloat16}.get(self.mixed_precision)
+
+    def prepare_model(self, model: torch.nn.Module, device_placement: Optional[bool] = None, evaluation_mode: bool = False):
+        """Place ``model`` on the device, add mixed precision and wrap it in the engine of the active strategy."""
+        if device_placement is None:
+            device_placement = self.device_placement and self.distributed_type != DistributedType.FSDP
+        self._models.append(model)
+
+        if self.verify_device_map(model) and self.distributed_type != DistributedType.NO and os.environ.get("ACCELERATE_BYPASS_DEVICE_MAP", "false") != "true":
+            raise ValueError("You can't train a model that has been loaded with `device_map='auto'` in any distributed mode.")
+
+        # ---- mixed precision on the forward
+        if self.native_amp:
+            model._original_forward = model.forward
+            autocast_context = self._get_autocast_context()
+            model_forward_func = model.forward.__func__ if hasattr(model.forward, "__func__") else model.forward
+            new_forward = autocast_context(model_forward_func)
+            if hasattr(model.forward, "__func__"):
+                model.forward = MethodType(new_forward, model)
+                model.forward = MethodType(convert_outputs_to_fp32(model.forward.__func__), model)
+            else:
+                model.forward = convert_outputs_to_fp32(new_forward)
+
+        if self.fp8_enabled and self._fp8_backend == FP8BackendType.NATIVE:
+            from .parallel.precision import convert_model_to_mxfp8
+
+            recipe = self.te_recipe_handler
+            model = convert_model_to_mxfp8(model, recipe)
+
+        if (getattr(model, "is_loaded_in_8bit", False) or getattr(model, "is_loaded_in_4bit", False)) and getattr(model, "hf_device_map", False):
+            model_devices = set(model.hf_device_map.values())
+            if len(model_devices) > 1 and self.distributed_type != DistributedType.NO:
+                raise ValueError("You can't train a model that has been loaded in 8-bit or 4-bit precision on multiple devices in any distributed mode.")
+        elif device_placement and not self.verify_device_map(model):
+            model = model.to(self.device)
+
+        if not evaluation_mode:
+            if self.distributed_type == DistributedType.MULTI_GPU or (self.distributed_type == DistributedType.MULTI_CPU):
+                if any(p.requires_grad for p in model.parameters()):
+                    model = self._wrap_data_parallel(model)
+            elif self.distributed_type in (DistributedType.FSDP, DistributedType.DEEPSPEED, DistributedType.MEGATRON_LM):
+                model = self._wrap_sharded(model)
+        # activation checkpointing can be requested through the FSDP plugin even on one process
+        plugin = self.state.fsdp_plugin
+        if plugin is not None and plugin.activation_checkpointing and self.distributed_type == DistributedType.NO:
+            from .parallel.fsdp import apply_activation_checkpointing
+
+            plugin.set_auto_wrap_policy(model)
+            apply_activation_checkpointing(model, plugin)
+
+        if self.state.dynamo_plugin.backend != DynamoBackend.NO and not is_compiled_module(model):
+            if self.state.dynamo_plugin.use_regional_compilation:
+                model = compile_regions(model, **self.state.dynamo_plugin.to_kwargs())
+            else:
+                model = torch.compile(model, **self.state.dynamo_plugin.to_kwargs())
+        self._models[-1] = model
+        return model
+
+    def _wrap_data_parallel(self, model):
+        kwargs = self.ddp_handler.to_kwargs() if self.ddp_handler is not None else {}
+        pc = self.parallelism_config
+        if pc is not None and pc.tp_enabled and self.device.type == "cuda":
+            from .parallel.tensor_parallel import apply_tensor_parallel
+
+            model = apply_tensor_parallel(model, self.torch_device_mesh["tp"], pc.tp_handler)
+        if self.device.type == "cuda" and os.environ.get("ACCELERATE_B200_DDP", "1") != "0":
+            from .parallel.ddp import B200DataParallel
+
+            group = None
+            if self.torch_device_mesh is not None and "dp_replicate" in (self.torch_device_mesh.mesh_dim_names or ()):
+                group = self.torch_device_mesh["dp_replicate"].get_group()
+            return B200DataParallel(model, process_group=group, handler=self.ddp_handler, gradient_state=self.gradient_state)
+        device_ids, output_device = (None, None)
+        if self.device.type == "cuda":
+            device_ids, output_device = [self.local_process_index], self.local_process_index
+        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=device_ids, output_device=output_device, **kwargs)
+        if self.ddp_handler is not None:
+            self.ddp_handler.register_comm_hook(model)
+        return model
+
+    def _wrap_sharded(self, model):
+        from .parallel.fsdp import B200ShardedModule
+
+        plugin = self.state.fsdp_plugin
+        if plugin is None and self.distributed_type == DistributedType.DEEPSPEED:
+            plugin = self.deepspeed_plugin.to_fsdp_plugin()
+        if plugin is None:
+            plugin = FullyShardedDataParallelPlugin(fsdp_version=2, auto_wrap_policy="no_wrap")
+        if self.mixed_precision != "no":
+            plugin.set_mixed_precision(self.mixed_precision)
+        pc = self.parallelism_config
+        mesh = self.torch_device_mesh
+        if pc is not None and pc.tp_enabled:
+            from .parallel.tensor_parallel import apply_tensor_parallel
+
+            model = apply_tensor_parallel(model, mesh["tp"], pc.tp_handler)
+        if pc is not None and pc.sp_enabled:
+            from .parallel.ulysses import apply_ulysses
+
+            model = apply_ulysses(model, mesh["sp"], pc.sp_handler)
+        if pc is not None and pc.cp_enabled:
+            from .parallel.context_parallel import apply_context_parallel
+
+            model = apply_context_parallel(model, mesh["cp"], pc.cp_handler)
+        shard_group = replicate_group = None
+        if mesh is not None:
+            names = mesh.mesh_dim_names or ()
+            if pc is not None and ("dp_shard" in names or "cp" in names):
+                shard_group = mesh["dp_shard_cp"].get_group()
+            elif pc is not None and pc.total_size > 1:
+                # only tp/sp axes are active: nothing to shard over
+                shard_group = torch.distributed.new_group([self.process_index]) if False else None
+            if "dp_replicate" in names:
+                replicate_group = mesh["dp_replicate"].get_group()
+        plugin.set_auto_wrap_policy(model)
+        return B200ShardedModule(model, plugin=plugin, device=self.device, shard_group=shard_group, replicate_group=replicate_group,
+                                 gradient_state=self.gradient_state, shard_group_is_world=(mesh is None))
+
+    def prepare_data_loader(self, data_loader: torch.utils.data.DataLoader, device_placement=None, slice_fn_for_dispatch=None):
+        if getattr(data_loader, "_is_accelerate_prepared", False):
+            if data_loader not in self._dataloaders:
+                self._dataloaders.append(data_loader)
+            return data_loader
+        if device_placement is None:
+            device_placement = self.device_placement
+        device_mesh = None
+        pc = self.parallelism_config
+        if pc is not None and pc.total_size > 1 and (pc.tp_enabled or pc.cp_enabled or pc.sp_enabled):
+            device_mesh = self.torch_device_mesh
+        prepared = prepare_data_loader(
+            data_loader, self.device, num_processes=self.num_processes, process_index=self.process_index,
+            split_batches=self.split_batches, put_on_device=device_placement, rng_types=self.rng_types.copy(),
+            dispatch_batches=self.dispatch_batches, even_batches=self.even_batches, slice_fn_for_dispatch=slice_fn_for_dispatch,
+            use_seedable_sampler=self.use_seedable_sampler, data_seed=self.dataloader_config.data_seed, non_blocking=self.non_blocking,
+            use_stateful_dataloader=self.use_stateful_dataloader, torch_device_mesh=device_mesh,
+        )
+        if pc is not None and pc.sp_enabled:
+            from .parallel.ulysses import UlyssesDataLoaderAdapter
+
+            prepared = UlyssesDataLoaderAdapter(prepared, self.torch_device_mesh["sp"], device=self.device)
+        self._dataloaders.append(prepared)
+        return prepared
+
+    def prepare_optimizer(self, optimizer: torch.optim.Optimizer, device_placement=None):
+        if getattr(optimizer, "_is_accelerate_prepared", False):
+            if optimizer not in self._optimizers:
+                self._optimizers.append(optimizer)
+            return optimizer
+        if device_placement is None:
+            device_placement = self.device_placement
+        scaler = None if self.is_fsdp2 and self.scaler is None else self.scaler
+        optimizer = AcceleratedOptimizer(optimizer, device_placement=device_placement, scaler=scaler)
+        self._optimizers.append(optimizer)
+        return optimizer
+
+    def prepare_scheduler(self, scheduler):
+        if getattr(scheduler, "_is_accelerate_prepared", False):
+            if scheduler not in self._schedulers:
+                self._schedulers.append(scheduler)
+            return scheduler
+        optimizer = self._optimizers
+        for opt in self._optimizers:
+            if getattr(scheduler, "optimizer", None) == opt.optimizer:
+                optimizer = opt
+                break
+        scheduler = AcceleratedScheduler(scheduler, optimizer, step_with_optimizer=self.step_scheduler_with_optimizer, split_batches=self.split_batches)
+        self._schedulers.append(scheduler)
+        return scheduler
+
+    def deepspeed_ulysses_dl_adapter(self, dl, model=None):
+        """Wrap a dataloader so each batch is sharded along the sequence over the ``sp`` axis."""
+        from .parallel.ulysses import UlyssesDataLoaderAdapter
+
+        return UlyssesDataLoaderAdapter(dl, self.torch_device_mesh["sp"], device=self.device)
+
+    # ================================================================== the training step
+    def backward(self, loss, **kwargs):
+        """``loss / gradient_accumulation_steps`` then backward (through the GradScaler for fp16)."""
+        learning_rate = kwargs.pop("learning_rate", None)
+        if self.distributed_type != DistributedType.DEEPSPEED or True:
+            loss = loss / self.gradient_accumulation_steps if self.gradient_accumulation_steps != 1 else loss
+        if learning_rate is not None and self.has_lomo_optimizer:
+            self.lomo_backward(loss, learning_rate)
+        elif self.scaler is not None:
+            self.scaler.scale(loss).backward(**kwargs)
+        else:
+            loss.backward(**kwargs)
+
+    def set_trigger(self):
+        """Raise the cross-rank flag (e.g. "stop training") checked by :meth:`check_trigger`."""
+        self.flag_tensor = torch.tensor(1, device=self.device)
+
+    def check_trigger(self):
+        """True on every rank if any rank called :meth:`set_trigger`; resets the flag."""
+        if self.flag_tensor is None:
+            self.flag_tensor = torch.tensor(0, device=self.device)
+        flag_tensor = self.reduce(self.flag_tensor)
+        if flag_tensor.item() >= 1:
+            self.flag_tensor = torch.tensor(0, device=self.device)
+            return True
+        return False
+
+    def unscale_gradients(self, optimizer=None):
+        """Unscale fp16 gradients (no-op unless a GradScaler is active)."""
+        if self.native_amp and self.mixed_precision == "fp16" and self.scaler is not None:
+            if optimizer is None:
+                optimizer = self._optimizers
+            elif not isinstance(optimizer, (tuple, list)):
+                optimizer = [optimizer]
+            for opt in optimizer:
+                while isinstance(opt, AcceleratedOptimizer):
+                    opt = opt.optimizer
+                self.scaler.unscale_(opt)
+
+    def clip_grad_norm_(self, parameters, max_norm, norm_type=2):
+        """Clip to ``max_norm`` and return the total norm (a device tensor; no host sync on the native path)."""
+        parameters = [p for p in parameters]
+        for model in self._models:
+            if hasattr(model, "clip_grad_norm_") and not isinstance(model, torch.nn.parallel.DistributedDataParallel):
+                mine = {id(p) for p in model.parameters()}
+                if parameters and all(id(p) in mine for p in parameters):
+                    self.unscale_gradients()
+                    return model.clip_grad_norm_(max_norm, norm_type)
+        self.unscale_gradients()
+        fused = [opt.optimizer for opt in self._optimizers if hasattr(opt.optimizer, "set_clip_coef")]
+        if norm_type == 2 and self.device.type == "cuda" and len(fused) == len(self._optimizers) and len(fused) > 0 and self.scaler is None:
+            from .optim import grad_global_norm
+
+            norm, coef, _ = grad_global_norm(parameters, max_norm)
+            for o in fused:
+                o.set_clip_coef(coef)  # applied inside the AdamW kernel: no extra pass over the gradients
+            return norm.reshape(())
+        return torch.nn.utils.clip_grad_norm_(parameters, max_norm, norm_type=norm_type)
+
+    def clip_grad_value_(self, parameters, clip_value):
+        if self.distributed_type in (DistributedType.DEEPSPEED, DistributedType.FSDP):
+            raise Exception("DeepSpeed and FSDP  do not support `clip_grad_value_`. Use `clip_grad_norm_` instead.")
+        self.unscale_gradients()
+        torch.nn.utils.clip_grad_value_(parameters, clip_value)
+
+    # ================================================================== collectives for metrics
+    def gather(self, tensor):
+        return gather(tensor)
+
+    def gather_for_metrics(self, input_data, use_gather_object: bool = False):
+        """Gather and drop the samples the last batch duplicated to keep ranks even."""
+        try:
+            recursively_apply(lambda x: x, input_data, error_on_other_type=True)
+            all_tensors = True
+        except TypeError:
+            all_tensors = False
+        use_gather_object = use_gather_object or not all_tensors
+        data = gather_object(input_data) if use_gather_object else self.gather(input_data)
+        try:
+            if self.gradient_state.end_of_dataloader:
+                if self.gradient_state.remainder == -1:
+                    logger.info("The used dataset had no length, returning gathered tensors. You should drop the remainder yourself.")
+                    return data
+                elif self.gradient_state.remainder > 0:
+                    def _adjust_samples(tensor):
+                        return tensor[: self.gradient_state.remainder]
+
+                    if use_gather_object:
+                        return _adjust_samples(data)
+                    return recursively_apply(_adjust_samples, data)
+                return data
+            return data
+        except Exception:
+            return data
+
+    def reduce(self, tensor, reduction="sum", scale=1.0):
+        return reduce(tensor, reduction, scale)
+
+    def pad_across_processes(self, tensor, dim=0, pad_index=0, pad_first=False):
+        return pad_across_processes(tensor, dim=dim, pad_index=pad_index, pad_first=pad_first)
+
+    # ================================================================== model utilities
+    def unwrap_model(self, model, keep_fp32_wrapper: bool = True, keep_torch_compile: bool = True):
+        return extract_model_from_parallel(model, keep_fp32_wrapper, keep_torch_compile)
+
+    def verify_device_map(self, model: torch.nn.Module) -> bool:
+        """True if ``model`` was dispatched over several devices with a ``device_map``."""
+        for m in model.modules():
+            if hasattr(m, "hf_device_map") and len(m.hf_device_map) > 1:
+                return True
+        return False
+
+    def lomo_backward(self, loss: torch.Tensor, learning_rate: float) -> None:
+        if learning_rate is None:
+            raise ValueError("A learning rate must be passed in order to call backward pass with LOMO optimizers.")
+        for optimizer in self._optimizers:
+            if hasattr(optimizer.optimizer, "fused_backward"):
+                optimizer.optimizer.fused_backward(loss, learning_rate)
+                return
+        raise ValueError("Backward pass not properly called on LOMO optimizers. Are you sure you passed a LOMO optimizer in `accelerator.prepare`?")
+
+    def get_state_dict(self, model, unwrap: bool = True):
+        """Full (un-sharded) state dict of ``model`` on every rank that needs it (CPU tensors under sharding)."""
+        if hasattr(model, "full_state_dict"):
+            return model.full_state_dict()
+        if unwrap:
+            model = self.unwrap_model(model)
+        return model.state_dict()
+
+    def save(self, obj, f, safe_serialization: bool = False):
+        save(obj, f, save_on_each_node=self.project_configuration.save_on_each_node, safe_serialization=safe_serialization)
+
+    def save_model(self, model: torch.nn.Module, save_directory: Union[str, os.PathLike], max_shard_size: Union[int, str] = "10GB",
+                   safe_serialization: bool = True):
+        """HF-style export: ``model.safetensors`` or ``model-0000X-of-0000Y.safetensors`` + index json."""
+        if os.path.isfile(save_directory):
+            logger.error(f"Provided path ({save_directory}) should be a directory, not a file")
+            return
+        os.makedirs(save_directory, exist_ok=True)
+        if any(getattr(m, "_hf_hook", None) is not None and getattr(m._hf_hook, "offload", False) for m in model.modules()):
+            from .utils.modeling import get_state_dict_offloaded_model
+
+            state_dict = get_state_dict_offloaded_model(model)
+        else:
+            if any(p.device == torch.device("meta") for p in model.parameters()):
+                raise RuntimeError("You can't save the model since some parameters are on the meta device.")
+            state_dict = self.get_state_dict(model)
+        if safe_serialization:
+            state_dict = clean_state_dict_for_safetensors(state_dict)
+        weights_name = SAFE_WEIGHTS_NAME if safe_serialization else WEIGHTS_NAME
+        filename_pattern = SAFE_WEIGHTS_PATTERN_NAME if safe_serialization else WEIGHTS_PATTERN_NAME
+        from .utils.modeling import shard_checkpoint
+
+        shards, index = shard_checkpoint(state_dict, max_shard_size=max_shard_size, weights_name=weights_name)
+        # remove stale shard files of an earlier, differently sharded save
+        for filename in os.listdir(save_directory):
+            full_filename = os.path.join(save_directory, filename)
+            weights_no_suffix = weights_name.replace(".bin", "").replace(".safetensors", "")
+            filename_no_suffix = filename.replace(".bin", "").replace(".safetensors", "")
+            reg = re.compile(r"(.*?)-\d{5}-of-\d{5}")
+            if filename.startswith(weights_no_suffix) and os.path.isfile(full_filename) and filename not in shards.keys() and reg.fullmatch(filename_no_suffix) is not None and PartialState().is_main_process:
+                os.remove(full_filename)
+        for shard_file, shard in shards.items():
+            self.save(shard, os.path.join(save_directory, shard_file), safe_serialization=safe_serialization)
+        if index is None:
+            logger.info(f"Model weights saved in {os.path.join(save_directory, weights_name)}")
+        else:
+            save_index_file = SAFE_WEIGHTS_INDEX_NAME if safe_serialization else WEIGHTS_INDEX_NAME
+            save_index_file = os.path.join(save_directory, save_index_file)
+            if self.is_main_process:
+                with open(save_index_file, "w", encoding="utf-8") as f:
+                    f.write(json.dumps(index, indent=2, sort_keys=True) + "\n")
+            logger.info(f"The model is bigger than the maximum size per checkpoint ({max_shard_size}) and is going to be split in {len(shards)} checkpoint shards. You can find where each parameters has been saved in the index located at {save_index_file}.")
+
+    # ================================================================== checkpoint hooks
+    def register_save_state_pre_hook(self, hook: Callable[..., None]):
+        """``hook(models, weights, output_dir)`` runs inside ``save_state`` before the files are written."""
+        handle = torch.utils.hooks.RemovableHandle(self._save_model_state_pre_hook)
+        self._save_model_state_pre_hook[handle.id] = hook
+        return handle
+
+    def register_load_state_pre_hook(self, hook: Callable[..., None]):
+        """``hook(models, input_dir)`` runs inside ``load_state`` before the files are read."""
+        handle = torch.utils.hooks.RemovableHandle(self._load_model_state_pre_hook)
+        self._load_model_state_pre_hook[handle.id] = hook
+        return handle
+
+    def register_for_checkpointing(self, *objects):
+        """Track extra objects (with ``state_dict`` / ``load_state_dict``) in ``save_state`` / ``load_state``."""
+        invalid_objects = []
+        for obj in objects:
+            if not hasattr(obj, "state_dict") or not hasattr(obj, "load_state_dict"):
+                invalid_objects.append(obj)
+        if len(invalid_objects) > 0:
+            err = "All `objects` must include a `state_dict` and `load_state_dict` function to be stored. The following inputs are invalid:"
+            for index, obj in enumerate(invalid_objects):
+                err += f"\n\t- Item at index {index}, `{get_pretty_name(obj)}`"
+            raise ValueError(err)
+        self._custom_objects.extend(objects)
+
+    # ================================================================== save_state / load_state
+    def save_state(self, output_dir: Optional[str] = None, safe_serialization: bool = True, **save_model_func_kwargs):
+        """Checkpoint everything ``prepare`` saw (plus registered objects and RNG state) under ``output_dir``."""
+        if self.project_configuration.automatic_checkpoint_naming:
+            output_dir = os.path.join(self.project_dir, "checkpoints")
+        os.makedirs(output_dir, exist_ok=True)
+        if self.project_configuration.automatic_checkpoint_naming:
+            folders = [os.path.join(output_dir, folder) for folder in os.listdir(output_dir)]
+            if self.project_configuration.total_limit is not None and (len(folders) + 1 > self.project_configuration.total_limit) and self.is_main_process:
+                def _inner(folder):
+                    return list(map(int, re.findall(r"[\/]?([0-9]+)(?=[^\/]*$)", folder)))[0]
+
+                folders.sort(key=_inner)
+                logger.warning(f"Deleting {len(folders) + 1 - self.project_configuration.total_limit} checkpoints to make room for new checkpoint.")
+                for folder in folders[: len(folders) + 1 - self.project_configuration.total_limit]:
+                    shutil.rmtree(folder, ignore_errors=True)
+            output_dir = os.path.join(output_dir, f"checkpoint_{self.save_iteration}")
+            if os.path.exists(output_dir):
+                raise ValueError(f"Checkpoint directory {output_dir} ({self.save_iteration}) already exists. Please manually override `self.save_iteration` with what iteration to start with.")
+            self.wait_for_everyone()
+        os.makedirs(output_dir, exist_ok=True)
+        logger.info(f"Saving current state to {output_dir}")
+
+        weights = []
+        sharded_models = []
+        for i, model in enumerate(self._models):
+            if hasattr(model, "save_sharded_state"):
+                model.save_sharded_state(output_dir, i, self.state.fsdp_plugin)
+                sharded_models.append(i)
+                logger.info(f"Sharded model saved to output dir {output_dir}")
+            else:
+                weights.append(self.get_state_dict(model, unwrap=False))
+        optimizers = []
+        for i, opt in enumerate(self._optimizers):
+            engine = getattr(opt, "_engine", None)
+            if engine is not None and hasattr(engine, "save_sharded_optimizer"):
+                engine.save_sharded_optimizer(opt, output_dir, i, self.state.fsdp_plugin)
+                logger.info(f"Sharded optimizer state saved to output dir {output_dir}")
+            else:
+                optimizers.append(opt)
+        schedulers = []
+        for scheduler in self._schedulers:
+            schedulers.append(scheduler)
+        dataloaders = self._dataloaders
+        for hook in self._save_model_state_pre_hook.values():
+            hook(self._models, weights, output_dir)
+        save_location = save_accelerator_state(
+            output_dir, weights, optimizers, schedulers, dataloaders, self.state.process_index, self.step, self.scaler,
+            save_on_each_node=self.project_configuration.save_on_each_node, safe_serialization=safe_serialization,
+        )
+        for i, obj in enumerate(self._custom_objects):
+            save_custom_state(obj, output_dir, i, save_on_each_node=self.project_configuration.save_on_each_node)
+        self.project_configuration.iteration += 1
+        return save_location
+
+    def load_state(self, input_dir: Optional[str] = None, load_kwargs: Optional[dict] = None, **load_model_func_kwargs):
+        """Restore what :meth:`save_state` wrote (latest ``checkpoint_N`` under automatic naming)."""
+        if input_dir is not None:
+            input_dir = os.path.expanduser(input_dir)
+            if not os.path.isdir(input_dir):
+                raise ValueError(f"Tried to find {input_dir} but folder does not exist")
+        elif self.project_configuration.automatic_checkpoint_naming:
+            input_dir = os.path.join(self.project_dir, "checkpoints")
+            folders = [os.path.join(input_dir, folder) for folder in os.listdir(input_dir)]
+
+            def _inner(folder):
+                return list(map(int, re.findall(r"[\/]?([0-9]+)(?=[^\/]*$)", folder)))[0]
+
+            folders.sort(key=_inner)
+            input_dir = folders[-1]
+        else:
+            raise ValueError("No input_dir provided and automatic checkpoint naming is disabled.")
+        logger.info(f"Loading states from {input_dir}")
+
+        models = []
+        for i, model in enumerate(self._models):
+            if hasattr(model, "load_sharded_state"):
+                model.load_sharded_state(input_dir, i, self.state.fsdp_plugin)
+                logger.info(f"Sharded model loaded from input dir {input_dir}")
+            else:
+                models.append(model)
+        optimizers = []
+        for i, opt in enumerate(self._optimizers):
+            engine = getattr(opt, "_engine", None)
+            if engine is not None and hasattr(engine, "load_sharded_optimizer"):
+                engine.load_sharded_optimizer(opt, input_dir, i, self.state.fsdp_plugin)
+            else:
+                optimizers.append(opt)
+        schedulers = list(self._schedulers)
+        dataloaders = self._dataloaders
+        for hook in self._load_model_state_pre_hook.values():
+            hook(models, input_dir)
+        map_location = load_model_func_kwargs.pop("map_location", None)
+        if map_location is None:
+            if self.num_processes > 1 and self.multi_device and self.distributed_type != DistributedType.MULTI_CPU:
+                map_location = "on_device"
+            else:
+                map_location = "cpu"
+        override_attributes = load_accelerator_state(
+            input_dir, models, optimizers, schedulers, dataloaders, self.state.process_index, self.scaler, map_location,
+            load_kwargs, **load_model_func_kwargs,
+        )
+        if "step" in override_attributes:
+            self.step = override_attributes["step"]
+        custom_checkpoints = [f for f in os.listdir(input_dir) if re.search(r"^custom_checkpoint_\d+\.pkl$", f) is not None]
+        if len(custom_checkpoints) != len(self._custom_objects):
+            err = f"Number of custom checkpoints in folder {input_dir} does not match the number of registered objects:"
+            err += f"\n\tFound checkpoints: {len(custom_checkpoints)}"
+            err += f"\n\tRegistered objects: {len(self._custom_objects)}\n"
+            err += "Please make sure to only load checkpoints from folders that were created with the same set of registered objects,"
+            err += "or avoid using `custom_checkpoint` in the filename for files in that same directory and load them in manually."
+            raise RuntimeError(err)
+        logger.info(f"Loading in {len(custom_checkpoints)} custom states")
+        for index, obj in enumerate(self._custom_objects):
+            load_custom_state(obj, input_dir, index)
+
+    def free_memory(self, *objects):
+        """Drop every reference the accelerator keeps and empty the device cache."""
+        for model in self._models:
+            if hasattr(model, "release"):
+                model.release()
+        if hasattr(self, "deepspeed_engine_wrapped"):
+            self.deepspeed_engine_wrapped = None
+        objects = release_memory(*objects)
+        self._schedulers = []
+        self._optimizers = []
+        self._models = []
+        self._dataloaders = []
+        self.step = 0
+        return objects
+
+    def clear(self, *objects):
+        return self.free_memory(*objects)
+
+    def _get_named_parameters(self, *args, drop_refs=False):
+        named_parameters = {}
+        for obj in args:
+            if isinstance(obj, torch.nn.Module):
+                obj = extract_model_from_parallel(obj)
+                named_parameters.update({n: p for n, p in obj.named_parameters()})
+        return named_parameters
+
+    def _get_devices(self, *args):
+        model_device = optimizer_device = None
+        for obj in args:
+            if isinstance(obj, torch.nn.Module):
+                for param in obj.parameters():
+                    model_device = param.device
+                    break
+            if isinstance(obj, torch.optim.Optimizer):
+                for param_group in obj.param_groups:
+                    if len(param_group["params"]) > 0:
+                        optimizer_device = param_group["params"][0].device
+                        break
+        return (model_device, optimizer_device)
+
+    # ================================================================== contexts
+    def _get_autocast_context(self, autocast_handler: AutocastKwargs = None):
+        if autocast_handler is None:
+            autocast_handler = self.autocast_handler
+        kwargs = autocast_handler.to_kwargs() if autocast_handler is not None else {}
+        dtype = self._mixed_precision_dtype()
+        if not self.native_amp or dtype is None:
+            return contextlib.nullcontext()
+        device_type = "cuda" if self.device.type == "cuda" else "cpu"
+        if device_type == "cpu" and dtype == torch.float16:
+            dtype = torch.bfloat16
+        return torch.autocast(device_type=device_type, dtype=dtype, **kwargs)
+
+    @contextmanager
+    def autocast(self, autocast_handler: AutocastKwargs = None):
+        """Run the block under the accelerator's mixed-precision autocast."""
+        ctx = self._get_autocast_context(autocast_handler)
+        ctx.__enter__()
+        try:
+            yield
+        finally:
+            ctx.__exit__(*sys.exc_info())
+
+    @contextmanager
+    def maybe_context_parallel(self, buffers=None, buffer_seq_dims=None, no_restore_buffers=None):
+        """Shard ``buffers`` along their sequence dims over the ``cp`` axis for the duration of the step."""
+        pc = self.parallelism_config
+        if pc is None or not pc.cp_enabled:
+            logger.warning_once("Context parallelism is not enabled: `maybe_context_parallel` is a no-op.")
+            yield
+            return
+        from .parallel.context_parallel import context_parallel_buffers
+
+        with context_parallel_buffers(self.torch_device_mesh["cp"], buffers or [], buffer_seq_dims or [], no_restore_buffers or set()):
+            yield
+
+    @contextmanager
+    def profile(self, profile_handler: Optional[ProfileKwargs] = None):
+        """``torch.profiler`` context; on exit writes ``profile_{rank}.json`` under ``output_trace_dir``."""
+        profile_handler = profile_handler or self.profile_handler or ProfileKwargs()
+        with profile_handler.build() as profiler:
+            yield profiler
+        if profile_handler.output_trace_dir is None:
+            return
+        os.makedirs(profile_handler.output_trace_dir, exist_ok=True)
+        profiler.export_chrome_trace(os.path.join(profile_handler.output_trace_dir, PROFILE_PATTERN_NAME.format(suffix=self.process_index)))
+        self.wait_for_everyone()
+
+    def skip_first_batches(self, dataloader, num_batches: int = 0):
+        return skip_first_batches(dataloader, num_batches=num_batches)
+
+    # ================================================================== trackers
+    def init_trackers(self, project_name: str, config: Optional[dict] = None, init_kwargs: Optional[dict] = None):
+        from .tracking import LOGGER_TYPE_TO_CLASS, GeneralTracker
+
+        init_kwargs = init_kwargs or {}
+        for tracker in self.log_with:
+            if issubclass(type(tracker), GeneralTracker):
+                self.trackers.append(tracker)
+            else:
+                tracker_init = LOGGER_TYPE_TO_CLASS[str(tracker)]
+                if tracker_init.requires_logging_directory:
+                    self.trackers.append(tracker_init(project_name, self.logging_dir, **init_kwargs.get(str(tracker), {})))
+                else:
+                    self.trackers.append(tracker_init(project_name, **init_kwargs.get(str(tracker), {})))
+        for tracker in self.trackers:
+            tracker.start()
+        if config is not None:
+            for tracker in self.trackers:
+                tracker.store_init_configuration(config)
+
+    def get_tracker(self, name: str, unwrap: bool = False):
+        from .tracking import GeneralTracker
+
+        if len(self.trackers) > 0:
+            for tracker in self.trackers:
+                if tracker.name == name:
+                    return tracker.tracker if unwrap else tracker
+            raise ValueError(f"{name} is not an available tracker stored inside the `Accelerator`.")
+        return GeneralTracker(_blank=True)
+
+    def log(self, values: dict, step: Optional[int] = None, log_kwargs: Optional[dict] = None):
+        log_kwargs = log_kwargs or {}
+        for tracker in self.trackers:
+            tracker.log(values, step=step, **log_kwargs.get(tracker.name, {}))
+
+    def end_training(self):
+        """Finish trackers and tear down the process group."""
+        for tracker in self.trackers:
+            tracker.finish()
+        self.state.destroy_process_group()
+
+    def __deepcopy__(self, memo):
+        logger.info("Deep copying the `Accelerator` object, note that this will point to the same original object.")
+        return self
+
+
+def get_pretty_name(obj):
+    from .utils.other import get_pretty_name as _g
+
+    return _g(obj)

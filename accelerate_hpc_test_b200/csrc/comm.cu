@@ -1,0 +1,381 @@
+// Peer-memory collectives over NVLink 5 / NVSwitch, issued from inside the kernels (no NCCL on the
+// data path).  Every rank maps every peer's symmetric buffer (runtime.cu: CUDA IPC); `peers[p]` is
+// the base address of rank p's buffer as seen from this GPU.  Ranks order their accesses with
+// monotonically increasing epochs written into each other's signal pads with st.release.sys and
+// polled with ld.acquire.sys.
+//
+// SURVEY.md §2.6 collectives C1 (DDP all-reduce, fused with cast+scale), C2 (FSDP2 all-gather), C3
+// (FSDP2 reduce-scatter, fused here with the sharded AdamW update), C6 (Ulysses all-to-all).  In the
+// reference these are ncclAllReduce / ncclAllGather / ncclReduceScatter / all_to_all_single issued by
+// torch DDP / FSDP2 / DeepSpeed (reference src/accelerate/accelerator.py:1865, utils/fsdp_utils.py:689).
+//
+// Signal pad layout (start of every symmetric buffer): uint32 flags[NUM_CHANNELS][MAX_RANKS];
+// flags[c][s] on rank d is written only by rank s.  All waits are bounded (device-side timeout ->
+// trap with a diagnostic) so a missing peer turns into an error, never into a hung GPU.
+#include "common.cuh"
+
+namespace b200 {
+
+static constexpr int MAX_RANKS = 8;
+static constexpr int NUM_CHANNELS = 2048;
+__device__ unsigned long long g_wait_timeout_ns = 60ull * 1000ull * 1000ull * 1000ull;
+
+struct Peers {
+  uint8_t* base[MAX_RANKS];
+};
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__device__ __forceinline__ uint32_t* flag_ptr(uint8_t* base, int channel, int src) {
+  return reinterpret_cast<uint32_t*>(base) + channel * MAX_RANKS + src;
+}
+
+// tell every peer (and myself) that `rank` reached `epoch` on `channel`; one thread per destination
+__device__ __forceinline__ void signal_all(const Peers& peers, int rank, int world, int channel, uint32_t epoch) {
+  if (threadIdx.x < world) st_release_sys(flag_ptr(peers.base[threadIdx.x], channel, rank), epoch);
+}
+
+// wait until every rank has reached `epoch` on `channel` (reads only my own pad); whole CTA syncs after
+__device__ __forceinline__ void wait_all(const Peers& peers, int rank, int world, int channel, uint32_t epoch) {
+  if (threadIdx.x < world) {
+    const uint32_t* f = flag_ptr(peers.base[rank], channel, threadIdx.x);
+    const unsigned long long t0 = global_ns();
+    while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+      __nanosleep(64);
+      if (global_ns() - t0 > g_wait_timeout_ns) {
+        printf("b200 comm: rank %d timed out waiting for rank %d on channel %d (epoch %u, saw %u)\n", rank,
+               (int)threadIdx.x, channel, epoch, ld_relaxed_sys(f));
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// last-CTA election on a local counter; returns true in exactly one CTA, after all CTAs arrived
+__device__ __forceinline__ bool last_cta(uint32_t* counter) {
+  __shared__ uint32_t is_last;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t prev = atomicAdd(counter, 1u);
+    is_last = (prev == gridDim.x - 1) ? 1u : 0u;
+    if (is_last) *counter = 0;  // re-arm for the next launch
+  }
+  __syncthreads();
+  return is_last != 0;
+}
+
+__device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.relaxed.sys.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+
+__device__ __forceinline__ void accum_bf16x8(float (&acc)[8], const uint4& v) {
+  float2 t;
+  t = bf2_to_f2(v.x); acc[0] += t.x; acc[1] += t.y;
+  t = bf2_to_f2(v.y); acc[2] += t.x; acc[3] += t.y;
+  t = bf2_to_f2(v.z); acc[4] += t.x; acc[5] += t.y;
+  t = bf2_to_f2(v.w); acc[6] += t.x; acc[7] += t.y;
+}
+
+// ------------------------------------------------------------------------------ barrier
+__global__ void barrier_kernel(Peers peers, int rank, int world, int channel, uint32_t epoch) {
+  signal_all(peers, rank, world, channel, epoch);
+  wait_all(peers, rank, world, channel, epoch);
+}
+
+// ------------------------------------------------------------------------------ all-gather (pull)
+// out[p * shard_bytes ...] = peer p's bytes at [shard_off, shard_off + shard_bytes).  If wait_channel
+// >= 0 the shard of peer p is read only once flags[wait_channel][p] >= wait_epoch (the owner
+// publishes that epoch when its shard holds the parameter version this gather needs).
+__global__ void __launch_bounds__(512)
+allgather_pull_kernel(Peers peers, int rank, int world, long long shard_off, long long shard_bytes,
+                      uint8_t* __restrict__ out, int wait_channel, uint32_t wait_epoch) {
+  if (wait_channel >= 0) wait_all(peers, rank, world, wait_channel, wait_epoch);
+  const long long nvec = shard_bytes >> 4;
+  const long long total = nvec * world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  // start with my right-hand neighbour so the 8 ranks spread their reads over distinct peers
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int slot = (int)(i / nvec);
+    const long long j = i - (long long)slot * nvec;
+    const int p = (rank + 1 + slot) % world;
+    const uint4 v = ld_peer_v4(peers.base[p] + shard_off + (j << 4));
+    *reinterpret_cast<uint4*>(out + (long long)p * shard_bytes + (j << 4)) = v;
+  }
+}
+
+// ------------------------------------------------------------------------------ reduce-scatter + AdamW
+struct AdamArgs {
+  float lr, beta1, beta2, eps, weight_decay, bias_c1, bias_c2, grad_scale;
+};
+
+// Rank r owns elements [r*n, (r+1)*n) of every rank's flat bf16 gradient (at byte offset grad_off of
+// the symmetric buffers).  It sums the 8 copies over NVLink, applies AdamW to its fp32 master /
+// moments and writes the new bf16 parameter shard (symmetric memory at param_off, where peers
+// all-gather it from).  do_adam == 0: only the reduced fp32 gradient shard is written (grad_out).
+__global__ void __launch_bounds__(512)
+reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off, long long n,
+                            float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
+                            long long param_off, float* __restrict__ grad_out, AdamArgs a, int do_adam,
+                            const float* __restrict__ clip_coef, int ch_arrive, int ch_done, uint32_t epoch,
+                            uint32_t* __restrict__ counter) {
+  // (1) everybody's gradients are complete
+  if (blockIdx.x == 0) signal_all(peers, rank, world, ch_arrive, epoch);
+  wait_all(peers, rank, world, ch_arrive, epoch);
+
+  const long long nvec = n >> 3;  // 8 bf16 per 16 B
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const float gs = a.grad_scale * (clip_coef ? *clip_coef : 1.f);
+  __nv_bfloat16* shard = reinterpret_cast<__nv_bfloat16*>(peers.base[rank] + param_off);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    uint4 vals[MAX_RANKS];
+#pragma unroll
+    for (int s = 0; s < MAX_RANKS; ++s) {
+      if (s < world) {
+        const int p = (rank + s) % world;
+        vals[s] = ld_peer_v4(peers.base[p] + grad_off + (((long long)rank * nvec + i) << 4));
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < MAX_RANKS; ++s)
+      if (s < world) accum_bf16x8(acc, vals[s]);
+    const long long e0 = i << 3;
+    if (do_adam) {
+      float pw[8];
+      const float4 m0 = *reinterpret_cast<const float4*>(m + e0), m1 = *reinterpret_cast<const float4*>(m + e0 + 4);
+      const float4 v0 = *reinterpret_cast<const float4*>(v + e0), v1 = *reinterpret_cast<const float4*>(v + e0 + 4);
+      const float4 p0 = *reinterpret_cast<const float4*>(master + e0), p1 = *reinterpret_cast<const float4*>(master + e0 + 4);
+      float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+      float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+      float pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float g = acc[k] * gs;
+        mm[k] = mm[k] * a.beta1 + (1.f - a.beta1) * g;
+        vv[k] = vv[k] * a.beta2 + (1.f - a.beta2) * g * g;
+        float p = pp[k] * (1.f - a.lr * a.weight_decay);
+        p -= (a.lr / a.bias_c1) * (mm[k] / (sqrtf(vv[k] / a.bias_c2) + a.eps));
+        pw[k] = p;
+      }
+      *reinterpret_cast<float4*>(m + e0) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+      *reinterpret_cast<float4*>(m + e0 + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
+      *reinterpret_cast<float4*>(v + e0) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+      *reinterpret_cast<float4*>(v + e0 + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+      *reinterpret_cast<float4*>(master + e0) = make_float4(pw[0], pw[1], pw[2], pw[3]);
+      *reinterpret_cast<float4*>(master + e0 + 4) = make_float4(pw[4], pw[5], pw[6], pw[7]);
+      uint4 o;
+      o.x = f2_to_bf2(pw[0], pw[1]); o.y = f2_to_bf2(pw[2], pw[3]);
+      o.z = f2_to_bf2(pw[4], pw[5]); o.w = f2_to_bf2(pw[6], pw[7]);
+      *reinterpret_cast<uint4*>(shard + e0) = o;
+    } else {
+      *reinterpret_cast<float4*>(grad_out + e0) = make_float4(acc[0] * gs, acc[1] * gs, acc[2] * gs, acc[3] * gs);
+      *reinterpret_cast<float4*>(grad_out + e0 + 4) = make_float4(acc[4] * gs, acc[5] * gs, acc[6] * gs, acc[7] * gs);
+    }
+  }
+  // (2) my shard is updated and I no longer read anybody's gradients; when every peer says the same,
+  //     my own gradient buffer is free again, which is what kernel completion promises the stream.
+  if (last_cta(counter)) {
+    __threadfence_system();
+    signal_all(peers, rank, world, ch_done, epoch);
+    wait_all(peers, rank, world, ch_done, epoch);
+  }
+}
+
+// ------------------------------------------------------------------------------ all-reduce (two-shot, in place)
+// buf (at byte offset `off` of every rank's symmetric buffer) holds n elements.  Rank r reduces
+// slice r of all ranks, scales it, and stores the result back into slice r of all ranks.
+template <typename T>
+__global__ void __launch_bounds__(512)
+allreduce_kernel(Peers peers, int rank, int world, long long off, long long n, float scale, int ch_arrive,
+                 int ch_done, uint32_t epoch, uint32_t* __restrict__ counter) {
+  if (blockIdx.x == 0) signal_all(peers, rank, world, ch_arrive, epoch);
+  wait_all(peers, rank, world, ch_arrive, epoch);
+  constexpr int EPV = 16 / sizeof(T);
+  const long long nvec_total = n / EPV;  // n is padded to world * EPV by the host
+  const long long nvec = nvec_total / world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    const long long byte = off + (((long long)rank * nvec + i) << 4);
+    uint4 vals[MAX_RANKS];
+#pragma unroll
+    for (int s = 0; s < MAX_RANKS; ++s)
+      if (s < world) vals[s] = ld_peer_v4(peers.base[(rank + s) % world] + byte);
+    uint4 o;
+    if (sizeof(T) == 2) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int s = 0; s < MAX_RANKS; ++s)
+        if (s < world) accum_bf16x8(acc, vals[s]);
+      o.x = f2_to_bf2(acc[0] * scale, acc[1] * scale); o.y = f2_to_bf2(acc[2] * scale, acc[3] * scale);
+      o.z = f2_to_bf2(acc[4] * scale, acc[5] * scale); o.w = f2_to_bf2(acc[6] * scale, acc[7] * scale);
+    } else {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int s = 0; s < MAX_RANKS; ++s)
+        if (s < world) {
+          acc[0] += __uint_as_float(vals[s].x); acc[1] += __uint_as_float(vals[s].y);
+          acc[2] += __uint_as_float(vals[s].z); acc[3] += __uint_as_float(vals[s].w);
+        }
+      o.x = __float_as_uint(acc[0] * scale); o.y = __float_as_uint(acc[1] * scale);
+      o.z = __float_as_uint(acc[2] * scale); o.w = __float_as_uint(acc[3] * scale);
+    }
+#pragma unroll
+    for (int s = 0; s < MAX_RANKS; ++s)
+      if (s < world) {
+        uint8_t* dst = peers.base[(rank + s) % world] + byte;
+        asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(o.x), "r"(o.y),
+                     "r"(o.z), "r"(o.w)
+                     : "memory");
+      }
+  }
+  if (last_cta(counter)) {
+    __threadfence_system();
+    signal_all(peers, rank, world, ch_done, epoch);
+    wait_all(peers, rank, world, ch_done, epoch);  // every slice of my buffer now holds the result
+  }
+}
+
+// ------------------------------------------------------------------------------ all-to-all (pull)
+// Every rank holds `world` send blocks of block_bytes each at send_off (block d is destined to rank
+// d).  Rank r pulls block r of every peer p into out[p * block_bytes].
+__global__ void __launch_bounds__(512)
+alltoall_pull_kernel(Peers peers, int rank, int world, long long send_off, long long block_bytes,
+                     uint8_t* __restrict__ out, int ch_arrive, int ch_done, uint32_t epoch,
+                     uint32_t* __restrict__ counter) {
+  if (blockIdx.x == 0) signal_all(peers, rank, world, ch_arrive, epoch);
+  wait_all(peers, rank, world, ch_arrive, epoch);
+  const long long nvec = block_bytes >> 4;
+  const long long total = nvec * world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int slot = (int)(i / nvec);
+    const long long j = i - (long long)slot * nvec;
+    const int p = (rank + 1 + slot) % world;
+    const uint4 v = ld_peer_v4(peers.base[p] + send_off + (long long)rank * block_bytes + (j << 4));
+    *reinterpret_cast<uint4*>(out + (long long)p * block_bytes + (j << 4)) = v;
+  }
+  if (last_cta(counter)) {
+    __threadfence_system();
+    signal_all(peers, rank, world, ch_done, epoch);
+    wait_all(peers, rank, world, ch_done, epoch);  // my send blocks may be overwritten after this kernel
+  }
+}
+
+static inline int load_peers(Peers& P, const void* const* peer_ptrs, int world) {
+  if (world < 1 || world > MAX_RANKS) return B200_ERR_UNSUPPORTED;
+  for (int i = 0; i < MAX_RANKS; ++i) P.base[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
+  return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+B200_API int b200_comm_limits(int* max_ranks, int* num_channels, long long* signal_pad_bytes) {
+  if (max_ranks) *max_ranks = MAX_RANKS;
+  if (num_channels) *num_channels = NUM_CHANNELS;
+  if (signal_pad_bytes) *signal_pad_bytes = (long long)NUM_CHANNELS * MAX_RANKS * 4;
+  return 0;
+}
+
+B200_API int b200_comm_set_timeout_ms(long long ms) {
+  unsigned long long ns = (unsigned long long)ms * 1000000ull;
+  B200_CUDA(cudaMemcpyToSymbol(g_wait_timeout_ns, &ns, sizeof(ns)));
+  return 0;
+}
+
+// peer_ptrs: HOST array of `world` device pointers (base of each rank's symmetric buffer)
+B200_API int b200_barrier_all(const void* const* peer_ptrs, int rank, int world, int channel, unsigned epoch,
+                              void* stream) {
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(P, rank, world, channel, epoch);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+B200_API int b200_allgather_pull(const void* const* peer_ptrs, int rank, int world, long long shard_off,
+                                 long long shard_bytes, void* out, int wait_channel, unsigned wait_epoch,
+                                 int ctas, void* stream) {
+  if (shard_bytes % 16 || shard_off % 16) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  if (ctas <= 0) ctas = 32;
+  allgather_pull_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(P, rank, world, shard_off, shard_bytes,
+                                                                (uint8_t*)out, wait_channel, wait_epoch);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// n = elements in MY shard (multiple of 8); every rank's flat gradient holds world * n bf16 elements
+B200_API int b200_reduce_scatter_adamw(const void* const* peer_ptrs, int rank, int world, long long grad_off,
+                                       long long n, void* master, void* m, void* v, long long param_off,
+                                       void* grad_out, float lr, float beta1, float beta2, float eps,
+                                       float weight_decay, int step, float grad_scale, int do_adam,
+                                       const void* clip_coef, int ch_arrive, int ch_done, unsigned epoch,
+                                       void* counter, int ctas, void* stream) {
+  if (n % 8 || grad_off % 16 || param_off % 16) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  AdamArgs a{lr, beta1, beta2, eps, weight_decay, 1.f - powf(beta1, (float)step), 1.f - powf(beta2, (float)step),
+             grad_scale};
+  if (ctas <= 0) ctas = 32;
+  reduce_scatter_adamw_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(
+      P, rank, world, grad_off, n, (float*)master, (float*)m, (float*)v, param_off, (float*)grad_out, a, do_adam,
+      (const float*)clip_coef, ch_arrive, ch_done, epoch, (uint32_t*)counter);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// in-place all-reduce of n elements (bf16 if is_bf16 else fp32) at byte offset `off`; n % (world * 16 / esize) == 0
+B200_API int b200_allreduce(const void* const* peer_ptrs, int rank, int world, long long off, long long n,
+                            int is_bf16, float scale, int ch_arrive, int ch_done, unsigned epoch, void* counter,
+                            int ctas, void* stream) {
+  const int epv = is_bf16 ? 8 : 4;
+  if (off % 16 || n % ((long long)world * epv)) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  if (ctas <= 0) ctas = 32;
+  if (is_bf16)
+    allreduce_kernel<__nv_bfloat16><<<ctas, 512, 0, (cudaStream_t)stream>>>(P, rank, world, off, n, scale, ch_arrive,
+                                                                         ch_done, epoch, (uint32_t*)counter);
+  else
+    allreduce_kernel<float><<<ctas, 512, 0, (cudaStream_t)stream>>>(P, rank, world, off, n, scale, ch_arrive, ch_done,
+                                                                  epoch, (uint32_t*)counter);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+B200_API int b200_alltoall_pull(const void* const* peer_ptrs, int rank, int world, long long send_off,
+                                long long block_bytes, void* out, int ch_arrive, int ch_done, unsigned epoch,
+                                void* counter, int ctas, void* stream) {
+  if (block_bytes % 16 || send_off % 16) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  if (ctas <= 0) ctas = 32;
+  alltoall_pull_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(P, rank, world, send_off, block_bytes, (uint8_t*)out,
+                                                               ch_arrive, ch_done, epoch, (uint32_t*)counter);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}

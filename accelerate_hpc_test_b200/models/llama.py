@@ -1,0 +1,298 @@
+"""Native Llama-3 family decoder built directly on the sm_100a kernels.
+
+Design (B200-first, not a translation of transformers' ``LlamaForCausalLM``):
+
+* Q/K/V and gate/up projections are stored *fused* (one GEMM each), RoPE is applied in place on
+  the fused QKV GEMM output, attention reads Q/K/V straight out of that buffer through TMA
+  descriptors, and the residual add is fused into the following RMSNorm.
+* The LM head and the loss are one op (chunked GEMM + cross-entropy + both gradient GEMMs), so
+  ``[tokens, vocab]`` logits never exist.  The reference instead materialises logits and then
+  up-casts them to fp32 (``convert_outputs_to_fp32``, reference src/accelerate/accelerator.py:1797-1802).
+* Parameters are bf16; fp32 master weights live in the fused optimizer (:mod:`..optim`).
+
+The BASELINE.json configs name Llama-3-8B (hidden 4096, FFN 14336, 32 layers, 32/8 heads,
+head_dim 128, vocab 128256, rope theta 5e5, eps 1e-5).  ``hf_state_dict`` /
+``load_hf_state_dict`` convert to and from the transformers parameter naming so checkpoints
+interchange.
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from ..ops import functional as F
+
+
+@dataclass
+class LlamaConfig:
+    vocab_size: int = 128256
+    hidden_size: int = 4096
+    intermediate_size: int = 14336
+    num_hidden_layers: int = 32
+    num_attention_heads: int = 32
+    num_key_value_heads: int = 8
+    head_dim: int = 128
+    rope_theta: float = 500000.0
+    rms_norm_eps: float = 1e-5
+    max_position_embeddings: int = 8192
+    tie_word_embeddings: bool = False
+    initializer_range: float = 0.02
+    loss_chunk_tokens: int = 4096
+    model_type: str = "llama"
+
+    @classmethod
+    def llama3_8b(cls, **kw) -> "LlamaConfig":
+        return cls(**kw)
+
+    @classmethod
+    def llama3_1b(cls, **kw) -> "LlamaConfig":
+        base = dict(hidden_size=2048, intermediate_size=8192, num_hidden_layers=16, num_attention_heads=16,
+                    num_key_value_heads=8)
+        base.update(kw)
+        return cls(**base)
+
+    @classmethod
+    def tiny(cls, **kw) -> "LlamaConfig":
+        base = dict(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                    num_attention_heads=2, num_key_value_heads=1, max_position_embeddings=512, loss_chunk_tokens=256)
+        base.update(kw)
+        return cls(**base)
+
+    @property
+    def qkv_width(self) -> int:
+        return (self.num_attention_heads + 2 * self.num_key_value_heads) * self.head_dim
+
+    def num_parameters(self) -> int:
+        h, i = self.hidden_size, self.intermediate_size
+        per_layer = h * self.qkv_width + self.num_attention_heads * self.head_dim * h + 3 * h * i + 2 * h
+        head = 0 if self.tie_word_embeddings else self.vocab_size * h
+        return self.num_hidden_layers * per_layer + self.vocab_size * h + head + h
+
+    def flops_per_token(self, seq_len: int) -> float:
+        """Training FLOPs per token (fwd + bwd = 3x fwd), causal attention counted at half."""
+        h = self.hidden_size
+        matmul_params = self.num_parameters() - (0 if self.tie_word_embeddings else self.vocab_size * h)
+        lin = 2.0 * matmul_params  # the embedding gather is not a matmul; the LM head is
+        attn = 2.0 * self.num_hidden_layers * self.num_attention_heads * self.head_dim * seq_len
+        return 3.0 * (lin + attn)
+
+
+@dataclass
+class CausalLMOutput:
+    loss: Optional[torch.Tensor] = None
+    logits: Optional[torch.Tensor] = None
+    hidden_states: Optional[torch.Tensor] = None
+
+    def __getitem__(self, k):
+        if isinstance(k, str):
+            return getattr(self, k)
+        return tuple(v for v in (self.loss, self.logits) if v is not None)[k]
+
+
+class B200Linear(nn.Module):
+    """Bias-free (by default) linear layer on the tcgen05 GEMM; weight is ``[out, in]`` like nn.Linear."""
+
+    def __init__(self, in_features: int, out_features: int, bias: bool = False, dtype=torch.bfloat16, device=None):
+        super().__init__()
+        self.in_features, self.out_features = in_features, out_features
+        self.weight = nn.Parameter(torch.empty(out_features, in_features, dtype=dtype, device=device))
+        self.bias = nn.Parameter(torch.zeros(out_features, dtype=dtype, device=device)) if bias else None
+
+    def forward(self, x):
+        return F.linear(x, self.weight, self.bias)
+
+    def extra_repr(self):
+        return f"in_features={self.in_features}, out_features={self.out_features}, bias={self.bias is not None}"
+
+
+class B200RMSNorm(nn.Module):
+    def __init__(self, hidden_size: int, eps: float = 1e-5, dtype=torch.bfloat16, device=None):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(hidden_size, dtype=dtype, device=device))
+        self.eps = eps
+
+    def forward(self, x, residual=None):
+        if residual is None:
+            return F.rmsnorm(x, self.weight, self.eps), x
+        return F.add_rmsnorm(x, residual, self.weight, self.eps)
+
+
+class LlamaAttention(nn.Module):
+    def __init__(self, cfg: LlamaConfig, dtype, device=None):
+        super().__init__()
+        self.cfg = cfg
+        self.qkv_proj = B200Linear(cfg.hidden_size, cfg.qkv_width, dtype=dtype, device=device)
+        self.o_proj = B200Linear(cfg.num_attention_heads * cfg.head_dim, cfg.hidden_size, dtype=dtype, device=device)
+
+    def forward(self, x, rope, B, S):
+        c = self.cfg
+        qkv = self.qkv_proj(x)
+        cos, sin, pos = rope
+        attn = F.rope_attention(qkv, cos, sin, pos, B, S, c.num_attention_heads, c.num_key_value_heads, c.head_dim,
+                                causal=True)
+        return self.o_proj(attn)
+
+
+class LlamaMLP(nn.Module):
+    def __init__(self, cfg: LlamaConfig, dtype, device=None):
+        super().__init__()
+        self.gate_up_proj = B200Linear(cfg.hidden_size, 2 * cfg.intermediate_size, dtype=dtype, device=device)
+        self.down_proj = B200Linear(cfg.intermediate_size, cfg.hidden_size, dtype=dtype, device=device)
+
+    def forward(self, x):
+        return self.down_proj(F.swiglu(self.gate_up_proj(x)))
+
+
+class LlamaDecoderLayer(nn.Module):
+    def __init__(self, cfg: LlamaConfig, layer_idx: int, dtype, device=None):
+        super().__init__()
+        self.layer_idx = layer_idx
+        self.input_layernorm = B200RMSNorm(cfg.hidden_size, cfg.rms_norm_eps, dtype, device)
+        self.self_attn = LlamaAttention(cfg, dtype, device)
+        self.post_attention_layernorm = B200RMSNorm(cfg.hidden_size, cfg.rms_norm_eps, dtype, device)
+        self.mlp = LlamaMLP(cfg, dtype, device)
+
+    def forward(self, x, residual, rope, B, S):
+        """``x``: previous sub-layer output, ``residual``: residual stream (None for the first layer)."""
+        normed, residual = self.input_layernorm(x, residual)
+        a = self.self_attn(normed, rope, B, S)
+        normed, residual = self.post_attention_layernorm(a, residual)
+        return self.mlp(normed), residual
+
+
+class LlamaModel(nn.Module):
+    def __init__(self, cfg: LlamaConfig, dtype=torch.bfloat16, device=None):
+        super().__init__()
+        self.cfg = cfg
+        self.embed_tokens = nn.Embedding(cfg.vocab_size, cfg.hidden_size, dtype=dtype, device=device)
+        self.layers = nn.ModuleList([LlamaDecoderLayer(cfg, i, dtype, device) for i in range(cfg.num_hidden_layers)])
+        self.norm = B200RMSNorm(cfg.hidden_size, cfg.rms_norm_eps, dtype, device)
+        self.gradient_checkpointing = False
+        self._rope_cache = None
+
+    def rope(self, position_ids: torch.Tensor, max_pos: int):
+        dev = position_ids.device
+        c = self._rope_cache
+        if c is None or c[0].device != dev or c[0].shape[0] < max_pos:
+            n = max(max_pos, self.cfg.max_position_embeddings)
+            self._rope_cache = F.rope_tables(n, self.cfg.head_dim, self.cfg.rope_theta, dev)
+        cos, sin = self._rope_cache
+        return cos, sin, position_ids.reshape(-1).to(torch.int32).contiguous()
+
+    def forward(self, input_ids: torch.Tensor, position_ids: Optional[torch.Tensor] = None):
+        B, S = input_ids.shape
+        if position_ids is None:
+            position_ids = torch.arange(S, device=input_ids.device).unsqueeze(0).expand(B, S)
+            max_pos = S
+        else:
+            max_pos = self.cfg.max_position_embeddings
+        rope = self.rope(position_ids, max_pos)
+        x = F.embedding(input_ids, self.embed_tokens.weight).view(B * S, -1)
+        residual = None
+        for layer in self.layers:
+            if self.gradient_checkpointing and self.training and torch.is_grad_enabled():
+                x, residual = torch.utils.checkpoint.checkpoint(layer, x, residual, rope, B, S, use_reentrant=False)
+            else:
+                x, residual = layer(x, residual, rope, B, S)
+        h, _ = self.norm(x, residual)
+        return h.view(B, S, -1)
+
+
+class LlamaForCausalLM(nn.Module):
+    """Causal LM with the fused LM-head + cross-entropy loss.
+
+    ``forward(input_ids, labels=..., position_ids=..., shift_labels=...)`` mirrors the transformers
+    call signature the reference's examples use (reference examples/torch_native_parallelism/
+    nd_parallel.py:57-80): ``labels`` are shifted inside, ``shift_labels`` (already shifted, used
+    by the CP / SP paths) are consumed as they are.  ``return_logits=True`` also materialises logits.
+    """
+
+    _no_split_modules = ["LlamaDecoderLayer"]
+    _tied_weights_keys = ["lm_head.weight"]
+
+    def __init__(self, cfg: LlamaConfig, dtype=torch.bfloat16, device=None):
+        super().__init__()
+        self.config = cfg
+        self.model = LlamaModel(cfg, dtype, device)
+        self.lm_head = B200Linear(cfg.hidden_size, cfg.vocab_size, dtype=dtype, device=device)
+        if cfg.tie_word_embeddings:
+            self.lm_head.weight = self.model.embed_tokens.weight
+        if device is None or torch.device(device).type != "meta":
+            self.reset_parameters()
+
+    @torch.no_grad()
+    def reset_parameters(self, seed: Optional[int] = None):
+        g = None
+        std = self.config.initializer_range
+        if seed is not None:
+            g = torch.Generator(device=self.lm_head.weight.device).manual_seed(seed)
+        for name, p in self.named_parameters():
+            if p.dim() >= 2:
+                # fill through an fp32 staging chunk so bf16 init matches an fp32 init rounded once
+                p.normal_(0.0, std, generator=g)
+            else:
+                p.fill_(1.0)
+
+    def gradient_checkpointing_enable(self, **_):
+        self.model.gradient_checkpointing = True
+
+    def gradient_checkpointing_disable(self):
+        self.model.gradient_checkpointing = False
+
+    def tie_weights(self):
+        if self.config.tie_word_embeddings:
+            self.lm_head.weight = self.model.embed_tokens.weight
+
+    def get_input_embeddings(self):
+        return self.model.embed_tokens
+
+    def forward(self, input_ids, labels=None, position_ids=None, shift_labels=None, attention_mask=None,
+                return_logits: bool = False, **_):
+        h = self.model(input_ids, position_ids)
+        loss = logits = None
+        if shift_labels is None and labels is not None:
+            shift_labels = torch.full_like(labels, -100)
+            shift_labels[:, :-1] = labels[:, 1:]
+        if shift_labels is not None:
+            loss = F.fused_linear_cross_entropy(h.reshape(-1, h.shape[-1]), self.lm_head.weight,
+                                                shift_labels.reshape(-1), -100, self.config.loss_chunk_tokens)
+        if return_logits or shift_labels is None:
+            logits = self.lm_head(h)
+        return CausalLMOutput(loss=loss, logits=logits)
+
+    # ------------------------------------------------------------------ transformers interchange
+    def hf_state_dict(self) -> dict:
+        """State dict under transformers' parameter names (q/k/v and gate/up un-fused)."""
+        c = self.config
+        nq, nk = c.num_attention_heads * c.head_dim, c.num_key_value_heads * c.head_dim
+        out = {"model.embed_tokens.weight": self.model.embed_tokens.weight, "model.norm.weight": self.model.norm.weight}
+        if not c.tie_word_embeddings:
+            out["lm_head.weight"] = self.lm_head.weight
+        for i, l in enumerate(self.model.layers):
+            pre = f"model.layers.{i}."
+            w = l.self_attn.qkv_proj.weight
+            out[pre + "self_attn.q_proj.weight"] = w[:nq]
+            out[pre + "self_attn.k_proj.weight"] = w[nq : nq + nk]
+            out[pre + "self_attn.v_proj.weight"] = w[nq + nk :]
+            out[pre + "self_attn.o_proj.weight"] = l.self_attn.o_proj.weight
+            gu = l.mlp.gate_up_proj.weight
+            out[pre + "mlp.gate_proj.weight"] = gu[: c.intermediate_size]
+            out[pre + "mlp.up_proj.weight"] = gu[c.intermediate_size :]
+            out[pre + "mlp.down_proj.weight"] = l.mlp.down_proj.weight
+            out[pre + "input_layernorm.weight"] = l.input_layernorm.weight
+            out[pre + "post_attention_layernorm.weight"] = l.post_attention_layernorm.weight
+        return {k: v.detach() for k, v in out.items()}
+
+    @torch.no_grad()
+    def load_hf_state_dict(self, sd: dict):
+        mine = self.hf_state_dict()
+        missing = [k for k in mine if k not in sd]
+        if missing:
+            raise KeyError(f"missing keys in transformers state dict: {missing[:5]}...")
+        for k, dst in mine.items():
+            dst.copy_(sd[k].to(dst.dtype))
+        return self

@@ -24,6 +24,7 @@ P = c_void_p
 I = c_int
 L = c_longlong
 F = c_float
+U = ctypes.c_uint
 
 # name -> argtypes (restype is always int unless listed in _RESTYPES)
 _SIGNATURES = {
@@ -61,12 +62,13 @@ _SIGNATURES = {
     "b200_ipc_close_handle": [P],
     "b200_memset_async": [P, I, L, P],
     "b200_memcpy_async": [P, P, L, P],
-    "b200_allreduce_bf16": [P, P, I, I, L, F, P, I, I, P],
-    "b200_allreduce_f32": [P, P, I, I, L, F, P, I, I, P],
-    "b200_reduce_scatter_adamw": [P, P, I, I, L, P, P, P, P, F, F, F, F, F, I, F, P, P, I, I, P],
-    "b200_allgather_bf16": [P, P, P, I, I, L, P, I, I, P],
-    "b200_alltoall_bf16": [P, P, P, I, I, L, P, I, I, P],
-    "b200_barrier_all": [P, I, I, I, P],
+    "b200_comm_limits": [P, P, P],
+    "b200_comm_set_timeout_ms": [L],
+    "b200_barrier_all": [P, I, I, I, U, P],
+    "b200_allgather_pull": [P, I, I, L, L, P, I, U, I, P],
+    "b200_reduce_scatter_adamw": [P, I, I, L, L, P, P, P, L, P, F, F, F, F, F, I, F, I, P, I, I, U, P, I, P],
+    "b200_allreduce": [P, I, I, L, L, I, F, I, I, U, P, I, P],
+    "b200_alltoall_pull": [P, I, I, L, L, P, I, I, U, P, I, P],
 }
 _RESTYPES = {
     "b200_launch_count": ctypes.c_ulonglong,

@@ -48,7 +48,7 @@ def gemm(
     b_mn_major: bool = False,
     bias: Optional[torch.Tensor] = None,
     out: Optional[torch.Tensor] = None,
-    out_dtype: torch.dtype = BF16,
+    out_dtype: Optional[torch.dtype] = None,
     accumulate: bool = False,
     max_ctas: int = 0,
 ) -> torch.Tensor:
@@ -70,6 +70,8 @@ def gemm(
     if out is None:
         if accumulate:
             raise ValueError("accumulate=True needs an existing `out`")
+        if out_dtype is None:
+            out_dtype = a.dtype
         out = torch.empty((M, N), dtype=out_dtype, device=a.device)
     else:
         out_dtype = out.dtype
@@ -105,6 +107,25 @@ def gemm(
     return out
 
 
+def deliver_weight_grad(weight: torch.Tensor, compute):
+    """Weight-gradient hand-off between the native ops and the data-parallel engines.
+
+    ``compute(out, accumulate)`` produces dW (into ``out`` when given).  If an engine has published a
+    destination for this parameter (``weight._b200_grad_buf``: a view of its flat gradient bucket /
+    shard buffer), dW is written — or accumulated — there directly, the engine is notified through
+    ``weight._b200_grad_hook`` and autograd receives ``None`` (no second copy, no AccumulateGrad pass).
+    Otherwise dW is returned to autograd as usual.
+    """
+    buf = getattr(weight, "_b200_grad_buf", None)
+    if buf is None:
+        return compute(None, False)
+    g = weight.grad
+    acc = bool(getattr(weight, "_b200_has_partial", False)) or (g is not None and g.data_ptr() == buf.data_ptr())
+    compute(buf, acc)
+    weight._b200_grad_hook(weight)
+    return None
+
+
 class _LinearFn(torch.autograd.Function):
     """y = x W^T (+ b).  fwd / dgrad / wgrad all run on the tcgen05 GEMM with no transposes in memory."""
 
@@ -130,7 +151,9 @@ class _LinearFn(torch.autograd.Function):
             dx = gemm(dy2, weight, b_mn_major=True).view(ctx.in_shape)
         if ctx.needs_input_grad[1]:
             # dW[N,K] = dY^T X : both operands stored [reduction(T), out] -> MN-major
-            dw = gemm(dy2, x2, a_mn_major=True, b_mn_major=True)
+            dw = deliver_weight_grad(
+                weight, lambda out, acc: gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=out, accumulate=acc)
+            )
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = dy2.float().sum(0).to(dy2.dtype)
         return dx, dw, db
@@ -316,6 +339,7 @@ class _EmbeddingFn(torch.autograd.Function):
             out = torch.empty((flat.numel(), H), dtype=table.dtype, device=table.device)
             check(lib.b200_embedding_fwd(ptr(flat), ptr(table), ptr(out), flat.numel(), H, V, cur_stream()), "embedding_fwd")
         ctx.save_for_backward(flat)
+        ctx.table = table  # the Parameter object (for the engines' gradient hand-off), not its data
         ctx.tshape = (V, H)
         ctx.tdtype = table.dtype
         return out.view(*ids.shape, H)
@@ -325,13 +349,20 @@ class _EmbeddingFn(torch.autograd.Function):
         (flat,) = ctx.saved_tensors
         V, H = ctx.tshape
         d2 = dout.reshape(-1, H).contiguous()
-        dtable = torch.zeros((V, H), dtype=ctx.tdtype, device=dout.device)
-        if not _on_gpu(dout):
-            dtable.index_add_(0, flat, d2.to(ctx.tdtype))
-        else:
-            lib = _lib.require_gpu_lib()
-            check(lib.b200_embedding_bwd(ptr(flat), ptr(d2), ptr(dtable), flat.numel(), H, V, cur_stream()), "embedding_bwd")
-        return None, dtable
+
+        def compute(out, acc):
+            if out is None:
+                out = torch.zeros((V, H), dtype=ctx.tdtype, device=dout.device)
+            elif not acc:
+                out.zero_()
+            if not _on_gpu(dout):
+                out.index_add_(0, flat, d2.to(ctx.tdtype))
+            else:
+                lib = _lib.require_gpu_lib()
+                check(lib.b200_embedding_bwd(ptr(flat), ptr(d2), ptr(out), flat.numel(), H, V, cur_stream()), "embedding_bwd")
+            return out
+
+        return None, deliver_weight_grad(ctx.table, compute)
 
 
 def embedding(ids: torch.Tensor, table: torch.Tensor) -> torch.Tensor:
@@ -421,6 +452,7 @@ class _FusedLinearCEFn(torch.autograd.Function):
             loss = rows.sum() * inv
         if need_grad:
             ctx.save_for_backward(dh, dw)
+        ctx.weight = weight
         ctx.h_shape = h.shape
         return loss
 
@@ -430,7 +462,19 @@ class _FusedLinearCEFn(torch.autograd.Function):
         g = dloss.to(torch.float32)
         # upstream scale (1/GA from Accelerator.backward, loss scaling): one cheap pass
         dh = dh.mul_(g.to(dh.dtype)) if ctx.needs_input_grad[0] else None
-        dw = dw.mul_(g.to(dw.dtype)) if ctx.needs_input_grad[1] else None
+        if ctx.needs_input_grad[1]:
+            gw = g.to(dw.dtype)
+
+            def compute(out, acc):
+                if out is None:
+                    return dw.mul_(gw)
+                if acc:
+                    return out.add_(dw * gw)
+                return torch.mul(dw, gw, out=out)
+
+            dw = deliver_weight_grad(ctx.weight, compute)
+        else:
+            dw = None
         return (dh.view(ctx.h_shape) if dh is not None else None), dw, None, None, None
 
 

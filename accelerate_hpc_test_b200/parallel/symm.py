@@ -1,0 +1,169 @@
+"""Symmetric (peer-mapped) device memory: the data plane of the fused collectives.
+
+Every rank ``cudaMalloc`` s one buffer of the same size, exports a CUDA-IPC handle, exchanges the
+handles through ``torch.distributed`` (control plane only) and maps every peer's buffer, so a kernel
+on GPU *r* can ``ld`` / ``st`` any byte of any peer over NVLink.  The first bytes of the buffer are
+the signal pad the kernels order themselves with; the rest is handed out by a bump allocator that
+every rank drives identically, so equal allocations land at equal offsets ("symmetric").
+
+There is no reference counterpart: the reference's data plane is NCCL's internal buffers
+(SURVEY.md §5.8).  The kernels that use this memory are in ``csrc/comm.cu``.
+"""
+
+from __future__ import annotations
+
+import ctypes
+import itertools
+import os
+from typing import Optional
+
+import torch
+
+from ..ops import _lib
+from ..ops._lib import check
+
+
+class _RawCudaBuffer:
+    """Object exposing ``__cuda_array_interface__`` so torch can wrap raw device memory without copying."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+
+
+class SymmetricWorkspace:
+    """One peer-mapped buffer per rank plus channel / epoch bookkeeping for the comm kernels."""
+
+    def __init__(self, group, nbytes: int, device: torch.device):
+        self.group = group
+        self.world = torch.distributed.get_world_size(group)
+        self.rank = torch.distributed.get_rank(group)
+        self.device = device
+        lib = _lib.require_gpu_lib()
+        self.lib = lib
+        max_ranks, n_channels, pad = ctypes.c_int(), ctypes.c_int(), ctypes.c_longlong()
+        check(lib.b200_comm_limits(ctypes.byref(max_ranks), ctypes.byref(n_channels), ctypes.byref(pad)))
+        if self.world > max_ranks.value:
+            raise RuntimeError(f"symmetric workspace supports up to {max_ranks.value} ranks per NVLink domain, got {self.world}")
+        self.num_channels = n_channels.value
+        self.pad_bytes = (pad.value + 4095) // 4096 * 4096
+        self.nbytes = int(nbytes) + self.pad_bytes
+        base = ctypes.c_void_p()
+        check(lib.b200_symm_alloc(ctypes.byref(base), self.nbytes), "symm_alloc")
+        self.base = base.value
+        handle = (ctypes.c_ubyte * 64)()
+        check(lib.b200_ipc_get_handle(ctypes.c_void_p(self.base), handle), "ipc_get_handle")
+        handles = [None] * self.world
+        torch.distributed.all_gather_object(handles, bytes(handle), group=group)
+        self.peer_bases = []
+        self._opened = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self.peer_bases.append(self.base)
+                continue
+            buf = (ctypes.c_ubyte * 64).from_buffer_copy(h)
+            p = ctypes.c_void_p()
+            check(lib.b200_ipc_open_handle(buf, ctypes.byref(p)), "ipc_open_handle")
+            self.peer_bases.append(p.value)
+            self._opened.append(p.value)
+        self.peer_array = (ctypes.c_void_p * self.world)(*self.peer_bases)
+        self._whole = torch.as_tensor(_RawCudaBuffer(self.base, self.nbytes), device=device)
+        self._cursor = self.pad_bytes
+        self._channel_iter = itertools.count(1)
+        self._epochs: dict[int, int] = {}
+        self._counters = torch.zeros(self.num_channels, dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device)
+        torch.distributed.barrier(group=group)
+        self.closed = False
+
+    # ------------------------------------------------------------------ construction helpers
+    @classmethod
+    def create_default(cls, state) -> "SymmetricWorkspace":
+        gb = float(os.environ.get("ACCELERATE_B200_SYMM_GB", "4"))
+        return cls(torch.distributed.group.WORLD, int(gb * 2**30), state.device)
+
+    # ------------------------------------------------------------------ allocation
+    def alloc(self, nbytes: int, align: int = 256) -> int:
+        """Reserve ``nbytes`` and return the byte offset (identical on every rank when called in lock-step)."""
+        off = (self._cursor + align - 1) // align * align
+        if off + nbytes > self.nbytes:
+            raise MemoryError(
+                f"symmetric workspace exhausted: need {nbytes} bytes at offset {off}, capacity {self.nbytes}. "
+                "Raise ACCELERATE_B200_SYMM_GB."
+            )
+        self._cursor = off + nbytes
+        return off
+
+    def tensor(self, offset: int, shape, dtype: torch.dtype) -> torch.Tensor:
+        """A tensor view of my own buffer at ``offset``."""
+        n = 1
+        for s in shape:
+            n *= int(s)
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        return self._whole[offset : offset + nbytes].view(dtype).view(*shape)
+
+    def alloc_tensor(self, shape, dtype: torch.dtype):
+        n = 1
+        for s in shape:
+            n *= int(s)
+        off = self.alloc(n * torch.empty((), dtype=dtype).element_size())
+        return off, self.tensor(off, shape, dtype)
+
+    def new_channel(self) -> int:
+        c = next(self._channel_iter)
+        if c >= self.num_channels:
+            raise RuntimeError("out of signal channels")
+        self._epochs[c] = 0
+        return c
+
+    def next_epoch(self, channel: int) -> int:
+        self._epochs[channel] += 1
+        return self._epochs[channel]
+
+    def epoch(self, channel: int) -> int:
+        return self._epochs[channel]
+
+    def counter_ptr(self, channel: int) -> ctypes.c_void_p:
+        return ctypes.c_void_p(self._counters.data_ptr() + 4 * channel)
+
+    # ------------------------------------------------------------------ collectives (thin launch wrappers)
+    def barrier(self, channel: int, stream=None):
+        e = self.next_epoch(channel)
+        check(self.lib.b200_barrier_all(self.peer_array, self.rank, self.world, channel, e, _stream(stream)), "barrier_all")
+
+    def allgather_pull(self, shard_off: int, shard_bytes: int, out: torch.Tensor, wait_channel: int = -1, wait_epoch: int = 0,
+                       ctas: int = 32, stream=None):
+        check(self.lib.b200_allgather_pull(self.peer_array, self.rank, self.world, shard_off, shard_bytes, _lib.ptr(out),
+                                           wait_channel, wait_epoch, ctas, _stream(stream)), "allgather_pull")
+
+    def allreduce_(self, off: int, numel: int, dtype: torch.dtype, scale: float, ch_arrive: int, ch_done: int, ctas: int = 32,
+                   stream=None):
+        e = self.next_epoch(ch_arrive)
+        self._epochs[ch_done] = e
+        check(self.lib.b200_allreduce(self.peer_array, self.rank, self.world, off, numel, int(dtype == torch.bfloat16), float(scale),
+                                      ch_arrive, ch_done, e, self.counter_ptr(ch_arrive), ctas, _stream(stream)), "allreduce")
+
+    def alltoall_pull(self, send_off: int, block_bytes: int, out: torch.Tensor, ch_arrive: int, ch_done: int, ctas: int = 32,
+                      stream=None):
+        e = self.next_epoch(ch_arrive)
+        self._epochs[ch_done] = e
+        check(self.lib.b200_alltoall_pull(self.peer_array, self.rank, self.world, send_off, block_bytes, _lib.ptr(out), ch_arrive,
+                                          ch_done, e, self.counter_ptr(ch_arrive), ctas, _stream(stream)), "alltoall_pull")
+
+    def close(self):
+        if self.closed:
+            return
+        self.closed = True
+        try:
+            torch.cuda.synchronize(self.device)
+            for p in self._opened:
+                self.lib.b200_ipc_close_handle(ctypes.c_void_p(p))
+            self._whole = None
+            self.lib.b200_symm_free(ctypes.c_void_p(self.base))
+        except Exception:  # pragma: no cover
+            pass
+
+
+def _stream(stream) -> ctypes.c_void_p:
+    if stream is None:
+        return _lib.cur_stream()
+    return ctypes.c_void_p(stream.cuda_stream)
