@@ -143,8 +143,8 @@ class _LinearFn(torch.autograd.Function):
     def backward(ctx, dy):
         x2, weight = ctx.saved_tensors
         dy2 = dy.reshape(-1, dy.shape[-1])
-        if dy2.dtype != BF16:
-            dy2 = dy2.to(BF16)
+        if dy2.dtype != weight.dtype:
+            dy2 = dy2.to(weight.dtype)
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             # dX[T,K] = dY[T,N] W[N,K] : B is stored [reduction, out] -> MN-major

@@ -56,6 +56,31 @@ def apply_activation_checkpointing(model: nn.Module, plugin) -> None:
             module._b200_checkpointed = True
 
 
+class _Pool:
+    """Equal-sized reusable buffers with the CUDA event that must pass before each can be reused."""
+
+    def __init__(self, make):
+        self._make = make  # () -> (symmetric byte offset, tensor)
+        self.bufs = []
+        self.events = []
+        self.free = []
+
+    def add(self, n: int = 1):
+        for _ in range(n):
+            self.bufs.append(self._make())
+            self.events.append(None)
+            self.free.append(len(self.bufs) - 1)
+
+    def take(self) -> int:
+        if not self.free:
+            self.add(1)  # grow rather than dead-lock (deep prefetch / many live units)
+        return self.free.pop(0)
+
+    def give(self, idx: int, event=None):
+        self.events[idx] = event
+        self.free.append(idx)
+
+
 class _Unit:
     """One sharded group of parameters (a wrapped module, or a leftover group of the root)."""
 
@@ -166,7 +191,9 @@ class B200ShardedModule(nn.Module):
             q = world * 8
             u.padded = (u.numel + q - 1) // q * q
             u.shard_numel = u.padded // world
-        max_padded = max(u.padded for u in self._units)
+        layer_units = [u for u in self._units if u.module is not None]
+        root_units = [u for u in self._units if u.module is None]
+        max_layer = max([u.padded for u in layer_units], default=0)
         total_shard = sum(u.shard_numel for u in self._units)
         esz = 2 if self.param_dtype == BF16 else 4
         n_grad_bufs = int(os.environ.get("ACCELERATE_B200_FSDP_GRAD_BUFFERS", "3"))
@@ -174,7 +201,8 @@ class B200ShardedModule(nn.Module):
         if self.use_symm:
             from .symm import SymmetricWorkspace
 
-            need = total_shard * esz + n_grad_bufs * max_padded * esz + 64 * 2**20
+            # shards + dedicated root gradient buffers + pooled layer gradient buffers (+ slack for pool growth)
+            need = total_shard * esz + sum(u.padded for u in root_units) * esz + (n_grad_bufs + 2) * max_layer * esz + 64 * 2**20
             self.ws = SymmetricWorkspace(self.group, need, self.device)
             self.comm_stream = torch.cuda.Stream(device=self.device)
             self.ch_step = self.ws.new_channel()
@@ -203,15 +231,27 @@ class B200ShardedModule(nn.Module):
             for p in u.params:
                 p._b200_full_shape = tuple(p.shape)
                 p.data = torch.empty(0, dtype=self.param_dtype, device=self.device)
-        self._full_pool = [torch.empty(max_padded, dtype=self.param_dtype, device=self.device) for _ in range(n_full_bufs)]
-        self._full_free = list(range(n_full_bufs))
-        self._full_events = [None] * n_full_bufs
-        if self.use_symm:
-            self._grad_pool = [self.ws.alloc_tensor((max_padded,), self.param_dtype) for _ in range(n_grad_bufs)]
-        else:
-            self._grad_pool = [(0, torch.empty(max_padded, dtype=self.param_dtype, device=self.device)) for _ in range(n_grad_bufs)]
-        self._grad_free = list(range(n_grad_bufs))
-        self._grad_events = [None] * n_grad_bufs
+        # layer units share pools sized by the largest layer; root units (live for the whole
+        # forward+backward) get dedicated buffers of their own size
+        def full_maker(n):
+            return lambda: (0, torch.empty(n, dtype=self.param_dtype, device=self.device))
+
+        def grad_maker(n):
+            if self.use_symm:
+                return lambda: self.ws.alloc_tensor((n,), self.param_dtype)
+            return lambda: (0, torch.empty(n, dtype=self.param_dtype, device=self.device))
+
+        layer_full, layer_grad = _Pool(full_maker(max_layer)), _Pool(grad_maker(max_layer))
+        if layer_units:
+            layer_full.add(n_full_bufs)
+            layer_grad.add(n_grad_bufs)
+        for u in self._units:
+            if u.module is not None:
+                u.fpool, u.gpool = layer_full, layer_grad
+            else:
+                u.fpool, u.gpool = _Pool(full_maker(u.padded)), _Pool(grad_maker(u.padded))
+                u.fpool.add(1)
+                u.gpool.add(1)
         if self.use_symm:
             torch.cuda.synchronize(self.device)
             self.ws.barrier(self.ch_step)
@@ -227,35 +267,16 @@ class B200ShardedModule(nn.Module):
                 p._b200_grad_hook = self._native_grad_ready
                 self._handles.append(p.register_post_accumulate_grad_hook(self._autograd_grad_ready))
 
-    # ------------------------------------------------------------------ buffer pools
-    def _take_full(self, u: _Unit) -> int:
-        if not self._full_free:
-            # evict: grow the pool rather than dead-lock (happens with deep prefetch or many live units)
-            self._full_pool.append(torch.empty_like(self._full_pool[0]))
-            self._full_events.append(None)
-            self._full_free.append(len(self._full_pool) - 1)
-        return self._full_free.pop(0)
-
-    def _take_grad(self) -> int:
-        if not self._grad_free:
-            if self.use_symm:
-                self._grad_pool.append(self.ws.alloc_tensor((self._grad_pool[0][1].numel(),), self.param_dtype))
-            else:
-                self._grad_pool.append((0, torch.empty_like(self._grad_pool[0][1])))
-            self._grad_events.append(None)
-            self._grad_free.append(len(self._grad_pool) - 1)
-        return self._grad_free.pop(0)
-
     # ------------------------------------------------------------------ all-gather / reshard
     def _launch_gather(self, u: _Unit):
         """Start (on the comm stream) the gather of ``u`` into a pooled buffer; idempotent."""
         if u.full is not None:
             return
-        idx = self._take_full(u)
+        idx = u.fpool.take()
         u.full_idx = idx
-        u.full = self._full_pool[idx][: u.padded]
+        u.full = u.fpool.bufs[idx][1][: u.padded]
         if self.use_symm:
-            ev = self._full_events[idx]
+            ev = u.fpool.events[idx]
             if ev is not None:
                 self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
@@ -295,11 +316,11 @@ class B200ShardedModule(nn.Module):
             u.master.copy_(u.shard)
         for p in u.params:
             p.data = torch.empty(0, dtype=self.param_dtype, device=self.device)
+        ev = None
         if self.use_symm:
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(self.device))
-            self._full_events[u.full_idx] = ev
-        self._full_free.append(u.full_idx)
+        u.fpool.give(u.full_idx, ev)
         u.full = None
         u.ag_event = None
         u.unsharded = False
@@ -356,12 +377,12 @@ class B200ShardedModule(nn.Module):
 
     def _attach_grad_buffer(self, u: _Unit):
         if u.grad is None:
-            idx = self._take_grad()
+            idx = u.gpool.take()
             u.grad_idx = idx
-            u.grad_off, buf = self._grad_pool[idx]
+            u.grad_off, buf = u.gpool.bufs[idx]
             u.grad = buf[: u.padded]
-            if self.use_symm and self._grad_events[idx] is not None:
-                torch.cuda.current_stream(self.device).wait_event(self._grad_events[idx])
+            if self.use_symm and u.gpool.events[idx] is not None:
+                torch.cuda.current_stream(self.device).wait_event(u.gpool.events[idx])
             u.has_partial = False
         u.ready = set()
         u.rs_launched = False
@@ -420,9 +441,7 @@ class B200ShardedModule(nn.Module):
         for p in u.params:
             p._b200_grad_buf = None
             p._b200_has_partial = False
-        if self.use_symm:
-            self._grad_events[u.grad_idx] = u.rs_event
-        self._grad_free.append(u.grad_idx)
+        u.gpool.give(u.grad_idx, u.rs_event if self.use_symm else None)
         u.grad = None
         u.has_partial = False
 
