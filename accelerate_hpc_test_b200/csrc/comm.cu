@@ -94,24 +94,81 @@ __global__ void barrier_kernel(Peers peers, int rank, int world, int channel, ui
 }
 
 // ------------------------------------------------------------------------------ all-gather (pull)
-// out[p * shard_bytes ...] = peer p's bytes at [shard_off, shard_off + shard_bytes).  If wait_channel
-// >= 0 the shard of peer p is read only once flags[wait_channel][p] >= wait_epoch (the owner
-// publishes that epoch when its shard holds the parameter version this gather needs).
-__global__ void __launch_bounds__(512)
+// out[p * shard_bytes ...] = peer p's bytes at [shard_off, shard_off + shard_bytes).
+// LSU loads over NVLink top out at a few GB/s per SM (outstanding-request limit), so the copy is
+// driven by the TMA engine instead: one thread per CTA streams 16 KB chunks peer -> smem ring ->
+// local memory with cp.async.bulk, several chunks in flight.  ~16-32 CTAs saturate the link and the
+// SMs stay free for the GEMMs running next to it.
+// If wait_channel >= 0 peer data is read only once flags[wait_channel][p] >= wait_epoch.
+// The ring is kept under ~25 KB so a copy CTA co-resides with a persistent GEMM CTA (198 KB of smem)
+// on every SM: the gather then runs *beside* the tensor-core work instead of waiting for an SM.
+static constexpr int AG_CHUNK = 8192;
+static constexpr int AG_STAGES = 3;
+static constexpr int AG_AHEAD = 2;
+static constexpr int AG_SMEM = AG_CHUNK * AG_STAGES + 128 + 128;
+
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)),
+               "r"(bytes)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(32)
 allgather_pull_kernel(Peers peers, int rank, int world, long long shard_off, long long shard_bytes,
                       uint8_t* __restrict__ out, int wait_channel, uint32_t wait_epoch) {
+  extern __shared__ uint8_t ag_smem_raw[];
+  uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ag_smem_raw) + 127) & ~(uintptr_t)127);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + AG_CHUNK * AG_STAGES);
   if (wait_channel >= 0) wait_all(peers, rank, world, wait_channel, wait_epoch);
-  const long long nvec = shard_bytes >> 4;
-  const long long total = nvec * world;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  // start with my right-hand neighbour so the 8 ranks spread their reads over distinct peers
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int slot = (int)(i / nvec);
-    const long long j = i - (long long)slot * nvec;
-    const int p = (rank + 1 + slot) % world;
-    const uint4 v = ld_peer_v4(peers.base[p] + shard_off + (j << 4));
-    *reinterpret_cast<uint4*>(out + (long long)p * shard_bytes + (j << 4)) = v;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < AG_STAGES; ++i) mbar_init(&bars[i], 1);
+    fence_barrier_init();
   }
+  __syncwarp();
+  if (threadIdx.x != 0) return;
+  const long long chunks_per_shard = (shard_bytes + AG_CHUNK - 1) / AG_CHUNK;
+  const long long total = chunks_per_shard * world;
+  // chunk g of this CTA: g = blockIdx.x + k * gridDim.x ; peers visited starting at my right neighbour
+  const long long n = (total > blockIdx.x) ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  auto locate = [&](long long k, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
+    const long long g = blockIdx.x + k * (long long)gridDim.x;
+    const int slot = (int)(g / chunks_per_shard);
+    const long long c = g - (long long)slot * chunks_per_shard;
+    const int p = (rank + 1 + slot) % world;
+    const long long o = c * AG_CHUNK;
+    const long long left = shard_bytes - o;
+    bytes = (uint32_t)(left < AG_CHUNK ? left : AG_CHUNK);
+    src = peers.base[p] + shard_off + o;
+    dst = out + (long long)p * shard_bytes + o;
+  };
+  auto issue_load = [&](long long k) {
+    const uint8_t* src; uint8_t* dst; uint32_t bytes;
+    locate(k, src, dst, bytes);
+    const int st = (int)(k % AG_STAGES);
+    mbar_arrive_expect_tx(&bars[st], bytes);
+    bulk_g2s(ring + st * AG_CHUNK, src, bytes, &bars[st]);
+  };
+  for (long long k = 0; k < AG_AHEAD && k < n; ++k) issue_load(k);
+  for (long long k = 0; k < n; ++k) {
+    if (k + AG_AHEAD < n) {
+      // the ring slot of chunk k+AHEAD was last read by the store of chunk k+AHEAD-STAGES
+      asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(AG_STAGES - AG_AHEAD - 1) : "memory");
+      issue_load(k + AG_AHEAD);
+    }
+    const int st = (int)(k % AG_STAGES);
+    mbar_wait(&bars[st], (uint32_t)((k / AG_STAGES) & 1));
+    const uint8_t* src; uint8_t* dst; uint32_t bytes;
+    locate(k, src, dst, bytes);
+    bulk_s2g(dst, ring + st * AG_CHUNK, bytes);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 // ------------------------------------------------------------------------------ reduce-scatter + AdamW
@@ -120,67 +177,109 @@ struct AdamArgs {
 };
 
 // Rank r owns elements [r*n, (r+1)*n) of every rank's flat bf16 gradient (at byte offset grad_off of
-// the symmetric buffers).  It sums the 8 copies over NVLink, applies AdamW to its fp32 master /
+// the symmetric buffers).  It sums the copies of all ranks, applies AdamW to its fp32 master /
 // moments and writes the new bf16 parameter shard (symmetric memory at param_off, where peers
 // all-gather it from).  do_adam == 0: only the reduced fp32 gradient shard is written (grad_out).
-__global__ void __launch_bounds__(512)
+//
+// Data path: warp 0 streams tiles of 1024 elements from every peer into shared memory with
+// cp.async.bulk (TMA engine, NVLink), warps 1-4 reduce them out of shared memory and run the
+// optimizer math; a full/empty mbarrier pair per stage overlaps the two.
+static constexpr int RS_TILE = 1024;           // elements per tile (128 consumer threads x 8)
+static constexpr int RS_TILE_BYTES = RS_TILE * 2;
+
+__global__ void __launch_bounds__(160)
 reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off, long long n,
                             float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
                             long long param_off, float* __restrict__ grad_out, AdamArgs a, int do_adam,
                             const float* __restrict__ clip_coef, int ch_arrive, int ch_done, uint32_t epoch,
-                            uint32_t* __restrict__ counter) {
+                            uint32_t* __restrict__ counter, int stages) {
+  extern __shared__ uint8_t rs_smem_raw[];
+  uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(rs_smem_raw) + 127) & ~(uintptr_t)127);
+  const int stage_bytes = world * RS_TILE_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(ring + stages * stage_bytes);
+  uint64_t* empty = full + 4;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 4);
+    }
+    fence_barrier_init();
+  }
   // (1) everybody's gradients are complete
   if (blockIdx.x == 0) signal_all(peers, rank, world, ch_arrive, epoch);
-  wait_all(peers, rank, world, ch_arrive, epoch);
+  wait_all(peers, rank, world, ch_arrive, epoch);  // ends with __syncthreads(): barrier inits are visible
 
-  const long long nvec = n >> 3;  // 8 bf16 per 16 B
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  const float gs = a.grad_scale * (clip_coef ? *clip_coef : 1.f);
-  __nv_bfloat16* shard = reinterpret_cast<__nv_bfloat16*>(peers.base[rank] + param_off);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    uint4 vals[MAX_RANKS];
-#pragma unroll
-    for (int s = 0; s < MAX_RANKS; ++s) {
-      if (s < world) {
-        const int p = (rank + s) % world;
-        vals[s] = ld_peer_v4(peers.base[p] + grad_off + (((long long)rank * nvec + i) << 4));
+  const long long ntiles = (n + RS_TILE - 1) / RS_TILE;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0) {
+    if (lane == 0) {
+      int st = 0;
+      uint32_t ph = 0;
+      for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        mbar_wait(&empty[st], ph ^ 1);
+        const long long e0 = t * RS_TILE;
+        const long long left = n - e0;
+        const uint32_t bytes = (uint32_t)((left < RS_TILE ? left : RS_TILE) * 2);
+        mbar_arrive_expect_tx(&full[st], bytes * world);
+        for (int s = 0; s < world; ++s) {
+          const int p = (rank + s) % world;
+          bulk_g2s(ring + st * stage_bytes + p * RS_TILE_BYTES, peers.base[p] + grad_off + (((long long)rank * n + e0) << 1), bytes,
+                   &full[st]);
+        }
+        if (++st == stages) { st = 0; ph ^= 1; }
       }
     }
-#pragma unroll
-    for (int s = 0; s < MAX_RANKS; ++s)
-      if (s < world) accum_bf16x8(acc, vals[s]);
-    const long long e0 = i << 3;
-    if (do_adam) {
-      float pw[8];
-      const float4 m0 = *reinterpret_cast<const float4*>(m + e0), m1 = *reinterpret_cast<const float4*>(m + e0 + 4);
-      const float4 v0 = *reinterpret_cast<const float4*>(v + e0), v1 = *reinterpret_cast<const float4*>(v + e0 + 4);
-      const float4 p0 = *reinterpret_cast<const float4*>(master + e0), p1 = *reinterpret_cast<const float4*>(master + e0 + 4);
-      float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-      float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-      float pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float g = acc[k] * gs;
-        mm[k] = mm[k] * a.beta1 + (1.f - a.beta1) * g;
-        vv[k] = vv[k] * a.beta2 + (1.f - a.beta2) * g * g;
-        float p = pp[k] * (1.f - a.lr * a.weight_decay);
-        p -= (a.lr / a.bias_c1) * (mm[k] / (sqrtf(vv[k] / a.bias_c2) + a.eps));
-        pw[k] = p;
+  } else {
+    const int ct = threadIdx.x - 32;  // 0..127
+    const float gs = a.grad_scale * (clip_coef ? *clip_coef : 1.f);
+    __nv_bfloat16* shard = reinterpret_cast<__nv_bfloat16*>(peers.base[rank] + param_off);
+    int st = 0;
+    uint32_t ph = 0;
+    for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
+      mbar_wait(&full[st], ph);
+      const long long e0 = t * RS_TILE + ct * 8;
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (e0 < n) {
+        for (int p = 0; p < world; ++p) {
+          const uint4 vv = *reinterpret_cast<const uint4*>(ring + st * stage_bytes + p * RS_TILE_BYTES + ct * 16);
+          accum_bf16x8(acc, vv);
+        }
       }
-      *reinterpret_cast<float4*>(m + e0) = make_float4(mm[0], mm[1], mm[2], mm[3]);
-      *reinterpret_cast<float4*>(m + e0 + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
-      *reinterpret_cast<float4*>(v + e0) = make_float4(vv[0], vv[1], vv[2], vv[3]);
-      *reinterpret_cast<float4*>(v + e0 + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
-      *reinterpret_cast<float4*>(master + e0) = make_float4(pw[0], pw[1], pw[2], pw[3]);
-      *reinterpret_cast<float4*>(master + e0 + 4) = make_float4(pw[4], pw[5], pw[6], pw[7]);
-      uint4 o;
-      o.x = f2_to_bf2(pw[0], pw[1]); o.y = f2_to_bf2(pw[2], pw[3]);
-      o.z = f2_to_bf2(pw[4], pw[5]); o.w = f2_to_bf2(pw[6], pw[7]);
-      *reinterpret_cast<uint4*>(shard + e0) = o;
-    } else {
-      *reinterpret_cast<float4*>(grad_out + e0) = make_float4(acc[0] * gs, acc[1] * gs, acc[2] * gs, acc[3] * gs);
-      *reinterpret_cast<float4*>(grad_out + e0 + 4) = make_float4(acc[4] * gs, acc[5] * gs, acc[6] * gs, acc[7] * gs);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[st]);  // the stage may be refilled while we do the optimizer math
+      if (++st == stages) { st = 0; ph ^= 1; }
+      if (e0 >= n) continue;
+      if (do_adam) {
+        float pw[8];
+        const float4 m0 = *reinterpret_cast<const float4*>(m + e0), m1 = *reinterpret_cast<const float4*>(m + e0 + 4);
+        const float4 v0 = *reinterpret_cast<const float4*>(v + e0), v1 = *reinterpret_cast<const float4*>(v + e0 + 4);
+        const float4 p0 = *reinterpret_cast<const float4*>(master + e0), p1 = *reinterpret_cast<const float4*>(master + e0 + 4);
+        float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+        float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+        float pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float g = acc[k] * gs;
+          mm[k] = mm[k] * a.beta1 + (1.f - a.beta1) * g;
+          vv[k] = vv[k] * a.beta2 + (1.f - a.beta2) * g * g;
+          float p = pp[k] * (1.f - a.lr * a.weight_decay);
+          p -= (a.lr / a.bias_c1) * (mm[k] / (sqrtf(vv[k] / a.bias_c2) + a.eps));
+          pw[k] = p;
+        }
+        *reinterpret_cast<float4*>(m + e0) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+        *reinterpret_cast<float4*>(m + e0 + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
+        *reinterpret_cast<float4*>(v + e0) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        *reinterpret_cast<float4*>(v + e0 + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+        *reinterpret_cast<float4*>(master + e0) = make_float4(pw[0], pw[1], pw[2], pw[3]);
+        *reinterpret_cast<float4*>(master + e0 + 4) = make_float4(pw[4], pw[5], pw[6], pw[7]);
+        uint4 o;
+        o.x = f2_to_bf2(pw[0], pw[1]); o.y = f2_to_bf2(pw[2], pw[3]);
+        o.z = f2_to_bf2(pw[4], pw[5]); o.w = f2_to_bf2(pw[6], pw[7]);
+        *reinterpret_cast<uint4*>(shard + e0) = o;
+      } else {
+        *reinterpret_cast<float4*>(grad_out + e0) = make_float4(acc[0] * gs, acc[1] * gs, acc[2] * gs, acc[3] * gs);
+        *reinterpret_cast<float4*>(grad_out + e0 + 4) = make_float4(acc[4] * gs, acc[5] * gs, acc[6] * gs, acc[7] * gs);
+      }
     }
   }
   // (2) my shard is updated and I no longer read anybody's gradients; when every peer says the same,
@@ -315,8 +414,13 @@ B200_API int b200_allgather_pull(const void* const* peer_ptrs, int rank, int wor
   int rc = load_peers(P, peer_ptrs, world);
   if (rc) return rc;
   if (ctas <= 0) ctas = 32;
-  allgather_pull_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(P, rank, world, shard_off, shard_bytes,
-                                                                (uint8_t*)out, wait_channel, wait_epoch);
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA(cudaFuncSetAttribute(allgather_pull_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AG_SMEM));
+    attr = true;
+  }
+  allgather_pull_kernel<<<ctas, 32, AG_SMEM, (cudaStream_t)stream>>>(P, rank, world, shard_off, shard_bytes,
+                                                                     (uint8_t*)out, wait_channel, wait_epoch);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;
@@ -335,10 +439,18 @@ B200_API int b200_reduce_scatter_adamw(const void* const* peer_ptrs, int rank, i
   if (rc) return rc;
   AdamArgs a{lr, beta1, beta2, eps, weight_decay, 1.f - powf(beta1, (float)step), 1.f - powf(beta2, (float)step),
              grad_scale};
-  if (ctas <= 0) ctas = 32;
-  reduce_scatter_adamw_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(
+  if (ctas <= 0) ctas = 148;
+  int stages = 24576 / (world * RS_TILE_BYTES);
+  stages = stages < 1 ? 1 : (stages > 3 ? 3 : stages);
+  const int smem = stages * world * RS_TILE_BYTES + 128 + 128;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA(cudaFuncSetAttribute(reduce_scatter_adamw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 8 * RS_TILE_BYTES + 256));
+    attr = true;
+  }
+  reduce_scatter_adamw_kernel<<<ctas, 160, smem, (cudaStream_t)stream>>>(
       P, rank, world, grad_off, n, (float*)master, (float*)m, (float*)v, param_off, (float*)grad_out, a, do_adam,
-      (const float*)clip_coef, ch_arrive, ch_done, epoch, (uint32_t*)counter);
+      (const float*)clip_coef, ch_arrive, ch_done, epoch, (uint32_t*)counter, stages);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;

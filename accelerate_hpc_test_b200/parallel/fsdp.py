@@ -204,11 +204,17 @@ class B200ShardedModule(nn.Module):
             # shards + dedicated root gradient buffers + pooled layer gradient buffers (+ slack for pool growth)
             need = total_shard * esz + sum(u.padded for u in root_units) * esz + (n_grad_bufs + 2) * max_layer * esz + 64 * 2**20
             self.ws = SymmetricWorkspace(self.group, need, self.device)
+            # gathers and reductions get their own streams: a reduce-scatter waits for its peers, and a
+            # prefetching all-gather must not queue behind that wait
             self.comm_stream = torch.cuda.Stream(device=self.device)
+            self.rs_stream = torch.cuda.Stream(device=self.device)
+            self.ag_ctas = int(os.environ.get("ACCELERATE_B200_AG_CTAS", "148"))
+            self.rs_ctas = int(os.environ.get("ACCELERATE_B200_RS_CTAS", "148"))
             self.ch_step = self.ws.new_channel()
         else:
             self.ws = None
             self.comm_stream = None
+            self.rs_stream = None
         # shards: bf16 parameter shard (symmetric), fp32 master + moments (local)
         for u in self._units:
             flat = torch.zeros(u.padded, dtype=self.param_dtype, device=self.device)
@@ -280,7 +286,7 @@ class B200ShardedModule(nn.Module):
             if ev is not None:
                 self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
-                self.ws.allgather_pull(u.shard_off, u.shard_numel * 2, u.full, stream=self.comm_stream)
+                self.ws.allgather_pull(u.shard_off, u.shard_numel * 2, u.full, ctas=self.ag_ctas, stream=self.comm_stream)
                 u.ag_event = torch.cuda.Event()
                 u.ag_event.record(self.comm_stream)
         else:
@@ -481,20 +487,20 @@ class B200ShardedModule(nn.Module):
 
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(self.device))
-            self.comm_stream.wait_event(ev)
+            self.rs_stream.wait_event(ev)
             e = self.ws.next_epoch(u.ch_arrive)
             self.ws._epochs[u.ch_done] = e
             if not fused and u.grad_shard is None:
                 u.grad_shard = torch.empty(u.shard_numel, dtype=torch.float32, device=self.device)
             h = self._adam_hyper() if fused else dict(lr=0.0, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0)
-            with torch.cuda.stream(self.comm_stream):
+            with torch.cuda.stream(self.rs_stream):
                 check(self.ws.lib.b200_reduce_scatter_adamw(
                     self.ws.peer_array, self.rank, self.world, u.grad_off, u.shard_numel, ptr(u.master), ptr(u.exp_avg),
                     ptr(u.exp_avg_sq), u.shard_off, ptr(u.grad_shard) if not fused else None, h["lr"], h["beta1"], h["beta2"], h["eps"],
                     h["weight_decay"], self.step_count + 1, scale, int(fused), None, u.ch_arrive, u.ch_done, e,
-                    self.ws.counter_ptr(u.ch_arrive), 32, ctypes.c_void_p(self.comm_stream.cuda_stream)), "reduce_scatter_adamw")
+                    self.ws.counter_ptr(u.ch_arrive), self.rs_ctas, ctypes.c_void_p(self.rs_stream.cuda_stream)), "reduce_scatter_adamw")
                 u.rs_event = torch.cuda.Event()
-                u.rs_event.record(self.comm_stream)
+                u.rs_event.record(self.rs_stream)
             u.updated_in_backward = fused
         else:
             full = u.grad.to(torch.float32)
@@ -503,13 +509,13 @@ class B200ShardedModule(nn.Module):
             u.grad_shard = full[lo : lo + u.shard_numel] * scale
             u.updated_in_backward = False
         if self.replicate_group is not None and not fused:
-            stream_ctx = torch.cuda.stream(self.comm_stream) if self.use_symm else contextlib.nullcontext()
+            stream_ctx = torch.cuda.stream(self.rs_stream) if self.use_symm else contextlib.nullcontext()
             with stream_ctx:
                 torch.distributed.all_reduce(u.grad_shard, group=self.replicate_group)
                 u.grad_shard /= torch.distributed.get_world_size(self.replicate_group)
                 if self.use_symm:
                     u.rs_event = torch.cuda.Event()
-                    u.rs_event.record(self.comm_stream)
+                    u.rs_event.record(self.rs_stream)
 
     # ------------------------------------------------------------------ optimizer integration
     def bind_optimizer(self, accelerated_optimizer):
@@ -548,9 +554,9 @@ class B200ShardedModule(nn.Module):
                 "Set ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD=0 when clipping is only used on some steps."
             )
         acc = torch.zeros(2, dtype=torch.float32, device=self.device)
-        ctx = torch.cuda.stream(self.comm_stream) if self.use_symm else contextlib.nullcontext()
+        ctx = torch.cuda.stream(self.rs_stream) if self.use_symm else contextlib.nullcontext()
         if self.use_symm:
-            self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+            self.rs_stream.wait_stream(torch.cuda.current_stream(self.device))
         with ctx:
             for u in self._units:
                 if u.grad_shard is not None:
@@ -560,7 +566,7 @@ class B200ShardedModule(nn.Module):
             coef = torch.ones(1, dtype=torch.float32, device=self.device)
             F.clip_coef_(acc, float(max_norm), norm, coef)
         if self.use_symm:
-            torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+            torch.cuda.current_stream(self.device).wait_stream(self.rs_stream)
         self._clip_coef = coef
         return norm.reshape(())
 
@@ -568,9 +574,9 @@ class B200ShardedModule(nn.Module):
         """Called by ``AcceleratedOptimizer.step``. Returns True if the step was skipped (never, for bf16)."""
         h = self._adam_hyper()
         self.step_count += 1
-        ctx = torch.cuda.stream(self.comm_stream) if self.use_symm else contextlib.nullcontext()
+        ctx = torch.cuda.stream(self.rs_stream) if self.use_symm else contextlib.nullcontext()
         if self.use_symm:
-            self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+            self.rs_stream.wait_stream(torch.cuda.current_stream(self.device))
         with ctx:
             for u in self._units:
                 if getattr(u, "updated_in_backward", False):
@@ -584,7 +590,8 @@ class B200ShardedModule(nn.Module):
                     u.shard.copy_(u.master)
             if self.use_symm:
                 # every rank's shards now hold version `step_count`: one barrier, then gathers need no handshake
-                self.ws.barrier(self.ch_step, stream=self.comm_stream)
+                self.ws.barrier(self.ch_step, stream=self.rs_stream)
+                self.comm_stream.wait_stream(self.rs_stream)
         self._clip_coef = None
         # first step ran in the safe mode; switch to the fused update if nobody asked for the gradients
         if self._fused_allowed and not self._fused and not self._saw_clip and os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto") == "auto":
