@@ -100,7 +100,7 @@ def check_collectives(ws, dev, rank, world):
     log("reduce_scatter+adamw ok")
     # ---- bandwidth numbers (CUDA events, max over ranks)
     res = {}
-    n = world * 8 * 16 * 2**20  # 256 MiB of bf16 per rank at world=2
+    n = 2**28  # 512 MiB of bf16
     off, buf = ws.alloc_tensor((n,), torch.bfloat16)
     buf.normal_()
     nccl_buf = buf.clone()
@@ -267,7 +267,7 @@ def main():
 
     what = sys.argv[1:] or ["coll", "ddp", "fsdp"]
     if "coll" in what:
-        ws = SymmetricWorkspace(dist.group.WORLD, 2 * 2**30, dev)
+        ws = SymmetricWorkspace(dist.group.WORLD, 3 * 2**30, dev)
         check_collectives(ws, dev, rank, world)
         ws.close()
     if "ddp" in what:
