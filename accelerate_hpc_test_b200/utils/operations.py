@@ -352,7 +352,8 @@ def reduce(tensor, reduction: str = "mean", scale: float = 1.0):
         cloned = t.clone()
         if state.distributed_type == DistributedType.NO:
             return cloned
-        cloned *= scale if cloned.is_floating_point() or scale == 1.0 else 1
+        if scale != 1.0 and cloned.is_floating_point():
+            cloned *= scale
         torch.distributed.all_reduce(cloned, torch.distributed.ReduceOp.SUM)
         if reduction == "mean":
             cloned = cloned / state.num_processes
