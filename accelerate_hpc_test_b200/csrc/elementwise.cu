@@ -456,3 +456,74 @@ B200_API int b200_add_inplace_bf16(void* y, const void* a, long long n, void* st
   B200_CHECK_LAUNCH();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// RMSNorm backward for callers that must not allocate.
+//
+// b200_rmsnorm_bwd() needs a [parts, H] fp32 scratch for the per-CTA partial sums of dW, and its
+// callers normally get that from an allocator.  Some callers cannot: a host whose device heap is
+// entirely owned by someone else's allocator (a fixed memory budget handed out at start-up, or a
+// framework caching allocator that must not be re-entered from the place this is called from, e.g.
+// inside one of its own callbacks), where cudaMalloc / cudaFree / a tensor allocation would fail,
+// deadlock, or break the budget.  For them the scratch lives in the library image itself: a
+// file-scope __device__ array of fixed size.  Every GPU that loads libb200.so holds those
+// NOALLOC_MAX_PARTS * NOALLOC_MAX_H * 4 bytes (8 MiB) until the process exits.
+//
+// Limits: H <= 8192 (larger H returns B200_ERR_TOO_LARGE); at most 256 partial rows are used, so
+// very long inputs run with fewer CTAs than b200_rmsnorm_bwd would pick.
+// Set-up: the first call on each device resolves the device address of the array with
+// cudaGetSymbolAddress (the array's name is only a host-side handle, never a pointer a kernel can
+// use) and caches it; make that first call before any stream capture begins on that device.
+// Sharing: all calls use the same array and it keeps whatever the previous call left in it.  Nothing
+// has to start at zero: each launch overwrites rows [0, parts) x [0, H) before its second kernel reads
+// them, and reads nothing else.  Two calls whose kernels overlap on the GPU (different streams with
+// no ordering between them) race on the array: serialise them.
+// No cudaMalloc, cudaFree or allocating library routine is called here.
+static constexpr int NOALLOC_MAX_PARTS = 256;
+static constexpr int NOALLOC_MAX_H = 8192;
+static __device__ __align__(256) float g_rmsnorm_bwd_noalloc_scratch[(size_t)NOALLOC_MAX_PARTS * NOALLOC_MAX_H];
+
+static int rmsnorm_noalloc_scratch(float** out) {
+  static float* cached[64] = {nullptr};
+  int dev = 0;
+  B200_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return B200_ERR_UNSUPPORTED;
+  if (cached[dev] == nullptr) {
+    void* p = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&p, g_rmsnorm_bwd_noalloc_scratch));
+    cached[dev] = static_cast<float*>(p);
+  }
+  *out = cached[dev];
+  return 0;
+}
+
+B200_API int b200_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const void* rstd, const void* dres,
+                                      void* dx, void* dw, long long T, int H, int accumulate_dw, void* stream) {
+  if (H % 8) return B200_ERR_BAD_ARG;
+  if (H > NOALLOC_MAX_H) return B200_ERR_TOO_LARGE;
+  if (T == 0) return 0;
+  float* scratch = nullptr;
+  int rc = rmsnorm_noalloc_scratch(&scratch);
+  if (rc) return rc;
+  long long want = (long long)num_sms() * 4;
+  if (want > NOALLOC_MAX_PARTS) want = NOALLOC_MAX_PARTS;
+  const int parts = (int)(T < want ? T : want);
+  const int nvec = H / 8;
+  const int vpt = (nvec + 255) / 256;
+  cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH_RB_NA(V)                                                                                \
+  rmsnorm_bwd_kernel<V><<<parts, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,       \
+                                               (const __nv_bfloat16*)w, (const float*)rstd,             \
+                                               (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, scratch, \
+                                               (int)T, H)
+  if (vpt <= 1) LAUNCH_RB_NA(1);
+  else if (vpt <= 2) LAUNCH_RB_NA(2);
+  else LAUNCH_RB_NA(4);
+#undef LAUNCH_RB_NA
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  rmsnorm_dw_reduce_kernel<<<ceil_div(H, 256), 256, 0, st>>>(scratch, (__nv_bfloat16*)dw, parts, H, accumulate_dw);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}

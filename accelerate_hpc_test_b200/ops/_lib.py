@@ -32,6 +32,7 @@ _SIGNATURES = {
     "b200_rmsnorm_fwd": [P, P, P, P, P, P, L, I, F, P],
     "b200_rmsnorm_bwd_parts": [L],
     "b200_rmsnorm_bwd": [P, P, P, P, P, P, P, P, L, I, I, P],
+    "b200_rmsnorm_bwd_noalloc": [P, P, P, P, P, P, P, L, I, I, P],
     "b200_rope_inplace": [P, P, P, P, L, L, I, I, I, P],
     "b200_swiglu_fwd": [P, P, L, I, P],
     "b200_swiglu_bwd": [P, P, P, L, I, P],

@@ -61,6 +61,14 @@ int b200_rmsnorm_fwd(const void* x, const void* res, const void* w, void* y, voi
 int b200_rmsnorm_bwd_parts(long long T); /* rows of fp32 scratch b200_rmsnorm_bwd needs: [parts, H] */
 int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, const void* rstd, const void* dres, void* dx, void* dw,
                      void* dw_partial_scratch, long long T, int H, int accumulate_dw, void* stream);
+/* No counterpart in the reference.  Same result as b200_rmsnorm_bwd for hosts that are not allowed to allocate
+ * where they call it (device heap owned by another allocator with a fixed budget, or a call made from inside that
+ * allocator's callback): the [parts, H] scratch is a fixed 8 MiB __device__ array inside the library instead of a
+ * caller buffer.  H <= 8192, else B200_ERR_TOO_LARGE; at most 256 partial rows.  The first call on a device looks up
+ * the array's device address (cudaGetSymbolAddress) and must come before any stream capture on that device.  All calls
+ * share the array: nothing needs clearing between calls, but calls that overlap on the GPU race on it. */
+int b200_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const void* rstd, const void* dres, void* dx, void* dw,
+                             long long T, int H, int accumulate_dw, void* stream);
 int b200_rope_inplace(void* buf, const void* cos_tab, const void* sin_tab, const void* pos, long long T, long long row_stride,
                       int n_heads, int D, int backward, void* stream);
 int b200_swiglu_fwd(const void* gate_up, void* act, long long T, int I, void* stream);
