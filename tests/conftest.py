@@ -3,6 +3,10 @@
 import os
 import sys
 
+# debug_launcher forks the test process: keep torch single-threaded so no OpenMP pool exists to deadlock the children
+os.environ.setdefault("OMP_NUM_THREADS", "1")
+os.environ.setdefault("MKL_NUM_THREADS", "1")
+
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
