@@ -670,6 +670,8 @@ class FullyShardedDataParallelPlugin:
         if self.fsdp_version == 1:
             if self.sharding_strategy is None:
                 self.sharding_strategy = os.environ.get(p + "SHARDING_STRATEGY", "FULL_SHARD")
+            if isinstance(self.sharding_strategy, int) and not isinstance(self.sharding_strategy, bool):
+                self.sharding_strategy = str(self.sharding_strategy)
             if isinstance(self.sharding_strategy, str):
                 s = self.sharding_strategy.upper()
                 if s.isdigit():
