@@ -1,0 +1,336 @@
+// 2-CTA ("cta_group::2") persistent bf16 GEMM for sm_100a: a cluster of two CTAs (one SM pair) computes a
+// 256 x 256 tile.  Each CTA stages its own 128 rows of A and *half* of the B tile (128 of the 256 n-rows), the
+// leader issues tcgen05.mma.cta_group::2 (M = 256) reading B from both CTAs' shared memory, and each CTA keeps its
+// 128 x 256 fp32 half of the accumulator in its own TMEM.  Compared with the 1-CTA kernel (gemm_tcgen05.cu) the
+// per-CTA operand traffic drops from 48 KB to 32 KB per k-block, which buys 6 pipeline stages instead of 4 and
+// halves the B reads from L2.  Same operand layouts and epilogue options as b200_gemm_bf16.
+#include "common.cuh"
+
+namespace b200 {
+
+int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long long outer, long long row_stride,
+                      int box_inner, int box_outer);
+int num_sms();
+
+namespace g2 {
+
+static constexpr int BM = 128;   // rows per CTA (256 per cluster)
+static constexpr int BN = 256;   // columns per cluster tile
+static constexpr int BNH = 128;  // B rows staged per CTA
+static constexpr int BK = 64;
+static constexpr int STAGES = 6;
+static constexpr int A_BYTES = BM * BK * 2;   // 16 KB
+static constexpr int B_BYTES = BNH * BK * 2;  // 16 KB
+static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+static constexpr int CHUNK = 64 * BK * 2;  // one MN-major 64 x 64 box
+static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 + 256;
+static constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address
+static constexpr int GROUP_M = 4;                   // in units of 256-row cluster tiles
+
+struct Params {
+  void* C;
+  const void* bias;
+  int M, N, K;
+  long long ldc;
+  int out_fp32, accumulate;
+  int num_m_tiles, num_n_tiles;
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load whose completion is signalled on the LEADER CTA's mbarrier
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const void* tmap, uint32_t leader_bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(leader_bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// arrive (once all earlier MMAs of this thread retired) on the same barrier in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_alloc_2sm(uint32_t* smem_result) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)), "n"(kCols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <uint32_t kCols>
+__device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+
+__device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& m_t, int& n_t) {
+  const int per_group = GROUP_M * num_n;
+  const int group = tile / per_group;
+  const int first_m = group * GROUP_M;
+  const int gm = min(GROUP_M, num_m - first_m);
+  const int r = tile - group * per_group;
+  m_t = first_m + (r % gm);
+  n_t = r / gm;
+}
+
+template <int A_MN, int B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * A_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* full_bar = bars;                    // [STAGES]  (only the leader's are waited on)
+  uint64_t* empty_bar = bars + STAGES;          // [STAGES]  per CTA, signalled by the multicast commit
+  uint64_t* tmem_full = bars + 2 * STAGES;      // [2]       per CTA, multicast commit
+  uint64_t* tmem_empty = bars + 2 * STAGES + 2; // [2]       leader's: 8 arrivals (4 epilogue warps x 2 CTAs)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = cta == 0;
+  const int num_k_blocks = (p.K + BK - 1) / BK;
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmap_a);
+    prefetch_tensormap(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 8);
+    }
+    fence_barrier_init();
+  }
+  cluster_sync_all();  // barriers of both CTAs exist before anybody signals across the pair
+  if (warp == 2) tmem_alloc_2sm<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================================ TMA producer (one per CTA) ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        int m_t, n_t;
+        tile_coords(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+        const int m0 = m_t * 256 + (int)cta * BM;
+        const int n0 = n_t * BN + (int)cta * BNH;
+        for (int kb = 0; kb < num_k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          const uint32_t lbar = smem_u32(&full_bar[stage]) & PEER_MASK;  // the leader's barrier
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+          uint8_t* sa = smem_a + stage * A_BYTES;
+          uint8_t* sb = smem_b + stage * B_BYTES;
+          const int k0 = kb * BK;
+          if (A_MN == 0) {
+            tma_load_2d_2sm(sa, &tmap_a, lbar, k0, m0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BM / 64; ++c) tma_load_2d_2sm(sa + c * CHUNK, &tmap_a, lbar, m0 + c * 64, k0);
+          }
+          if (B_MN == 0) {
+            tma_load_2d_2sm(sb, &tmap_b, lbar, k0, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BNH / 64; ++c) tma_load_2d_2sm(sb + c * CHUNK, &tmap_b, lbar, n0 + c * 64, k0);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer (leader CTA only) ================================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(256, BN, A_MN, B_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem_a + stage * A_BYTES);
+          const uint32_t sb = smem_u32(smem_b + stage * B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = A_MN == 0 ? make_umma_desc(sa + k * 32, 16, 1024) : make_umma_desc(sa + k * 16 * 128, CHUNK, 1024);
+            const uint64_t db = B_MN == 0 ? make_umma_desc(sb + k * 32, 16, 1024) : make_umma_desc(sb + k * 16 * 128, CHUNK, 1024);
+            umma_bf16_2sm(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_2sm(&empty_bar[stage]);
+          if (kb == num_k_blocks - 1) umma_commit_2sm(&tmem_full[acc]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ================================ epilogue (both CTAs, own 128 rows) ================================
+    const int e = warp - 4;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      int m_t, n_t;
+      tile_coords(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+      const int row = m_t * 256 + (int)cta * BM + e * 32 + lane;
+      const int n0 = n_t * BN;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + acc * BN;
+      const bool row_ok = row < p.M;
+      const bool vec_ok = (p.ldc % 8 == 0);
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(taddr + c, v);
+        tmem_ld_wait();
+        const int col0 = n0 + c;
+        if (row_ok && col0 < p.N) {
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+          if (p.bias != nullptr) {
+            const __nv_bfloat16* bias = reinterpret_cast<const __nv_bfloat16*>(p.bias);
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (col0 + i < p.N) f[i] += __bfloat162float(__ldg(bias + col0 + i));
+          }
+          if (p.out_fp32) {
+            float* crow = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + col0;
+            if (col0 + 32 <= p.N && (p.ldc % 4 == 0)) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 4) {
+                float4 o = make_float4(f[i], f[i + 1], f[i + 2], f[i + 3]);
+                if (p.accumulate) {
+                  float4 old = *reinterpret_cast<float4*>(crow + i);
+                  o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+                }
+                *reinterpret_cast<float4*>(crow + i) = o;
+              }
+            } else {
+              for (int i = 0; i < 32; ++i)
+                if (col0 + i < p.N) crow[i] = p.accumulate ? crow[i] + f[i] : f[i];
+            }
+          } else {
+            __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + (long long)row * p.ldc + col0;
+            if (col0 + 32 <= p.N && vec_ok) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 8) {
+                if (p.accumulate) {
+                  uint4 old = *reinterpret_cast<uint4*>(crow + i);
+                  float2 a0 = bf2_to_f2(old.x), a1 = bf2_to_f2(old.y), a2 = bf2_to_f2(old.z), a3 = bf2_to_f2(old.w);
+                  f[i] += a0.x; f[i + 1] += a0.y; f[i + 2] += a1.x; f[i + 3] += a1.y;
+                  f[i + 4] += a2.x; f[i + 5] += a2.y; f[i + 6] += a3.x; f[i + 7] += a3.y;
+                }
+                uint4 o;
+                o.x = f2_to_bf2(f[i], f[i + 1]); o.y = f2_to_bf2(f[i + 2], f[i + 3]);
+                o.z = f2_to_bf2(f[i + 4], f[i + 5]); o.w = f2_to_bf2(f[i + 6], f[i + 7]);
+                *reinterpret_cast<uint4*>(crow + i) = o;
+              }
+            } else {
+              for (int i = 0; i < 32; ++i)
+                if (col0 + i < p.N) {
+                  float o = f[i];
+                  if (p.accumulate) o += __bfloat162float(crow[i]);
+                  crow[i] = __float2bfloat16(o);
+                }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(smem_u32(&tmem_empty[acc]) & PEER_MASK);  // the leader's barrier
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();  // nobody frees TMEM / exits while the partner may still signal or read
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_2sm<512>(tmem_base);
+  }
+}
+
+template <int A_MN, int B_MN>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    B200_CUDA(cudaFuncSetAttribute(gemm2_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    attr_set = true;
+  }
+  int clusters = p.num_m_tiles * p.num_n_tiles;
+  const int max_clusters = num_sms() / 2;
+  if (clusters > max_clusters) clusters = max_clusters;
+  gemm2_kernel<A_MN, B_MN><<<clusters * 2, 256, SMEM, st>>>(ta, tb, p);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace g2
+}  // namespace b200
+
+// Same contract as b200_gemm_bf16 (see include/b200_ops.h); picked by the Python layer for plain GEMMs.
+B200_API int b200_gemm2_bf16(const void* A, const void* B, void* C, const void* bias, int M, int N, int K, long long lda,
+                             long long ldb, long long ldc, int a_mn_major, int b_mn_major, int out_fp32, int accumulate,
+                             void* stream) {
+  using namespace b200;
+  using namespace b200::g2;
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((lda % 8) || (ldb % 8) || (reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) return B200_ERR_BAD_ARG;
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = make_tmap_bf16_2d(&ta, A, K, M, lda, BK, BM);
+  else rc = make_tmap_bf16_2d(&ta, A, M, K, lda, 64, BK);
+  if (rc) return rc;
+  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BK, BNH);
+  else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  Params p;
+  p.C = C; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.num_m_tiles = (M + 255) / 256;
+  p.num_n_tiles = (N + BN - 1) / BN;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!a_mn_major && !b_mn_major) return launch<0, 0>(ta, tb, p, st);
+  if (!a_mn_major && b_mn_major) return launch<0, 1>(ta, tb, p, st);
+  if (a_mn_major && !b_mn_major) return launch<1, 0>(ta, tb, p, st);
+  return launch<1, 1>(ta, tb, p, st);
+}

@@ -38,7 +38,39 @@ struct GemmParams {
   int out_fp32;
   int accumulate;
   int num_m_blocks, num_n_blocks;
+  // ---- GEMM -> reduce-scatter: rows of D are scattered to the rank that owns them (rs_world > 0).
+  // Row r belongs to rank r / rs_rows; this rank's partial goes to slot rs_rank of the owner's buffer
+  // [rs_world][rs_rows][N] (bf16) at byte offset rs_off of its symmetric buffer.
+  uint8_t* rs_peer[8];
+  long long rs_off;
+  int rs_rows, rs_rank, rs_world;
+  // ---- all-gather -> GEMM: A is [ag_world * ag_rows, K] assembled in `ag_full` (local) from the
+  // ag_rows-row shards every rank keeps at byte offset ag_off + rank * shard_bytes of its symmetric
+  // buffer.  Warp 3 of every CTA pulls the peers' shards with cp.async.bulk while the tensor cores
+  // already work on the rows that are present; ag_ready[p] counts the bytes of shard p that landed.
+  uint8_t* ag_peer[8];
+  long long ag_off;
+  uint8_t* ag_full;
+  unsigned long long* ag_ready;
+  unsigned long long ag_expect;  // value ag_ready[p] reaches when shard p is complete (epoch * shard_bytes)
+  int ag_rows, ag_rank, ag_world;
 };
+
+static constexpr int AGG_CHUNK = 8192;
+static constexpr int AGG_STAGES = 3;
+static constexpr int AGG_SMEM = AGG_CHUNK * AGG_STAGES + 64;
+
+__device__ __forceinline__ void bulk_g2s_gemm(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g_gemm(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)),
+               "r"(bytes)
+               : "memory");
+}
 
 __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& m_blk, int& n_blk) {
   const int per_group = GROUP_M * num_n;
@@ -50,7 +82,14 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
   n_blk = r / gm;
 }
 
-template <int A_MN, int B_MN>
+// with the fused all-gather, visit the m-blocks of my own shard first, then the shards in arrival order
+__device__ __forceinline__ int ag_rotate(int m_blk, const GemmParams& p) {
+  const int per_shard = (p.ag_rows + BM - 1) / BM;
+  int r = m_blk + p.ag_rank * per_shard;
+  return r >= p.num_m_blocks ? r - p.num_m_blocks : r;
+}
+
+template <int A_MN, int B_MN, int FUSE_AG>
 __global__ void __launch_bounds__(256, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const GemmParams p) {
@@ -66,6 +105,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint64_t* tmem_full = bars + 2 * STAGES;    // [2]
   uint64_t* tmem_empty = bars + 2 * STAGES + 2;  // [2]
   uint32_t* tmem_base_smem = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* ag_bars = bars + 2 * STAGES + 6;                                   // [AGG_STAGES]
+  uint8_t* ag_ring = smem + STAGES * STAGE_BYTES + 256;                        // only with FUSE_AG
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -85,6 +126,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], 4);  // one arrive per epilogue warp
     }
+    if (FUSE_AG) {
+      for (int i = 0; i < AGG_STAGES; ++i) mbar_init(&ag_bars[i], 1);
+    }
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -103,7 +147,26 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int m_blk, n_blk;
         tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+        if (FUSE_AG) m_blk = ag_rotate(m_blk, p);
         const int m0 = m_blk * BM, n0 = n_blk * BN;
+        if (FUSE_AG) {
+          // rows [m0, m0 + BM) must have arrived: wait for the shard(s) they belong to
+          const int s_lo = m0 / p.ag_rows;
+          const int s_hi = min((m0 + BM - 1) / p.ag_rows, p.ag_world - 1);
+          for (int sh = s_lo; sh <= s_hi; ++sh) {
+            if (sh == p.ag_rank) continue;
+            uint32_t spins = 0;
+            while (*reinterpret_cast<volatile unsigned long long*>(p.ag_ready + sh) < p.ag_expect) {
+              __nanosleep(32);
+              if (++spins > kSpinLimit) {
+                printf("b200 gemm: all-gather shard %d never arrived (block %d)\n", sh, blockIdx.x);
+                __trap();
+              }
+            }
+          }
+          __threadfence();
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         for (int kb = 0; kb < num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
@@ -170,6 +233,60 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
       }
     }
+  } else if (FUSE_AG && warp == 3) {
+    // ================================ all-gather warp ================================
+    if (lane == 0 && p.ag_world > 1) {
+      const long long shard_bytes = (long long)p.ag_rows * p.K * 2;
+      const long long cps = (shard_bytes + AGG_CHUNK - 1) / AGG_CHUNK;
+      const long long total = cps * (p.ag_world - 1);
+      const long long n = (total > blockIdx.x) ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+      auto locate = [&](long long k, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes, int& peer) {
+        const long long g = blockIdx.x + k * (long long)gridDim.x;
+        const int slot = (int)(g / cps);
+        const long long c = g - (long long)slot * cps;
+        peer = (p.ag_rank + 1 + slot) % p.ag_world;
+        const long long o = c * AGG_CHUNK;
+        const long long left = shard_bytes - o;
+        bytes = (uint32_t)(left < AGG_CHUNK ? left : AGG_CHUNK);
+        src = p.ag_peer[peer] + p.ag_off + (long long)peer * shard_bytes + o;
+        dst = p.ag_full + (long long)peer * shard_bytes + o;
+      };
+      // loads run 2 chunks ahead; a chunk is accounted for once its store to local memory is complete
+      auto issue_load = [&](long long k) {
+        const uint8_t* src; uint8_t* dst; uint32_t bytes; int peer;
+        locate(k, src, dst, bytes, peer);
+        const int st = (int)(k % AGG_STAGES);
+        mbar_arrive_expect_tx(&ag_bars[st], bytes);
+        bulk_g2s_gemm(ag_ring + st * AGG_CHUNK, src, bytes, &ag_bars[st]);
+      };
+      for (long long k = 0; k < 2 && k < n; ++k) issue_load(k);
+      for (long long k = 0; k < n; ++k) {
+        const int st = (int)(k % AGG_STAGES);
+        mbar_wait(&ag_bars[st], (uint32_t)((k / AGG_STAGES) & 1));
+        const uint8_t* src; uint8_t* dst; uint32_t bytes; int peer;
+        locate(k, src, dst, bytes, peer);
+        bulk_s2g_gemm(dst, ag_ring + st * AGG_CHUNK, bytes);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        if (k >= 1) {
+          // store k-1 has completed: publish its bytes, and its ring slot may be refilled
+          asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
+          const uint8_t* s2; uint8_t* d2; uint32_t b2; int p2;
+          locate(k - 1, s2, d2, b2, p2);
+          asm volatile("fence.proxy.async;" ::: "memory");
+          __threadfence();
+          atomicAdd(p.ag_ready + p2, (unsigned long long)b2);
+        }
+        if (k + 2 < n) issue_load(k + 2);
+      }
+      if (n > 0) {
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        const uint8_t* s2; uint8_t* d2; uint32_t b2; int p2;
+        locate(n - 1, s2, d2, b2, p2);
+        asm volatile("fence.proxy.async;" ::: "memory");
+        __threadfence();
+        atomicAdd(p.ag_ready + p2, (unsigned long long)b2);
+      }
+    }
   } else if (warp >= 4) {
     // ================================ epilogue ================================
     const int e = warp - 4;  // == warp % 4 -> TMEM lane quadrant
@@ -178,6 +295,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int m_blk, n_blk;
       tile_coords(tile, p.num_m_blocks, p.num_n_blocks, m_blk, n_blk);
+      if (FUSE_AG) m_blk = ag_rotate(m_blk, p);
       const int row = m_blk * BM + e * 32 + lane;
       const int n0 = n_blk * BN;
       mbar_wait(&tmem_full[acc], acc_phase);
@@ -219,6 +337,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
           } else {
             __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + (long long)row * p.ldc + col0;
+            if (p.rs_world > 0) {
+              // scatter: this row lives on rank `owner`; my partial goes to my slot of its buffer
+              const int owner = row / p.rs_rows;
+              const long long lrow = (long long)p.rs_rank * p.rs_rows + (row - owner * p.rs_rows);
+              crow = reinterpret_cast<__nv_bfloat16*>(p.rs_peer[owner] + p.rs_off) + lrow * p.N + col0;
+            }
             if (col0 + 32 <= p.N && vec_ok) {
 #pragma unroll
               for (int i = 0; i < 32; i += 8) {
@@ -320,20 +444,21 @@ int num_sms() {
   return cached[dev];
 }
 
-template <int A_MN, int B_MN>
+template <int A_MN, int B_MN, int FUSE_AG = 0>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st,
                        int max_ctas) {
   static bool attr_set = false;
+  constexpr int smem_bytes = GEMM_SMEM + (FUSE_AG ? AGG_SMEM : 0);
   if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   GEMM_SMEM));
+    B200_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<A_MN, B_MN, FUSE_AG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   smem_bytes));
     attr_set = true;
   }
   int grid = p.num_m_blocks * p.num_n_blocks;
   int sms = num_sms();
   if (max_ctas > 0 && max_ctas < sms) sms = max_ctas;
   if (grid > sms) grid = sms;
-  gemm_bf16_kernel<A_MN, B_MN><<<grid, 256, GEMM_SMEM, st>>>(ta, tb, p);
+  gemm_bf16_kernel<A_MN, B_MN, FUSE_AG><<<grid, 256, smem_bytes, st>>>(ta, tb, p);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;
@@ -374,9 +499,109 @@ B200_API int b200_gemm_bf16(const void* A, const void* B, void* C, const void* b
   p.accumulate = accumulate;
   p.num_m_blocks = (M + BM - 1) / BM;
   p.num_n_blocks = (N + BN - 1) / BN;
+  p.rs_world = 0;
+  p.ag_world = 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (!a_mn_major && !b_mn_major) return launch_gemm<0, 0>(ta, tb, p, st, max_ctas);
   if (!a_mn_major && b_mn_major) return launch_gemm<0, 1>(ta, tb, p, st, max_ctas);
   if (a_mn_major && !b_mn_major) return launch_gemm<1, 0>(ta, tb, p, st, max_ctas);
   return launch_gemm<1, 1>(ta, tb, p, st, max_ctas);
+}
+
+
+// ---- tensor-parallel fused GEMMs --------------------------------------
+
+// All-gather -> GEMM in ONE kernel.  Every rank keeps its [rows, K] bf16 shard of A at byte offset
+// a_off + rank * rows*K*2 of its symmetric buffer (peer_ptrs: host array of the mapped bases) and has already written
+// its own shard there; `a_full` is the local [world*rows, K] assembly buffer whose own slot is also filled.
+// `ready` is a local array of `world` zero-initialised uint64 counters, `epoch` the 1-based use count of them.
+// D[world*rows, N] = A_full x B^T with B as in b200_gemm_bf16.
+B200_API int b200_gemm_bf16_allgather_a(const void* const* peer_ptrs, int rank, int world, long long a_off, void* a_full,
+                                        int rows, const void* B, void* C, int N, int K, long long ldb, long long ldc,
+                                        int b_mn_major, void* ready, unsigned long long epoch, void* stream) {
+  using namespace b200;
+  if (world < 1 || world > 8 || rows <= 0 || (K % 8) || (ldb % 8)) return B200_ERR_BAD_ARG;
+  const int M = rows * world;
+  CUtensorMap ta, tb;
+  int rc;
+  if ((rc = make_tmap_bf16_2d(&ta, a_full, K, M, K, BK, BM))) return rc;
+  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BK, BN);
+  else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  GemmParams p;
+  p.C = C; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = 0; p.accumulate = 0;
+  p.num_m_blocks = (M + BM - 1) / BM; p.num_n_blocks = (N + BN - 1) / BN;
+  p.rs_world = 0;
+  for (int i = 0; i < 8; ++i) p.ag_peer[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
+  p.ag_off = a_off; p.ag_full = (uint8_t*)a_full; p.ag_ready = (unsigned long long*)ready;
+  p.ag_expect = epoch * (unsigned long long)rows * K * 2; p.ag_rows = rows; p.ag_rank = rank; p.ag_world = world;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!b_mn_major) return launch_gemm<0, 0, 1>(ta, tb, p, st, 0);
+  return launch_gemm<0, 1, 1>(ta, tb, p, st, 0);
+}
+
+// GEMM -> reduce-scatter, first half: D = A x B^T is never written locally; the epilogue stores row r of this rank's
+// partial straight into slot `rank` of the owner's [world][rows][N] bf16 buffer (byte offset out_off of its symmetric
+// buffer) over NVLink.  After a cross-rank barrier, b200_reduce_slots folds the slots on the owner.
+B200_API int b200_gemm_bf16_scatter(const void* A, const void* B, const void* const* peer_ptrs, int rank, int world,
+                                    long long out_off, int rows, int N, int K, long long lda, long long ldb, int a_mn_major,
+                                    int b_mn_major, void* stream) {
+  using namespace b200;
+  if (world < 1 || world > 8 || rows <= 0 || (N % 8) || (lda % 8) || (ldb % 8)) return B200_ERR_BAD_ARG;
+  const int M = rows * world;
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = make_tmap_bf16_2d(&ta, A, K, M, lda, BK, BM);
+  else rc = make_tmap_bf16_2d(&ta, A, M, K, lda, 64, BK);
+  if (rc) return rc;
+  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BK, BN);
+  else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  GemmParams p;
+  p.C = nullptr; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = N; p.out_fp32 = 0; p.accumulate = 0;
+  p.num_m_blocks = (M + BM - 1) / BM; p.num_n_blocks = (N + BN - 1) / BN;
+  p.ag_world = 0;
+  for (int i = 0; i < 8; ++i) p.rs_peer[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
+  p.rs_off = out_off; p.rs_rows = rows; p.rs_rank = rank; p.rs_world = world;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!a_mn_major && !b_mn_major) return launch_gemm<0, 0>(ta, tb, p, st, 0);
+  if (!a_mn_major && b_mn_major) return launch_gemm<0, 1>(ta, tb, p, st, 0);
+  if (a_mn_major && !b_mn_major) return launch_gemm<1, 0>(ta, tb, p, st, 0);
+  return launch_gemm<1, 1>(ta, tb, p, st, 0);
+}
+
+namespace b200 {
+// out[r, :] = sum_s slots[s][r, :]   (bf16 in, fp32 accumulate, bf16 out)
+__global__ void __launch_bounds__(256)
+reduce_slots_kernel(const __nv_bfloat16* __restrict__ slots, __nv_bfloat16* __restrict__ out, int world, long long per_slot_vec) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_slot_vec;
+       i += (long long)gridDim.x * blockDim.x) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int s = 0; s < world; ++s) {
+      const uint4 v = ld_nc_v4(reinterpret_cast<const uint4*>(slots) + (long long)s * per_slot_vec + i);
+      float2 t;
+      t = bf2_to_f2(v.x); acc[0] += t.x; acc[1] += t.y;
+      t = bf2_to_f2(v.y); acc[2] += t.x; acc[3] += t.y;
+      t = bf2_to_f2(v.z); acc[4] += t.x; acc[5] += t.y;
+      t = bf2_to_f2(v.w); acc[6] += t.x; acc[7] += t.y;
+    }
+    uint4 o;
+    o.x = f2_to_bf2(acc[0], acc[1]); o.y = f2_to_bf2(acc[2], acc[3]);
+    o.z = f2_to_bf2(acc[4], acc[5]); o.w = f2_to_bf2(acc[6], acc[7]);
+    st_v4(reinterpret_cast<uint4*>(out) + i, o);
+  }
+}
+}  // namespace b200
+
+B200_API int b200_reduce_slots(const void* slots, void* out, int world, long long elems_per_slot, void* stream) {
+  if (elems_per_slot % 8) return B200_ERR_BAD_ARG;
+  if (elems_per_slot == 0) return 0;
+  long long nv = elems_per_slot / 8;
+  long long g = (nv + 255) / 256;
+  long long cap = (long long)b200::num_sms() * 8;
+  if (g > cap) g = cap;
+  b200::reduce_slots_kernel<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)slots, (__nv_bfloat16*)out, world, nv);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
 }

@@ -132,8 +132,8 @@ class LlamaAttention(nn.Module):
         c = self.cfg
         qkv = self.qkv_proj(x)
         cos, sin, pos = rope
-        attn = F.rope_attention(qkv, cos, sin, pos, B, S, c.num_attention_heads, c.num_key_value_heads, c.head_dim,
-                                causal=True)
+        hq, hkv = getattr(self, "tp_heads", (c.num_attention_heads, c.num_key_value_heads))  # local heads under TP
+        attn = F.rope_attention(qkv, cos, sin, pos, B, S, hq, hkv, c.head_dim, causal=True)
         return self.o_proj(attn)
 
 
@@ -192,6 +192,11 @@ class LlamaModel(nn.Module):
             max_pos = self.cfg.max_position_embeddings
         rope = self.rope(position_ids, max_pos)
         x = F.embedding(input_ids, self.embed_tokens.weight).view(B * S, -1)
+        tp = getattr(self, "tp_comm", None)
+        if tp is not None and tp.world > 1:
+            from ..parallel.tensor_parallel import scatter_tokens
+
+            x = scatter_tokens(x, tp)  # activations between blocks are token-sharded (sequence parallel)
         residual = None
         for layer in self.layers:
             if self.gradient_checkpointing and self.training and torch.is_grad_enabled():
@@ -199,6 +204,8 @@ class LlamaModel(nn.Module):
             else:
                 x, residual = layer(x, residual, rope, B, S)
         h, _ = self.norm(x, residual)
+        if tp is not None and tp.world > 1:
+            return h  # [B*S / tp, H]: the caller works on this rank's token shard
         return h.view(B, S, -1)
 
 
@@ -257,12 +264,32 @@ class LlamaForCausalLM(nn.Module):
         if shift_labels is None and labels is not None:
             shift_labels = torch.full_like(labels, -100)
             shift_labels[:, :-1] = labels[:, 1:]
+        tp = getattr(self, "tp_comm", None)
+        if tp is not None and tp.world > 1:
+            return self._tp_loss(h, shift_labels, tp)
         if shift_labels is not None:
             loss = F.fused_linear_cross_entropy(h.reshape(-1, h.shape[-1]), self.lm_head.weight,
                                                 shift_labels.reshape(-1), -100, self.config.loss_chunk_tokens)
         if return_logits or shift_labels is None:
             logits = self.lm_head(h)
         return CausalLMOutput(loss=loss, logits=logits)
+
+    def _tp_loss(self, h_shard, shift_labels, tp):
+        """Loss over this rank's token shard, combined over the TP group into the global token mean."""
+        if shift_labels is None:
+            from ..parallel.tensor_parallel import gather_tokens
+
+            return CausalLMOutput(loss=None, logits=self.lm_head(gather_tokens(h_shard, tp)))
+        lab = shift_labels.reshape(-1)
+        t = lab.numel() // tp.world
+        lab = lab[tp.rank * t : (tp.rank + 1) * t]
+        local = F.fused_linear_cross_entropy(h_shard, self.lm_head.weight, lab, -100, self.config.loss_chunk_tokens)
+        cnt = (lab != -100).sum().to(torch.float32)
+        tot = tp.all_reduce_(cnt.clone())
+        part = local * (cnt / tot.clamp(min=1.0))
+        whole = tp.all_reduce_(part.detach().clone())
+        # value = global mean; gradient flows through the local part only (the other ranks own theirs)
+        return CausalLMOutput(loss=part + (whole - part.detach()))
 
     # ------------------------------------------------------------------ transformers interchange
     def hf_state_dict(self) -> dict:

@@ -17,6 +17,8 @@ from __future__ import annotations
 import math
 from typing import Optional
 
+import os
+
 import torch
 
 from . import _lib
@@ -96,6 +98,16 @@ def gemm(
     b = _rowmajor2d(b)
     if bias is not None:
         bias = bias.to(BF16).contiguous()
+    if _GEMM_2CTA and max_ctas == 0 and M > 128:
+        # SM-pair kernel (cta_group::2, 256x256 tiles, 6 stages): the default for plain GEMMs
+        check(
+            lib.b200_gemm2_bf16(
+                ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, a.stride(0), b.stride(0), out.stride(0),
+                int(a_mn_major), int(b_mn_major), int(out_dtype == torch.float32), int(accumulate), cur_stream(),
+            ),
+            "gemm2_bf16",
+        )
+        return out
     check(
         lib.b200_gemm_bf16(
             ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, a.stride(0), b.stride(0), out.stride(0),
@@ -105,6 +117,9 @@ def gemm(
         "gemm_bf16",
     )
     return out
+
+
+_GEMM_2CTA = os.environ.get("ACCELERATE_B200_GEMM_2CTA", "1") != "0"
 
 
 def deliver_weight_grad(weight: torch.Tensor, compute):

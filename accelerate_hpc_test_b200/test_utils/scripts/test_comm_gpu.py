@@ -257,6 +257,91 @@ def check_fsdp(dev, rank, world, fused_env):
     GradientState._reset_state()
 
 
+def check_tp(dev, rank, world):
+    """Fused all-gather->GEMM / GEMM->reduce-scatter against NCCL + a plain matmul, then a TP Llama against one GPU."""
+    from accelerate_hpc_test_b200.models import LlamaConfig, LlamaForCausalLM
+    from accelerate_hpc_test_b200.parallel.tensor_parallel import TPComm, apply_tensor_parallel
+
+    torch.manual_seed(11 + rank)
+    H, N, t = 512, 1024, 256
+    comm = TPComm(dist.group.WORLD, dev, H, 4096, fused=True)
+    for it in range(3):
+        x = torch.randn(t, H, device=dev).to(torch.bfloat16)
+        w = (torch.randn(N, H, device=dev) * 0.05).to(torch.bfloat16)
+        dist.broadcast(w, 0)
+        y, full = comm.ag_gemm(x, w)
+        ref_full = torch.empty(t * world, H, device=dev, dtype=torch.bfloat16)
+        dist.all_gather_into_tensor(ref_full, x)
+        torch.cuda.synchronize()
+        assert torch.equal(full, ref_full), "fused all-gather moved wrong data"
+        assert rel(y, ref_full.float() @ w.float().t()) < 1e-2, ("ag_gemm", rel(y, ref_full.float() @ w.float().t()))
+        # GEMM -> reduce-scatter: x2 [T, H] differs per rank (partial products)
+        x2 = torch.randn(t * world, H, device=dev).to(torch.bfloat16)
+        out = comm.gemm_rs(x2, w)
+        part = (x2.float() @ w.float().t())
+        ref = torch.empty(t, N, device=dev)
+        dist.reduce_scatter_tensor(ref, part)
+        torch.cuda.synchronize()
+        assert rel(out, ref) < 2e-2, ("gemm_rs", rel(out, ref))
+    log("fused ag->gemm and gemm->rs ok")
+    # timing at Llama-3-8B shapes: x [T/tp, 4096] -> qkv/gate_up column parallel
+    H, T = 4096, 8192
+    big = TPComm(dist.group.WORLD, dev, H, T, fused=True)
+    x = torch.randn(T // world, H, device=dev).to(torch.bfloat16)
+    w = (torch.randn(28672 // world, H, device=dev) * 0.02).to(torch.bfloat16)
+    xf = torch.randn(T, H, device=dev).to(torch.bfloat16)
+    wr = (torch.randn(H, 14336 // world, device=dev) * 0.02).to(torch.bfloat16)
+    xr = torch.randn(T, 14336 // world, device=dev).to(torch.bfloat16)
+    full = torch.empty(T, H, device=dev, dtype=torch.bfloat16)
+    rs_out = torch.empty(T // world, H, device=dev, dtype=torch.bfloat16)
+
+    def nccl_ag_gemm():
+        dist.all_gather_into_tensor(full, x)
+        return full @ w.t()
+
+    def nccl_gemm_rs():
+        yy = xr @ wr.t()
+        dist.reduce_scatter_tensor(rs_out, yy)
+        return rs_out
+
+    from accelerate_hpc_test_b200.ops import functional as F
+    for name, fn in (("fused_ag_gemm", lambda: big.ag_gemm(x, w)), ("nccl_ag_then_cublas", nccl_ag_gemm), ("gemm_only", lambda: F.gemm(xf, w)),
+                     ("fused_gemm_rs", lambda: big.gemm_rs(xr, wr)), ("cublas_then_nccl_rs", nccl_gemm_rs), ("gemm_only_rs_shape", lambda: F.gemm(xr, wr))):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        s, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(10):
+            fn()
+        e2.record()
+        torch.cuda.synchronize()
+        tt = torch.tensor([s.elapsed_time(e2) / 10], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        log(f"tp {name}: {tt.item():.3f} ms")
+    # whole model: TP Llama vs single-GPU replica
+    cfg = LlamaConfig.tiny(num_attention_heads=4, num_key_value_heads=2, hidden_size=512, intermediate_size=1024)
+    torch.manual_seed(0)
+    ref = LlamaForCausalLM(cfg, device=dev)
+    torch.manual_seed(0)
+    model = apply_tensor_parallel(LlamaForCausalLM(cfg, device=dev), dist.group.WORLD)
+    g = torch.Generator().manual_seed(5)
+    ids = torch.randint(0, cfg.vocab_size, (2, 256), generator=g).to(dev)
+    out = model(ids, labels=ids)
+    out.loss.backward()
+    r = ref(ids, labels=ids)
+    r.loss.backward()
+    torch.cuda.synchronize()
+    assert abs(out.loss.item() - r.loss.item()) < 2e-2 * abs(r.loss.item()), (out.loss.item(), r.loss.item())
+    gw = model.model.layers[1].self_attn.o_proj.weight.grad
+    gr = ref.model.layers[1].self_attn.o_proj.weight.grad
+    n = gr.shape[1] // world
+    assert rel(gw, gr[:, rank * n : (rank + 1) * n]) < 8e-2, rel(gw, gr[:, rank * n : (rank + 1) * n])
+    assert rel(model.lm_head.weight.grad, ref.lm_head.weight.grad) < 8e-2
+    log(f"tp llama ok (loss {out.loss.item():.4f} vs {r.loss.item():.4f})")
+
+
 def main():
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -265,7 +350,7 @@ def main():
     rank, world = dist.get_rank(), dist.get_world_size()
     from accelerate_hpc_test_b200.parallel.symm import SymmetricWorkspace
 
-    what = sys.argv[1:] or ["coll", "ddp", "fsdp"]
+    what = sys.argv[1:] or ["coll", "ddp", "fsdp", "tp"]
     if "coll" in what:
         ws = SymmetricWorkspace(dist.group.WORLD, 3 * 2**30, dev)
         check_collectives(ws, dev, rank, world)
@@ -275,6 +360,8 @@ def main():
     if "fsdp" in what:
         check_fsdp(dev, rank, world, "0")
         check_fsdp(dev, rank, world, "1")
+    if "tp" in what:
+        check_tp(dev, rank, world)
     dist.barrier()
     log("ALL MULTI-GPU CHECKS PASSED")
     dist.destroy_process_group()
