@@ -829,11 +829,15 @@ class Accelerator:
         shard_group = replicate_group = None
         if mesh is not None:
             names = mesh.mesh_dim_names or ()
-            if pc is not None and ("dp_shard" in names or "cp" in names):
+            if pc is not None and ("dp_shard" in names or "cp" in names or "sp" in names):
                 shard_group = mesh["dp_shard_cp"].get_group()
-            elif pc is not None and pc.total_size > 1:
-                # only tp/sp axes are active: nothing to shard over
-                shard_group = torch.distributed.new_group([self.process_index]) if False else None
+            elif "dp_replicate" not in names:
+                # only model-parallel axes (tp) are active: every rank keeps its whole (already tp-sharded) parameters.
+                # new_group is collective, so all ranks create all singleton groups in the same order.
+                for r in range(self.num_processes):
+                    g = torch.distributed.new_group([r])
+                    if r == self.process_index:
+                        shard_group = g
             if "dp_replicate" in names:
                 replicate_group = mesh["dp_replicate"].get_group()
         plugin.set_auto_wrap_policy(model)

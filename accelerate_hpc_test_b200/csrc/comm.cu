@@ -371,6 +371,105 @@ alltoall_pull_kernel(Peers peers, int rank, int world, long long send_off, long 
   }
 }
 
+// ------------------------------------------------------------------------------ Ulysses sequence <-> head exchange
+// The all-to-all of Ulysses sequence parallelism, with both layout changes folded into the copy (C6): the reference
+// path (DeepSpeed UlyssesSPAttentionHF) permutes to a contiguous send buffer, calls all_to_all_single and permutes
+// again.  Here every rank PULLS, row by row, exactly the column segments it needs from each peer's matrix and drops
+// them at their final place, with TMA bulk copies through a small smem ring (same engine-driven scheme as the
+// all-gather above, so the SMs stay free and the kernel co-resides with a GEMM).
+//   mode 0 (sequence-sharded -> head-sharded): peer p holds [B*S_loc, src_pitch]; I take, for every segment, the
+//          `bytes`-wide column block number `rank` and write it to row (b*S + p*S_loc + r) of my [B*S, dst_pitch].
+//   mode 1 (head-sharded -> sequence-sharded): peer p holds [B*S, src_pitch]; I take rows (b*S + rank*S_loc + r) and
+//          write each segment to column block number p of my [B*S_loc, dst_pitch].
+struct ExSeg {
+  long long src_base, dst_base, bytes;
+};
+struct ExSegs {
+  ExSeg s[3];
+  int n;
+};
+static constexpr int EX_CHUNK = 4096;
+static constexpr int EX_STAGES = 6;
+static constexpr int EX_AHEAD = 4;
+static constexpr int EX_SMEM = EX_CHUNK * EX_STAGES + 128 + 128;
+
+__global__ void __launch_bounds__(32)
+seq_head_exchange_kernel(Peers peers, int rank, int world, long long src_off, uint8_t* __restrict__ out, int mode, int B,
+                         int S_loc, long long src_pitch, long long dst_pitch, ExSegs segs, int ch_arrive, int ch_done,
+                         uint32_t epoch, uint32_t* __restrict__ counter) {
+  extern __shared__ uint8_t ex_smem_raw[];
+  uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ex_smem_raw) + 127) & ~(uintptr_t)127);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + EX_CHUNK * EX_STAGES);
+  if (blockIdx.x == 0) signal_all(peers, rank, world, ch_arrive, epoch);  // my source matrix is complete (stream order)
+  wait_all(peers, rank, world, ch_arrive, epoch);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < EX_STAGES; ++i) mbar_init(&bars[i], 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+  if (threadIdx.x == 0) {
+    int seg_chunks[3], chunks_per_row = 0;
+    for (int i = 0; i < segs.n; ++i) {
+      seg_chunks[i] = (int)((segs.s[i].bytes + EX_CHUNK - 1) / EX_CHUNK);
+      chunks_per_row += seg_chunks[i];
+    }
+    const long long rows = (long long)B * S_loc;
+    const long long per_peer = rows * chunks_per_row;
+    const long long total = per_peer * world;
+    const long long S = (long long)S_loc * world;
+    const long long n = (total > blockIdx.x) ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    auto locate = [&](long long k, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
+      const long long g = blockIdx.x + k * (long long)gridDim.x;
+      const int slot = (int)(g / per_peer);
+      long long rem = g - (long long)slot * per_peer;
+      const long long row = rem / chunks_per_row;
+      int c = (int)(rem - row * chunks_per_row);
+      int si = 0;
+      while (c >= seg_chunks[si]) { c -= seg_chunks[si]; ++si; }
+      const ExSeg sg = segs.s[si];
+      const long long o = (long long)c * EX_CHUNK;
+      const long long left = sg.bytes - o;
+      bytes = (uint32_t)(left < EX_CHUNK ? left : EX_CHUNK);
+      const int p = (rank + 1 + slot) % world;
+      const long long b = row / S_loc, r = row - b * S_loc;
+      if (mode == 0) {
+        src = peers.base[p] + src_off + row * src_pitch + sg.src_base + (long long)rank * sg.bytes + o;
+        dst = out + (b * S + (long long)p * S_loc + r) * dst_pitch + sg.dst_base + o;
+      } else {
+        src = peers.base[p] + src_off + (b * S + (long long)rank * S_loc + r) * src_pitch + sg.src_base + o;
+        dst = out + row * dst_pitch + sg.dst_base + (long long)p * sg.bytes + o;
+      }
+    };
+    auto issue_load = [&](long long k) {
+      const uint8_t* src; uint8_t* dst; uint32_t bytes;
+      locate(k, src, dst, bytes);
+      const int st = (int)(k % EX_STAGES);
+      mbar_arrive_expect_tx(&bars[st], bytes);
+      bulk_g2s(ring + st * EX_CHUNK, src, bytes, &bars[st]);
+    };
+    for (long long k = 0; k < EX_AHEAD && k < n; ++k) issue_load(k);
+    for (long long k = 0; k < n; ++k) {
+      if (k + EX_AHEAD < n) {
+        asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(EX_STAGES - EX_AHEAD - 1) : "memory");
+        issue_load(k + EX_AHEAD);
+      }
+      const int st = (int)(k % EX_STAGES);
+      mbar_wait(&bars[st], (uint32_t)((k / EX_STAGES) & 1));
+      const uint8_t* src; uint8_t* dst; uint32_t bytes;
+      locate(k, src, dst, bytes);
+      bulk_s2g(dst, ring + st * EX_CHUNK, bytes);
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  __syncwarp();
+  if (last_cta(counter)) {
+    __threadfence_system();
+    signal_all(peers, rank, world, ch_done, epoch);
+    wait_all(peers, rank, world, ch_done, epoch);  // every peer finished reading my source: it may be reused
+  }
+}
+
 static inline int load_peers(Peers& P, const void* const* peer_ptrs, int world) {
   if (world < 1 || world > MAX_RANKS) return B200_ERR_UNSUPPORTED;
   for (int i = 0; i < MAX_RANKS; ++i) P.base[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
@@ -487,6 +586,35 @@ B200_API int b200_alltoall_pull(const void* const* peer_ptrs, int rank, int worl
   if (ctas <= 0) ctas = 32;
   alltoall_pull_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(P, rank, world, send_off, block_bytes, (uint8_t*)out,
                                                                ch_arrive, ch_done, epoch, (uint32_t*)counter);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// segs: host array of 3*nseg long longs {src_base, dst_base, bytes}; all byte quantities multiples of 16
+B200_API int b200_seq_head_exchange(const void* const* peer_ptrs, int rank, int world, long long src_off, void* out, int mode,
+                                    int B, int S_loc, long long src_pitch, long long dst_pitch, const long long* segs, int nseg,
+                                    int ch_arrive, int ch_done, unsigned epoch, void* counter, int ctas, void* stream) {
+  if (nseg < 1 || nseg > 3 || (mode != 0 && mode != 1)) return B200_ERR_BAD_ARG;
+  if ((src_off | src_pitch | dst_pitch | (long long)(uintptr_t)out) % 16) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  ExSegs sg;
+  sg.n = nseg;
+  for (int i = 0; i < nseg; ++i) {
+    sg.s[i] = ExSeg{segs[3 * i], segs[3 * i + 1], segs[3 * i + 2]};
+    if ((sg.s[i].src_base | sg.s[i].dst_base | sg.s[i].bytes) % 16 || sg.s[i].bytes <= 0) return B200_ERR_BAD_ARG;
+  }
+  if (ctas <= 0) ctas = 148;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA(cudaFuncSetAttribute(seq_head_exchange_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EX_SMEM));
+    attr = true;
+  }
+  seq_head_exchange_kernel<<<ctas, 32, EX_SMEM, (cudaStream_t)stream>>>(P, rank, world, src_off, (uint8_t*)out, mode, B, S_loc,
+                                                                        src_pitch, dst_pitch, sg, ch_arrive, ch_done, epoch,
+                                                                        (uint32_t*)counter);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;

@@ -133,7 +133,18 @@ class LlamaAttention(nn.Module):
         qkv = self.qkv_proj(x)
         cos, sin, pos = rope
         hq, hkv = getattr(self, "tp_heads", (c.num_attention_heads, c.num_key_value_heads))  # local heads under TP
-        attn = F.rope_attention(qkv, cos, sin, pos, B, S, hq, hkv, c.head_dim, causal=True)
+        sp = getattr(self, "sp_comm", None)
+        cp = getattr(self, "cp_comm", None)
+        if sp is not None and sp.world > 1:
+            from ..parallel.ulysses import ulysses_attention
+
+            attn = ulysses_attention(qkv, cos, sin, pos, B, S, hq, hkv, c.head_dim, sp, causal=True)
+        elif cp is not None and cp.world > 1:
+            from ..parallel.context_parallel import cp_attention
+
+            attn = cp_attention(qkv, cos, sin, pos, B, S, hq, hkv, c.head_dim, cp)
+        else:
+            attn = F.rope_attention(qkv, cos, sin, pos, B, S, hq, hkv, c.head_dim, causal=True)
         return self.o_proj(attn)
 
 
@@ -185,7 +196,16 @@ class LlamaModel(nn.Module):
 
     def forward(self, input_ids: torch.Tensor, position_ids: Optional[torch.Tensor] = None):
         B, S = input_ids.shape
-        if position_ids is None:
+        sp = getattr(self, "sp_comm", None)
+        cp = getattr(self, "cp_comm", None)
+        if position_ids is None and sp is not None and sp.world > 1:
+            # `input_ids` is this rank's contiguous S/sp slice of the sequence
+            position_ids = (torch.arange(S, device=input_ids.device) + sp.rank * S).unsqueeze(0).expand(B, S)
+            max_pos = S * sp.world
+        elif position_ids is None and cp is not None and cp.world > 1:
+            position_ids = cp.local_positions(S, input_ids.device).unsqueeze(0).expand(B, S)
+            max_pos = S * cp.world
+        elif position_ids is None:
             position_ids = torch.arange(S, device=input_ids.device).unsqueeze(0).expand(B, S)
             max_pos = S
         else:
@@ -261,18 +281,37 @@ class LlamaForCausalLM(nn.Module):
                 return_logits: bool = False, **_):
         h = self.model(input_ids, position_ids)
         loss = logits = None
+        given_shifted = shift_labels is not None
         if shift_labels is None and labels is not None:
             shift_labels = torch.full_like(labels, -100)
             shift_labels[:, :-1] = labels[:, 1:]
         tp = getattr(self, "tp_comm", None)
         if tp is not None and tp.world > 1:
             return self._tp_loss(h, shift_labels, tp)
+        seq = getattr(self, "sp_comm", None) or getattr(self, "cp_comm", None)
+        if seq is not None and seq.world > 1 and (shift_labels is not None or labels is not None):
+            return self._seq_sharded_loss(h, labels, shift_labels, seq, given_shifted=given_shifted)
         if shift_labels is not None:
             loss = F.fused_linear_cross_entropy(h.reshape(-1, h.shape[-1]), self.lm_head.weight,
                                                 shift_labels.reshape(-1), -100, self.config.loss_chunk_tokens)
         if return_logits or shift_labels is None:
             logits = self.lm_head(h)
         return CausalLMOutput(loss=loss, logits=logits)
+
+    def _seq_sharded_loss(self, h, labels, shift_labels, comm, given_shifted: bool):
+        """Loss when the sequence is sharded over an ``sp`` / ``cp`` group (each rank holds a slice of the tokens).
+
+        ``shift_labels`` supplied by the caller (dataloader adapter / ``maybe_context_parallel``) were shifted
+        before the sequence was cut.  Plain ``labels`` are shifted here, fetching the label that follows this
+        rank's last token from the rank holding the next slice."""
+        from ..parallel.ulysses import sp_loss
+
+        if not given_shifted:
+            shift_labels = comm.shift_labels_across_ranks(labels)
+        lab = shift_labels.reshape(-1)
+        local = F.fused_linear_cross_entropy(h.reshape(-1, h.shape[-1]), self.lm_head.weight, lab, -100,
+                                             self.config.loss_chunk_tokens)
+        return CausalLMOutput(loss=sp_loss(local, (lab != -100).sum(), comm))
 
     def _tp_loss(self, h_shard, shift_labels, tp):
         """Loss over this rank's token shard, combined over the TP group into the global token mean."""

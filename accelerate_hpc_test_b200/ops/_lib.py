@@ -29,6 +29,7 @@ U = ctypes.c_uint
 # name -> argtypes (restype is always int unless listed in _RESTYPES)
 _SIGNATURES = {
     "b200_gemm_bf16": [P, P, P, P, I, I, I, L, L, L, I, I, I, I, I, P],
+    "b200_seq_head_exchange": [P, I, I, L, P, I, I, I, L, L, P, I, I, I, U, P, I, P],
     "b200_gemm2_bf16": [P, P, P, P, I, I, I, L, L, L, I, I, I, I, P],
     "b200_gemm_bf16_allgather_a": [P, I, I, L, P, I, P, P, I, I, L, L, I, P, ctypes.c_ulonglong, P],
     "b200_gemm_bf16_scatter": [P, P, P, I, I, L, I, I, I, L, L, I, I, P],

@@ -94,6 +94,8 @@ class ParallelismConfig:
             dims.append("dp_shard")
         if self.cp_enabled:
             dims.append("cp")
+        if self.sp_enabled:
+            dims.append("sp")  # sequence shards are data shards for the sharded engine (cp and sp are exclusive)
         return dims
 
     @property

@@ -342,6 +342,80 @@ def check_tp(dev, rank, world):
     log(f"tp llama ok (loss {out.loss.item():.4f} vs {r.loss.item():.4f})")
 
 
+def check_seq(dev, rank, world):
+    """Ulysses exchange kernel against all_to_all_single + permutes; SP / CP Llama against one GPU."""
+    from accelerate_hpc_test_b200.models import LlamaConfig, LlamaForCausalLM
+    from accelerate_hpc_test_b200.parallel.context_parallel import apply_context_parallel, shard_sequence
+    from accelerate_hpc_test_b200.parallel.ulysses import SPComm, apply_ulysses
+
+    comm = SPComm(dist.group.WORLD, dev)
+    torch.manual_seed(21 + rank)
+    B, S_loc, Hq, Hkv, D = 2, 192, 2 * world, world, 128
+    widths = (Hq * D, Hkv * D, Hkv * D)
+    x = torch.randn(B * S_loc, sum(widths), device=dev).to(torch.bfloat16)
+    for it in range(3):
+        y = comm.exchange(x, 0, B, S_loc, widths)
+        y_ref = comm._exchange_reference(x, 0, B, S_loc, widths)
+        assert torch.equal(y, y_ref), "seq->head exchange mismatch"
+        z = comm.exchange(y, 1, B, S_loc, widths)
+        assert torch.equal(z, x), "head->seq exchange is not the inverse"
+        assert torch.equal(comm._exchange_reference(y, 1, B, S_loc, widths), x)
+    # timing at the Llama-3-8B shape (per layer: qkv forward exchange)
+    Bq, Sl, hq, hkv = 1, 8192 // world, 32, 8
+    wd = (hq * D, hkv * D, hkv * D)
+    xb = torch.randn(Bq * Sl, sum(wd), device=dev).to(torch.bfloat16)
+    for name, fn in (("exchange_kernel", lambda: comm.exchange(xb, 0, Bq, Sl, wd)),
+                     ("nccl_all_to_all+permutes", lambda: comm._exchange_reference(xb, 0, Bq, Sl, wd))):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        s, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(10):
+            fn()
+        e2.record()
+        torch.cuda.synchronize()
+        tt = torch.tensor([s.elapsed_time(e2) / 10], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        log(f"ulysses {name}: {tt.item():.3f} ms ({xb.numel() * 2 * (world - 1) / world / tt.item() / 1e6:.0f} GB/s ingress)")
+    log("ulysses exchange ok")
+
+    cfg = LlamaConfig.tiny(num_attention_heads=2 * world, num_key_value_heads=world, hidden_size=512, intermediate_size=1024)
+    torch.manual_seed(0)
+    ref = LlamaForCausalLM(cfg, device=dev)
+    g = torch.Generator().manual_seed(5)
+    S = 512
+    ids = torch.randint(0, cfg.vocab_size, (2, S), generator=g).to(dev)
+    r = ref(ids, labels=ids)
+    r.loss.backward()
+
+    def compare(model, tag, out):
+        torch.cuda.synchronize()
+        assert abs(out.loss.item() - r.loss.item()) < 2e-2 * abs(r.loss.item()), (tag, out.loss.item(), r.loss.item())
+        for name in ("model.layers.1.self_attn.qkv_proj.weight", "model.layers.0.mlp.down_proj.weight", "lm_head.weight"):
+            gw = dict(model.named_parameters())[name].grad.float().clone()
+            dist.all_reduce(gw)
+            gw /= world
+            gr = dict(ref.named_parameters())[name].grad
+            assert rel(gw, gr) < 8e-2, (tag, name, rel(gw, gr))
+        log(f"{tag} llama ok (loss {out.loss.item():.4f} vs {r.loss.item():.4f})")
+
+    torch.manual_seed(0)
+    sp_model = apply_ulysses(LlamaForCausalLM(cfg, device=dev), dist.group.WORLD)
+    c = S // world
+    out = sp_model(ids[:, rank * c : (rank + 1) * c].contiguous(), labels=ids[:, rank * c : (rank + 1) * c].contiguous())
+    out.loss.backward()
+    compare(sp_model, "ulysses", out)
+
+    torch.manual_seed(0)
+    cp_model = apply_context_parallel(LlamaForCausalLM(cfg, device=dev), dist.group.WORLD)
+    loc = shard_sequence(ids, 1, rank, world).contiguous()
+    out = cp_model(loc, labels=loc)
+    out.loss.backward()
+    compare(cp_model, "context-parallel", out)
+
+
 def main():
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -350,7 +424,7 @@ def main():
     rank, world = dist.get_rank(), dist.get_world_size()
     from accelerate_hpc_test_b200.parallel.symm import SymmetricWorkspace
 
-    what = sys.argv[1:] or ["coll", "ddp", "fsdp", "tp"]
+    what = sys.argv[1:] or ["coll", "ddp", "fsdp", "tp", "seq"]
     if "coll" in what:
         ws = SymmetricWorkspace(dist.group.WORLD, 3 * 2**30, dev)
         check_collectives(ws, dev, rank, world)
@@ -362,6 +436,8 @@ def main():
         check_fsdp(dev, rank, world, "1")
     if "tp" in what:
         check_tp(dev, rank, world)
+    if "seq" in what:
+        check_seq(dev, rank, world)
     dist.barrier()
     log("ALL MULTI-GPU CHECKS PASSED")
     dist.destroy_process_group()

@@ -41,6 +41,25 @@ int b200_memcpy_async(void* dst, const void* src, long long bytes, void* stream)
 int b200_gemm_bf16(const void* A, const void* B, void* C, const void* bias, int M, int N, int K, long long lda, long long ldb,
                    long long ldc, int a_mn_major, int b_mn_major, int out_fp32, int accumulate, int max_ctas, void* stream);
 
+/* Same contract on an SM pair: cluster of 2 CTAs, tcgen05.mma.cta_group::2, 256x256 tiles, 6 TMA stages
+ * (csrc/gemm2_tcgen05.cu).  The Python layer uses this one for plain GEMMs. */
+int b200_gemm2_bf16(const void* A, const void* B, void* C, const void* bias, int M, int N, int K, long long lda, long long ldb,
+                    long long ldc, int a_mn_major, int b_mn_major, int out_fp32, int accumulate, void* stream);
+
+/* ---- tensor-parallel fused compute+collective GEMMs over peer memory (csrc/gemm_tcgen05.cu)
+ * all-gather -> GEMM: every rank owns `rows` rows of A at byte offset a_off inside its symmetric workspace
+ * (peer_ptrs[r] = base of rank r's workspace mapped here).  A gather warp inside the GEMM pulls the remote shards
+ * into a_full with TMA bulk copies while the tensor cores already work on the local shard; ready[s] is bumped to
+ * `epoch` when shard s has landed.  C[world*rows, N] = gathered(A) @ B^T. */
+int b200_gemm_bf16_allgather_a(const void* const* peer_ptrs, int rank, int world, long long a_off, void* a_full, int rows,
+                               const void* B, void* C, int N, int K, long long ldb, long long ldc, int b_mn_major,
+                               unsigned* ready, unsigned long long epoch, void* stream);
+/* GEMM -> reduce-scatter: the epilogue stores the fp32 tile rows owned by rank d straight into d's slot `rank`
+ * (at byte offset out_off of d's workspace); after a device barrier each rank sums its `world` slots. */
+int b200_gemm_bf16_scatter(const void* A, const void* B, void* const* peer_ptrs, int rank, int world, long long out_off,
+                           int rows, int N, int K, long long lda, long long ldb, int a_mn_major, int b_mn_major, void* stream);
+int b200_reduce_slots(const void* slots, void* out_bf16, int world, long long elems_per_slot, void* stream);
+
 /* ---- K4: flash attention, head_dim 128, GQA, causal or full (csrc/flash_attn.cu)
  * q/k/v/o are [B*S, heads*128] views (row strides in elements); lse/delta are fp32 [B, Hq, S]. */
 int b200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, void* lse, int B, int S, int Hq, int Hkv, int D,

@@ -1,0 +1,41 @@
+"""Tensor parallelism on 2 CPU (gloo) ranks: sharded Llama vs the unsharded model — loss, replicated-parameter
+gradients after the TP all-reduce hook, and the local slices of column/row-sharded weight gradients
+(reference: accelerator.py:1592-1607 `_prepare_tp`, tests/tp/)."""
+
+import torch
+
+from accelerate_hpc_test_b200.launchers import debug_launcher
+
+
+def _tp_parity():
+    import torch.distributed as dist
+    from accelerate_hpc_test_b200 import PartialState
+    from accelerate_hpc_test_b200.models import LlamaConfig, LlamaForCausalLM
+    from accelerate_hpc_test_b200.parallel.tensor_parallel import apply_tensor_parallel
+    st = PartialState()
+    cfg = LlamaConfig.tiny(head_dim=32, hidden_size=64, intermediate_size=128, vocab_size=128, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2)
+    torch.manual_seed(0); ref = LlamaForCausalLM(cfg, dtype=torch.float32)
+    torch.manual_seed(0); model = LlamaForCausalLM(cfg, dtype=torch.float32)
+    model = apply_tensor_parallel(model, dist.group.WORLD)
+    g = torch.Generator().manual_seed(3)
+    ids = torch.randint(0, cfg.vocab_size, (2, 16), generator=g)
+    lab = ids.clone(); lab[0, :5] = -100
+    out = model(ids, labels=lab); out.loss.backward()
+    r = ref(ids, labels=lab); r.loss.backward()
+    assert abs(out.loss.item() - r.loss.item()) < 1e-5, (out.loss.item(), r.loss.item())
+    # replicated params: grads equal after the hook all-reduce
+    for n in ["model.norm.weight", "model.embed_tokens.weight", "lm_head.weight", "model.layers.0.input_layernorm.weight"]:
+        a = dict(model.named_parameters())[n].grad; b = dict(ref.named_parameters())[n].grad
+        assert torch.allclose(a, b, atol=1e-5), (n, (a-b).abs().max())
+    # sharded params: compare the local slice
+    w = model.model.layers[1].self_attn.o_proj.weight.grad
+    wr = ref.model.layers[1].self_attn.o_proj.weight.grad
+    n = wr.shape[1] // 2
+    assert torch.allclose(w, wr[:, st.process_index*n:(st.process_index+1)*n], atol=1e-5)
+    gu = model.model.layers[0].mlp.gate_up_proj.weight.grad; gur = ref.model.layers[0].mlp.gate_up_proj.weight.grad
+    I = cfg.intermediate_size; h = I // 2; k = st.process_index
+    assert torch.allclose(gu, torch.cat([gur[:I][k*h:(k+1)*h], gur[I:][k*h:(k+1)*h]]), atol=1e-5)
+
+
+def test_tensor_parallel_llama_two_processes():
+    debug_launcher(_tp_parity, num_processes=2)
