@@ -240,6 +240,15 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
          | ((uint32_t)(M >> 4) << 24);   // m_dim
 }
 
+// instruction descriptor for kind::f8f6f4, e4m3 x e4m3 -> fp32 (both operands K-major)
+__host__ __device__ constexpr uint32_t make_idesc_e4m3(int M, int N) {
+  return (1u << 4)                     // c_format = F32
+         | (0u << 7)                   // a_format = E4M3
+         | (0u << 10)                  // b_format = E4M3
+         | ((uint32_t)(N >> 3) << 17)  // n_dim
+         | ((uint32_t)(M >> 4) << 24); // m_dim
+}
+
 // ------------------------------------------------------------------ system-scope sync
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

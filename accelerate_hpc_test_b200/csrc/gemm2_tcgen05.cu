@@ -10,6 +10,8 @@ namespace b200 {
 
 int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long long outer, long long row_stride,
                       int box_inner, int box_outer);
+int make_tmap_u8_2d(CUtensorMap* out, const void* base, long long inner, long long outer, long long row_stride,
+                    int box_inner, int box_outer);
 int num_sms();
 
 namespace g2 {
@@ -34,6 +36,8 @@ struct Params {
   long long ldc;
   int out_fp32, accumulate;
   int num_m_tiles, num_n_tiles;
+  const float* deq_a;  // fp8 only: per-tensor dequantisation factors (device scalars), result *= deq_a * deq_b
+  const float* deq_b;
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -62,6 +66,14 @@ __device__ __forceinline__ void umma_bf16_2sm(uint32_t tmem_d, uint64_t da, uint
       : "memory");
 }
 // arrive (once all earlier MMAs of this thread retired) on the same barrier in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_e4m3_2sm(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(acc)
+      : "memory");
+}
 __device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
   asm volatile(
       "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
@@ -93,7 +105,9 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
   n_t = r / gm;
 }
 
-template <int A_MN, int B_MN>
+// FP8 = 1: operands are e4m3 bytes, K-major only; a k-block is still 128 bytes per row (128 elements), the MMA is
+// kind::f8f6f4 with K = 32 per instruction, and the epilogue applies the two per-tensor dequantisation factors.
+template <int A_MN, int B_MN, int FP8 = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const Params p) {
   extern __shared__ uint8_t smem_raw[];
@@ -110,7 +124,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();
   const bool leader = cta == 0;
-  const int num_k_blocks = (p.K + BK - 1) / BK;
+  constexpr int BKE = FP8 ? 128 : BK;  // elements per k-block
+  const int num_k_blocks = (p.K + BKE - 1) / BKE;
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
   const int cluster_id = blockIdx.x >> 1;
   const int num_clusters = gridDim.x >> 1;
@@ -153,7 +168,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
           if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
           uint8_t* sa = smem_a + stage * A_BYTES;
           uint8_t* sb = smem_b + stage * B_BYTES;
-          const int k0 = kb * BK;
+          const int k0 = kb * BKE;
           if (A_MN == 0) {
             tma_load_2d_2sm(sa, &tmap_a, lbar, k0, m0);
           } else {
@@ -173,7 +188,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   } else if (warp == 1) {
     // ================================ MMA issuer (leader CTA only) ================================
     if (leader && lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(256, BN, A_MN, B_MN);
+      constexpr uint32_t idesc = FP8 ? make_idesc_e4m3(256, BN) : make_idesc_bf16(256, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -191,7 +206,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t da = A_MN == 0 ? make_umma_desc(sa + k * 32, 16, 1024) : make_umma_desc(sa + k * 16 * 128, CHUNK, 1024);
             const uint64_t db = B_MN == 0 ? make_umma_desc(sb + k * 32, 16, 1024) : make_umma_desc(sb + k * 16 * 128, CHUNK, 1024);
-            umma_bf16_2sm(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            if (FP8) umma_e4m3_2sm(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            else umma_bf16_2sm(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit_2sm(&empty_bar[stage]);
           if (kb == num_k_blocks - 1) umma_commit_2sm(&tmem_full[acc]);
@@ -205,6 +221,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     const int e = warp - 4;
     int acc = 0;
     uint32_t acc_phase = 0;
+    float alpha = 1.f;
+    if (FP8) alpha = __ldg(p.deq_a) * __ldg(p.deq_b);
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       int m_t, n_t;
       tile_coords(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
@@ -225,6 +243,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
           float f[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+          if (FP8) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] *= alpha;
+          }
           if (p.bias != nullptr) {
             const __nv_bfloat16* bias = reinterpret_cast<const __nv_bfloat16*>(p.bias);
 #pragma unroll
@@ -289,17 +311,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   }
 }
 
-template <int A_MN, int B_MN>
+template <int A_MN, int B_MN, int FP8 = 0>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(gemm2_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    B200_CUDA(cudaFuncSetAttribute(gemm2_kernel<A_MN, B_MN, FP8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     attr_set = true;
   }
   int clusters = p.num_m_tiles * p.num_n_tiles;
   const int max_clusters = num_sms() / 2;
   if (clusters > max_clusters) clusters = max_clusters;
-  gemm2_kernel<A_MN, B_MN><<<clusters * 2, 256, SMEM, st>>>(ta, tb, p);
+  gemm2_kernel<A_MN, B_MN, FP8><<<clusters * 2, 256, SMEM, st>>>(ta, tb, p);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;
@@ -328,9 +350,35 @@ B200_API int b200_gemm2_bf16(const void* A, const void* B, void* C, const void* 
   p.C = C; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.num_m_tiles = (M + 255) / 256;
   p.num_n_tiles = (N + BN - 1) / BN;
+  p.deq_a = p.deq_b = nullptr;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (!a_mn_major && !b_mn_major) return launch<0, 0>(ta, tb, p, st);
   if (!a_mn_major && b_mn_major) return launch<0, 1>(ta, tb, p, st);
   if (a_mn_major && !b_mn_major) return launch<1, 0>(ta, tb, p, st);
   return launch<1, 1>(ta, tb, p, st);
+}
+
+// e4m3 x e4m3 -> bf16/fp32 with per-tensor scaling: D[M,N] (+)= deq_a * deq_b * sum_k A(m,k) B(n,k) (+ bias[n]).
+// A is [M,K] bytes (row stride lda), B is [N,K] bytes (row stride ldb): both K-major, strides multiples of 16.
+// deq_a / deq_b are device fp32 scalars (written by b200_quantize_e4m3).
+B200_API int b200_gemm2_e4m3(const void* A, const void* B, void* C, const void* bias, const void* deq_a, const void* deq_b, int M,
+                             int N, int K, long long lda, long long ldb, long long ldc, int out_fp32, int accumulate,
+                             void* stream) {
+  using namespace b200;
+  using namespace b200::g2;
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((lda % 16) || (ldb % 16) || (reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) || !deq_a || !deq_b)
+    return B200_ERR_BAD_ARG;
+  CUtensorMap ta, tb;
+  int rc = make_tmap_u8_2d(&ta, A, K, M, lda, 128, BM);
+  if (rc) return rc;
+  rc = make_tmap_u8_2d(&tb, B, K, N, ldb, 128, BNH);
+  if (rc) return rc;
+  Params p;
+  p.C = C; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.num_m_tiles = (M + 255) / 256;
+  p.num_n_tiles = (N + BN - 1) / BN;
+  p.deq_a = (const float*)deq_a;
+  p.deq_b = (const float*)deq_b;
+  return launch<0, 0, 1>(ta, tb, p, reinterpret_cast<cudaStream_t>(stream));
 }

@@ -435,6 +435,31 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long inner, long 
   return 0;
 }
 
+// same for a row-major byte matrix (fp8 operands): 128-byte swizzled boxes of `box_inner` bytes
+int make_tmap_u8_2d(CUtensorMap* out, const void* base, long long inner, long long outer, long long row_stride,
+                    int box_inner, int box_outer) {
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(0);
+    ctx_bound = true;
+  }
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return B200_ERR_DRIVER;
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)row_stride};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr, "b200: cuTensorMapEncodeTiled(u8) failed (CUresult %d): base=%p inner=%lld outer=%lld stride=%lld box=%dx%d\n",
+            (int)r, base, inner, outer, row_stride, box_inner, box_outer);
+    return B200_ERR_DRIVER;
+  }
+  return 0;
+}
+
 int num_sms() {
   static int cached[64] = {0};
   int dev = 0;
