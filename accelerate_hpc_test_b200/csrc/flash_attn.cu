@@ -14,6 +14,7 @@
 // and over 64-row query blocks. dK and dV accumulate in TMEM over the whole loop; S^T, dP^T and
 // dQ^T are per-iteration TMEM tiles; dQ is reduced with fp32 atomics into a scratch buffer.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -110,7 +111,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   const uint32_t tS = tmem_base, tO = tmem_base + 64;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_arrive_expect_tx(q_full, FWD_Q_BYTES);
       tma_load_2d(sQ, &tmap_q, q_full, hq * FA_D, row_base + q0);
       tma_load_2d(sQ + FWD_Q_BYTES / 2, &tmap_q, q_full, hq * FA_D + 64, row_base + q0);
@@ -128,7 +129,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc_s = make_idesc_bf16(128, FWD_BN, 0, 0);
       constexpr uint32_t idesc_o = make_idesc_bf16(128, FA_D, 0, 1);
       const uint32_t aQ = smem_u32(sQ), aK = smem_u32(sK), aV = smem_u32(sV), aP = smem_u32(sP);
@@ -282,25 +283,53 @@ flash_bwd_prep_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat1
 struct FaBwdParams {
   const float* lse;
   const float* delta;
-  float* dq_acc;  // [B*S, Hq*D] fp32, zero-initialised
+  float* dq_acc;  // [B, Hq, S_pad, D] fp32, zero-initialised; S_pad = S rounded up to 64
   __nv_bfloat16* dk;
   __nv_bfloat16* dv;
-  int B, S, Hq, Hkv;
+  int B, S, S_pad, Hq, Hkv;
   long long dkv_stride;
   float scale, scale_log2;
   int causal;
+  int dbg;
 };
 
+// One CTA owns a 128-row K/V block of one kv head and walks over the q blocks (64 rows) of its GQA group.
+// Per q block:   A:  S^T = K Q^T, dP^T = V dO^T                         (tensor cores -> TMEM stage it&1)
+//                    P^T = exp2(S^T*scale - lse), dS^T = P^T (dP^T - delta)   (8 softmax warps -> smem stage it&1)
+//                B:  dQ^T = K^T dS^T (into the S^T columns of the stage), dV += P^T dO, dK += dS^T Q
+//                    dQ tile: TMEM -> smem -> ONE bulk reduce-add into the fp32 accumulator  (4 readout warps)
+// A(it+1) is issued before B(it), the TMEM S/dP stage is double buffered, Q/dO sit in a 3-deep TMA ring, and the dQ
+// readout has its own warps, so the tensor cores run A(it+1) while the softmax warps work on `it`, and B(it) while
+// the readout warps drain dQ(it-1).  P^T / dS^T have a single smem buffer: the softmax warps compute both in
+// registers and only wait for B(it-1) to retire before the (short) stores.  dQ goes to global memory as a 32 KB cp.reduce.async.bulk (TMA engine) instead of 8192 scalar atomics
+// per q block, which is what bounded the first version of this kernel (L2 atomic throughput).
 static constexpr int BWD_BN = 128;  // kv rows per CTA
 static constexpr int BWD_BM = 64;   // q rows per iteration
 static constexpr int BWD_KV_BYTES = BWD_BN * FA_D * 2;   // 32 KB each for K and V
 static constexpr int BWD_QDO_BYTES = BWD_BM * FA_D * 2;  // 16 KB each for Q_i and dO_i
 static constexpr int BWD_STAGE_BYTES = 2 * BWD_QDO_BYTES;
 static constexpr int BWD_PT_BYTES = BWD_BN * BWD_BM * 2;  // 16 KB
-static constexpr int BWD_SMEM =
-    2 * BWD_KV_BYTES + 2 * BWD_STAGE_BYTES + 2 * BWD_PT_BYTES + 2 * 2 * BWD_BM * 4 + 1024 + 128;
+static constexpr int BWD_DQ_BYTES = BWD_BM * FA_D * 4;    // 32 KB fp32 staging tile [64 q][128 d]
+static constexpr int BWD_THREADS = 512;
+static constexpr int BWD_QSTAGES = 3;  // Q/dO ring: TMA latency spans more than one iteration
+static constexpr int BWD_SMEM = 2 * BWD_KV_BYTES + BWD_QSTAGES * BWD_STAGE_BYTES + 2 * BWD_PT_BYTES + BWD_DQ_BYTES +
+                                2 * 2 * BWD_BM * 4 + 256 + 1024;
 
-__global__ void __launch_bounds__(192, 1)
+// 32 bf16 values (half of a 128 B row) of a K-major SWIZZLE_128B tile: chunks 4*half .. 4*half+3
+__device__ __forceinline__ void store_half_row_sw128(uint8_t* tile, int row, int half, const float (&f)[32]) {
+  uint8_t* rp = tile + row * 128;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint4 o;
+    o.x = f2_to_bf2(f[c * 8 + 0], f[c * 8 + 1]);
+    o.y = f2_to_bf2(f[c * 8 + 2], f[c * 8 + 3]);
+    o.z = f2_to_bf2(f[c * 8 + 4], f[c * 8 + 5]);
+    o.w = f2_to_bf2(f[c * 8 + 6], f[c * 8 + 7]);
+    *reinterpret_cast<uint4*>(rp + ((((half << 2) + c) ^ (row & 7)) << 4)) = o;
+  }
+}
+
+__global__ void __launch_bounds__(BWD_THREADS, 1)
 flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                  const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_do,
                  const FaBwdParams p) {
@@ -308,20 +337,23 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sK = smem;
   uint8_t* sV = sK + BWD_KV_BYTES;
-  uint8_t* sQdO = sV + BWD_KV_BYTES;           // [2 stages][Q_i 16 KB | dO_i 16 KB]
-  uint8_t* sPt = sQdO + 2 * BWD_STAGE_BYTES;   // P^T   [128 kv x 64 q]
-  uint8_t* sdSt = sPt + BWD_PT_BYTES;          // dS^T  [128 kv x 64 q]
-  float* sLse = reinterpret_cast<float*>(sdSt + BWD_PT_BYTES);  // [2][64]
-  float* sDelta = sLse + 2 * BWD_BM;                             // [2][64]
+  uint8_t* sQdO = sV + BWD_KV_BYTES;                      // [3 stages][Q_i 16 KB | dO_i 16 KB]
+  uint8_t* sPt = sQdO + BWD_QSTAGES * BWD_STAGE_BYTES;    // P^T   [128 kv x 64 q]
+  uint8_t* sdSt = sPt + BWD_PT_BYTES;                     // dS^T  [128 kv x 64 q]
+  float* sDQ = reinterpret_cast<float*>(sdSt + BWD_PT_BYTES);  // [64 q][128 d] fp32
+  float* sLse = sDQ + BWD_BM * FA_D;            // [2][64]
+  float* sDelta = sLse + 2 * BWD_BM;            // [2][64]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sDelta + 2 * BWD_BM);
   uint64_t* kv_full = bars + 0;
-  uint64_t* qdo_full = bars + 1;   // [2]
-  uint64_t* qdo_empty = bars + 3;  // [2]
-  uint64_t* s_full = bars + 5;
-  uint64_t* pds_ready = bars + 6;
-  uint64_t* dq_full = bars + 7;
-  uint64_t* dkv_full = bars + 8;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  uint64_t* qdo_full = bars + 1;    // [3] TMA -> MMA
+  uint64_t* qdo_free = bars + 4;    // [3] B(it) retired: Q/dO stage it%3 may be refilled   MMA -> TMA
+  uint64_t* s_full = bars + 7;      // [2] A(it) retired            MMA -> softmax
+  uint64_t* pds_ready = bars + 9;   // [2] P^T / dS^T written       softmax (256) -> MMA
+  uint64_t* dq_full = bars + 11;    // [2] dQ^T(it) retired         MMA -> readout
+  uint64_t* dq_done = bars + 13;    // [2] dQ^T(it) is in registers: TMEM stage free       readout (128) -> MMA
+  uint64_t* pds_free = bars + 15;   //     B(it) retired: the P^T / dS^T buffer may be overwritten  MMA -> softmax
+  uint64_t* dkv_full = bars + 16;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kvb = blockIdx.x, hkv = blockIdx.y, b = blockIdx.z;
@@ -337,31 +369,37 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     prefetch_tensormap(&tmap_q); prefetch_tensormap(&tmap_k);
     prefetch_tensormap(&tmap_v); prefetch_tensormap(&tmap_do);
     mbar_init(kv_full, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(&qdo_full[i], 1); mbar_init(&qdo_empty[i], 1); }
-    mbar_init(s_full, 1); mbar_init(pds_ready, 128); mbar_init(dq_full, 1); mbar_init(dkv_full, 1);
+    for (int i = 0; i < BWD_QSTAGES; ++i) { mbar_init(&qdo_full[i], 1); mbar_init(&qdo_free[i], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1); mbar_init(&pds_ready[i], 256);
+      mbar_init(&dq_full[i], 1); mbar_init(&dq_done[i], 128);
+    }
+    mbar_init(pds_free, 1);
+    mbar_init(dkv_full, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<512>(tmem_slot);
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tdK = tmem_base, tdV = tmem_base + 128, tSt = tmem_base + 256, tdPt = tmem_base + 320,
-                 tdQt = tmem_base + 384;
+  const uint32_t tdK = tmem_base, tdV = tmem_base + 128;
+  // stage s: S^T (later dQ^T) at 256 + 128 s, dP^T at 320 + 128 s
 
   if (warp == 0) {
-    if (lane == 0) {
+    // ================================================= TMA producer
+    if (elect_one()) {
       mbar_arrive_expect_tx(kv_full, 2 * BWD_KV_BYTES);
       tma_load_2d(sK, &tmap_k, kv_full, hkv * FA_D, row_base + kv0);
       tma_load_2d(sK + BWD_KV_BYTES / 2, &tmap_k, kv_full, hkv * FA_D + 64, row_base + kv0);
       tma_load_2d(sV, &tmap_v, kv_full, hkv * FA_D, row_base + kv0);
       tma_load_2d(sV + BWD_KV_BYTES / 2, &tmap_v, kv_full, hkv * FA_D + 64, row_base + kv0);
+      int st = 0;
+      uint32_t ph = 0;
       for (int it = 0; it < n_iter; ++it) {
-        const int st = it & 1;
-        const uint32_t ph = (it >> 1) & 1;
         const int hq = hkv * G + it / per_head;
         const int qrow = row_base + (i_begin + it % per_head) * BWD_BM;
-        mbar_wait(&qdo_empty[st], ph ^ 1);
+        mbar_wait(&qdo_free[st], ph ^ 1);  // B(it-3) has consumed this stage
         mbar_arrive_expect_tx(&qdo_full[st], BWD_STAGE_BYTES);
         uint8_t* sq = sQdO + st * BWD_STAGE_BYTES;
         uint8_t* sd = sq + BWD_QDO_BYTES;
@@ -369,21 +407,23 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         tma_load_2d(sq + BWD_QDO_BYTES / 2, &tmap_q, &qdo_full[st], hq * FA_D + 64, qrow);
         tma_load_2d(sd, &tmap_do, &qdo_full[st], hq * FA_D, qrow);
         tma_load_2d(sd + BWD_QDO_BYTES / 2, &tmap_do, &qdo_full[st], hq * FA_D + 64, qrow);
+        if (++st == BWD_QSTAGES) { st = 0; ph ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // ================================================= MMA issuer
+    if (elect_one()) {
       constexpr uint32_t idesc_st = make_idesc_bf16(128, BWD_BM, 0, 0);  // K Q^T / V dO^T  (N = 64)
       constexpr uint32_t idesc_dkv = make_idesc_bf16(128, FA_D, 0, 1);   // P^T dO / dS^T Q  (N = 128)
       constexpr uint32_t idesc_dq = make_idesc_bf16(128, BWD_BM, 1, 1);  // K^T dS^T        (N = 64)
-      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aPt = smem_u32(sPt), adSt = smem_u32(sdSt);
-      mbar_wait(kv_full, 0);
-      for (int it = 0; it < n_iter; ++it) {
-        const int st = it & 1;
-        const uint32_t ph = (it >> 1) & 1;
-        const uint32_t aQ = smem_u32(sQdO + st * BWD_STAGE_BYTES);
+      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV);
+      auto issue_A = [&](int it) {
+        const int st = it & 1, qs = it % BWD_QSTAGES;
+        const uint32_t aQ = smem_u32(sQdO + qs * BWD_STAGE_BYTES);
         const uint32_t adO = aQ + BWD_QDO_BYTES;
-        mbar_wait(&qdo_full[st], ph);
+        const uint32_t tSt = tmem_base + 256 + st * 128, tdPt = tSt + 64;
+        mbar_wait(&qdo_full[qs], (it / BWD_QSTAGES) & 1);
+        mbar_wait(&dq_done[st], ((it >> 1) & 1) ^ 1);  // dQ^T(it-2) left this TMEM stage
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < FA_D / 16; ++k) {  // S^T = K Q^T
@@ -397,108 +437,106 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           const uint64_t db = make_umma_desc(adO + (k >> 2) * (BWD_QDO_BYTES / 2) + (k & 3) * 32, 16, 1024);
           umma_bf16_ss(tdPt, da, db, idesc_st, k > 0 ? 1u : 0u);
         }
-        umma_commit(s_full);
-        mbar_wait(pds_ready, it & 1);
+        umma_commit(&s_full[st]);
+      };
+      mbar_wait(kv_full, 0);
+      if (n_iter > 0) issue_A(0);
+      for (int it = 0; it < n_iter; ++it) {
+        const int st = it & 1, qs = it % BWD_QSTAGES;
+        if (it + 1 < n_iter) issue_A(it + 1);
+        const uint32_t aQ = smem_u32(sQdO + qs * BWD_STAGE_BYTES);
+        const uint32_t adO = aQ + BWD_QDO_BYTES;
+        const uint32_t aPt = smem_u32(sPt), adSt = smem_u32(sdSt);
+        const uint32_t tdQt = tmem_base + 256 + st * 128;
+        mbar_wait(&pds_ready[st], (it >> 1) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int k = 0; k < BWD_BM / 16; ++k) {  // dV += P^T dO ; dK += dS^T Q   (reduction over q rows)
+        for (int k = 0; k < BWD_BN / 16; ++k) {  // dQ^T[d, q] = sum_kv K[kv, d] dS^T[kv, q]  (first: its readout overlaps dV/dK)
+          const uint64_t da = make_umma_desc(aK + k * 16 * 128, BWD_KV_BYTES / 2, 1024);
+          const uint64_t db = make_umma_desc(adSt + k * 16 * 128, BWD_PT_BYTES, 1024);
+          umma_bf16_ss(tdQt, da, db, idesc_dq, k > 0 ? 1u : 0u);
+        }
+        umma_commit(&dq_full[st]);
+#pragma unroll
+        for (int k = 0; k < BWD_BM / 16; ++k) {  // dV += P^T dO   (reduction over the q rows)
           const uint64_t dap = make_umma_desc(aPt + k * 32, 16, 1024);
           const uint64_t dbo = make_umma_desc(adO + k * 16 * 128, BWD_QDO_BYTES / 2, 1024);
           umma_bf16_ss(tdV, dap, dbo, idesc_dkv, (it > 0 || k > 0) ? 1u : 0u);
         }
 #pragma unroll
-        for (int k = 0; k < BWD_BM / 16; ++k) {
+        for (int k = 0; k < BWD_BM / 16; ++k) {  // dK += dS^T Q
           const uint64_t das = make_umma_desc(adSt + k * 32, 16, 1024);
           const uint64_t dbq = make_umma_desc(aQ + k * 16 * 128, BWD_QDO_BYTES / 2, 1024);
           umma_bf16_ss(tdK, das, dbq, idesc_dkv, (it > 0 || k > 0) ? 1u : 0u);
         }
-#pragma unroll
-        for (int k = 0; k < BWD_BN / 16; ++k) {  // dQ^T[d, q] = sum_kv K[kv, d] dS^T[kv, q]
-          const uint64_t da = make_umma_desc(aK + k * 16 * 128, BWD_KV_BYTES / 2, 1024);
-          const uint64_t db = make_umma_desc(adSt + k * 16 * 128, BWD_PT_BYTES, 1024);
-          umma_bf16_ss(tdQt, da, db, idesc_dq, k > 0 ? 1u : 0u);
-        }
-        umma_commit(&qdo_empty[st]);
-        umma_commit(dq_full);
+        umma_commit(&qdo_free[qs]);
+        umma_commit(pds_free);
       }
       umma_commit(dkv_full);
     }
-  } else {
+  } else if (warp >= 4 && warp < 12) {
+    // ================================================= softmax / dS warps: 128 kv rows x two 32-column halves
     const int quad = warp & 3;
-    const int r = quad * 32 + lane;  // kv row inside the block, and d index for the dQ^T readout
-    const int tid = threadIdx.x - 64;  // 0..127
+    const int half = (warp - 4) >> 2;
+    const int r = quad * 32 + lane;     // kv row inside the block
+    const int tid = threadIdx.x - 128;  // 0..255
     const int kv_idx = kv0 + r;
     const bool kv_ok = kv_idx < p.S;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    // lse / delta of a q block are staged through smem; each of the first 128 threads prefetches its value one
+    // iteration ahead so the global-load latency is off the critical path (rows past S: lse = +inf -> p = 0)
+    auto fetch_stat = [&](int it) -> float {
+      if (tid >= 128 || it >= n_iter) return 0.f;
+      const int hq = hkv * G + it / per_head;
+      const int qi = (i_begin + it % per_head) * BWD_BM + (tid & 63);
+      const long long idx = ((long long)b * p.Hq + hq) * p.S + qi;
+      if (tid < 64) return (qi < p.S) ? p.lse[idx] * kLog2e : INFINITY;
+      return (qi < p.S) ? p.delta[idx] : 0.f;
+    };
+    float stat = fetch_stat(0);
     for (int it = 0; it < n_iter; ++it) {
       const int st = it & 1;
-      const int hq = hkv * G + it / per_head;
+      const uint32_t ph = (it >> 1) & 1;
       const int q0 = (i_begin + it % per_head) * BWD_BM;
-      // stage lse / delta of this q block (OOB rows get lse = +inf -> p = 0)
-      {
-        const int qi = q0 + (tid & 63);
-        const long long idx = ((long long)b * p.Hq + hq) * p.S + qi;
-        if (tid < 64) sLse[st * BWD_BM + tid] = (qi < p.S) ? p.lse[idx] * kLog2e : INFINITY;
-        else sDelta[st * BWD_BM + (tid - 64)] = (qi < p.S) ? p.delta[idx] : 0.f;
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      mbar_wait(s_full, it & 1);
+      if (tid < 64) sLse[st * BWD_BM + tid] = stat;
+      else if (tid < 128) sDelta[st * BWD_BM + (tid - 64)] = stat;
+      stat = fetch_stat(it + 1);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mbar_wait(&s_full[st], ph);
       tc_fence_after();
-      float pr[64];
+      const uint32_t tSt = tmem_base + 256 + st * 128 + half * 32, tdPt = tSt + 64;
+      const float* lse_s = sLse + st * BWD_BM + half * 32;
+      const float* del_s = sDelta + st * BWD_BM + half * 32;
+      const int qc = q0 + half * 32;
+      float pr[32], ds[32];
       {
-        uint32_t v0[32], v1[32];
-        tmem_ld_32x32b_x32(tSt + lane_addr, v0);
-        tmem_ld_32x32b_x32(tSt + lane_addr + 32, v1);
+        uint32_t v[32], w[32];
+        tmem_ld_32x32b_x32(tSt + lane_addr, v);
+        tmem_ld_32x32b_x32(tdPt + lane_addr, w);
         tmem_ld_wait();
         const bool diag = p.causal && (q0 < kv0 + BWD_BN);  // some (q, kv) pairs of this tile are masked
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          float a = exp2f(__uint_as_float(v0[i]) * p.scale_log2 - sLse[st * BWD_BM + i]);
-          float c = exp2f(__uint_as_float(v1[i]) * p.scale_log2 - sLse[st * BWD_BM + 32 + i]);
-          if (!kv_ok || (diag && (q0 + i < kv_idx))) a = 0.f;
-          if (!kv_ok || (diag && (q0 + 32 + i < kv_idx))) c = 0.f;
+          float a = exp2f(__uint_as_float(v[i]) * p.scale_log2 - lse_s[i]);
+          if (!kv_ok || (diag && (qc + i < kv_idx))) a = 0.f;
           pr[i] = a;
-          pr[32 + i] = c;
+          ds[i] = a * (__uint_as_float(w[i]) - del_s[i]);
         }
       }
-      store_row_sw128(sPt, r, pr);
-      {
-        uint32_t v0[32], v1[32];
-        tmem_ld_32x32b_x32(tdPt + lane_addr, v0);
-        tmem_ld_32x32b_x32(tdPt + lane_addr + 32, v1);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          pr[i] = pr[i] * (__uint_as_float(v0[i]) - sDelta[st * BWD_BM + i]);
-          pr[32 + i] = pr[32 + i] * (__uint_as_float(v1[i]) - sDelta[st * BWD_BM + 32 + i]);
-        }
-      }
-      store_row_sw128(sdSt, r, pr);
+      mbar_wait(pds_free, (it & 1) ^ 1);  // B(it-1) no longer reads the P^T / dS^T buffer
+      store_half_row_sw128(sPt, r, half, pr);
+      store_half_row_sw128(sdSt, r, half, ds);
       fence_proxy_async();
       tc_fence_before();
-      mbar_arrive(pds_ready);
-      // dQ^T readout: thread r owns feature d = r, columns are the 64 q rows of this block
-      mbar_wait(dq_full, it & 1);
-      tc_fence_after();
-      float* dq_base = p.dq_acc + (long long)(row_base + q0) * (p.Hq * FA_D) + hq * FA_D + r;
-#pragma unroll 1
-      for (int c = 0; c < BWD_BM; c += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tdQt + lane_addr + c, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (q0 + c + i < p.S) atomicAdd(dq_base + (long long)(c + i) * (p.Hq * FA_D), __uint_as_float(v[i]));
-      }
-      tc_fence_before();
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // lse/delta stage and dQ^T tile are free again
+      mbar_arrive(&pds_ready[st]);
     }
+    // ---- dK / dV epilogue: this warp group's 64 of the 128 feature columns
     mbar_wait(dkv_full, 0);
     tc_fence_after();
     __nv_bfloat16* dkrow = p.dk + (long long)(row_base + kv_idx) * p.dkv_stride + hkv * FA_D;
     __nv_bfloat16* dvrow = p.dv + (long long)(row_base + kv_idx) * p.dkv_stride + hkv * FA_D;
 #pragma unroll 1
-    for (int c = 0; c < FA_D; c += 32) {
+    for (int c = half * 64; c < half * 64 + 64; c += 32) {
       uint32_t vk[32], vv[32];
       tmem_ld_32x32b_x32(tdK + lane_addr + c, vk);
       tmem_ld_32x32b_x32(tdV + lane_addr + c, vv);
@@ -520,30 +558,70 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
       }
     }
+  } else if (warp >= 12) {
+    // ================================================= dQ readout warps: TMEM -> smem tile -> bulk reduce-add
+    const int quad = warp & 3;
+    const int d = quad * 32 + lane;  // feature index = TMEM lane of dQ^T
+    const int tid = threadIdx.x - 384;
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    for (int it = 0; it < n_iter; ++it) {
+      const int st = it & 1;
+      const int hq = hkv * G + it / per_head;
+      const int q0 = (i_begin + it % per_head) * BWD_BM;
+      mbar_wait(&dq_full[st], (it >> 1) & 1);
+      tc_fence_after();
+      uint32_t v0[32], v1[32];
+      const uint32_t tdQt = tmem_base + 256 + st * 128;
+      tmem_ld_32x32b_x32(tdQt + lane_addr, v0);
+      tmem_ld_32x32b_x32(tdQt + lane_addr + 32, v1);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&dq_done[st]);
+      if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // previous tile left the staging buffer
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        sDQ[i * FA_D + d] = __uint_as_float(v0[i]);
+        sDQ[(32 + i) * FA_D + d] = __uint_as_float(v1[i]);
+      }
+      fence_proxy_async();
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+      if (tid == 0 && !(p.dbg & 1)) {
+        float* dst = p.dq_acc + (((long long)b * p.Hq + hq) * p.S_pad + q0) * FA_D;
+        asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst),
+                     "r"(smem_u32(sDQ)), "n"(BWD_DQ_BYTES)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    }
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
 }
 
-// dq (bf16, strided) = dq_acc (fp32, dense [T, width]) * scale
+// dq[(b*S + s), h*D + d] (bf16, strided rows) = dq_acc[b, h, s, d] (fp32, S padded to S_pad) * scale
 __global__ void __launch_bounds__(256)
-dq_finalize_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dst, long long T, int width,
+dq_finalize_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dst, int B, int S, int S_pad, int Hq,
                    long long dst_stride, float scale) {
-  const int nvec = width >> 2;
-  const long long total = T * nvec;
+  constexpr int nvec = FA_D / 4;
+  const long long total = (long long)B * S * Hq * nvec;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const long long t = idx / nvec;
-    const int i = (int)(idx - t * nvec);
-    const float4 v = *reinterpret_cast<const float4*>(acc + t * width + i * 4);
+    const int i = (int)(idx % nvec);
+    long long t = idx / nvec;
+    const int h = (int)(t % Hq);
+    t /= Hq;  // token index b*S + s
+    const int bb = (int)(t / S), ss = (int)(t - (long long)bb * S);
+    const float4 v = *reinterpret_cast<const float4*>(acc + (((long long)bb * Hq + h) * S_pad + ss) * FA_D + i * 4);
     uint2 o;
     o.x = f2_to_bf2(v.x * scale, v.y * scale);
     o.y = f2_to_bf2(v.z * scale, v.w * scale);
-    *reinterpret_cast<uint2*>(dst + t * dst_stride + i * 4) = o;
+    *reinterpret_cast<uint2*>(dst + t * dst_stride + h * FA_D + i * 4) = o;
   }
 }
 
@@ -613,24 +691,26 @@ B200_API int b200_flash_attn_bwd(const void* q, const void* k, const void* v, co
   FaBwdParams p;
   p.lse = (const float*)lse; p.delta = (const float*)delta; p.dq_acc = (float*)dq_acc;
   p.dk = (__nv_bfloat16*)dk; p.dv = (__nv_bfloat16*)dv; p.B = B; p.S = S; p.Hq = Hq; p.Hkv = Hkv;
+  p.S_pad = (S + BWD_BM - 1) / BWD_BM * BWD_BM;
+  { const char* e = getenv("B200_FA_DBG"); p.dbg = e ? atoi(e) : 0; }
   p.dkv_stride = dkv_stride; p.scale = scale; p.scale_log2 = scale * kLog2e; p.causal = causal;
   dim3 grid((S + BWD_BN - 1) / BWD_BN, Hkv, B);
-  flash_bwd_kernel<<<grid, 192, BWD_SMEM, (cudaStream_t)stream>>>(tq, tk, tv, tdo, p);
+  flash_bwd_kernel<<<grid, BWD_THREADS, BWD_SMEM, (cudaStream_t)stream>>>(tq, tk, tv, tdo, p);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;
 }
 
-B200_API int b200_dq_finalize(const void* acc, void* dst, long long T, int width, long long dst_stride,
-                              float scale, void* stream) {
-  if (width % 4) return B200_ERR_BAD_ARG;
-  if (T == 0) return 0;
-  long long work = T * (width / 4);
+B200_API int b200_dq_finalize(const void* acc, void* dst, int B, int S, int Hq, long long dst_stride, float scale,
+                              void* stream) {
+  if ((long long)B * S == 0) return 0;
+  const int S_pad = (S + BWD_BM - 1) / BWD_BM * BWD_BM;
+  long long work = (long long)B * S * Hq * (FA_D / 4);
   long long g = (work + 255) / 256;
   long long cap = (long long)num_sms() * 16;
   if (g > cap) g = cap;
-  dq_finalize_kernel<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>((const float*)acc, (__nv_bfloat16*)dst, T,
-                                                                    width, dst_stride, scale);
+  dq_finalize_kernel<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>((const float*)acc, (__nv_bfloat16*)dst, B, S, S_pad, Hq,
+                                                                    dst_stride, scale);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;

@@ -154,7 +154,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 
   if (warp == 0) {
     // ================================ TMA producer (one per CTA) ================================
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
@@ -187,7 +187,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     }
   } else if (warp == 1) {
     // ================================ MMA issuer (leader CTA only) ================================
-    if (leader && lane == 0) {
+    if (leader && elect_one()) {
       constexpr uint32_t idesc = FP8 ? make_idesc_e4m3(256, BN) : make_idesc_bf16(256, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;

@@ -141,7 +141,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -196,7 +196,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
-    if (lane == 0) {
+    if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
@@ -235,7 +235,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   } else if (FUSE_AG && warp == 3) {
     // ================================ all-gather warp ================================
-    if (lane == 0 && p.ag_world > 1) {
+    if (p.ag_world > 1 && elect_one()) {
       const long long shard_bytes = (long long)p.ag_rows * p.K * 2;
       const long long cps = (shard_bytes + AGG_CHUNK - 1) / AGG_CHUNK;
       const long long total = cps * (p.ag_world - 1);

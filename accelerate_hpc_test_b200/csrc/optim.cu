@@ -22,6 +22,70 @@ __device__ __forceinline__ float load_grad<__nv_bfloat16>(const __nv_bfloat16* g
   return __bfloat162float(g[i]);
 }
 
+// one AdamW element update (decoupled weight decay, bias-corrected)
+__device__ __forceinline__ void adamw_one(float& p, float& mi, float& vi, float g, const AdamArgs& a) {
+  mi = mi * a.beta1 + (1.f - a.beta1) * g;
+  vi = vi * a.beta2 + (1.f - a.beta2) * g * g;
+  p *= (1.f - a.lr * a.weight_decay);
+  p -= (a.lr / a.bias_c1) * (mi / (sqrtf(vi / a.bias_c2) + a.eps));
+}
+
+__device__ __forceinline__ void load_grad4(const float* g, long long i, float (&o)[4]) {
+  const float4 t = __ldcs(reinterpret_cast<const float4*>(g + i));
+  o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+}
+__device__ __forceinline__ void load_grad4(const __nv_bfloat16* g, long long i, float (&o)[4]) {
+  const uint2 t = __ldcs(reinterpret_cast<const uint2*>(g + i));
+  const float2 a = bf2_to_f2(t.x), b = bf2_to_f2(t.y);
+  o[0] = a.x; o[1] = a.y; o[2] = b.x; o[3] = b.y;
+}
+
+// AdamW over elements [begin, end) of one tensor, shared by `nthreads` threads (this thread is `tid`).
+// The optimizer state is touched exactly once per step, so everything goes through 16-byte streaming
+// loads / stores (28 bytes of traffic per element: the kernel is pure HBM bandwidth).
+template <typename GradT>
+__device__ __forceinline__ void adamw_span(float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
+                                           const GradT* __restrict__ grad, __nv_bfloat16* __restrict__ shadow,
+                                           long long begin, long long end, long long tid, long long nthreads,
+                                           const AdamArgs& a, float gs) {
+  const uintptr_t mis = reinterpret_cast<uintptr_t>(master + begin) | reinterpret_cast<uintptr_t>(m + begin) |
+                        reinterpret_cast<uintptr_t>(v + begin);
+  const bool vec = ((mis & 15) == 0) && ((reinterpret_cast<uintptr_t>(grad + begin) & (sizeof(GradT) * 4 - 1)) == 0) &&
+                   (shadow == nullptr || (reinterpret_cast<uintptr_t>(shadow + begin) & 7) == 0);
+  long long i = begin;
+  if (vec) {
+    const long long nvec = (end - begin) >> 2;
+    for (long long k = tid; k < nvec; k += nthreads) {
+      const long long j = begin + (k << 2);
+      float4 p4 = __ldcs(reinterpret_cast<const float4*>(master + j));
+      float4 m4 = __ldcs(reinterpret_cast<const float4*>(m + j));
+      float4 v4 = __ldcs(reinterpret_cast<const float4*>(v + j));
+      float g[4];
+      load_grad4(grad, j, g);
+      adamw_one(p4.x, m4.x, v4.x, g[0] * gs, a);
+      adamw_one(p4.y, m4.y, v4.y, g[1] * gs, a);
+      adamw_one(p4.z, m4.z, v4.z, g[2] * gs, a);
+      adamw_one(p4.w, m4.w, v4.w, g[3] * gs, a);
+      __stcs(reinterpret_cast<float4*>(master + j), p4);
+      __stcs(reinterpret_cast<float4*>(m + j), m4);
+      __stcs(reinterpret_cast<float4*>(v + j), v4);
+      if (shadow) {
+        uint2 o;
+        o.x = f2_to_bf2(p4.x, p4.y);
+        o.y = f2_to_bf2(p4.z, p4.w);
+        *reinterpret_cast<uint2*>(shadow + j) = o;  // the bf16 parameter is read again soon: normal store
+      }
+    }
+    i = begin + (nvec << 2);
+  }
+  for (long long j = i + tid; j < end; j += nthreads) {
+    float p = master[j], mi = m[j], vi = v[j];
+    adamw_one(p, mi, vi, load_grad<GradT>(grad, j) * gs, a);
+    master[j] = p; m[j] = mi; v[j] = vi;
+    if (shadow) shadow[j] = __float2bfloat16(p);
+  }
+}
+
 // flat AdamW over n elements.  clip_coef (device scalar, may be null) multiplies grads;
 // found_inf (device scalar, may be null) != 0 skips the whole update (GradScaler semantics).
 template <typename GradT>
@@ -31,20 +95,8 @@ adamw_flat_kernel(float* __restrict__ master, float* __restrict__ m, float* __re
                   AdamArgs a, const float* __restrict__ clip_coef, const float* __restrict__ found_inf) {
   if (found_inf && *found_inf != 0.f) return;
   const float gs = a.grad_scale * (clip_coef ? *clip_coef : 1.f);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-       i += (long long)gridDim.x * blockDim.x) {
-    const float g = load_grad<GradT>(grad, i) * gs;
-    float p = master[i];
-    float mi = m[i] * a.beta1 + (1.f - a.beta1) * g;
-    float vi = v[i] * a.beta2 + (1.f - a.beta2) * g * g;
-    m[i] = mi;
-    v[i] = vi;
-    p *= (1.f - a.lr * a.weight_decay);
-    const float denom = sqrtf(vi / a.bias_c2) + a.eps;
-    p -= (a.lr / a.bias_c1) * (mi / denom);
-    master[i] = p;
-    if (shadow) shadow[i] = __float2bfloat16(p);
-  }
+  adamw_span<GradT>(master, m, v, grad, shadow, 0, n, (long long)blockIdx.x * blockDim.x + threadIdx.x,
+                    (long long)gridDim.x * blockDim.x, a, gs);
 }
 
 // multi-tensor variant: tensor table in device memory, one CTA per (tensor, 64K-element chunk)
@@ -76,18 +128,7 @@ adamw_mt_kernel(const MTEntry* __restrict__ table, int ntensors, AdamArgs a,
   const long long end = min(begin + (long long)MT_CHUNK, e.n);
   const float gs = a.grad_scale * (clip_coef ? *clip_coef : 1.f);
   const GradT* grad = reinterpret_cast<const GradT*>(e.grad);
-  for (long long i = begin + threadIdx.x; i < end; i += blockDim.x) {
-    const float g = load_grad<GradT>(grad, i) * gs;
-    float p = e.master[i];
-    float mi = e.m[i] * a.beta1 + (1.f - a.beta1) * g;
-    float vi = e.v[i] * a.beta2 + (1.f - a.beta2) * g * g;
-    e.m[i] = mi;
-    e.v[i] = vi;
-    p *= (1.f - a.lr * a.weight_decay);
-    p -= (a.lr / a.bias_c1) * (mi / (sqrtf(vi / a.bias_c2) + a.eps));
-    e.master[i] = p;
-    if (e.shadow) e.shadow[i] = __float2bfloat16(p);
-  }
+  adamw_span<GradT>(e.master, e.m, e.v, grad, e.shadow, begin, end, threadIdx.x, blockDim.x, a, gs);
 }
 
 // out[0] += sum(g^2) ; also flags non-finite values in out[1]
@@ -97,8 +138,22 @@ sumsq_kernel(const GradT* __restrict__ g, long long n, float* __restrict__ out) 
   __shared__ float red[32];
   float s = 0.f;
   bool bad = false;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-       i += (long long)gridDim.x * blockDim.x) {
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  long long i0 = 0;
+  if ((reinterpret_cast<uintptr_t>(g) & (sizeof(GradT) * 4 - 1)) == 0) {
+    const long long nvec = n >> 2;
+    for (long long k = tid; k < nvec; k += nth) {
+      float x[4];
+      load_grad4(g, k << 2, x);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        s += x[j] * x[j];
+        bad |= !isfinite(x[j]);
+      }
+    }
+    i0 = nvec << 2;
+  }
+  for (long long i = i0 + tid; i < n; i += nth) {
     const float x = load_grad<GradT>(g, i);
     s += x * x;
     bad |= !isfinite(x);
@@ -122,7 +177,7 @@ __global__ void clip_coef_kernel(const float* __restrict__ sumsq, float max_norm
 using namespace b200;
 
 static inline int flat_grid(long long n) {
-  long long g = (n + 255) / 256;
+  long long g = (n / 4 + 255) / 256;  // 4 elements per thread per iteration
   long long cap = (long long)num_sms() * 8;
   return (int)(g < cap ? (g > 0 ? g : 1) : cap);
 }

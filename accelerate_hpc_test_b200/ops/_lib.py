@@ -58,7 +58,7 @@ _SIGNATURES = {
     "b200_flash_attn_fwd": [P, P, P, P, P, I, I, I, I, I, L, L, L, L, F, I, P],
     "b200_flash_attn_bwd_prep": [P, P, P, I, I, I, L, L, P],
     "b200_flash_attn_bwd": [P, P, P, P, P, P, P, P, P, I, I, I, I, I, L, L, L, L, L, F, I, P],
-    "b200_dq_finalize": [P, P, L, I, L, F, P],
+    "b200_dq_finalize": [P, P, I, I, I, L, F, P],
     "b200_launch_count": [],
     "b200_reset_launch_count": [],
     "b200_version": [],

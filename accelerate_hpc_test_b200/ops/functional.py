@@ -541,7 +541,8 @@ def flash_attn_bwd(do, qkv, o, lse, B, S, Hq, Hkv, D, causal, scale):
     do = do.contiguous()
     dqkv = torch.empty_like(qkv)
     delta = torch.empty((B, Hq, S), dtype=torch.float32, device=qkv.device)
-    dq_acc = torch.zeros((T, Hq * D), dtype=torch.float32, device=qkv.device)
+    s_pad = (S + 63) // 64 * 64
+    dq_acc = torch.zeros((B, Hq, s_pad, D), dtype=torch.float32, device=qkv.device)  # tiles of 64 q rows are contiguous
     check(lib.b200_flash_attn_bwd_prep(ptr(do), ptr(o), ptr(delta), B, S, Hq, do.stride(0), o.stride(0), cur_stream()), "flash_attn_bwd_prep")
     q = qkv
     k = qkv[:, Hq * D :]
@@ -554,7 +555,7 @@ def flash_attn_bwd(do, qkv, o, lse, B, S, Hq, Hkv, D, causal, scale):
                                 float(scale), int(causal), cur_stream()),
         "flash_attn_bwd",
     )
-    check(lib.b200_dq_finalize(ptr(dq_acc), ptr(dqkv), T, Hq * D, dqkv.stride(0), float(scale), cur_stream()), "dq_finalize")
+    check(lib.b200_dq_finalize(ptr(dq_acc), ptr(dqkv), B, S, Hq, dqkv.stride(0), float(scale), cur_stream()), "dq_finalize")
     return dqkv
 
 

@@ -129,7 +129,7 @@ def _pair_fwd(q, k, v, S, Hq, Hkv, D, causal, scale):
 
 def _pair_bwd(q, k, v, do, lse, delta, dq_acc, S, Hq, Hkv, D, causal, scale):
     """Backward of one block with the GLOBAL ``lse`` / ``delta`` of the Q rows.  Adds the unscaled dQ into ``dq_acc``
-    (fp32 ``[S, Hq*D]`` view) and returns this block's ``(dk, dv)`` ``[S, Hkv*D]``."""
+    (fp32 ``[Hq, S_pad, D]``, the kernel's accumulator layout) and returns this block's ``(dk, dv)`` ``[S, Hkv*D]``."""
     if q.is_cuda:
         lib = _lib.require_gpu_lib()
         dkv = torch.empty((S, 2 * Hkv * D), dtype=torch.bfloat16, device=q.device)
@@ -150,7 +150,7 @@ def _pair_bwd(q, k, v, do, lse, delta, dq_acc, S, Hq, Hkv, D, causal, scale):
     p = torch.exp(s - lse[..., None])
     dv = p.transpose(-1, -2) @ dof
     ds = p * (dof @ vf.transpose(-1, -2) - delta[..., None])
-    dq_acc.view(S, Hq, D).add_((ds @ kf).transpose(0, 1))  # unscaled, like the kernel's accumulator
+    dq_acc[:, :S].add_(ds @ kf)  # unscaled, like the kernel's accumulator
     dk = (ds.transpose(-1, -2) @ qf) * scale
     dk = dk.view(Hkv, rep, S, D).sum(1).transpose(0, 1).reshape(S, Hkv * D)
     dv = dv.view(Hkv, rep, S, D).sum(1).transpose(0, 1).reshape(S, Hkv * D)
@@ -211,7 +211,8 @@ class _CPAttentionFn(torch.autograd.Function):
         do = do.reshape(T, Hq * D).contiguous()
         # delta[b, half, h, s] = sum_d do * o for every local q row
         delta = (do.float() * o.float()).view(B, 2, c, Hq, D).sum(-1).permute(0, 1, 3, 2).contiguous()
-        dq_acc = torch.zeros((T, Hq * D), dtype=torch.float32, device=do.device)
+        c_pad = (c + 63) // 64 * 64
+        dq_acc = torch.zeros((B, 2, Hq, c_pad, D), dtype=torch.float32, device=do.device)
         dkv_all = torch.zeros(kv_all.shape, dtype=torch.float32, device=do.device)
         for b in range(B):
             for half, qi in enumerate((r, 2 * w - 1 - r)):
@@ -222,12 +223,14 @@ class _CPAttentionFn(torch.autograd.Function):
                     krows = slice(b * S_loc + h2 * c, b * S_loc + h2 * c + c)
                     kv = kv_all[owner, krows]
                     dk, dv = _pair_bwd(q, kv[:, : Hkv * D], kv[:, Hkv * D :], do[rows], lse[b, half], delta[b, half],
-                                       dq_acc[rows], c, Hq, Hkv, D, j == qi, scale)
+                                       dq_acc[b, half], c, Hq, Hkv, D, j == qi, scale)
                     dkv_all[owner, krows, : Hkv * D] += dk
                     dkv_all[owner, krows, Hkv * D :] += dv
         dkv = comm.reduce_scatter_rows(dkv_all)
         dqkv = torch.empty_like(qkv2)
-        dqkv[:, : Hq * D] = (dq_acc * scale).to(dqkv.dtype)
+        # [B, 2, Hq, c, D] -> token-major [B*S_loc, Hq*D]
+        dq = dq_acc[:, :, :, :c].permute(0, 1, 3, 2, 4).reshape(T, Hq * D)
+        dqkv[:, : Hq * D] = (dq * scale).to(dqkv.dtype)
         dqkv[:, Hq * D :] = dkv.to(dqkv.dtype)
         F.rope_inplace(dqkv, cos, sin, pos, Hq + Hkv, D, backward=True)
         return (dqkv.view(ctx.in_shape),) + (None,) * 10

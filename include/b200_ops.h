@@ -67,12 +67,13 @@ int b200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, vo
                         void* stream);
 int b200_flash_attn_bwd_prep(const void* dout, const void* out, void* delta, int B, int S, int Hq, long long do_stride,
                              long long o_stride, void* stream);
-/* dq_acc: fp32 [B*S, Hq*128] scratch, zero-initialised by the caller (unscaled dQ is accumulated there) */
+/* dq_acc: fp32 [B, Hq, S_pad, 128] scratch (S_pad = S rounded up to 64), zero-initialised by the caller; every 64-row
+ * dQ tile is added with one cp.reduce.async.bulk; b200_dq_finalize scales it and writes token-major bf16. */
 int b200_flash_attn_bwd(const void* q, const void* k, const void* v, const void* dout, const void* lse, const void* delta,
                         void* dq_acc, void* dk, void* dv, int B, int S, int Hq, int Hkv, int D, long long q_stride,
                         long long k_stride, long long v_stride, long long do_stride, long long dkv_stride, float scale,
                         int causal, void* stream);
-int b200_dq_finalize(const void* acc, void* dst, long long T, int width, long long dst_stride, float scale, void* stream);
+int b200_dq_finalize(const void* acc, void* dst, int B, int S, int Hq, long long dst_stride, float scale, void* stream);
 
 /* ---- K5 / K6 / K7 / K11 / K12: bandwidth-bound fused ops (csrc/elementwise.cu) */
 int b200_rmsnorm_fwd(const void* x, const void* res, const void* w, void* y, void* sum_out, void* rstd, long long T, int H,
