@@ -87,8 +87,12 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qb = gridDim.x - 1 - blockIdx.x;  // heavy (late) causal blocks first
-  const int hq = blockIdx.y, b = blockIdx.z;
+  // 1-D grid ordered q-block-major with the heavy (late) causal blocks first: the hardware scheduler hands out CTAs
+  // in index order, so this is longest-processing-time-first across ALL (head, batch) pairs, not per pair
+  const int nqb = (p.S + FWD_BM - 1) / FWD_BM;
+  const int qb = nqb - 1 - (int)(blockIdx.x / (unsigned)(p.Hq * p.B));
+  const int hb = (int)(blockIdx.x % (unsigned)(p.Hq * p.B));
+  const int hq = hb % p.Hq, b = hb / p.Hq;
   const int hkv = hq / (p.Hq / p.Hkv);
   const int q0 = qb * FWD_BM;
   const int kv_end = p.causal ? min(p.S, q0 + FWD_BM) : p.S;
@@ -356,7 +360,10 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 17);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int kvb = blockIdx.x, hkv = blockIdx.y, b = blockIdx.z;
+  // 1-D grid, kv-block-major: kv block 0 sees every q block (most work) -> longest CTAs are scheduled first
+  const int kvb = (int)(blockIdx.x / (unsigned)(p.Hkv * p.B));
+  const int hb = (int)(blockIdx.x % (unsigned)(p.Hkv * p.B));
+  const int hkv = hb % p.Hkv, b = hb / p.Hkv;
   const int G = p.Hq / p.Hkv;
   const int kv0 = kvb * BWD_BN;
   const int row_base = b * p.S;
@@ -650,7 +657,7 @@ B200_API int b200_flash_attn_fwd(const void* q, const void* k, const void* v, vo
   FaFwdParams p;
   p.o = (__nv_bfloat16*)o; p.lse = (float*)lse; p.B = B; p.S = S; p.Hq = Hq; p.Hkv = Hkv;
   p.o_stride = o_stride; p.scale_log2 = scale * kLog2e; p.causal = causal;
-  dim3 grid((S + FWD_BM - 1) / FWD_BM, Hq, B);
+  const unsigned grid = (unsigned)((S + FWD_BM - 1) / FWD_BM) * Hq * B;
   flash_fwd_kernel<<<grid, 192, FWD_SMEM, (cudaStream_t)stream>>>(tq, tk, tv, p);
   b200_count_launch();
   B200_CHECK_LAUNCH();
@@ -694,7 +701,7 @@ B200_API int b200_flash_attn_bwd(const void* q, const void* k, const void* v, co
   p.S_pad = (S + BWD_BM - 1) / BWD_BM * BWD_BM;
   { const char* e = getenv("B200_FA_DBG"); p.dbg = e ? atoi(e) : 0; }
   p.dkv_stride = dkv_stride; p.scale = scale; p.scale_log2 = scale * kLog2e; p.causal = causal;
-  dim3 grid((S + BWD_BN - 1) / BWD_BN, Hkv, B);
+  const unsigned grid = (unsigned)((S + BWD_BN - 1) / BWD_BN) * Hkv * B;
   flash_bwd_kernel<<<grid, BWD_THREADS, BWD_SMEM, (cudaStream_t)stream>>>(tq, tk, tv, tdo, p);
   b200_count_launch();
   B200_CHECK_LAUNCH();
