@@ -64,27 +64,36 @@ static constexpr int FWD_BM = 128, FWD_BN = 64;
 static constexpr int FWD_Q_BYTES = FWD_BM * FA_D * 2;   // 32 KB (2 chunks of 128 x 64)
 static constexpr int FWD_KV_BYTES = FWD_BN * FA_D * 2;  // 16 KB (2 chunks of 64 x 64)
 static constexpr int FWD_P_BYTES = FWD_BM * FWD_BN * 2;  // 16 KB
-static constexpr int FWD_SMEM = FWD_Q_BYTES + 2 * FWD_KV_BYTES + FWD_P_BYTES + 1024 + 128;
+// Q + 2-stage K ring + 2-stage V ring + P = 112 KB; two CTAs per SM must fit in 228 KB together with the 1 KB the
+// driver reserves per CTA, so there is no 1 KB alignment slack: the kernel checks the (in practice 1024-aligned)
+// dynamic shared memory base instead.
+static constexpr int FWD_SMEM = FWD_Q_BYTES + 4 * FWD_KV_BYTES + FWD_P_BYTES + 128;
 
+// One CTA = one 128-row Q tile of one head; two CTAs per SM.  Per 64-row KV block j:
+//   tensor:  S_j = Q K_j^T  (TMEM stage j&1, issued TWO blocks ahead),  O += P_j V_j
+//   softmax: 128 threads, one query row each: online softmax with lazy rescale, P_j -> smem (bf16)
+// S is double buffered in TMEM and K / V each have a 2-stage TMA ring, so S_{j+1} is already waiting when the
+// softmax warps finish block j and the TMA latency of block j+2 is hidden behind a whole iteration.
 __global__ void __launch_bounds__(192, 2)
 flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                  const __grid_constant__ CUtensorMap tmap_v, const FaFwdParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
   uint8_t* sQ = smem;
-  uint8_t* sK = sQ + FWD_Q_BYTES;
-  uint8_t* sV = sK + FWD_KV_BYTES;
-  uint8_t* sP = sV + FWD_KV_BYTES;
+  uint8_t* sK = sQ + FWD_Q_BYTES;      // [2 stages]
+  uint8_t* sV = sK + 2 * FWD_KV_BYTES;  // [2 stages]
+  uint8_t* sP = sV + 2 * FWD_KV_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sP + FWD_P_BYTES);
   uint64_t* q_full = bars + 0;
-  uint64_t* k_full = bars + 1;
-  uint64_t* k_empty = bars + 2;
-  uint64_t* v_full = bars + 3;
-  uint64_t* v_empty = bars + 4;
-  uint64_t* s_full = bars + 5;
-  uint64_t* p_ready = bars + 6;
-  uint64_t* o_full = bars + 7;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* k_full = bars + 1;    // [2]
+  uint64_t* k_empty = bars + 3;   // [2]
+  uint64_t* v_full = bars + 5;    // [2]
+  uint64_t* v_empty = bars + 7;   // [2]
+  uint64_t* s_full = bars + 9;    // [2]
+  uint64_t* p_ready = bars + 11;  // softmax (128) -> MMA
+  uint64_t* pv_done = bars + 12;  // PV_j retired: P buffer free, O stable
+  uint64_t* o_full = bars + 13;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // 1-D grid ordered q-block-major with the heavy (late) causal blocks first: the hardware scheduler hands out CTAs
@@ -100,11 +109,19 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   const int row_base = b * p.S;
 
   if (warp == 0 && lane == 0) {
+    if (smem_u32(smem) & 1023u) {
+      printf("b200 flash_fwd: dynamic shared memory base is not 1024-byte aligned\n");
+      __trap();
+    }
     prefetch_tensormap(&tmap_q);
     prefetch_tensormap(&tmap_k);
     prefetch_tensormap(&tmap_v);
-    mbar_init(q_full, 1); mbar_init(k_full, 1); mbar_init(k_empty, 1); mbar_init(v_full, 1);
-    mbar_init(v_empty, 1); mbar_init(s_full, 1); mbar_init(p_ready, 128); mbar_init(o_full, 1);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+    }
+    mbar_init(p_ready, 128); mbar_init(pv_done, 1); mbar_init(o_full, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<256>(tmem_slot);
@@ -112,7 +129,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tS = tmem_base, tO = tmem_base + 64;
+  const uint32_t tS = tmem_base, tO = tmem_base + 128;  // S stage s at tS + 64 s
 
   if (warp == 0) {
     if (elect_one()) {
@@ -120,38 +137,48 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       tma_load_2d(sQ, &tmap_q, q_full, hq * FA_D, row_base + q0);
       tma_load_2d(sQ + FWD_Q_BYTES / 2, &tmap_q, q_full, hq * FA_D + 64, row_base + q0);
       for (int j = 0; j < nblk; ++j) {
-        const uint32_t par = (j & 1) ^ 1;
+        const int st = j & 1;
+        const uint32_t par = ((j >> 1) & 1) ^ 1;
         const int kvrow = row_base + j * FWD_BN;
-        mbar_wait(k_empty, par);
-        mbar_arrive_expect_tx(k_full, FWD_KV_BYTES);
-        tma_load_2d(sK, &tmap_k, k_full, hkv * FA_D, kvrow);
-        tma_load_2d(sK + FWD_KV_BYTES / 2, &tmap_k, k_full, hkv * FA_D + 64, kvrow);
-        mbar_wait(v_empty, par);
-        mbar_arrive_expect_tx(v_full, FWD_KV_BYTES);
-        tma_load_2d(sV, &tmap_v, v_full, hkv * FA_D, kvrow);
-        tma_load_2d(sV + FWD_KV_BYTES / 2, &tmap_v, v_full, hkv * FA_D + 64, kvrow);
+        uint8_t* k_dst = sK + st * FWD_KV_BYTES;
+        uint8_t* v_dst = sV + st * FWD_KV_BYTES;
+        mbar_wait(&k_empty[st], par);
+        mbar_arrive_expect_tx(&k_full[st], FWD_KV_BYTES);
+        tma_load_2d(k_dst, &tmap_k, &k_full[st], hkv * FA_D, kvrow);
+        tma_load_2d(k_dst + FWD_KV_BYTES / 2, &tmap_k, &k_full[st], hkv * FA_D + 64, kvrow);
+        mbar_wait(&v_empty[st], par);
+        mbar_arrive_expect_tx(&v_full[st], FWD_KV_BYTES);
+        tma_load_2d(v_dst, &tmap_v, &v_full[st], hkv * FA_D, kvrow);
+        tma_load_2d(v_dst + FWD_KV_BYTES / 2, &tmap_v, &v_full[st], hkv * FA_D + 64, kvrow);
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc_s = make_idesc_bf16(128, FWD_BN, 0, 0);
       constexpr uint32_t idesc_o = make_idesc_bf16(128, FA_D, 0, 1);
-      const uint32_t aQ = smem_u32(sQ), aK = smem_u32(sK), aV = smem_u32(sV), aP = smem_u32(sP);
-      mbar_wait(q_full, 0);
-      for (int j = 0; j < nblk; ++j) {
-        const uint32_t par = j & 1;
-        mbar_wait(k_full, par);
+      const uint32_t aQ = smem_u32(sQ), aP = smem_u32(sP);
+      auto issue_S = [&](int j) {
+        const int st = j & 1;
+        const uint32_t aK = smem_u32(sK + st * FWD_KV_BYTES);
+        mbar_wait(&k_full[st], (j >> 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < FA_D / 16; ++k) {
           const uint64_t da = make_umma_desc(aQ + (k >> 2) * (FWD_Q_BYTES / 2) + (k & 3) * 32, 16, 1024);
           const uint64_t db = make_umma_desc(aK + (k >> 2) * (FWD_KV_BYTES / 2) + (k & 3) * 32, 16, 1024);
-          umma_bf16_ss(tS, da, db, idesc_s, k > 0 ? 1u : 0u);
+          umma_bf16_ss(tS + st * 64, da, db, idesc_s, k > 0 ? 1u : 0u);
         }
-        umma_commit(k_empty);
-        umma_commit(s_full);
-        mbar_wait(p_ready, par);
-        mbar_wait(v_full, par);
+        umma_commit(&k_empty[st]);
+        umma_commit(&s_full[st]);
+      };
+      mbar_wait(q_full, 0);
+      issue_S(0);
+      if (nblk > 1) issue_S(1);
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        const uint32_t aV = smem_u32(sV + st * FWD_KV_BYTES);
+        mbar_wait(p_ready, j & 1);
+        mbar_wait(&v_full[st], (j >> 1) & 1);
         tc_fence_after();
 #pragma unroll
         for (int k = 0; k < FWD_BN / 16; ++k) {
@@ -160,8 +187,10 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           const uint64_t db = make_umma_desc(aV + k * 16 * 128, FWD_KV_BYTES / 2, 1024);
           umma_bf16_ss(tO, da, db, idesc_o, (j > 0 || k > 0) ? 1u : 0u);
         }
-        umma_commit(v_empty);
+        umma_commit(&v_empty[st]);
+        umma_commit(pv_done);
         if (j == nblk - 1) umma_commit(o_full);
+        if (j + 2 < nblk) issue_S(j + 2);  // the softmax warps finished reading S_j before p_ready(j)
       }
     }
   } else {
@@ -170,21 +199,22 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     const int r = quad * 32 + lane;
     const int q_idx = q0 + r;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-    float m_used = -INFINITY, l = 0.f;
+    float m_used = -INFINITY, l = 0.f;  // running max (in scaled log2 units) and row sum
     for (int j = 0; j < nblk; ++j) {
       const int kv0 = j * FWD_BN;
-      mbar_wait(s_full, j & 1);
+      const int st = j & 1;
+      mbar_wait(&s_full[st], (j >> 1) & 1);
       tc_fence_after();
       float s[64];
       {
         uint32_t v0[32], v1[32];
-        tmem_ld_32x32b_x32(tS + lane_addr, v0);
-        tmem_ld_32x32b_x32(tS + lane_addr + 32, v1);
+        tmem_ld_32x32b_x32(tS + st * 64 + lane_addr, v0);
+        tmem_ld_32x32b_x32(tS + st * 64 + lane_addr + 32, v1);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          s[i] = __uint_as_float(v0[i]) * p.scale_log2;
-          s[32 + i] = __uint_as_float(v1[i]) * p.scale_log2;
+          s[i] = __uint_as_float(v0[i]);
+          s[32 + i] = __uint_as_float(v1[i]);
         }
       }
       const bool need_mask = (p.causal && (kv0 + FWD_BN - 1 > q0)) || (kv0 + FWD_BN > p.S);
@@ -195,10 +225,13 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
           if (kv >= p.S || (p.causal && kv > q_idx)) s[i] = -INFINITY;
         }
       }
-      float mx = s[0];
+      float mx0 = fmaxf(s[0], s[1]), mx1 = fmaxf(s[2], s[3]);
 #pragma unroll
-      for (int i = 1; i < 64; ++i) mx = fmaxf(mx, s[i]);
-      const float m_new = fmaxf(m_used, mx);
+      for (int i = 4; i < 64; i += 4) {
+        mx0 = fmaxf(mx0, fmaxf(s[i], s[i + 1]));
+        mx1 = fmaxf(mx1, fmaxf(s[i + 2], s[i + 3]));
+      }
+      const float m_new = fmaxf(m_used, fmaxf(mx0, mx1) * p.scale_log2);  // scale > 0: max commutes with it
       float alpha = 1.f;
       const bool need = (m_new - m_used) > 8.f;  // also true for the first finite max (m_used = -inf)
       if (need) {
@@ -206,17 +239,22 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         m_used = m_new;
         l *= alpha;
       }
-      const float m_eff = (m_used == -INFINITY) ? 0.f : m_used;
-      float rs = 0.f;
+      const float neg_m = (m_used == -INFINITY) ? 0.f : -m_used;
+      float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) {
-        s[i] = exp2f(s[i] - m_eff);
-        rs += s[i];
+      for (int i = 0; i < 64; i += 2) {
+        s[i] = exp2f(fmaf(s[i], p.scale_log2, neg_m));
+        s[i + 1] = exp2f(fmaf(s[i + 1], p.scale_log2, neg_m));
+        rs0 += s[i];
+        rs1 += s[i + 1];
       }
-      l += rs;
+      l += rs0 + rs1;
+      if (j > 0) {
+        mbar_wait(pv_done, (j - 1) & 1);  // PV_{j-1} retired: the P buffer is free and O is stable
+        tc_fence_after();
+      }
       store_row_sw128(sP, r, s);
       if (j > 0 && __any_sync(0xffffffffu, need)) {
-        // PV_{j-1} has retired (it was issued before S_j, whose completion we waited for)
 #pragma unroll 1
         for (int c = 0; c < FA_D; c += 32) {
           uint32_t v[32];
