@@ -877,6 +877,11 @@ class Accelerator:
         if device_placement is None:
             device_placement = self.device_placement
         scaler = None if self.is_fsdp2 and self.scaler is None else self.scaler
+        if (hasattr(optimizer, "enable_update_in_backward") and self.distributed_type == DistributedType.NO
+                and self.device.type == "cuda" and scaler is None):
+            # single device: nothing has to be reduced first, so FusedAdamW may update each parameter inside backward
+            gs = self.gradient_state
+            optimizer.enable_update_in_backward(sync_gradients_fn=lambda: gs.sync_gradients)
         optimizer = AcceleratedOptimizer(optimizer, device_placement=device_placement, scaler=scaler)
         self._optimizers.append(optimizer)
         return optimizer
@@ -950,6 +955,7 @@ class Accelerator:
                     self.unscale_gradients()
                     return model.clip_grad_norm_(max_norm, norm_type)
         self.unscale_gradients()
+        self._notify_grad_consumer("gradient clipping")
         fused = [opt.optimizer for opt in self._optimizers if hasattr(opt.optimizer, "set_clip_coef")]
         if norm_type == 2 and self.device.type == "cuda" and len(fused) == len(self._optimizers) and len(fused) > 0 and self.scaler is None:
             from .optim import grad_global_norm
@@ -964,7 +970,14 @@ class Accelerator:
         if self.distributed_type in (DistributedType.DEEPSPEED, DistributedType.FSDP):
             raise Exception("DeepSpeed and FSDP  do not support `clip_grad_value_`. Use `clip_grad_norm_` instead.")
         self.unscale_gradients()
+        self._notify_grad_consumer("gradient clipping")
         torch.nn.utils.clip_grad_value_(parameters, clip_value)
+
+    def _notify_grad_consumer(self, what: str):
+        for opt in self._optimizers:
+            inner = getattr(opt, "optimizer", opt)
+            if hasattr(inner, "_note_grad_consumer"):
+                inner._note_grad_consumer(what)
 
     # ================================================================== collectives for metrics
     def gather(self, tensor):

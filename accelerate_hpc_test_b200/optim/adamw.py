@@ -12,6 +12,7 @@ Reference parity: the reference uses ``torch.optim.AdamW`` wrapped by ``Accelera
 
 from __future__ import annotations
 
+import os
 from typing import Iterable, Optional
 
 import torch
@@ -30,14 +31,102 @@ class FusedAdamW(torch.optim.Optimizer):
         self._clip_coef: Optional[torch.Tensor] = None
         self._found_inf: Optional[torch.Tensor] = None
         self.grad_scale: float = 1.0
+        # ---- "optimizer in backward" (see enable_update_in_backward)
+        self._bwd_mode = "off"          # off | probing | active
+        self._bwd_stream = None
+        self._bwd_hooks = []
+        self._bwd_fired = {}            # param -> hook firings since the last step (probing)
+        self._bwd_updated = set()       # params already updated during this step's backward
+        self._saw_grad_consumer = False  # clip / found_inf / grad_scale used: gradients are needed after backward
+        self._sync_fn = None
 
     # -- hooks used by Accelerator.clip_grad_norm_ / GradScaler integration --------------------
     def set_clip_coef(self, coef: Optional[torch.Tensor]):
         """Device scalar multiplied into every gradient inside the update kernel (consumed by the next step)."""
+        self._note_grad_consumer("gradient clipping")
         self._clip_coef = coef
 
     def set_found_inf(self, flag: Optional[torch.Tensor]):
+        self._note_grad_consumer("a GradScaler")
         self._found_inf = flag
+
+    # -- optimizer step fused into the backward pass ----------------------------------------------
+    def enable_update_in_backward(self, sync_gradients_fn=None, mode: Optional[str] = None):
+        """Update every parameter as soon as its gradient is final, on a side stream, while the rest of the backward
+        pass still runs (the update is pure HBM traffic, the backward GEMMs are tensor-core bound, so the two overlap
+        almost for free; the gradient is released right away).  The single-device counterpart of the sharded engine's
+        fused reduce-scatter + AdamW.
+
+        ``mode``: ``"1"`` on from the first step, ``"0"`` never, ``"auto"`` (default, or
+        ``ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD``): the first step runs normally and the fusion switches on only if
+        nothing needed the gradients after backward (no clipping, no GradScaler, one backward per step).  Once on,
+        ``p.grad`` is ``None`` after backward; asking for clipping then raises with a pointer to the switch.
+        ``sync_gradients_fn`` returns False on gradient-accumulation micro-steps (no update then)."""
+        mode = mode or os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto")
+        if mode == "0" or self._bwd_hooks:
+            return
+        params = [p for g in self.param_groups for p in g["params"] if p.requires_grad]
+        if not params or not all(p.is_cuda for p in params):
+            return
+        self._sync_fn = sync_gradients_fn
+        self._bwd_stream = torch.cuda.Stream(device=params[0].device)
+        self._group_of = {p: g for g in self.param_groups for p in g["params"]}
+        for p in params:
+            self._bwd_hooks.append(p.register_post_accumulate_grad_hook(self._on_grad_ready))
+        self._bwd_mode = "active" if mode == "1" else "probing"
+
+    def _note_grad_consumer(self, what: str):
+        self._saw_grad_consumer = True
+        if self._bwd_mode == "active" and self._bwd_updated:
+            raise RuntimeError(
+                f"{what} was requested after the optimizer update already ran inside backward. "
+                "Set ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD=0 when gradients are needed after backward on some steps only."
+            )
+        if self._bwd_mode == "probing":
+            self._bwd_mode = "off"
+
+    @torch.no_grad()
+    def _on_grad_ready(self, p: torch.Tensor):
+        if self._bwd_mode == "probing":
+            self._bwd_fired[p] = self._bwd_fired.get(p, 0) + 1
+            return
+        if self._bwd_mode != "active" or p.grad is None:
+            return
+        if self._sync_fn is not None and not self._sync_fn():
+            return  # accumulation micro-step: keep summing into p.grad
+        if p in self._bwd_updated:
+            raise RuntimeError("a parameter received a second gradient after it was already updated inside backward "
+                               "(several backward passes per step): set ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD=0.")
+        g = p.grad
+        cur = torch.cuda.current_stream(p.device)
+        self._bwd_stream.wait_stream(cur)
+        with torch.cuda.stream(self._bwd_stream):
+            self._update_one(p, g, self._group_of[p])
+        g.record_stream(self._bwd_stream)
+        p.grad = None
+        self._bwd_updated.add(p)
+
+    def _update_one(self, p, g, group):
+        st = self.state[p]
+        if len(st) == 0:
+            st = self._init_state(p)
+        st["step"] += 1
+        b1, b2 = group["betas"]
+        if not g.is_contiguous():
+            g = g.contiguous()
+        if p.dtype == torch.float32:
+            master, shadow = p.data, None
+        elif "master" in st:
+            master, shadow = st["master"], p.data
+        else:  # no master copy requested: update an fp32 staging copy then write back
+            master, shadow = p.data.float(), p.data
+        if g.dtype not in (torch.float32, torch.bfloat16):
+            g = g.float()
+        F.adamw_flat_(master.view(-1), st["exp_avg"].view(-1), st["exp_avg_sq"].view(-1), g.view(-1),
+                      shadow.view(-1) if shadow is not None else None,
+                      lr=group["lr"], beta1=b1, beta2=b2, eps=group["eps"], weight_decay=group["weight_decay"],
+                      step=st["step"], grad_scale=self.grad_scale, clip_coef=self._clip_coef,
+                      found_inf=self._found_inf)
 
     def _init_state(self, p: torch.Tensor):
         st = self.state[p]
@@ -55,30 +144,19 @@ class FusedAdamW(torch.optim.Optimizer):
             with torch.enable_grad():
                 loss = closure()
         for group in self.param_groups:
-            b1, b2 = group["betas"]
             for p in group["params"]:
-                g = p.grad
-                if g is None:
+                if p.grad is None or p in self._bwd_updated:
                     continue
-                st = self.state[p]
-                if len(st) == 0:
-                    st = self._init_state(p)
-                st["step"] += 1
-                if not g.is_contiguous():
-                    g = g.contiguous()
-                if p.dtype == torch.float32:
-                    master, shadow = p.data, None
-                elif "master" in st:
-                    master, shadow = st["master"], p.data
-                else:  # no master copy requested: update an fp32 staging copy then write back
-                    master, shadow = p.data.float(), p.data
-                if g.dtype not in (torch.float32, torch.bfloat16):
-                    g = g.float()
-                F.adamw_flat_(master.view(-1), st["exp_avg"].view(-1), st["exp_avg_sq"].view(-1), g.view(-1),
-                              shadow.view(-1) if shadow is not None else None,
-                              lr=group["lr"], beta1=b1, beta2=b2, eps=group["eps"], weight_decay=group["weight_decay"],
-                              step=st["step"], grad_scale=self.grad_scale, clip_coef=self._clip_coef,
-                              found_inf=self._found_inf)
+                self._update_one(p, p.grad, group)
+        if self._bwd_updated:
+            # the next forward reads the parameters the side stream has just written
+            torch.cuda.current_stream().wait_stream(self._bwd_stream)
+            self._bwd_updated.clear()
+        if self._bwd_mode == "probing":
+            ok = (not self._saw_grad_consumer and self.grad_scale == 1.0 and self._bwd_fired
+                  and all(n == 1 for n in self._bwd_fired.values()))
+            self._bwd_mode = "active" if ok else "off"
+            self._bwd_fired.clear()
         self._clip_coef = None
         return loss
 

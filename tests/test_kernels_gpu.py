@@ -243,3 +243,36 @@ def test_rope_attention_autograd():
     oc.backward(do.cpu())
     assert rel_err(o.cpu(), oc) < 2e-2
     assert rel_err(x.grad.cpu(), xc.grad) < 4e-2
+
+
+@pytest.mark.gpu
+def test_fused_adamw_update_in_backward_matches_plain_step():
+    """FusedAdamW with the update fused into backward (side stream, grads released) == the ordinary step."""
+    from accelerate_hpc_test_b200.models import LlamaConfig, LlamaForCausalLM
+    from accelerate_hpc_test_b200.optim import FusedAdamW
+
+    cfg = LlamaConfig.tiny(num_hidden_layers=2)
+    torch.manual_seed(0)
+    a = LlamaForCausalLM(cfg, device="cuda")
+    torch.manual_seed(0)
+    b = LlamaForCausalLM(cfg, device="cuda")
+    oa = FusedAdamW(a.parameters(), lr=1e-3, weight_decay=0.01)
+    ob = FusedAdamW(b.parameters(), lr=1e-3, weight_decay=0.01)
+    ob.enable_update_in_backward(mode="auto")
+    ids = torch.randint(0, cfg.vocab_size, (2, 256), device="cuda")
+    for step in range(4):
+        for m, o in ((a, oa), (b, ob)):
+            o.zero_grad()
+            m(ids, labels=ids).loss.backward()
+            o.step()
+        if step == 0:
+            assert ob._bwd_mode == "active"  # probing step saw no clipping: fusion switched on
+        else:
+            assert all(p.grad is None for p in b.parameters())
+    torch.cuda.synchronize()
+    for (n, p), (_, q) in zip(a.named_parameters(), b.named_parameters()):
+        # the embedding gradient is accumulated with atomics (order-dependent rounding): one bf16 ulp of slack
+        assert (p.float() - q.float()).abs().max().item() <= 2e-4, n
+    with pytest.raises(RuntimeError):
+        b(ids, labels=ids).loss.backward()
+        ob.set_clip_coef(torch.ones(1, device="cuda"))
