@@ -38,7 +38,46 @@ struct Params {
   int num_m_tiles, num_n_tiles;
   const float* deq_a;  // fp8 only: per-tensor dequantisation factors (device scalars), result *= deq_a * deq_b
   const float* deq_b;
+  // ---- GEMM -> reduce-scatter (rs_world > 0): row r of D belongs to rank r / rs_rows; the epilogue stores this rank's
+  // partial straight into slot rs_rank of the owner's [rs_world][rs_rows][N] bf16 buffer (byte offset rs_off of its
+  // symmetric buffer) over NVLink.
+  uint8_t* rs_peer[8];
+  long long rs_off;
+  int rs_rows, rs_rank, rs_world;
+  // ---- all-gather -> GEMM (FUSE_AG): A = [ag_world * ag_rows, K] is assembled in ag_full from the shards every rank
+  // keeps at byte offset ag_off + rank * shard_bytes of its symmetric buffer.  Warp 3 of every CTA pulls the peers'
+  // shards with cp.async.bulk while the tensor cores already work on rows that are present; ag_ready[p] counts the
+  // bytes of shard p that landed (reaches ag_expect when complete).
+  uint8_t* ag_peer[8];
+  long long ag_off;
+  uint8_t* ag_full;
+  unsigned long long* ag_ready;
+  unsigned long long ag_expect;
+  int ag_rows, ag_rank, ag_world;
 };
+
+static constexpr int AGG_CHUNK = 8192;
+static constexpr int AGG_STAGES = 3;
+static constexpr int AGG_SMEM = AGG_CHUNK * AGG_STAGES + 64;
+static constexpr uint32_t kSpinLimit2 = 1u << 27;
+
+__device__ __forceinline__ void bulk_g2s_g2(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_s2g_g2(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)),
+               "r"(bytes)
+               : "memory");
+}
+// with the fused all-gather, visit the 256-row tiles of my own shard first, then the shards in arrival order
+__device__ __forceinline__ int ag_rotate2(int m_t, const Params& p) {
+  const int per_shard = (p.ag_rows + 255) / 256;
+  int r = m_t + p.ag_rank * per_shard;
+  return r >= p.num_m_tiles ? r - p.num_m_tiles : r;
+}
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -107,7 +146,7 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
 
 // FP8 = 1: operands are e4m3 bytes, K-major only; a k-block is still 128 bytes per row (128 elements), the MMA is
 // kind::f8f6f4 with K = 32 per instruction, and the epilogue applies the two per-tensor dequantisation factors.
-template <int A_MN, int B_MN, int FP8 = 0>
+template <int A_MN, int B_MN, int FP8 = 0, int FUSE_AG = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const Params p) {
   extern __shared__ uint8_t smem_raw[];
@@ -120,6 +159,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   uint64_t* tmem_full = bars + 2 * STAGES;      // [2]       per CTA, multicast commit
   uint64_t* tmem_empty = bars + 2 * STAGES + 2; // [2]       leader's: 8 arrivals (4 epilogue warps x 2 CTAs)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* ag_bars = bars + 2 * STAGES + 6;                        // [AGG_STAGES] (FUSE_AG)
+  uint8_t* ag_ring = smem + STAGES * STAGE_BYTES + 256;  // after the 256-byte barrier block
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();
@@ -143,6 +184,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], 8);
     }
+    if (FUSE_AG)
+      for (int i = 0; i < AGG_STAGES; ++i) mbar_init(&ag_bars[i], 1);
     fence_barrier_init();
   }
   cluster_sync_all();  // barriers of both CTAs exist before anybody signals across the pair
@@ -160,8 +203,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         int m_t, n_t;
         tile_coords(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+        if (FUSE_AG) m_t = ag_rotate2(m_t, p);
         const int m0 = m_t * 256 + (int)cta * BM;
         const int n0 = n_t * BN + (int)cta * BNH;
+        if (FUSE_AG && m0 < p.M) {
+          // rows [m0, m0 + BM) of A must have arrived: wait for the shard(s) they belong to
+          const int s_lo = m0 / p.ag_rows;
+          const int s_hi = min((m0 + BM - 1) / p.ag_rows, p.ag_world - 1);
+          for (int sh = s_lo; sh <= s_hi; ++sh) {
+            if (sh == p.ag_rank) continue;
+            uint32_t spins = 0;
+            while (*reinterpret_cast<volatile unsigned long long*>(p.ag_ready + sh) < p.ag_expect) {
+              __nanosleep(32);
+              if (++spins > kSpinLimit2) {
+                printf("b200 gemm2: all-gather shard %d never arrived (block %d)\n", sh, blockIdx.x);
+                __trap();
+              }
+            }
+          }
+          __threadfence();
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         for (int kb = 0; kb < num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           const uint32_t lbar = smem_u32(&full_bar[stage]) & PEER_MASK;  // the leader's barrier
@@ -216,6 +278,57 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
+  } else if (FUSE_AG && warp == 3) {
+    // ================================ all-gather warp (every CTA moves its share of the chunks) ================================
+    if (p.ag_world > 1 && elect_one()) {
+      const long long shard_bytes = (long long)p.ag_rows * p.K * 2;
+      const long long cps = (shard_bytes + AGG_CHUNK - 1) / AGG_CHUNK;
+      const long long total = cps * (p.ag_world - 1);
+      const long long n = (total > blockIdx.x) ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+      auto locate = [&](long long k, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes, int& peer) {
+        const long long g = blockIdx.x + k * (long long)gridDim.x;
+        const int slot = (int)(g / cps);
+        const long long c = g - (long long)slot * cps;
+        peer = (p.ag_rank + 1 + slot) % p.ag_world;
+        const long long o = c * AGG_CHUNK;
+        const long long left = shard_bytes - o;
+        bytes = (uint32_t)(left < AGG_CHUNK ? left : AGG_CHUNK);
+        src = p.ag_peer[peer] + p.ag_off + (long long)peer * shard_bytes + o;
+        dst = p.ag_full + (long long)peer * shard_bytes + o;
+      };
+      auto issue_load = [&](long long k) {
+        const uint8_t* src; uint8_t* dst; uint32_t bytes; int peer;
+        locate(k, src, dst, bytes, peer);
+        const int st = (int)(k % AGG_STAGES);
+        mbar_arrive_expect_tx(&ag_bars[st], bytes);
+        bulk_g2s_g2(ag_ring + st * AGG_CHUNK, src, bytes, &ag_bars[st]);
+      };
+      auto publish = [&](long long k) {  // chunk k is in local memory: account for its bytes
+        const uint8_t* s2; uint8_t* d2; uint32_t b2; int p2;
+        locate(k, s2, d2, b2, p2);
+        asm volatile("fence.proxy.async;" ::: "memory");
+        __threadfence();
+        atomicAdd(p.ag_ready + p2, (unsigned long long)b2);
+      };
+      for (long long k = 0; k < 2 && k < n; ++k) issue_load(k);
+      for (long long k = 0; k < n; ++k) {
+        const int st = (int)(k % AGG_STAGES);
+        mbar_wait(&ag_bars[st], (uint32_t)((k / AGG_STAGES) & 1));
+        const uint8_t* src; uint8_t* dst; uint32_t bytes; int peer;
+        locate(k, src, dst, bytes, peer);
+        bulk_s2g_g2(dst, ag_ring + st * AGG_CHUNK, bytes);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        if (k >= 1) {
+          asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");  // store k-1 done: publish it, its slot may refill
+          publish(k - 1);
+        }
+        if (k + 2 < n) issue_load(k + 2);
+      }
+      if (n > 0) {
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        publish(n - 1);
+      }
+    }
   } else if (warp >= 4) {
     // ================================ epilogue (both CTAs, own 128 rows) ================================
     const int e = warp - 4;
@@ -226,6 +339,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       int m_t, n_t;
       tile_coords(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+      if (FUSE_AG) m_t = ag_rotate2(m_t, p);
       const int row = m_t * 256 + (int)cta * BM + e * 32 + lane;
       const int n0 = n_t * BN;
       mbar_wait(&tmem_full[acc], acc_phase);
@@ -271,6 +385,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
             }
           } else {
             __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + (long long)row * p.ldc + col0;
+            if (p.rs_world > 0) {
+              // scatter: this row lives on rank `owner`; my partial goes to my slot of its buffer
+              const int owner = row / p.rs_rows;
+              const long long lrow = (long long)p.rs_rank * p.rs_rows + (row - owner * p.rs_rows);
+              crow = reinterpret_cast<__nv_bfloat16*>(p.rs_peer[owner] + p.rs_off) + lrow * p.N + col0;
+            }
             if (col0 + 32 <= p.N && vec_ok) {
 #pragma unroll
               for (int i = 0; i < 32; i += 8) {
@@ -311,17 +431,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   }
 }
 
-template <int A_MN, int B_MN, int FP8 = 0>
+template <int A_MN, int B_MN, int FP8 = 0, int FUSE_AG = 0>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t st) {
   static bool attr_set = false;
+  constexpr int smem_bytes = SMEM + (FUSE_AG ? AGG_SMEM : 0);
   if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(gemm2_kernel<A_MN, B_MN, FP8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    B200_CUDA(cudaFuncSetAttribute(gemm2_kernel<A_MN, B_MN, FP8, FUSE_AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
     attr_set = true;
   }
   int clusters = p.num_m_tiles * p.num_n_tiles;
   const int max_clusters = num_sms() / 2;
   if (clusters > max_clusters) clusters = max_clusters;
-  gemm2_kernel<A_MN, B_MN, FP8><<<clusters * 2, 256, SMEM, st>>>(ta, tb, p);
+  gemm2_kernel<A_MN, B_MN, FP8, FUSE_AG><<<clusters * 2, 256, smem_bytes, st>>>(ta, tb, p);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;
@@ -351,6 +472,7 @@ B200_API int b200_gemm2_bf16(const void* A, const void* B, void* C, const void* 
   p.num_m_tiles = (M + 255) / 256;
   p.num_n_tiles = (N + BN - 1) / BN;
   p.deq_a = p.deq_b = nullptr;
+  p.rs_world = 0; p.ag_world = 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (!a_mn_major && !b_mn_major) return launch<0, 0>(ta, tb, p, st);
   if (!a_mn_major && b_mn_major) return launch<0, 1>(ta, tb, p, st);
@@ -380,5 +502,62 @@ B200_API int b200_gemm2_e4m3(const void* A, const void* B, void* C, const void* 
   p.num_n_tiles = (N + BN - 1) / BN;
   p.deq_a = (const float*)deq_a;
   p.deq_b = (const float*)deq_b;
+  p.rs_world = 0; p.ag_world = 0;
   return launch<0, 0, 1>(ta, tb, p, reinterpret_cast<cudaStream_t>(stream));
+}
+
+// all-gather -> GEMM and GEMM -> reduce-scatter on the SM-pair kernel; same contracts as the b200_gemm_bf16_* versions
+B200_API int b200_gemm2_bf16_allgather_a(const void* const* peer_ptrs, int rank, int world, long long a_off, void* a_full,
+                                         int rows, const void* B, void* C, int N, int K, long long ldb, long long ldc,
+                                         int b_mn_major, void* ready, unsigned long long epoch, void* stream) {
+  using namespace b200;
+  using namespace b200::g2;
+  if (world < 1 || world > 8 || rows <= 0 || (K % 8) || (ldb % 8)) return B200_ERR_BAD_ARG;
+  const int M = rows * world;
+  CUtensorMap ta, tb;
+  int rc;
+  if ((rc = make_tmap_bf16_2d(&ta, a_full, K, M, K, BK, BM))) return rc;
+  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BK, BNH);
+  else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  Params p;
+  p.C = C; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = 0; p.accumulate = 0;
+  p.num_m_tiles = (M + 255) / 256; p.num_n_tiles = (N + BN - 1) / BN;
+  p.deq_a = p.deq_b = nullptr;
+  p.rs_world = 0;
+  for (int i = 0; i < 8; ++i) p.ag_peer[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
+  p.ag_off = a_off; p.ag_full = (uint8_t*)a_full; p.ag_ready = (unsigned long long*)ready;
+  p.ag_expect = epoch * (unsigned long long)rows * K * 2; p.ag_rows = rows; p.ag_rank = rank; p.ag_world = world;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!b_mn_major) return launch<0, 0, 0, 1>(ta, tb, p, st);
+  return launch<0, 1, 0, 1>(ta, tb, p, st);
+}
+
+B200_API int b200_gemm2_bf16_scatter(const void* A, const void* B, const void* const* peer_ptrs, int rank, int world,
+                                     long long out_off, int rows, int N, int K, long long lda, long long ldb, int a_mn_major,
+                                     int b_mn_major, void* stream) {
+  using namespace b200;
+  using namespace b200::g2;
+  if (world < 1 || world > 8 || rows <= 0 || (N % 8) || (lda % 8) || (ldb % 8)) return B200_ERR_BAD_ARG;
+  const int M = rows * world;
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = make_tmap_bf16_2d(&ta, A, K, M, lda, BK, BM);
+  else rc = make_tmap_bf16_2d(&ta, A, M, K, lda, 64, BK);
+  if (rc) return rc;
+  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BK, BNH);
+  else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  Params p;
+  p.C = nullptr; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = N; p.out_fp32 = 0; p.accumulate = 0;
+  p.num_m_tiles = (M + 255) / 256; p.num_n_tiles = (N + BN - 1) / BN;
+  p.deq_a = p.deq_b = nullptr;
+  p.ag_world = 0;
+  for (int i = 0; i < 8; ++i) p.rs_peer[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
+  p.rs_off = out_off; p.rs_rows = rows; p.rs_rank = rank; p.rs_world = world;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!a_mn_major && !b_mn_major) return launch<0, 0>(ta, tb, p, st);
+  if (!a_mn_major && b_mn_major) return launch<0, 1>(ta, tb, p, st);
+  if (a_mn_major && !b_mn_major) return launch<1, 0>(ta, tb, p, st);
+  return launch<1, 1>(ta, tb, p, st);
 }

@@ -34,6 +34,8 @@ _SIGNATURES = {
     "b200_amax_bf16": [P, L, P, P],
     "b200_quantize_e4m3": [P, L, I, I, P, P, L, P, L, P, P],
     "b200_gemm2_bf16": [P, P, P, P, I, I, I, L, L, L, I, I, I, I, P],
+    "b200_gemm2_bf16_allgather_a": [P, I, I, L, P, I, P, P, I, I, L, L, I, P, ctypes.c_ulonglong, P],
+    "b200_gemm2_bf16_scatter": [P, P, P, I, I, L, I, I, I, L, L, I, I, P],
     "b200_gemm_bf16_allgather_a": [P, I, I, L, P, I, P, P, I, I, L, L, I, P, ctypes.c_ulonglong, P],
     "b200_gemm_bf16_scatter": [P, P, P, I, I, L, I, I, I, L, L, I, I, P],
     "b200_reduce_slots": [P, P, I, L, P],

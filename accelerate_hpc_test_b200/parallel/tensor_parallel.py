@@ -33,6 +33,12 @@ from ..ops._lib import check, ptr
 BF16 = torch.bfloat16
 
 
+# SM-pair (cta_group::2) kernels by default; ACCELERATE_B200_GEMM_2CTA=0 selects the single-CTA versions
+_TWO_CTA = os.environ.get("ACCELERATE_B200_GEMM_2CTA", "1") != "0"
+_AG_GEMM = "b200_gemm2_bf16_allgather_a" if _TWO_CTA else "b200_gemm_bf16_allgather_a"
+_GEMM_RS = "b200_gemm2_bf16_scatter" if _TWO_CTA else "b200_gemm_bf16_scatter"
+
+
 class TPComm:
     """Communication context of one tensor-parallel group (symmetric buffers, channels, epochs)."""
 
@@ -132,7 +138,7 @@ class TPComm:
         self.ws.barrier(self.ch_ag)  # every rank's own slot is written (and nobody still reads this buffer)
         self.ready_epoch[buf] += 1
         y = torch.empty((t * self.world, n), dtype=BF16, device=x.device)
-        check(self.ws.lib.b200_gemm_bf16_allgather_a(
+        check(getattr(self.ws.lib, _AG_GEMM)(
             self.ws.peer_array, self.rank, self.world, off, ctypes.c_void_p(self.ws.base + off), t, ptr(w), ptr(y), n, k,
             w.stride(0), y.stride(0), int(b_mn_major), ptr(self.ready[buf]), self.ready_epoch[buf], _lib.cur_stream()), "gemm_allgather_a")
         return y, full
@@ -148,7 +154,7 @@ class TPComm:
         self.flip_rs ^= 1
         off = self.rs_off[buf]
         x = F._rowmajor2d(x)
-        check(self.ws.lib.b200_gemm_bf16_scatter(ptr(x), ptr(w), self.ws.peer_array, self.rank, self.world, off, t, n, k, x.stride(0),
+        check(getattr(self.ws.lib, _GEMM_RS)(ptr(x), ptr(w), self.ws.peer_array, self.rank, self.world, off, t, n, k, x.stride(0),
                                                  w.stride(0), 0, int(b_mn_major), _lib.cur_stream()), "gemm_scatter")
         self.ws.barrier(self.ch_rs)  # all partial tiles have landed in my slots
         out = torch.empty((t, n), dtype=BF16, device=x.device)
