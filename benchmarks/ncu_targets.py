@@ -22,5 +22,15 @@ for _ in range(3):
     o, lse = F.flash_attn_fwd(qkv, B, S, Hq, Hkv, D, True, 1 / math.sqrt(D))
     dqkv = F.flash_attn_bwd(torch.randn_like(o), qkv, o, lse, B, S, Hq, Hkv, D, True, 1 / math.sqrt(D))
     act = F.swiglu_fwd(y)
+# optimizer + fp8 path
+n = 4096 * 14336
+master = torch.randn(n, device=dev); m1 = torch.zeros(n, device=dev); v1 = torch.zeros(n, device=dev)
+g = torch.randn(n, device=dev).to(torch.bfloat16); sh = torch.empty(n, device=dev, dtype=torch.bfloat16)
+from accelerate_hpc_test_b200.parallel.precision import gemm_e4m3, quantize_e4m3
+for _ in range(2):
+    F.adamw_flat_(master, m1, v1, g, sh, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.01, step=3)
+    xq, _, dxs = quantize_e4m3(x)
+    wq, wqt, dws = quantize_e4m3(w, transpose=True)
+    y8 = gemm_e4m3(xq, wq, dxs, dws)
 torch.cuda.synchronize()
 print("ok")
