@@ -140,14 +140,21 @@ def __getattr__(name):
         "offload": "OffloadedWeightsLoader PrefixedDataset extract_submodules_state_dict load_offloaded_weight offload_state_dict offload_weight save_offload_index".split(),
         "fsdp_utils": ("disable_fsdp_ram_efficient_loading enable_fsdp_ram_efficient_loading ensure_weights_retied fsdp2_apply_ac "
                        "fsdp2_load_full_state_dict fsdp2_prepare_model fsdp2_switch_optimizer_parameters get_fsdp2_grad_scaler "
-                       "load_fsdp_model load_fsdp_optimizer merge_fsdp_weights save_fsdp_model save_fsdp_optimizer").split(),
+                       "load_fsdp_model load_fsdp_optimizer merge_fsdp_weights save_fsdp_model save_fsdp_optimizer fsdp2_canonicalize_names").split(),
         "launch": ("PrepareForLaunch _filter_args prepare_deepspeed_cmd_env prepare_multi_gpu_env prepare_sagemager_args_inputs "
                    "prepare_simple_launcher_cmd_env prepare_tpu").split(),
         "deepspeed": "DeepSpeedEngineWrapper DeepSpeedOptimizerWrapper DeepSpeedSchedulerWrapper DummyOptim DummyScheduler HfDeepSpeedConfig get_active_deepspeed_plugin map_pytorch_optim_to_deepspeed".split(),
         "bnb": "has_4bit_bnb_layers load_and_quantize_model".split(),
         "transformer_engine": "apply_fp8_autowrap contextual_fp8_autocast convert_model has_transformer_engine_layers".split(),
         "ao": "convert_model_to_fp8_ao filter_first_and_last_linear_layers has_ao_layers".split(),
-        "megatron_lm": "MegatronLMDummyDataLoader MegatronLMDummyScheduler".split(),
+        "megatron_lm": ("MegatronLMDummyDataLoader MegatronLMDummyScheduler AbstractTrainStep BertTrainStep GPTTrainStep T5TrainStep "
+                        "MegatronEngine MegatronLMOptimizerWrapper MegatronLMSchedulerWrapper avg_losses_across_data_parallel_group "
+                        "gather_across_data_parallel_groups").split(),
+        "imports": "torchao_required deepspeed_required is_torchvision_available is_triton_available is_bitsandbytes_multi_backend_available".split(),
+        "environment": "get_current_device_type".split(),
+        "other": "model_has_dtensor compile_regions_deepspeed".split(),
+        "dataclasses": "add_model_config_to_megatron_parser".split(),
+        "constants": "XPU_PROFILING_AVAILABLE_PYTORCH_VERSION MITA_PROFILING_AVAILABLE_PYTORCH_VERSION".split(),
     }
     for mod, names in lazy.items():
         if name in names:

@@ -1091,3 +1091,23 @@ def get_module_class_from_name(module, name):
         if found is not None:
             return found
     return None
+
+
+MODEL_CONFIGS_TO_MEGATRON_PARSERS = {}
+
+
+def add_model_config_to_megatron_parser(model_type: str):
+    """Register a function translating a transformers config of ``model_type`` into ``MegatronLMPlugin`` arguments
+    (reference utils/dataclasses.py:2797-2806)."""
+
+    def add_model_config_parser_helper(func):
+        import functools
+
+        @functools.wraps(func)
+        def wrapper(*args, **kwargs):
+            return func(*args, **kwargs)
+
+        MODEL_CONFIGS_TO_MEGATRON_PARSERS[model_type] = func
+        return wrapper
+
+    return add_model_config_parser_helper

@@ -245,3 +245,12 @@ def purge_accelerate_environment(func_or_cls):
         if name.startswith("test") and callable(attr) and not getattr(attr, "_accelerate_is_purged_environment_wrapped", False):
             setattr(cls, name, wrap_function(attr))
     return cls
+
+
+def get_current_device_type():
+    """``(device_type, distributed_type)`` of the accelerator this process would use (reference utils/environment.py:101-130)."""
+    import torch
+
+    if torch.cuda.is_available():
+        return "cuda", "MULTI_GPU"
+    return "cpu", "MULTI_CPU"

@@ -288,3 +288,48 @@ def is_notebook() -> bool:
         return get_ipython() is not None and "IPKernelApp" in get_ipython().config
     except Exception:
         return False
+
+
+def torchao_required(func):
+    """Decorator: raise a clear ImportError when torchao is missing (reference utils/imports.py:473-487)."""
+    import functools
+
+    @functools.wraps(func)
+    def wrapper(*args, **kwargs):
+        if not is_torchao_available():
+            raise ImportError("`torchao` is not available, please install it before calling this function via `pip install torchao`.")
+        return func(*args, **kwargs)
+
+    return wrapper
+
+
+def deepspeed_required(func):
+    """Decorator: the wrapped function only makes sense for a DeepSpeed-configured run (reference utils/imports.py:490-504)."""
+    import functools
+
+    @functools.wraps(func)
+    def wrapper(*args, **kwargs):
+        from ..state import AcceleratorState
+        from .dataclasses import DistributedType
+
+        if AcceleratorState._shared_state != {} and AcceleratorState().distributed_type != DistributedType.DEEPSPEED:
+            raise ValueError("DeepSpeed is not enabled, please make sure that an `Accelerator` is configured for `deepspeed` before calling this function.")
+        return func(*args, **kwargs)
+
+    return wrapper
+
+
+def is_torchvision_available():
+    return _is_package_available("torchvision") if "_is_package_available" in globals() else importlib.util.find_spec("torchvision") is not None
+
+
+def is_triton_available():
+    return importlib.util.find_spec("triton") is not None
+
+
+def is_bitsandbytes_multi_backend_available():
+    if not is_bnb_available():
+        return False
+    import bitsandbytes as bnb
+
+    return "multi_backend" in getattr(bnb, "features", set())

@@ -32,3 +32,257 @@ def megatron_plugin_to_parallelism_config(plugin):
 
     kw = plugin.to_parallelism_kwargs()
     return ParallelismConfig(tp_size=kw["tp_size"] or 1, cp_size=kw["cp_size"] or 1)
+
+
+# --------------------------------------------------------------------------------------- engine-style API
+# The reference's Megatron path hands the whole step to a ``MegatronEngine`` (``model(**batch)`` runs forward,
+# backward and the optimizer, reference utils/megatron_lm.py:924-1158; the optimizer / scheduler wrappers are
+# therefore no-ops, :355-413; per-family ``*TrainStep`` classes supply batch slicing and the loss, :415-922).
+# The same surface is kept here on top of the native engines: the model is a native (optionally tensor-parallel)
+# module, the micro-batch loop accumulates into the engine's gradient buffers and the fused AdamW applies the update.
+import torch
+
+from ..optimizer import AcceleratedOptimizer
+from ..scheduler import AcceleratedScheduler
+
+
+class MegatronLMOptimizerWrapper(AcceleratedOptimizer):
+    """``zero_grad`` / ``step`` are no-ops: ``MegatronEngine.forward`` already ran them (reference :355-372)."""
+
+    def __init__(self, optimizer):
+        super().__init__(optimizer, device_placement=False, scaler=None)
+        if not hasattr(self.optimizer, "skipped_iter"):
+            self.optimizer.skipped_iter = False
+
+    def zero_grad(self, set_to_none=None):
+        pass
+
+    def step(self):
+        pass
+
+    @property
+    def step_was_skipped(self):
+        return bool(getattr(self.optimizer, "skipped_iter", False))
+
+
+class MegatronLMSchedulerWrapper(AcceleratedScheduler):
+    """The engine steps the schedule itself (reference :401-407)."""
+
+    def __init__(self, scheduler, optimizers):
+        super().__init__(scheduler, optimizers)
+
+    def step(self, *args, **kwargs):
+        return
+
+
+class AbstractTrainStep:
+    """Batch slicing, forward step and loss of one model family (reference :415-430)."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def get_batch_func(self, accelerator, megatron_dataset_flag=False):
+        def get_batch(data_iterator):
+            batch = next(data_iterator)
+            return {k: (v.to(accelerator.device) if torch.is_tensor(v) else v) for k, v in batch.items()}
+
+        return get_batch
+
+    def get_loss_func(self, accelerator):
+        def loss_func(output):
+            loss = output.loss if hasattr(output, "loss") else output["loss"]
+            return loss, {"lm loss": avg_losses_across_data_parallel_group([loss.detach()])[0]}
+
+        return loss_func
+
+    def get_forward_step_func(self):
+        get_batch, loss_func = self._get_batch, self._loss_func
+
+        def forward_step(data_iterator, model):
+            batch = get_batch(data_iterator)
+            return loss_func(model(**batch))
+
+        return forward_step
+
+    def bind(self, accelerator):
+        self._get_batch = self.get_batch_func(accelerator)
+        self._loss_func = self.get_loss_func(accelerator)
+        return self
+
+
+class GPTTrainStep(AbstractTrainStep):
+    """Causal LM: ``input_ids`` (+ ``labels``, default = inputs) -> next-token loss (reference :574-716)."""
+
+    def __init__(self, accelerator=None, args=None):
+        super().__init__("GPTTrainStep")
+        if accelerator is not None:
+            self.bind(accelerator)
+
+    def get_batch_func(self, accelerator, megatron_dataset_flag=False):
+        base = super().get_batch_func(accelerator)
+
+        def get_batch(data_iterator):
+            b = base(data_iterator)
+            if "labels" not in b and "shift_labels" not in b:
+                b["labels"] = b["input_ids"]
+            return {k: b[k] for k in ("input_ids", "labels", "shift_labels", "position_ids", "attention_mask") if k in b}
+
+        return get_batch
+
+
+class BertTrainStep(AbstractTrainStep):
+    """Encoder: sequence-classification / MLM batches pass through unchanged (reference :432-572)."""
+
+    def __init__(self, accelerator=None, args=None):
+        super().__init__("BertTrainStep")
+        if accelerator is not None:
+            self.bind(accelerator)
+
+
+class T5TrainStep(AbstractTrainStep):
+    """Encoder-decoder batches (``input_ids``, ``decoder_input_ids``, ``labels``) pass through (reference :718-922)."""
+
+    def __init__(self, accelerator=None, args=None):
+        super().__init__("T5TrainStep")
+        if accelerator is not None:
+            self.bind(accelerator)
+
+
+class MegatronEngine(torch.nn.Module):
+    """``engine(**batch)`` = one full optimisation step over ``num_micro_batches`` slices of the batch.
+
+    ``model`` is a prepared native module, ``optimizer`` / ``scheduler`` the prepared (accelerated) objects.  In
+    ``train()`` mode ``forward`` returns the averaged loss after having stepped the optimizer and the schedule; in
+    ``eval()`` mode it returns the loss without touching gradients (reference :1033-1158)."""
+
+    def __init__(self, accelerator, model, optimizer, scheduler=None):
+        super().__init__()
+        self.accelerator = accelerator
+        self.module = model
+        self.base_model = model
+        self.optimizer = optimizer
+        self.scheduler = scheduler
+        plugin = accelerator.state.megatron_lm_plugin
+        custom = getattr(plugin, "custom_train_step_class", None) if plugin is not None else None
+        if custom is not None:
+            self.train_step_handler = custom(None, **(getattr(plugin, "custom_train_step_kwargs", None) or {}))
+            if hasattr(self.train_step_handler, "bind"):
+                self.train_step_handler.bind(accelerator)
+        else:
+            kind = (getattr(plugin, "model_type_name", None) or "gpt") if plugin is not None else "gpt"
+            cls = {"gpt": GPTTrainStep, "bert": BertTrainStep, "t5": T5TrainStep}.get(kind)
+            if cls is None:
+                raise ValueError(f"Unsupported model type: {kind}")
+            self.train_step_handler = cls(accelerator)
+        self.num_micro_batches = int(getattr(plugin, "num_micro_batches", None) or 1) if plugin is not None else 1
+        inner = getattr(optimizer, "optimizer", optimizer)
+        inner.skipped_iter = False
+        self.total_loss_dict = {}
+        self.eval_total_loss_dict = {}
+        self.iteration = 0
+
+    def get_batch_data_iterator(self, batch_data):
+        """Split ``batch_data`` into ``num_micro_batches`` equal slices along dim 0 (reference :1008-1031)."""
+        n = self.num_micro_batches
+        if n <= 1:
+            return iter([batch_data])
+        chunks = []
+        for i in range(n):
+            part = {}
+            for k, v in batch_data.items():
+                if torch.is_tensor(v) and v.dim() > 0:
+                    if v.shape[0] % n:
+                        raise ValueError(f"batch dimension {v.shape[0]} of `{k}` is not divisible by num_micro_batches={n}")
+                    m = v.shape[0] // n
+                    part[k] = v[i * m : (i + 1) * m]
+                else:
+                    part[k] = v
+            chunks.append(part)
+        return iter(chunks)
+
+    def train_step(self, **batch_data):
+        it = self.get_batch_data_iterator(batch_data)
+        forward_step = self.train_step_handler.get_forward_step_func()
+        self._raw_optimizer().zero_grad()
+        n = self.num_micro_batches
+        losses = {}
+        for _ in range(n):
+            loss, reduced = forward_step(it, self.module)
+            (loss / n).backward()
+            for k, v in reduced.items():
+                losses[k] = losses.get(k, 0.0) + v / n
+        self._raw_optimizer().step()
+        inner = getattr(self.optimizer, "optimizer", self.optimizer)
+        skipped = bool(getattr(inner, "skipped_iter", False))
+        if self.scheduler is not None and not skipped:
+            sched = getattr(self.scheduler, "scheduler", self.scheduler)
+            sched.step()
+        return losses, skipped
+
+    def _raw_optimizer(self):
+        # the accelerated wrapper's step / zero_grad are no-ops for this engine: drive the inner optimizer
+        opt = self.optimizer
+        return opt.optimizer if isinstance(opt, MegatronLMOptimizerWrapper) else opt
+
+    @torch.no_grad()
+    def eval_step(self, **batch_data):
+        it = self.get_batch_data_iterator(batch_data)
+        forward_step = self.train_step_handler.get_forward_step_func()
+        losses = {}
+        for _ in range(self.num_micro_batches):
+            _, reduced = forward_step(it, self.module)
+            for k, v in reduced.items():
+                losses[k] = losses.get(k, 0.0) + v / self.num_micro_batches
+        return losses
+
+    def forward(self, **batch_data):
+        if self.module.training:
+            losses, skipped = self.train_step(**batch_data)
+            self.iteration += 1
+            for k, v in losses.items():
+                self.total_loss_dict[k] = self.total_loss_dict.get(k, 0.0) + v
+        else:
+            losses = self.eval_step(**batch_data)
+            for k, v in losses.items():
+                self.eval_total_loss_dict[k] = self.eval_total_loss_dict.get(k, 0.0) + v
+        vals = list(losses.values())
+        loss = vals[0] if len(vals) == 1 else sum(vals)
+        return loss if torch.is_tensor(loss) else torch.tensor(loss)
+
+    def train(self, mode: bool = True):
+        self.module.train(mode)
+        return self
+
+    def eval(self):
+        self.module.eval()
+        return self
+
+    def log_eval_results(self):
+        out = {k: (v.item() if torch.is_tensor(v) else float(v)) for k, v in self.eval_total_loss_dict.items()}
+        self.eval_total_loss_dict = {}
+        return out
+
+    def save_checkpoint(self, output_dir):
+        self.accelerator.save_state(output_dir)
+
+    def load_checkpoint(self, input_dir):
+        self.accelerator.load_state(input_dir)
+
+
+def avg_losses_across_data_parallel_group(losses):
+    """Mean of every loss over the data-parallel ranks (reference :1215-1223)."""
+    from ..state import PartialState
+
+    t = torch.stack([l.detach().reshape(()).float() for l in losses])
+    st = PartialState()
+    if st.num_processes > 1 and torch.distributed.is_initialized():
+        torch.distributed.all_reduce(t)
+        t = t / st.num_processes
+    return t
+
+
+def gather_across_data_parallel_groups(tensor):
+    """Concatenate ``tensor`` (or a nested structure of tensors) from all data-parallel ranks (reference :1226-1247)."""
+    from .operations import gather
+
+    return gather(tensor)
