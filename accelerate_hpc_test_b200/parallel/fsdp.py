@@ -435,6 +435,7 @@ class B200ShardedModule(nn.Module):
                     off = u.offsets[i]
                     u.grad[off : off + _numel(u.params[i]._b200_full_shape)].zero_()
             if self.requires_gradient_sync:
+                self._reduce_model_parallel_replicas(u)
                 self._reduce_unit(u)
                 self._release_grad(u)
             else:
@@ -442,6 +443,17 @@ class B200ShardedModule(nn.Module):
         if u.unsharded and (self.reshard_after_forward or u.module is None or True):
             self.reshard(u)
         u.in_backward = False
+
+    def _reduce_model_parallel_replicas(self, u: _Unit):
+        """Parameters that a tensor-parallel group keeps whole (norms, LM head) only saw that rank's token shard: their
+        gradients are summed over the tp group before the data-parallel reduce-scatter (tensor_parallel._mark_replicated
+        leaves this to the engine when the parameter belongs to a sharded unit)."""
+        for p, off in zip(u.params, u.offsets):
+            g = getattr(p, "_b200_tp_group", None)
+            if g is None or torch.distributed.get_world_size(g) == 1:
+                continue
+            view = u.grad[off : off + _numel(p._b200_full_shape)]
+            torch.distributed.all_reduce(view, group=g)
 
     def _release_grad(self, u: _Unit):
         for p in u.params:

@@ -39,3 +39,41 @@ def _tp_parity():
 
 def test_tensor_parallel_llama_two_processes():
     debug_launcher(_tp_parity, num_processes=2)
+
+
+def _nd_parallel_parity():
+    """ParallelismConfig(tp_size=2, dp_shard_size=2): tensor-parallel model inside the sharded engine (BASELINE config 4,
+    reference examples/torch_native_parallelism/nd_parallel.py) against a single-process replay with the global batch."""
+    from accelerate_hpc_test_b200 import Accelerator
+    from accelerate_hpc_test_b200.parallelism_config import ParallelismConfig
+    from accelerate_hpc_test_b200.utils import FullyShardedDataParallelPlugin
+    from accelerate_hpc_test_b200.models import LlamaConfig, LlamaForCausalLM
+    cfg = LlamaConfig.tiny(head_dim=32, hidden_size=64, intermediate_size=128, vocab_size=128, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2)
+    torch.manual_seed(0); ref = LlamaForCausalLM(cfg, dtype=torch.float32)
+    torch.manual_seed(0); model = LlamaForCausalLM(cfg, dtype=torch.float32)
+    pc = ParallelismConfig(tp_size=2, dp_shard_size=2)
+    plugin = FullyShardedDataParallelPlugin(fsdp_version=2, auto_wrap_policy="transformer_based_wrap", transformer_cls_names_to_wrap=["LlamaDecoderLayer"])
+    acc = Accelerator(parallelism_config=pc, fsdp_plugin=plugin)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=0.0)
+    model, opt = acc.prepare(model, opt)
+    ropt = torch.optim.AdamW(ref.parameters(), lr=1e-3, weight_decay=0.0)
+    g = torch.Generator().manual_seed(3)
+    ids_all = torch.randint(0, cfg.vocab_size, (4, 16), generator=g)
+    dp_rank = acc.torch_device_mesh.get_local_rank("dp_shard")
+    ids = ids_all[dp_rank*2:(dp_rank+1)*2]
+    for step in range(2):
+        out = model(input_ids=ids, labels=ids)
+        acc.backward(out.loss)
+        opt.step(); opt.zero_grad()
+        ropt.zero_grad()
+        for r in range(2):
+            sub = ids_all[r*2:(r+1)*2]
+            (ref(input_ids=sub, labels=sub).loss / 2).backward()
+        ropt.step()
+    rl = ref(input_ids=ids, labels=ids).loss.item()
+    ml = model(input_ids=ids, labels=ids).loss.item()
+    assert abs(ml - rl) < 2e-4 * abs(rl), (ml, rl)
+
+
+def test_nd_parallel_tp2_x_fsdp2_four_processes():
+    debug_launcher(_nd_parallel_parity, num_processes=4)
