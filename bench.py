@@ -56,7 +56,9 @@ def parse_args():
     ap.add_argument("--model", default=os.environ.get("BENCH_MODEL", "llama3-8b"), choices=list(MODELS))
     ap.add_argument("--seq-len", type=int, default=2048)
     ap.add_argument("--micro-batch", type=int, default=int(os.environ.get("BENCH_MICRO_BATCH", 2)))
-    ap.add_argument("--parallelism", default="auto", help="auto | ddp | fsdp")
+    ap.add_argument("--parallelism", default="auto",
+                    help="auto | ddp | fsdp | tpN | spN | cpN  (tp/sp/cp: N ranks per model-parallel group, the rest is dp_shard)")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp8"], help="fp8: native e4m3 linear layers (ours arm)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -174,7 +176,12 @@ def run(args, build_fn):
     cfg = MODELS[args.model]
     step_device, step_e2e, info = build_fn(args, cfg, rank, world, local)
     n_host = 4
-    host_batches = make_batches(n_host, args.micro_batch, args.seq_len, cfg["vocab_size"], seed=1234 + rank)
+    # ranks of one tp / sp / cp group work on the same sequences; the model-parallel axis is the fastest mesh axis
+    mp = int(info.get("model_parallel_size", 1))
+    dp_world = world // mp
+    host_batches = make_batches(n_host, args.micro_batch, args.seq_len, cfg["vocab_size"], seed=1234 + rank // mp)
+    if info.get("shard_batch") is not None:
+        host_batches = [info["shard_batch"](b).contiguous().pin_memory() for b in host_batches]
     dev_batches = [b.cuda(non_blocking=True) for b in host_batches]
     torch.cuda.synchronize()
 
@@ -188,7 +195,7 @@ def run(args, build_fn):
     clocks = sampler.stop() if rank == 0 else {}
     launches = (info["launch_count"]() - launches0) if info.get("launch_count") else None
 
-    tokens_per_step = args.micro_batch * args.seq_len * world
+    tokens_per_step = args.micro_batch * args.seq_len * dp_world
     value = tokens_per_step * args.steps / (ms / 1e3)
 
     e2e = None
@@ -206,8 +213,8 @@ def run(args, build_fn):
             "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": value / (BASELINE_TOKENS_PER_S_PER_DEVICE * world) if args.model == "llama3-8b" else None,
-            "dtype": "bf16", "data": "synthetic random token ids; random-init weights", "impl": args.impl,
-            "config": {"model": args.model, "global_batch": args.micro_batch * world, "micro_batch_per_gpu": args.micro_batch,
+            "dtype": args.precision if args.impl == "ours" else "bf16", "data": "synthetic random token ids; random-init weights", "impl": args.impl,
+            "config": {"model": args.model, "global_batch": args.micro_batch * dp_world, "micro_batch_per_gpu": args.micro_batch,
                        "seq_len": args.seq_len, "parallelism": info["parallelism"], "optimizer": "AdamW",
                        "l2_policy": "working set per step (>100 GB) exceeds the 126 MB L2; no explicit flush",
                        "baseline_note": "vs_baseline = value / (8000 tokens/s/device x N), the reference's published 8xH100 FSDP2 bf16 figure"},
@@ -236,10 +243,22 @@ def build_ours(args, cfg, rank, world, local):
     if par == "auto":
         par = "fsdp" if world > 1 else "single"
     plugin = None
-    if par == "fsdp":
+    pc = None
+    mp_kind, mp = None, 1
+    if par[:2] in ("tp", "sp", "cp") and par[2:].isdigit():
+        from accelerate_hpc_test_b200.parallelism_config import ParallelismConfig
+
+        mp_kind, mp = par[:2], int(par[2:])
+        if world % mp:
+            raise SystemExit(f"--parallelism {par} needs a world size divisible by {mp}")
+        kw = {f"{mp_kind}_size": mp, "dp_shard_size": world // mp}
+        if mp_kind == "sp":
+            kw["sp_backend"] = "b200"
+        pc = ParallelismConfig(**kw)
+    if par == "fsdp" or pc is not None:
         plugin = FullyShardedDataParallelPlugin(fsdp_version=2, auto_wrap_policy="transformer_based_wrap",
                                                 transformer_cls_names_to_wrap=["LlamaDecoderLayer"])
-    accelerator = Accelerator(mixed_precision="bf16", fsdp_plugin=plugin)
+    accelerator = Accelerator(mixed_precision=args.precision, fsdp_plugin=plugin, parallelism_config=pc)
     lcfg = LlamaConfig(**cfg)
     torch.manual_seed(0)
     model = LlamaForCausalLM(lcfg, dtype=torch.bfloat16, device=accelerator.device)
@@ -259,8 +278,20 @@ def build_ours(args, cfg, rank, world, local):
         loss = step_device(ids)
         return float(loss.item())
 
-    info = {"parallelism": {"single": "single-gpu", "fsdp": f"fsdp2 full-shard dp_shard={world}", "ddp": f"ddp dp={world}"}[par],
-            "launch_count": _lib.launch_count, "flops_per_token": lcfg.flops_per_token(args.seq_len)}
+    names = {"single": "single-gpu", "fsdp": f"fsdp2 full-shard dp_shard={world}", "ddp": f"ddp dp={world}"}
+    shard_batch = None
+    if mp_kind == "sp":
+        c = args.seq_len // mp
+        r = accelerator.torch_device_mesh.get_local_rank("sp")
+        shard_batch = lambda b: b[:, r * c : (r + 1) * c]  # noqa: E731 - contiguous sequence slice of this sp rank
+    elif mp_kind == "cp":
+        from accelerate_hpc_test_b200.parallel.context_parallel import shard_sequence
+
+        r = accelerator.torch_device_mesh.get_local_rank("cp")
+        shard_batch = lambda b: shard_sequence(b, 1, r, mp)  # noqa: E731 - head + tail chunk of this cp rank
+    info = {"parallelism": names.get(par, f"{mp_kind}={mp} x fsdp2 dp_shard={world // mp}"),
+            "launch_count": _lib.launch_count, "flops_per_token": lcfg.flops_per_token(args.seq_len),
+            "model_parallel_size": mp, "shard_batch": shard_batch}
     return step_device, step_e2e, info
 
 
