@@ -10,9 +10,14 @@ bf16 master weights and run
 * dgrad    ``dx = dy W``     e4m3 x e4m3 (the weight is quantised once per forward into ``W_q`` and ``W_q^T``),
 * wgrad    ``dW = dy^T x``   bf16 (kept in high precision: it feeds the optimizer directly),
 
-with just-in-time per-tensor scaling (``amax`` pass + fused scale/cast/transpose, csrc/fp8.cu) — the "current
-scaling" recipe.  32-element MX block scales (``kind::mxf8f6f4.block_scale``) are the planned refinement; the
-entry point keeps the name the accelerator imports.
+in one of two recipes:
+
+* ``mxfp8`` (default): OCP microscaling — one UE8M0 power-of-two scale per 32 elements along the reduction dimension,
+  applied inside the tensor core by ``tcgen05.mma.kind::mxf8f6f4.block_scale`` (csrc/gemm_mxfp8.cu; quantisers produce the
+  scale bytes directly in the layout ``tcgen05.cp`` loads into TMEM);
+* ``tensorwise``: one just-in-time scale per tensor (``amax`` pass + fused scale/cast/transpose, csrc/fp8.cu) on the
+  2-CTA ``kind::f8f6f4`` GEMM.  Select with ``ACCELERATE_B200_FP8_RECIPE=tensorwise`` or
+  ``TERecipeKwargs(use_mxfp8_block_scaling=False)``.
 
 On CPU the same arithmetic is emulated with ``torch.float8_e4m3fn`` casts (the test oracle).
 """
@@ -79,6 +84,124 @@ def gemm_e4m3(a_q, b_q, deq_a, deq_b, bias=None, out_dtype=torch.bfloat16, out=N
     return out
 
 
+# ------------------------------------------------------------------------------------------- MXFP8 (block scaled)
+MX_BLOCK = 32
+
+
+def _sf_bytes(rows: int, k: int) -> int:
+    return ((rows + 127) // 128) * (k // 128) * 512
+
+
+def _mx_emulate(x: torch.Tensor):
+    """fp32 emulation of the OCP MX quantiser along the last dim: returns (q e4m3 [R, C], scale fp32 [R, C/32])."""
+    R, C = x.shape
+    g = x.float().view(R, C // MX_BLOCK, MX_BLOCK)
+    amax = g.abs().amax(-1)
+    e = torch.floor(torch.log2(amax.clamp(min=2.0**-126))) - 8.0
+    e = torch.where(amax == 0, torch.full_like(e, -127.0), e).clamp(-127.0, 127.0)
+    scale = torch.exp2(e)
+    q = (g / scale[..., None]).clamp(-E4M3_MAX, E4M3_MAX).to(FP8).view(R, C)
+    return q, scale
+
+
+class MXTensor:
+    """An e4m3 matrix ``[rows, k]`` with one power-of-two scale per 32 elements along ``k``.
+
+    On the GPU ``sf`` is the UE8M0 byte buffer in the 512-byte block layout the tensor core reads (csrc/gemm_mxfp8.cu);
+    on the CPU it is the fp32 scale matrix ``[rows, k/32]`` of the emulation."""
+
+    __slots__ = ("q", "sf")
+
+    def __init__(self, q, sf):
+        self.q, self.sf = q, sf
+
+    def dequantize(self) -> torch.Tensor:
+        if self.q.is_cuda:
+            raise NotImplementedError("dequantize() is the CPU oracle")
+        R, C = self.q.shape
+        return (self.q.float().view(R, C // MX_BLOCK, MX_BLOCK) * self.sf[..., None]).view(R, C)
+
+
+def quantize_mx(x: torch.Tensor, transpose: bool = False) -> MXTensor:
+    """MX-quantise ``x [R, C]`` along ``C``; with ``transpose`` the result is ``x^T [C, R]`` quantised along ``R``."""
+    R, C = x.shape
+    if not x.is_cuda:
+        return MXTensor(*_mx_emulate(x.t().contiguous() if transpose else x))
+    lib = _lib.require_gpu_lib()
+    if x.dtype != torch.bfloat16:
+        x = x.to(torch.bfloat16)
+    if x.stride(1) != 1:
+        x = x.contiguous()
+    rows, k = (C, R) if transpose else (R, C)
+    if k % 128:
+        raise ValueError(f"MXFP8 needs the reduction dimension ({k}) to be a multiple of 128")
+    q = torch.empty((rows, k), dtype=FP8, device=x.device)
+    sf = torch.zeros(_sf_bytes(rows, k), dtype=torch.uint8, device=x.device)
+    fn = lib.b200_quantize_mx_colwise if transpose else lib.b200_quantize_mx_rowwise
+    _lib.check(fn(_lib.ptr(x), x.stride(0), R, C, _lib.ptr(q), q.stride(0), _lib.ptr(sf), _lib.cur_stream()), "quantize_mx")
+    return MXTensor(q, sf)
+
+
+def gemm_mxfp8(a: MXTensor, b: MXTensor, bias=None, out_dtype=torch.bfloat16, out=None, accumulate=False):
+    """``D[M,N] = dequant(A)[M,K] dequant(B)[N,K]^T (+ bias)`` with the scales applied inside the tensor core."""
+    M, K = a.q.shape
+    N = b.q.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=a.q.device)
+    if not a.q.is_cuda:
+        r = a.dequantize() @ b.dequantize().t()
+        if bias is not None:
+            r = r + bias.float()
+        if accumulate:
+            r = r + out.float()
+        out.copy_(r.to(out.dtype))
+        return out
+    lib = _lib.require_gpu_lib()
+    if bias is not None:
+        bias = bias.to(torch.bfloat16).contiguous()
+    _lib.check(lib.b200_gemm_mxfp8(_lib.ptr(a.q), _lib.ptr(b.q), _lib.ptr(a.sf), _lib.ptr(b.sf), _lib.ptr(out), _lib.ptr(bias), M, N, K,
+                                   a.q.stride(0), b.q.stride(0), out.stride(0), int(out.dtype == torch.float32), int(accumulate),
+                                   _lib.cur_stream()), "gemm_mxfp8")
+    return out
+
+
+class _MxFp8LinearFn(torch.autograd.Function):
+    """fwd and dgrad on the block-scaled fp8 tensor cores; wgrad in bf16 (see module docstring)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        shp = x.shape
+        x2 = x.reshape(-1, shp[-1])
+        cdt = torch.bfloat16 if x2.is_cuda else x2.dtype
+        y = gemm_mxfp8(quantize_mx(x2), quantize_mx(weight.detach()), bias=bias, out_dtype=cdt)
+        ctx.save_for_backward(x2, weight)
+        ctx.has_bias = bias is not None
+        ctx.in_shape = shp
+        return y.view(*shp[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if dy2.dtype != weight.dtype:
+            dy2 = dy2.to(weight.dtype)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            # dX[M,K] = dY[M,N] W[N,K]: reduction over N -> dY scaled along N, W^T [K,N] scaled along N
+            dx = gemm_mxfp8(quantize_mx(dy2), quantize_mx(weight.detach(), transpose=True), out_dtype=dy2.dtype).view(ctx.in_shape)
+        if ctx.needs_input_grad[1]:
+            dw = F.deliver_weight_grad(
+                weight, lambda out, acc: F.gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=out, accumulate=acc)
+            )
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = dy2.float().sum(0).to(dy2.dtype)
+        return dx, dw, db
+
+
+def mxfp8_linear(x, weight, bias=None):
+    return _MxFp8LinearFn.apply(x, weight, bias)
+
+
 class _Fp8LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias):
@@ -117,9 +240,21 @@ def fp8_linear(x, weight, bias=None):
     return _Fp8LinearFn.apply(x, weight, bias)
 
 
-def _eligible(mod: nn.Module) -> bool:
+def _eligible(mod: nn.Module, multiple: int = 16) -> bool:
     w = getattr(mod, "weight", None)
-    return w is not None and w.dim() == 2 and w.shape[0] % 16 == 0 and w.shape[1] % 16 == 0
+    return w is not None and w.dim() == 2 and w.shape[0] % multiple == 0 and w.shape[1] % multiple == 0
+
+
+def _recipe_name(recipe) -> str:
+    """``mxfp8`` (1x32 block scales, the default) or ``tensorwise`` (one just-in-time scale per tensor)."""
+    import os
+
+    env = os.environ.get("ACCELERATE_B200_FP8_RECIPE")
+    if env:
+        return env.lower()
+    if recipe is not None and getattr(recipe, "use_mxfp8_block_scaling", None) is False:
+        return "tensorwise"
+    return "mxfp8"
 
 
 def convert_model_to_mxfp8(model: nn.Module, recipe=None, skip: Optional[Iterable[str]] = None) -> nn.Module:
@@ -139,23 +274,26 @@ def convert_model_to_mxfp8(model: nn.Module, recipe=None, skip: Optional[Iterabl
         model._fp8_use_during_eval = bool(recipe.use_during_eval)
     if keep_ends and len(linears) > 2:
         skip.update({linears[0][0], linears[-1][0]})
+    kind = _recipe_name(recipe)
     converted = 0
     for name, mod in linears:
-        if name in skip or name.endswith("lm_head") or not _eligible(mod):
+        if name in skip or name.endswith("lm_head") or not _eligible(mod, 128 if kind == "mxfp8" else 16):
             continue
-        _patch_forward(mod)
+        _patch_forward(mod, kind)
         converted += 1
     model._b200_fp8_layers = converted
+    model._b200_fp8_recipe = kind
     return model
 
 
-def _patch_forward(mod: nn.Module):
+def _patch_forward(mod: nn.Module, kind: str = "mxfp8"):
     if getattr(mod, "_b200_fp8", False):
         return
     mod._b200_fp8 = True
+    fn = mxfp8_linear if kind == "mxfp8" else fp8_linear
 
-    def forward(x, _m=mod):
-        return fp8_linear(x, _m.weight, _m.bias)
+    def forward(x, _m=mod, _fn=fn):
+        return _fn(x, _m.weight, _m.bias)
 
     mod.forward = forward
 

@@ -29,3 +29,23 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def main_mx():
+    from accelerate_hpc_test_b200.parallel.precision import gemm_mxfp8, quantize_mx
+
+    T = 8192
+    for name, M, N, K in [("qkv", T, 6144, 4096), ("gate_up", T, 28672, 4096), ("down", T, 4096, 14336)]:
+        x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+        w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16)
+        xq, wq = quantize_mx(x), quantize_mx(w)
+        fl = 2.0 * M * N * K
+        t8 = timeit(lambda: gemm_mxfp8(xq, wq))
+        tq = timeit(lambda: quantize_mx(x))
+        tqt = timeit(lambda: quantize_mx(w, transpose=True))
+        print(json.dumps(dict(shape=name, kind="mxfp8", M=M, N=N, K=K, ms=t8, tflops=fl / t8 / 1e9, quant_x_ms=tq, quant_w_t_ms=tqt)), flush=True)
+
+
+if __name__ == "__main__":
+    if os.environ.get("MX", "1") == "1":
+        main_mx()
