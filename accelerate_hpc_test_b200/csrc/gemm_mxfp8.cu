@@ -10,13 +10,14 @@
 //   w0 TMA producer, w1 MMA issuer (UTCCP scale copies + 4 MMAs of K = 32 per stage), w2 TMEM allocator, w4-7 epilogue.
 // Scale-factor storage (global and shared): 512-byte blocks, one per (128 rows, 128 k): byte (r % 32) * 16 + (r / 32) * 4 + g
 // holds the scale of row r, k-group g — the layout tcgen05.cp.32x128b.warpx4 turns into "lane r % 32, column r / 32".
-#include "common.cuh"
+#include "cluster2.cuh"
 #include <cuda_fp8.h>
 
 namespace b200 {
 
 int make_tmap_u8_2d(CUtensorMap* out, const void* base, long long inner, long long outer, long long row_stride,
                     int box_inner, int box_outer);
+int make_tmap_sf_blocks(CUtensorMap* out, const void* base, long long nblocks);
 int num_sms();
 
 namespace mx {
@@ -341,6 +342,241 @@ quantize_mx_colwise_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, i
 }
 
 }  // namespace mx
+
+// ------------------------------------------------------------------------------------------------ SM-pair version
+// Cluster of two CTAs, 256 x 256 x 128 tile: each CTA stages its 128 rows of A, half of B, its own 128 rows of A-scales
+// and the B-scales of all 256 columns; the leader issues tcgen05.cp.cta_group::2 (scales smem -> TMEM in both CTAs) and
+// tcgen05.mma.cta_group::2.kind::mxf8f6f4.block_scale (M = 256).  512 TMEM columns cannot hold two 256-column
+// accumulators plus the scale columns, so there is ONE accumulator stage; eight epilogue warps drain it into
+// registers (bf16-packed), hand TMEM back, and only then do the global stores, which overlap the next tile's MMAs.
+namespace mx2 {
+
+static constexpr int BM = 128, BN = 256, BNH = 128, BK = 128;
+static constexpr int STAGES = 5;
+static constexpr int A_BYTES = BM * BK, B_BYTES = BNH * BK, SFA_BYTES = 512, SFB_BYTES = 1024;
+static constexpr int STAGE_BYTES = A_BYTES + B_BYTES + SFA_BYTES + SFB_BYTES;  // 34,304
+static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 + 256;
+static constexpr int THREADS = 384;  // w0 TMA, w1 MMA, w2 TMEM alloc, w3 idle, w4-11 epilogue
+static constexpr int GROUP_M = 4;
+
+struct Params {
+  void* C;
+  const void* bias;
+  int M, N, K;
+  long long ldc;
+  int out_fp32, accumulate;
+  int num_m_tiles, num_n_tiles;
+};
+
+__device__ __forceinline__ void utccp_2sm(uint32_t tmem_dst, uint64_t sdesc) {
+  asm volatile("tcgen05.cp.cta_group::2.32x128b.warpx4 [%0], %1;" ::"r"(tmem_dst), "l"(sdesc) : "memory");
+}
+__device__ __forceinline__ void umma_mxf8_2sm(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc,
+                                              uint32_t tsfa, uint32_t tsfb) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::mxf8f6f4.block_scale [%0], %1, %2, %3, [%5], [%6], p;\n\t}\n" ::"r"(tmem_d),
+      "l"(da), "l"(db), "r"(idesc), "r"(acc), "r"(tsfa), "r"(tsfb)
+      : "memory");
+}
+__device__ __forceinline__ void tile_coords2(int tile, int num_m, int num_n, int& m_t, int& n_t) {
+  const int per_group = GROUP_M * num_n;
+  const int group = tile / per_group;
+  const int first_m = group * GROUP_M;
+  const int gm = min(GROUP_M, num_m - first_m);
+  const int r = tile - group * per_group;
+  m_t = first_m + (r % gm);
+  n_t = r / gm;
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
+gemm2_mxfp8_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                   const __grid_constant__ CUtensorMap tmap_sfa, const __grid_constant__ CUtensorMap tmap_sfb, const Params p) {
+  using namespace c2;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + STAGES * A_BYTES;
+  uint8_t* smem_sf = smem_b + STAGES * B_BYTES;  // [STAGES][SFA 512 | SFB 1024]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_sf + STAGES * (SFA_BYTES + SFB_BYTES));
+  uint64_t* full_bar = bars;                 // [STAGES] leader's are waited on
+  uint64_t* empty_bar = bars + STAGES;       // [STAGES] per CTA (multicast commit)
+  uint64_t* tmem_full = bars + 2 * STAGES;   // per CTA (multicast commit)
+  uint64_t* tmem_empty = bars + 2 * STAGES + 1;  // leader's: 16 arrivals (8 epilogue warps x 2 CTAs)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = cta == 0;
+  const int num_k_blocks = p.K / BK;
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tensormap(&tmap_a); prefetch_tensormap(&tmap_b);
+    prefetch_tensormap(&tmap_sfa); prefetch_tensormap(&tmap_sfb);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(tmem_full, 1);
+    mbar_init(tmem_empty, 16);
+    fence_barrier_init();
+  }
+  cluster_sync_all();
+  if (warp == 2) tmem_alloc_2sm<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tsfa = tmem_base + 256, tsfb = tmem_base + 260;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        int m_t, n_t;
+        tile_coords2(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+        const int m_blk = m_t * 2 + (int)cta;  // my 128 rows of A (and their scales)
+        const int n_blk = n_t * 2 + (int)cta;  // my 128 rows of B
+        for (int kb = 0; kb < num_k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          const uint32_t lbar = smem_u32(&full_bar[stage]) & PEER_MASK;
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+          uint8_t* ssf = smem_sf + stage * (SFA_BYTES + SFB_BYTES);
+          tma_load_2d_2sm(smem_a + stage * A_BYTES, &tmap_a, lbar, kb * BK, m_blk * BM);
+          tma_load_2d_2sm(smem_b + stage * B_BYTES, &tmap_b, lbar, kb * BK, n_blk * BNH);
+          tma_load_2d_2sm(ssf, &tmap_sfa, lbar, 0, m_blk * num_k_blocks + kb);
+          tma_load_2d_2sm(ssf + SFA_BYTES, &tmap_sfb, lbar, 0, (n_t * 2) * num_k_blocks + kb);
+          tma_load_2d_2sm(ssf + SFA_BYTES + 512, &tmap_sfb, lbar, 0, (n_t * 2 + 1) * num_k_blocks + kb);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader && elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        mbar_wait(tmem_empty, acc_phase ^ 1);
+        tc_fence_after();
+        for (int kb = 0; kb < num_k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem_a + stage * A_BYTES);
+          const uint32_t sb = smem_u32(smem_b + stage * B_BYTES);
+          const uint32_t ssf = smem_u32(smem_sf + stage * (SFA_BYTES + SFB_BYTES));
+          // the tensor pipe executes these in issue order: the copies overwrite the scale columns only after the
+          // previous k-block's MMAs have read them
+          utccp_2sm(tsfa, mx::sf_desc(ssf));
+          utccp_2sm(tsfb, mx::sf_desc(ssf + SFA_BYTES));
+          utccp_2sm(tsfb + 4, mx::sf_desc(ssf + SFA_BYTES + 512));
+#pragma unroll
+          for (int k = 0; k < BK / 32; ++k) {
+            const uint64_t da = make_umma_desc(sa + k * 32, 16, 1024);
+            const uint64_t db = make_umma_desc(sb + k * 32, 16, 1024);
+            umma_mxf8_2sm(tmem_base, da, db, mx::idesc_mx(256, BN, (uint32_t)k), (kb > 0 || k > 0) ? 1u : 0u, tsfa, tsfb);
+          }
+          umma_commit_2sm(&empty_bar[stage]);
+          if (kb == num_k_blocks - 1) umma_commit_2sm(tmem_full);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        acc_phase ^= 1;
+      }
+    }
+  } else if (warp >= 4) {
+    // ---- epilogue: 8 warps; warp pair (quadrant q) splits the 256 columns in two halves
+    const int q = warp & 3, half = (warp - 4) >> 2;
+    uint32_t acc_phase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      int m_t, n_t;
+      tile_coords2(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+      const int row = m_t * 256 + (int)cta * BM + q * 32 + lane;
+      const int n0 = n_t * BN + half * 128;
+      mbar_wait(tmem_full, acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + half * 128;
+      if (!p.out_fp32) {
+        const __nv_bfloat16* bias = reinterpret_cast<const __nv_bfloat16*>(p.bias);
+#pragma unroll 1
+        for (int rnd = 0; rnd < 2; ++rnd) {  // 64 columns per round, held as 32 packed bf16 pairs
+          uint32_t packed[32];
+#pragma unroll
+          for (int c = 0; c < 64; c += 32) {
+            uint32_t v[32];
+            tmem_ld_32x32b_x32(taddr + rnd * 64 + c, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) packed[(c + i) >> 1] = f2_to_bf2(__uint_as_float(v[i]), __uint_as_float(v[i + 1]));
+          }
+          if (rnd == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(smem_u32(tmem_empty) & PEER_MASK);  // TMEM is free: the next tile may start
+          }
+          const int nc = n0 + rnd * 64;
+          if (row < p.M && nc < p.N) {
+            __nv_bfloat16* crow = reinterpret_cast<__nv_bfloat16*>(p.C) + (long long)row * p.ldc + nc;
+            const bool fast = (nc + 64 <= p.N) && (p.ldc % 8 == 0) && bias == nullptr && !p.accumulate;
+            if (fast) {
+#pragma unroll
+              for (int i = 0; i < 32; i += 4)
+                *reinterpret_cast<uint4*>(crow + 2 * i) = make_uint4(packed[i], packed[i + 1], packed[i + 2], packed[i + 3]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {  // compile-time indices keep `packed` in registers
+                const int col = nc + 2 * i;
+                if (col < p.N) {
+                  float2 t = bf2_to_f2(packed[i]);
+                  if (bias) {
+                    t.x += __bfloat162float(__ldg(bias + col));
+                    if (col + 1 < p.N) t.y += __bfloat162float(__ldg(bias + col + 1));
+                  }
+                  if (p.accumulate) {
+                    t.x += __bfloat162float(crow[2 * i]);
+                    if (col + 1 < p.N) t.y += __bfloat162float(crow[2 * i + 1]);
+                  }
+                  crow[2 * i] = __float2bfloat16(t.x);
+                  if (col + 1 < p.N) crow[2 * i + 1] = __float2bfloat16(t.y);
+                }
+              }
+            }
+          }
+        }
+      } else {
+        // fp32 output: stream straight from TMEM (keeps full precision), then release
+#pragma unroll 1
+        for (int c = 0; c < 128; c += 32) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(taddr + c, v);
+          tmem_ld_wait();
+          if (row < p.M) {
+            float* crow = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + n0 + c;
+            for (int i = 0; i < 32; ++i)
+              if (n0 + c + i < p.N) {
+                float o = __uint_as_float(v[i]);
+                if (p.bias) o += __bfloat162float(__ldg(reinterpret_cast<const __nv_bfloat16*>(p.bias) + n0 + c + i));
+                crow[i] = p.accumulate ? crow[i] + o : o;
+              }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(smem_u32(tmem_empty) & PEER_MASK);
+      }
+      acc_phase ^= 1;
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_2sm<512>(tmem_base);
+  }
+}
+
+}  // namespace mx2
 }  // namespace b200
 
 using namespace b200;
@@ -400,6 +636,37 @@ B200_API int b200_quantize_mx_colwise(const void* x, long long ldx, int R, int C
   dim3 grid((C + 63) / 64, R / 128);
   quantize_mx_colwise_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ldx, R, C, (uint8_t*)qt, ldqt,
                                                                      (uint8_t*)sft);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// Same contract as b200_gemm_mxfp8 on an SM pair (256 x 256 tiles).  The scale buffers must cover whole 256-row
+// tiles: b200_mx_sf_bytes(round_up(rows, 256), k) bytes, zero-initialised.
+B200_API int b200_gemm2_mxfp8(const void* A, const void* B, const void* sfa, const void* sfb, void* C, const void* bias, int M,
+                              int N, int K, long long lda, long long ldb, long long ldc, int out_fp32, int accumulate,
+                              void* stream) {
+  using namespace b200::mx2;
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((K % BK) || (lda % 16) || (ldb % 16) || !sfa || !sfb) return B200_ERR_BAD_ARG;
+  CUtensorMap ta, tb, tsa, tsb;
+  int rc;
+  if ((rc = make_tmap_u8_2d(&ta, A, K, M, lda, BK, BM))) return rc;
+  if ((rc = make_tmap_u8_2d(&tb, B, K, N, ldb, BK, BNH))) return rc;
+  Params p;
+  p.C = C; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.num_m_tiles = (M + 255) / 256; p.num_n_tiles = (N + BN - 1) / BN;
+  const long long kblocks = K / BK;
+  if ((rc = make_tmap_sf_blocks(&tsa, sfa, (long long)p.num_m_tiles * 2 * kblocks))) return rc;
+  if ((rc = make_tmap_sf_blocks(&tsb, sfb, (long long)p.num_n_tiles * 2 * kblocks))) return rc;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA(cudaFuncSetAttribute(gemm2_mxfp8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    attr = true;
+  }
+  int clusters = p.num_m_tiles * p.num_n_tiles;
+  if (clusters > num_sms() / 2) clusters = num_sms() / 2;
+  gemm2_mxfp8_kernel<<<clusters * 2, THREADS, SMEM, (cudaStream_t)stream>>>(ta, tb, tsa, tsb, p);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;

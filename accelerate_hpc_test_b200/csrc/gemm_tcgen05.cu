@@ -460,6 +460,29 @@ int make_tmap_u8_2d(CUtensorMap* out, const void* base, long long inner, long lo
   return 0;
 }
 
+// scale-factor blocks of the MXFP8 GEMM: `nblocks` rows of 512 bytes, loaded one row at a time, no swizzle
+int make_tmap_sf_blocks(CUtensorMap* out, const void* base, long long nblocks) {
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(0);
+    ctx_bound = true;
+  }
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return B200_ERR_DRIVER;
+  cuuint64_t dims[2] = {128, (cuuint64_t)nblocks};  // 128 x uint32 = 512 bytes per row
+  cuuint64_t strides[1] = {512};
+  cuuint32_t box[2] = {128, 1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr, "b200: cuTensorMapEncodeTiled(sf) failed (CUresult %d): base=%p nblocks=%lld\n", (int)r, base, nblocks);
+    return B200_ERR_DRIVER;
+  }
+  return 0;
+}
+
 int num_sms() {
   static int cached[64] = {0};
   int dev = 0;

@@ -30,6 +30,7 @@ U = ctypes.c_uint
 _SIGNATURES = {
     "b200_gemm_bf16": [P, P, P, P, I, I, I, L, L, L, I, I, I, I, I, P],
     "b200_seq_head_exchange": [P, I, I, L, P, I, I, I, L, L, P, I, I, I, U, P, I, P],
+    "b200_gemm2_mxfp8": [P, P, P, P, P, P, I, I, I, L, L, L, I, I, P],
     "b200_gemm_mxfp8": [P, P, P, P, P, P, I, I, I, L, L, L, I, I, P],
     "b200_quantize_mx_rowwise": [P, L, I, I, P, L, P, P],
     "b200_quantize_mx_colwise": [P, L, I, I, P, L, P, P],

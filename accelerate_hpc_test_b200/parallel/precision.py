@@ -89,7 +89,8 @@ MX_BLOCK = 32
 
 
 def _sf_bytes(rows: int, k: int) -> int:
-    return ((rows + 127) // 128) * (k // 128) * 512
+    # whole 256-row tiles: the SM-pair kernel's tensor map covers both 128-row blocks of its last tile
+    return ((rows + 255) // 256) * 2 * (k // 128) * 512
 
 
 def _mx_emulate(x: torch.Tensor):
@@ -159,7 +160,10 @@ def gemm_mxfp8(a: MXTensor, b: MXTensor, bias=None, out_dtype=torch.bfloat16, ou
     lib = _lib.require_gpu_lib()
     if bias is not None:
         bias = bias.to(torch.bfloat16).contiguous()
-    _lib.check(lib.b200_gemm_mxfp8(_lib.ptr(a.q), _lib.ptr(b.q), _lib.ptr(a.sf), _lib.ptr(b.sf), _lib.ptr(out), _lib.ptr(bias), M, N, K,
+    import os
+
+    fn = lib.b200_gemm_mxfp8 if os.environ.get("ACCELERATE_B200_GEMM_2CTA", "1") == "0" or M <= 128 else lib.b200_gemm2_mxfp8
+    _lib.check(fn(_lib.ptr(a.q), _lib.ptr(b.q), _lib.ptr(a.sf), _lib.ptr(b.sf), _lib.ptr(out), _lib.ptr(bias), M, N, K,
                                    a.q.stride(0), b.q.stride(0), out.stride(0), int(out.dtype == torch.float32), int(accumulate),
                                    _lib.cur_stream()), "gemm_mxfp8")
     return out

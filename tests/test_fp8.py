@@ -118,7 +118,7 @@ def test_mx_quantizers_match_emulation(R, C):
     qe, se = _mx_emulate(x)
     assert torch.equal(t.q.float(), qe.float())
     # un-swizzle the scale bytes: block (r/128, g/4), byte (r%32)*16 + ((r/32)%4)*4 + g%4
-    sf = t.sf.view(-1, C // 128, 32, 4, 4)  # [mblk, kblk, r%32, (r/32)%4, g%4]
+    sf = t.sf.view(-1, C // 128, 32, 4, 4)  # [mblk (padded to whole 256-row tiles), kblk, r%32, (r/32)%4, g%4]
     r = torch.arange(R, device="cuda")
     g = torch.arange(C // 32, device="cuda")
     got = sf[(r // 128)[:, None], (g // 4)[None, :], (r % 32)[:, None], ((r // 32) % 4)[:, None], (g % 4)[None, :]]
