@@ -267,23 +267,22 @@ __device__ __forceinline__ long long sf_offset(long long r, long long g, long lo
   return ((r >> 7) * kblocks + (g >> 2)) * 512 + (r & 31) * 16 + ((r >> 5) & 3) * 4 + (g & 3);
 }
 
-// x [R, C] bf16 (row stride ldx) -> q [R, C] e4m3 (row stride ldq), scales along C.  One thread per (row, 128 columns).
+// x [R, C] bf16 (row stride ldx) -> q [R, C] e4m3 (row stride ldq), scales along C.
+// One thread per 32-element group: a warp reads 2 KB of one row contiguously (64 B per lane), every lane owns the
+// scale of its group, and each quad of lanes merges its four scale bytes into one 32-bit store.
 __global__ void __launch_bounds__(256)
 quantize_mx_rowwise_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int R, int C, uint8_t* __restrict__ q,
                            long long ldq, uint8_t* __restrict__ sf) {
-  const int chunks = C >> 7;
-  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long long)R * chunks) return;
-  const int r = (int)(idx / chunks), j = (int)(idx - (long long)r * chunks);
-  const __nv_bfloat16* src = x + (long long)r * ldx + j * 128;
-  uint8_t* dst = q + (long long)r * ldq + j * 128;
-  uint32_t sfw = 0;
-#pragma unroll
-  for (int g = 0; g < 4; ++g) {
+  const int groups = C >> 5;  // multiple of 4
+  const long long total = (long long)R * groups;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(idx / groups), g = (int)(idx - (long long)r * groups);
+    const uint4* src = reinterpret_cast<const uint4*>(x + (long long)r * ldx + g * 32);
     float v[32];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const uint4 t = ld_nc_v4(reinterpret_cast<const uint4*>(src + g * 32) + i);
+      const uint4 t = ld_nc_v4(src + i);
       const float2 a = bf2_to_f2(t.x), b = bf2_to_f2(t.y), c = bf2_to_f2(t.z), d = bf2_to_f2(t.w);
       v[i * 8 + 0] = a.x; v[i * 8 + 1] = a.y; v[i * 8 + 2] = b.x; v[i * 8 + 3] = b.y;
       v[i * 8 + 4] = c.x; v[i * 8 + 5] = c.y; v[i * 8 + 6] = d.x; v[i * 8 + 7] = d.y;
@@ -293,30 +292,44 @@ quantize_mx_rowwise_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, i
     for (int i = 0; i < 32; ++i) amax = fmaxf(amax, fabsf(v[i]));
     const uint32_t be = mx_biased_exp(amax);
     const float inv = mx_inv_scale(be);
-    sfw |= be << (8 * g);
     uint32_t w[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
       w[i] = (uint32_t)f_to_e4m3(v[4 * i] * inv) | ((uint32_t)f_to_e4m3(v[4 * i + 1] * inv) << 8) |
              ((uint32_t)f_to_e4m3(v[4 * i + 2] * inv) << 16) | ((uint32_t)f_to_e4m3(v[4 * i + 3] * inv) << 24);
-    reinterpret_cast<uint4*>(dst + g * 32)[0] = make_uint4(w[0], w[1], w[2], w[3]);
-    reinterpret_cast<uint4*>(dst + g * 32)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    uint4* dst = reinterpret_cast<uint4*>(q + (long long)r * ldq + g * 32);
+    dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    // the four groups of one 128-column block sit in four consecutive lanes (groups % 4 == 0, 256 % 4 == 0)
+    uint32_t sfw = be << (8 * (g & 3));
+    sfw |= __shfl_xor_sync(0xffffffffu, sfw, 1);
+    sfw |= __shfl_xor_sync(0xffffffffu, sfw, 2);
+    if ((g & 3) == 0) *reinterpret_cast<uint32_t*>(sf + sf_offset(r, g, groups >> 2)) = sfw;
   }
-  *reinterpret_cast<uint32_t*>(sf + sf_offset(r, (long long)j * 4, chunks)) = sfw;
 }
 
 // x [R, C] bf16 -> qt [C, R] e4m3 (row stride ldqt), scales along R (groups of 32 consecutive x-rows).
-// CTA tile: 128 x-rows x 64 x-columns through shared memory; thread = (column, 32-row group).
+// CTA tile: 128 x-rows x 64 x-columns staged in shared memory with 16-byte loads; thread = (column, 32-row group).
 __global__ void __launch_bounds__(256)
 quantize_mx_colwise_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, int R, int C, uint8_t* __restrict__ qt,
                            long long ldqt, uint8_t* __restrict__ sft) {
-  __shared__ __nv_bfloat16 tile[128][64 + 2];
+  __shared__ __align__(16) __nv_bfloat16 tile[128][64 + 8];
   const int r0 = blockIdx.y * 128, c0 = blockIdx.x * 64;
-  for (int i = threadIdx.x; i < 128 * 32; i += 256) {  // 2 bf16 per load
-    const int rr = i >> 5, cc = (i & 31) * 2;
-    uint32_t v = 0;
-    if (r0 + rr < R && c0 + cc < C) v = *reinterpret_cast<const uint32_t*>(x + (long long)(r0 + rr) * ldx + c0 + cc);
-    *reinterpret_cast<uint32_t*>(&tile[rr][cc]) = v;
+  const bool vec = (ldx % 8 == 0) && (c0 + 64 <= C);
+  if (vec) {
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int i = threadIdx.x + it * 256;  // 1024 16-byte pieces
+      const int rr = i >> 3, cc = (i & 7) * 8;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (r0 + rr < R) v = ld_nc_v4(reinterpret_cast<const uint4*>(x + (long long)(r0 + rr) * ldx + c0 + cc));
+      *reinterpret_cast<uint4*>(&tile[rr][cc]) = v;
+    }
+  } else {
+    for (int i = threadIdx.x; i < 128 * 64; i += 256) {
+      const int rr = i >> 6, cc = i & 63;
+      tile[rr][cc] = (r0 + rr < R && c0 + cc < C) ? x[(long long)(r0 + rr) * ldx + c0 + cc] : __float2bfloat16(0.f);
+    }
   }
   __syncthreads();
   const int c = threadIdx.x & 63, g = threadIdx.x >> 6;  // 4 groups of 32 rows
@@ -619,8 +632,11 @@ B200_API int b200_quantize_mx_rowwise(const void* x, long long ldx, int R, int C
   using namespace b200::mx;
   if (R <= 0 || C <= 0) return 0;
   if ((C % 128) || (ldx % 8) || (ldq % 16)) return B200_ERR_BAD_ARG;
-  const long long work = (long long)R * (C / 128);
-  quantize_mx_rowwise_kernel<<<(unsigned)((work + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+  const long long work = (long long)R * (C / 32);
+  long long blocks = (work + 255) / 256;
+  const long long cap = (long long)num_sms() * 32;
+  if (blocks > cap) blocks = cap;
+  quantize_mx_rowwise_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)x, ldx, R, C, (uint8_t*)q, ldq, (uint8_t*)sf);
   b200_count_launch();
   B200_CHECK_LAUNCH();

@@ -137,7 +137,9 @@ def quantize_mx(x: torch.Tensor, transpose: bool = False) -> MXTensor:
     if k % 128:
         raise ValueError(f"MXFP8 needs the reduction dimension ({k}) to be a multiple of 128")
     q = torch.empty((rows, k), dtype=FP8, device=x.device)
-    sf = torch.zeros(_sf_bytes(rows, k), dtype=torch.uint8, device=x.device)
+    # rows past the end of the tensor keep whatever the allocator left there: they only ever scale zero-filled data
+    # whose products are never stored
+    sf = torch.empty(_sf_bytes(rows, k), dtype=torch.uint8, device=x.device)
     fn = lib.b200_quantize_mx_colwise if transpose else lib.b200_quantize_mx_rowwise
     _lib.check(fn(_lib.ptr(x), x.stride(0), R, C, _lib.ptr(q), q.stride(0), _lib.ptr(sf), _lib.cur_stream()), "quantize_mx")
     return MXTensor(q, sf)
