@@ -60,6 +60,42 @@ int b200_gemm_bf16_scatter(const void* A, const void* B, void* const* peer_ptrs,
                            int rows, int N, int K, long long lda, long long ldb, int a_mn_major, int b_mn_major, void* stream);
 int b200_reduce_slots(const void* slots, void* out_bf16, int world, long long elems_per_slot, void* stream);
 
+/* SM-pair versions of the two fused tensor-parallel GEMMs (csrc/gemm2_tcgen05.cu); same contracts as above */
+int b200_gemm2_bf16_allgather_a(const void* const* peer_ptrs, int rank, int world, long long a_off, void* a_full, int rows,
+                                const void* B, void* C, int N, int K, long long ldb, long long ldc, int b_mn_major,
+                                unsigned* ready, unsigned long long epoch, void* stream);
+int b200_gemm2_bf16_scatter(const void* A, const void* B, void* const* peer_ptrs, int rank, int world, long long out_off,
+                            int rows, int N, int K, long long lda, long long ldb, int a_mn_major, int b_mn_major, void* stream);
+
+/* ---- K2: fp8 (e4m3) with one scale per tensor (csrc/fp8.cu, csrc/gemm2_tcgen05.cu)
+ * amax[0] = max(amax[0], max|x|); q = sat(x * 448/amax), qt = q^T when qt != NULL, deq[0] = amax/448;
+ * D = deq_a * deq_b * A_q B_q^T on tcgen05.mma.kind::f8f6f4 (both operands K-major byte matrices). */
+int b200_amax_bf16(const void* x, long long n, void* amax, void* stream);
+int b200_quantize_e4m3(const void* x, long long ldx, int R, int C, const void* amax, void* q, long long ldq, void* qt,
+                       long long ldqt, void* deq, void* stream);
+int b200_gemm2_e4m3(const void* A, const void* B, void* C, const void* bias, const void* deq_a, const void* deq_b, int M, int N,
+                    int K, long long lda, long long ldb, long long ldc, int out_fp32, int accumulate, void* stream);
+
+/* ---- K3: MXFP8 — e4m3 elements, one UE8M0 scale per 32 elements along K, applied inside the tensor core
+ * (tcgen05.mma.kind::mxf8f6f4.block_scale; csrc/gemm_mxfp8.cu).  Scale buffers: 512-byte blocks, one per (128 rows, 128 k):
+ * byte (r % 32) * 16 + ((r / 32) % 4) * 4 + g holds the scale of row r, k-group g.  K % 128 == 0.
+ * b200_gemm2_mxfp8 is the SM-pair kernel (256x256 tiles); its scale buffers must cover whole 256-row tiles. */
+long long b200_mx_sf_bytes(long long rows, long long k);
+int b200_quantize_mx_rowwise(const void* x, long long ldx, int R, int C, void* q, long long ldq, void* sf, void* stream);
+int b200_quantize_mx_colwise(const void* x, long long ldx, int R, int C, void* qt, long long ldqt, void* sft, void* stream);
+int b200_gemm_mxfp8(const void* A, const void* B, const void* sfa, const void* sfb, void* C, const void* bias, int M, int N, int K,
+                    long long lda, long long ldb, long long ldc, int out_fp32, int accumulate, void* stream);
+int b200_gemm2_mxfp8(const void* A, const void* B, const void* sfa, const void* sfb, void* C, const void* bias, int M, int N, int K,
+                     long long lda, long long ldb, long long ldc, int out_fp32, int accumulate, void* stream);
+
+/* ---- C6: Ulysses sequence <-> head exchange (csrc/comm.cu): the all-to-all with both layout changes folded into the copy.
+ * mode 0: peers hold [B*S_loc, src_pitch]; column block `rank` of every segment lands at row (b*S + p*S_loc + r) of out.
+ * mode 1: peers hold [B*S, src_pitch]; rows (b*S + rank*S_loc + r) land in column block p of every segment of out.
+ * segs: host array of nseg x {src_base, dst_base, bytes} (all multiples of 16). */
+int b200_seq_head_exchange(const void* const* peer_ptrs, int rank, int world, long long src_off, void* out, int mode, int B,
+                           int S_loc, long long src_pitch, long long dst_pitch, const long long* segs, int nseg, int ch_arrive,
+                           int ch_done, unsigned epoch, void* counter, int ctas, void* stream);
+
 /* ---- K4: flash attention, head_dim 128, GQA, causal or full (csrc/flash_attn.cu)
  * q/k/v/o are [B*S, heads*128] views (row strides in elements); lse/delta are fp32 [B, Hq, S]. */
 int b200_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, void* lse, int B, int S, int Hq, int Hkv, int D,
