@@ -321,7 +321,7 @@ def check_tp(dev, rank, world):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         log(f"tp {name}: {tt.item():.3f} ms")
     # whole model: TP Llama vs single-GPU replica
-    cfg = LlamaConfig.tiny(num_attention_heads=4, num_key_value_heads=2, hidden_size=512, intermediate_size=1024)
+    cfg = LlamaConfig.tiny(num_attention_heads=max(4, 2 * world), num_key_value_heads=max(2, world), hidden_size=512, intermediate_size=1024)
     torch.manual_seed(0)
     ref = LlamaForCausalLM(cfg, device=dev)
     torch.manual_seed(0)
