@@ -5,6 +5,7 @@
 // per-CTA operand traffic drops from 48 KB to 32 KB per k-block, which buys 6 pipeline stages instead of 4 and
 // halves the B reads from L2.  Same operand layouts and epilogue options as b200_gemm_bf16.
 #include "common.cuh"
+#include <string.h>
 
 namespace b200 {
 
@@ -55,6 +56,13 @@ struct Params {
   unsigned long long ag_expect;
   int ag_rows, ag_rank, ag_world;
 };
+
+// GEMM -> reduce-scatter epilogue: every epilogue warp stages 32 rows x 64 columns (4 KB, 128-byte swizzled) and sends
+// them to the owner's slot with ONE 2-D TMA store — LSU stores over NVLink are an order of magnitude slower.
+struct RsMaps {
+  CUtensorMap m[8];  // m[d]: rank d's [world * rows, N] bf16 slot buffer
+};
+static constexpr int RS_STAGING = 4 * 4096;
 
 static constexpr int AGG_CHUNK = 8192;
 static constexpr int AGG_STAGES = 3;
@@ -148,7 +156,8 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
 // kind::f8f6f4 with K = 32 per instruction, and the epilogue applies the two per-tensor dequantisation factors.
 template <int A_MN, int B_MN, int FP8 = 0, int FUSE_AG = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
-gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const Params p) {
+gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+             const __grid_constant__ RsMaps rs_maps, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* smem_a = smem;
@@ -160,7 +169,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   uint64_t* tmem_empty = bars + 2 * STAGES + 2; // [2]       leader's: 8 arrivals (4 epilogue warps x 2 CTAs)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
   uint64_t* ag_bars = bars + 2 * STAGES + 6;                        // [AGG_STAGES] (FUSE_AG)
-  uint8_t* ag_ring = smem + STAGES * STAGE_BYTES + 256;  // after the 256-byte barrier block
+  uint8_t* ag_ring = smem + STAGES * STAGE_BYTES + 256;   // after the 256-byte barrier block (FUSE_AG)
+  uint8_t* rs_stage = smem + STAGES * STAGE_BYTES + 1024;  // 4 x 4 KB, 1024-aligned (reduce-scatter epilogue)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();
@@ -347,6 +357,48 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + acc * BN;
       const bool row_ok = row < p.M;
       const bool vec_ok = (p.ldc % 8 == 0);
+      if (p.rs_world > 0 && (p.rs_rows % 32) == 0) {
+        // ---- reduce-scatter: TMEM -> swizzled smem tile -> one TMA store per 32 x 64 block into the owner's slot
+        const int row0 = row - lane;  // first of this warp's 32 rows: all owned by the same rank
+        const int owner = row0 / p.rs_rows;
+        const int dst_row = p.rs_rank * p.rs_rows + (row0 - owner * p.rs_rows);
+        uint8_t* stg = rs_stage + e * 4096;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 64) {
+          uint32_t v0[32], v1[32];
+          tmem_ld_32x32b_x32(taddr + c, v0);
+          tmem_ld_32x32b_x32(taddr + c + 32, v1);
+          tmem_ld_wait();
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // previous block left the staging tile
+          __syncwarp();
+          uint8_t* rp = stg + lane * 128;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 o;
+            o.x = f2_to_bf2(__uint_as_float(v0[8 * j]), __uint_as_float(v0[8 * j + 1]));
+            o.y = f2_to_bf2(__uint_as_float(v0[8 * j + 2]), __uint_as_float(v0[8 * j + 3]));
+            o.z = f2_to_bf2(__uint_as_float(v0[8 * j + 4]), __uint_as_float(v0[8 * j + 5]));
+            o.w = f2_to_bf2(__uint_as_float(v0[8 * j + 6]), __uint_as_float(v0[8 * j + 7]));
+            *reinterpret_cast<uint4*>(rp + ((j ^ (lane & 7)) << 4)) = o;
+            o.x = f2_to_bf2(__uint_as_float(v1[8 * j]), __uint_as_float(v1[8 * j + 1]));
+            o.y = f2_to_bf2(__uint_as_float(v1[8 * j + 2]), __uint_as_float(v1[8 * j + 3]));
+            o.z = f2_to_bf2(__uint_as_float(v1[8 * j + 4]), __uint_as_float(v1[8 * j + 5]));
+            o.w = f2_to_bf2(__uint_as_float(v1[8 * j + 6]), __uint_as_float(v1[8 * j + 7]));
+            *reinterpret_cast<uint4*>(rp + (((j + 4) ^ (lane & 7)) << 4)) = o;
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0 && row0 < p.M && n0 + c < p.N) {
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                             reinterpret_cast<uint64_t>(&rs_maps.m[owner])),
+                         "r"(smem_u32(stg)), "r"(n0 + c), "r"(dst_row)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        }
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // data is on its way before TMEM / smem are recycled
+        __syncwarp();
+      } else
 #pragma unroll 1
       for (int c = 0; c < BN; c += 32) {
         uint32_t v[32];
@@ -431,18 +483,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   }
 }
 
+static RsMaps g_no_rs_maps;  // zero-filled: launches without the reduce-scatter epilogue never touch it
+
 template <int A_MN, int B_MN, int FP8 = 0, int FUSE_AG = 0>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t st) {
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t st,
+                  const RsMaps& rs = g_no_rs_maps) {
   static bool attr_set = false;
-  constexpr int smem_bytes = SMEM + (FUSE_AG ? AGG_SMEM : 0);
+  constexpr int smem_max = SMEM + (FUSE_AG ? AGG_SMEM : RS_STAGING + 768);
+  // plain GEMMs stay at 198 KB so that a comm CTA (< 25 KB ring) still fits next to them on every SM
+  const int smem_bytes = SMEM + (FUSE_AG ? AGG_SMEM : (p.rs_world > 0 ? RS_STAGING + 768 : 0));
   if (!attr_set) {
-    B200_CUDA(cudaFuncSetAttribute(gemm2_kernel<A_MN, B_MN, FP8, FUSE_AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    B200_CUDA(cudaFuncSetAttribute(gemm2_kernel<A_MN, B_MN, FP8, FUSE_AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     attr_set = true;
   }
   int clusters = p.num_m_tiles * p.num_n_tiles;
   const int max_clusters = num_sms() / 2;
   if (clusters > max_clusters) clusters = max_clusters;
-  gemm2_kernel<A_MN, B_MN, FP8, FUSE_AG><<<clusters * 2, 256, smem_bytes, st>>>(ta, tb, p);
+  gemm2_kernel<A_MN, B_MN, FP8, FUSE_AG><<<clusters * 2, 256, smem_bytes, st>>>(ta, tb, rs, p);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;
@@ -555,9 +612,15 @@ B200_API int b200_gemm2_bf16_scatter(const void* A, const void* B, const void* c
   p.ag_world = 0;
   for (int i = 0; i < 8; ++i) p.rs_peer[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
   p.rs_off = out_off; p.rs_rows = rows; p.rs_rank = rank; p.rs_world = world;
+  RsMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  if (rows % 32 == 0) {
+    for (int d = 0; d < world; ++d)
+      if ((rc = make_tmap_bf16_2d(&maps.m[d], (const uint8_t*)peer_ptrs[d] + out_off, N, (long long)world * rows, N, 64, 32))) return rc;
+  }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (!a_mn_major && !b_mn_major) return launch<0, 0>(ta, tb, p, st);
-  if (!a_mn_major && b_mn_major) return launch<0, 1>(ta, tb, p, st);
-  if (a_mn_major && !b_mn_major) return launch<1, 0>(ta, tb, p, st);
-  return launch<1, 1>(ta, tb, p, st);
+  if (!a_mn_major && !b_mn_major) return launch<0, 0>(ta, tb, p, st, maps);
+  if (!a_mn_major && b_mn_major) return launch<0, 1>(ta, tb, p, st, maps);
+  if (a_mn_major && !b_mn_major) return launch<1, 0>(ta, tb, p, st, maps);
+  return launch<1, 1>(ta, tb, p, st, maps);
 }
