@@ -45,6 +45,11 @@ struct Params {
   uint8_t* rs_peer[8];
   long long rs_off;
   int rs_rows, rs_rank, rs_world;
+  // ---- GEMM -> Ulysses all-to-all (ux_world > 0, uses the same TMA-store epilogue): D = X W^T is the fused projection of
+  // this rank's S_loc tokens for ALL heads.  Column block `d` of every segment (q | k | v, or one segment) belongs to rank d,
+  // which keeps the whole sequence for its heads: rows land at (b * S + ux_rank * S_loc + s) of d's [B*S, part] buffer.
+  int ux_world, ux_rank, ux_S_loc, ux_nseg;
+  int ux_start[3], ux_width[3], ux_dst[3];  // per segment: first column, columns per rank, first destination column
   // ---- all-gather -> GEMM (FUSE_AG): A = [ag_world * ag_rows, K] is assembled in ag_full from the shards every rank
   // keeps at byte offset ag_off + rank * shard_bytes of its symmetric buffer.  Warp 3 of every CTA pulls the peers'
   // shards with cp.async.bulk while the tensor cores already work on rows that are present; ag_ready[p] counts the
@@ -357,11 +362,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       const uint32_t taddr = tmem_base + ((uint32_t)(e * 32) << 16) + acc * BN;
       const bool row_ok = row < p.M;
       const bool vec_ok = (p.ldc % 8 == 0);
-      if (p.rs_world > 0 && (p.rs_rows % 32) == 0) {
-        // ---- reduce-scatter: TMEM -> swizzled smem tile -> one TMA store per 32 x 64 block into the owner's slot
+      if ((p.rs_world > 0 && (p.rs_rows % 32) == 0) || p.ux_world > 0) {
+        // ---- reduce-scatter / Ulysses scatter: TMEM -> swizzled smem tile -> one TMA store per 32 x 64 block to its owner
         const int row0 = row - lane;  // first of this warp's 32 rows: all owned by the same rank
-        const int owner = row0 / p.rs_rows;
-        const int dst_row = p.rs_rank * p.rs_rows + (row0 - owner * p.rs_rows);
+        int owner = 0, dst_row = 0;
+        if (p.ux_world > 0) {
+          const int b = row0 / p.ux_S_loc;
+          dst_row = b * p.ux_S_loc * p.ux_world + p.ux_rank * p.ux_S_loc + (row0 - b * p.ux_S_loc);
+        } else {
+          owner = row0 / p.rs_rows;
+          dst_row = p.rs_rank * p.rs_rows + (row0 - owner * p.rs_rows);
+        }
         uint8_t* stg = rs_stage + e * 4096;
 #pragma unroll 1
         for (int c = 0; c < BN; c += 64) {
@@ -389,9 +400,17 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
           fence_proxy_async();
           __syncwarp();
           if (lane == 0 && row0 < p.M && n0 + c < p.N) {
+            int dst_col = n0 + c;
+            if (p.ux_world > 0) {  // 64-column blocks never straddle a segment or a rank (widths are multiples of 64)
+              int sgm = 0;
+              while (sgm + 1 < p.ux_nseg && dst_col >= p.ux_start[sgm + 1]) ++sgm;
+              const int rel = dst_col - p.ux_start[sgm];
+              owner = rel / p.ux_width[sgm];
+              dst_col = p.ux_dst[sgm] + (rel - owner * p.ux_width[sgm]);
+            }
             asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
                              reinterpret_cast<uint64_t>(&rs_maps.m[owner])),
-                         "r"(smem_u32(stg)), "r"(n0 + c), "r"(dst_row)
+                         "r"(smem_u32(stg)), "r"(dst_col), "r"(dst_row)
                          : "memory");
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
@@ -491,7 +510,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p,
   static bool attr_set = false;
   constexpr int smem_max = SMEM + (FUSE_AG ? AGG_SMEM : RS_STAGING + 768);
   // plain GEMMs stay at 198 KB so that a comm CTA (< 25 KB ring) still fits next to them on every SM
-  const int smem_bytes = SMEM + (FUSE_AG ? AGG_SMEM : (p.rs_world > 0 ? RS_STAGING + 768 : 0));
+  const int smem_bytes = SMEM + (FUSE_AG ? AGG_SMEM : ((p.rs_world > 0 || p.ux_world > 0) ? RS_STAGING + 768 : 0));
   if (!attr_set) {
     B200_CUDA(cudaFuncSetAttribute(gemm2_kernel<A_MN, B_MN, FP8, FUSE_AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     attr_set = true;
@@ -529,7 +548,7 @@ B200_API int b200_gemm2_bf16(const void* A, const void* B, void* C, const void* 
   p.num_m_tiles = (M + 255) / 256;
   p.num_n_tiles = (N + BN - 1) / BN;
   p.deq_a = p.deq_b = nullptr;
-  p.rs_world = 0; p.ag_world = 0;
+  p.rs_world = 0; p.ag_world = 0; p.ux_world = 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (!a_mn_major && !b_mn_major) return launch<0, 0>(ta, tb, p, st);
   if (!a_mn_major && b_mn_major) return launch<0, 1>(ta, tb, p, st);
@@ -559,7 +578,7 @@ B200_API int b200_gemm2_e4m3(const void* A, const void* B, void* C, const void* 
   p.num_n_tiles = (N + BN - 1) / BN;
   p.deq_a = (const float*)deq_a;
   p.deq_b = (const float*)deq_b;
-  p.rs_world = 0; p.ag_world = 0;
+  p.rs_world = 0; p.ag_world = 0; p.ux_world = 0;
   return launch<0, 0, 1>(ta, tb, p, reinterpret_cast<cudaStream_t>(stream));
 }
 
@@ -581,7 +600,7 @@ B200_API int b200_gemm2_bf16_allgather_a(const void* const* peer_ptrs, int rank,
   p.C = C; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = 0; p.accumulate = 0;
   p.num_m_tiles = (M + 255) / 256; p.num_n_tiles = (N + BN - 1) / BN;
   p.deq_a = p.deq_b = nullptr;
-  p.rs_world = 0;
+  p.rs_world = 0; p.ux_world = 0;
   for (int i = 0; i < 8; ++i) p.ag_peer[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
   p.ag_off = a_off; p.ag_full = (uint8_t*)a_full; p.ag_ready = (unsigned long long*)ready;
   p.ag_expect = epoch * (unsigned long long)rows * K * 2; p.ag_rows = rows; p.ag_rank = rank; p.ag_world = world;
@@ -609,7 +628,7 @@ B200_API int b200_gemm2_bf16_scatter(const void* A, const void* B, const void* c
   p.C = nullptr; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = N; p.out_fp32 = 0; p.accumulate = 0;
   p.num_m_tiles = (M + 255) / 256; p.num_n_tiles = (N + BN - 1) / BN;
   p.deq_a = p.deq_b = nullptr;
-  p.ag_world = 0;
+  p.ag_world = 0; p.ux_world = 0;
   for (int i = 0; i < 8; ++i) p.rs_peer[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
   p.rs_off = out_off; p.rs_rows = rows; p.rs_rank = rank; p.rs_world = world;
   RsMaps maps;
@@ -623,4 +642,48 @@ B200_API int b200_gemm2_bf16_scatter(const void* A, const void* B, const void* c
   if (!a_mn_major && b_mn_major) return launch<0, 1>(ta, tb, p, st, maps);
   if (a_mn_major && !b_mn_major) return launch<1, 0>(ta, tb, p, st, maps);
   return launch<1, 1>(ta, tb, p, st, maps);
+}
+
+// GEMM -> Ulysses sequence->head all-to-all in one kernel: D = A W^T for this rank's B*S_loc tokens; the epilogue sends every
+// 32 x 64 block straight to the rank that owns those heads (2-D TMA store over NVLink).  widths[i] = full width (columns of D)
+// of segment i (q | k | v for the fused QKV projection, a single segment for a plain matrix), each a multiple of 64 * world.
+// Rank d's destination buffer is [B * S_loc * world, sum(widths) / world] bf16 at byte offset out_off of its workspace.
+// The caller runs a device barrier afterwards (all ranks' blocks have landed) before reading its buffer.
+B200_API int b200_gemm2_bf16_ulysses_scatter(const void* A, const void* W, const void* const* peer_ptrs, int rank, int world,
+                                             long long out_off, int B, int S_loc, const int* widths, int nseg, int K, long long lda,
+                                             long long ldb, int b_mn_major, void* stream) {
+  using namespace b200;
+  using namespace b200::g2;
+  if (world < 1 || world > 8 || nseg < 1 || nseg > 3 || (S_loc % 32) || (lda % 8) || (ldb % 8)) return B200_ERR_BAD_ARG;
+  const int M = B * S_loc;
+  int N = 0;
+  for (int i = 0; i < nseg; ++i) {
+    if (widths[i] <= 0 || widths[i] % (64 * world)) return B200_ERR_BAD_ARG;
+    N += widths[i];
+  }
+  const int part = N / world;
+  CUtensorMap ta, tb;
+  int rc;
+  if ((rc = make_tmap_bf16_2d(&ta, A, K, M, lda, BK, BM))) return rc;
+  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, W, K, N, ldb, BK, BNH);
+  else rc = make_tmap_bf16_2d(&tb, W, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  Params p;
+  p.C = nullptr; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = N; p.out_fp32 = 0; p.accumulate = 0;
+  p.num_m_tiles = (M + 255) / 256; p.num_n_tiles = (N + BN - 1) / BN;
+  p.deq_a = p.deq_b = nullptr;
+  p.ag_world = 0; p.rs_world = 0;
+  p.ux_world = world; p.ux_rank = rank; p.ux_S_loc = S_loc; p.ux_nseg = nseg;
+  int start = 0, dst = 0;
+  for (int i = 0; i < 3; ++i) {
+    p.ux_start[i] = start; p.ux_width[i] = i < nseg ? widths[i] / world : 1; p.ux_dst[i] = dst;
+    if (i < nseg) { start += widths[i]; dst += widths[i] / world; }
+  }
+  RsMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  for (int d = 0; d < world; ++d)
+    if ((rc = make_tmap_bf16_2d(&maps.m[d], (const uint8_t*)peer_ptrs[d] + out_off, part, (long long)M * world, part, 64, 32))) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!b_mn_major) return launch<0, 0>(ta, tb, p, st, maps);
+  return launch<0, 1>(ta, tb, p, st, maps);
 }

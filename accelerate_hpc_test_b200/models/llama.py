@@ -130,11 +130,18 @@ class LlamaAttention(nn.Module):
 
     def forward(self, x, rope, B, S):
         c = self.cfg
-        qkv = self.qkv_proj(x)
-        cos, sin, pos = rope
+        cos, sin, pos = rope[:3]
         hq, hkv = getattr(self, "tp_heads", (c.num_attention_heads, c.num_key_value_heads))  # local heads under TP
         sp = getattr(self, "sp_comm", None)
         cp = getattr(self, "cp_comm", None)
+        if sp is not None and sp.world > 1 and len(rope) > 3 and self.qkv_proj.bias is None and self.o_proj.bias is None \
+                and not getattr(self.qkv_proj, "_b200_fp8", False):
+            from ..parallel.ulysses import ulysses_attention_block
+
+            # projections and all-to-alls are fused: QKV GEMM -> head-sharded buffers, attention, heads -> output GEMM
+            return ulysses_attention_block(x, self.qkv_proj.weight, self.o_proj.weight, cos, sin, rope[3], B, S, hq, hkv,
+                                           c.head_dim, sp, causal=True)
+        qkv = self.qkv_proj(x)
         if sp is not None and sp.world > 1:
             from ..parallel.ulysses import ulysses_attention
 
@@ -211,6 +218,8 @@ class LlamaModel(nn.Module):
         else:
             max_pos = self.cfg.max_position_embeddings
         rope = self.rope(position_ids, max_pos)
+        if sp is not None and sp.world > 1:
+            rope = rope + (sp.gather_positions(rope[2], B, S),)  # positions of the whole sequence, head-sharded row order
         x = F.embedding(input_ids, self.embed_tokens.weight).view(B * S, -1)
         tp = getattr(self, "tp_comm", None)
         if tp is not None and tp.world > 1:

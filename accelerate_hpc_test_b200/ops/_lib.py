@@ -39,6 +39,7 @@ _SIGNATURES = {
     "b200_quantize_e4m3": [P, L, I, I, P, P, L, P, L, P, P],
     "b200_gemm2_bf16": [P, P, P, P, I, I, I, L, L, L, I, I, I, I, P],
     "b200_gemm2_bf16_allgather_a": [P, I, I, L, P, I, P, P, I, I, L, L, I, P, ctypes.c_ulonglong, P],
+    "b200_gemm2_bf16_ulysses_scatter": [P, P, P, I, I, L, I, I, P, I, I, L, L, I, P],
     "b200_gemm2_bf16_scatter": [P, P, P, I, I, L, I, I, I, L, L, I, I, P],
     "b200_gemm_bf16_allgather_a": [P, I, I, L, P, I, P, P, I, I, L, L, I, P, ctypes.c_ulonglong, P],
     "b200_gemm_bf16_scatter": [P, P, P, I, I, L, I, I, I, L, L, I, I, P],

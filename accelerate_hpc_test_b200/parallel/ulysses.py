@@ -6,7 +6,11 @@ The reference reaches this through DeepSpeed (reference src/accelerate/accelerat
 ``UlyssesSPAttentionHF.register_with_transformers`` + ``UlyssesSPDataLoaderAdapter``; config
 utils/dataclasses.py:2214 ``DeepSpeedSequenceParallelConfig``).  Here it is part of the engine:
 
-* on B200 the two layout changes around the all-to-all are folded into the copy itself —
+* the QKV projection and the all-to-all are ONE kernel: the GEMM epilogue TMA-stores every output block straight into the
+  head-sharded buffer of the rank that owns those heads (``SPComm.gemm_scatter``); the same kernel serves the backward of the
+  output projection (dgrad GEMM -> all-to-all).  Its two destination buffers alternate, and every call ends with one device
+  barrier, which also proves that all ranks are done reading the buffer the next call will overwrite;
+* in the other direction (head- to sequence-sharded) the two layout changes are folded into the copy itself —
   ``b200_seq_head_exchange`` (csrc/comm.cu) pulls the needed column segments row by row from every
   peer's symmetric buffer with TMA bulk copies over NVLink, so there is no pack / unpack pass;
 * on CPU (gloo) the same exchange is ``all_to_all_single`` plus the two permutes (the oracle path);
@@ -18,6 +22,7 @@ from __future__ import annotations
 
 import ctypes
 import math
+import os
 from typing import Optional
 
 import torch
@@ -108,6 +113,54 @@ class SPComm:
         )
         return out
 
+    # ------------------------------------------------------------------ GEMM fused with the sequence->head exchange
+    def gemm_scatter(self, x2: torch.Tensor, w: torch.Tensor, B: int, S_loc: int, widths, b_mn_major: bool = False) -> torch.Tensor:
+        """``exchange(x2 @ W^T, mode 0)`` in one kernel: the GEMM epilogue TMA-stores every 32 x 64 block straight into the
+        buffer of the rank that owns those heads (csrc/gemm2_tcgen05.cu, ``b200_gemm2_bf16_ulysses_scatter``)."""
+        w_ = self.world
+        full = sum(widths)
+        part = full // w_
+        fused = (self._native(x2) and x2.dtype == torch.bfloat16 and S_loc % 32 == 0 and all(wd % (64 * w_) == 0 for wd in widths)
+                 and os.environ.get("ACCELERATE_B200_ULYSSES_FUSED", "1") != "0")
+        if not fused:
+            y = F.gemm(x2, w, b_mn_major=b_mn_major)
+            return self.exchange(y, 0, B, S_loc, widths)
+        rows = B * S_loc * w_
+        nbytes = rows * part * 2
+        self._ensure_dst(nbytes)
+        off = self._dst_off[self._dst_flip]
+        self._dst_flip ^= 1
+        x2 = F._rowmajor2d(x2)
+        arr = (ctypes.c_int * len(widths))(*widths)
+        _lib.check(
+            self.ws_dst.lib.b200_gemm2_bf16_ulysses_scatter(_lib.ptr(x2), _lib.ptr(w), self.ws_dst.peer_array, self.rank, w_, off, B, S_loc, arr,
+                                                            len(widths), x2.shape[1], x2.stride(0), w.stride(0), int(b_mn_major),
+                                                            _lib.cur_stream()),
+            "gemm_ulysses_scatter",
+        )
+        # one barrier per call: everybody's blocks have landed here; the two destination buffers alternate, so a rank
+        # that passed this barrier has also finished reading the buffer the NEXT call writes (see module docstring)
+        self.ws_dst.barrier(self._dst_ch)
+        return self.ws_dst.tensor(off, (rows, part), torch.bfloat16).clone()
+
+    def _ensure_dst(self, nbytes: int):
+        if getattr(self, "ws_dst", None) is not None and nbytes <= self._dst_bytes:
+            return
+        if getattr(self, "ws_dst", None) is not None:
+            self.ws_dst.close()
+        cap = int(nbytes * 1.1) + 4096
+        self.ws_dst = self._ws_cls(self.group, 2 * cap + (1 << 20), self.device)
+        self._dst_off = [self.ws_dst.alloc(cap, align=1024), self.ws_dst.alloc(cap, align=1024)]
+        self._dst_bytes = cap
+        self._dst_flip = 0
+        self._dst_ch = self.ws_dst.new_channel()
+
+    def gather_positions(self, pos: torch.Tensor, B: int, S_loc: int) -> torch.Tensor:
+        """Positions of the whole sequence in head-sharded row order ``(b, rank, s)`` from every rank's local ones."""
+        parts = [torch.empty_like(pos) for _ in range(self.world)]
+        dist.all_gather(parts, pos.contiguous(), group=self.group)
+        return torch.stack([p_.view(B, S_loc) for p_ in parts], dim=1).reshape(-1).contiguous()
+
     def _exchange_reference(self, x, mode, B, S_loc, widths):
         w = self.world
         outs = []
@@ -191,6 +244,71 @@ class _UlyssesAttentionFn(torch.autograd.Function):
         dqkv = comm.exchange(dqkv_h, 1, B, S_loc, (Hq * D, Hkv * D, Hkv * D))
         F.rope_inplace(dqkv, cos, sin, pos, Hq + Hkv, D, backward=True)
         return (dqkv.view(ctx.in_shape),) + (None,) * 11
+
+
+class _UlyssesQKVFn(torch.autograd.Function):
+    """QKV projection of the local tokens, delivered head-sharded: ``[B*S, (Hq+2Hkv)*D / sp]`` for the whole sequence.
+    Forward is one kernel (GEMM + all-to-all); backward brings dQKV back (exchange kernel) and runs dgrad / wgrad."""
+
+    @staticmethod
+    def forward(ctx, x, weight, comm: SPComm, B, S_loc, widths):
+        x2 = x.reshape(B * S_loc, x.shape[-1])
+        out = comm.gemm_scatter(x2, weight, B, S_loc, widths)
+        ctx.save_for_backward(x2, weight)
+        ctx.comm, ctx.cfg, ctx.in_shape = comm, (B, S_loc, widths), x.shape
+        return out
+
+    @staticmethod
+    def backward(ctx, dqkv_h):
+        x2, weight = ctx.saved_tensors
+        B, S_loc, widths = ctx.cfg
+        dy = ctx.comm.exchange(dqkv_h.contiguous(), 1, B, S_loc, widths)  # [B*S_loc, N]
+        if dy.dtype != weight.dtype:
+            dy = dy.to(weight.dtype)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = F.gemm(dy, weight, b_mn_major=True).view(ctx.in_shape)
+        if ctx.needs_input_grad[1]:
+            dw = F.deliver_weight_grad(weight, lambda out, acc: F.gemm(dy, x2, a_mn_major=True, b_mn_major=True, out=out, accumulate=acc))
+        return dx, dw, None, None, None, None
+
+
+class _UlyssesOutProjFn(torch.autograd.Function):
+    """Attention output projection fed by head-sharded attention output: forward brings the local tokens' heads together
+    (exchange kernel) and multiplies; backward is one kernel again — dgrad GEMM whose epilogue scatters d(attn out) back to the
+    ranks that own the heads."""
+
+    @staticmethod
+    def forward(ctx, o_h, weight, comm: SPComm, B, S_loc):
+        width = weight.shape[1]
+        o = comm.exchange(o_h.contiguous(), 1, B, S_loc, (width,))  # [B*S_loc, Hq*D]
+        y = F.gemm(o, weight)
+        ctx.save_for_backward(o, weight)
+        ctx.comm, ctx.cfg = comm, (B, S_loc, width)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        o, weight = ctx.saved_tensors
+        B, S_loc, width = ctx.cfg
+        dy2 = dy.reshape(B * S_loc, dy.shape[-1])
+        if dy2.dtype != weight.dtype:
+            dy2 = dy2.to(weight.dtype)
+        do_h = dw = None
+        if ctx.needs_input_grad[0]:
+            do_h = ctx.comm.gemm_scatter(dy2, weight, B, S_loc, (width,), b_mn_major=True)  # dO = dY W, scattered by heads
+        if ctx.needs_input_grad[1]:
+            dw = F.deliver_weight_grad(weight, lambda out, acc: F.gemm(dy2, o, a_mn_major=True, b_mn_major=True, out=out, accumulate=acc))
+        return do_h, dw, None, None, None
+
+
+def ulysses_attention_block(x, qkv_weight, o_weight, cos, sin, pos_full, B, S_loc, Hq, Hkv, D, comm: SPComm, causal=True):
+    """The whole attention block under Ulysses: fused QKV-projection + all-to-all, flash attention over the full sequence for
+    this rank's heads (RoPE with global positions), all-to-all + output projection."""
+    w = comm.world
+    qkv_h = _UlyssesQKVFn.apply(x, qkv_weight, comm, B, S_loc, (Hq * D, Hkv * D, Hkv * D))
+    o_h = F.rope_attention(qkv_h, cos, sin, pos_full, B, S_loc * w, Hq // w, Hkv // w, D, causal=causal)
+    return _UlyssesOutProjFn.apply(o_h, o_weight, comm, B, S_loc)
 
 
 def ulysses_attention(qkv, cos, sin, pos, B, S_loc, Hq, Hkv, D, comm: SPComm, causal=True, scale=None):
