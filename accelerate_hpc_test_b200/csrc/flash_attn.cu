@@ -39,16 +39,11 @@ __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_
 
 // write 64 bf16 values (one 128 B row) of a K-major SWIZZLE_128B tile: 16 B chunk c lands at c ^ (row & 7)
 __device__ __forceinline__ void store_row_sw128(uint8_t* tile, int row, const float (&f)[64]) {
-  uint8_t* rp = tile + row * 128;
+  const uint32_t rp = smem_u32(tile) + row * 128;
 #pragma unroll
-  for (int c = 0; c < 8; ++c) {
-    uint4 o;
-    o.x = f2_to_bf2(f[c * 8 + 0], f[c * 8 + 1]);
-    o.y = f2_to_bf2(f[c * 8 + 2], f[c * 8 + 3]);
-    o.z = f2_to_bf2(f[c * 8 + 4], f[c * 8 + 5]);
-    o.w = f2_to_bf2(f[c * 8 + 6], f[c * 8 + 7]);
-    *reinterpret_cast<uint4*>(rp + ((c ^ (row & 7)) << 4)) = o;
-  }
+  for (int c = 0; c < 8; ++c)
+    sts_v4(rp + ((c ^ (row & 7)) << 4), f2_to_bf2(f[c * 8 + 0], f[c * 8 + 1]), f2_to_bf2(f[c * 8 + 2], f[c * 8 + 3]),
+           f2_to_bf2(f[c * 8 + 4], f[c * 8 + 5]), f2_to_bf2(f[c * 8 + 6], f[c * 8 + 7]));
 }
 
 struct FaFwdParams {
@@ -200,6 +195,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     const int q_idx = q0 + r;
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     float m_used = -INFINITY, l = 0.f;  // running max (in scaled log2 units) and row sum
+    const float sl2 = p.scale_log2;
     for (int j = 0; j < nblk; ++j) {
       const int kv0 = j * FWD_BN;
       const int st = j & 1;
@@ -231,7 +227,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         mx0 = fmaxf(mx0, fmaxf(s[i], s[i + 1]));
         mx1 = fmaxf(mx1, fmaxf(s[i + 2], s[i + 3]));
       }
-      const float m_new = fmaxf(m_used, fmaxf(mx0, mx1) * p.scale_log2);  // scale > 0: max commutes with it
+      const float m_new = fmaxf(m_used, fmaxf(mx0, mx1) * sl2);  // scale > 0: max commutes with it
       float alpha = 1.f;
       const bool need = (m_new - m_used) > 8.f;  // also true for the first finite max (m_used = -inf)
       if (need) {
@@ -243,8 +239,8 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
       for (int i = 0; i < 64; i += 2) {
-        s[i] = exp2f(fmaf(s[i], p.scale_log2, neg_m));
-        s[i + 1] = exp2f(fmaf(s[i + 1], p.scale_log2, neg_m));
+        s[i] = ex2_approx(fmaf(s[i], sl2, neg_m));
+        s[i + 1] = ex2_approx(fmaf(s[i + 1], sl2, neg_m));
         rs0 += s[i];
         rs1 += s[i + 1];
       }
@@ -539,38 +535,71 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
       return (qi < p.S) ? p.delta[idx] : 0.f;
     };
     float stat = fetch_stat(0);
+    const float sl2 = p.scale_log2;
     for (int it = 0; it < n_iter; ++it) {
       const int st = it & 1;
       const uint32_t ph = (it >> 1) & 1;
       const int q0 = (i_begin + it % per_head) * BWD_BM;
-      if (tid < 64) sLse[st * BWD_BM + tid] = stat;
-      else if (tid < 128) sDelta[st * BWD_BM + (tid - 64)] = stat;
+      if (tid < 64) sts_f32(smem_u32(sLse + st * BWD_BM + tid), stat);
+      else if (tid < 128) sts_f32(smem_u32(sDelta + st * BWD_BM + (tid - 64)), stat);
       stat = fetch_stat(it + 1);
       asm volatile("bar.sync 1, 256;" ::: "memory");
       mbar_wait(&s_full[st], ph);
       tc_fence_after();
       const uint32_t tSt = tmem_base + 256 + st * 128 + half * 32, tdPt = tSt + 64;
-      const float* lse_s = sLse + st * BWD_BM + half * 32;
-      const float* del_s = sDelta + st * BWD_BM + half * 32;
+      const uint32_t lse_a = smem_u32(sLse + st * BWD_BM + half * 32), del_a = smem_u32(sDelta + st * BWD_BM + half * 32);
       const int qc = q0 + half * 32;
-      float pr[32], ds[32];
+      uint32_t pp[16], dd[16];  // P^T and dS^T of this thread's 32 q columns, packed bf16 pairs
       {
         uint32_t v[32], w[32];
         tmem_ld_32x32b_x32(tSt + lane_addr, v);
         tmem_ld_32x32b_x32(tdPt + lane_addr, w);
         tmem_ld_wait();
-        const bool diag = p.causal && (q0 < kv0 + BWD_BN);  // some (q, kv) pairs of this tile are masked
+        // only tiles on the causal diagonal / past the end of the sequence need the per-element mask
+        const bool masked = (p.causal && (q0 < kv0 + BWD_BN)) || (kv0 + BWD_BN > p.S);
+        if (!masked) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float a = exp2f(__uint_as_float(v[i]) * p.scale_log2 - lse_s[i]);
-          if (!kv_ok || (diag && (qc + i < kv_idx))) a = 0.f;
-          pr[i] = a;
-          ds[i] = a * (__uint_as_float(w[i]) - del_s[i]);
+          for (int i = 0; i < 32; i += 4) {
+            const float4 l4 = lds_f4(lse_a + i * 4), d4 = lds_f4(del_a + i * 4);
+            const float a0 = ex2_approx(fmaf(__uint_as_float(v[i]), sl2, -l4.x));
+            const float a1 = ex2_approx(fmaf(__uint_as_float(v[i + 1]), sl2, -l4.y));
+            const float a2 = ex2_approx(fmaf(__uint_as_float(v[i + 2]), sl2, -l4.z));
+            const float a3 = ex2_approx(fmaf(__uint_as_float(v[i + 3]), sl2, -l4.w));
+            pp[i >> 1] = f2_to_bf2(a0, a1);
+            pp[(i >> 1) + 1] = f2_to_bf2(a2, a3);
+            dd[i >> 1] = f2_to_bf2(a0 * (__uint_as_float(w[i]) - d4.x), a1 * (__uint_as_float(w[i + 1]) - d4.y));
+            dd[(i >> 1) + 1] = f2_to_bf2(a2 * (__uint_as_float(w[i + 2]) - d4.z), a3 * (__uint_as_float(w[i + 3]) - d4.w));
+          }
+        } else {
+          const bool diag = p.causal && (q0 < kv0 + BWD_BN);
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            const float4 l4 = lds_f4(lse_a + i * 4), d4 = lds_f4(del_a + i * 4);
+            const float lv[4] = {l4.x, l4.y, l4.z, l4.w}, dv4[4] = {d4.x, d4.y, d4.z, d4.w};
+            float a[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              a[j] = ex2_approx(fmaf(__uint_as_float(v[i + j]), sl2, -lv[j]));
+              if (!kv_ok || (diag && (qc + i + j < kv_idx))) a[j] = 0.f;
+            }
+            pp[i >> 1] = f2_to_bf2(a[0], a[1]);
+            pp[(i >> 1) + 1] = f2_to_bf2(a[2], a[3]);
+            dd[i >> 1] = f2_to_bf2(a[0] * (__uint_as_float(w[i]) - dv4[0]), a[1] * (__uint_as_float(w[i + 1]) - dv4[1]));
+            dd[(i >> 1) + 1] = f2_to_bf2(a[2] * (__uint_as_float(w[i + 2]) - dv4[2]), a[3] * (__uint_as_float(w[i + 3]) - dv4[3]));
+          }
         }
       }
       mbar_wait(pds_free, (it & 1) ^ 1);  // B(it-1) no longer reads the P^T / dS^T buffer
-      store_half_row_sw128(sPt, r, half, pr);
-      store_half_row_sw128(sdSt, r, half, ds);
+      {
+        // half a 128-byte row of the K-major SWIZZLE_128B tiles: 16-byte chunks 4*half .. 4*half+3, chunk c at c ^ (r & 7)
+        const uint32_t prow = smem_u32(sPt) + r * 128, drow = smem_u32(sdSt) + r * 128;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const uint32_t o = (uint32_t)((((half << 2) + c) ^ (r & 7)) << 4);
+          sts_v4(prow + o, pp[4 * c], pp[4 * c + 1], pp[4 * c + 2], pp[4 * c + 3]);
+          sts_v4(drow + o, dd[4 * c], dd[4 * c + 1], dd[4 * c + 2], dd[4 * c + 3]);
+        }
+      }
       fence_proxy_async();
       tc_fence_before();
       mbar_arrive(&pds_ready[st]);
