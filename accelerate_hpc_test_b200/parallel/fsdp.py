@@ -183,6 +183,7 @@ class B200ShardedModule(nn.Module):
             for p in u.params:
                 self._unit_of_param[id(p)] = u
                 p._b200_fsdp_unit = u
+                u.engine = self
         self._ignored_params = [p for p in self.module.parameters() if id(p) in ignored]
 
     def _allocate(self):

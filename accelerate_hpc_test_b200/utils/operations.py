@@ -409,9 +409,9 @@ def GatheredParameters(params, modifier_rank=None, fwd_module=None, enabled=True
             if unit is not None and unit not in units:
                 units.append(unit)
     for u in units:
-        u.unshard()
+        u.engine.unshard(u)
     try:
         yield
     finally:
         for u in units:
-            u.reshard(write_back=modifier_rank is not None)
+            u.engine.reshard(u, write_back=modifier_rank is not None)

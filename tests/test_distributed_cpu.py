@@ -109,3 +109,32 @@ def _fsdp_checkpoint(tmpdir):
 
 def test_sharded_checkpoint_resume_two_processes(tmp_path):
     debug_launcher(_fsdp_checkpoint, args=(str(tmp_path),), num_processes=2)
+
+
+def _gathered_parameters():
+    from accelerate_hpc_test_b200 import Accelerator
+    from accelerate_hpc_test_b200.models import LlamaConfig, LlamaForCausalLM
+    from accelerate_hpc_test_b200.utils import FullyShardedDataParallelPlugin
+    from accelerate_hpc_test_b200.utils.operations import GatheredParameters
+
+    cfg = LlamaConfig.tiny(head_dim=32, hidden_size=64, intermediate_size=128, vocab_size=128, num_hidden_layers=2)
+    torch.manual_seed(0)
+    model = LlamaForCausalLM(cfg, dtype=torch.float32)
+    ref = {n: p.detach().clone() for n, p in model.named_parameters()}
+    plugin = FullyShardedDataParallelPlugin(fsdp_version=2, auto_wrap_policy="transformer_based_wrap",
+                                            transformer_cls_names_to_wrap=["LlamaDecoderLayer"])
+    acc = Accelerator(fsdp_plugin=plugin)
+    model = acc.prepare(model)
+    inner = acc.unwrap_model(model)
+    w = inner.model.layers[1].mlp.down_proj.weight
+    assert w.numel() == 0  # sharded away between uses
+    with GatheredParameters([w], modifier_rank=0):
+        assert torch.equal(w, ref["model.layers.1.mlp.down_proj.weight"])
+        w.data.mul_(2.0)  # every rank applies the same modification; it is written back to the shards
+    assert w.numel() == 0
+    with GatheredParameters([w]):
+        assert torch.allclose(w, 2.0 * ref["model.layers.1.mlp.down_proj.weight"])
+
+
+def test_gathered_parameters_two_processes():
+    debug_launcher(_gathered_parameters, num_processes=2)
