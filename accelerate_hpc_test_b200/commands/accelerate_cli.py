@@ -7,6 +7,7 @@ from .launch import launch_command_parser
 from .merge import merge_command_parser
 from .test import test_command_parser
 from .to_fsdp2 import to_fsdp2_command_parser
+from .tpu import tpu_command_parser
 from .utils import CustomArgumentParser
 
 
@@ -20,6 +21,7 @@ def main():
     merge_command_parser(subparsers=subparsers)
     test_command_parser(subparsers=subparsers)
     to_fsdp2_command_parser(subparsers=subparsers)
+    tpu_command_parser(subparsers=subparsers)
     args = parser.parse_args()
     if not hasattr(args, "func"):
         parser.print_help()

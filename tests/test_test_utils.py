@@ -1,0 +1,65 @@
+"""test_utils helpers (reference src/accelerate/test_utils/testing.py, examples.py; tests/test_examples.py)."""
+
+import os
+import textwrap
+import unittest
+
+import pytest
+
+from accelerate_hpc_test_b200.test_utils.examples import compare_against_test
+from accelerate_hpc_test_b200.test_utils.testing import (AccelerateTestCase, assert_exception, capture_call_output, get_launch_command,
+                                                         parse_flag_from_env, path_in_accelerate_package, require_cuda, require_xpu,
+                                                         run_command)
+
+
+def test_launch_command_and_flags(monkeypatch):
+    cmd = get_launch_command(num_processes=2, multi_gpu=True, mixed_precision=None, debug=False)
+    assert cmd[-2:] == ["--num_processes=2", "--multi_gpu"]
+    monkeypatch.setenv("X_FLAG", "yes")
+    assert parse_flag_from_env("X_FLAG") is True and parse_flag_from_env("NOPE", default=False) is False
+    assert path_in_accelerate_package("test_utils", "scripts", "test_script.py").exists()
+    assert capture_call_output(print, "hi").strip() == "hi"
+    assert "ok" in run_command(["python", "-c", "print('ok')"], return_stdout=True)
+    with assert_exception(ValueError, "boom"):
+        raise ValueError("boom!")
+
+
+def test_skip_decorators():
+    @require_xpu
+    class T(unittest.TestCase):
+        def test_x(self):
+            raise AssertionError("must be skipped")
+
+    res = unittest.TestResult()
+    unittest.defaultTestLoader.loadTestsFromTestCase(T).run(res)
+    assert len(res.skipped) == 1 and not res.failures
+    assert callable(require_cuda) and issubclass(AccelerateTestCase, unittest.TestCase)
+
+
+def test_compare_against_test(tmp_path, monkeypatch):
+    ex = tmp_path / "examples"
+    ex.mkdir()
+    template = textwrap.dedent('''
+        def training_function(config, args):
+            accelerator = Accelerator()
+            model = get_model()
+            for batch in loader:
+                loss = model(batch)
+        def main():
+            parser = argparse.ArgumentParser()
+            args = parser.parse_args()
+        if __name__ == "__main__":
+            main()
+    ''')
+    feature = template.replace("    accelerator = Accelerator()\n", "    accelerator = Accelerator(log_with='all')\n    accelerator.init_trackers('x')\n")
+    complete_ok = feature.replace("    model = get_model()\n", "    model = get_model()\n    extra_thing()\n")
+    complete_missing = template
+    (ex / "nlp_example.py").write_text(template)
+    (tmp_path / "feature.py").write_text(feature)
+    (tmp_path / "ok.py").write_text(complete_ok)
+    (tmp_path / "missing.py").write_text(complete_missing)
+    monkeypatch.chdir(tmp_path)
+    assert compare_against_test(str(tmp_path / "ok.py"), str(tmp_path / "feature.py"), parser_only=False) == []
+    diff = compare_against_test(str(tmp_path / "missing.py"), str(tmp_path / "feature.py"), parser_only=False)
+    assert any("init_trackers" in ln for ln in diff) and len(diff) == 2
+    assert compare_against_test(str(tmp_path / "ok.py"), str(tmp_path / "feature.py"), parser_only=True) == []
