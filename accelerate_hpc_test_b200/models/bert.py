@@ -164,7 +164,7 @@ def synthetic_mrpc(n: int, vocab_size: int = 28996, max_len: int = 128, seed: in
     for _ in range(n):
         la = int(torch.randint(8, max_len // 2 - 2, (1,), generator=g))
         lb = int(torch.randint(8, max_len // 2 - 2, (1,), generator=g))
-        ids = torch.randint(1000, vocab_size, (la + lb + 3,), generator=g)
+        ids = torch.randint(min(1000, vocab_size // 4), vocab_size, (la + lb + 3,), generator=g)
         ids[0], ids[la + 1], ids[-1] = 101, 102, 102
         tt = torch.cat([torch.zeros(la + 2, dtype=torch.long), torch.ones(lb + 1, dtype=torch.long)])
         label = int(torch.randint(0, 2, (1,), generator=g))
