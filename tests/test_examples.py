@@ -1,0 +1,116 @@
+"""The example scripts run, and the "complete" example contains what the by-feature examples add
+(reference tests/test_examples.py: ExampleDifferenceTests :70-155, FeatureExamplesTests :157-330).
+BASELINE config 1: BERT sequence classification (nlp_example.py shape, synthetic MRPC) on 2 CPU / gloo processes."""
+
+import os
+import subprocess
+import sys
+
+import pytest
+
+from accelerate_hpc_test_b200.test_utils.examples import compare_against_test
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EX = os.path.join(ROOT, "examples")
+SMALL = ["--cpu", "--model", "tiny", "--num_epochs", "1", "--train_size", "64", "--eval_size", "41"]
+
+
+def _run(cmd, cwd=None, timeout=420):
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""), OMP_NUM_THREADS="1")
+    r = subprocess.run(cmd, cwd=cwd or ROOT, env=env, capture_output=True, text=True, timeout=timeout)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    return r.stdout
+
+
+def _run_inproc(script, *args):
+    """Run an example's ``main()`` in this process (fresh state singletons), returning what it printed."""
+    import contextlib
+    import io
+    import runpy
+
+    from accelerate_hpc_test_b200.state import AcceleratorState, GradientState, PartialState
+
+    for st in (AcceleratorState, GradientState, PartialState):
+        st._reset_state(True) if st is AcceleratorState else st._reset_state()
+    path = os.path.join(EX, script)
+    old_argv, old_path = sys.argv, list(sys.path)
+    sys.argv = [path, *args]
+    sys.path.insert(0, os.path.dirname(path))  # what `python script.py` does
+    buf = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(buf):
+            runpy.run_path(path, run_name="__main__")
+    finally:
+        sys.argv, sys.path[:] = old_argv, old_path
+        for mod in ("_common", "nlp_example"):
+            sys.modules.pop(mod, None)
+    return buf.getvalue()
+
+
+def _launch(nproc, script, *args):
+    return _run([sys.executable, "-m", "accelerate_hpc_test_b200.commands.accelerate_cli", "launch", "--num_processes", str(nproc), "--cpu",
+                 "--main_process_port", str(29650 + (os.getpid() + hash(script)) % 200), os.path.join(EX, script), *args])
+
+
+def test_nlp_example_two_cpu_processes():
+    out = _launch(2, "nlp_example.py", *SMALL)
+    assert "epoch 0:" in out and "'eval_samples': 41" in out  # gather_for_metrics dropped the padding duplicates
+
+
+@pytest.mark.parametrize("script,extra", [
+    ("by_feature/gradient_accumulation.py", ["--gradient_accumulation_steps", "2"]),
+    ("by_feature/memory.py", []),
+    ("by_feature/early_stopping.py", []),
+    ("by_feature/profiler.py", []),
+    ("by_feature/automatic_gradient_accumulation.py", []),
+])
+def test_by_feature_single_process(script, extra):
+    assert "epoch 0" in _run_inproc(script, *SMALL, *extra)
+
+
+@pytest.mark.parametrize("script,extra", [("by_feature/local_sgd.py", ["--local_sgd_steps", "2"]), ("by_feature/multi_process_metrics.py", [])])
+def test_by_feature_two_processes(script, extra):
+    assert "'eval_samples': 41" in _launch(2, script, *SMALL, *extra)
+
+
+def test_checkpointing_and_tracking_examples(tmp_path):
+    ck = str(tmp_path / "ck")
+    _run_inproc("by_feature/checkpointing.py", *SMALL, "--checkpointing_steps", "2", "--output_dir", ck)
+    assert os.path.isdir(os.path.join(ck, "step_2"))
+    out = _run_inproc("by_feature/checkpointing.py", *SMALL, "--resume_from_checkpoint", os.path.join(ck, "step_2"))
+    assert "epoch 0" in out
+    logs = str(tmp_path / "logs")
+    _run_inproc("by_feature/tracking.py", *SMALL, "--with_tracking", "--project_dir", logs)
+    assert os.path.isfile(os.path.join(logs, "tracking", "metrics.jsonl"))
+    out = _run_inproc("complete_nlp_example.py", *SMALL, "--checkpointing_steps", "epoch", "--output_dir", ck,
+                      "--with_tracking", "--project_dir", logs)
+    assert os.path.isfile(os.path.join(ck, "epoch_0", "model.safetensors"))
+
+
+def test_native_parallelism_examples_on_cpu():
+    out = _launch(4, "torch_native_parallelism/nd_parallel.py", "--cpu", "--model", "tiny", "--tp-size", "2", "--dp-shard-size", "2",
+                  "--sequence-length", "64", "--num-steps", "3")
+    assert "tokens/s over 4 processes" in out
+    out = _launch(2, "alst_ulysses_sequence_parallelism/sp_alst.py", "--cpu", "--model", "tiny", "--sp-size", "2", "--sequence-length", "128",
+                  "--num-steps", "2")
+    assert "sp=2" in out
+    out = _launch(2, "inference/distributed_split.py", "--cpu")
+    assert out.count("generated") == 5
+
+
+@pytest.mark.parametrize("feature", ["checkpointing.py", "tracking.py"])
+def test_complete_example_covers_feature(feature, monkeypatch):
+    """Everything a by-feature script adds to its training function is also in the complete example."""
+    monkeypatch.chdir(ROOT)
+    complete = os.path.join(EX, "complete_nlp_example.py")
+    diff = compare_against_test(complete, os.path.join(EX, "by_feature", feature), parser_only=False)
+    # the by-feature scripts are written against the shared helper module, so only feature-API lines are compared
+    api = [ln for ln in diff if any(k in ln for k in ("save_state", "load_state", "skip_first_batches", "init_trackers", "accelerator.log(",
+                                                      "end_training"))]
+    missing = []
+    text = open(complete).read()
+    for ln in api:
+        call = ln.strip().split("(")[0].split("=")[-1].strip()
+        if call and call not in text:
+            missing.append(ln)
+    assert not missing, missing
