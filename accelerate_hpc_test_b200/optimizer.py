@@ -27,6 +27,9 @@ def move_to_device(state, device):
     return state
 
 
+from .utils.diagnostics import fault_injector
+
+
 class AcceleratedOptimizer(torch.optim.Optimizer):
     """Wraps a torch optimizer so user code can call ``step`` / ``zero_grad`` on every micro-batch.
 
@@ -123,6 +126,11 @@ class AcceleratedOptimizer(torch.optim.Optimizer):
     def step(self, closure=None):
         if not self.gradient_state.sync_gradients:
             return
+        # test hook: ACCELERATE_B200_FAULT_INJECT makes a chosen rank die at a chosen optimizer step (utils/diagnostics.py)
+        self._steps_taken = getattr(self, "_steps_taken", 0) + 1
+        inj = fault_injector()
+        if inj.armed:
+            inj.maybe_fail(self._steps_taken)
         if self._engine is not None and hasattr(self._engine, "optimizer_step"):
             self._is_overflow = bool(self._engine.optimizer_step(self.optimizer, self.scaler))
             return

@@ -81,6 +81,9 @@ class _Pool:
         self.free.append(idx)
 
 
+from ..utils.diagnostics import shadow_check
+
+
 class _Unit:
     """One sharded group of parameters (a wrapped module, or a leftover group of the root)."""
 
@@ -118,6 +121,10 @@ class B200ShardedModule(nn.Module):
         self.device = torch.device(device)
         self.gradient_state = gradient_state
         self.group = shard_group if shard_group is not None else torch.distributed.group.WORLD
+        from ..utils.diagnostics import CommTrace, comm_poison_enabled, comm_shadow_enabled
+
+        self.trace = CommTrace()  # exposed-communication accounting (ACCELERATE_B200_TRACE_COMM=1 or .enabled = True)
+        self._shadow, self._poison = comm_shadow_enabled(), comm_poison_enabled()
         self.replicate_group = replicate_group
         self.world = torch.distributed.get_world_size(self.group)
         self.rank = torch.distributed.get_rank(self.group)
@@ -305,7 +312,12 @@ class B200ShardedModule(nn.Module):
             return
         self._launch_gather(u)
         if self.use_symm and u.ag_event is not None:
-            torch.cuda.current_stream(self.device).wait_event(u.ag_event)
+            self.trace.wait_event(torch.cuda.current_stream(self.device), u.ag_event, "all_gather")
+            if self._shadow:
+                # debug: the same gather through torch.distributed must give the same bytes
+                ref = torch.empty_like(u.full[: self.world * u.shard_numel])
+                torch.distributed.all_gather_into_tensor(ref, u.shard, group=self.group)
+                shadow_check(f"all_gather[{u.name}]", u.full[: self.world * u.shard_numel], ref)
         for p, off in zip(u.params, u.offsets):
             p.data = u.full[off : off + _numel(p._b200_full_shape)].view(p._b200_full_shape)
         u.unsharded = True
@@ -324,6 +336,8 @@ class B200ShardedModule(nn.Module):
         for p in u.params:
             p.data = torch.empty(0, dtype=self.param_dtype, device=self.device)
         ev = None
+        if self._poison:
+            u.full.fill_(float("nan"))  # debug: anything that still reads the released buffer turns into NaN
         if self.use_symm:
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(self.device))
@@ -389,7 +403,7 @@ class B200ShardedModule(nn.Module):
             u.grad_off, buf = u.gpool.bufs[idx]
             u.grad = buf[: u.padded]
             if self.use_symm and u.gpool.events[idx] is not None:
-                torch.cuda.current_stream(self.device).wait_event(u.gpool.events[idx])
+                self.trace.wait_event(torch.cuda.current_stream(self.device), u.gpool.events[idx], "grad_buffer_reuse")
             u.has_partial = False
         u.ready = set()
         u.rs_launched = False
@@ -480,7 +494,7 @@ class B200ShardedModule(nn.Module):
             for u in self._units:
                 ev = getattr(u, "rs_event", None)
                 if ev is not None:
-                    cur.wait_event(ev)
+                    self.trace.wait_event(cur, ev, "reduce_scatter_tail")
 
     # ------------------------------------------------------------------ reduce-scatter (+ AdamW)
     def _adam_hyper(self):
@@ -653,6 +667,11 @@ class B200ShardedModule(nn.Module):
     # ------------------------------------------------------------------ state dicts / checkpoints
     def _unit_tensors(self, u: _Unit, flat: torch.Tensor):
         return {n: flat[off : off + _numel(p._b200_full_shape)].view(p._b200_full_shape) for n, p, off in zip(u.param_names, u.params, u.offsets)}
+
+    def exposed_comm_ms(self, by_tag: bool = False):
+        """Milliseconds (since the last call) the compute stream spent waiting for all-gathers / reduce-scatters that were not
+        hidden behind compute.  Needs ``self.trace.enabled = True`` (or ACCELERATE_B200_TRACE_COMM=1); synchronises."""
+        return self.trace.exposed_ms(by_tag=by_tag)
 
     def full_state_dict(self, cpu: bool = True) -> dict:
         """Gather every unit (one at a time) and return name -> full tensor (on CPU by default)."""

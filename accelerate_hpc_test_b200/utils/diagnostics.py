@@ -1,0 +1,219 @@
+"""Device-side timing, exposed-communication accounting, collective shadow checks and fault injection.
+
+The reference has none of this (its profiling is ``ProfileKwargs`` -> ``torch.profiler``, its only
+distributed debug aid is ``ACCELERATE_DEBUG_MODE`` shape verification, recovery is torchelastic's restart).  A framework that
+owns its kernels and its cross-GPU memory needs more:
+
+* :class:`DeviceTimer` — named regions timed with CUDA events on the launching stream (never wall clock), optional NVTX
+  ranges, summary reduced as the **max over ranks**;
+* :class:`CommTrace` — every place where the compute stream waits for a communication stream is bracketed by two events; the
+  time between them is communication that was *not* hidden behind compute ("exposed comm ms/step", the second half of the
+  BASELINE.json metric);
+* shadow mode (``ACCELERATE_B200_COMM_SHADOW=1``) — the engines re-run a collective through torch.distributed next to the
+  peer-memory kernel and compare;  poison mode (``ACCELERATE_B200_COMM_POISON=1``) — recycled communication buffers are filled
+  with NaN so that a read of stale data cannot go unnoticed;
+* fault injection (``ACCELERATE_B200_FAULT_INJECT="kill:rank=1,step=3"``) — makes a rank die at a given optimizer step of the
+  first launch attempt, to exercise ``--max_restarts`` + ``save_state`` / ``load_state`` recovery.
+"""
+
+from __future__ import annotations
+
+import os
+import time
+from collections import OrderedDict
+from contextlib import contextmanager
+from typing import Optional
+
+import torch
+
+
+def _cuda() -> bool:
+    return torch.cuda.is_available()
+
+
+class DeviceTimer:
+    """``with timer.region("fwd"): ...`` — CUDA-event timing of named regions on the current stream.
+
+    On CPU the regions fall back to ``perf_counter`` (tests, gloo runs).  ``summary()`` synchronises once, and returns
+    ``{name: {"ms": total, "calls": n, "ms_per_call": ...}}``; with ``reduce=True`` every number is the max over ranks.
+    """
+
+    def __init__(self, nvtx: Optional[bool] = None, enabled: bool = True):
+        self.enabled = enabled
+        self.nvtx = bool(int(os.environ.get("ACCELERATE_B200_NVTX", "0"))) if nvtx is None else nvtx
+        self._pending = []  # (name, start_event, end_event)
+        self._acc = OrderedDict()
+
+    @contextmanager
+    def region(self, name: str):
+        if not self.enabled:
+            yield
+            return
+        if _cuda():
+            if self.nvtx:
+                torch.cuda.nvtx.range_push(name)
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            try:
+                yield
+            finally:
+                e.record()
+                if self.nvtx:
+                    torch.cuda.nvtx.range_pop()
+                self._pending.append((name, s, e))
+        else:
+            t0 = time.perf_counter()
+            try:
+                yield
+            finally:
+                self._add(name, (time.perf_counter() - t0) * 1e3)
+
+    def _add(self, name, ms):
+        tot, n = self._acc.get(name, (0.0, 0))
+        self._acc[name] = (tot + ms, n + 1)
+
+    def _drain(self):
+        if self._pending:
+            torch.cuda.synchronize()
+            for name, s, e in self._pending:
+                self._add(name, s.elapsed_time(e))
+            self._pending = []
+
+    def summary(self, reduce: bool = True, reset: bool = True) -> dict:
+        self._drain()
+        names = list(self._acc)
+        vals = torch.tensor([self._acc[n][0] for n in names], dtype=torch.float64)
+        if reduce and names and torch.distributed.is_available() and torch.distributed.is_initialized():
+            dev = torch.device("cuda", torch.cuda.current_device()) if torch.distributed.get_backend() == "nccl" else torch.device("cpu")
+            t = vals.to(dev)
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            vals = t.cpu()
+        out = {n: {"ms": float(v), "calls": self._acc[n][1], "ms_per_call": float(v) / max(1, self._acc[n][1])} for n, v in zip(names, vals)}
+        if reset:
+            self._acc = OrderedDict()
+        return out
+
+
+class CommTrace:
+    """Accounting of the time the compute stream spends waiting for communication streams.
+
+    The engines call :meth:`wait_event` / :meth:`wait_stream` instead of the raw stream methods.  When tracing is on, the
+    wait is bracketed by two timing events recorded on the waiting stream; nothing else runs on that stream between them, so
+    their distance is exactly the stall.  :meth:`exposed_ms` synchronises and returns the accumulated stall.
+    """
+
+    def __init__(self, enabled: Optional[bool] = None):
+        self.enabled = bool(int(os.environ.get("ACCELERATE_B200_TRACE_COMM", "0"))) if enabled is None else enabled
+        self._pairs = []
+
+    def wait_event(self, stream: "torch.cuda.Stream", event: "torch.cuda.Event", tag: str = ""):
+        if not self.enabled:
+            stream.wait_event(event)
+            return
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        stream.wait_event(event)
+        b.record(stream)
+        self._pairs.append((tag, a, b))
+
+    def wait_stream(self, stream: "torch.cuda.Stream", other: "torch.cuda.Stream", tag: str = ""):
+        if not self.enabled:
+            stream.wait_stream(other)
+            return
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        stream.wait_stream(other)
+        b.record(stream)
+        self._pairs.append((tag, a, b))
+
+    def exposed_ms(self, by_tag: bool = False, reset: bool = True):
+        if not self._pairs:
+            return {} if by_tag else 0.0
+        torch.cuda.synchronize()
+        per = {}
+        for tag, a, b in self._pairs:
+            per[tag] = per.get(tag, 0.0) + a.elapsed_time(b)
+        if reset:
+            self._pairs = []
+        return per if by_tag else float(sum(per.values()))
+
+
+# ---------------------------------------------------------------------------------------------- debug switches
+def comm_shadow_enabled() -> bool:
+    return os.environ.get("ACCELERATE_B200_COMM_SHADOW", "0") == "1"
+
+
+def comm_poison_enabled() -> bool:
+    return os.environ.get("ACCELERATE_B200_COMM_POISON", "0") == "1"
+
+
+def shadow_check(name: str, ours: torch.Tensor, reference: torch.Tensor, rtol: float = 0.0, atol: float = 0.0):
+    """Raise with a precise diagnostic when a peer-memory collective disagrees with its torch.distributed twin."""
+    a, b = ours.float(), reference.float()
+    bad = ~torch.isclose(a, b, rtol=rtol, atol=atol, equal_nan=True)
+    if bool(bad.any()):
+        idx = int(bad.flatten().nonzero()[0])
+        rank = torch.distributed.get_rank() if torch.distributed.is_initialized() else 0
+        raise RuntimeError(
+            f"[comm shadow] {name}: rank {rank}: {int(bad.sum())} of {bad.numel()} elements differ from the torch.distributed "
+            f"result (first at flat index {idx}: ours {a.flatten()[idx].item()!r} vs reference {b.flatten()[idx].item()!r})"
+        )
+
+
+# ---------------------------------------------------------------------------------------------- fault injection
+class FaultInjector:
+    """``ACCELERATE_B200_FAULT_INJECT="kill:rank=R,step=S[,code=C][,every_attempt=1]"``.
+
+    ``maybe_fail(step)`` is called by ``AcceleratedOptimizer.step`` with the number of optimizer steps taken so far.  By
+    default the fault fires only on the first launch attempt (``TORCHELASTIC_RESTART_COUNT == 0``), so a job started with
+    ``--max_restarts 1`` dies once, restarts and must finish from its last checkpoint."""
+
+    def __init__(self, spec: Optional[str] = None):
+        spec = os.environ.get("ACCELERATE_B200_FAULT_INJECT", "") if spec is None else spec
+        self.kind = None
+        self.args = {}
+        if spec:
+            kind, _, rest = spec.partition(":")
+            self.kind = kind.strip()
+            for kv in filter(None, rest.split(",")):
+                k, _, v = kv.partition("=")
+                self.args[k.strip()] = v.strip()
+            if self.kind not in ("kill", "raise", "hang"):
+                raise ValueError(f"unknown fault kind {self.kind!r} in ACCELERATE_B200_FAULT_INJECT (kill | raise | hang)")
+
+    @property
+    def armed(self) -> bool:
+        return self.kind is not None
+
+    def maybe_fail(self, step: int, rank: Optional[int] = None):
+        if not self.armed:
+            return
+        if rank is None:
+            rank = int(os.environ.get("RANK", "0"))
+        if int(self.args.get("rank", 0)) != rank or int(self.args.get("step", 0)) != step:
+            return
+        if not int(self.args.get("every_attempt", 0)) and int(os.environ.get("TORCHELASTIC_RESTART_COUNT", "0")) > 0:
+            return
+        msg = f"[fault injection] rank {rank}: injected `{self.kind}` at optimizer step {step}"
+        print(msg, flush=True)
+        if self.kind == "kill":
+            os._exit(int(self.args.get("code", 17)))
+        if self.kind == "raise":
+            raise RuntimeError(msg)
+        if self.kind == "hang":
+            time.sleep(float(self.args.get("seconds", 3600)))
+
+
+_injector: Optional[FaultInjector] = None
+
+
+def fault_injector() -> FaultInjector:
+    global _injector
+    if _injector is None:
+        _injector = FaultInjector()
+    return _injector
+
+
+def _reset_fault_injector():
+    global _injector
+    _injector = None

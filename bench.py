@@ -207,6 +207,10 @@ def run(args, build_fn):
                "h2d_bytes_per_step": int(host_batches[0].numel() * host_batches[0].element_size()),
                "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e / args.steps, "last_loss": losses[-1] if losses else None}
 
+    exposed = None
+    if info.get("exposed_comm") is not None and world > 1:
+        exposed = info["exposed_comm"](step_device, dev_batches)
+
     if rank == 0:
         out = {
             "metric": "Llama-3-8B training tokens/s (whole job)" if args.model == "llama3-8b" else f"{args.model} training tokens/s",
@@ -218,7 +222,7 @@ def run(args, build_fn):
                        "seq_len": args.seq_len, "parallelism": info["parallelism"], "optimizer": "AdamW",
                        "l2_policy": "working set per step (>100 GB) exceeds the 126 MB L2; no explicit flush",
                        "baseline_note": "vs_baseline = value / (8000 tokens/s/device x N), the reference's published 8xH100 FSDP2 bf16 figure"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "exposed_comm_ms_per_step": exposed,
             "tflops_per_gpu": info.get("flops_per_token", 0) * value / world / 1e12 if info.get("flops_per_token") else None,
             "peak_mem_gb": torch.cuda.max_memory_allocated() / 2**30,
         }
@@ -289,7 +293,25 @@ def build_ours(args, cfg, rank, world, local):
 
         r = accelerator.torch_device_mesh.get_local_rank("cp")
         shard_batch = lambda b: shard_sequence(b, 1, r, mp)  # noqa: E731 - head + tail chunk of this cp rank
-    info = {"parallelism": names.get(par, f"{mp_kind}={mp} x fsdp2 dp_shard={world // mp}"),
+    def exposed_comm(step_fn, batches, steps=3):
+        """ms/step the compute stream waited for un-hidden all-gathers / reduce-scatters (max over ranks); outside the timed region"""
+        trace = getattr(model, "trace", None)
+        if trace is None:
+            return None
+        trace.enabled = True
+        trace.exposed_ms()  # reset
+        for i in range(steps):
+            step_fn(batches[i % len(batches)])
+        per = trace.exposed_ms(by_tag=True)
+        trace.enabled = False
+        t = torch.tensor([sum(per.values()) / steps] + [per.get(k, 0.0) / steps for k in ("all_gather", "grad_buffer_reuse", "reduce_scatter_tail")],
+                         device=accelerator.device)
+        if world > 1:
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        v = [round(float(x), 3) for x in t.tolist()]
+        return {"total": v[0], "all_gather": v[1], "grad_buffer_reuse": v[2], "reduce_scatter_tail": v[3]}
+
+    info = {"parallelism": names.get(par, f"{mp_kind}={mp} x fsdp2 dp_shard={world // mp}"), "exposed_comm": exposed_comm,
             "launch_count": _lib.launch_count, "flops_per_token": lcfg.flops_per_token(args.seq_len),
             "model_parallel_size": mp, "shard_batch": shard_batch}
     return step_device, step_e2e, info
