@@ -169,6 +169,19 @@ class PartialState:
             kwargs["store"] = torch.distributed.FileStore(rdv_file, int(os.environ["WORLD_SIZE"]))
             kwargs["rank"] = int(os.environ["RANK"])
             kwargs["world_size"] = int(os.environ["WORLD_SIZE"])
+        attempt = int(os.environ.get("TORCHELASTIC_RESTART_COUNT", "0") or 0)
+        if (attempt > 0 and "gloo" in str(backend) and "init_method" not in kwargs and "store" not in kwargs
+                and os.environ.get("LOCAL_WORLD_SIZE") == os.environ.get("WORLD_SIZE")):
+            # Restarted worker group (torchelastic --max_restarts) on one node with gloo: in this torch build gloo's
+            # connectFullMesh finds the addresses the dead attempt left in the agent's store ("Connection refused").  A
+            # fresh file store per attempt has no such leftovers.  (NCCL groups do not go through these keys.)
+            import tempfile
+
+            run_id = os.environ.get("TORCHELASTIC_RUN_ID", "none")
+            path = os.path.join(tempfile.gettempdir(), f"b200_rdv_{run_id}_{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}_{attempt}")
+            kwargs["store"] = torch.distributed.FileStore(path, int(os.environ["WORLD_SIZE"]))
+            kwargs["rank"] = int(os.environ["RANK"])
+            kwargs["world_size"] = int(os.environ["WORLD_SIZE"])
         if not use_cpu and torch.cuda.is_available():
             local_rank = int(os.environ.get("LOCAL_RANK", 0))
             torch.cuda.set_device(local_rank % max(torch.cuda.device_count(), 1))
