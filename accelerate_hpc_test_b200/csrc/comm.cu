@@ -171,6 +171,65 @@ allgather_pull_kernel(Peers peers, int rank, int world, long long shard_off, lon
   asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+// All-reduce phase 2: slice p of the buffer (already reduced by its owner p) is pulled from p into the same place of my
+// buffer.  Same TMA ring as the all-gather; the last CTA closes with a cross-rank barrier so that nobody reuses its buffer
+// while a peer is still copying out of it.
+__global__ void __launch_bounds__(32)
+allgather_inplace_kernel(Peers peers, int rank, int world, long long off, long long slice_bytes, int ch_done, uint32_t epoch,
+                         uint32_t* __restrict__ counter) {
+  extern __shared__ uint8_t ag_smem_raw[];
+  uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ag_smem_raw) + 127) & ~(uintptr_t)127);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + AG_CHUNK * AG_STAGES);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < AG_STAGES; ++i) mbar_init(&bars[i], 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+  if (threadIdx.x == 0) {
+    const long long cps = (slice_bytes + AG_CHUNK - 1) / AG_CHUNK;
+    const long long total = cps * (world - 1);
+    const long long n = (total > blockIdx.x) ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    auto locate = [&](long long k, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
+      const long long g = blockIdx.x + k * (long long)gridDim.x;
+      const int slot = (int)(g / cps);
+      const long long c = g - (long long)slot * cps;
+      const int p = (rank + 1 + slot) % world;
+      const long long o = c * AG_CHUNK;
+      const long long left = slice_bytes - o;
+      bytes = (uint32_t)(left < AG_CHUNK ? left : AG_CHUNK);
+      src = peers.base[p] + off + (long long)p * slice_bytes + o;
+      dst = peers.base[rank] + off + (long long)p * slice_bytes + o;
+    };
+    auto issue_load = [&](long long k) {
+      const uint8_t* src; uint8_t* dst; uint32_t bytes;
+      locate(k, src, dst, bytes);
+      const int st = (int)(k % AG_STAGES);
+      mbar_arrive_expect_tx(&bars[st], bytes);
+      bulk_g2s(ring + st * AG_CHUNK, src, bytes, &bars[st]);
+    };
+    for (long long k = 0; k < AG_AHEAD && k < n; ++k) issue_load(k);
+    for (long long k = 0; k < n; ++k) {
+      if (k + AG_AHEAD < n) {
+        asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(AG_STAGES - AG_AHEAD - 1) : "memory");
+        issue_load(k + AG_AHEAD);
+      }
+      const int st = (int)(k % AG_STAGES);
+      mbar_wait(&bars[st], (uint32_t)((k / AG_STAGES) & 1));
+      const uint8_t* src; uint8_t* dst; uint32_t bytes;
+      locate(k, src, dst, bytes);
+      bulk_s2g(dst, ring + st * AG_CHUNK, bytes);
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  __syncwarp();
+  if (last_cta(counter)) {
+    __threadfence_system();
+    signal_all(peers, rank, world, ch_done, epoch);
+    wait_all(peers, rank, world, ch_done, epoch);
+  }
+}
+
 // ------------------------------------------------------------------------------ reduce-scatter + AdamW
 struct AdamArgs {
   float lr, beta1, beta2, eps, weight_decay, bias_c1, bias_c2, grad_scale;
@@ -249,7 +308,7 @@ reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off
       if (lane == 0) mbar_arrive(&empty[st]);  // the stage may be refilled while we do the optimizer math
       if (++st == stages) { st = 0; ph ^= 1; }
       if (e0 >= n) continue;
-      if (do_adam) {
+      if (do_adam == 1) {
         float pw[8];
         const float4 m0 = *reinterpret_cast<const float4*>(m + e0), m1 = *reinterpret_cast<const float4*>(m + e0 + 4);
         const float4 v0 = *reinterpret_cast<const float4*>(v + e0), v1 = *reinterpret_cast<const float4*>(v + e0 + 4);
@@ -275,6 +334,12 @@ reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off
         uint4 o;
         o.x = f2_to_bf2(pw[0], pw[1]); o.y = f2_to_bf2(pw[2], pw[3]);
         o.z = f2_to_bf2(pw[4], pw[5]); o.w = f2_to_bf2(pw[6], pw[7]);
+        *reinterpret_cast<uint4*>(shard + e0) = o;
+      } else if (do_adam == 2) {
+        // all-reduce phase 1: the scaled sum goes back, as bf16, into my slice of my own buffer (param_off points there)
+        uint4 o;
+        o.x = f2_to_bf2(acc[0] * gs, acc[1] * gs); o.y = f2_to_bf2(acc[2] * gs, acc[3] * gs);
+        o.z = f2_to_bf2(acc[4] * gs, acc[5] * gs); o.w = f2_to_bf2(acc[6] * gs, acc[7] * gs);
         *reinterpret_cast<uint4*>(shard + e0) = o;
       } else {
         *reinterpret_cast<float4*>(grad_out + e0) = make_float4(acc[0] * gs, acc[1] * gs, acc[2] * gs, acc[3] * gs);
@@ -615,6 +680,42 @@ B200_API int b200_seq_head_exchange(const void* const* peer_ptrs, int rank, int 
   seq_head_exchange_kernel<<<ctas, 32, EX_SMEM, (cudaStream_t)stream>>>(P, rank, world, src_off, (uint8_t*)out, mode, B, S_loc,
                                                                         src_pitch, dst_pitch, sg, ch_arrive, ch_done, epoch,
                                                                         (uint32_t*)counter);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// In-place bf16 all-reduce (times `scale`) of n elements at byte offset `off`, driven by the TMA engine end to end:
+//   phase 1  every rank reduces ITS slice: peers' copies -> smem (cp.async.bulk) -> fp32 sum -> bf16 back into its own buffer
+//            (the reduce-scatter kernel in its "do_adam = 2" mode; it ends with a cross-rank barrier),
+//   phase 2  every rank pulls the other slices from their owners (allgather_inplace_kernel, ends with a barrier).
+// n % (8 * world) == 0.  Uses channels ch[0..2] and two counters (counter, counter + 1).
+B200_API int b200_allreduce_tma(const void* const* peer_ptrs, int rank, int world, long long off, long long n, float scale,
+                                int ch_arrive, int ch_mid, int ch_done, unsigned epoch, void* counter, int ctas, void* stream) {
+  if (off % 16 || n % ((long long)world * 8)) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  if (ctas <= 0) ctas = 148;
+  const long long slice = n / world;
+  AdamArgs a{0.f, 0.9f, 0.999f, 1e-8f, 0.f, 1.f, 1.f, scale};
+  int stages = 24576 / (world * RS_TILE_BYTES);
+  stages = stages < 1 ? 1 : (stages > 3 ? 3 : stages);
+  const int smem = stages * world * RS_TILE_BYTES + 128 + 128;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA(cudaFuncSetAttribute(reduce_scatter_adamw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 8 * RS_TILE_BYTES + 256));
+    B200_CUDA(cudaFuncSetAttribute(allgather_inplace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AG_SMEM));
+    attr = true;
+  }
+  // the slices of this all-reduce start at `off`: rank r owns elements [r * slice, (r + 1) * slice)
+  reduce_scatter_adamw_kernel<<<ctas, 160, smem, (cudaStream_t)stream>>>(
+      P, rank, world, off, slice, nullptr, nullptr, nullptr, off + (long long)rank * slice * 2, nullptr, a, 2, nullptr, ch_arrive, ch_mid,
+      epoch, (uint32_t*)counter, stages);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  allgather_inplace_kernel<<<ctas, 32, AG_SMEM, (cudaStream_t)stream>>>(P, rank, world, off, slice * 2, ch_done, epoch,
+                                                                       (uint32_t*)counter + 1);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;

@@ -21,6 +21,8 @@ import contextlib
 import weakref
 from typing import Optional
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -77,6 +79,7 @@ class B200DataParallel(nn.Module):
             self._own_workspace = False
         self.ws = workspace
         self.comm_stream = torch.cuda.Stream(device=self.device)
+        self._tma_allreduce = os.environ.get("ACCELERATE_B200_ALLREDUCE", "tma") == "tma"
         self._buckets: list[_Bucket] = []
         self._param_slot: dict[int, tuple[_Bucket, int]] = {}
         self._build_buckets(params)
@@ -113,6 +116,7 @@ class B200DataParallel(nn.Module):
             b.offset_bytes, b.buffer = self.ws.alloc_tensor((b.padded,), b.dtype)
             b.buffer.zero_()
             b.ch_arrive, b.ch_done = self.ws.new_channel(), self.ws.new_channel()
+            b.ch_mid = self.ws.new_channel()  # between the two phases of the TMA all-reduce
             for p, off in zip(b.params, b.offsets):
                 self._param_slot[id(p)] = (b, off)
                 view = b.buffer[off : off + p.numel()].view(p.shape)
@@ -175,7 +179,11 @@ class B200DataParallel(nn.Module):
         ev.record(torch.cuda.current_stream(self.device))
         self.comm_stream.wait_event(ev)
         with torch.cuda.stream(self.comm_stream):
-            self.ws.allreduce_(b.offset_bytes, b.padded, b.dtype, 1.0 / self.world, b.ch_arrive, b.ch_done, stream=self.comm_stream)
+            if b.dtype == torch.bfloat16 and self._tma_allreduce:
+                # TMA engine end to end (reduce my slice from all peers, then pull the other slices): ~1.5x the LSU kernel
+                self.ws.allreduce_tma_(b.offset_bytes, b.padded, 1.0 / self.world, (b.ch_arrive, b.ch_mid, b.ch_done), stream=self.comm_stream)
+            else:
+                self.ws.allreduce_(b.offset_bytes, b.padded, b.dtype, 1.0 / self.world, b.ch_arrive, b.ch_done, stream=self.comm_stream)
             b.done_event = torch.cuda.Event()
             b.done_event.record(self.comm_stream)
 

@@ -142,6 +142,16 @@ class SymmetricWorkspace:
         check(self.lib.b200_allreduce(self.peer_array, self.rank, self.world, off, numel, int(dtype == torch.bfloat16), float(scale),
                                       ch_arrive, ch_done, e, self.counter_ptr(ch_arrive), ctas, _stream(stream)), "allreduce")
 
+    def allreduce_tma_(self, off: int, numel: int, scale: float, channels, ctas: int = 148, stream=None):
+        """In-place bf16 all-reduce on the TMA engine (reduce my slice, then pull the others).  ``channels`` = three channel
+        ids reserved for this buffer (arrive / between the phases / done)."""
+        ch_a, ch_m, ch_d = channels
+        e = self.next_epoch(ch_a)
+        self._epochs[ch_m] = e
+        self._epochs[ch_d] = e
+        check(self.lib.b200_allreduce_tma(self.peer_array, self.rank, self.world, off, numel, float(scale), ch_a, ch_m, ch_d, e,
+                                          self.counter_ptr(ch_a), ctas, _stream(stream)), "allreduce_tma")
+
     def alltoall_pull(self, send_off: int, block_bytes: int, out: torch.Tensor, ch_arrive: int, ch_done: int, ctas: int = 32,
                       stream=None):
         e = self.next_epoch(ch_arrive)

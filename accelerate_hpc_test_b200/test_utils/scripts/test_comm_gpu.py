@@ -4,6 +4,7 @@ Launch: ``torchrun --nproc-per-node N --master-addr 127.0.0.1 -m accelerate_hpc_
 Every check compares against torch.distributed (NCCL) or a single-process replay of the same math.
 """
 
+import json
 import os
 import sys
 import time
@@ -15,6 +16,40 @@ import torch.distributed as dist
 def log(*a):
     if dist.get_rank() == 0:
         print(*a, flush=True)
+
+
+RESULTS = []  # rows of profiles/fused_paths_n{world}.json
+NVLINK_GBS = 900.0      # NVLink 5 per direction and GPU (nominal)
+try:
+    _mp = json.load(open(os.path.join(os.path.dirname(__file__), "..", "..", "..", "MEASURED_PEAKS.json")))
+    PEAK_TFLOPS, HBM_GBS = float(_mp["bf16_tflops"]), float(_mp["hbm_gbs"])
+except Exception:  # noqa: BLE001
+    PEAK_TFLOPS, HBM_GBS = 2250.0, 7700.0
+
+
+def record(row, name, ours_ms, baseline, baseline_ms, flops=0.0, link_bytes=0.0, hbm_bytes=0.0):
+    """Roofline of a fused path = the slower of its math at the measured bf16 peak and its bytes over the link / HBM."""
+    roof_ms = max(flops / (PEAK_TFLOPS * 1e9), link_bytes / (NVLINK_GBS * 1e6), hbm_bytes / (HBM_GBS * 1e6))
+    RESULTS.append(dict(row=row, op=name, ours_ms=round(ours_ms, 4), baseline=baseline, baseline_ms=round(baseline_ms, 4),
+                        speedup_vs_baseline=round(baseline_ms / ours_ms, 3), roofline_ms=round(roof_ms, 4),
+                        roofline_fraction=round(roof_ms / ours_ms, 3)))
+
+
+def timed(fn, iters=10, warm=3):
+    """ms per call: CUDA events on the launching stream, max over ranks."""
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(iters):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([s.elapsed_time(e) / iters], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
 
 
 def rel(a, b):
@@ -105,7 +140,23 @@ def check_collectives(ws, dev, rank, world):
     buf.normal_()
     nccl_buf = buf.clone()
     ch_a, ch_d = ws.new_channel(), ws.new_channel()
+    # correctness of the TMA all-reduce first (small integers: the bf16 sum is exact, so the comparison is bitwise)
+    chs = (ws.new_channel(), ws.new_channel(), ws.new_channel())
+    nt = world * 8 * 1031
+    toff, tbuf = ws.alloc_tensor((nt,), torch.bfloat16)
+    vals = torch.randint(-8, 8, (nt,), device=dev).to(torch.bfloat16)
+    tbuf.copy_(vals)
+    tref = vals.clone()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ws.allreduce_tma_(toff, nt, 1.0, chs)
+    dist.all_reduce(tref)
+    torch.cuda.synchronize()
+    assert torch.equal(tbuf, tref), "allreduce_tma"
+    log("allreduce_tma ok")
+    chs2 = (ws.new_channel(), ws.new_channel(), ws.new_channel())
     for name, fn in (("ours_allreduce", lambda: ws.allreduce_(off, n, torch.bfloat16, 1.0 / world, ch_a, ch_d, ctas=64)),
+                     ("ours_allreduce_tma", lambda: ws.allreduce_tma_(off, n, 1.0 / world, chs2)),
                      ("nccl_allreduce", lambda: dist.all_reduce(nccl_buf))):
         for _ in range(3):
             fn()
@@ -122,6 +173,9 @@ def check_collectives(ws, dev, rank, world):
         busbw = 2 * (world - 1) / world * n * 2 / (t.item() * 1e-3) / 1e9
         res[name] = (t.item(), busbw)
         log(f"{name}: {t.item():.3f} ms, bus bw {busbw:.1f} GB/s ({n * 2 / 2**20:.0f} MiB)")
+    record("W7", "all-reduce 512 MiB bf16, scale fused (TMA: reduce own slice + pull the rest)", res["ours_allreduce_tma"][0], "ncclAllReduce",
+           res["nccl_allreduce"][0],
+           link_bytes=2 * (world - 1) / world * n * 2)
     # all-gather of one Llama-3-8B decoder layer (436 MB gathered) vs NCCL
     layer_elems = 218_112_000 // (world * 8) * (world * 8)
     sh = layer_elems // world
@@ -159,6 +213,36 @@ def check_collectives(ws, dev, rank, world):
     t = torch.tensor([s.elapsed_time(e2) / 5], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     log(f"nccl_allgather: {t.item():.3f} ms, ingress {(world - 1) / world * layer_elems * 2 / (t.item() * 1e-3) / 1e9:.1f} GB/s")
+    t_ag = timed(lambda: ws.allgather_pull(soff, sh * 2, full, ctas=148), iters=5)
+    record("W9", "all-gather of one Llama-3-8B layer (436 MB, TMA bulk pull, 148 CTAs)", t_ag, "ncclAllGather", t.item(),
+           link_bytes=(world - 1) / world * layer_elems * 2)
+    # ---- W8: reduce-scatter + AdamW on one layer's gradients vs NCCL reduce-scatter + our flat AdamW kernel
+    nsh = sh
+    g_off, g_all = ws.alloc_tensor((layer_elems,), torch.bfloat16)
+    p_off, p_sh = ws.alloc_tensor((nsh,), torch.bfloat16)
+    g_all.normal_()
+    mst, m1, v1 = torch.randn(nsh, device=dev), torch.zeros(nsh, device=dev), torch.zeros(nsh, device=dev)
+    ch_a2, ch_d2 = ws.new_channel(), ws.new_channel()
+    hp = dict(lr=1e-4, beta1=0.9, beta2=0.95, eps=1e-8, weight_decay=0.1)
+
+    def ours_rs_adamw():
+        e_ = ws.next_epoch(ch_a2)
+        ws._epochs[ch_d2] = e_
+        check(ws.lib.b200_reduce_scatter_adamw(ws.peer_array, rank, world, g_off, nsh, ptr(mst), ptr(m1), ptr(v1), p_off, None, hp["lr"],
+                                               hp["beta1"], hp["beta2"], hp["eps"], hp["weight_decay"], 2, 1.0 / world, 1, None, ch_a2, ch_d2, e_,
+                                               ws.counter_ptr(ch_a2), 148, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+
+    g_red = torch.empty(nsh, dtype=torch.bfloat16, device=dev)
+    sh_out = torch.empty(nsh, dtype=torch.bfloat16, device=dev)
+
+    def nccl_rs_adamw():
+        dist.reduce_scatter_tensor(g_red, g_all)
+        F.adamw_flat_(mst, m1, v1, g_red, sh_out, step=2, grad_scale=1.0 / world, **hp)
+
+    t_o, t_b = timed(ours_rs_adamw, iters=5), timed(nccl_rs_adamw, iters=5)
+    log(f"rs+adamw one layer: ours {t_o:.3f} ms, nccl reduce_scatter + adamw kernel {t_b:.3f} ms")
+    record("W8", "reduce-scatter fused with sharded AdamW (one layer, 436 MB of gradients)", t_o, "ncclReduceScatter + AdamW kernel", t_b,
+           link_bytes=(world - 1) / world * layer_elems * 2, hbm_bytes=layer_elems * 2 + nsh * 26.0)
     assert torch.equal(full, full2)
     return res
 
@@ -305,6 +389,7 @@ def check_tp(dev, rank, world):
         return rs_out
 
     from accelerate_hpc_test_b200.ops import functional as F
+    tms = {}
     for name, fn in (("fused_ag_gemm", lambda: big.ag_gemm(x, w)), ("nccl_ag_then_cublas", nccl_ag_gemm), ("gemm_only", lambda: F.gemm(xf, w)),
                      ("fused_gemm_rs", lambda: big.gemm_rs(xr, wr)), ("cublas_then_nccl_rs", nccl_gemm_rs), ("gemm_only_rs_shape", lambda: F.gemm(xr, wr))):
         for _ in range(3):
@@ -320,6 +405,13 @@ def check_tp(dev, rank, world):
         tt = torch.tensor([s.elapsed_time(e2) / 10], device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         log(f"tp {name}: {tt.item():.3f} ms")
+        tms[name] = tt.item()
+    record("W10", f"all-gather -> GEMM (x [{T // world}x{H}] per rank, W [{28672 // world}x{H}])", tms["fused_ag_gemm"],
+           "ncclAllGather + cuBLASLt", tms["nccl_ag_then_cublas"], flops=2.0 * T * (28672 // world) * H,
+           link_bytes=(world - 1) / world * T * H * 2)
+    record("W11", f"GEMM -> reduce-scatter (x [{T}x{14336 // world}], W [{H}x{14336 // world}])", tms["fused_gemm_rs"],
+           "cuBLASLt + ncclReduceScatter", tms["cublas_then_nccl_rs"], flops=2.0 * T * H * (14336 // world),
+           link_bytes=(world - 1) / world * T * H * 2)
     # whole model: TP Llama vs single-GPU replica
     cfg = LlamaConfig.tiny(num_attention_heads=max(4, 2 * world), num_key_value_heads=max(2, world), hidden_size=512, intermediate_size=1024)
     torch.manual_seed(0)
@@ -380,6 +472,28 @@ def check_seq(dev, rank, world):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         log(f"ulysses {name}: {tt.item():.3f} ms ({xb.numel() * 2 * (world - 1) / world / tt.item() / 1e6:.0f} GB/s ingress)")
     log("ulysses exchange ok")
+    # W12 / W13: QKV projection fused with the sequence->head all-to-all (also the dgrad of the output projection)
+    from accelerate_hpc_test_b200.ops import functional as F
+
+    Hm = 4096
+    xa = torch.randn(Bq * Sl, Hm, device=dev).to(torch.bfloat16)
+    wqkv = (torch.randn(sum(wd), Hm, device=dev) * 0.02).to(torch.bfloat16)
+    fused = comm.gemm_scatter(xa, wqkv, Bq, Sl, wd)
+    unfused = comm._exchange_reference(F.gemm(xa, wqkv), 0, Bq, Sl, wd)
+    assert torch.equal(fused, unfused), "fused QKV projection + all-to-all differs from GEMM + all_to_all_single"
+    t_f = timed(lambda: comm.gemm_scatter(xa, wqkv, Bq, Sl, wd))
+    t_u = timed(lambda: comm._exchange_reference(xa @ wqkv.t(), 0, Bq, Sl, wd))
+    log(f"ulysses fused qkv-projection + all-to-all: {t_f:.3f} ms vs cuBLAS + NCCL all_to_all + permutes {t_u:.3f} ms")
+    record("W12", f"Ulysses QKV projection + all-to-all ({Bq * Sl} tokens per rank, W [{sum(wd)}x{Hm}])", t_f,
+           "cuBLASLt + all_to_all_single + permutes", t_u, flops=2.0 * Bq * Sl * sum(wd) * Hm,
+           link_bytes=(world - 1) / world * Bq * Sl * sum(wd) * 2)
+    wo = (torch.randn(Hm, hq * D, device=dev) * 0.02).to(torch.bfloat16)
+    dyo = torch.randn(Bq * Sl, Hm, device=dev).to(torch.bfloat16)
+    t_f = timed(lambda: comm.gemm_scatter(dyo, wo, Bq, Sl, (hq * D,), b_mn_major=True))
+    t_u = timed(lambda: comm._exchange_reference(dyo @ wo, 0, Bq, Sl, (hq * D,)))
+    log(f"ulysses fused out-projection dgrad + all-to-all: {t_f:.3f} ms vs cuBLAS + NCCL {t_u:.3f} ms")
+    record("W13", "Ulysses output-projection dgrad + all-to-all", t_f, "cuBLASLt + all_to_all_single + permutes", t_u,
+           flops=2.0 * Bq * Sl * hq * D * Hm, link_bytes=(world - 1) / world * Bq * Sl * hq * D * 2)
 
     cfg = LlamaConfig.tiny(num_attention_heads=2 * world, num_key_value_heads=world, hidden_size=512, intermediate_size=1024)
     torch.manual_seed(0)
@@ -439,6 +553,13 @@ def main():
     if "seq" in what:
         check_seq(dev, rank, world)
     dist.barrier()
+    if rank == 0 and RESULTS:
+        os.makedirs("gpurun_out", exist_ok=True)
+        with open(f"gpurun_out/fused_paths_n{world}.json", "w") as f:
+            json.dump({"world": world, "peaks": {"bf16_tflops": PEAK_TFLOPS, "nvlink_gbs_per_direction": NVLINK_GBS, "hbm_gbs": HBM_GBS},
+                       "rows": RESULTS}, f, indent=1)
+        for r_ in RESULTS:
+            log(json.dumps(r_))
     log("ALL MULTI-GPU CHECKS PASSED")
     dist.destroy_process_group()
 
