@@ -87,9 +87,9 @@ __device__ __forceinline__ void bulk_s2g_g2(void* gdst, const void* smem_src, ui
 }
 // with the fused all-gather, visit the 256-row tiles of my own shard first, then the shards in arrival order
 __device__ __forceinline__ int ag_rotate2(int m_t, const Params& p) {
-  const int per_shard = (p.ag_rows + 255) / 256;
-  int r = m_t + p.ag_rank * per_shard;
-  return r >= p.num_m_tiles ? r - p.num_m_tiles : r;
+  // start at the tile that holds the first row of my shard (a tile may span several small shards, or a shard several tiles)
+  const int start = (int)(((long long)p.ag_rank * p.ag_rows) / 256);
+  return (m_t + start) % p.num_m_tiles;
 }
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {

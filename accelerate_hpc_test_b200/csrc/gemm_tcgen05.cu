@@ -84,9 +84,8 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
 
 // with the fused all-gather, visit the m-blocks of my own shard first, then the shards in arrival order
 __device__ __forceinline__ int ag_rotate(int m_blk, const GemmParams& p) {
-  const int per_shard = (p.ag_rows + BM - 1) / BM;
-  int r = m_blk + p.ag_rank * per_shard;
-  return r >= p.num_m_blocks ? r - p.num_m_blocks : r;
+  const int start = (int)(((long long)p.ag_rank * p.ag_rows) / BM);  // block holding the first row of my shard
+  return (m_blk + start) % p.num_m_blocks;
 }
 
 template <int A_MN, int B_MN, int FUSE_AG>
