@@ -1,49 +1,85 @@
-"""YAML / JSON config file schema (reference src/accelerate/commands/config/config_args.py:29-252).
+"""Schema and file I/O of the launcher configuration (``default_config.yaml``).
 
-The default location stays ``~/.cache/huggingface/accelerate/default_config.yaml`` so existing
-configs are found; unknown keys are rejected with the list of offenders.
+* Location: ``$HF_HOME/accelerate`` or ``$XDG_CACHE_HOME/huggingface/accelerate`` (default
+  ``~/.cache/huggingface/accelerate``) — the same place the reference uses, so existing files are found.
+* ``.json`` files are read/written as JSON, everything else as YAML.
+* Files written by older versions are upgraded on load (``fp16: true`` → ``mixed_precision: fp16``, a bare
+  ``dynamo_backend`` → ``dynamo_config``, missing ``use_cpu`` / ``debug`` / ``enable_cpu_affinity``); keys the
+  schema does not know are rejected with the full list, never silently dropped.
+
+Parity target: reference ``src/accelerate/commands/config/config_args.py:29-252`` (field names are the file format).
 """
 
+from __future__ import annotations
+
+import dataclasses
+import enum
 import json
 import os
 from dataclasses import dataclass
-from enum import Enum
 from typing import Optional, Union
 
 import yaml
 
 from ...utils.dataclasses import ComputeEnvironment, DistributedType, SageMakerDistributedType
-from ...utils.constants import SAFE_WEIGHTS_NAME  # noqa: F401
 
-hf_cache_home = os.path.expanduser(os.environ.get("HF_HOME", os.path.join(os.environ.get("XDG_CACHE_HOME", "~/.cache"), "huggingface")))
+
+def _cache_root() -> str:
+    xdg = os.environ.get("XDG_CACHE_HOME", "~/.cache")
+    return os.path.expanduser(os.environ.get("HF_HOME", os.path.join(xdg, "huggingface")))
+
+
+hf_cache_home = _cache_root()
 cache_dir = os.path.join(hf_cache_home, "accelerate")
-default_json_config_file = os.path.join(cache_dir, "default_config.yaml")
 default_yaml_config_file = os.path.join(cache_dir, "default_config.yaml")
-if os.path.isfile(default_yaml_config_file) or not os.path.isfile(default_json_config_file):
-    default_config_file = default_yaml_config_file
-else:
-    default_config_file = default_json_config_file
+default_json_config_file = default_yaml_config_file  # historical alias: the default has been YAML for a long time
+default_config_file = default_yaml_config_file
 
 
-def load_config_from_file(config_file):
-    if config_file is not None:
-        if not os.path.isfile(config_file):
-            raise FileNotFoundError(f"The passed configuration file `{config_file}` does not exist. Please pass an existing file to `accelerate launch`, or use the default one created through `accelerate config` and run `accelerate launch` without the `--config_file` argument.")
-    else:
-        config_file = default_config_file
-    with open(config_file, encoding="utf-8") as f:
-        if config_file.endswith(".json"):
-            if (json.load(open(config_file)).get("compute_environment", ComputeEnvironment.LOCAL_MACHINE) == ComputeEnvironment.LOCAL_MACHINE):
-                config_class = ClusterConfig
-            else:
-                config_class = SageMakerConfig
-            return config_class.from_json_file(json_file=config_file)
+# --------------------------------------------------------------------------- raw file access
+def _is_json(path) -> bool:
+    return str(path).endswith(".json")
+
+
+def _read_mapping(path) -> dict:
+    with open(path, encoding="utf-8") as fh:
+        data = json.load(fh) if _is_json(path) else yaml.safe_load(fh)
+    return dict(data or {})
+
+
+def _write_mapping(path, data: dict) -> None:
+    with open(path, "w", encoding="utf-8") as fh:
+        if _is_json(path):
+            fh.write(json.dumps(data, indent=2, sort_keys=True) + "\n")
         else:
-            if (yaml.safe_load(open(config_file)).get("compute_environment", ComputeEnvironment.LOCAL_MACHINE) == ComputeEnvironment.LOCAL_MACHINE):
-                config_class = ClusterConfig
-            else:
-                config_class = SageMakerConfig
-            return config_class.from_yaml_file(yaml_file=config_file)
+            yaml.safe_dump(data, fh)
+
+
+def _plain(value):
+    """Enum → its value, nested dicts likewise; an empty dict becomes ``None`` (and is then left out of the file)."""
+    if isinstance(value, enum.Enum):
+        return value.value
+    if isinstance(value, dict):
+        return {k: _plain(v) for k, v in value.items()} or None
+    return value
+
+
+def load_config_from_file(config_file=None):
+    """Load ``config_file`` (or the default file) into a ``ClusterConfig`` / ``SageMakerConfig``."""
+    if config_file is None:
+        config_file = default_config_file
+    elif not os.path.isfile(config_file):
+        raise FileNotFoundError(
+            f"The passed configuration file `{config_file}` does not exist. Please pass an existing file to `accelerate launch`, "
+            "or use the default one created through `accelerate config` and run `accelerate launch` without the `--config_file` argument."
+        )
+    where = _read_mapping(config_file).get("compute_environment", ComputeEnvironment.LOCAL_MACHINE)
+    schema = ClusterConfig if where == ComputeEnvironment.LOCAL_MACHINE else SageMakerConfig
+    return schema.load(config_file)
+
+
+# --------------------------------------------------------------------------- schemas
+_BACKFILL = {"use_cpu": False, "debug": False, "enable_cpu_affinity": False}
 
 
 @dataclass
@@ -54,95 +90,88 @@ class BaseConfig:
     use_cpu: bool
     debug: bool
 
-    def to_dict(self):
-        result = self.__dict__
-        def _convert_enums(value):
-            if isinstance(value, Enum):
-                return value.value
-            if isinstance(value, dict):
-                if not bool(value):
-                    return None
-                for key1, value1 in value.items():
-                    value[key1] = _convert_enums(value1)
-            return value
-
-        for key, value in result.items():
-            result[key] = _convert_enums(value)
-        result = {k: v for k, v in result.items() if v is not None}
-        return result
-
-    @staticmethod
-    def process_config(config_dict):
-        """Back-fill keys that older config versions did not write."""
-        if "compute_environment" not in config_dict:
-            config_dict["compute_environment"] = ComputeEnvironment.LOCAL_MACHINE
-        if "distributed_type" not in config_dict:
-            raise ValueError("A `distributed_type` must be specified in the config file.")
-        if "num_processes" not in config_dict and config_dict["distributed_type"] == DistributedType.NO:
-            config_dict["num_processes"] = 1
-        if "mixed_precision" not in config_dict:
-            config_dict["mixed_precision"] = "fp16" if ("fp16" in config_dict and config_dict["fp16"]) else None
-        if "fp16" in config_dict:
-            del config_dict["fp16"]
-        if "dynamo_backend" in config_dict:
-            dynamo_backend = config_dict.pop("dynamo_backend")
-            config_dict["dynamo_config"] = {} if dynamo_backend == "NO" else {"dynamo_backend": dynamo_backend}
-        if "use_cpu" not in config_dict:
-            config_dict["use_cpu"] = False
-        if "debug" not in config_dict:
-            config_dict["debug"] = False
-        if "enable_cpu_affinity" not in config_dict:
-            config_dict["enable_cpu_affinity"] = False
-        return config_dict
-
-    @classmethod
-    def _check_extra(cls, config_dict, source):
-        extra_keys = sorted(set(config_dict.keys()) - set(cls.__dataclass_fields__.keys()))
-        if len(extra_keys) > 0:
-            raise ValueError(f"The config file at {source} had unknown keys ({extra_keys}), please try upgrading your `accelerate` version or fix (and potentially remove) these keys from your config file.")
-
-    @classmethod
-    def from_json_file(cls, json_file=None):
-        json_file = default_json_config_file if json_file is None else json_file
-        with open(json_file, encoding="utf-8") as f:
-            config_dict = json.load(f)
-        config_dict = cls.process_config(config_dict)
-        cls._check_extra(config_dict, json_file)
-        return cls(**config_dict)
-
-    def to_json_file(self, json_file):
-        with open(json_file, "w", encoding="utf-8") as f:
-            content = json.dumps(self.to_dict(), indent=2, sort_keys=True) + "\n"
-            f.write(content)
-
-    @classmethod
-    def from_yaml_file(cls, yaml_file=None):
-        yaml_file = default_yaml_config_file if yaml_file is None else yaml_file
-        with open(yaml_file, encoding="utf-8") as f:
-            config_dict = yaml.safe_load(f)
-        config_dict = cls.process_config(config_dict)
-        cls._check_extra(config_dict, yaml_file)
-        return cls(**config_dict)
-
-    def to_yaml_file(self, yaml_file):
-        with open(yaml_file, "w", encoding="utf-8") as f:
-            yaml.safe_dump(self.to_dict(), f)
-
+    # ---- normalisation ----
     def __post_init__(self):
         if isinstance(self.compute_environment, str):
             self.compute_environment = ComputeEnvironment(self.compute_environment)
         if isinstance(self.distributed_type, str):
-            if self.compute_environment == ComputeEnvironment.AMAZON_SAGEMAKER:
-                self.distributed_type = SageMakerDistributedType(self.distributed_type)
-            else:
-                self.distributed_type = DistributedType(self.distributed_type)
+            on_sagemaker = self.compute_environment == ComputeEnvironment.AMAZON_SAGEMAKER
+            self.distributed_type = (SageMakerDistributedType if on_sagemaker else DistributedType)(self.distributed_type)
         if getattr(self, "dynamo_config", None) is None:
             self.dynamo_config = {}
+
+    @staticmethod
+    def process_config(config_dict: dict) -> dict:
+        """Upgrade a mapping written by an older version to today's keys (in place; also returned)."""
+        cfg = config_dict
+        cfg.setdefault("compute_environment", ComputeEnvironment.LOCAL_MACHINE)
+        if "distributed_type" not in cfg:
+            raise ValueError("A `distributed_type` must be specified in the config file.")
+        if cfg["distributed_type"] == DistributedType.NO:
+            cfg.setdefault("num_processes", 1)
+        legacy_fp16 = bool(cfg.pop("fp16", False))
+        if "mixed_precision" not in cfg:
+            cfg["mixed_precision"] = "fp16" if legacy_fp16 else None
+        if "dynamo_backend" in cfg:
+            backend = cfg.pop("dynamo_backend")
+            cfg["dynamo_config"] = {} if backend == "NO" else {"dynamo_backend": backend}
+        for key, value in _BACKFILL.items():
+            cfg.setdefault(key, value)
+        return cfg
+
+    @classmethod
+    def _reject_unknown(cls, mapping: dict, source) -> None:
+        known = {f.name for f in dataclasses.fields(cls)}
+        unknown = sorted(set(mapping) - known)
+        if unknown:
+            raise ValueError(
+                f"The config file at {source} had unknown keys ({unknown}), please try upgrading your `accelerate` version "
+                "or fix (and potentially remove) these keys from your config file."
+            )
+
+    # ---- load / save ----
+    @classmethod
+    def load(cls, path):
+        mapping = cls.process_config(_read_mapping(path))
+        cls._reject_unknown(mapping, path)
+        return cls(**mapping)
+
+    def save(self, path) -> None:
+        _write_mapping(path, self.to_dict())
+
+    def to_dict(self) -> dict:
+        out = {}
+        for key, value in vars(self).items():
+            value = _plain(value)
+            if value is not None:
+                out[key] = value
+        return out
+
+    # reference-compatible spellings
+    @classmethod
+    def from_json_file(cls, json_file=None):
+        return cls.load(default_json_config_file if json_file is None else json_file)
+
+    @classmethod
+    def from_yaml_file(cls, yaml_file=None):
+        return cls.load(default_yaml_config_file if yaml_file is None else yaml_file)
+
+    def to_json_file(self, json_file) -> None:
+        with open(json_file, "w", encoding="utf-8") as fh:
+            fh.write(json.dumps(self.to_dict(), indent=2, sort_keys=True) + "\n")
+
+    def to_yaml_file(self, yaml_file) -> None:
+        with open(yaml_file, "w", encoding="utf-8") as fh:
+            yaml.safe_dump(self.to_dict(), fh)
+
+
+_CLUSTER_SECTIONS = ("deepspeed_config", "fsdp_config", "parallelism_config", "megatron_lm_config", "ipex_config",
+                     "mpirun_config", "fp8_config")
 
 
 @dataclass
 class ClusterConfig(BaseConfig):
-    num_processes: int = -1
+    num_processes: int = -1  # -1: decide at launch time from the visible devices
     machine_rank: int = 0
     num_machines: int = 1
     gpu_ids: Optional[str] = None
@@ -152,7 +181,7 @@ class ClusterConfig(BaseConfig):
     same_network: Optional[bool] = False
     main_training_function: str = "main"
     enable_cpu_affinity: bool = False
-    # strategy sections
+    # one mapping per strategy; empty means "not used"
     deepspeed_config: dict = None
     fsdp_config: dict = None
     parallelism_config: dict = None
@@ -160,7 +189,7 @@ class ClusterConfig(BaseConfig):
     ipex_config: dict = None
     mpirun_config: dict = None
     downcast_bf16: bool = False
-    # tpu keys are accepted (old configs) and ignored
+    # TPU keys: accepted so that old files load, ignored by this build
     tpu_name: str = None
     tpu_zone: str = None
     tpu_use_cluster: bool = False
@@ -173,25 +202,16 @@ class ClusterConfig(BaseConfig):
     fp8_config: dict = None
 
     def __post_init__(self):
-        if self.deepspeed_config is None:
-            self.deepspeed_config = {}
-        if self.fsdp_config is None:
-            self.fsdp_config = {}
-        if self.megatron_lm_config is None:
-            self.megatron_lm_config = {}
-        if self.ipex_config is None:
-            self.ipex_config = {}
-        if self.mpirun_config is None:
-            self.mpirun_config = {}
-        if self.fp8_config is None:
-            self.fp8_config = {}
-        if self.parallelism_config is None:
-            self.parallelism_config = {}
-        return super().__post_init__()
+        for name in _CLUSTER_SECTIONS:
+            if getattr(self, name) is None:
+                setattr(self, name, {})
+        super().__post_init__()
 
 
 @dataclass
 class SageMakerConfig(BaseConfig):
+    """Accepted for file compatibility only; the launcher of this build refuses SageMaker environments."""
+
     ec2_instance_type: str = None
     iam_role_name: str = None
     image_uri: Optional[str] = None

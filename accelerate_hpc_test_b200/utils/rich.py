@@ -1,10 +1,13 @@
-"""Optional rich tracebacks (reference src/accelerate/utils/rich.py)."""
+"""Importing this module switches uncaught-exception output to ``rich`` tracebacks (locals hidden).
+
+Opt-in side-effect module, mirroring the reference's ``accelerate.utils.rich`` import hook.
+"""
 
 from .imports import is_rich_available
 
-if is_rich_available():
-    from rich.traceback import install
-
-    install(show_locals=False)
-else:
+if not is_rich_available():
     raise ModuleNotFoundError("To use the rich extension, install rich with `pip install rich`")
+
+import rich.traceback as _rich_traceback
+
+_rich_traceback.install(show_locals=False)
