@@ -13,6 +13,7 @@
 // flags[c][s] on rank d is written only by rank s.  All waits are bounded (device-side timeout ->
 // trap with a diagnostic) so a missing peer turns into an error, never into a hung GPU.
 #include "common.cuh"
+#include <string.h>
 
 namespace b200 {
 
@@ -119,8 +120,19 @@ __device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint3
                : "memory");
 }
 
+// Segment table of a sharded unit.  A unit's shard is the concatenation of one piece per segment; in the gathered ("full")
+// buffer segment i occupies [full_off, full_off + world * bytes) with rank q's piece at full_off + q * bytes.  A 2-D weight
+// sharded along dim 0 is one segment (piece = a block of rows), so the gathered buffer holds it in its natural layout.
+static constexpr int MAX_SEGS = 32;
+struct Segs {
+  long long shard_off[MAX_SEGS];  // byte offset of the piece inside the shard
+  long long full_off[MAX_SEGS];   // byte offset of the segment inside the gathered buffer
+  long long bytes[MAX_SEGS];      // bytes per piece
+  int n;
+};
+
 __global__ void __launch_bounds__(32)
-allgather_pull_kernel(Peers peers, int rank, int world, long long shard_off, long long shard_bytes,
+allgather_pull_kernel(Peers peers, int rank, int world, long long shard_off, Segs segs,
                       uint8_t* __restrict__ out, int wait_channel, uint32_t wait_epoch) {
   extern __shared__ uint8_t ag_smem_raw[];
   uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ag_smem_raw) + 127) & ~(uintptr_t)127);
@@ -132,20 +144,27 @@ allgather_pull_kernel(Peers peers, int rank, int world, long long shard_off, lon
   }
   __syncwarp();
   if (threadIdx.x != 0) return;
-  const long long chunks_per_shard = (shard_bytes + AG_CHUNK - 1) / AG_CHUNK;
+  long long chunks_per_shard = 0;
+  for (int i = 0; i < segs.n; ++i) chunks_per_shard += (segs.bytes[i] + AG_CHUNK - 1) / AG_CHUNK;
   const long long total = chunks_per_shard * world;
   // chunk g of this CTA: g = blockIdx.x + k * gridDim.x ; peers visited starting at my right neighbour
   const long long n = (total > blockIdx.x) ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
   auto locate = [&](long long k, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes) {
     const long long g = blockIdx.x + k * (long long)gridDim.x;
     const int slot = (int)(g / chunks_per_shard);
-    const long long c = g - (long long)slot * chunks_per_shard;
+    long long c = g - (long long)slot * chunks_per_shard;
     const int p = (rank + 1 + slot) % world;
+    int si = 0;
+    for (; si + 1 < segs.n; ++si) {
+      const long long sc = (segs.bytes[si] + AG_CHUNK - 1) / AG_CHUNK;
+      if (c < sc) break;
+      c -= sc;
+    }
     const long long o = c * AG_CHUNK;
-    const long long left = shard_bytes - o;
+    const long long left = segs.bytes[si] - o;
     bytes = (uint32_t)(left < AG_CHUNK ? left : AG_CHUNK);
-    src = peers.base[p] + shard_off + o;
-    dst = out + (long long)p * shard_bytes + o;
+    src = peers.base[p] + shard_off + segs.shard_off[si] + o;
+    dst = out + segs.full_off[si] + (long long)p * segs.bytes[si] + o;
   };
   auto issue_load = [&](long long k) {
     const uint8_t* src; uint8_t* dst; uint32_t bytes;
@@ -246,8 +265,16 @@ struct AdamArgs {
 static constexpr int RS_TILE = 1024;           // elements per tile (128 consumer threads x 8)
 static constexpr int RS_TILE_BYTES = RS_TILE * 2;
 
+// Element-unit segment table for the reduce-scatter: piece i of my shard covers shard elements [start, start + len) and is
+// the sum over ranks of gradient elements [full + rank * len, full + (rank + 1) * len) of every rank's flat gradient.
+// With more than one segment every len is a multiple of RS_TILE, so a tile never straddles two segments.
+struct RsSegs {
+  long long start[MAX_SEGS], full[MAX_SEGS], len[MAX_SEGS];
+  int n;
+};
+
 __global__ void __launch_bounds__(160)
-reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off, long long n,
+reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off, long long n, RsSegs segs,
                             float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
                             long long param_off, float* __restrict__ grad_out, AdamArgs a, int do_adam,
                             const float* __restrict__ clip_coef, int ch_arrive, int ch_done, uint32_t epoch,
@@ -279,11 +306,13 @@ reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off
         const long long e0 = t * RS_TILE;
         const long long left = n - e0;
         const uint32_t bytes = (uint32_t)((left < RS_TILE ? left : RS_TILE) * 2);
+        int si = 0;
+        while (si + 1 < segs.n && e0 >= segs.start[si] + segs.len[si]) ++si;
+        const long long src_elem = segs.full[si] + (long long)rank * segs.len[si] + (e0 - segs.start[si]);
         mbar_arrive_expect_tx(&full[st], bytes * world);
         for (int s = 0; s < world; ++s) {
           const int p = (rank + s) % world;
-          bulk_g2s(ring + st * stage_bytes + p * RS_TILE_BYTES, peers.base[p] + grad_off + (((long long)rank * n + e0) << 1), bytes,
-                   &full[st]);
+          bulk_g2s(ring + st * stage_bytes + p * RS_TILE_BYTES, peers.base[p] + grad_off + (src_elem << 1), bytes, &full[st]);
         }
         if (++st == stages) { st = 0; ph ^= 1; }
       }
@@ -583,8 +612,41 @@ B200_API int b200_allgather_pull(const void* const* peer_ptrs, int rank, int wor
     B200_CUDA(cudaFuncSetAttribute(allgather_pull_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AG_SMEM));
     attr = true;
   }
-  allgather_pull_kernel<<<ctas, 32, AG_SMEM, (cudaStream_t)stream>>>(P, rank, world, shard_off, shard_bytes,
+  Segs sg;
+  memset(&sg, 0, sizeof(sg));
+  sg.n = 1;
+  sg.bytes[0] = shard_bytes;
+  allgather_pull_kernel<<<ctas, 32, AG_SMEM, (cudaStream_t)stream>>>(P, rank, world, shard_off, sg,
                                                                      (uint8_t*)out, wait_channel, wait_epoch);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// All-gather of a sharded unit with a segment table: segs = host array of nseg x {shard_off, full_off, bytes} (bytes,
+// multiples of 16; shard_off relative to shard_off_base).  Rank q's piece of segment i lands at out + full_off + q * bytes.
+B200_API int b200_allgather_pull_segs(const void* const* peer_ptrs, int rank, int world, long long shard_off_base,
+                                      const long long* segs, int nseg, void* out, int wait_channel, unsigned wait_epoch,
+                                      int ctas, void* stream) {
+  if (nseg < 1 || nseg > MAX_SEGS || shard_off_base % 16) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  Segs sg;
+  memset(&sg, 0, sizeof(sg));
+  sg.n = nseg;
+  for (int i = 0; i < nseg; ++i) {
+    sg.shard_off[i] = segs[3 * i]; sg.full_off[i] = segs[3 * i + 1]; sg.bytes[i] = segs[3 * i + 2];
+    if ((sg.shard_off[i] | sg.full_off[i] | sg.bytes[i]) % 16 || sg.bytes[i] <= 0) return B200_ERR_BAD_ARG;
+  }
+  if (ctas <= 0) ctas = 32;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA(cudaFuncSetAttribute(allgather_pull_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AG_SMEM));
+    attr = true;
+  }
+  allgather_pull_kernel<<<ctas, 32, AG_SMEM, (cudaStream_t)stream>>>(P, rank, world, shard_off_base, sg, (uint8_t*)out,
+                                                                     wait_channel, wait_epoch);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;
@@ -612,8 +674,51 @@ B200_API int b200_reduce_scatter_adamw(const void* const* peer_ptrs, int rank, i
     B200_CUDA(cudaFuncSetAttribute(reduce_scatter_adamw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 8 * RS_TILE_BYTES + 256));
     attr = true;
   }
+  RsSegs sg;
+  memset(&sg, 0, sizeof(sg));
+  sg.n = 1;
+  sg.len[0] = n;
   reduce_scatter_adamw_kernel<<<ctas, 160, smem, (cudaStream_t)stream>>>(
-      P, rank, world, grad_off, n, (float*)master, (float*)m, (float*)v, param_off, (float*)grad_out, a, do_adam,
+      P, rank, world, grad_off, n, sg, (float*)master, (float*)m, (float*)v, param_off, (float*)grad_out, a, do_adam,
+      (const float*)clip_coef, ch_arrive, ch_done, epoch, (uint32_t*)counter, stages);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// Same kernel for a unit whose shard is made of several pieces (see RsSegs): segs = host array of nseg x {start, full, len}
+// in ELEMENTS; start values ascending and contiguous, every len a multiple of 1024 (RS_TILE).  n = sum of len.
+B200_API int b200_reduce_scatter_adamw_segs(const void* const* peer_ptrs, int rank, int world, long long grad_off,
+                                            const long long* segs, int nseg, void* master, void* m, void* v, long long param_off,
+                                            void* grad_out, float lr, float beta1, float beta2, float eps, float weight_decay,
+                                            int step, float grad_scale, int do_adam, const void* clip_coef, int ch_arrive,
+                                            int ch_done, unsigned epoch, void* counter, int ctas, void* stream) {
+  if (nseg < 1 || nseg > MAX_SEGS || grad_off % 16 || param_off % 16) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  RsSegs sg;
+  memset(&sg, 0, sizeof(sg));
+  sg.n = nseg;
+  long long n = 0;
+  for (int i = 0; i < nseg; ++i) {
+    sg.start[i] = segs[3 * i]; sg.full[i] = segs[3 * i + 1]; sg.len[i] = segs[3 * i + 2];
+    if (sg.start[i] != n || sg.len[i] <= 0 || (sg.len[i] % RS_TILE) || (sg.full[i] % 8)) return B200_ERR_BAD_ARG;
+    n += sg.len[i];
+  }
+  AdamArgs a{lr, beta1, beta2, eps, weight_decay, 1.f - powf(beta1, (float)step), 1.f - powf(beta2, (float)step),
+             grad_scale};
+  if (ctas <= 0) ctas = 148;
+  int stages = 24576 / (world * RS_TILE_BYTES);
+  stages = stages < 1 ? 1 : (stages > 3 ? 3 : stages);
+  const int smem = stages * world * RS_TILE_BYTES + 128 + 128;
+  static bool attr = false;
+  if (!attr) {
+    B200_CUDA(cudaFuncSetAttribute(reduce_scatter_adamw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 8 * RS_TILE_BYTES + 256));
+    attr = true;
+  }
+  reduce_scatter_adamw_kernel<<<ctas, 160, smem, (cudaStream_t)stream>>>(
+      P, rank, world, grad_off, n, sg, (float*)master, (float*)m, (float*)v, param_off, (float*)grad_out, a, do_adam,
       (const float*)clip_coef, ch_arrive, ch_done, epoch, (uint32_t*)counter, stages);
   b200_count_launch();
   B200_CHECK_LAUNCH();
@@ -709,8 +814,12 @@ B200_API int b200_allreduce_tma(const void* const* peer_ptrs, int rank, int worl
     attr = true;
   }
   // the slices of this all-reduce start at `off`: rank r owns elements [r * slice, (r + 1) * slice)
+  RsSegs sg;
+  memset(&sg, 0, sizeof(sg));
+  sg.n = 1;
+  sg.len[0] = slice;
   reduce_scatter_adamw_kernel<<<ctas, 160, smem, (cudaStream_t)stream>>>(
-      P, rank, world, off, slice, nullptr, nullptr, nullptr, off + (long long)rank * slice * 2, nullptr, a, 2, nullptr, ch_arrive, ch_mid,
+      P, rank, world, off, slice, sg, nullptr, nullptr, nullptr, off + (long long)rank * slice * 2, nullptr, a, 2, nullptr, ch_arrive, ch_mid,
       epoch, (uint32_t*)counter, stages);
   b200_count_launch();
   B200_CHECK_LAUNCH();

@@ -54,12 +54,20 @@ struct Params {
   // keeps at byte offset ag_off + rank * shard_bytes of its symmetric buffer.  Warp 3 of every CTA pulls the peers'
   // shards with cp.async.bulk while the tensor cores already work on rows that are present; ag_ready[p] counts the
   // bytes of shard p that landed (reaches ag_expect when complete).
+  //
+  // The same gather warp also serves the FSDP weight gather (ag_mode 1-3): every rank keeps its dim-0 piece of a weight
+  // W[rows * world, cols] at byte offset ag_off of its symmetric buffer (ag_src_stride = 0) and the pieces are assembled in
+  // ag_full.  ag_mode says what the tensor cores must wait for:
+  //   0  A rows (activations, above)            1  B rows indexed by n  (forward:  D = X W^T, W is this GEMM's B operand)
+  //   2  B rows indexed by k (dgrad: D = dY W)  3  nothing: the buffer belongs to a LATER kernel of the stream ("carry")
   uint8_t* ag_peer[8];
   long long ag_off;
+  long long ag_src_stride;   // byte distance between consecutive ranks' pieces inside one source buffer (0: same offset everywhere)
+  long long ag_shard_bytes;  // bytes of one rank's piece
   uint8_t* ag_full;
   unsigned long long* ag_ready;
   unsigned long long ag_expect;
-  int ag_rows, ag_rank, ag_world;
+  int ag_rows, ag_rank, ag_world, ag_mode;
 };
 
 // GEMM -> reduce-scatter epilogue: every epilogue warp stages 32 rows x 64 columns (4 KB, 128-byte swizzled) and sends
@@ -88,8 +96,33 @@ __device__ __forceinline__ void bulk_s2g_g2(void* gdst, const void* smem_src, ui
 // with the fused all-gather, visit the 256-row tiles of my own shard first, then the shards in arrival order
 __device__ __forceinline__ int ag_rotate2(int m_t, const Params& p) {
   // start at the tile that holds the first row of my shard (a tile may span several small shards, or a shard several tiles)
+  if (p.ag_mode != 0) return m_t;
   const int start = (int)(((long long)p.ag_rank * p.ag_rows) / 256);
   return (m_t + start) % p.num_m_tiles;
+}
+// weight gather, forward: begin with the n-tiles made of my own rows of W
+__device__ __forceinline__ int ag_rotate_n(int n_t, const Params& p) {
+  if (p.ag_mode != 1) return n_t;
+  const int start = (int)(((long long)p.ag_rank * p.ag_rows) / BN);
+  return (n_t + start) % p.num_n_tiles;
+}
+// bounded wait until the pieces that hold rows [r0, r1] of the gathered matrix have landed
+__device__ __forceinline__ void ag_wait_rows(const Params& p, int r0, int r1) {
+  const int s_lo = r0 / p.ag_rows;
+  const int s_hi = min(r1 / p.ag_rows, p.ag_world - 1);
+  for (int sh = s_lo; sh <= s_hi; ++sh) {
+    if (sh == p.ag_rank) continue;
+    uint32_t spins = 0;
+    while (*reinterpret_cast<volatile unsigned long long*>(p.ag_ready + sh) < p.ag_expect) {
+      __nanosleep(32);
+      if (++spins > kSpinLimit2) {
+        printf("b200 gemm2: all-gather piece %d never arrived (block %d, mode %d)\n", sh, blockIdx.x, p.ag_mode);
+        __trap();
+      }
+    }
+  }
+  __threadfence();
+  asm volatile("fence.proxy.async;" ::: "memory");
 }
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -147,6 +180,16 @@ __device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr) {
   asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
 }
 
+// groups of GROUP_M n-tiles, m fastest: the order used when B arrives piece by piece (rows of B = n)
+__device__ __forceinline__ void tile_coords_nmajor(int tile, int num_m, int num_n, int& m_t, int& n_t) {
+  const int per_group = GROUP_M * num_m;
+  const int group = tile / per_group;
+  const int first_n = group * GROUP_M;
+  const int gn = min(GROUP_M, num_n - first_n);
+  const int r = tile - group * per_group;
+  n_t = first_n + (r % gn);
+  m_t = r / gn;
+}
 __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& m_t, int& n_t) {
   const int per_group = GROUP_M * num_n;
   const int group = tile / per_group;
@@ -217,35 +260,33 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         int m_t, n_t;
-        tile_coords(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
-        if (FUSE_AG) m_t = ag_rotate2(m_t, p);
+        if (FUSE_AG && p.ag_mode == 1) tile_coords_nmajor(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+        else tile_coords(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+        if (FUSE_AG) { m_t = ag_rotate2(m_t, p); n_t = ag_rotate_n(n_t, p); }
         const int m0 = m_t * 256 + (int)cta * BM;
         const int n0 = n_t * BN + (int)cta * BNH;
-        if (FUSE_AG && m0 < p.M) {
-          // rows [m0, m0 + BM) of A must have arrived: wait for the shard(s) they belong to
-          const int s_lo = m0 / p.ag_rows;
-          const int s_hi = min((m0 + BM - 1) / p.ag_rows, p.ag_world - 1);
-          for (int sh = s_lo; sh <= s_hi; ++sh) {
-            if (sh == p.ag_rank) continue;
-            uint32_t spins = 0;
-            while (*reinterpret_cast<volatile unsigned long long*>(p.ag_ready + sh) < p.ag_expect) {
-              __nanosleep(32);
-              if (++spins > kSpinLimit2) {
-                printf("b200 gemm2: all-gather shard %d never arrived (block %d)\n", sh, blockIdx.x);
-                __trap();
-              }
-            }
-          }
-          __threadfence();
-          asm volatile("fence.proxy.async;" ::: "memory");
-        }
-        for (int kb = 0; kb < num_k_blocks; ++kb) {
+        // rows [m0, m0 + BM) of A (mode 0) / rows [n0, n0 + BNH) of B (mode 1) must have arrived
+        if (FUSE_AG && p.ag_world > 1 && p.ag_mode == 0 && m0 < p.M) ag_wait_rows(p, m0, m0 + BM - 1);
+        if (FUSE_AG && p.ag_world > 1 && p.ag_mode == 1 && n0 < p.N) ag_wait_rows(p, n0, min(n0 + BNH, p.N) - 1);
+        // mode 2: the reduction runs over the rows of the gathered matrix; every tile starts in my own piece
+        const int kb_start = (FUSE_AG && p.ag_mode == 2) ? (int)(((long long)p.ag_rank * p.ag_rows) / BKE) % num_k_blocks : 0;
+        int k_piece = -1;
+        for (int kq = 0; kq < num_k_blocks; ++kq) {
+          int kb = kq + kb_start;
+          if (kb >= num_k_blocks) kb -= num_k_blocks;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           const uint32_t lbar = smem_u32(&full_bar[stage]) & PEER_MASK;  // the leader's barrier
           if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
           uint8_t* sa = smem_a + stage * A_BYTES;
           uint8_t* sb = smem_b + stage * B_BYTES;
           const int k0 = kb * BKE;
+          if (FUSE_AG && p.ag_mode == 2 && p.ag_world > 1) {
+            const int k1 = min(k0 + BKE, p.K) - 1;
+            if (k1 / p.ag_rows != k_piece || k0 / p.ag_rows != k_piece) {
+              ag_wait_rows(p, k0, k1);
+              k_piece = k1 / p.ag_rows;
+            }
+          }
           if (A_MN == 0) {
             tma_load_2d_2sm(sa, &tmap_a, lbar, k0, m0);
           } else {
@@ -296,7 +337,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   } else if (FUSE_AG && warp == 3) {
     // ================================ all-gather warp (every CTA moves its share of the chunks) ================================
     if (p.ag_world > 1 && elect_one()) {
-      const long long shard_bytes = (long long)p.ag_rows * p.K * 2;
+      const long long shard_bytes = p.ag_shard_bytes;
       const long long cps = (shard_bytes + AGG_CHUNK - 1) / AGG_CHUNK;
       const long long total = cps * (p.ag_world - 1);
       const long long n = (total > blockIdx.x) ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
@@ -308,7 +349,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         const long long o = c * AGG_CHUNK;
         const long long left = shard_bytes - o;
         bytes = (uint32_t)(left < AGG_CHUNK ? left : AGG_CHUNK);
-        src = p.ag_peer[peer] + p.ag_off + (long long)peer * shard_bytes + o;
+        src = p.ag_peer[peer] + p.ag_off + (long long)peer * p.ag_src_stride + o;
         dst = p.ag_full + (long long)peer * shard_bytes + o;
       };
       auto issue_load = [&](long long k) {
@@ -353,8 +394,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     if (FP8) alpha = __ldg(p.deq_a) * __ldg(p.deq_b);
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       int m_t, n_t;
-      tile_coords(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
-      if (FUSE_AG) m_t = ag_rotate2(m_t, p);
+      if (FUSE_AG && p.ag_mode == 1) tile_coords_nmajor(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+      else tile_coords(tile, p.num_m_tiles, p.num_n_tiles, m_t, n_t);
+      if (FUSE_AG) { m_t = ag_rotate2(m_t, p); n_t = ag_rotate_n(n_t, p); }
       const int row = m_t * 256 + (int)cta * BM + e * 32 + lane;
       const int n0 = n_t * BN;
       mbar_wait(&tmem_full[acc], acc_phase);
@@ -543,7 +585,7 @@ B200_API int b200_gemm2_bf16(const void* A, const void* B, void* C, const void* 
   if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BK, BNH);
   else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BK);
   if (rc) return rc;
-  Params p;
+  Params p = {};
   p.C = C; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.num_m_tiles = (M + 255) / 256;
   p.num_n_tiles = (N + BN - 1) / BN;
@@ -572,7 +614,7 @@ B200_API int b200_gemm2_e4m3(const void* A, const void* B, void* C, const void* 
   if (rc) return rc;
   rc = make_tmap_u8_2d(&tb, B, K, N, ldb, 128, BNH);
   if (rc) return rc;
-  Params p;
+  Params p = {};
   p.C = C; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = out_fp32; p.accumulate = accumulate;
   p.num_m_tiles = (M + 255) / 256;
   p.num_n_tiles = (N + BN - 1) / BN;
@@ -596,7 +638,7 @@ B200_API int b200_gemm2_bf16_allgather_a(const void* const* peer_ptrs, int rank,
   if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BK, BNH);
   else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BK);
   if (rc) return rc;
-  Params p;
+  Params p = {};
   p.C = C; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = 0; p.accumulate = 0;
   p.num_m_tiles = (M + 255) / 256; p.num_n_tiles = (N + BN - 1) / BN;
   p.deq_a = p.deq_b = nullptr;
@@ -604,9 +646,55 @@ B200_API int b200_gemm2_bf16_allgather_a(const void* const* peer_ptrs, int rank,
   for (int i = 0; i < 8; ++i) p.ag_peer[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
   p.ag_off = a_off; p.ag_full = (uint8_t*)a_full; p.ag_ready = (unsigned long long*)ready;
   p.ag_expect = epoch * (unsigned long long)rows * K * 2; p.ag_rows = rows; p.ag_rank = rank; p.ag_world = world;
+  p.ag_mode = 0; p.ag_shard_bytes = (long long)rows * K * 2; p.ag_src_stride = p.ag_shard_bytes;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (!b_mn_major) return launch<0, 0, 0, 1>(ta, tb, p, st);
   return launch<0, 1, 0, 1>(ta, tb, p, st);
+}
+
+// GEMM with a weight-gather job riding on it (FSDP2 parameter all-gather).  Same GEMM contract as
+// b200_gemm2_bf16.  Every rank keeps its dim-0 piece (piece_bytes) of a weight at byte offset src_off of its symmetric buffer;
+// warp 3 of every CTA pulls the peers' pieces into gathered + q * piece_bytes (q = owning rank; the caller has already put its own
+// piece there) while the tensor cores run.  mode 1: the weight is this GEMM's B operand, stored [N, K] (forward) - n-tiles wait
+// for the piece that holds their rows and the tile order starts in this rank's piece; mode 2: the weight is B stored [K, N]
+// (b_mn_major, dgrad) - k-blocks wait for their piece, every tile starts its reduction in this rank's piece; mode 3: the
+// gathered buffer is for a later kernel of the same stream, nothing waits.  piece_rows = rows of the weight per rank (modes 1, 2).
+// ready: 8 device counters (bytes landed per piece, monotonic across calls); expect = value that means "complete" for this call.
+B200_API int b200_gemm2_bf16_gather(const void* A, const void* B, void* C, const void* bias, int M, int N, int K, long long lda,
+                                    long long ldb, long long ldc, int a_mn_major, int b_mn_major, int out_fp32, int accumulate,
+                                    const void* const* peer_ptrs, int rank, int world, long long src_off, void* gathered,
+                                    long long piece_bytes, int piece_rows, int mode, void* ready, unsigned long long expect,
+                                    void* stream) {
+  using namespace b200;
+  using namespace b200::g2;
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if (world < 1 || world > 8 || mode < 1 || mode > 3 || piece_bytes <= 0 || (piece_bytes % 16) || (src_off % 16)) return B200_ERR_BAD_ARG;
+  if ((mode == 1 && (a_mn_major || b_mn_major)) || (mode == 2 && (a_mn_major || !b_mn_major))) return B200_ERR_BAD_ARG;
+  if (mode != 3 && piece_rows <= 0) return B200_ERR_BAD_ARG;
+  if ((lda % 8) || (ldb % 8) || (reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15) ||
+      (reinterpret_cast<uintptr_t>(gathered) & 15))
+    return B200_ERR_BAD_ARG;
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = make_tmap_bf16_2d(&ta, A, K, M, lda, BK, BM);
+  else rc = make_tmap_bf16_2d(&ta, A, M, K, lda, 64, BK);
+  if (rc) return rc;
+  if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BK, BNH);
+  else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  Params p = {};
+  p.C = C; p.bias = bias; p.M = M; p.N = N; p.K = K; p.ldc = ldc; p.out_fp32 = out_fp32; p.accumulate = accumulate;
+  p.num_m_tiles = (M + 255) / 256;
+  p.num_n_tiles = (N + BN - 1) / BN;
+  for (int i = 0; i < 8; ++i) p.ag_peer[i] = i < world ? (uint8_t*)peer_ptrs[i] : nullptr;
+  p.ag_off = src_off; p.ag_src_stride = 0; p.ag_shard_bytes = piece_bytes; p.ag_full = (uint8_t*)gathered;
+  p.ag_ready = (unsigned long long*)ready; p.ag_expect = expect; p.ag_rows = piece_rows > 0 ? piece_rows : 1;
+  p.ag_rank = rank; p.ag_world = world; p.ag_mode = mode;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!a_mn_major && !b_mn_major) return launch<0, 0, 0, 1>(ta, tb, p, st);
+  if (!a_mn_major && b_mn_major) return launch<0, 1, 0, 1>(ta, tb, p, st);
+  if (a_mn_major && b_mn_major) return launch<1, 1, 0, 1>(ta, tb, p, st);
+  return B200_ERR_UNSUPPORTED;
 }
 
 B200_API int b200_gemm2_bf16_scatter(const void* A, const void* B, const void* const* peer_ptrs, int rank, int world,
@@ -624,7 +712,7 @@ B200_API int b200_gemm2_bf16_scatter(const void* A, const void* B, const void* c
   if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, B, K, N, ldb, BK, BNH);
   else rc = make_tmap_bf16_2d(&tb, B, N, K, ldb, 64, BK);
   if (rc) return rc;
-  Params p;
+  Params p = {};
   p.C = nullptr; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = N; p.out_fp32 = 0; p.accumulate = 0;
   p.num_m_tiles = (M + 255) / 256; p.num_n_tiles = (N + BN - 1) / BN;
   p.deq_a = p.deq_b = nullptr;
@@ -668,7 +756,7 @@ B200_API int b200_gemm2_bf16_ulysses_scatter(const void* A, const void* W, const
   if (!b_mn_major) rc = make_tmap_bf16_2d(&tb, W, K, N, ldb, BK, BNH);
   else rc = make_tmap_bf16_2d(&tb, W, N, K, ldb, 64, BK);
   if (rc) return rc;
-  Params p;
+  Params p = {};
   p.C = nullptr; p.bias = nullptr; p.M = M; p.N = N; p.K = K; p.ldc = N; p.out_fp32 = 0; p.accumulate = 0;
   p.num_m_tiles = (M + 255) / 256; p.num_n_tiles = (N + BN - 1) / BN;
   p.deq_a = p.deq_b = nullptr;

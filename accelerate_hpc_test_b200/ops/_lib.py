@@ -39,6 +39,7 @@ _SIGNATURES = {
     "b200_quantize_e4m3": [P, L, I, I, P, P, L, P, L, P, P],
     "b200_gemm2_bf16": [P, P, P, P, I, I, I, L, L, L, I, I, I, I, P],
     "b200_gemm2_bf16_allgather_a": [P, I, I, L, P, I, P, P, I, I, L, L, I, P, ctypes.c_ulonglong, P],
+    "b200_gemm2_bf16_gather": [P, P, P, P, I, I, I, L, L, L, I, I, I, I, P, I, I, L, P, L, I, I, P, ctypes.c_ulonglong, P],
     "b200_gemm2_bf16_ulysses_scatter": [P, P, P, I, I, L, I, I, P, I, I, L, L, I, P],
     "b200_gemm2_bf16_scatter": [P, P, P, I, I, L, I, I, I, L, L, I, I, P],
     "b200_gemm_bf16_allgather_a": [P, I, I, L, P, I, P, P, I, I, L, L, I, P, ctypes.c_ulonglong, P],
@@ -82,6 +83,8 @@ _SIGNATURES = {
     "b200_comm_set_timeout_ms": [L],
     "b200_barrier_all": [P, I, I, I, U, P],
     "b200_allgather_pull": [P, I, I, L, L, P, I, U, I, P],
+    "b200_allgather_pull_segs": [P, I, I, L, P, I, P, I, U, I, P],
+    "b200_reduce_scatter_adamw_segs": [P, I, I, L, P, I, P, P, P, L, P, F, F, F, F, F, I, F, I, P, I, I, U, P, I, P],
     "b200_reduce_scatter_adamw": [P, I, I, L, L, P, P, P, L, P, F, F, F, F, F, I, F, I, P, I, I, U, P, I, P],
     "b200_allreduce": [P, I, I, L, L, I, F, I, I, U, P, I, P],
     "b200_allreduce_tma": [P, I, I, L, L, F, I, I, I, U, P, I, P],

@@ -217,3 +217,90 @@ def fault_injector() -> FaultInjector:
 def _reset_fault_injector():
     global _injector
     _injector = None
+
+
+# --------------------------------------------------------------------------- clock record for every timed number
+class ClockRecord:
+    """``nvidia-smi`` clocks / power / throttle reasons of one GPU sampled every 200 ms while a timed region runs.
+
+    Every kernel- or step-level number this repository reports carries ``summary()`` next to it, so a reader can
+    tell a power-capped (normal on a 1 kW part) run from a thermally throttled or clock-locked one::
+
+        with sample_clocks() as clk:
+            ms = timed(fn)
+        row = {"ms": ms, "clocks": clk.summary()}
+    """
+
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASONS = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+
+    def __init__(self, gpu_index: Optional[int] = None, period_ms: int = 200):
+        self.gpu_index = gpu_index
+        self.period_ms = period_ms
+        self._proc = None
+        self._lines: list = []
+        self._thread = None
+
+    def __enter__(self):
+        import subprocess
+        import threading
+
+        idx = self.gpu_index
+        if idx is None:
+            idx = torch.cuda.current_device() if _cuda() else 0
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            if vis:
+                try:
+                    idx = int(vis.split(",")[idx])
+                except (ValueError, IndexError):
+                    pass
+        try:
+            self._proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms",
+                                           str(self.period_ms), "-i", str(idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except (OSError, ValueError):
+            self._proc = None
+            return self
+
+        def pump():
+            for line in self._proc.stdout:
+                self._lines.append(line.strip())
+
+        self._thread = threading.Thread(target=pump, daemon=True)
+        self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        if self._proc is not None:
+            self._proc.terminate()
+            try:
+                self._proc.wait(timeout=5)
+            except Exception:  # noqa: BLE001
+                self._proc.kill()
+        return False
+
+    def summary(self) -> dict:
+        import statistics
+
+        if self._proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
+        sm, smax, power, seen = [], [], [], set()
+        for line in self._lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax.append(float(f[2]))
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(self.REASONS, f[4:8]):
+                if val.lower().startswith("active"):
+                    seen.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(seen)}
+
+
+def sample_clocks(gpu_index: Optional[int] = None) -> ClockRecord:
+    return ClockRecord(gpu_index)
