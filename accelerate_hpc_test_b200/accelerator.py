@@ -711,6 +711,13 @@ class Accelerator:
             if engine is not None:
                 for opt in optimizers_this_call or self._optimizers:
                     engine.bind_optimizer(opt)
+            remap = getattr(engine_model, "_b200_param_remap", None)
+            if remap:
+                # torch FSDP2 fallback: same repair the reference makes after fully_shard (accelerator.py:1690-1744)
+                for opt in optimizers_this_call or self._optimizers:
+                    for group in opt.optimizer.param_groups:
+                        group["params"] = [remap.get(id(q), q) for q in group["params"]]
+                    opt.optimizer.state.clear()
         # schedulers last: they need the prepared optimizers
         result = [self.prepare_scheduler(o) if (_is_scheduler(o) and not getattr(o, "_is_accelerate_prepared", False)) else o for o in result]
         for item in result:
@@ -789,11 +796,20 @@ class Accelerator:
             model = apply_tensor_parallel(model, self.torch_device_mesh["tp"], pc.tp_handler)
         if self.device.type == "cuda" and os.environ.get("ACCELERATE_B200_DDP", "1") != "0":
             from .parallel.ddp import B200DataParallel
+            from .parallel.symm import peer_domain
+            from .utils.dataclasses import DDPCommunicationHookType
 
             group = None
             if self.torch_device_mesh is not None and "dp_replicate" in (self.torch_device_mesh.mesh_dim_names or ()):
                 group = self.torch_device_mesh["dp_replicate"].get_group()
-            return B200DataParallel(model, process_group=group, handler=self.ddp_handler, gradient_state=self.gradient_state)
+            ok, why = peer_domain(group)
+            hook = getattr(self.ddp_handler, "comm_hook", None)
+            if hook in (DDPCommunicationHookType.POWER_SGD, DDPCommunicationHookType.BATCHED_POWER_SGD):
+                ok, why = False, f"comm_hook={hook} is a torch DDP communication hook"
+            if ok:
+                return B200DataParallel(model, process_group=group, handler=self.ddp_handler, gradient_state=self.gradient_state)
+            # groups that span hosts / more than 8 ranks, or torch-only comm hooks: the reference's own path (torch DDP over NCCL)
+            logger.warning(f"native data-parallel engine not used ({why}); falling back to torch DistributedDataParallel", main_process_only=True)
         device_ids, output_device = (None, None)
         if self.device.type == "cuda":
             device_ids, output_device = [self.local_process_index], self.local_process_index
@@ -841,8 +857,74 @@ class Accelerator:
             if "dp_replicate" in names:
                 replicate_group = mesh["dp_replicate"].get_group()
         plugin.set_auto_wrap_policy(model)
+        dp_group = None
+        if replicate_group is not None and mesh is not None:
+            names = mesh.mesh_dim_names or ()
+            flat = "dp_cp" if ("cp" in names or "sp" in names) else "dp"
+            try:
+                dp_group = mesh[flat].get_group()
+            except Exception:  # noqa: BLE001 - no flattened mesh of that name: keep the two-collective path
+                dp_group = None
+        fallback = self._torch_fsdp2_reason(model, plugin, dp_group if dp_group is not None else shard_group)
+        if fallback:
+            logger.warning(f"native sharded engine not used ({fallback}); falling back to torch FSDP2 (fully_shard)", main_process_only=True)
+            return self._wrap_torch_fsdp2(model, plugin, mesh)
         return B200ShardedModule(model, plugin=plugin, device=self.device, shard_group=shard_group, replicate_group=replicate_group,
-                                 gradient_state=self.gradient_state, shard_group_is_world=(mesh is None))
+                                 gradient_state=self.gradient_state, shard_group_is_world=(mesh is None), dp_group=dp_group)
+
+    def _torch_fsdp2_reason(self, model, plugin, group) -> str:
+        """Why the native sharded engine cannot take this job ('' if it can).  It needs one NVLink domain (<= 8 ranks on one
+        host) and bf16 compute on CUDA; everything else runs the reference's path: torch FSDP2 over NCCL."""
+        if os.environ.get("ACCELERATE_B200_FSDP", "1") == "0":
+            return "ACCELERATE_B200_FSDP=0"
+        if self.device.type != "cuda":
+            return ""  # the gloo oracle path of the native engine
+        from .parallel.symm import peer_domain
+
+        ok, why = peer_domain(group)
+        if not ok:
+            return why
+        first = next((p for p in model.parameters()), None)
+        pol = plugin.mixed_precision_policy
+        bf16 = first is not None and (first.dtype == torch.bfloat16 or (pol is not None and getattr(pol, "param_dtype", None) == torch.bfloat16))
+        if not bf16:
+            return f"{first.dtype if first is not None else 'no'} parameters without a bf16 mixed-precision policy"
+        if getattr(plugin, "cpu_offload", False) and getattr(getattr(plugin, "cpu_offload", None), "offload_params", True):
+            return "CPU offload of parameters"
+        return ""
+
+    def _wrap_torch_fsdp2(self, model, plugin, mesh):
+        """The reference's FSDP2 path (utils/fsdp_utils.py:621-737): ``fully_shard`` per auto-wrapped module, then the root."""
+        from torch.distributed.fsdp import CPUOffloadPolicy, MixedPrecisionPolicy, fully_shard
+
+        kw = {"reshard_after_forward": plugin.effective_reshard_after_forward}
+        pol = plugin.mixed_precision_policy
+        if pol is not None:
+            kw["mp_policy"] = pol if isinstance(pol, MixedPrecisionPolicy) else MixedPrecisionPolicy(
+                param_dtype=getattr(pol, "param_dtype", None), reduce_dtype=getattr(pol, "reduce_dtype", None),
+                output_dtype=getattr(pol, "output_dtype", None))
+        if getattr(plugin, "cpu_offload", False):
+            kw["offload_policy"] = CPUOffloadPolicy()
+        if mesh is not None:
+            names = mesh.mesh_dim_names or ()
+            dims = tuple(n for n in ("dp_replicate", "dp_shard_cp") if n in names or n == "dp_shard_cp" and ("dp_shard" in names or "cp" in names))
+            if dims:
+                kw["mesh"] = mesh[dims] if len(dims) > 1 else mesh[dims[0]]
+        if plugin.activation_checkpointing:
+            from .parallel.fsdp import apply_activation_checkpointing
+
+            apply_activation_checkpointing(model, plugin)
+        model = model.to(self.device)
+        before = {name: p for name, p in model.named_parameters()}
+        for sub in list(model.modules())[::-1]:
+            if sub is not model and plugin.should_wrap(sub):
+                fully_shard(sub, **kw)
+        fully_shard(model, **kw)
+        # fully_shard replaced every Parameter by a DTensor one: optimizers built on the old objects are re-pointed in prepare()
+        after = dict(model.named_parameters())
+        model._b200_param_remap = {id(before[n]): after[n] for n in before if n in after}
+        model._b200_torch_fsdp2 = True
+        return model
 
     def prepare_data_loader(self, data_loader: torch.utils.data.DataLoader, device_placement=None, slice_fn_for_dispatch=None):
         if getattr(data_loader, "_is_accelerate_prepared", False):

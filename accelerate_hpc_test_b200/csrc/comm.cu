@@ -266,12 +266,30 @@ static constexpr int RS_TILE = 1024;           // elements per tile (128 consume
 static constexpr int RS_TILE_BYTES = RS_TILE * 2;
 
 // Element-unit segment table for the reduce-scatter: piece i of my shard covers shard elements [start, start + len) and is
-// the sum over ranks of gradient elements [full + rank * len, full + (rank + 1) * len) of every rank's flat gradient.
-// With more than one segment every len is a multiple of RS_TILE, so a tile never straddles two segments.
+// the sum over ranks of gradient elements [full + slice * len, full + (slice + 1) * len) of every rank's flat gradient
+// (slice = the index of the pieces I own: my rank, or my rank inside the shard group under hybrid sharding, where the
+// `world` ranks being summed are shard x replicate).  Tiles are enumerated per segment, so len only has to be a multiple of 8.
 struct RsSegs {
   long long start[MAX_SEGS], full[MAX_SEGS], len[MAX_SEGS];
-  int n;
+  int n, slice;
 };
+__device__ __forceinline__ long long rs_total_tiles(const RsSegs& sg) {
+  long long t = 0;
+  for (int i = 0; i < sg.n; ++i) t += (sg.len[i] + RS_TILE - 1) / RS_TILE;
+  return t;
+}
+// tile t -> (segment, first element inside the segment, elements in the tile)
+__device__ __forceinline__ void rs_locate(const RsSegs& sg, long long t, int& si, long long& in_seg, int& cnt) {
+  si = 0;
+  for (; si + 1 < sg.n; ++si) {
+    const long long c = (sg.len[si] + RS_TILE - 1) / RS_TILE;
+    if (t < c) break;
+    t -= c;
+  }
+  in_seg = t * RS_TILE;
+  const long long left = sg.len[si] - in_seg;
+  cnt = (int)(left < RS_TILE ? left : RS_TILE);
+}
 
 __global__ void __launch_bounds__(160)
 reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off, long long n, RsSegs segs,
@@ -295,7 +313,7 @@ reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off
   if (blockIdx.x == 0) signal_all(peers, rank, world, ch_arrive, epoch);
   wait_all(peers, rank, world, ch_arrive, epoch);  // ends with __syncthreads(): barrier inits are visible
 
-  const long long ntiles = (n + RS_TILE - 1) / RS_TILE;
+  const long long ntiles = rs_total_tiles(segs);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0) {
     if (lane == 0) {
@@ -303,12 +321,11 @@ reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off
       uint32_t ph = 0;
       for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
         mbar_wait(&empty[st], ph ^ 1);
-        const long long e0 = t * RS_TILE;
-        const long long left = n - e0;
-        const uint32_t bytes = (uint32_t)((left < RS_TILE ? left : RS_TILE) * 2);
-        int si = 0;
-        while (si + 1 < segs.n && e0 >= segs.start[si] + segs.len[si]) ++si;
-        const long long src_elem = segs.full[si] + (long long)rank * segs.len[si] + (e0 - segs.start[si]);
+        int si, cnt;
+        long long in_seg;
+        rs_locate(segs, t, si, in_seg, cnt);
+        const uint32_t bytes = (uint32_t)(cnt * 2);
+        const long long src_elem = segs.full[si] + (long long)segs.slice * segs.len[si] + in_seg;
         mbar_arrive_expect_tx(&full[st], bytes * world);
         for (int s = 0; s < world; ++s) {
           const int p = (rank + s) % world;
@@ -325,7 +342,11 @@ reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off
     uint32_t ph = 0;
     for (long long t = blockIdx.x; t < ntiles; t += gridDim.x) {
       mbar_wait(&full[st], ph);
-      const long long e0 = t * RS_TILE + ct * 8;
+      int si, cnt;
+      long long in_seg;
+      rs_locate(segs, t, si, in_seg, cnt);
+      const bool valid = ct * 8 < cnt;
+      const long long e0 = valid ? segs.start[si] + in_seg + ct * 8 : n;
       float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       if (e0 < n) {
         for (int p = 0; p < world; ++p) {
@@ -678,6 +699,7 @@ B200_API int b200_reduce_scatter_adamw(const void* const* peer_ptrs, int rank, i
   memset(&sg, 0, sizeof(sg));
   sg.n = 1;
   sg.len[0] = n;
+  sg.slice = rank;
   reduce_scatter_adamw_kernel<<<ctas, 160, smem, (cudaStream_t)stream>>>(
       P, rank, world, grad_off, n, sg, (float*)master, (float*)m, (float*)v, param_off, (float*)grad_out, a, do_adam,
       (const float*)clip_coef, ch_arrive, ch_done, epoch, (uint32_t*)counter, stages);
@@ -687,8 +709,9 @@ B200_API int b200_reduce_scatter_adamw(const void* const* peer_ptrs, int rank, i
 }
 
 // Same kernel for a unit whose shard is made of several pieces (see RsSegs): segs = host array of nseg x {start, full, len}
-// in ELEMENTS; start values ascending and contiguous, every len a multiple of 1024 (RS_TILE).  n = sum of len.
-B200_API int b200_reduce_scatter_adamw_segs(const void* const* peer_ptrs, int rank, int world, long long grad_off,
+// in ELEMENTS; start values ascending and contiguous, every len a multiple of 8.  n = sum of len.  slice = index of the pieces
+// this rank owns (== rank, except under hybrid sharding where `world` spans shard x replicate and slice is the shard rank).
+B200_API int b200_reduce_scatter_adamw_segs(const void* const* peer_ptrs, int rank, int world, int slice, long long grad_off,
                                             const long long* segs, int nseg, void* master, void* m, void* v, long long param_off,
                                             void* grad_out, float lr, float beta1, float beta2, float eps, float weight_decay,
                                             int step, float grad_scale, int do_adam, const void* clip_coef, int ch_arrive,
@@ -700,10 +723,11 @@ B200_API int b200_reduce_scatter_adamw_segs(const void* const* peer_ptrs, int ra
   RsSegs sg;
   memset(&sg, 0, sizeof(sg));
   sg.n = nseg;
+  sg.slice = slice;
   long long n = 0;
   for (int i = 0; i < nseg; ++i) {
     sg.start[i] = segs[3 * i]; sg.full[i] = segs[3 * i + 1]; sg.len[i] = segs[3 * i + 2];
-    if (sg.start[i] != n || sg.len[i] <= 0 || (sg.len[i] % RS_TILE) || (sg.full[i] % 8)) return B200_ERR_BAD_ARG;
+    if (sg.start[i] != n || sg.len[i] <= 0 || (sg.len[i] % 8) || (sg.full[i] % 8)) return B200_ERR_BAD_ARG;
     n += sg.len[i];
   }
   AdamArgs a{lr, beta1, beta2, eps, weight_decay, 1.f - powf(beta1, (float)step), 1.f - powf(beta2, (float)step),
@@ -818,6 +842,7 @@ B200_API int b200_allreduce_tma(const void* const* peer_ptrs, int rank, int worl
   memset(&sg, 0, sizeof(sg));
   sg.n = 1;
   sg.len[0] = slice;
+  sg.slice = rank;
   reduce_scatter_adamw_kernel<<<ctas, 160, smem, (cudaStream_t)stream>>>(
       P, rank, world, off, slice, sg, nullptr, nullptr, nullptr, off + (long long)rank * slice * 2, nullptr, a, 2, nullptr, ch_arrive, ch_mid,
       epoch, (uint32_t*)counter, stages);

@@ -339,6 +339,42 @@ class LlamaForCausalLM(nn.Module):
         # value = global mean; gradient flows through the local part only (the other ranks own theirs)
         return CausalLMOutput(loss=part + (whole - part.detach()))
 
+    # ------------------------------------------------------------------ pipeline-parallel inference
+    def pipeline_blocks(self):
+        """The model as an ordered list of blocks for ``prepare_pippy`` (inference.py): token embedding, one block per decoder
+        layer, then final norm + LM head.  What travels between blocks is ``(x, residual, meta)`` with ``meta = [B, S]``, so a
+        stage that starts in the middle can rebuild positions and the RoPE tables on its own device."""
+        from ..inference import Block
+
+        core = self.model
+
+        def embed(input_ids, **_):
+            B, S = input_ids.shape
+            x = F.embedding(input_ids, core.embed_tokens.weight).view(B * S, -1)
+            meta = torch.tensor([B, S], dtype=torch.int64, device=x.device)
+            return x, torch.zeros_like(x), meta
+
+        def layer_fn(layer, first):
+            def run(x, residual, meta):
+                B, S = int(meta[0]), int(meta[1])
+                pos = torch.arange(S, device=x.device).unsqueeze(0).expand(B, S)
+                rope = core.rope(pos, S)
+                y, res = layer(x, None if first else residual, rope, B, S)
+                return y, res, meta
+
+            return run
+
+        def head(x, residual, meta):
+            B, S = int(meta[0]), int(meta[1])
+            h, _ = core.norm(x, residual)
+            return (self.lm_head(h).view(B, S, -1),)
+
+        blocks = [Block("model.embed_tokens", embed, core.embed_tokens)]
+        for i, layer in enumerate(core.layers):
+            blocks.append(Block(f"model.layers.{i}", layer_fn(layer, i == 0), layer))
+        blocks.append(Block("model.norm", head, [core.norm, self.lm_head]))
+        return blocks
+
     # ------------------------------------------------------------------ transformers interchange
     def hf_state_dict(self) -> dict:
         """State dict under transformers' parameter names (q/k/v and gate/up un-fused)."""

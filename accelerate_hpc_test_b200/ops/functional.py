@@ -94,11 +94,43 @@ def gemm(
         raise TypeError("b200 gemm expects bf16 operands")
     if out_dtype not in (BF16, torch.float32):
         raise TypeError("b200 gemm writes bf16 or fp32")
+    # a dim-0-sharded FSDP weight whose peers' rows have not been fetched yet (parallel/fsdp.py): this GEMM fetches them
+    job = _pending_gather(b)
+    if isinstance(b, torch.nn.Parameter) and getattr(b, "_b200_fsdp_unit", None) is not None:
+        b._b200_gemm_b_seen = True  # from the next step on the engine leaves this weight's gather to the GEMMs
+    a_job = _pending_gather(a)
+    if a_job is not None:
+        a_job.materialize()
     a = _rowmajor2d(a)
     b = _rowmajor2d(b)
     if bias is not None:
         bias = bias.to(BF16).contiguous()
-    if _GEMM_2CTA and max_ctas == 0 and M > 128:
+    two_cta = _GEMM_2CTA and max_ctas == 0 and M > 128
+    if job is not None and not (two_cta and not a_mn_major):
+        job.materialize()
+        job = None
+    mode = 0
+    if job is not None:
+        mode = 2 if b_mn_major else 1  # B rows are the reduction dimension (dgrad) / the output columns (forward)
+    elif two_cta and not (a_mn_major and not b_mn_major) and _CARRY_SOURCES and 2.0 * M * N * K >= 4e9:
+        # nothing of its own to fetch: carry the next weight the stream will need (backward: the weight-gradient GEMMs)
+        for src in _CARRY_SOURCES:
+            job = src.pop_carry_job()
+            if job is not None:
+                mode = 3
+                break
+    if mode:
+        peers, rank, world, src_off, dst, piece_bytes, rows, ready, expect = job.launch_args()
+        check(
+            lib.b200_gemm2_bf16_gather(
+                ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, a.stride(0), b.stride(0), out.stride(0),
+                int(a_mn_major), int(b_mn_major), int(out_dtype == torch.float32), int(accumulate),
+                peers, rank, world, src_off, dst, piece_bytes, rows, mode, ready, expect, cur_stream(),
+            ),
+            "gemm2_bf16_gather",
+        )
+        return out
+    if two_cta:
         # SM-pair kernel (cta_group::2, 256x256 tiles, 6 stages): the default for plain GEMMs
         check(
             lib.b200_gemm2_bf16(
@@ -120,6 +152,30 @@ def gemm(
 
 
 _GEMM_2CTA = os.environ.get("ACCELERATE_B200_GEMM_2CTA", "1") != "0"
+_CARRY_SOURCES: list = []  # sharded engines that may hand a weight gather to any big GEMM (see B200ShardedModule.pop_carry_job)
+
+
+def _pending_gather(t):
+    job = getattr(t, "_b200_ag", None)
+    return job if (job is not None and job.pending) else None
+
+
+def register_carry_source(engine) -> None:
+    if engine not in _CARRY_SOURCES:
+        _CARRY_SOURCES.append(engine)
+
+
+def unregister_carry_source(engine) -> None:
+    if engine in _CARRY_SOURCES:
+        _CARRY_SOURCES.remove(engine)
+
+
+def materialize(t: torch.Tensor) -> torch.Tensor:
+    """Make sure a sharded-engine weight is completely gathered before an op other than the GEMM reads it."""
+    job = _pending_gather(t)
+    if job is not None:
+        job.materialize()
+    return t
 
 
 def deliver_weight_grad(weight: torch.Tensor, compute):
@@ -135,8 +191,12 @@ def deliver_weight_grad(weight: torch.Tensor, compute):
     if buf is None:
         return compute(None, False)
     g = weight.grad
-    acc = bool(getattr(weight, "_b200_has_partial", False)) or (g is not None and g.data_ptr() == buf.data_ptr())
+    # accumulate when an earlier micro-batch (no_sync) or an earlier use of a shared parameter (tied embeddings) already
+    # wrote this step's gradient into the buffer
+    acc = (bool(getattr(weight, "_b200_has_partial", False)) or bool(getattr(weight, "_b200_grad_seen", False))
+           or (g is not None and g.data_ptr() == buf.data_ptr()))
     compute(buf, acc)
+    weight._b200_grad_seen = True
     weight._b200_grad_hook(weight)
     return None
 
@@ -150,6 +210,7 @@ class _LinearFn(torch.autograd.Function):
         x2 = x.reshape(-1, shp[-1])
         y = gemm(x2, weight, bias=bias)
         ctx.save_for_backward(x2, weight)
+        ctx.weight_ref = weight  # the Parameter object itself: the engines hang their hand-off attributes on it
         ctx.has_bias = bias is not None
         ctx.in_shape = shp
         return y.view(*shp[:-1], weight.shape[0])
@@ -157,6 +218,7 @@ class _LinearFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         x2, weight = ctx.saved_tensors
+        weight = ctx.weight_ref
         dy2 = dy.reshape(-1, dy.shape[-1])
         if dy2.dtype != weight.dtype:
             dy2 = dy2.to(weight.dtype)
@@ -346,6 +408,7 @@ class _EmbeddingFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, ids, table):
         flat = ids.reshape(-1).contiguous()
+        materialize(table)
         V, H = table.shape
         if not _on_gpu(table):
             out = table[flat]

@@ -70,7 +70,22 @@ class B200DataParallel(nn.Module):
             for t in list(module.parameters()) + (list(module.buffers()) if self.handler.broadcast_buffers else []):
                 torch.distributed.broadcast(t.data, src=torch.distributed.get_global_rank(self.process_group, 0), group=self.process_group)
         wire = self.handler.comm_hook
+        if wire in (DDPCommunicationHookType.POWER_SGD, DDPCommunicationHookType.BATCHED_POWER_SGD):
+            raise NotImplementedError(
+                f"comm_hook={wire} (low-rank gradient compression) is not implemented by the native data-parallel engine: its "
+                "all-reduce already runs at NVLink speed inside one node. Use comm_hook NO / BF16, or set ACCELERATE_B200_DDP=0 to "
+                "run torch DistributedDataParallel with the PowerSGD hook."
+            )
+        if wire == DDPCommunicationHookType.FP16:
+            import warnings
+
+            warnings.warn("comm_hook=FP16: the native engine reduces 16-bit gradients as bfloat16 (same bytes on the wire, no "
+                          "overflow handling needed); pass BF16 to silence this.")
         self._wire_dtype = {DDPCommunicationHookType.BF16: torch.bfloat16, DDPCommunicationHookType.FP16: torch.bfloat16}.get(wire)
+        # a parameter registered in several modules (tied embeddings) is handed one gradient per use
+        self._uses: dict[int, int] = {}
+        for _, q in module.named_parameters(remove_duplicate=False):
+            self._uses[id(q)] = self._uses.get(id(q), 0) + 1
         total_bytes = sum(p.numel() * (2 if (self._wire_dtype or p.dtype) == torch.bfloat16 else 4) for p in params)
         if workspace is None:
             workspace = SymmetricWorkspace(self.process_group, total_bytes + 64 * 2**20, self.device)
@@ -139,25 +154,36 @@ class B200DataParallel(nn.Module):
             b.pending = len(b.params)
             b.launched = False
             b._ready = set()
+            b._deliveries = {}
         torch.autograd.Variable._execution_engine.queue_callback(self._finish_backward)
 
     def _native_grad_ready(self, p):
         """Called by native ops after they wrote (or accumulated) dW into ``p._b200_grad_buf``."""
         self._begin_backward()
         p.grad = p._b200_grad_buf
-        self._mark_ready(p)
+        b, _ = self._param_slot[id(p)]
+        got = b._deliveries.get(id(p), 0) + 1
+        b._deliveries[id(p)] = got
+        if got >= self._uses.get(id(p), 1):  # the bucket may only be reduced once every use has added its share
+            self._mark_ready(p)
 
     def _autograd_grad_ready(self, p):
         """Post-accumulate hook: gradients produced by foreign ops are moved into the bucket view."""
         self._begin_backward()
         view = p._b200_bucket_view
         g = p.grad
-        if g is not None and g.data_ptr() != view.data_ptr():
-            if getattr(p, "_b200_has_partial", False):
+        if g is None:
+            return  # a native op delivered this gradient straight into the bucket (and reported it)
+        if g.data_ptr() != view.data_ptr():
+            if view.dtype != p.dtype:
+                # compressed wire (bf16 bucket, fp32 parameter): p.grad keeps accumulating in full precision across
+                # no_sync micro-steps, the bucket is always a fresh cast of that running total
+                F.scale_cast(g.contiguous().view(-1), view.view(-1), 1.0) if g.dtype in (torch.float32, torch.bfloat16) else view.copy_(g)
+            elif getattr(p, "_b200_has_partial", False):
                 view.add_(g.to(view.dtype))
+                p.grad = view
             else:
                 F.scale_cast(g.contiguous().view(-1), view.view(-1), 1.0) if g.dtype in (torch.float32, torch.bfloat16) else view.copy_(g)
-            if view.dtype == p.dtype:
                 p.grad = view
         self._mark_ready(p)
 
@@ -190,6 +216,9 @@ class B200DataParallel(nn.Module):
     def _finish_backward(self):
         self._callback_queued = False
         sync = self._sync_now()
+        for b in self._buckets:
+            for p in b.params:
+                p._b200_grad_seen = False  # per-backward flag of ops.functional.deliver_weight_grad
         for b in self._buckets:
             if b.pending > 0:
                 # parameters that took no part in this backward contribute zeros

@@ -3,29 +3,37 @@
 The reference hands the model to torch's ``fully_shard`` (reference src/accelerate/utils/fsdp_utils.py:
 621-737) and lets FSDP2 issue ``ncclAllGather`` / ``ncclReduceScatter`` per wrapped module.  Here:
 
-* every wrapped unit (the modules picked by the plugin's auto-wrap policy, plus one unit per large
-  leftover tensor group) owns a flat bf16 parameter buffer; each rank keeps ``1/world`` of it — its
-  *shard* — in the symmetric workspace, together with local fp32 master / Adam moments;
-* **all-gather** is a *pull* kernel: a rank reads its peers' shards over NVLink into a pooled full
-  buffer, on the communication stream, one unit ahead of the compute stream (forward and backward
-  prefetch).  No rank-to-rank handshake is needed per gather: shards only change in the optimizer
-  step, which ends with one cross-rank barrier;
-* **reduce-scatter + AdamW** is one kernel: when a unit's backward is complete, each rank sums its
-  shard of the 8 flat gradient buffers through NVLink loads, applies AdamW to its fp32 shard and
-  writes the new bf16 shard — overlapped with the backward of the next unit.  If gradients must
-  survive until ``optimizer.step()`` (gradient clipping, foreign optimizers) the same kernel only
-  reduces (``do_adam=0``) and the sharded update runs at ``step()``;
-* native weight-gradient GEMMs write straight into the unit's flat gradient buffer.
+* **Per-parameter dim-0 shards** (the FSDP2 layout).  Every wrapped unit (the modules picked by the plugin's
+  auto-wrap policy, plus one unit per large leftover tensor) keeps, for each of its parameters, rows
+  ``[r * N/W, (r+1) * N/W)`` on rank ``r`` (``W`` = shard-group size; parameters whose first dimension does not
+  divide are cut as flat 1-D tensors).  The pieces of one unit are concatenated into one *shard* buffer in
+  symmetric (peer-mapped) memory, next to local fp32 master weights and optimizer moments.  In the gathered
+  ("full") buffer every parameter sits in its natural ``[N, K]`` layout, rank ``q``'s piece at row ``q * N/W``.
+* **All-gather fused into GEMMs.**  A weight that the model consumes as the B operand of the tcgen05 GEMM is not
+  gathered by a separate collective: the GEMM that first needs it pulls the peers' row blocks over NVLink with a
+  gather warp while its tensor cores start on this rank's own rows (forward, n-gated), and in backward the
+  weight-gradient GEMMs carry the gather of the next weights the stream will need (dgrad GEMMs would have to wait
+  for the whole reduction dimension, so their weights travel one GEMM ahead).  Everything else (norm weights,
+  biases, parameters other ops consume) is gathered by a TMA pull kernel on a side stream one unit ahead.
+* **Reduce-scatter + optimizer in one kernel**: when a unit's backward is complete each rank sums its pieces of
+  all ranks' flat gradients through NVLink loads, applies AdamW to its fp32 shard and writes the new bf16 shard.
+  With hybrid sharding (``dp_replicate`` x ``dp_shard``) the same kernel reads the pieces of *all* data-parallel
+  ranks, so the replicate all-reduce needs no second collective and the fused update stays on.  If gradients must
+  survive until ``optimizer.step()`` (gradient clipping, any optimizer other than single-group AdamW) the kernel
+  only reduces and the update runs at ``step()`` — for foreign optimizers through shard-shaped parameter views
+  handed to the user's own optimizer (the reference's ``data_ptr`` swap, accelerator.py:1690-1744).
+* Native weight-gradient GEMMs write straight into the unit's flat gradient buffer.
 
 On CPU (gloo) the same engine runs with c10d collectives — that path is the test oracle.
-Checkpoint layout: ``pytorch_model_fsdp_{i}/`` and ``optimizer_{i}/`` directories (SHARDED) or
-``pytorch_model_fsdp.bin`` / ``optimizer.bin`` (FULL), as in reference utils/fsdp_utils.py:103-335.
+Checkpoints: ``pytorch_model_fsdp_{i}/`` and ``optimizer_{i}/`` are ``torch.distributed.checkpoint`` directories
+with one ``Shard(0)`` DTensor per parameter (interchangeable with the reference's, utils/fsdp_utils.py:147-158,
+270-278); ``pytorch_model_fsdp.bin`` / ``optimizer.bin`` for FULL_STATE_DICT.
 """
 
 from __future__ import annotations
 
 import contextlib
-import json
+import ctypes
 import os
 from typing import Optional
 
@@ -34,9 +42,11 @@ import torch.nn as nn
 
 from ..ops import functional as F
 from ..utils.constants import FSDP_MODEL_NAME, OPTIMIZER_NAME
+from ..utils.diagnostics import shadow_check
 from ..utils.other import get_module_children_bottom_up
 
 BF16 = torch.bfloat16
+SEGS_PER_LAUNCH = 32  # csrc/comm.cu MAX_SEGS
 
 
 def apply_activation_checkpointing(model: nn.Module, plugin) -> None:
@@ -81,7 +91,83 @@ class _Pool:
         self.free.append(idx)
 
 
-from ..utils.diagnostics import shadow_check
+class _Seg:
+    """One parameter of a unit: where its per-rank piece sits in the shard and where it sits in the gathered buffer."""
+
+    __slots__ = ("param", "name", "shape", "numel", "rows", "piece", "full_off", "shard_off", "job")
+
+    def __init__(self, param, name):
+        self.param = param
+        self.name = name
+        self.shape = tuple(param.shape)
+        self.numel = param.numel()
+        self.rows = 0        # rows per rank when the parameter is cut along dim 0 (0: cut as a flat tensor)
+        self.piece = 0       # elements per rank
+        self.full_off = 0    # element offset of the parameter in the gathered buffer
+        self.shard_off = 0   # element offset of my piece in the shard
+        self.job = None      # _GatherJob when this weight's gather rides on GEMMs
+
+    def layout(self, world: int):
+        d0 = self.shape[0] if len(self.shape) >= 2 else 0
+        row_len = self.numel // d0 if d0 else 0
+        if d0 and d0 % world == 0 and ((d0 // world) * row_len) % 8 == 0:
+            self.rows = d0 // world
+            self.piece = self.rows * row_len
+        else:
+            self.rows = 0
+            self.piece = ((self.numel + world - 1) // world + 7) // 8 * 8
+        return self.piece
+
+    @property
+    def piece_shape(self):
+        """Shape of my piece when it is a dim-0 block of the parameter (rows > 0, or an evenly cut 1-D tensor)."""
+        if self.rows:
+            return (self.rows,) + self.shape[1:]
+        return None
+
+
+class _GatherJob:
+    """Gather of one dim-0-sharded weight performed by the gather warp of a GEMM (ops.functional.gemm)."""
+
+    __slots__ = ("engine", "unit", "seg", "pending", "queued", "calls", "ready", "src_off", "piece_bytes", "rows")
+
+    def __init__(self, engine, unit, seg):
+        self.engine, self.unit, self.seg = engine, unit, seg
+        self.pending = False   # the gathered buffer does not hold the peers' pieces yet
+        self.queued = False    # waiting in the engine's carry queue
+        self.calls = 0         # completed gathers: the byte counters are monotonic
+        self.ready = torch.zeros(8, dtype=torch.int64, device=engine.device)
+        self.src_off = unit.shard_off + seg.shard_off * 2
+        self.piece_bytes = seg.piece * 2
+        self.rows = seg.rows
+
+    # called by ops.functional.gemm ---------------------------------------------------------------
+    def launch_args(self):
+        """(peer array, rank, world, src_off, dst pointer, piece_bytes, rows, ready pointer, expect)."""
+        e = self.engine
+        self.calls += 1
+        self.pending = False
+        if self.queued:
+            self.queued = False
+            try:
+                e._carry.remove(self)
+            except ValueError:
+                pass
+        dst = self.unit.full.data_ptr() + self.seg.full_off * 2  # (the parameter's .data is only re-pointed at unshard time)
+        return (e._ag_peers, e.rank, e.world, self.src_off, ctypes.c_void_p(dst), self.piece_bytes, self.rows,
+                ctypes.c_void_p(self.ready.data_ptr()), self.calls * self.piece_bytes)
+
+    def materialize(self):
+        """Stand-alone gather on the current stream, for consumers that are not a GEMM."""
+        if self.pending:
+            self.engine._pull_segments(self.unit, [self.seg], stream=None)
+            self.pending = False
+            if self.queued:
+                self.queued = False
+                try:
+                    self.engine._carry.remove(self)
+                except ValueError:
+                    pass
 
 
 class _Unit:
@@ -92,29 +178,49 @@ class _Unit:
         self.module = module
         self.params = params
         self.param_names = names
-        self.offsets = []
-        n = 0
-        for p in params:
-            self.offsets.append(n)
-            n += (p.numel() + 7) // 8 * 8
-        self.numel = n
+        self.segs = [_Seg(p, n) for p, n in zip(params, names)]
+        self.offsets = []          # element offset of every parameter in the gathered buffer
+        self.numel = sum(p.numel() for p in params)
         self.padded = 0
         self.shard_numel = 0
-        self.full: Optional[torch.Tensor] = None  # pooled full bf16 buffer while unsharded
+        self.full: Optional[torch.Tensor] = None  # pooled full buffer while unsharded
         self.grad: Optional[torch.Tensor] = None  # pooled flat gradient buffer during backward
         self.grad_off = 0
         self.ag_event = None
-        self.free_event = None
         self.unsharded = False
         self.in_backward = False
-        self.ready = set()
+        self.ready = {}
+        self.expected = {}
         self.has_partial = False
         self.rs_launched = False
+        self.rs_event = None
+        self.updated_in_backward = False
+
+    def layout(self, world: int):
+        full, shard = 0, 0
+        self.offsets = []
+        for s in self.segs:
+            piece = s.layout(world)
+            s.full_off, s.shard_off = full, shard
+            self.offsets.append(full)
+            full += piece * world
+            shard += piece
+        self.padded, self.shard_numel = full, shard
+
+    def piece_view(self, flat: torch.Tensor, seg: _Seg) -> torch.Tensor:
+        return flat[seg.shard_off : seg.shard_off + seg.piece]
+
+
+def _seg_table(rows):
+    arr = (ctypes.c_longlong * (3 * len(rows)))()
+    for i, r in enumerate(rows):
+        arr[3 * i], arr[3 * i + 1], arr[3 * i + 2] = r
+    return arr
 
 
 class B200ShardedModule(nn.Module):
     def __init__(self, module: nn.Module, plugin, device, shard_group=None, replicate_group=None, gradient_state=None,
-                 shard_group_is_world: bool = True):
+                 shard_group_is_world: bool = True, dp_group=None):
         super().__init__()
         self.module = module
         self.plugin = plugin
@@ -126,21 +232,32 @@ class B200ShardedModule(nn.Module):
         self.trace = CommTrace()  # exposed-communication accounting (ACCELERATE_B200_TRACE_COMM=1 or .enabled = True)
         self._shadow, self._poison = comm_shadow_enabled(), comm_poison_enabled()
         self.replicate_group = replicate_group
+        self.dp_group = dp_group  # shard x replicate ranks (hybrid sharding); None: the shard group is all there is
         self.world = torch.distributed.get_world_size(self.group)
         self.rank = torch.distributed.get_rank(self.group)
         self.use_symm = self.device.type == "cuda"
         self.reshard_after_forward = plugin.effective_reshard_after_forward
         self.requires_gradient_sync = True
-        self.param_dtype = BF16 if self.use_symm else next(module.parameters()).dtype
+        first = next(module.parameters())
         pol = plugin.mixed_precision_policy
-        if pol is not None and pol.param_dtype is not None and self.use_symm and pol.param_dtype != BF16:
-            raise ValueError("the native sharded engine computes in bf16; use mixed_precision='bf16'")
+        if self.use_symm:
+            wants_bf16 = first.dtype == BF16 or (pol is not None and getattr(pol, "param_dtype", None) == BF16)
+            if not wants_bf16:
+                raise ValueError(
+                    "the native sharded engine computes in bf16 (bf16 parameters, or mixed_precision='bf16' on fp32 parameters); "
+                    f"got {first.dtype} parameters with mixed-precision policy {pol}. Accelerator.prepare falls back to torch FSDP2 "
+                    "for that case; constructing B200ShardedModule directly needs bf16."
+                )
+            self.param_dtype = BF16
+        else:
+            self.param_dtype = first.dtype
         self.step_count = 0
         self._optimizer = None
-        self._hyper = None
         self._fused = False
         self._hyper_ok = False
         self._fused_allowed = False
+        self._generic = False          # foreign optimizer: stepped on shard-shaped parameter views
+        self._shard_params = {}        # id(original param) -> shard-shaped nn.Parameter (generic optimizers)
         self._clip_requested_this_step = False
         self._saw_clip = False
         self._clip_coef = None
@@ -148,9 +265,14 @@ class B200ShardedModule(nn.Module):
         self._units: list[_Unit] = []
         self._order: list[_Unit] = []  # forward execution order, learnt on the first iteration
         self._order_locked = False
+        self._carry: list[_GatherJob] = []  # gathers waiting for a GEMM to ride on
+        self._fuse_gather = os.environ.get("ACCELERATE_B200_FSDP_FUSED_GATHER", "1") != "0"
+        self._fwd_gather = os.environ.get("ACCELERATE_B200_FSDP_FWD_GATHER", "jit")  # jit | carry
         self._build_units()
         self._allocate()
         self._install_hooks()
+        if self.use_symm:
+            F.register_carry_source(self)
 
     # ------------------------------------------------------------------ construction
     def _build_units(self):
@@ -161,6 +283,11 @@ class B200ShardedModule(nn.Module):
             for m in plugin.ignored_modules:
                 ignored.update(id(p) for p in m.parameters())
         names = {id(p): n for n, p in self.module.named_parameters()}
+        # a parameter registered in several modules (tied embeddings) receives one gradient per use
+        uses = {}
+        for _, p in self.module.named_parameters(remove_duplicate=False):
+            uses[id(p)] = uses.get(id(p), 0) + 1
+        self._uses = uses
         if plugin.activation_checkpointing:
             apply_activation_checkpointing(self.module, plugin)
         for fqn, sub in get_module_children_bottom_up(self.module, return_fqns=True):
@@ -191,14 +318,14 @@ class B200ShardedModule(nn.Module):
                 self._unit_of_param[id(p)] = u
                 p._b200_fsdp_unit = u
                 u.engine = self
+        self._seg_of_param = {id(s.param): s for u in self._units for s in u.segs}
         self._ignored_params = [p for p in self.module.parameters() if id(p) in ignored]
+        self._frozen = [p for p in self.module.parameters() if not p.requires_grad and id(p) not in ignored]
 
     def _allocate(self):
         world = self.world
         for u in self._units:
-            q = world * 8
-            u.padded = (u.numel + q - 1) // q * q
-            u.shard_numel = u.padded // world
+            u.layout(world)
         layer_units = [u for u in self._units if u.module is not None]
         root_units = [u for u in self._units if u.module is None]
         max_layer = max([u.padded for u in layer_units], default=0)
@@ -206,12 +333,13 @@ class B200ShardedModule(nn.Module):
         esz = 2 if self.param_dtype == BF16 else 4
         n_grad_bufs = int(os.environ.get("ACCELERATE_B200_FSDP_GRAD_BUFFERS", "3"))
         n_full_bufs = int(os.environ.get("ACCELERATE_B200_FSDP_PARAM_BUFFERS", "3"))
+        self._ws_group = self.dp_group if (self.dp_group is not None and self.replicate_group is not None) else self.group
         if self.use_symm:
             from .symm import SymmetricWorkspace
 
             # shards + dedicated root gradient buffers + pooled layer gradient buffers (+ slack for pool growth)
             need = total_shard * esz + sum(u.padded for u in root_units) * esz + (n_grad_bufs + 2) * max_layer * esz + 64 * 2**20
-            self.ws = SymmetricWorkspace(self.group, need, self.device)
+            self.ws = SymmetricWorkspace(self._ws_group, need, self.device)
             # gathers and reductions get their own streams: a reduce-scatter waits for its peers, and a
             # prefetching all-gather must not queue behind that wait
             self.comm_stream = torch.cuda.Stream(device=self.device)
@@ -219,32 +347,52 @@ class B200ShardedModule(nn.Module):
             self.ag_ctas = int(os.environ.get("ACCELERATE_B200_AG_CTAS", "148"))
             self.rs_ctas = int(os.environ.get("ACCELERATE_B200_RS_CTAS", "148"))
             self.ch_step = self.ws.new_channel()
+            # all-gathers stay inside the shard group; reductions span shard x replicate (hybrid sharding)
+            ws_ranks = torch.distributed.get_process_group_ranks(self._ws_group)
+            shard_ranks = torch.distributed.get_process_group_ranks(self.group)
+            self._ag_peers = (ctypes.c_void_p * self.world)(*[self.ws.peer_bases[ws_ranks.index(g)] for g in shard_ranks])
+            self.rs_world = self.ws.world
+            self.rs_rank = self.ws.rank
         else:
             self.ws = None
             self.comm_stream = None
             self.rs_stream = None
-        # shards: bf16 parameter shard (symmetric), fp32 master + moments (local)
+            self._ag_peers = None
+            self.rs_world = self.world * (torch.distributed.get_world_size(self.replicate_group) if self.replicate_group is not None else 1)
+        meta_init = any(p.device.type == "meta" for u in self._units for p in u.params)
+        src = torch.distributed.get_global_rank(self.group, 0)
+        # shards: parameter shard (symmetric), fp32 master + moments (local)
         for u in self._units:
-            flat = torch.zeros(u.padded, dtype=self.param_dtype, device=self.device)
-            for p, off in zip(u.params, u.offsets):
-                flat[off : off + p.numel()].copy_(p.detach().reshape(-1).to(self.param_dtype))
-            # replicas must start identical: rank 0's values win (reference: fsdp2_load_full_state_dict)
-            torch.distributed.broadcast(flat, src=torch.distributed.get_global_rank(self.group, 0), group=self.group)
-            lo = self.rank * u.shard_numel
             if self.use_symm:
                 u.shard_off, u.shard = self.ws.alloc_tensor((u.shard_numel,), self.param_dtype)
-                u.shard.copy_(flat[lo : lo + u.shard_numel])
                 u.ch_arrive, u.ch_done = self.ws.new_channel(), self.ws.new_channel()
             else:
-                u.shard = flat[lo : lo + u.shard_numel].clone()
-            u.master = u.shard.to(torch.float32)
+                u.shard_off, u.shard = 0, torch.zeros(u.shard_numel, dtype=self.param_dtype, device=self.device)
+            u.master = torch.zeros(u.shard_numel, dtype=torch.float32, device=self.device)
+            for s in u.segs:
+                p = s.param
+                if meta_init or p.device.type == "meta":
+                    # meta-device construction (cpu_ram_efficient_loading): values arrive later through load_full_state_dict
+                    pass
+                else:
+                    # replicas must start identical: the values of the group's first rank win, one parameter at a time so
+                    # that no rank ever holds a second full copy of the model (reference: fsdp2_load_full_state_dict)
+                    full = p.detach().to(self.device, torch.float32).reshape(-1)
+                    if self.world > 1:
+                        torch.distributed.broadcast(full, src=src, group=self.group)
+                    lo = self.rank * s.piece
+                    n = max(0, min(s.piece, s.numel - lo))
+                    if n > 0:
+                        u.master[s.shard_off : s.shard_off + n].copy_(full[lo : lo + n])
+                    del full
+                p._b200_full_shape = s.shape
+                p.data = torch.empty(0, dtype=self.param_dtype, device=self.device)
+            u.shard.copy_(u.master)
             u.exp_avg = torch.zeros_like(u.master)
             u.exp_avg_sq = torch.zeros_like(u.master)
             u.grad_shard = None
-            del flat
             for p in u.params:
-                p._b200_full_shape = tuple(p.shape)
-                p.data = torch.empty(0, dtype=self.param_dtype, device=self.device)
+                u.expected[id(p)] = self._uses.get(id(p), 1)
         # layer units share pools sized by the largest layer; root units (live for the whole
         # forward+backward) get dedicated buffers of their own size
         def full_maker(n):
@@ -266,6 +414,9 @@ class B200ShardedModule(nn.Module):
                 u.fpool, u.gpool = _Pool(full_maker(u.padded)), _Pool(grad_maker(u.padded))
                 u.fpool.add(1)
                 u.gpool.add(1)
+        for p in self._frozen:
+            if p.device != self.device and p.device.type != "meta":
+                p.data = p.data.to(self.device)
         if self.use_symm:
             torch.cuda.synchronize(self.device)
             self.ws.barrier(self.ch_step)
@@ -282,8 +433,26 @@ class B200ShardedModule(nn.Module):
                 self._handles.append(p.register_post_accumulate_grad_hook(self._autograd_grad_ready))
 
     # ------------------------------------------------------------------ all-gather / reshard
-    def _launch_gather(self, u: _Unit):
-        """Start (on the comm stream) the gather of ``u`` into a pooled buffer; idempotent."""
+    def _rides_on_gemm(self, s: _Seg) -> bool:
+        """Weights the model feeds to the tcgen05 GEMM as its B operand are gathered by that GEMM (or one before it)."""
+        return (self._fuse_gather and self.use_symm and self.world > 1 and s.rows > 0 and len(s.shape) == 2 and s.piece >= 2**16
+                and getattr(s.param, "_b200_gemm_b_seen", False) and not getattr(s.param, "_b200_no_fused_gather", False))
+
+    def _pull_segments(self, u: _Unit, segs, stream):
+        """TMA pull kernel for `segs` of `u` into u.full (stream None: the current stream)."""
+        lib = self.ws.lib
+        from ..ops._lib import check, cur_stream, ptr
+
+        st = cur_stream() if stream is None else ctypes.c_void_p(stream.cuda_stream)
+        for i in range(0, len(segs), SEGS_PER_LAUNCH):
+            part = segs[i : i + SEGS_PER_LAUNCH]
+            tab = _seg_table([(s.shard_off * 2, s.full_off * 2, s.piece * 2) for s in part])
+            check(lib.b200_allgather_pull_segs(self._ag_peers, self.rank, self.world, u.shard_off, tab, len(part), ptr(u.full), -1, 0,
+                                               self.ag_ctas, st), "allgather_pull_segs")
+
+    def _launch_gather(self, u: _Unit, carry: bool = False):
+        """Give ``u`` a full buffer and start filling it; idempotent.  Segments that ride on GEMMs get a pending job (queued for
+        the next GEMMs when ``carry``), the rest is pulled on the comm stream."""
         if u.full is not None:
             return
         idx = u.fpool.take()
@@ -291,36 +460,74 @@ class B200ShardedModule(nn.Module):
         u.full = u.fpool.bufs[idx][1][: u.padded]
         if self.use_symm:
             ev = u.fpool.events[idx]
-            if ev is not None:
-                self.comm_stream.wait_event(ev)
-            with torch.cuda.stream(self.comm_stream):
-                self.ws.allgather_pull(u.shard_off, u.shard_numel * 2, u.full, ctas=self.ag_ctas, stream=self.comm_stream)
+            riding = [s for s in u.segs if self._rides_on_gemm(s)]
+            pulled = [s for s in u.segs if not self._rides_on_gemm(s)]
+            cur = torch.cuda.current_stream(self.device)
+            if riding:
+                if ev is not None:
+                    cur.wait_event(ev)
+                for s in riding:
+                    if s.job is None:
+                        s.job = _GatherJob(self, u, s)
+                    # my own rows go in place now; the GEMM's gather warp brings the peers'
+                    lo = s.full_off + self.rank * s.piece
+                    u.full[lo : lo + s.piece].copy_(u.shard[s.shard_off : s.shard_off + s.piece])
+                    s.job.pending = True
+                    if carry and not s.job.queued:
+                        s.job.queued = True
+                        self._carry.append(s.job)
+            if pulled:
+                if ev is not None:
+                    self.comm_stream.wait_event(ev)
+                self._pull_segments(u, pulled, self.comm_stream)
                 u.ag_event = torch.cuda.Event()
                 u.ag_event.record(self.comm_stream)
+            else:
+                u.ag_event = None
         else:
             parts = [torch.empty_like(u.shard) for _ in range(self.world)]
             torch.distributed.all_gather(parts, u.shard, group=self.group)
-            u.full.copy_(torch.cat(parts))
+            for s in u.segs:
+                for q in range(self.world):
+                    u.full[s.full_off + q * s.piece : s.full_off + (q + 1) * s.piece].copy_(parts[q][s.shard_off : s.shard_off + s.piece])
 
-    def unshard(self, u: Optional[_Unit] = None):
-        """Make the parameters of ``u`` (or of every unit) whole: ``param.data`` becomes a view of the gathered buffer."""
+    def pop_carry_job(self) -> Optional[_GatherJob]:
+        """Next weight gather waiting for a GEMM to ride on (ops.functional.gemm asks before every plain launch)."""
+        while self._carry:
+            job = self._carry.pop(0)
+            job.queued = False
+            if job.pending:
+                return job
+        return None
+
+    def unshard(self, u: Optional[_Unit] = None, complete: bool = False):
+        """Make the parameters of ``u`` (or of every unit) whole: ``param.data`` becomes a view of the gathered buffer.
+        ``complete`` also runs, right away, the gathers that would otherwise ride on later GEMMs."""
         if u is None:
             for x in self._units:
-                self.unshard(x)
+                self.unshard(x, complete)
             return
-        if u.unsharded:
-            return
-        self._launch_gather(u)
-        if self.use_symm and u.ag_event is not None:
-            self.trace.wait_event(torch.cuda.current_stream(self.device), u.ag_event, "all_gather")
-            if self._shadow:
+        if not u.unsharded:
+            self._launch_gather(u)
+            if self.use_symm and u.ag_event is not None:
+                self.trace.wait_event(torch.cuda.current_stream(self.device), u.ag_event, "all_gather")
+            for s in u.segs:
+                s.param.data = u.full[s.full_off : s.full_off + s.numel].view(s.shape)
+                s.param._b200_ag = s.job if (s.job is not None and s.job.pending) else None
+            u.unsharded = True
+        if complete:
+            for s in u.segs:
+                if s.job is not None and s.job.pending:
+                    s.job.materialize()
+                s.param._b200_ag = None
+            if self.use_symm and self._shadow:
                 # debug: the same gather through torch.distributed must give the same bytes
-                ref = torch.empty_like(u.full[: self.world * u.shard_numel])
+                ref = torch.empty(self.world * u.shard_numel, dtype=u.shard.dtype, device=self.device)
                 torch.distributed.all_gather_into_tensor(ref, u.shard, group=self.group)
-                shadow_check(f"all_gather[{u.name}]", u.full[: self.world * u.shard_numel], ref)
-        for p, off in zip(u.params, u.offsets):
-            p.data = u.full[off : off + _numel(p._b200_full_shape)].view(p._b200_full_shape)
-        u.unsharded = True
+                for s in u.segs:
+                    for q in range(self.world):
+                        shadow_check(f"all_gather[{u.name}:{s.name}:{q}]", u.full[s.full_off + q * s.piece : s.full_off + (q + 1) * s.piece],
+                                     ref[q * u.shard_numel + s.shard_off : q * u.shard_numel + s.shard_off + s.piece])
 
     def reshard(self, u: Optional[_Unit] = None, write_back: bool = False):
         if u is None:
@@ -330,11 +537,17 @@ class B200ShardedModule(nn.Module):
         if not u.unsharded:
             return
         if write_back:
-            lo = self.rank * u.shard_numel
-            u.shard.copy_(u.full[lo : lo + u.shard_numel])
-            u.master.copy_(u.shard)
-        for p in u.params:
-            p.data = torch.empty(0, dtype=self.param_dtype, device=self.device)
+            for s in u.segs:
+                if s.job is not None and s.job.pending:
+                    s.job.materialize()
+                lo = s.full_off + self.rank * s.piece
+                u.master[s.shard_off : s.shard_off + s.piece].copy_(u.full[lo : lo + s.piece])
+            u.shard.copy_(u.master)
+        for s in u.segs:
+            s.param.data = torch.empty(0, dtype=self.param_dtype, device=self.device)
+            s.param._b200_ag = None
+            if s.job is not None:
+                s.job.pending = False
         ev = None
         if self._poison:
             u.full.fill_(float("nan"))  # debug: anything that still reads the released buffer turns into NaN
@@ -359,14 +572,10 @@ class B200ShardedModule(nn.Module):
         self.unshard(u)
         nxt = self._next_in_order(u, +1)
         if nxt is not None and not u.in_backward:
-            self._launch_gather(nxt)
+            self._launch_gather(nxt, carry=self._fwd_gather == "carry")
         if torch.is_grad_enabled() and not u.in_backward:
-            self._register_pre_backward(u, args, kwargs)
+            u._want_pre_backward = True
         return None
-
-    def _register_pre_backward(self, u: _Unit, args, kwargs):
-        """Arrange for ``_pre_backward(u)`` to run when gradients reach the unit's outputs."""
-        u._want_pre_backward = True
 
     def _post_forward(self, u: _Unit, out):
         if torch.is_grad_enabled() and getattr(u, "_want_pre_backward", False) and not u.in_backward:
@@ -393,7 +602,8 @@ class B200ShardedModule(nn.Module):
         self.unshard(u)
         prv = self._next_in_order(u, -1)
         if prv is not None and not prv.in_backward:
-            self._launch_gather(prv)
+            # the weight-gradient GEMMs of this unit carry the gathers of the unit that runs next
+            self._launch_gather(prv, carry=True)
         self._attach_grad_buffer(u)
 
     def _attach_grad_buffer(self, u: _Unit):
@@ -405,11 +615,12 @@ class B200ShardedModule(nn.Module):
             if self.use_symm and u.gpool.events[idx] is not None:
                 self.trace.wait_event(torch.cuda.current_stream(self.device), u.gpool.events[idx], "grad_buffer_reuse")
             u.has_partial = False
-        u.ready = set()
+        u.ready = {}
         u.rs_launched = False
-        for p, off in zip(u.params, u.offsets):
-            p._b200_grad_buf = u.grad[off : off + _numel(p._b200_full_shape)].view(p._b200_full_shape)
-            p._b200_has_partial = u.has_partial
+        for s in u.segs:
+            s.param._b200_grad_buf = u.grad[s.full_off : s.full_off + s.numel].view(s.shape)
+            s.param._b200_has_partial = u.has_partial
+            s.param._b200_grad_seen = False
 
     def _native_grad_ready(self, p):
         u = self._unit_of_param[id(p)]
@@ -418,12 +629,14 @@ class B200ShardedModule(nn.Module):
     def _autograd_grad_ready(self, p):
         """Gradient produced by a foreign op landed in ``p.grad``: move it into the flat buffer."""
         u = self._unit_of_param[id(p)]
+        g = p.grad
+        if g is None:
+            return  # the native op already wrote this gradient into the flat buffer and reported it (deliver_weight_grad)
         if u.grad is None:
             # root-level parameters have no pre-backward hook of their own
             self._queue_final_callback()
             u.in_backward = True
             self._attach_grad_buffer(u)
-        g = p.grad
         if g is not None:
             view = p._b200_grad_buf
             if u.has_partial or id(p) in u.ready:
@@ -431,11 +644,14 @@ class B200ShardedModule(nn.Module):
             else:
                 view.copy_(g)
             p.grad = None
+            # autograd has already summed every use of a shared parameter into this one gradient
+            u.ready[id(p)] = u.expected.get(id(p), 1) - 1
         self._mark_ready(u, p)
 
     def _mark_ready(self, u: _Unit, p):
-        u.ready.add(id(p))
-        if len(u.ready) == len(u.params) and u.module is not None:
+        u.ready[id(p)] = u.ready.get(id(p), 0) + 1
+        if all(u.ready.get(id(q), 0) >= u.expected.get(id(q), 1) for q in u.params):
+            # root units too: the LM head's reduce-scatter starts at the top of backward instead of after it
             self._post_backward(u)
 
     def _post_backward(self, u: _Unit):
@@ -444,31 +660,42 @@ class B200ShardedModule(nn.Module):
             return
         u.rs_launched = True
         if u.grad is not None:
-            missing = [i for i, p in enumerate(u.params) if id(p) not in u.ready]
+            missing = [s for s in u.segs if id(s.param) not in u.ready]
             if missing and not u.has_partial:
-                for i in missing:
-                    off = u.offsets[i]
-                    u.grad[off : off + _numel(u.params[i]._b200_full_shape)].zero_()
+                for s in missing:
+                    u.grad[s.full_off : s.full_off + s.numel].zero_()
             if self.requires_gradient_sync:
                 self._reduce_model_parallel_replicas(u)
                 self._reduce_unit(u)
                 self._release_grad(u)
             else:
                 u.has_partial = True
-        if u.unsharded and (self.reshard_after_forward or u.module is None or True):
+        if u.unsharded:
             self.reshard(u)
         u.in_backward = False
 
     def _reduce_model_parallel_replicas(self, u: _Unit):
         """Parameters that a tensor-parallel group keeps whole (norms, LM head) only saw that rank's token shard: their
         gradients are summed over the tp group before the data-parallel reduce-scatter (tensor_parallel._mark_replicated
-        leaves this to the engine when the parameter belongs to a sharded unit)."""
-        for p, off in zip(u.params, u.offsets):
-            g = getattr(p, "_b200_tp_group", None)
+        leaves this to the engine when the parameter belongs to a sharded unit).  One all-reduce per unit and group: the
+        replicated parameters of a unit are copied into one staging tensor."""
+        by_group = {}
+        for s in u.segs:
+            g = getattr(s.param, "_b200_tp_group", None)
             if g is None or torch.distributed.get_world_size(g) == 1:
                 continue
-            view = u.grad[off : off + _numel(p._b200_full_shape)]
-            torch.distributed.all_reduce(view, group=g)
+            by_group.setdefault(g, []).append(s)
+        for g, segs in by_group.items():
+            if len(segs) == 1:
+                s = segs[0]
+                torch.distributed.all_reduce(u.grad[s.full_off : s.full_off + s.numel], group=g)
+                continue
+            stage = torch.cat([u.grad[s.full_off : s.full_off + s.numel] for s in segs])
+            torch.distributed.all_reduce(stage, group=g)
+            o = 0
+            for s in segs:
+                u.grad[s.full_off : s.full_off + s.numel].copy_(stage[o : o + s.numel])
+                o += s.numel
 
     def _release_grad(self, u: _Unit):
         for p in u.params:
@@ -489,12 +716,15 @@ class B200ShardedModule(nn.Module):
                 if u.unsharded:
                     self.reshard(u)
                 u.in_backward = False
+        # gathers nobody picked up (a backward that ended early) must not leak into the next step
+        for job in self._carry:
+            job.queued = False
+        self._carry.clear()
         if self.use_symm:
             cur = torch.cuda.current_stream(self.device)
             for u in self._units:
-                ev = getattr(u, "rs_event", None)
-                if ev is not None:
-                    self.trace.wait_event(cur, ev, "reduce_scatter_tail")
+                if u.rs_event is not None:
+                    self.trace.wait_event(cur, u.rs_event, "reduce_scatter_tail")
 
     # ------------------------------------------------------------------ reduce-scatter (+ AdamW)
     def _adam_hyper(self):
@@ -507,67 +737,88 @@ class B200ShardedModule(nn.Module):
 
     def _reduce_unit(self, u: _Unit):
         fused = self._fused and self._hyper_ok
-        scale = 1.0 / self.world
+        scale = 1.0 / self.rs_world
         if self.use_symm:
             from ..ops._lib import check, ptr
-            import ctypes
 
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(self.device))
             self.rs_stream.wait_event(ev)
-            e = self.ws.next_epoch(u.ch_arrive)
-            self.ws._epochs[u.ch_done] = e
             if not fused and u.grad_shard is None:
                 u.grad_shard = torch.empty(u.shard_numel, dtype=torch.float32, device=self.device)
             h = self._adam_hyper() if fused else dict(lr=0.0, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0)
             with torch.cuda.stream(self.rs_stream):
-                check(self.ws.lib.b200_reduce_scatter_adamw(
-                    self.ws.peer_array, self.rank, self.world, u.grad_off, u.shard_numel, ptr(u.master), ptr(u.exp_avg),
-                    ptr(u.exp_avg_sq), u.shard_off, ptr(u.grad_shard) if not fused else None, h["lr"], h["beta1"], h["beta2"], h["eps"],
-                    h["weight_decay"], self.step_count + 1, scale, int(fused), None, u.ch_arrive, u.ch_done, e,
-                    self.ws.counter_ptr(u.ch_arrive), self.rs_ctas, ctypes.c_void_p(self.rs_stream.cuda_stream)), "reduce_scatter_adamw")
+                for i in range(0, len(u.segs), SEGS_PER_LAUNCH):
+                    part = u.segs[i : i + SEGS_PER_LAUNCH]
+                    base = part[0].shard_off
+                    # hybrid sharding: the pieces I own are indexed by my SHARD rank, read from every rank of shard x replicate
+                    tab = _seg_table([(s.shard_off - base, s.full_off, s.piece) for s in part])
+                    e = self.ws.next_epoch(u.ch_arrive)
+                    self.ws._epochs[u.ch_done] = e
+                    fo = base * 4
+                    check(self.ws.lib.b200_reduce_scatter_adamw_segs(
+                        self.ws.peer_array, self.rs_rank, self.rs_world, self.rank, u.grad_off, tab, len(part),
+                        ctypes.c_void_p(u.master.data_ptr() + fo), ctypes.c_void_p(u.exp_avg.data_ptr() + fo), ctypes.c_void_p(u.exp_avg_sq.data_ptr() + fo),
+                        u.shard_off + base * 2, ctypes.c_void_p(u.grad_shard.data_ptr() + fo) if not fused else None,
+                        h["lr"], h["beta1"], h["beta2"], h["eps"], h["weight_decay"], self.step_count + 1, scale, int(fused), None,
+                        u.ch_arrive, u.ch_done, e, self.ws.counter_ptr(u.ch_arrive), self.rs_ctas,
+                        ctypes.c_void_p(self.rs_stream.cuda_stream)), "reduce_scatter_adamw_segs")
                 u.rs_event = torch.cuda.Event()
                 u.rs_event.record(self.rs_stream)
             u.updated_in_backward = fused
         else:
             full = u.grad.to(torch.float32)
             torch.distributed.all_reduce(full, group=self.group)
-            lo = self.rank * u.shard_numel
-            u.grad_shard = full[lo : lo + u.shard_numel] * scale
+            if self.replicate_group is not None:
+                torch.distributed.all_reduce(full, group=self.replicate_group)
+            u.grad_shard = torch.cat([full[s.full_off + self.rank * s.piece : s.full_off + (self.rank + 1) * s.piece] for s in u.segs]) * scale
             u.updated_in_backward = False
-        if self.replicate_group is not None and not fused:
-            stream_ctx = torch.cuda.stream(self.rs_stream) if self.use_symm else contextlib.nullcontext()
-            with stream_ctx:
-                torch.distributed.all_reduce(u.grad_shard, group=self.replicate_group)
-                u.grad_shard /= torch.distributed.get_world_size(self.replicate_group)
-                if self.use_symm:
-                    u.rs_event = torch.cuda.Event()
-                    u.rs_event.record(self.rs_stream)
 
     # ------------------------------------------------------------------ optimizer integration
     def bind_optimizer(self, accelerated_optimizer):
-        """Take over the parameter update of ``accelerated_optimizer`` (sharded state lives in this engine)."""
+        """Take over the parameter update of ``accelerated_optimizer`` (sharded state lives in this engine).
+
+        Single-group Adam/AdamW runs on the engine's own kernels (and may fuse with the reduce-scatter).  Any other optimizer
+        keeps working the way the reference keeps it working after ``fully_shard``: its parameter references are swapped for
+        shard-shaped fp32 views of the master weights, the reduced gradient shard becomes their ``.grad`` and the user's
+        ``optimizer.step()`` runs on them.
+        """
         inner = accelerated_optimizer.optimizer
         self._optimizer = inner
         accelerated_optimizer.attach_engine(self)
         name = type(inner).__name__
         g = inner.param_groups[0] if inner.param_groups else {}
-        self._hyper_ok = name in ("AdamW", "FusedAdamW", "Adam") and not g.get("amsgrad", False) and not g.get("maximize", False) and len(inner.param_groups) == 1
-        if not self._hyper_ok:
-            raise NotImplementedError(
-                f"the native sharded engine implements (fused) AdamW on its shards; got optimizer {name} with {len(inner.param_groups)} param groups. "
-                "Use torch.optim.AdamW / FusedAdamW with a single param group."
-            )
+        self._hyper_ok = (name in ("AdamW", "FusedAdamW", "Adam") and not g.get("amsgrad", False) and not g.get("maximize", False)
+                          and len(inner.param_groups) == 1 and not (name == "Adam" and float(g.get("weight_decay", 0.0)) != 0.0))
+        self._generic = not self._hyper_ok
         if name == "Adam":
             g.setdefault("weight_decay", 0.0)
         allow = os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto")
-        self._fused_allowed = allow != "0" and self.use_symm and self.replicate_group is None
+        self._fused_allowed = allow != "0" and self.use_symm and self._hyper_ok
         self._fused = allow == "1" and self._fused_allowed
-        # the user's optimizer never sees real tensors again: drop its (empty) state
+        # the user's optimizer never sees the full-size tensors again: drop their (empty) state
         inner.state.clear()
+        if self._generic:
+            self._swap_in_shard_params(inner)
+
+    def _swap_in_shard_params(self, inner):
+        mapping = {}
+        for u in self._units:
+            for s in u.segs:
+                view = u.master[s.shard_off : s.shard_off + s.piece]
+                if s.piece_shape is not None:
+                    view = view.view(s.piece_shape)
+                sp = nn.Parameter(view, requires_grad=True)
+                sp._b200_origin = s.name
+                self._shard_params[id(s.param)] = sp
+                mapping[id(s.param)] = sp
+        for group in inner.param_groups:
+            group["params"] = [mapping.get(id(p), p) for p in group["params"]]
 
     def zero_grad(self):
         self._clip_requested_this_step = False
+        for sp in self._shard_params.values():
+            sp.grad = None
 
     def clip_grad_norm_(self, max_norm, norm_type=2):
         """Global gradient norm over all shards; the clip coefficient is applied inside the update kernel."""
@@ -575,7 +826,7 @@ class B200ShardedModule(nn.Module):
             raise NotImplementedError("only the L2 norm is implemented for sharded gradients")
         self._clip_requested_this_step = True
         self._saw_clip = True
-        if any(getattr(u, "updated_in_backward", False) for u in self._units):
+        if any(u.updated_in_backward for u in self._units):
             raise RuntimeError(
                 "clip_grad_norm_ was called after the fused reduce-scatter+AdamW already consumed the gradients in backward. "
                 "Set ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD=0 when clipping is only used on some steps."
@@ -599,26 +850,30 @@ class B200ShardedModule(nn.Module):
 
     def optimizer_step(self, optimizer, scaler=None) -> bool:
         """Called by ``AcceleratedOptimizer.step``. Returns True if the step was skipped (never, for bf16)."""
-        h = self._adam_hyper()
         self.step_count += 1
         ctx = torch.cuda.stream(self.rs_stream) if self.use_symm else contextlib.nullcontext()
         if self.use_symm:
             self.rs_stream.wait_stream(torch.cuda.current_stream(self.device))
         with ctx:
-            for u in self._units:
-                if getattr(u, "updated_in_backward", False):
-                    u.updated_in_backward = False
-                    continue
-                if u.grad_shard is None:
-                    continue
-                F.adamw_flat_(u.master, u.exp_avg, u.exp_avg_sq, u.grad_shard, u.shard if u.shard.dtype == BF16 else None,
-                              step=self.step_count, clip_coef=self._clip_coef, **h)
-                if u.shard.dtype != BF16:
-                    u.shard.copy_(u.master)
+            if self._generic:
+                self._generic_step(optimizer)
+            else:
+                h = self._adam_hyper()
+                for u in self._units:
+                    if u.updated_in_backward:
+                        u.updated_in_backward = False
+                        continue
+                    if u.grad_shard is None:
+                        continue
+                    F.adamw_flat_(u.master, u.exp_avg, u.exp_avg_sq, u.grad_shard, u.shard if u.shard.dtype == BF16 else None,
+                                  step=self.step_count, clip_coef=self._clip_coef, **h)
+                    if u.shard.dtype != BF16:
+                        u.shard.copy_(u.master)
             if self.use_symm:
                 # every rank's shards now hold version `step_count`: one barrier, then gathers need no handshake
                 self.ws.barrier(self.ch_step, stream=self.rs_stream)
                 self.comm_stream.wait_stream(self.rs_stream)
+                torch.cuda.current_stream(self.device).wait_stream(self.rs_stream)
         self._clip_coef = None
         # first step ran in the safe mode; switch to the fused update if nobody asked for the gradients
         if self._fused_allowed and not self._fused and not self._saw_clip and os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto") == "auto":
@@ -626,6 +881,27 @@ class B200ShardedModule(nn.Module):
             for u in self._units:
                 u.grad_shard = None
         return False
+
+    def _generic_step(self, optimizer):
+        """The user's optimizer on shard-shaped views: grads are the reduced fp32 shards (clipped if asked)."""
+        any_grad = False
+        for u in self._units:
+            if u.grad_shard is None:
+                continue
+            if self._clip_coef is not None:
+                u.grad_shard.mul_(self._clip_coef)
+            for s in u.segs:
+                sp = self._shard_params[id(s.param)]
+                g = u.grad_shard[s.shard_off : s.shard_off + s.piece]
+                sp.grad = g.view(sp.shape)
+                any_grad = True
+        if any_grad:
+            optimizer.step()
+        for u in self._units:
+            if u.shard.dtype == BF16 and self.use_symm:
+                F.scale_cast(u.master, u.shard, 1.0)
+            else:
+                u.shard.copy_(u.master)
 
     # ------------------------------------------------------------------ module surface
     def forward(self, *args, **kwargs):
@@ -645,7 +921,6 @@ class B200ShardedModule(nn.Module):
     def _queue_root_backward(self, u: _Unit):
         u.in_backward = True
         self._attach_grad_buffer(u)
-        u._root_pending = True
 
     def set_requires_gradient_sync(self, flag: bool):
         self.requires_gradient_sync = bool(flag)
@@ -661,57 +936,86 @@ class B200ShardedModule(nn.Module):
 
     def parameters_full(self):
         """Context-free helper for tools: un-shard everything and return the module."""
-        self.unshard()
+        self.unshard(complete=True)
         return self.module
-
-    # ------------------------------------------------------------------ state dicts / checkpoints
-    def _unit_tensors(self, u: _Unit, flat: torch.Tensor):
-        return {n: flat[off : off + _numel(p._b200_full_shape)].view(p._b200_full_shape) for n, p, off in zip(u.param_names, u.params, u.offsets)}
 
     def exposed_comm_ms(self, by_tag: bool = False):
         """Milliseconds (since the last call) the compute stream spent waiting for all-gathers / reduce-scatters that were not
         hidden behind compute.  Needs ``self.trace.enabled = True`` (or ACCELERATE_B200_TRACE_COMM=1); synchronises."""
         return self.trace.exposed_ms(by_tag=by_tag)
 
-    def full_state_dict(self, cpu: bool = True) -> dict:
-        """Gather every unit (one at a time) and return name -> full tensor (on CPU by default)."""
+    # ------------------------------------------------------------------ state dicts / checkpoints
+    def _gather_flat(self, u: _Unit, shard: torch.Tensor) -> torch.Tensor:
+        """All-gather a shard-layout tensor (any dtype) into the full layout, through torch.distributed (off the hot path)."""
+        parts = [torch.empty_like(shard) for _ in range(self.world)]
+        torch.distributed.all_gather(parts, shard.contiguous(), group=self.group)
+        full = torch.empty(u.padded, dtype=shard.dtype, device=shard.device)
+        for s in u.segs:
+            for q in range(self.world):
+                full[s.full_off + q * s.piece : s.full_off + (q + 1) * s.piece].copy_(parts[q][s.shard_off : s.shard_off + s.piece])
+        return full
+
+    def _unit_tensors(self, u: _Unit, flat: torch.Tensor):
+        return {s.name: flat[s.full_off : s.full_off + s.numel].view(s.shape) for s in u.segs}
+
+    def full_state_dict(self, cpu: bool = True, dtype: Optional[torch.dtype] = None) -> dict:
+        """name -> full tensor, gathered one unit at a time from the fp32 master shards (so a save / load round trip is exact);
+        ``dtype`` down-casts on request.  On CPU by default."""
         out = {}
         for u in self._units:
-            was = u.unsharded
-            self.unshard(u)
-            if self.use_symm:
-                torch.cuda.current_stream(self.device).synchronize()
-            for n, t in self._unit_tensors(u, u.full).items():
+            full = self._gather_flat(u, u.master)
+            for n, t in self._unit_tensors(u, full).items():
+                t = t if dtype is None else t.to(dtype)
                 out[n] = t.detach().to("cpu", copy=True) if cpu else t.detach().clone()
-            if not was:
-                self.reshard(u)
+            del full
         for n, b in self.module.named_buffers():
             out[n] = b.detach().cpu() if cpu else b.detach()
-        for p in self._ignored_params:
-            for n, q in self.module.named_parameters():
-                if q is p:
-                    out[n] = p.detach().cpu() if cpu else p.detach()
+        extra = {id(p) for p in self._ignored_params} | {id(p) for p in self._frozen}
+        for n, q in self.module.named_parameters():
+            if id(q) in extra:
+                out[n] = q.detach().cpu() if cpu else q.detach()
         return out
 
     def state_dict(self, *args, **kwargs):
         return self.full_state_dict()
 
     @torch.no_grad()
-    def load_full_state_dict(self, sd: dict):
+    def load_full_state_dict(self, sd: dict, strict: bool = True):
+        """Every rank passes the same full dict (or only rank 0 passes values and the others ``None`` entries are filled by a
+        broadcast — ``cpu_ram_efficient_loading``)."""
+        have = torch.tensor([1 if sd else 0], device=self.device)
+        counts = [torch.zeros_like(have) for _ in range(self.world)]
+        torch.distributed.all_gather(counts, have, group=self.group)
+        bcast = any(int(c) == 0 for c in counts)
+        src = torch.distributed.get_global_rank(self.group, 0)
         for u in self._units:
-            flat = torch.zeros(u.padded, dtype=torch.float32)
-            for n, p, off in zip(u.param_names, u.params, u.offsets):
-                flat[off : off + _numel(p._b200_full_shape)].copy_(sd[n].reshape(-1).float())
-            lo = self.rank * u.shard_numel
-            u.master.copy_(flat[lo : lo + u.shard_numel].to(self.device))
+            for s in u.segs:
+                if bcast:
+                    full = torch.empty(s.numel, dtype=torch.float32, device=self.device)
+                    if self.rank == 0:
+                        full.copy_(sd[s.name].reshape(-1).float())
+                    torch.distributed.broadcast(full, src=src, group=self.group)
+                else:
+                    if s.name not in sd:
+                        if strict:
+                            raise KeyError(f"missing key {s.name!r} in state dict")
+                        continue
+                    full = sd[s.name].reshape(-1)
+                lo = self.rank * s.piece
+                n = max(0, min(s.piece, s.numel - lo))
+                dst = u.master[s.shard_off : s.shard_off + s.piece]
+                dst.zero_()
+                if n > 0:
+                    dst[:n].copy_(full[lo : lo + n].to(self.device, torch.float32))
             u.shard.copy_(u.master)
-        for n, b in self.module.named_buffers():
-            if n in sd:
-                b.copy_(sd[n])
+        if sd:
+            for n, b in self.module.named_buffers():
+                if n in sd:
+                    b.copy_(sd[n])
         self._sync_after_external_update()
 
     def load_state_dict(self, sd, strict: bool = True):
-        self.load_full_state_dict(sd)
+        self.load_full_state_dict(sd, strict=strict)
 
     def _sync_after_external_update(self):
         if self.use_symm:
@@ -721,14 +1025,59 @@ class B200ShardedModule(nn.Module):
         else:
             torch.distributed.barrier(group=self.group)
 
-    def _meta(self) -> dict:
-        return {"world": self.world, "units": [{"name": u.name, "padded": u.padded, "shard_numel": u.shard_numel,
-                                                 "params": [{"name": n, "shape": list(p._b200_full_shape), "offset": off}
-                                                            for n, p, off in zip(u.param_names, u.params, u.offsets)]} for u in self._units]}
+    # ---- torch.distributed.checkpoint (DCP) views -------------------------------------------------
+    def _mesh(self):
+        m = getattr(self, "_dcp_mesh", None)
+        if m is None:
+            from torch.distributed.device_mesh import DeviceMesh
+
+            m = DeviceMesh.from_group(self.group, "cuda" if self.use_symm else "cpu")
+            self._dcp_mesh = m
+        return m
+
+    def _as_dtensor(self, u: _Unit, flat: torch.Tensor, s: _Seg):
+        """Shard(0) DTensor over my piece of parameter `s` taken from the shard-layout tensor `flat`; parameters that are not cut
+        along dim 0 in whole rows (odd shapes) are gathered and returned as plain (replicated) tensors."""
+        from torch.distributed.tensor import DTensor, Shard
+
+        even_1d = s.rows == 0 and len(s.shape) == 1 and s.numel % self.world == 0 and s.piece == s.numel // self.world
+        if s.rows or even_1d:
+            shape = s.piece_shape if s.rows else (s.piece,)
+            local = flat[s.shard_off : s.shard_off + s.piece].view(shape)
+            return DTensor.from_local(local, self._mesh(), [Shard(0)], run_check=False)
+        return None
+
+    def sharded_state_dict(self, which: str = "master") -> dict:
+        """FQN -> DTensor (or full tensor for oddly shaped parameters) over ``master`` / ``exp_avg`` / ``exp_avg_sq``."""
+        out = {}
+        for u in self._units:
+            flat = getattr(u, which)
+            gathered = None
+            for s in u.segs:
+                dt = self._as_dtensor(u, flat, s)
+                if dt is None:
+                    if gathered is None:
+                        gathered = self._gather_flat(u, flat)
+                    dt = gathered[s.full_off : s.full_off + s.numel].view(s.shape).clone()
+                out[s.name] = dt
+        return out
+
+    def _load_sharded_into(self, which: str, loaded: dict):
+        for u in self._units:
+            flat = getattr(u, which)
+            for s in u.segs:
+                t = loaded[s.name]
+                if hasattr(t, "to_local"):
+                    flat[s.shard_off : s.shard_off + s.piece].copy_(t.to_local().reshape(-1))
+                else:
+                    lo = self.rank * s.piece
+                    n = max(0, min(s.piece, s.numel - lo))
+                    if n > 0:
+                        flat[s.shard_off : s.shard_off + n].copy_(t.reshape(-1)[lo : lo + n])
 
     def save_sharded_state(self, output_dir: str, index: int, plugin=None):
-        """``pytorch_model_fsdp_{i}/`` (one file per rank + metadata) or ``pytorch_model_fsdp.bin`` (full)."""
-        sdt = getattr(plugin or self.plugin, "state_dict_type", "SHARDED_STATE_DICT")
+        """``pytorch_model_fsdp_{i}/`` (DCP directory, ``{"model": state_dict}``) or ``pytorch_model_fsdp.bin`` (full)."""
+        sdt = str(getattr(plugin or self.plugin, "state_dict_type", "SHARDED_STATE_DICT")).split(".")[-1]
         if sdt == "FULL_STATE_DICT":
             sd = self.full_state_dict()
             if torch.distributed.get_rank() == 0:
@@ -736,108 +1085,162 @@ class B200ShardedModule(nn.Module):
                 torch.save(sd, os.path.join(output_dir, name))
             torch.distributed.barrier()
             return
+        import torch.distributed.checkpoint as dist_cp
+
         d = os.path.join(output_dir, f"{FSDP_MODEL_NAME}_{index}")
         os.makedirs(d, exist_ok=True)
-        torch.save({u.name: u.master.detach().cpu() for u in self._units}, os.path.join(d, f"__{self.rank}_0.distcp"))
-        if self.rank == 0:
-            with open(os.path.join(d, ".metadata"), "w") as f:
-                json.dump(self._meta(), f)
-        torch.distributed.barrier()
+        sd = self.sharded_state_dict("master")
+        for n, b in self.module.named_buffers():
+            sd[n] = b.detach()
+        dist_cp.save({"model": sd}, storage_writer=dist_cp.FileSystemWriter(d), process_group=self.group if self.dp_group is None else None)
 
     @torch.no_grad()
     def load_sharded_state(self, input_dir: str, index: int, plugin=None):
-        sdt = getattr(plugin or self.plugin, "state_dict_type", "SHARDED_STATE_DICT")
+        sdt = str(getattr(plugin or self.plugin, "state_dict_type", "SHARDED_STATE_DICT")).split(".")[-1]
         full_name = os.path.join(input_dir, f"{FSDP_MODEL_NAME}.bin" if index == 0 else f"{FSDP_MODEL_NAME}_{index}.bin")
-        if sdt == "FULL_STATE_DICT" or (os.path.exists(full_name) and not os.path.isdir(os.path.join(input_dir, f"{FSDP_MODEL_NAME}_{index}"))):
+        d = os.path.join(input_dir, f"{FSDP_MODEL_NAME}_{index}")
+        if sdt == "FULL_STATE_DICT" or (os.path.exists(full_name) and not os.path.isdir(d)):
             self.load_full_state_dict(torch.load(full_name, map_location="cpu", weights_only=True))
             return
-        d = os.path.join(input_dir, f"{FSDP_MODEL_NAME}_{index}")
-        with open(os.path.join(d, ".metadata")) as f:
-            meta = json.load(f)
-        if meta["world"] != self.world:
-            sd = merge_sharded_checkpoint(d)
-            self.load_full_state_dict(sd)
-            return
-        mine = torch.load(os.path.join(d, f"__{self.rank}_0.distcp"), map_location="cpu", weights_only=True)
+        import torch.distributed.checkpoint as dist_cp
+
+        target = self.sharded_state_dict("master")  # DCP loads in place into these views of the master shards
+        holder = {"model": target}
+        dist_cp.load(holder, storage_reader=dist_cp.FileSystemReader(d), process_group=self.group if self.dp_group is None else None)
+        self._load_sharded_into("master", holder["model"])
         for u in self._units:
-            u.master.copy_(mine[u.name].to(self.device))
             u.shard.copy_(u.master)
         self._sync_after_external_update()
 
     # optimizer state ------------------------------------------------------------------------------
-    def optimizer_state_dict(self, optimizer) -> dict:
-        """Full (gathered) AdamW state in torch's layout: usable as ``optimizer.bin``."""
-        state, idx = {}, 0
-        index_of = {}
+    def _param_index(self, optimizer):
+        index_of, idx = {}, 0
+        reverse = {id(sp): pid for pid, sp in self._shard_params.items()}
         for g in optimizer.param_groups:
             for p in g["params"]:
-                index_of[id(p)] = idx
+                index_of[reverse.get(id(p), id(p))] = idx
                 idx += 1
-        for u in self._units:
-            full_m = self._gather_fp32(u.exp_avg)
-            full_v = self._gather_fp32(u.exp_avg_sq)
-            for p, off in zip(u.params, u.offsets):
-                n = _numel(p._b200_full_shape)
-                if id(p) in index_of:
-                    state[index_of[id(p)]] = {"step": torch.tensor(float(self.step_count)), "exp_avg": full_m[off : off + n].view(p._b200_full_shape).cpu(),
-                                              "exp_avg_sq": full_v[off : off + n].view(p._b200_full_shape).cpu()}
-        groups = [{k: (list(range(len(v))) if k == "params" else v) for k, v in g.items()} for g in optimizer.param_groups]
-        # re-number params across groups
-        c = 0
-        for g in groups:
-            g["params"] = list(range(c, c + len(g["params"])))
+        return index_of
+
+    def optimizer_state_dict(self, optimizer) -> dict:
+        """Full (gathered) optimizer state in torch's layout: usable as ``optimizer.bin``."""
+        index_of = self._param_index(optimizer)
+        state = {}
+        if self._generic:
+            for u in self._units:
+                for s in u.segs:
+                    sp = self._shard_params[id(s.param)]
+                    st = optimizer.state.get(sp, {})
+                    entry = {}
+                    for k, v in st.items():
+                        if torch.is_tensor(v) and v.numel() == s.piece and s.piece > 1:
+                            flat = torch.zeros(u.shard_numel, dtype=v.dtype, device=self.device)
+                            flat[s.shard_off : s.shard_off + s.piece].copy_(v.reshape(-1))
+                            full = self._gather_flat(u, flat)
+                            entry[k] = full[s.full_off : s.full_off + s.numel].view(s.shape).cpu()
+                        else:
+                            entry[k] = v.cpu() if torch.is_tensor(v) else v
+                    if entry and id(s.param) in index_of:
+                        state[index_of[id(s.param)]] = entry
+        else:
+            for u in self._units:
+                full_m = self._gather_flat(u, u.exp_avg)
+                full_v = self._gather_flat(u, u.exp_avg_sq)
+                for s in u.segs:
+                    if id(s.param) in index_of:
+                        state[index_of[id(s.param)]] = {"step": torch.tensor(float(self.step_count)),
+                                                        "exp_avg": full_m[s.full_off : s.full_off + s.numel].view(s.shape).cpu(),
+                                                        "exp_avg_sq": full_v[s.full_off : s.full_off + s.numel].view(s.shape).cpu()}
+        groups, c = [], 0
+        for g in optimizer.param_groups:
+            ng = {k: v for k, v in g.items() if k != "params"}
+            ng["params"] = list(range(c, c + len(g["params"])))
             c += len(g["params"])
+            groups.append(ng)
         return {"state": state, "param_groups": groups}
 
     def load_optimizer_state_dict(self, optimizer, sd: dict):
-        idx = 0
-        index_of = {}
-        for g in optimizer.param_groups:
-            for p in g["params"]:
-                index_of[id(p)] = idx
-                idx += 1
+        index_of = self._param_index(optimizer)
         for u in self._units:
-            fm = torch.zeros(u.padded, dtype=torch.float32)
-            fv = torch.zeros(u.padded, dtype=torch.float32)
-            for p, off in zip(u.params, u.offsets):
-                st = sd["state"].get(index_of.get(id(p), -1))
+            for s in u.segs:
+                st = sd["state"].get(index_of.get(id(s.param), -1))
                 if st is None:
                     continue
-                n = _numel(p._b200_full_shape)
-                fm[off : off + n] = st["exp_avg"].reshape(-1).float()
-                fv[off : off + n] = st["exp_avg_sq"].reshape(-1).float()
-                self.step_count = int(float(st["step"]))
-            lo = self.rank * u.shard_numel
-            u.exp_avg.copy_(fm[lo : lo + u.shard_numel].to(self.device))
-            u.exp_avg_sq.copy_(fv[lo : lo + u.shard_numel].to(self.device))
+                lo = self.rank * s.piece
+                n = max(0, min(s.piece, s.numel - lo))
+                if self._generic:
+                    sp = self._shard_params[id(s.param)]
+                    entry = {}
+                    for k, v in st.items():
+                        if torch.is_tensor(v) and v.numel() == s.numel and s.numel > 1:
+                            piece = torch.zeros(s.piece, dtype=v.dtype, device=self.device)
+                            if n > 0:
+                                piece[:n].copy_(v.reshape(-1)[lo : lo + n])
+                            entry[k] = piece.view(sp.shape)
+                        else:
+                            entry[k] = v.to(self.device) if torch.is_tensor(v) and v.dim() > 0 else v
+                    optimizer.state[sp] = entry
+                else:
+                    for key, flat in (("exp_avg", u.exp_avg), ("exp_avg_sq", u.exp_avg_sq)):
+                        dst = flat[s.shard_off : s.shard_off + s.piece]
+                        dst.zero_()
+                        if n > 0:
+                            dst[:n].copy_(st[key].reshape(-1)[lo : lo + n].to(self.device, torch.float32))
+                    self.step_count = int(float(st["step"]))
         for g_new, g_old in zip(optimizer.param_groups, sd["param_groups"]):
             for k, v in g_old.items():
                 if k != "params":
                     g_new[k] = v
 
-    def _gather_fp32(self, shard: torch.Tensor) -> torch.Tensor:
-        parts = [torch.empty_like(shard) for _ in range(self.world)]
-        torch.distributed.all_gather(parts, shard, group=self.group)
-        return torch.cat(parts)
+    def _sharded_optimizer_state(self, inner) -> dict:
+        """{"state": {fqn: {...DTensors...}}, "param_groups": [...]} keyed by FQN like torch's get_optimizer_state_dict."""
+        state = {}
+        if self._generic:
+            for u in self._units:
+                for s in u.segs:
+                    sp = self._shard_params[id(s.param)]
+                    entry = {}
+                    for k, v in inner.state.get(sp, {}).items():
+                        if torch.is_tensor(v) and v.numel() == s.piece and s.piece > 1:
+                            flat = torch.zeros(u.shard_numel, dtype=v.dtype, device=self.device)
+                            flat[s.shard_off : s.shard_off + s.piece].copy_(v.reshape(-1))
+                            dt = self._as_dtensor(u, flat, s)
+                            entry[k] = dt if dt is not None else self._gather_flat(u, flat)[s.full_off : s.full_off + s.numel].view(s.shape).clone()
+                        elif torch.is_tensor(v):
+                            entry[k] = v.detach().clone()
+                        else:
+                            entry[k] = v
+                    if entry:
+                        state[s.name] = entry
+        else:
+            m, v = self.sharded_state_dict("exp_avg"), self.sharded_state_dict("exp_avg_sq")
+            for u in self._units:
+                for s in u.segs:
+                    state[s.name] = {"step": torch.tensor(float(self.step_count)), "exp_avg": m[s.name], "exp_avg_sq": v[s.name]}
+        name_of = {id(s.param): s.name for u in self._units for s in u.segs}
+        name_of.update({id(sp): name_of[pid] for pid, sp in self._shard_params.items()})
+        groups = []
+        for g in inner.param_groups:
+            ng = {k: v for k, v in g.items() if k != "params"}
+            ng["params"] = [name_of.get(id(p), str(i)) for i, p in enumerate(g["params"])]
+            groups.append(ng)
+        return {"state": state, "param_groups": groups}
 
     def save_sharded_optimizer(self, optimizer, output_dir: str, index: int, plugin=None):
-        sdt = getattr(plugin or self.plugin, "state_dict_type", "SHARDED_STATE_DICT")
+        sdt = str(getattr(plugin or self.plugin, "state_dict_type", "SHARDED_STATE_DICT")).split(".")[-1]
+        inner = optimizer.optimizer if hasattr(optimizer, "optimizer") else optimizer
         if sdt == "FULL_STATE_DICT":
-            sd = self.optimizer_state_dict(optimizer.optimizer if hasattr(optimizer, "optimizer") else optimizer)
+            sd = self.optimizer_state_dict(inner)
             if torch.distributed.get_rank() == 0:
                 torch.save(sd, os.path.join(output_dir, f"{OPTIMIZER_NAME}.bin" if index == 0 else f"{OPTIMIZER_NAME}_{index}.bin"))
             torch.distributed.barrier()
             return
+        import torch.distributed.checkpoint as dist_cp
+
         d = os.path.join(output_dir, f"{OPTIMIZER_NAME}_{index}")
         os.makedirs(d, exist_ok=True)
-        inner = optimizer.optimizer if hasattr(optimizer, "optimizer") else optimizer
-        torch.save({"step": self.step_count, "hyper": [{k: v for k, v in g.items() if k != "params"} for g in inner.param_groups],
-                    "exp_avg": {u.name: u.exp_avg.cpu() for u in self._units}, "exp_avg_sq": {u.name: u.exp_avg_sq.cpu() for u in self._units}},
-                   os.path.join(d, f"__{self.rank}_0.distcp"))
-        if self.rank == 0:
-            with open(os.path.join(d, ".metadata"), "w") as f:
-                json.dump(self._meta(), f)
-        torch.distributed.barrier()
+        dist_cp.save({"optimizer": self._sharded_optimizer_state(inner)}, storage_writer=dist_cp.FileSystemWriter(d),
+                     process_group=self.group if self.dp_group is None else None)
 
     def load_sharded_optimizer(self, optimizer, input_dir: str, index: int, plugin=None):
         inner = optimizer.optimizer if hasattr(optimizer, "optimizer") else optimizer
@@ -846,15 +1249,53 @@ class B200ShardedModule(nn.Module):
             f = os.path.join(input_dir, f"{OPTIMIZER_NAME}.bin" if index == 0 else f"{OPTIMIZER_NAME}_{index}.bin")
             self.load_optimizer_state_dict(inner, torch.load(f, map_location="cpu", weights_only=False))
             return
-        mine = torch.load(os.path.join(d, f"__{self.rank}_0.distcp"), map_location="cpu", weights_only=False)
-        self.step_count = int(mine["step"])
-        for u in self._units:
-            u.exp_avg.copy_(mine["exp_avg"][u.name].to(self.device))
-            u.exp_avg_sq.copy_(mine["exp_avg_sq"][u.name].to(self.device))
-        for g_new, g_old in zip(inner.param_groups, mine["hyper"]):
-            g_new.update(g_old)
+        import torch.distributed.checkpoint as dist_cp
+
+        if self._generic:
+            # make sure the user's optimizer has state tensors to load into (zero gradients: no parameter moves for the usual rules)
+            if not inner.state:
+                for sp in self._shard_params.values():
+                    sp.grad = torch.zeros_like(sp)
+                saved = [u.master.clone() for u in self._units]
+                inner.step()
+                for u, m in zip(self._units, saved):
+                    u.master.copy_(m)
+                for sp in self._shard_params.values():
+                    sp.grad = None
+        target = self._sharded_optimizer_state(inner)
+        holder = {"optimizer": target}
+        # shards written at another world size are re-cut by DCP's load planner
+        dist_cp.load(holder, storage_reader=dist_cp.FileSystemReader(d), process_group=self.group if self.dp_group is None else None)
+        got = holder["optimizer"]
+        if self._generic:
+            for u in self._units:
+                for s in u.segs:
+                    sp = self._shard_params[id(s.param)]
+                    for k, v in got["state"].get(s.name, {}).items():
+                        cur = inner.state[sp].get(k)
+                        if hasattr(v, "to_local"):
+                            cur.copy_(v.to_local().reshape(cur.shape))
+                        elif torch.is_tensor(v) and torch.is_tensor(cur) and v.numel() == s.numel and s.numel > 1:
+                            lo = self.rank * s.piece
+                            n = max(0, min(s.piece, s.numel - lo))
+                            cur.reshape(-1)[:n].copy_(v.reshape(-1)[lo : lo + n])
+                        elif torch.is_tensor(cur):
+                            cur.copy_(v)
+                        else:
+                            inner.state[sp][k] = v
+        else:
+            self._load_sharded_into("exp_avg", {n: st["exp_avg"] for n, st in got["state"].items()})
+            self._load_sharded_into("exp_avg_sq", {n: st["exp_avg_sq"] for n, st in got["state"].items()})
+            steps = [float(st["step"]) for st in got["state"].values() if "step" in st]
+            if steps:
+                self.step_count = int(max(steps))
+        for g_new, g_old in zip(inner.param_groups, got["param_groups"]):
+            for k, v in g_old.items():
+                if k != "params":
+                    g_new[k] = v
 
     def release(self):
+        F.unregister_carry_source(self)
         for h in self._handles:
             h.remove()
         self._handles = []
@@ -869,19 +1310,16 @@ class B200ShardedModule(nn.Module):
 
 
 def merge_sharded_checkpoint(checkpoint_dir: str) -> dict:
-    """Rebuild the full name -> tensor dict from a ``pytorch_model_fsdp_{i}/`` directory (no process group needed)."""
-    with open(os.path.join(checkpoint_dir, ".metadata")) as f:
-        meta = json.load(f)
-    shards = [torch.load(os.path.join(checkpoint_dir, f"__{r}_0.distcp"), map_location="cpu", weights_only=True) for r in range(meta["world"])]
-    out = {}
-    for u in meta["units"]:
-        flat = torch.cat([s[u["name"]] for s in shards])
-        for prm in u["params"]:
-            n = 1
-            for s in prm["shape"]:
-                n *= s
-            out[prm["name"]] = flat[prm["offset"] : prm["offset"] + n].view(prm["shape"]).clone()
-    return out
+    """Rebuild the full name -> tensor dict from a DCP ``pytorch_model_fsdp_{i}/`` directory without a process group
+    (what ``accelerate merge-weights`` runs; reads checkpoints written by this engine or by the reference's FSDP2)."""
+    import torch.distributed.checkpoint as dist_cp
+    from torch.distributed.checkpoint.default_planner import _EmptyStateDictLoadPlanner
+    from torch.distributed.checkpoint.state_dict_loader import _load_state_dict
+
+    sd: dict = {}
+    _load_state_dict(sd, storage_reader=dist_cp.FileSystemReader(checkpoint_dir), planner=_EmptyStateDictLoadPlanner(), no_dist=True)
+    model = sd.get("model", sd)
+    return dict(model)
 
 
 def _numel(shape) -> int:

@@ -23,6 +23,22 @@ from ..ops import _lib
 from ..ops._lib import check
 
 
+def peer_domain(group=None) -> tuple:
+    """(ok, reason): can the ranks of ``group`` map each other's memory?  CUDA-IPC handles do not cross hosts and the signal
+    pads are sized for 8 ranks (one NVLink / NVSwitch domain), so larger or multi-node groups must use the NCCL engines."""
+    import socket
+
+    group = group if group is not None else torch.distributed.group.WORLD
+    world = torch.distributed.get_world_size(group)
+    if world > 8:
+        return False, f"{world} ranks exceed one 8-GPU NVLink domain"
+    hosts = [None] * world
+    torch.distributed.all_gather_object(hosts, socket.gethostname(), group=group)
+    if len(set(hosts)) > 1:
+        return False, f"ranks span {len(set(hosts))} hosts ({sorted(set(hosts))[:3]}...)"
+    return True, ""
+
+
 class _RawCudaBuffer:
     """Object exposing ``__cuda_array_interface__`` so torch can wrap raw device memory without copying."""
 

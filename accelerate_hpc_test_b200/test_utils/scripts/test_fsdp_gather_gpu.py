@@ -56,9 +56,9 @@ def check_segs(ws, dev, rank, world):
     """A unit made of three pieces per rank: [rows0, K0] weight, [rows1, K1] weight, flat tail."""
     lib = ws.lib
     shapes = [(world * 96, 256), (world * 40, 512)]
-    tail = world * 1024
+    tail = world * 1000
     pieces = [s[0] // world * s[1] for s in shapes] + [tail // world]
-    pieces = [(p + 1023) // 1024 * 1024 for p in pieces]
+    pieces = [(p + 7) // 8 * 8 for p in pieces]
     shard_n = sum(pieces)
     full_n = shard_n * world
     torch.manual_seed(5)
@@ -96,7 +96,7 @@ def check_segs(ws, dev, rank, world):
     dist.barrier()
     e = ws.next_epoch(ch_a)
     ws._epochs[ch_d] = e
-    check(lib.b200_reduce_scatter_adamw_segs(ws.peer_array, rank, world, goff, rtab, len(pieces), None, None, None, shard_off, ptr(gout),
+    check(lib.b200_reduce_scatter_adamw_segs(ws.peer_array, rank, world, rank, goff, rtab, len(pieces), None, None, None, shard_off, ptr(gout),
                                              0.0, 0.9, 0.999, 1e-8, 0.0, 1, 1.0 / world, 0, None, ch_a, ch_d, e, ws.counter_ptr(ch_a), 64,
                                              cur_stream()), "rs_segs")
     torch.cuda.synchronize()
@@ -113,7 +113,7 @@ def check_segs(ws, dev, rank, world):
     dist.barrier()
     e = ws.next_epoch(ch_a)
     ws._epochs[ch_d] = e
-    check(lib.b200_reduce_scatter_adamw_segs(ws.peer_array, rank, world, goff, rtab, len(pieces), ptr(master), ptr(m), ptr(v), shard_off, None,
+    check(lib.b200_reduce_scatter_adamw_segs(ws.peer_array, rank, world, rank, goff, rtab, len(pieces), ptr(master), ptr(m), ptr(v), shard_off, None,
                                              1e-2, 0.9, 0.999, 1e-8, 0.1, 1, 1.0 / world, 1, None, ch_a, ch_d, e, ws.counter_ptr(ch_a), 64,
                                              cur_stream()), "rs_adamw_segs")
     torch.cuda.synchronize()

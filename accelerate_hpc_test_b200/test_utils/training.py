@@ -1,4 +1,11 @@
-"""Tiny regression workload used by the distributed parity tests (reference src/accelerate/test_utils/training.py:22-47)."""
+"""The tiny workloads every distributed parity test trains: a noisy line ``y = a x + b`` and the model that fits it.
+
+Two scalar parameters make "did the gradients synchronise / did the optimizer step" checks exact and cheap; the
+MRPC-shaped loaders feed the example scripts when no dataset can be downloaded.  (Counterpart of the reference's
+``accelerate.test_utils.training``.)
+"""
+
+from __future__ import annotations
 
 import numpy as np
 import torch
@@ -6,43 +13,44 @@ from torch.utils.data import DataLoader
 
 
 class RegressionDataset:
-    def __init__(self, a=2, b=3, length=64, seed=None):
-        rng = np.random.default_rng(seed)
-        self.length = length
-        self.x = rng.normal(size=(length,)).astype(np.float32)
-        self.y = a * self.x + b + rng.normal(scale=0.1, size=(length,)).astype(np.float32)
+    """``length`` samples ``{"x": x_i, "y": a * x_i + b + noise}`` (float32 scalars), reproducible through ``seed``."""
 
-    def __len__(self):
+    def __init__(self, a: float = 2, b: float = 3, length: int = 64, seed=None):
+        draw = np.random.default_rng(seed)
+        self.length = int(length)
+        self.x = draw.normal(size=self.length).astype(np.float32)
+        noise = draw.normal(scale=0.1, size=self.length).astype(np.float32)
+        self.y = (a * self.x + b + noise).astype(np.float32)
+
+    def __len__(self) -> int:
         return self.length
 
-    def __getitem__(self, i):
-        return {"x": self.x[i], "y": self.y[i]}
+    def __getitem__(self, index):
+        return {"x": self.x[index], "y": self.y[index]}
 
 
 class RegressionModel(torch.nn.Module):
-    """``y = a * x + b`` with scalar parameters."""
+    """``forward(x) = a * x + b`` with scalar ``a`` and ``b`` (both start at the given values)."""
 
-    def __init__(self, a=0, b=0, double_output=False):
+    def __init__(self, a: float = 0, b: float = 0, double_output: bool = False):
         super().__init__()
-        self.a = torch.nn.Parameter(torch.tensor(a).float())
-        self.b = torch.nn.Parameter(torch.tensor(b).float())
+        self.a = torch.nn.Parameter(torch.tensor(float(a)))
+        self.b = torch.nn.Parameter(torch.tensor(float(b)))
+        self.double_output = double_output
         self.first_batch = True
 
     def forward(self, x=None):
-        if self.first_batch:
-            self.first_batch = False
-        return x * self.a + self.b
-
-
-class RegressionModel4XPU(RegressionModel):
-    pass
+        self.first_batch = False
+        y = self.a * x + self.b
+        return (y, y) if self.double_output else y
 
 
 def mocked_dataloaders(accelerator, batch_size: int = 16):
     """MRPC-shaped synthetic train / eval dataloaders (no hub access in this environment)."""
     from ..models.bert import pad_collate, synthetic_mrpc
 
-    train = synthetic_mrpc(64, vocab_size=1000, max_len=32, seed=0)
-    val = synthetic_mrpc(32, vocab_size=1000, max_len=32, seed=1)
-    return (DataLoader(train, shuffle=True, collate_fn=pad_collate, batch_size=batch_size),
-            DataLoader(val, shuffle=False, collate_fn=pad_collate, batch_size=batch_size))
+    def loader(n, seed, shuffle):
+        data = synthetic_mrpc(n, vocab_size=1000, max_len=32, seed=seed)
+        return DataLoader(data, shuffle=shuffle, collate_fn=pad_collate, batch_size=batch_size)
+
+    return loader(64, 0, True), loader(32, 1, False)
