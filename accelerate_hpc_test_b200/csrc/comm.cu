@@ -406,6 +406,143 @@ reduce_scatter_adamw_kernel(Peers peers, int rank, int world, long long grad_off
   }
 }
 
+// ------------------------------------------------------------------------------ NVLS (in-switch) variants
+// When the symmetric buffers are bound to an NVLink multicast object (parallel/symm.py takes the mapping from
+// torch.distributed._symmetric_memory), `mc` is the multicast alias of the same buffer: a multimem.ld_reduce through it
+// returns the SUM of the addressed bytes of every rank - the NVSwitch adds them - and a multimem.st stores to every rank.
+// Per reduced byte the GPU then receives 1 stream instead of `world`, and nothing is staged in shared memory.
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st_bf16x8(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
+// Reduce-scatter + AdamW with the reduction done by the switch.  Same contract as reduce_scatter_adamw_kernel; every thread
+// owns 8 consecutive shard elements per iteration: one multimem.ld_reduce (16 B) brings their sum over all ranks.
+static constexpr int NVLS_UNROLL = 4;
+__global__ void __launch_bounds__(512)
+reduce_scatter_adamw_nvls_kernel(Peers peers, const uint8_t* __restrict__ mc, int rank, int world, long long grad_off, long long n,
+                                 RsSegs segs, float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
+                                 long long param_off, float* __restrict__ grad_out, AdamArgs a, int do_adam,
+                                 const float* __restrict__ clip_coef, int ch_arrive, int ch_done, uint32_t epoch,
+                                 uint32_t* __restrict__ counter) {
+  if (blockIdx.x == 0) signal_all(peers, rank, world, ch_arrive, epoch);
+  wait_all(peers, rank, world, ch_arrive, epoch);
+  const float gs = a.grad_scale * (clip_coef ? *clip_coef : 1.f);
+  __nv_bfloat16* shard = reinterpret_cast<__nv_bfloat16*>(peers.base[rank] + param_off);
+  const long long nvec = n >> 3;  // every segment length is a multiple of 8
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * NVLS_UNROLL) {
+    uint4 sums[NVLS_UNROLL];
+    long long e[NVLS_UNROLL];
+#pragma unroll
+    for (int u = 0; u < NVLS_UNROLL; ++u) {
+      const long long i = i0 + u * stride;
+      e[u] = -1;
+      if (i < nvec) {
+        const long long e0 = i << 3;
+        int si = 0;
+        while (si + 1 < segs.n && e0 >= segs.start[si] + segs.len[si]) ++si;
+        const long long src = segs.full[si] + (long long)segs.slice * segs.len[si] + (e0 - segs.start[si]);
+        sums[u] = multimem_ld_reduce_bf16x8(mc + grad_off + (src << 1));
+        e[u] = e0;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < NVLS_UNROLL; ++u) {
+      if (e[u] < 0) continue;
+      const long long e0 = e[u];
+      float g[8];
+      float2 t;
+      t = bf2_to_f2(sums[u].x); g[0] = t.x * gs; g[1] = t.y * gs;
+      t = bf2_to_f2(sums[u].y); g[2] = t.x * gs; g[3] = t.y * gs;
+      t = bf2_to_f2(sums[u].z); g[4] = t.x * gs; g[5] = t.y * gs;
+      t = bf2_to_f2(sums[u].w); g[6] = t.x * gs; g[7] = t.y * gs;
+      if (do_adam == 1) {
+        const float4 m0 = *reinterpret_cast<const float4*>(m + e0), m1 = *reinterpret_cast<const float4*>(m + e0 + 4);
+        const float4 v0 = *reinterpret_cast<const float4*>(v + e0), v1 = *reinterpret_cast<const float4*>(v + e0 + 4);
+        const float4 p0 = *reinterpret_cast<const float4*>(master + e0), p1 = *reinterpret_cast<const float4*>(master + e0 + 4);
+        float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+        float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+        float pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          mm[k] = mm[k] * a.beta1 + (1.f - a.beta1) * g[k];
+          vv[k] = vv[k] * a.beta2 + (1.f - a.beta2) * g[k] * g[k];
+          float p = pp[k] * (1.f - a.lr * a.weight_decay);
+          p -= (a.lr / a.bias_c1) * (mm[k] / (sqrtf(vv[k] / a.bias_c2) + a.eps));
+          pp[k] = p;
+        }
+        *reinterpret_cast<float4*>(m + e0) = make_float4(mm[0], mm[1], mm[2], mm[3]);
+        *reinterpret_cast<float4*>(m + e0 + 4) = make_float4(mm[4], mm[5], mm[6], mm[7]);
+        *reinterpret_cast<float4*>(v + e0) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+        *reinterpret_cast<float4*>(v + e0 + 4) = make_float4(vv[4], vv[5], vv[6], vv[7]);
+        *reinterpret_cast<float4*>(master + e0) = make_float4(pp[0], pp[1], pp[2], pp[3]);
+        *reinterpret_cast<float4*>(master + e0 + 4) = make_float4(pp[4], pp[5], pp[6], pp[7]);
+        uint4 o;
+        o.x = f2_to_bf2(pp[0], pp[1]); o.y = f2_to_bf2(pp[2], pp[3]);
+        o.z = f2_to_bf2(pp[4], pp[5]); o.w = f2_to_bf2(pp[6], pp[7]);
+        *reinterpret_cast<uint4*>(shard + e0) = o;
+      } else {
+        *reinterpret_cast<float4*>(grad_out + e0) = make_float4(g[0], g[1], g[2], g[3]);
+        *reinterpret_cast<float4*>(grad_out + e0 + 4) = make_float4(g[4], g[5], g[6], g[7]);
+      }
+    }
+  }
+  if (last_cta(counter)) {
+    __threadfence_system();
+    signal_all(peers, rank, world, ch_done, epoch);
+    wait_all(peers, rank, world, ch_done, epoch);
+  }
+}
+
+// One-pass in-place bf16 all-reduce: rank r sums slice r of every rank inside the switch (multimem.ld_reduce), scales it and
+// writes it back to every rank with one multicast store (multimem.st).  n % (8 * world) == 0.
+__global__ void __launch_bounds__(512)
+allreduce_nvls_kernel(Peers peers, uint8_t* __restrict__ mc, int rank, int world, long long off, long long n, float scale,
+                      int ch_arrive, int ch_done, uint32_t epoch, uint32_t* __restrict__ counter) {
+  if (blockIdx.x == 0) signal_all(peers, rank, world, ch_arrive, epoch);
+  wait_all(peers, rank, world, ch_arrive, epoch);
+  const long long nvec = (n >> 3) / world;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  uint8_t* base = mc + off + (((long long)rank * nvec) << 4);
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * NVLS_UNROLL) {
+    uint4 sums[NVLS_UNROLL];
+#pragma unroll
+    for (int u = 0; u < NVLS_UNROLL; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < nvec) sums[u] = multimem_ld_reduce_bf16x8(base + (i << 4));
+    }
+#pragma unroll
+    for (int u = 0; u < NVLS_UNROLL; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= nvec) continue;
+      uint4 o = sums[u];
+      if (scale != 1.f) {
+        float2 t;
+        t = bf2_to_f2(o.x); o.x = f2_to_bf2(t.x * scale, t.y * scale);
+        t = bf2_to_f2(o.y); o.y = f2_to_bf2(t.x * scale, t.y * scale);
+        t = bf2_to_f2(o.z); o.z = f2_to_bf2(t.x * scale, t.y * scale);
+        t = bf2_to_f2(o.w); o.w = f2_to_bf2(t.x * scale, t.y * scale);
+      }
+      multimem_st_bf16x8(base + (i << 4), o);
+    }
+  }
+  if (last_cta(counter)) {
+    __threadfence_system();
+    signal_all(peers, rank, world, ch_done, epoch);
+    wait_all(peers, rank, world, ch_done, epoch);  // every rank's stores to my buffer have been issued and fenced
+  }
+}
+
 // ------------------------------------------------------------------------------ all-reduce (two-shot, in place)
 // buf (at byte offset `off` of every rank's symmetric buffer) holds n elements.  Rank r reduces
 // slice r of all ranks, scales it, and stores the result back into slice r of all ranks.
@@ -850,6 +987,53 @@ B200_API int b200_allreduce_tma(const void* const* peer_ptrs, int rank, int worl
   B200_CHECK_LAUNCH();
   allgather_inplace_kernel<<<ctas, 32, AG_SMEM, (cudaStream_t)stream>>>(P, rank, world, off, slice * 2, ch_done, epoch,
                                                                        (uint32_t*)counter + 1);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// NVLS versions (see the kernels): mc = multicast alias of the symmetric buffers (0 / NULL: not available -> B200_ERR_UNSUPPORTED)
+B200_API int b200_reduce_scatter_adamw_nvls(const void* const* peer_ptrs, const void* mc, int rank, int world, int slice,
+                                            long long grad_off, const long long* segs, int nseg, void* master, void* m, void* v,
+                                            long long param_off, void* grad_out, float lr, float beta1, float beta2, float eps,
+                                            float weight_decay, int step, float grad_scale, int do_adam, const void* clip_coef,
+                                            int ch_arrive, int ch_done, unsigned epoch, void* counter, int ctas, void* stream) {
+  if (mc == nullptr) return B200_ERR_UNSUPPORTED;
+  if (nseg < 1 || nseg > MAX_SEGS || grad_off % 16 || param_off % 16 || (do_adam != 0 && do_adam != 1)) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  RsSegs sg;
+  memset(&sg, 0, sizeof(sg));
+  sg.n = nseg;
+  sg.slice = slice;
+  long long n = 0;
+  for (int i = 0; i < nseg; ++i) {
+    sg.start[i] = segs[3 * i]; sg.full[i] = segs[3 * i + 1]; sg.len[i] = segs[3 * i + 2];
+    if (sg.start[i] != n || sg.len[i] <= 0 || (sg.len[i] % 8) || (sg.full[i] % 8)) return B200_ERR_BAD_ARG;
+    n += sg.len[i];
+  }
+  AdamArgs a{lr, beta1, beta2, eps, weight_decay, 1.f - powf(beta1, (float)step), 1.f - powf(beta2, (float)step),
+             grad_scale};
+  if (ctas <= 0) ctas = 148;
+  reduce_scatter_adamw_nvls_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(
+      P, (const uint8_t*)mc, rank, world, grad_off, n, sg, (float*)master, (float*)m, (float*)v, param_off, (float*)grad_out, a,
+      do_adam, (const float*)clip_coef, ch_arrive, ch_done, epoch, (uint32_t*)counter);
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+B200_API int b200_allreduce_nvls(const void* const* peer_ptrs, void* mc, int rank, int world, long long off, long long n,
+                                 float scale, int ch_arrive, int ch_done, unsigned epoch, void* counter, int ctas, void* stream) {
+  if (mc == nullptr) return B200_ERR_UNSUPPORTED;
+  if (off % 16 || n % ((long long)world * 8)) return B200_ERR_BAD_ARG;
+  Peers P;
+  int rc = load_peers(P, peer_ptrs, world);
+  if (rc) return rc;
+  if (ctas <= 0) ctas = 148;
+  allreduce_nvls_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(P, (uint8_t*)mc, rank, world, off, n, scale, ch_arrive, ch_done,
+                                                               epoch, (uint32_t*)counter);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;

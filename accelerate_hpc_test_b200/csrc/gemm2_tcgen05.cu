@@ -111,7 +111,7 @@ __device__ __forceinline__ void ag_wait_rows(const Params& p, int r0, int r1) {
   const int s_lo = r0 / p.ag_rows;
   const int s_hi = min(r1 / p.ag_rows, p.ag_world - 1);
   for (int sh = s_lo; sh <= s_hi; ++sh) {
-    if (sh == p.ag_rank) continue;
+    if (sh == p.ag_rank && p.ag_mode == 0) continue;
     uint32_t spins = 0;
     while (*reinterpret_cast<volatile unsigned long long*>(p.ag_ready + sh) < p.ag_expect) {
       __nanosleep(32);
@@ -267,7 +267,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         const int n0 = n_t * BN + (int)cta * BNH;
         // rows [m0, m0 + BM) of A (mode 0) / rows [n0, n0 + BNH) of B (mode 1) must have arrived
         if (FUSE_AG && p.ag_world > 1 && p.ag_mode == 0 && m0 < p.M) ag_wait_rows(p, m0, m0 + BM - 1);
-        if (FUSE_AG && p.ag_world > 1 && p.ag_mode == 1 && n0 < p.N) ag_wait_rows(p, n0, min(n0 + BNH, p.N) - 1);
+        if (FUSE_AG && p.ag_mode == 1 && n0 < p.N) ag_wait_rows(p, n0, min(n0 + BNH, p.N) - 1);
         // mode 2: the reduction runs over the rows of the gathered matrix; every tile starts in my own piece
         const int kb_start = (FUSE_AG && p.ag_mode == 2) ? (int)(((long long)p.ag_rank * p.ag_rows) / BKE) % num_k_blocks : 0;
         int k_piece = -1;
@@ -280,7 +280,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
           uint8_t* sa = smem_a + stage * A_BYTES;
           uint8_t* sb = smem_b + stage * B_BYTES;
           const int k0 = kb * BKE;
-          if (FUSE_AG && p.ag_mode == 2 && p.ag_world > 1) {
+          if (FUSE_AG && p.ag_mode == 2) {
             const int k1 = min(k0 + BKE, p.K) - 1;
             if (k1 / p.ag_rows != k_piece || k0 / p.ag_rows != k_piece) {
               ag_wait_rows(p, k0, k1);
@@ -336,16 +336,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
     }
   } else if (FUSE_AG && warp == 3) {
     // ================================ all-gather warp (every CTA moves its share of the chunks) ================================
-    if (p.ag_world > 1 && elect_one()) {
+    if ((p.ag_world > 1 || p.ag_mode != 0) && elect_one()) {
       const long long shard_bytes = p.ag_shard_bytes;
       const long long cps = (shard_bytes + AGG_CHUNK - 1) / AGG_CHUNK;
-      const long long total = cps * (p.ag_world - 1);
+      // weight gather (modes 1-3): slot 0 is my own piece (a local copy out of my shard), then the peers; activation gather
+      // (mode 0): the caller already placed my rows
+      const int first_slot = p.ag_mode == 0 ? 1 : 0;
+      const long long total = cps * (p.ag_world - first_slot);
       const long long n = (total > blockIdx.x) ? (total - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
       auto locate = [&](long long k, const uint8_t*& src, uint8_t*& dst, uint32_t& bytes, int& peer) {
         const long long g = blockIdx.x + k * (long long)gridDim.x;
         const int slot = (int)(g / cps);
         const long long c = g - (long long)slot * cps;
-        peer = (p.ag_rank + 1 + slot) % p.ag_world;
+        peer = (p.ag_rank + first_slot + slot) % p.ag_world;
         const long long o = c * AGG_CHUNK;
         const long long left = shard_bytes - o;
         bytes = (uint32_t)(left < AGG_CHUNK ? left : AGG_CHUNK);
@@ -654,8 +657,8 @@ B200_API int b200_gemm2_bf16_allgather_a(const void* const* peer_ptrs, int rank,
 
 // GEMM with a weight-gather job riding on it (FSDP2 parameter all-gather).  Same GEMM contract as
 // b200_gemm2_bf16.  Every rank keeps its dim-0 piece (piece_bytes) of a weight at byte offset src_off of its symmetric buffer;
-// warp 3 of every CTA pulls the peers' pieces into gathered + q * piece_bytes (q = owning rank; the caller has already put its own
-// piece there) while the tensor cores run.  mode 1: the weight is this GEMM's B operand, stored [N, K] (forward) - n-tiles wait
+// warp 3 of every CTA pulls the peers' pieces into gathered + q * piece_bytes (q = owning rank; this rank's own piece is copied
+// out of its shard the same way, first) while the tensor cores run.  mode 1: the weight is this GEMM's B operand, stored [N, K] (forward) - n-tiles wait
 // for the piece that holds their rows and the tile order starts in this rank's piece; mode 2: the weight is B stored [K, N]
 // (b_mn_major, dgrad) - k-blocks wait for their piece, every tile starts its reduction in this rank's piece; mode 3: the
 // gathered buffer is for a later kernel of the same stream, nothing waits.  piece_rows = rows of the weight per rank (modes 1, 2).

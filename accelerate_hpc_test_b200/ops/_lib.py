@@ -85,6 +85,8 @@ _SIGNATURES = {
     "b200_allgather_pull": [P, I, I, L, L, P, I, U, I, P],
     "b200_allgather_pull_segs": [P, I, I, L, P, I, P, I, U, I, P],
     "b200_reduce_scatter_adamw_segs": [P, I, I, I, L, P, I, P, P, P, L, P, F, F, F, F, F, I, F, I, P, I, I, U, P, I, P],
+    "b200_reduce_scatter_adamw_nvls": [P, P, I, I, I, L, P, I, P, P, P, L, P, F, F, F, F, F, I, F, I, P, I, I, U, P, I, P],
+    "b200_allreduce_nvls": [P, P, I, I, L, L, F, I, I, U, P, I, P],
     "b200_reduce_scatter_adamw": [P, I, I, L, L, P, P, P, L, P, F, F, F, F, F, I, F, I, P, I, I, U, P, I, P],
     "b200_allreduce": [P, I, I, L, L, I, F, I, I, U, P, I, P],
     "b200_allreduce_tma": [P, I, I, L, L, F, I, I, I, U, P, I, P],

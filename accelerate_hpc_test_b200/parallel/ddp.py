@@ -94,7 +94,8 @@ class B200DataParallel(nn.Module):
             self._own_workspace = False
         self.ws = workspace
         self.comm_stream = torch.cuda.Stream(device=self.device)
-        self._tma_allreduce = os.environ.get("ACCELERATE_B200_ALLREDUCE", "tma") == "tma"
+        self._tma_allreduce = os.environ.get("ACCELERATE_B200_ALLREDUCE", "nvls") in ("tma", "nvls")
+        self._nvls_allreduce = os.environ.get("ACCELERATE_B200_ALLREDUCE", "nvls") == "nvls"
         self._buckets: list[_Bucket] = []
         self._param_slot: dict[int, tuple[_Bucket, int]] = {}
         self._build_buckets(params)
@@ -205,7 +206,10 @@ class B200DataParallel(nn.Module):
         ev.record(torch.cuda.current_stream(self.device))
         self.comm_stream.wait_event(ev)
         with torch.cuda.stream(self.comm_stream):
-            if b.dtype == torch.bfloat16 and self._tma_allreduce:
+            if b.dtype == torch.bfloat16 and self.ws.has_multicast and self._nvls_allreduce:
+                # the NVSwitch sums the 8 copies and multicasts the result: one pass over the bucket, no shared-memory staging
+                self.ws.allreduce_nvls_(b.offset_bytes, b.padded, 1.0 / self.world, b.ch_arrive, b.ch_done, stream=self.comm_stream)
+            elif b.dtype == torch.bfloat16 and self._tma_allreduce:
                 # TMA engine end to end (reduce my slice from all peers, then pull the other slices): ~1.5x the LSU kernel
                 self.ws.allreduce_tma_(b.offset_bytes, b.padded, 1.0 / self.world, (b.ch_arrive, b.ch_mid, b.ch_done), stream=self.comm_stream)
             else:

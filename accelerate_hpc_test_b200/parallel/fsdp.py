@@ -268,6 +268,7 @@ class B200ShardedModule(nn.Module):
         self._carry: list[_GatherJob] = []  # gathers waiting for a GEMM to ride on
         self._fuse_gather = os.environ.get("ACCELERATE_B200_FSDP_FUSED_GATHER", "1") != "0"
         self._fwd_gather = os.environ.get("ACCELERATE_B200_FSDP_FWD_GATHER", "jit")  # jit | carry
+        self._early_root_rs = os.environ.get("ACCELERATE_B200_FSDP_EARLY_ROOT_RS", "1") != "0"
         self._build_units()
         self._allocate()
         self._install_hooks()
@@ -353,11 +354,13 @@ class B200ShardedModule(nn.Module):
             self._ag_peers = (ctypes.c_void_p * self.world)(*[self.ws.peer_bases[ws_ranks.index(g)] for g in shard_ranks])
             self.rs_world = self.ws.world
             self.rs_rank = self.ws.rank
+            self._nvls_rs = self.ws.has_multicast and os.environ.get("ACCELERATE_B200_FSDP_NVLS_RS", "1") != "0"
         else:
             self.ws = None
             self.comm_stream = None
             self.rs_stream = None
             self._ag_peers = None
+            self._nvls_rs = False
             self.rs_world = self.world * (torch.distributed.get_world_size(self.replicate_group) if self.replicate_group is not None else 1)
         meta_init = any(p.device.type == "meta" for u in self._units for p in u.params)
         src = torch.distributed.get_global_rank(self.group, 0)
@@ -469,9 +472,7 @@ class B200ShardedModule(nn.Module):
                 for s in riding:
                     if s.job is None:
                         s.job = _GatherJob(self, u, s)
-                    # my own rows go in place now; the GEMM's gather warp brings the peers'
-                    lo = s.full_off + self.rank * s.piece
-                    u.full[lo : lo + s.piece].copy_(u.shard[s.shard_off : s.shard_off + s.piece])
+                    # the GEMM's gather warp brings every piece, this rank's own included (a local copy out of the shard)
                     s.job.pending = True
                     if carry and not s.job.queued:
                         s.job.queued = True
@@ -652,7 +653,8 @@ class B200ShardedModule(nn.Module):
         u.ready[id(p)] = u.ready.get(id(p), 0) + 1
         if all(u.ready.get(id(q), 0) >= u.expected.get(id(q), 1) for q in u.params):
             # root units too: the LM head's reduce-scatter starts at the top of backward instead of after it
-            self._post_backward(u)
+            if u.module is not None or self._early_root_rs:
+                self._post_backward(u)
 
     def _post_backward(self, u: _Unit):
         """All gradients of ``u`` are in its flat buffer: reduce (+ update) and let go of the parameters."""
@@ -756,6 +758,16 @@ class B200ShardedModule(nn.Module):
                     e = self.ws.next_epoch(u.ch_arrive)
                     self.ws._epochs[u.ch_done] = e
                     fo = base * 4
+                    if self._nvls_rs:
+                        # the switch adds the ranks' gradient pieces: one incoming stream instead of rs_world
+                        check(self.ws.lib.b200_reduce_scatter_adamw_nvls(
+                            self.ws.peer_array, ctypes.c_void_p(self.ws.mc_base), self.rs_rank, self.rs_world, self.rank, u.grad_off, tab, len(part),
+                            ctypes.c_void_p(u.master.data_ptr() + fo), ctypes.c_void_p(u.exp_avg.data_ptr() + fo), ctypes.c_void_p(u.exp_avg_sq.data_ptr() + fo),
+                            u.shard_off + base * 2, ctypes.c_void_p(u.grad_shard.data_ptr() + fo) if not fused else None,
+                            h["lr"], h["beta1"], h["beta2"], h["eps"], h["weight_decay"], self.step_count + 1, scale, int(fused), None,
+                            u.ch_arrive, u.ch_done, e, self.ws.counter_ptr(u.ch_arrive), self.rs_ctas,
+                            ctypes.c_void_p(self.rs_stream.cuda_stream)), "reduce_scatter_adamw_nvls")
+                        continue
                     check(self.ws.lib.b200_reduce_scatter_adamw_segs(
                         self.ws.peer_array, self.rs_rank, self.rs_world, self.rank, u.grad_off, tab, len(part),
                         ctypes.c_void_p(u.master.data_ptr() + fo), ctypes.c_void_p(u.exp_avg.data_ptr() + fo), ctypes.c_void_p(u.exp_avg_sq.data_ptr() + fo),

@@ -1,10 +1,17 @@
 """Symmetric (peer-mapped) device memory: the data plane of the fused collectives.
 
-Every rank ``cudaMalloc`` s one buffer of the same size, exports a CUDA-IPC handle, exchanges the
-handles through ``torch.distributed`` (control plane only) and maps every peer's buffer, so a kernel
-on GPU *r* can ``ld`` / ``st`` any byte of any peer over NVLink.  The first bytes of the buffer are
-the signal pad the kernels order themselves with; the rest is handed out by a bump allocator that
-every rank drives identically, so equal allocations land at equal offsets ("symmetric").
+Every rank owns one buffer of the same size and maps every peer's buffer, so a kernel on GPU *r* can ``ld`` / ``st`` any
+byte of any peer over NVLink.  Two ways to get there, tried in this order:
+
+* **VMM + NVLS multicast** (``torch.distributed._symmetric_memory``: ``cuMemCreate`` allocations exchanged as file
+  descriptors and bound to a ``cuMulticast`` object).  Besides the per-peer addresses this yields ``mc_base``, the
+  *multicast alias* of the buffer: ``multimem.ld_reduce`` through it returns the sum over all ranks computed inside the
+  NVSwitch, ``multimem.st`` stores to all ranks at once (csrc/comm.cu, the ``*_nvls`` kernels).
+* **CUDA IPC** (``cudaMalloc`` + ``cudaIpcGetMemHandle``): peer addresses only, ``mc_base == 0``; used when the first
+  path is not available (``ACCELERATE_B200_SYMM_BACKEND=ipc`` forces it).
+
+The first bytes of the buffer are the signal pad the kernels order themselves with; the rest is handed out by a bump
+allocator that every rank drives identically, so equal allocations land at equal offsets ("symmetric").
 
 There is no reference counterpart: the reference's data plane is NCCL's internal buffers
 (SURVEY.md §5.8).  The kernels that use this memory are in ``csrc/comm.cu``.
@@ -63,6 +70,56 @@ class SymmetricWorkspace:
         self.num_channels = n_channels.value
         self.pad_bytes = (pad.value + 4095) // 4096 * 4096
         self.nbytes = int(nbytes) + self.pad_bytes
+        self.mc_base = 0
+        self._opened = []
+        self._symm_tensor = None
+        self.backend = "ipc"
+        if os.environ.get("ACCELERATE_B200_SYMM_BACKEND", "auto") != "ipc" and self._try_vmm_multicast(group, device):
+            self.backend = "vmm"
+        else:
+            self._alloc_ipc(group, device, lib)
+        self.peer_array = (ctypes.c_void_p * self.world)(*self.peer_bases)
+        self._cursor = self.pad_bytes
+        self._channel_iter = itertools.count(1)
+        self._epochs: dict[int, int] = {}
+        self._counters = torch.zeros(self.num_channels, dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device)
+        torch.distributed.barrier(group=group)
+        self.closed = False
+
+    def _try_vmm_multicast(self, group, device) -> bool:
+        """Allocate through torch's symmetric-memory allocator (VMM handles + NVLS multicast binding).  Every rank must reach
+        the same verdict, so success is agreed on with an all-reduce before anything is kept."""
+        ok, t, hdl = 1, None, None
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+
+            if torch.distributed.get_backend(group) != "nccl":
+                raise RuntimeError("symmetric memory needs an NCCL group")
+            nbytes = (self.nbytes + (1 << 21) - 1) >> 21 << 21
+            t = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+            hdl = symm_mem.rendezvous(t, group)
+            if len(hdl.buffer_ptrs) != self.world:
+                raise RuntimeError("unexpected peer count")
+        except Exception:  # noqa: BLE001 - any failure means: use CUDA IPC instead
+            ok = 0
+        flag = torch.tensor([ok], device=device, dtype=torch.int32)
+        torch.distributed.all_reduce(flag, op=torch.distributed.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 0:
+            del hdl, t
+            return False
+        t.zero_()
+        self._symm_tensor, self._symm_handle = t, hdl
+        self._whole = t[: self.nbytes]
+        self.peer_bases = [int(x) for x in hdl.buffer_ptrs]
+        self.base = self.peer_bases[self.rank]
+        try:
+            self.mc_base = int(hdl.multicast_ptr or 0)
+        except Exception:  # noqa: BLE001
+            self.mc_base = 0
+        return True
+
+    def _alloc_ipc(self, group, device, lib):
         base = ctypes.c_void_p()
         check(lib.b200_symm_alloc(ctypes.byref(base), self.nbytes), "symm_alloc")
         self.base = base.value
@@ -71,7 +128,6 @@ class SymmetricWorkspace:
         handles = [None] * self.world
         torch.distributed.all_gather_object(handles, bytes(handle), group=group)
         self.peer_bases = []
-        self._opened = []
         for r, h in enumerate(handles):
             if r == self.rank:
                 self.peer_bases.append(self.base)
@@ -81,15 +137,11 @@ class SymmetricWorkspace:
             check(lib.b200_ipc_open_handle(buf, ctypes.byref(p)), "ipc_open_handle")
             self.peer_bases.append(p.value)
             self._opened.append(p.value)
-        self.peer_array = (ctypes.c_void_p * self.world)(*self.peer_bases)
         self._whole = torch.as_tensor(_RawCudaBuffer(self.base, self.nbytes), device=device)
-        self._cursor = self.pad_bytes
-        self._channel_iter = itertools.count(1)
-        self._epochs: dict[int, int] = {}
-        self._counters = torch.zeros(self.num_channels, dtype=torch.int32, device=device)
-        torch.cuda.synchronize(device)
-        torch.distributed.barrier(group=group)
-        self.closed = False
+
+    @property
+    def has_multicast(self) -> bool:
+        return self.mc_base != 0 and os.environ.get("ACCELERATE_B200_NVLS", "1") != "0"
 
     # ------------------------------------------------------------------ construction helpers
     @classmethod
@@ -158,6 +210,13 @@ class SymmetricWorkspace:
         check(self.lib.b200_allreduce(self.peer_array, self.rank, self.world, off, numel, int(dtype == torch.bfloat16), float(scale),
                                       ch_arrive, ch_done, e, self.counter_ptr(ch_arrive), ctas, _stream(stream)), "allreduce")
 
+    def allreduce_nvls_(self, off: int, numel: int, scale: float, ch_arrive: int, ch_done: int, ctas: int = 148, stream=None):
+        """In-place bf16 all-reduce with the sum done inside the NVSwitch (needs ``has_multicast``)."""
+        e = self.next_epoch(ch_arrive)
+        self._epochs[ch_done] = e
+        check(self.lib.b200_allreduce_nvls(self.peer_array, ctypes.c_void_p(self.mc_base), self.rank, self.world, off, numel, float(scale),
+                                           ch_arrive, ch_done, e, self.counter_ptr(ch_arrive), ctas, _stream(stream)), "allreduce_nvls")
+
     def allreduce_tma_(self, off: int, numel: int, scale: float, channels, ctas: int = 148, stream=None):
         """In-place bf16 all-reduce on the TMA engine (reduce my slice, then pull the others).  ``channels`` = three channel
         ids reserved for this buffer (arrive / between the phases / done)."""
@@ -181,10 +240,14 @@ class SymmetricWorkspace:
         self.closed = True
         try:
             torch.cuda.synchronize(self.device)
-            for p in self._opened:
-                self.lib.b200_ipc_close_handle(ctypes.c_void_p(p))
             self._whole = None
-            self.lib.b200_symm_free(ctypes.c_void_p(self.base))
+            if self.backend == "vmm":
+                self._symm_handle = None
+                self._symm_tensor = None
+            else:
+                for p in self._opened:
+                    self.lib.b200_ipc_close_handle(ctypes.c_void_p(p))
+                self.lib.b200_symm_free(ctypes.c_void_p(self.base))
         except Exception:  # pragma: no cover
             pass
 

@@ -120,6 +120,51 @@ def check_segs(ws, dev, rank, world):
     assert rel(master, pr) < 1e-3, ("rs_adamw_segs master", rel(master, pr))
     assert rel(shard, pr) < 1e-2, ("rs_adamw_segs shard", rel(shard, pr))
     log(f"reduce_scatter_adamw_segs ok (reduce err {err:.1e})")
+    if not ws.has_multicast:
+        log("NVLS multicast not available on this workspace: skipping the multimem reduce-scatter / all-reduce checks")
+        return
+    # the same reduction done by the switch (multimem.ld_reduce): reduce only, then with AdamW
+    mc = ctypes.c_void_p(ws.mc_base)
+    grad.copy_(g_local)
+    gout.zero_()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e = ws.next_epoch(ch_a)
+    ws._epochs[ch_d] = e
+    check(lib.b200_reduce_scatter_adamw_nvls(ws.peer_array, mc, rank, world, rank, goff, rtab, len(pieces), None, None, None, shard_off, ptr(gout),
+                                             0.0, 0.9, 0.999, 1e-8, 0.0, 1, 1.0 / world, 0, None, ch_a, ch_d, e, ws.counter_ptr(ch_a), 64,
+                                             cur_stream()), "rs_nvls")
+    torch.cuda.synchronize()
+    err = rel(gout, want)
+    assert err < 1e-2 and (gout - want).abs().max().item() < 2e-2 * want.abs().max().item() + 1e-3, ("reduce_scatter_nvls", err)
+    master2 = torch.cat([full_ref[full_off[i] + rank * p : full_off[i] + (rank + 1) * p] for i, p in enumerate(pieces)]).float()
+    m2, v2 = torch.zeros_like(master2), torch.zeros_like(master2)
+    torch.cuda.synchronize()
+    dist.barrier()
+    e = ws.next_epoch(ch_a)
+    ws._epochs[ch_d] = e
+    check(lib.b200_reduce_scatter_adamw_nvls(ws.peer_array, mc, rank, world, rank, goff, rtab, len(pieces), ptr(master2), ptr(m2), ptr(v2), shard_off, None,
+                                             1e-2, 0.9, 0.999, 1e-8, 0.1, 1, 1.0 / world, 1, None, ch_a, ch_d, e, ws.counter_ptr(ch_a), 64,
+                                             cur_stream()), "rs_adamw_nvls")
+    torch.cuda.synchronize()
+    assert rel(master2, pr) < 2e-3, ("rs_adamw_nvls master", rel(master2, pr))
+    log(f"reduce_scatter_adamw_nvls ok (reduce err {err:.1e})")
+    # one-pass NVLS all-reduce, in place
+    n = world * 8 * 4099
+    aoff, abuf = ws.alloc_tensor((n,), torch.bfloat16)
+    src = torch.randn(n, device=dev).to(torch.bfloat16)
+    ref = src.float().clone()
+    dist.all_reduce(ref)
+    ref /= world
+    ca, cd = ws.new_channel(), ws.new_channel()
+    for it in range(3):
+        abuf.copy_(src)
+        torch.cuda.synchronize()
+        dist.barrier()
+        ws.allreduce_nvls_(aoff, n, 1.0 / world, ca, cd)
+        torch.cuda.synchronize()
+        assert rel(abuf, ref) < 2e-2, ("allreduce_nvls", it, rel(abuf, ref))
+    log("allreduce_nvls ok")
 
 
 class WeightGather:
@@ -137,8 +182,7 @@ class WeightGather:
         self.calls = 0
 
     def reset(self):
-        self.full.zero_()
-        self.full[self.rank * self.rows : (self.rank + 1) * self.rows].copy_(self.piece)
+        self.full.zero_()  # the gather warp also places this rank's own piece
 
     def gemm(self, a, b, mode, out=None, b_mn=False, a_mn=False, gathered=None):
         """GEMM(a, b) carrying the gather of this weight (mode 1/2: b is self.full)."""
@@ -241,16 +285,75 @@ def bench_gemm_gather(ws, dev, rank, world, results):
         del wg
 
 
+def bench_reductions(ws, dev, rank, world, results):
+    """All-reduce (25 MB DDP bucket, 512 MiB) and reduce-scatter+AdamW of one Llama-3-8B layer: TMA pull, NVLS, NCCL."""
+    lib = ws.lib
+    for label, nbytes in (("allreduce_25MB", 25 * 2**20), ("allreduce_512MiB", 512 * 2**20)):
+        n = nbytes // 2 // (world * 8) * (world * 8)
+        off, buf = ws.alloc_tensor((n,), torch.bfloat16)
+        buf.normal_()
+        chans = [ws.new_channel() for _ in range(3)]
+        ref = torch.randn(n, device=dev).to(torch.bfloat16)
+        with sample_clocks() as clk:
+            t_tma = timed(lambda: ws.allreduce_tma_(off, n, 1.0 / world, chans))
+            t_nvls = timed(lambda: ws.allreduce_nvls_(off, n, 1.0 / world, chans[0], chans[2])) if ws.has_multicast else float("nan")
+            t_nccl = timed(lambda: dist.all_reduce(ref))
+        bus = lambda t: 2.0 * (world - 1) / world * n * 2 / t / 1e6  # noqa: E731
+        row = dict(op=label, world=world, bytes=n * 2, ours_tma_ms=round(t_tma, 4), ours_nvls_ms=round(t_nvls, 4), nccl_ms=round(t_nccl, 4),
+                   busbw_tma_gbs=round(bus(t_tma), 1), busbw_nvls_gbs=round(bus(t_nvls), 1), busbw_nccl_gbs=round(bus(t_nccl), 1),
+                   nvls_vs_nccl=round(t_nccl / t_nvls, 3), clocks=clk.summary())
+        results.append(row)
+        log(json.dumps(row))
+    # reduce-scatter + AdamW of one decoder layer (218.1 M parameters)
+    shard_n = 218_112_000 // world // 8 * 8
+    full_n = shard_n * world
+    goff, grad = ws.alloc_tensor((full_n,), torch.bfloat16)
+    soff, shard = ws.alloc_tensor((shard_n,), torch.bfloat16)
+    grad.normal_(std=0.01)
+    master = torch.zeros(shard_n, device=dev)
+    m, v = torch.zeros_like(master), torch.zeros_like(master)
+    ch_a, ch_d = ws.new_channel(), ws.new_channel()
+    tab = seg_table([(0, 0, shard_n)])
+
+    def ours(fn_name, *extra):
+        def run():
+            e = ws.next_epoch(ch_a)
+            ws._epochs[ch_d] = e
+            fn = getattr(lib, fn_name)
+            check(fn(ws.peer_array, *extra, rank, world, rank, goff, tab, 1, ptr(master), ptr(m), ptr(v), soff, None, 1e-4, 0.9, 0.999, 1e-8,
+                     0.01, 1, 1.0 / world, 1, None, ch_a, ch_d, e, ws.counter_ptr(ch_a), 148, cur_stream()), fn_name)
+        return run
+
+    gfull = torch.randn(full_n, device=dev).to(torch.bfloat16)
+    gsh = torch.empty(shard_n, device=dev, dtype=torch.bfloat16)
+
+    def nccl():
+        dist.reduce_scatter_tensor(gsh, gfull)
+        F.adamw_flat_(master, m, v, gsh, shard, lr=1e-4, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.01, step=1)
+
+    with sample_clocks() as clk:
+        t_tma = timed(ours("b200_reduce_scatter_adamw_segs"))
+        t_nvls = timed(ours("b200_reduce_scatter_adamw_nvls", ctypes.c_void_p(ws.mc_base))) if ws.has_multicast else float("nan")
+        t_nccl = timed(nccl)
+    row = dict(op="reduce_scatter+adamw one layer", world=world, params=full_n, ours_tma_ms=round(t_tma, 4), ours_nvls_ms=round(t_nvls, 4),
+               nccl_rs_plus_adamw_kernel_ms=round(t_nccl, 4), nvls_vs_nccl=round(t_nccl / t_nvls, 3), tma_vs_nccl=round(t_nccl / t_tma, 3),
+               clocks=clk.summary())
+    results.append(row)
+    log(json.dumps(row))
+
+
 def main():
     dist.init_process_group("nccl")
     rank, world = dist.get_rank(), dist.get_world_size()
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
     dev = torch.device("cuda", torch.cuda.current_device())
-    ws = SymmetricWorkspace(dist.group.WORLD, int(3 * 2**30), dev)
+    ws = SymmetricWorkspace(dist.group.WORLD, int(6 * 2**30), dev)
+    log(f"symmetric workspace backend: {ws.backend}, multicast: {ws.has_multicast}")
     check_segs(ws, dev, rank, world)
     check_gemm_gather(ws, dev, rank, world)
     results = []
     if "--bench" in sys.argv:
+        bench_reductions(ws, dev, rank, world, results)
         bench_gemm_gather(ws, dev, rank, world, results)
         if rank == 0:
             os.makedirs("gpurun_out", exist_ok=True)
