@@ -14,6 +14,7 @@
 // trap with a diagnostic) so a missing peer turns into an error, never into a hung GPU.
 #include "common.cuh"
 #include <string.h>
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -506,6 +507,7 @@ reduce_scatter_adamw_nvls_kernel(Peers peers, const uint8_t* __restrict__ mc, in
 
 // One-pass in-place bf16 all-reduce: rank r sums slice r of every rank inside the switch (multimem.ld_reduce), scales it and
 // writes it back to every rank with one multicast store (multimem.st).  n % (8 * world) == 0.
+template <int UNROLL>
 __global__ void __launch_bounds__(512)
 allreduce_nvls_kernel(Peers peers, uint8_t* __restrict__ mc, int rank, int world, long long off, long long n, float scale,
                       int ch_arrive, int ch_done, uint32_t epoch, uint32_t* __restrict__ counter) {
@@ -514,15 +516,15 @@ allreduce_nvls_kernel(Peers peers, uint8_t* __restrict__ mc, int rank, int world
   const long long nvec = (n >> 3) / world;
   const long long stride = (long long)gridDim.x * blockDim.x;
   uint8_t* base = mc + off + (((long long)rank * nvec) << 4);
-  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * NVLS_UNROLL) {
-    uint4 sums[NVLS_UNROLL];
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < nvec; i0 += stride * UNROLL) {
+    uint4 sums[UNROLL];
 #pragma unroll
-    for (int u = 0; u < NVLS_UNROLL; ++u) {
+    for (int u = 0; u < UNROLL; ++u) {
       const long long i = i0 + u * stride;
       if (i < nvec) sums[u] = multimem_ld_reduce_bf16x8(base + (i << 4));
     }
 #pragma unroll
-    for (int u = 0; u < NVLS_UNROLL; ++u) {
+    for (int u = 0; u < UNROLL; ++u) {
       const long long i = i0 + u * stride;
       if (i >= nvec) continue;
       uint4 o = sums[u];
@@ -1032,8 +1034,19 @@ B200_API int b200_allreduce_nvls(const void* const* peer_ptrs, void* mc, int ran
   int rc = load_peers(P, peer_ptrs, world);
   if (rc) return rc;
   if (ctas <= 0) ctas = 148;
-  allreduce_nvls_kernel<<<ctas, 512, 0, (cudaStream_t)stream>>>(P, (uint8_t*)mc, rank, world, off, n, scale, ch_arrive, ch_done,
-                                                               epoch, (uint32_t*)counter);
+  static int unroll = 0;
+  if (unroll == 0) {
+    const char* e = getenv("ACCELERATE_B200_NVLS_UNROLL");
+    unroll = e ? atoi(e) : 4;
+    if (unroll != 2 && unroll != 4 && unroll != 8) unroll = 4;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (unroll == 2)
+    allreduce_nvls_kernel<2><<<ctas, 512, 0, st>>>(P, (uint8_t*)mc, rank, world, off, n, scale, ch_arrive, ch_done, epoch, (uint32_t*)counter);
+  else if (unroll == 8)
+    allreduce_nvls_kernel<8><<<ctas, 512, 0, st>>>(P, (uint8_t*)mc, rank, world, off, n, scale, ch_arrive, ch_done, epoch, (uint32_t*)counter);
+  else
+    allreduce_nvls_kernel<4><<<ctas, 512, 0, st>>>(P, (uint8_t*)mc, rank, world, off, n, scale, ch_arrive, ch_done, epoch, (uint32_t*)counter);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;

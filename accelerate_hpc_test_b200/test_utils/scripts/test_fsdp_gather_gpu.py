@@ -296,7 +296,8 @@ def bench_reductions(ws, dev, rank, world, results):
         ref = torch.randn(n, device=dev).to(torch.bfloat16)
         with sample_clocks() as clk:
             t_tma = timed(lambda: ws.allreduce_tma_(off, n, 1.0 / world, chans))
-            t_nvls = timed(lambda: ws.allreduce_nvls_(off, n, 1.0 / world, chans[0], chans[2])) if ws.has_multicast else float("nan")
+            nv_ctas = int(os.environ.get("NVLS_CTAS", "148"))
+            t_nvls = timed(lambda: ws.allreduce_nvls_(off, n, 1.0 / world, chans[0], chans[2], ctas=nv_ctas)) if ws.has_multicast else float("nan")
             t_nccl = timed(lambda: dist.all_reduce(ref))
         bus = lambda t: 2.0 * (world - 1) / world * n * 2 / t / 1e6  # noqa: E731
         row = dict(op=label, world=world, bytes=n * 2, ours_tma_ms=round(t_tma, 4), ours_nvls_ms=round(t_nvls, 4), nccl_ms=round(t_nccl, 4),
