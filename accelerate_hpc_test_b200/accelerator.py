@@ -1221,9 +1221,12 @@ class Accelerator:
 
         weights = []
         sharded_models = []
+        from .utils.fsdp_utils import load_fsdp_model, load_fsdp_optimizer, save_fsdp_model, save_fsdp_optimizer  # noqa: F401
+
+        torch_fsdp2 = [m for m in self._models if getattr(m, "_b200_torch_fsdp2", False)]
         for i, model in enumerate(self._models):
-            if hasattr(model, "save_sharded_state"):
-                model.save_sharded_state(output_dir, i, self.state.fsdp_plugin)
+            if hasattr(model, "save_sharded_state") or getattr(model, "_b200_torch_fsdp2", False):
+                save_fsdp_model(self.state.fsdp_plugin, self, model, output_dir, i)
                 sharded_models.append(i)
                 logger.info(f"Sharded model saved to output dir {output_dir}")
             else:
@@ -1234,6 +1237,8 @@ class Accelerator:
             if engine is not None and hasattr(engine, "save_sharded_optimizer"):
                 engine.save_sharded_optimizer(opt, output_dir, i, self.state.fsdp_plugin)
                 logger.info(f"Sharded optimizer state saved to output dir {output_dir}")
+            elif torch_fsdp2:
+                save_fsdp_optimizer(self.state.fsdp_plugin, self, opt, torch_fsdp2[0], output_dir, i)
             else:
                 optimizers.append(opt)
         schedulers = []
@@ -1271,9 +1276,12 @@ class Accelerator:
         logger.info(f"Loading states from {input_dir}")
 
         models = []
+        from .utils.fsdp_utils import load_fsdp_model, load_fsdp_optimizer
+
+        torch_fsdp2 = [m for m in self._models if getattr(m, "_b200_torch_fsdp2", False)]
         for i, model in enumerate(self._models):
-            if hasattr(model, "load_sharded_state"):
-                model.load_sharded_state(input_dir, i, self.state.fsdp_plugin)
+            if hasattr(model, "load_sharded_state") or getattr(model, "_b200_torch_fsdp2", False):
+                load_fsdp_model(self.state.fsdp_plugin, self, model, input_dir, i)
                 logger.info(f"Sharded model loaded from input dir {input_dir}")
             else:
                 models.append(model)
@@ -1282,6 +1290,8 @@ class Accelerator:
             engine = getattr(opt, "_engine", None)
             if engine is not None and hasattr(engine, "load_sharded_optimizer"):
                 engine.load_sharded_optimizer(opt, input_dir, i, self.state.fsdp_plugin)
+            elif torch_fsdp2:
+                load_fsdp_optimizer(self.state.fsdp_plugin, self, opt, torch_fsdp2[0], input_dir, i)
             else:
                 optimizers.append(opt)
         schedulers = list(self._schedulers)

@@ -1,8 +1,17 @@
-"""``accelerate to-fsdp2``: rewrite an FSDP1 YAML config for FSDP2 (reference commands/to_fsdp2.py:31-172)."""
+"""``accelerate to-fsdp2 --config_file old.yaml (--output_file new.yaml | --overwrite)`` — translate the ``fsdp_config``
+section of a launcher config from FSDP1 vocabulary to FSDP2.
+
+Each FSDP1 key falls in one of four classes (table ``ARGUMENT_KEY_MAPPING``, same content as the reference's): kept as is,
+renamed (``fsdp_sharding_strategy`` → ``fsdp_reshard_after_forward``, with its value translated through
+``ARGUMENT_VALUE_MAPPING``), gone in FSDP2 (dropped with a warning) or not available yet (dropped with a warning).  Keys the
+table does not know are carried over untouched.
+"""
+
+from __future__ import annotations
 
 import enum
 import logging
-from pathlib import Path
+import os
 
 import yaml
 
@@ -16,8 +25,9 @@ class ConversionStatus(enum.Enum):
     REMOVED = -1
 
 
+_SAME = object()  # marker: key keeps its name
+
 ARGUMENT_KEY_MAPPING = {
-    # key: same key (kept), new key (renamed), or a ConversionStatus
     "fsdp_version": "fsdp_version",
     "fsdp_auto_wrap_policy": "fsdp_auto_wrap_policy",
     "fsdp_backward_prefetch": ConversionStatus.REMOVED,
@@ -33,86 +43,82 @@ ARGUMENT_KEY_MAPPING = {
     "fsdp_activation_checkpointing": "fsdp_activation_checkpointing",
 }
 
-ARGUMENT_VALUE_MAPPING = {
-    "fsdp_sharding_strategy": {"FULL_SHARD": True, "SHARD_GRAD_OP": False, "HYBRID_SHARD": True, "HYBRID_SHARD_ZERO2": False, "NO_SHARD": False},
-    "fsdp_reshard_after_forward": {"FULL_SHARD": True, "SHARD_GRAD_OP": False, "HYBRID_SHARD": True, "HYBRID_SHARD_ZERO2": False, "NO_SHARD": False},
+_RESHARD = {"FULL_SHARD": True, "SHARD_GRAD_OP": False, "HYBRID_SHARD": True, "HYBRID_SHARD_ZERO2": False, "NO_SHARD": False}
+ARGUMENT_VALUE_MAPPING = {"fsdp_sharding_strategy": _RESHARD, "fsdp_reshard_after_forward": _RESHARD}
+
+_DROP_NOTES = {
+    ConversionStatus.REMOVED: "Argument {key} has been removed in FSDP2, skipping this key...",
+    ConversionStatus.NOT_YET_IMPLEMENTED: "Argument {key} is not yet implemented in FSDP2, skipping this key...",
 }
 
 
-def _validate_to_fsdp2_args(args):
-    if not Path(args.config_file).exists():
-        raise FileNotFoundError(f"Config file {args.config_file} not found")
-    if not args.overwrite and args.output_file is None:
-        raise ValueError("If --overwrite is not set, --output_file must be provided")
-    if not args.overwrite and Path(args.output_file).exists():
-        raise FileExistsError(f"Output file {args.output_file} already exists and --overwrite is not set")
+def _translate(key: str, value):
+    """(new key or None when dropped, new value)."""
+    target = ARGUMENT_KEY_MAPPING.get(key, _SAME)
+    if isinstance(target, ConversionStatus):
+        logger.warning(_DROP_NOTES[target].format(key=key))
+        return None, None
+    if target is _SAME:
+        return key, value
+    return target, ARGUMENT_VALUE_MAPPING.get(key, {}).get(value, value)
 
 
 def convert_config_to_fsdp2(config: dict) -> dict:
-    fsdp_config = config.get("fsdp_config", {})
-    if not fsdp_config:
+    """Returns ``config`` with its ``fsdp_config`` rewritten (in place); configs without one, or already at version 2, pass through."""
+    old = config.get("fsdp_config") or {}
+    if not old:
         logger.info("No FSDP config found in the config file, skipping conversion...")
         return config
-    new_fsdp_config = {}
-    if fsdp_config.get("fsdp_version", 1) == 2:
-        logger.warning("Config already specfies FSDP2, skipping conversion...")
+    if old.get("fsdp_version", 1) == 2:
+        logger.warning("Config already specifies FSDP2, skipping conversion...")
         logger.warning("If the config doesn't use new argument names, change `fsdp_version` to `1` and rerun the command.")
         return config
-    for key, value in fsdp_config.items():
-        conversion_status = ARGUMENT_KEY_MAPPING.get(key, None)
-        if isinstance(conversion_status, ConversionStatus) or conversion_status is None:
-            conversion_status = key
-            new_fsdp_config[conversion_status] = value
-            continue
-        if conversion_status == ConversionStatus.REMOVED:
-            logger.warning(f"Argument {key} has been removed in FSDP2, skipping this key...")
-            continue
-        if conversion_status == ConversionStatus.NOT_YET_IMPLEMENTED:
-            logger.warning(f"Argument {key} is not yet implemented in FSDP2, skipping this key...")
-            continue
-        if conversion_status is None:
-            logger.warning(f"Argument {key} is not being converted, skipping this key...")
-            new_fsdp_config[key] = value
-        else:
-            if key in ARGUMENT_VALUE_MAPPING:
-                value = ARGUMENT_VALUE_MAPPING[key].get(value, value)
-            new_fsdp_config[ARGUMENT_KEY_MAPPING[key]] = value
-    # drop the keys that do not exist in FSDP2
-    for key in [k for k, v in ARGUMENT_KEY_MAPPING.items() if isinstance(v, ConversionStatus)]:
-        new_fsdp_config.pop(key, None)
-    new_fsdp_config["fsdp_version"] = 2
-    config["fsdp_config"] = new_fsdp_config
+    new = {}
+    for key, value in old.items():
+        new_key, new_value = _translate(key, value)
+        if new_key is not None:
+            new[new_key] = new_value
+    new["fsdp_version"] = 2
+    config["fsdp_config"] = new
     return config
 
 
-def to_fsdp2_command(args):
+def _validate_to_fsdp2_args(args) -> None:
+    if not os.path.exists(args.config_file):
+        raise FileNotFoundError(f"Config file {args.config_file} not found")
+    if args.overwrite:
+        return
+    if args.output_file is None:
+        raise ValueError("If --overwrite is not set, --output_file must be provided")
+    if os.path.exists(args.output_file):
+        raise FileExistsError(f"Output file {args.output_file} already exists and --overwrite is not set")
+
+
+def to_fsdp2_command(args) -> None:
     _validate_to_fsdp2_args(args)
-    config = yaml.safe_load(open(args.config_file))
-    if args.overwrite and args.output_file is None:
-        args.output_file = args.config_file
-    new_config = convert_config_to_fsdp2(config)
-    with open(args.output_file, "w") as f:
-        yaml.dump(new_config, f)
+    with open(args.config_file) as fh:
+        config = yaml.safe_load(fh)
+    destination = args.output_file if args.output_file is not None else args.config_file
+    with open(destination, "w") as fh:
+        yaml.dump(convert_config_to_fsdp2(config), fh)
 
 
 def to_fsdp2_command_parser(subparsers=None):
     description = "Convert an Accelerate config from FSDP1 to FSDP2"
-    if subparsers is not None:
-        parser = subparsers.add_parser("to-fsdp2", description=description)
-    else:
-        parser = CustomArgumentParser(description=description)
-    parser.add_argument("--config_file", type=str, help="The config file to convert to FSDP2", required=True)
-    parser.add_argument("--overwrite", action="store_true", help="Overwrite the config file if it exists", default=False)
-    parser.add_argument("--output_file", type=str, help="The path to the output file to write the converted config to. If not provided, the input file will be overwritten (if --overwrite is set)", default=None)
-    if subparsers is not None:
+    standalone = subparsers is None
+    parser = CustomArgumentParser(description=description) if standalone else subparsers.add_parser("to-fsdp2", description=description)
+    parser.add_argument("--config_file", type=str, required=True, help="The config file to convert to FSDP2")
+    parser.add_argument("--overwrite", action="store_true", default=False, help="Overwrite the config file if it exists")
+    parser.add_argument("--output_file", type=str, default=None,
+                        help="The path to the output file to write the converted config to. If not provided, the input file will be "
+                             "overwritten (if --overwrite is set)")
+    if not standalone:
         parser.set_defaults(func=to_fsdp2_command)
     return parser
 
 
 def main():
-    parser = to_fsdp2_command_parser()
-    args = parser.parse_args()
-    to_fsdp2_command(args)
+    to_fsdp2_command(to_fsdp2_command_parser().parse_args())
 
 
 if __name__ == "__main__":

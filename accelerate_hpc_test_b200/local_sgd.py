@@ -1,60 +1,69 @@
-"""``LocalSGD``: skip gradient synchronisation and average the *parameters* every ``local_sgd_steps`` steps
-(reference src/accelerate/local_sgd.py:41-106)."""
+"""Local SGD: let every rank take ``local_sgd_steps`` optimizer steps on its own gradients, then average the *parameters*.
+
+    with LocalSGD(accelerator=accelerator, model=model, local_sgd_steps=8) as local_sgd:
+        for batch in loader:
+            ...
+            optimizer.step()
+            local_sgd.step()
+
+Inside the block gradient synchronisation is off (``model.no_sync()``); every ``local_sgd_steps`` calls of ``step()`` — and once
+more on exit — the parameters are replaced by their mean over the ranks.  Plain data parallelism only (no sharded engines),
+as in the reference (``local_sgd.py:41-106``).  Parameters are averaged through one flat buffer per dtype, so the cost is one
+fused all-reduce instead of one per tensor.
+"""
+
+from __future__ import annotations
 
 import torch
 
 from .accelerator import Accelerator
 from .utils.dataclasses import DistributedType
 
+_SUPPORTED = (DistributedType.NO, DistributedType.MULTI_CPU, DistributedType.MULTI_GPU)
+
 
 class LocalSGD:
-    """Context manager; call ``step()`` after each optimizer step.
-
-        with LocalSGD(accelerator=accelerator, model=model, local_sgd_steps=8) as local_sgd:
-            for batch in loader:
-                ...; optimizer.step(); local_sgd.step()
-    """
+    def __init__(self, accelerator: Accelerator, model: torch.nn.Module, local_sgd_steps: int, enabled: bool = True):
+        if accelerator.distributed_type not in _SUPPORTED:
+            raise NotImplementedError("LocalSGD is supported only for CPUs and GPUs (no DeepSpeed or MegatronLM)")
+        self.enabled = bool(enabled) and accelerator.distributed_type != DistributedType.NO
+        self.num_steps = 0
+        self.accelerator = accelerator
+        self.model = model
+        self.local_sgd_steps = local_sgd_steps
+        self._no_sync = None
 
     def __enter__(self):
         if self.enabled:
-            self.model_sync_obj = self.model.no_sync()
-            self.model_sync_obj.__enter__()
+            self._no_sync = self.model.no_sync()
+            self._no_sync.__enter__()
         return self
 
-    def __exit__(self, type, value, tb):
-        if self.enabled:
-            self._sync_and_avg_model_params()
-            self.model_sync_obj.__exit__(type, value, tb)
-
-    def __init__(self, accelerator: Accelerator, model: torch.nn.Module, local_sgd_steps: int, enabled: bool = True):
-        if accelerator.distributed_type not in [DistributedType.NO, DistributedType.MULTI_CPU, DistributedType.MULTI_GPU]:
-            raise NotImplementedError("LocalSGD is supported only for CPUs and GPUs (no DeepSpeed or MegatronLM)")
-        self.enabled = enabled and accelerator.distributed_type != DistributedType.NO
-        self.num_steps = 0
-        if self.enabled:
-            self.accelerator = accelerator
-            self.model = model
-            self.local_sgd_steps = local_sgd_steps
-
-    def step(self):
-        self.num_steps += 1
+    def __exit__(self, exc_type, exc, tb):
         if not self.enabled:
-            return
-        if self.num_steps % self.local_sgd_steps == 0:
-            self._sync_and_avg_model_params()
+            return None
+        self._average_parameters()
+        return self._no_sync.__exit__(exc_type, exc, tb)
 
-    def _sync_and_avg_model_params(self):
-        """Average every parameter over the ranks: one flat all-reduce per dtype instead of one per tensor."""
-        self.accelerator.wait_for_everyone()
-        with self.accelerator.autocast():
-            by_dtype = {}
-            for param in self.model.parameters():
-                by_dtype.setdefault(param.dtype, []).append(param)
-            for params in by_dtype.values():
-                flat = torch.cat([p.data.reshape(-1) for p in params])
-                flat = self.accelerator.reduce(flat, reduction="mean")
-                off = 0
-                for p in params:
-                    n = p.numel()
-                    p.data.copy_(flat[off : off + n].view_as(p.data))
-                    off += n
+    def step(self) -> None:
+        self.num_steps += 1
+        if self.enabled and self.num_steps % self.local_sgd_steps == 0:
+            self._average_parameters()
+
+    def _average_parameters(self) -> None:
+        acc = self.accelerator
+        acc.wait_for_everyone()
+        groups: dict = {}
+        for p in self.model.parameters():
+            groups.setdefault(p.dtype, []).append(p)
+        with acc.autocast():
+            for members in groups.values():
+                flat = torch.cat([p.data.reshape(-1) for p in members])
+                mean = acc.reduce(flat, reduction="mean")
+                cursor = 0
+                for p in members:
+                    p.data.copy_(mean[cursor : cursor + p.numel()].view_as(p.data))
+                    cursor += p.numel()
+
+    # kept for callers that used the reference's private name
+    _sync_and_avg_model_params = _average_parameters
