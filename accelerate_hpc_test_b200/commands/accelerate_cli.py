@@ -1,32 +1,41 @@
-"""``accelerate`` console entry point (reference src/accelerate/commands/accelerate_cli.py:28-50)."""
+"""The ``accelerate`` console entry point: one sub-command per module of this package."""
 
-from .config import get_config_parser
-from .env import env_command_parser
-from .estimate import estimate_command_parser
-from .launch import launch_command_parser
-from .merge import merge_command_parser
-from .test import test_command_parser
-from .to_fsdp2 import to_fsdp2_command_parser
-from .tpu import tpu_command_parser
+from __future__ import annotations
+
+import sys
+
+from . import config, env, estimate, launch, merge, test, to_fsdp2, tpu
 from .utils import CustomArgumentParser
+
+# (module, name of its parser factory); every factory registers itself on the sub-parser object and sets `func`
+_SUBCOMMANDS = (
+    (config, "get_config_parser"),
+    (estimate, "estimate_command_parser"),
+    (env, "env_command_parser"),
+    (launch, "launch_command_parser"),
+    (merge, "merge_command_parser"),
+    (test, "test_command_parser"),
+    (to_fsdp2, "to_fsdp2_command_parser"),
+    (tpu, "tpu_command_parser"),
+)
+
+
+def build_parser() -> CustomArgumentParser:
+    parser = CustomArgumentParser("Accelerate CLI tool", usage="accelerate <command> [<args>]", allow_abbrev=False)
+    commands = parser.add_subparsers(help="accelerate command helpers")
+    for module, factory in _SUBCOMMANDS:
+        getattr(module, factory)(subparsers=commands)
+    return parser
 
 
 def main():
-    parser = CustomArgumentParser("Accelerate CLI tool", usage="accelerate <command> [<args>]", allow_abbrev=False)
-    subparsers = parser.add_subparsers(help="accelerate command helpers")
-    get_config_parser(subparsers=subparsers)
-    estimate_command_parser(subparsers=subparsers)
-    env_command_parser(subparsers=subparsers)
-    launch_command_parser(subparsers=subparsers)
-    merge_command_parser(subparsers=subparsers)
-    test_command_parser(subparsers=subparsers)
-    to_fsdp2_command_parser(subparsers=subparsers)
-    tpu_command_parser(subparsers=subparsers)
+    parser = build_parser()
     args = parser.parse_args()
-    if not hasattr(args, "func"):
+    handler = getattr(args, "func", None)
+    if handler is None:
         parser.print_help()
-        exit(1)
-    args.func(args)
+        sys.exit(1)
+    handler(args)
 
 
 if __name__ == "__main__":

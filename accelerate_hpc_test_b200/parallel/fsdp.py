@@ -616,6 +616,12 @@ class B200ShardedModule(nn.Module):
             if self.use_symm and u.gpool.events[idx] is not None:
                 self.trace.wait_event(torch.cuda.current_stream(self.device), u.gpool.events[idx], "grad_buffer_reuse")
             u.has_partial = False
+            # elements that pad a parameter up to a whole number of pieces belong to no gradient: keep them zero so that the
+            # reduced shard (and the gradient norm taken over it) never sees what an earlier user of the buffer left there
+            for s in u.segs:
+                tail = s.piece * self.world - s.numel
+                if tail > 0:
+                    u.grad[s.full_off + s.numel : s.full_off + s.numel + tail].zero_()
         u.ready = {}
         u.rs_launched = False
         for s in u.segs:
