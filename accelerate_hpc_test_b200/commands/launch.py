@@ -262,122 +262,159 @@ def sagemaker_launcher(sagemaker_config, args):
     raise NotImplementedError("SageMaker launch is out of scope for the B200 build")
 
 
-def _validate_launch_command(args):
-    """Fill ``args`` from the config file (explicit flags win), infer process counts, sanity-check combos."""
-    if sum([args.multi_gpu, args.cpu, args.tpu, args.use_deepspeed, args.use_fsdp]) > 1:
-        raise ValueError("You can only use one of `--cpu`, `--multi_gpu`, `--tpu`, `--use_deepspeed`, `--use_fsdp` at a time.")
-    if args.multi_gpu and (args.num_processes is not None) and (args.num_processes < 2):
-        raise ValueError("You need to use at least 2 processes to use `--multi_gpu`.")
-    if (not args.use_fsdp or args.fsdp_version == "1" or args.fsdp_version == 1) and args.use_parallelism_config:
-        raise ValueError("You cannot use `--use_parallelism_config` without `--use_fsdp` and `--fsdp_version=2`. ")
-    defaults = None
-    warned = []
-    mp_from_config_flag = False
-    nondefault = getattr(args, "nondefault", None) or set()
-    if args.config_file is not None or os.path.isfile(default_config_file) and not args.cpu:
-        defaults = load_config_from_file(args.config_file)
-        if (not args.multi_gpu and not args.tpu and not args.use_deepspeed and not args.use_fsdp and not args.use_megatron_lm):
-            args.use_deepspeed = defaults.distributed_type == DistributedType.DEEPSPEED
-            args.multi_gpu = defaults.distributed_type in (DistributedType.MULTI_GPU,)
-            args.tpu = defaults.distributed_type == DistributedType.XLA
-            args.use_fsdp = defaults.distributed_type == DistributedType.FSDP
-            args.use_megatron_lm = defaults.distributed_type == DistributedType.MEGATRON_LM
-            args.tpu_use_cluster = defaults.tpu_use_cluster if args.tpu else False
-            args.use_parallelism_config = bool(defaults.parallelism_config)
-        if args.gpu_ids is None:
-            if defaults.gpu_ids is not None:
-                args.gpu_ids = defaults.gpu_ids
-            else:
-                args.gpu_ids = "all"
-        if len(args.gpu_ids.split(",")) < 2 and (args.gpu_ids != "all") and args.multi_gpu and args.num_machines is not None and args.num_machines <= 1:
-            raise ValueError("Less than two GPU ids were configured and tried to run on on multiple GPUs. Please ensure at least two are specified for `--gpu_ids`, or use `--gpu_ids='all'`.")
-        if defaults.compute_environment == ComputeEnvironment.LOCAL_MACHINE:
-            # plain attributes
-            for name, attr in defaults.__dict__.items():
-                if isinstance(attr, dict):
-                    # nested sections: fsdp_config.fsdp_x -> args.fsdp_x, deepspeed_config.x -> args.x, ...
-                    for key, value in attr.items():
-                        if name == "fsdp_config" and not key.startswith("fsdp"):
-                            key = "fsdp_" + key
-                        elif name == "fp8_config" and not key.startswith("fp8"):
-                            key = "fp8_" + key
-                        elif name == "parallelism_config" and not key.startswith("parallelism_config"):
-                            key = "parallelism_config_" + key
-                        elif name == "megatron_lm_config" and not key.startswith("megatron_lm"):
-                            key = "megatron_lm_" + key
-                        if key not in nondefault:
-                            setattr(args, key, value)
-                elif name not in ["compute_environment", "mixed_precision", "distributed_type"] and getattr(args, name, None) is None:
-                    # an explicit CLI value always wins
-                    setattr(args, name, attr)
-        if not args.debug:
-            args.debug = defaults.debug
-        if not args.mixed_precision:
-            if defaults.mixed_precision is None:
-                args.mixed_precision = "no"
-            else:
-                args.mixed_precision = defaults.mixed_precision
-                mp_from_config_flag = True
-        else:
-            native_amp = True
-            if args.mixed_precision == "fp16" and not native_amp:
-                raise ValueError("fp16 mixed precision requires a GPU")
-        if args.dynamo_backend is None:
-            args.dynamo_backend = "no"
-        if args.num_processes == -1:
-            raise ValueError("You need to manually pass in `--num_processes` using this config yaml.")
-    else:
-        if args.num_processes is None:
-            if torch.cuda.is_available() and not args.cpu:
-                args.num_processes = torch.cuda.device_count()
-            else:
-                args.num_processes = 1
-            warned.append(f"\t`--num_processes` was set to a value of `{args.num_processes}`")
-        if args.debug is None:
-            args.debug = False
-        if (not args.multi_gpu and args.num_processes > 1 and torch.cuda.is_available() and not args.cpu
-                and not args.use_deepspeed and not args.use_fsdp and not args.use_megatron_lm):
-            warned.append("\t\tMore than one GPU was found, enabling multi-GPU training.\n\t\tIf this was unintended please pass in `--num_processes=1`.")
-            args.multi_gpu = True
-        if args.num_machines is None:
-            warned.append("\t`--num_machines` was set to a value of `1`")
-            args.num_machines = 1
-        if args.mixed_precision is None:
-            warned.append("\t`--mixed_precision` was set to a value of `'no'`")
-            args.mixed_precision = "no"
-        if not hasattr(args, "use_cpu"):
-            args.use_cpu = args.cpu
-        if args.dynamo_backend is None:
-            warned.append("\t`--dynamo_backend` was set to a value of `'no'`")
-            args.dynamo_backend = "no"
-        if args.gpu_ids is None:
-            args.gpu_ids = "all"
-    if args.debug:
-        logger.debug("Running script in debug mode, expect distributed operations to be slightly slower.")
-    is_aws_env_disabled = defaults is None or (defaults is not None and defaults.compute_environment != ComputeEnvironment.AMAZON_SAGEMAKER)
-    if is_aws_env_disabled and args.num_cpu_threads_per_process is None:
-        args.num_cpu_threads_per_process = 1
-        if args.cpu and args.num_processes >= 1 and (args.num_machines or 1) >= 1:
-            local_size = max(1, args.num_processes // (args.num_machines or 1))
-            try:
-                import psutil
+_SECTION_PREFIX = {"fsdp_config": "fsdp", "fp8_config": "fp8", "parallelism_config": "parallelism_config", "megatron_lm_config": "megatron_lm"}
+_STRATEGY_FLAGS = ("multi_gpu", "tpu", "use_deepspeed", "use_fsdp", "use_megatron_lm")
+_NOT_COPIED = ("compute_environment", "mixed_precision", "distributed_type")
 
-                threads_per_process = int(psutil.cpu_count(logical=False) / local_size)
-            except Exception:
-                threads_per_process = 1
-            if threads_per_process > 1:
-                args.num_cpu_threads_per_process = threads_per_process
-                warned.append(f"\t`--num_cpu_threads_per_process` was set to `{args.num_cpu_threads_per_process}` to improve out-of-box performance when training on CPUs")
-    if args.num_machines is None:
-        args.num_machines = 1
-    if args.machine_rank is None:
-        args.machine_rank = 0
-    if any(warned):
-        message = "The following values were not passed to `accelerate launch` and had defaults used instead:\n"
-        message += "\n".join(warned)
-        message += "\nTo avoid this warning pass in values for each of the problematic parameters or run `accelerate config`."
-        logger.warning(message)
-    return args, defaults, mp_from_config_flag
+
+class _LaunchResolver:
+    """Completes the launch namespace from three sources, strongest first: flags typed on the command line
+    (``args.nondefault``), the YAML config (``--config_file`` or the default file), built-in defaults that are reported back
+    to the user.  One instance per launch; ``resolve()`` returns ``(args, config or None, mixed_precision_came_from_config)``."""
+
+    def __init__(self, args):
+        self.args = args
+        self.typed = getattr(args, "nondefault", None) or set()
+        self.notes: list = []
+        self.config = None
+        self.precision_from_config = False
+
+    # ---- rules that need no config ------------------------------------------------------------------------
+    def _reject_contradictions(self) -> None:
+        a = self.args
+        if sum(bool(x) for x in (a.multi_gpu, a.cpu, a.tpu, a.use_deepspeed, a.use_fsdp)) > 1:
+            raise ValueError("You can only use one of `--cpu`, `--multi_gpu`, `--tpu`, `--use_deepspeed`, `--use_fsdp` at a time.")
+        if a.multi_gpu and a.num_processes is not None and a.num_processes < 2:
+            raise ValueError("You need to use at least 2 processes to use `--multi_gpu`.")
+        fsdp2 = a.use_fsdp and str(a.fsdp_version) != "1"
+        if a.use_parallelism_config and not fsdp2:
+            raise ValueError("You cannot use `--use_parallelism_config` without `--use_fsdp` and `--fsdp_version=2`. ")
+
+    def _config_applies(self) -> bool:
+        a = self.args
+        return a.config_file is not None or (os.path.isfile(default_config_file) and not a.cpu)
+
+    # ---- with a config file --------------------------------------------------------------------------------
+    def _adopt_strategy(self, cfg) -> None:
+        a = self.args
+        if any(getattr(a, flag) for flag in _STRATEGY_FLAGS):
+            return  # the command line already picked one
+        kind = cfg.distributed_type
+        a.multi_gpu = kind == DistributedType.MULTI_GPU
+        a.use_deepspeed = kind == DistributedType.DEEPSPEED
+        a.use_fsdp = kind == DistributedType.FSDP
+        a.use_megatron_lm = kind == DistributedType.MEGATRON_LM
+        a.tpu = kind == DistributedType.XLA
+        a.tpu_use_cluster = cfg.tpu_use_cluster if a.tpu else False
+        a.use_parallelism_config = bool(cfg.parallelism_config)
+
+    def _adopt_gpu_ids(self, cfg) -> None:
+        a = self.args
+        if a.gpu_ids is None:
+            a.gpu_ids = cfg.gpu_ids if cfg.gpu_ids is not None else "all"
+        one_machine = a.num_machines is not None and a.num_machines <= 1
+        if a.multi_gpu and one_machine and a.gpu_ids != "all" and len(a.gpu_ids.split(",")) < 2:
+            raise ValueError("Less than two GPU ids were configured and tried to run on on multiple GPUs. Please ensure at least two "
+                             "are specified for `--gpu_ids`, or use `--gpu_ids='all'`.")
+
+    def _adopt_fields(self, cfg) -> None:
+        """Top-level keys fill flags that are still unset; the nested sections (``fsdp_config.x`` → ``--fsdp_x`` …) fill every
+        flag the user did not type."""
+        a = self.args
+        for name, value in vars(cfg).items():
+            if isinstance(value, dict):
+                prefix = _SECTION_PREFIX.get(name)
+                for key, item in value.items():
+                    flag = key if (prefix is None or key.startswith(prefix)) else f"{prefix}_{key}"
+                    if flag not in self.typed:
+                        setattr(a, flag, item)
+            elif name not in _NOT_COPIED and getattr(a, name, None) is None:
+                setattr(a, name, value)
+
+    def _from_config(self) -> None:
+        a = self.args
+        cfg = self.config = load_config_from_file(a.config_file)
+        self._adopt_strategy(cfg)
+        self._adopt_gpu_ids(cfg)
+        if cfg.compute_environment == ComputeEnvironment.LOCAL_MACHINE:
+            self._adopt_fields(cfg)
+        a.debug = a.debug or cfg.debug
+        if not a.mixed_precision:
+            a.mixed_precision = cfg.mixed_precision if cfg.mixed_precision is not None else "no"
+            self.precision_from_config = cfg.mixed_precision is not None
+        if a.dynamo_backend is None:
+            a.dynamo_backend = "no"
+        if a.num_processes == -1:
+            raise ValueError("You need to manually pass in `--num_processes` using this config yaml.")
+
+    # ---- without a config file -----------------------------------------------------------------------------
+    def _default(self, flag: str, value, shown: str = None) -> None:
+        if getattr(self.args, flag, None) is None:
+            setattr(self.args, flag, value)
+            if shown is not None:
+                self.notes.append(f"\t`--{flag}` was set to a value of `{shown}`")
+
+    def _from_defaults(self) -> None:
+        a = self.args
+        gpus = torch.cuda.device_count() if (torch.cuda.is_available() and not a.cpu) else 0
+        self._default("num_processes", gpus or 1, str(gpus or 1))
+        self._default("debug", False)
+        picked = a.multi_gpu or a.use_deepspeed or a.use_fsdp or a.use_megatron_lm
+        if not picked and gpus and a.num_processes > 1:
+            a.multi_gpu = True
+            self.notes.append("\t\tMore than one GPU was found, enabling multi-GPU training.\n"
+                              "\t\tIf this was unintended please pass in `--num_processes=1`.")
+        self._default("num_machines", 1, "1")
+        self._default("mixed_precision", "no", "'no'")
+        if not hasattr(a, "use_cpu"):
+            a.use_cpu = a.cpu
+        self._default("dynamo_backend", "no", "'no'")
+        self._default("gpu_ids", "all")
+
+    # ---- common tail ---------------------------------------------------------------------------------------------
+    def _cpu_threads(self) -> None:
+        a = self.args
+        on_sagemaker = self.config is not None and self.config.compute_environment == ComputeEnvironment.AMAZON_SAGEMAKER
+        if on_sagemaker or a.num_cpu_threads_per_process is not None:
+            return
+        a.num_cpu_threads_per_process = 1
+        if not (a.cpu and a.num_processes >= 1):
+            return
+        per_node = max(1, a.num_processes // (a.num_machines or 1))
+        try:
+            import psutil
+
+            share = int(psutil.cpu_count(logical=False) / per_node)
+        except Exception:  # noqa: BLE001 - psutil missing or no physical-core count: keep one thread
+            share = 1
+        if share > 1:
+            a.num_cpu_threads_per_process = share
+            self.notes.append(f"\t`--num_cpu_threads_per_process` was set to `{share}` to improve out-of-box performance when training on CPUs")
+
+    def resolve(self):
+        a = self.args
+        self._reject_contradictions()
+        if self._config_applies():
+            self._from_config()
+        else:
+            self._from_defaults()
+        if a.debug:
+            logger.debug("Running script in debug mode, expect distributed operations to be slightly slower.")
+        self._cpu_threads()
+        if a.num_machines is None:
+            a.num_machines = 1
+        if a.machine_rank is None:
+            a.machine_rank = 0
+        if self.notes:
+            logger.warning("The following values were not passed to `accelerate launch` and had defaults used instead:\n"
+                           + "\n".join(self.notes)
+                           + "\nTo avoid this warning pass in values for each of the problematic parameters or run `accelerate config`.")
+        return a, self.config, self.precision_from_config
+
+
+def _validate_launch_command(args):
+    """Fill ``args`` from the config file (explicitly typed flags win), infer process counts, reject contradictory flags."""
+    return _LaunchResolver(args).resolve()
 
 
 def launch_command(args):

@@ -1,11 +1,12 @@
-"""Turning launch arguments into commands and environment variables.
+"""From launch arguments to a command line and an environment.
 
-The launcher never imports the training script: everything crosses the process boundary as
-environment variables read by ``PartialState`` / the plugins.  Parity with reference
-src/accelerate/utils/launch.py: ``_filter_args`` :46-54, ``setup_fp8_env`` :81-96,
-``prepare_simple_launcher_cmd_env`` :99-195, ``prepare_multi_gpu_env`` :198-394,
-``prepare_extend_env_parallelism_config`` :397-421, ``prepare_deepspeed_cmd_env`` :424-583,
-``PrepareForLaunch`` :776-819.  TPU / SageMaker / vendor-CCL branches are not carried over.
+``accelerate launch`` never imports the training script: every setting crosses the process boundary as an environment
+variable that ``PartialState`` / ``AcceleratorState`` / the plugin dataclasses read back.  This module
+is that translation.  Most of it is tabular — *flag X becomes variable Y, formatted like Z* — so the mapping tables below
+are the single place where a flag is wired (variable names are the interface shared with the reference,
+``utils/launch.py:99-583``); the functions only decide which tables apply.
+
+Not carried over: TPU, SageMaker and vendor-CCL launch paths (they raise).
 """
 
 from __future__ import annotations
@@ -15,273 +16,295 @@ import os
 import subprocess
 import sys
 import warnings
-from ast import literal_eval
 from shutil import which
-from typing import Any
+from typing import Callable, Optional
 
 import torch
 
 from .constants import DEEPSPEED_MULTINODE_LAUNCHERS
-from .dataclasses import DistributedType
-from .environment import patch_environment
-from .other import get_free_port, is_port_in_use
+from .dataclasses import DistributedType, DynamoBackend, PrecisionType
+from .other import is_port_in_use
 
 
+# --------------------------------------------------------------------------- small formatters
+def _text(value) -> str:
+    return str(value)
+
+
+def _lower(value) -> str:
+    return str(value).lower()
+
+
+class EnvRule:
+    """``args.<flag>`` → ``env[<variable>]`` through ``fmt``; skipped when the flag is absent or (``optional``) None."""
+
+    __slots__ = ("flag", "variable", "fmt", "optional")
+
+    def __init__(self, flag: str, variable: str, fmt: Callable = _text, optional: bool = False):
+        self.flag, self.variable, self.fmt, self.optional = flag, variable, fmt, optional
+
+    def apply(self, args, env: dict) -> None:
+        if not hasattr(args, self.flag):
+            return
+        value = getattr(args, self.flag)
+        if value is None and self.optional:
+            return
+        env[self.variable] = self.fmt(value)
+
+
+def _apply(rules, args, env: dict) -> None:
+    for rule in rules:
+        rule.apply(args, env)
+
+
+_FSDP_RULES = (
+    EnvRule("fsdp_sharding_strategy", "FSDP_SHARDING_STRATEGY", optional=True),  # FSDP1 spelling
+    EnvRule("fsdp_reshard_after_forward", "FSDP_RESHARD_AFTER_FORWARD", _lower, optional=True),  # FSDP2 spelling
+    EnvRule("fsdp_offload_params", "FSDP_OFFLOAD_PARAMS", _lower),
+    EnvRule("fsdp_min_num_params", "FSDP_MIN_NUM_PARAMS"),
+    EnvRule("fsdp_auto_wrap_policy", "FSDP_AUTO_WRAP_POLICY", optional=True),
+    EnvRule("fsdp_transformer_layer_cls_to_wrap", "FSDP_TRANSFORMER_CLS_TO_WRAP", optional=True),
+    EnvRule("fsdp_backward_prefetch", "FSDP_BACKWARD_PREFETCH", optional=True),
+    EnvRule("fsdp_state_dict_type", "FSDP_STATE_DICT_TYPE", optional=True),
+    EnvRule("fsdp_forward_prefetch", "FSDP_FORWARD_PREFETCH", _lower),
+    EnvRule("fsdp_use_orig_params", "FSDP_USE_ORIG_PARAMS", _lower),
+    EnvRule("fsdp_cpu_ram_efficient_loading", "FSDP_CPU_RAM_EFFICIENT_LOADING", _lower),
+    EnvRule("fsdp_sync_module_states", "FSDP_SYNC_MODULE_STATES", _lower),
+    EnvRule("fsdp_activation_checkpointing", "FSDP_ACTIVATION_CHECKPOINTING", _lower),
+    EnvRule("fsdp_ignored_modules", "FSDP_IGNORED_MODULES", optional=True),
+)
+
+_MEGATRON_RULES = (
+    EnvRule("megatron_lm_tp_degree", "MEGATRON_LM_TP_DEGREE"),
+    EnvRule("megatron_lm_pp_degree", "MEGATRON_LM_PP_DEGREE"),
+    EnvRule("megatron_lm_gradient_clipping", "MEGATRON_LM_GRADIENT_CLIPPING"),
+    EnvRule("megatron_lm_num_micro_batches", "MEGATRON_LM_NUM_MICRO_BATCHES", optional=True),
+    EnvRule("megatron_lm_sequence_parallelism", "MEGATRON_LM_SEQUENCE_PARALLELISM", optional=True),
+    EnvRule("megatron_lm_recompute_activations", "MEGATRON_LM_RECOMPUTE_ACTIVATIONS", optional=True),
+    EnvRule("megatron_lm_use_distributed_optimizer", "MEGATRON_LM_USE_DISTRIBUTED_OPTIMIZER", optional=True),
+)
+
+_PARALLELISM_RULES = (
+    EnvRule("parallelism_config_dp_replicate_size", "PARALLELISM_CONFIG_DP_REPLICATE_SIZE"),
+    EnvRule("parallelism_config_dp_shard_size", "PARALLELISM_CONFIG_DP_SHARD_SIZE"),
+    EnvRule("parallelism_config_tp_size", "PARALLELISM_CONFIG_TP_SIZE"),
+    EnvRule("parallelism_config_cp_size", "PARALLELISM_CONFIG_CP_SIZE"),
+    EnvRule("parallelism_config_cp_backend", "PARALLELISM_CONFIG_CP_BACKEND"),
+    EnvRule("parallelism_config_sp_size", "PARALLELISM_CONFIG_SP_SIZE"),
+    EnvRule("parallelism_config_sp_backend", "PARALLELISM_CONFIG_SP_BACKEND"),
+)
+_CP_ONLY_RULES = (EnvRule("parallelism_config_cp_comm_strategy", "PARALLELISM_CONFIG_CP_COMM_STRATEGY"),)
+_SP_ONLY_RULES = (
+    EnvRule("parallelism_config_sp_seq_length", "PARALLELISM_CONFIG_SP_SEQ_LENGTH"),
+    EnvRule("parallelism_config_sp_seq_length_is_variable", "PARALLELISM_CONFIG_SP_SEQ_LENGTH_IS_VARIABLE", _lower),
+    EnvRule("parallelism_config_sp_attn_implementation", "PARALLELISM_CONFIG_SP_ATTN_IMPLEMENTATION"),
+)
+
+_DEEPSPEED_RULES = (
+    EnvRule("zero_stage", "ACCELERATE_DEEPSPEED_ZERO_STAGE", optional=True),
+    EnvRule("gradient_accumulation_steps", "ACCELERATE_GRADIENT_ACCUMULATION_STEPS", optional=True),
+    EnvRule("gradient_clipping", "ACCELERATE_GRADIENT_CLIPPING", _lower, optional=True),
+    EnvRule("offload_optimizer_device", "ACCELERATE_DEEPSPEED_OFFLOAD_OPTIMIZER_DEVICE", _lower, optional=True),
+    EnvRule("offload_param_device", "ACCELERATE_DEEPSPEED_OFFLOAD_PARAM_DEVICE", _lower, optional=True),
+    EnvRule("zero3_init_flag", "ACCELERATE_DEEPSPEED_ZERO3_INIT", _lower, optional=True),
+    EnvRule("zero3_save_16bit_model", "ACCELERATE_DEEPSPEED_ZERO3_SAVE_16BIT_MODEL", _lower, optional=True),
+    EnvRule("deepspeed_config_file", "ACCELERATE_DEEPSPEED_CONFIG_FILE", optional=True),
+    EnvRule("deepspeed_moe_layer_cls_names", "ACCELERATE_DEEPSPEED_MOE_LAYER_CLS_NAMES", optional=True),
+)
+
+_DYNAMO_RULES = (
+    EnvRule("dynamo_mode", "ACCELERATE_DYNAMO_MODE", lambda v: v),
+    EnvRule("dynamo_use_fullgraph", "ACCELERATE_DYNAMO_USE_FULLGRAPH"),
+    EnvRule("dynamo_use_dynamic", "ACCELERATE_DYNAMO_USE_DYNAMIC"),
+    EnvRule("dynamo_use_regional_compilation", "ACCELERATE_DYNAMO_USE_REGIONAL_COMPILATION"),
+)
+
+
+# --------------------------------------------------------------------------- pieces shared by every launcher
 def _filter_args(args: argparse.Namespace, parser, default_args=()):
-    """Keep only the attributes of ``args`` that ``parser`` (e.g. torch.distributed.run's) knows."""
-    new_args, _ = parser.parse_known_args(list(default_args))
-    for key, value in vars(args).items():
-        if key in vars(new_args).keys():
-            setattr(new_args, key, value)
-    return new_args
+    """A namespace for ``parser`` (e.g. ``torch.distributed.run``'s) holding its defaults overridden by the attributes of
+    ``args`` that it knows; everything else in ``args`` is dropped."""
+    accepted, _ = parser.parse_known_args(list(default_args))
+    for name in vars(accepted):
+        if hasattr(args, name):
+            setattr(accepted, name, getattr(args, name))
+    return accepted
 
 
-def _get_mpirun_args():
-    """(mpirun binary, hostfile flag, -n flag, -ppn flag, bind-to flag) for the MPI flavour installed."""
-    mpi_apps = [x for x in ["mpirun", "mpiexec"] if which(x)]
-    if len(mpi_apps) == 0:
-        raise OSError("mpirun or mpiexec were not found. Ensure that Intel MPI, Open MPI, or MVAPICH are installed.")
-    mpi_app = mpi_apps[0]
-    mpirun_version = subprocess.check_output([mpi_app, "--version"])
-    if b"Open MPI" in mpirun_version:
-        return mpi_app, "--hostfile", "-n", "--npernode", "--bind-to"
-    return mpi_app, "-f", "-n", "-ppn", ""
-
-
-def setup_fp8_env(args: argparse.Namespace, current_env: dict):
-    """``--fp8_*`` flags -> ``ACCELERATE_FP8_*`` variables."""
-    prefix = "ACCELERATE_"
-    for arg in vars(args):
-        if arg.startswith("fp8_"):
-            value = getattr(args, arg)
-            if value is not None:
-                if arg == "fp8_override_linear_precision":
-                    current_env[prefix + "FP8_OVERRIDE_FPROP"] = str(value[0])
-                    current_env[prefix + "FP8_OVERRIDE_DGRAD"] = str(value[1])
-                    current_env[prefix + "FP8_OVERRIDE_WGRAD"] = str(value[2])
-                else:
-                    current_env[f"{prefix}{arg.upper()}"] = str(getattr(args, arg))
+def setup_fp8_env(args: argparse.Namespace, current_env: dict) -> dict:
+    """Every ``--fp8_*`` flag that was given becomes ``ACCELERATE_FP8_*`` (the linear-precision triple becomes three variables)."""
+    for flag, value in vars(args).items():
+        if not flag.startswith("fp8_") or value is None:
+            continue
+        if flag == "fp8_override_linear_precision":
+            for part, item in zip(("FPROP", "DGRAD", "WGRAD"), value):
+                current_env[f"ACCELERATE_FP8_OVERRIDE_{part}"] = str(item)
+        else:
+            current_env[f"ACCELERATE_{flag.upper()}"] = str(value)
     return current_env
 
 
-def _mixed_precision(args) -> str:
+def _precision_and_compile_env(args, env: dict) -> None:
+    wanted = str(args.mixed_precision).lower()
     try:
-        from .dataclasses import PrecisionType
-
-        mixed_precision = PrecisionType(str(args.mixed_precision).lower())
+        env["ACCELERATE_MIXED_PRECISION"] = str(PrecisionType(wanted))
     except ValueError:
-        from .dataclasses import PrecisionType
-
-        raise ValueError(f"Unknown mixed_precision mode: {str(args.mixed_precision).lower()}. Choose between {PrecisionType.list()}.")
-    return str(mixed_precision)
-
-
-def _dynamo_env(args, current_env):
-    from .dataclasses import DynamoBackend
-
+        raise ValueError(f"Unknown mixed_precision mode: {wanted}. Choose between {PrecisionType.list()}.") from None
+    if wanted == "fp8":
+        setup_fp8_env(args, env)
+    backend = str(args.dynamo_backend).upper()
     try:
-        dynamo_backend = DynamoBackend(str(args.dynamo_backend).upper())
+        env["ACCELERATE_DYNAMO_BACKEND"] = DynamoBackend(backend).value
     except ValueError:
-        raise ValueError(f"Unknown dynamo backend: {str(args.dynamo_backend).upper()}. Choose between {DynamoBackend.list()}.")
-    current_env["ACCELERATE_DYNAMO_BACKEND"] = dynamo_backend.value
-    current_env["ACCELERATE_DYNAMO_MODE"] = args.dynamo_mode
-    current_env["ACCELERATE_DYNAMO_USE_FULLGRAPH"] = str(args.dynamo_use_fullgraph)
-    current_env["ACCELERATE_DYNAMO_USE_DYNAMIC"] = str(args.dynamo_use_dynamic)
-    current_env["ACCELERATE_DYNAMO_USE_REGIONAL_COMPILATION"] = str(args.dynamo_use_regional_compilation)
+        raise ValueError(f"Unknown dynamo backend: {backend}. Choose between {DynamoBackend.list()}.") from None
+    _apply(_DYNAMO_RULES, args, env)
+
+
+def _common_env(args) -> dict:
+    env = os.environ.copy()
+    if args.debug:
+        env["ACCELERATE_DEBUG_MODE"] = "true"
+    visible = getattr(args, "gpu_ids", "all")
+    if visible not in ("all", None):
+        env["CUDA_VISIBLE_DEVICES"] = visible
+    _precision_and_compile_env(args, env)
+    return env
+
+
+def _check_module_flags(args) -> None:
+    if args.module and args.no_python:
+        raise ValueError("--module and --no_python cannot be used together")
+
+
+# --------------------------------------------------------------------------- single process / mpirun
+def _get_mpirun_args():
+    """(launcher binary, hostfile flag, total-process flag, per-node flag, binding flag) of the installed MPI flavour."""
+    found = next((exe for exe in ("mpirun", "mpiexec") if which(exe)), None)
+    if found is None:
+        raise OSError("mpirun or mpiexec were not found. Ensure that Intel MPI, Open MPI, or MVAPICH are installed.")
+    banner = subprocess.check_output([found, "--version"])
+    if b"Open MPI" in banner:
+        return found, "--hostfile", "-n", "--npernode", "--bind-to"
+    return found, "-f", "-n", "-ppn", ""
+
+
+def _mpirun_prefix(args) -> list:
+    exe, hostfile_flag, total_flag, per_node_flag, bind_flag = _get_mpirun_args()
+    total, machines = getattr(args, "num_processes", None), args.num_machines
+    per_node = str(total // machines) if total and machines else "1"
+    prefix = [exe, hostfile_flag, args.mpirun_hostfile, per_node_flag, per_node]
+    if total:
+        prefix += [total_flag, str(total)]
+    if bind_flag:
+        prefix += [bind_flag, "socket", "-x", "MASTER_ADDR", "-x", "MASTER_PORT"]
+    return prefix
 
 
 def prepare_simple_launcher_cmd_env(args: argparse.Namespace) -> tuple[list[str], dict[str, str]]:
-    """Command + env of a single-process (or mpirun multi-CPU) launch."""
-    cmd = []
-    if args.no_python and args.module:
-        raise ValueError("--module and --no_python cannot be used together")
-    num_processes = getattr(args, "num_processes", None)
-    num_machines = args.num_machines
-    if args.mpirun_hostfile is not None:
-        mpi_app_name, hostfile_arg, num_proc_arg, proc_per_node_arg, bind_to_arg = _get_mpirun_args()
-        bind_to = getattr(args, "mpirun_ccl", None)
-        nproc_per_node = str(num_processes // num_machines) if num_processes and num_machines else "1"
-        cmd += [mpi_app_name, hostfile_arg, args.mpirun_hostfile, proc_per_node_arg, nproc_per_node]
-        if num_processes:
-            cmd += [num_proc_arg, str(num_processes)]
-        if bind_to_arg:
-            cmd += [bind_to_arg, "socket", "-x", "MASTER_ADDR", "-x", "MASTER_PORT"]
+    """``python script.py ...`` for one process, or the same behind ``mpirun`` for a multi-CPU job with a hostfile."""
+    _check_module_flags(args)
+    via_mpi = args.mpirun_hostfile is not None
+    cmd = _mpirun_prefix(args) if via_mpi else []
     if not args.no_python:
         cmd.append(sys.executable)
         if args.module:
             cmd.append("-m")
-    cmd.append(args.training_script)
-    cmd.extend(args.training_script_args)
+    cmd += [args.training_script, *args.training_script_args]
 
-    current_env = os.environ.copy()
-    current_env["ACCELERATE_USE_CPU"] = str(args.cpu or getattr(args, "use_cpu", False))
-    if args.debug:
-        current_env["ACCELERATE_DEBUG_MODE"] = "true"
-    if args.gpu_ids != "all" and args.gpu_ids is not None:
-        current_env["CUDA_VISIBLE_DEVICES"] = args.gpu_ids
-    if num_machines > 1:
-        current_env["MASTER_ADDR"] = args.main_process_ip
-        current_env["MASTER_PORT"] = str(args.main_process_port)
-    elif args.mpirun_hostfile is not None:
-        current_env["MASTER_ADDR"] = args.main_process_ip or "127.0.0.1"
-        current_env["MASTER_PORT"] = str(args.main_process_port or 29500)
-    current_env["ACCELERATE_MIXED_PRECISION"] = _mixed_precision(args)
-    if str(args.mixed_precision).lower() == "fp8":
-        setup_fp8_env(args, current_env)
-    _dynamo_env(args, current_env)
-    current_env["OMP_NUM_THREADS"] = str(getattr(args, "num_cpu_threads_per_process", 1) or 1)
+    env = _common_env(args)
+    env["ACCELERATE_USE_CPU"] = str(args.cpu or getattr(args, "use_cpu", False))
+    if args.num_machines > 1:
+        env["MASTER_ADDR"], env["MASTER_PORT"] = args.main_process_ip, str(args.main_process_port)
+    elif via_mpi:
+        env["MASTER_ADDR"], env["MASTER_PORT"] = args.main_process_ip or "127.0.0.1", str(args.main_process_port or 29500)
+    env["OMP_NUM_THREADS"] = str(getattr(args, "num_cpu_threads_per_process", 1) or 1)
     if getattr(args, "enable_cpu_affinity", False):
-        current_env["ACCELERATE_CPU_AFFINITY"] = "1"
-    return cmd, current_env
+        env["ACCELERATE_CPU_AFFINITY"] = "1"
+    return cmd, env
+
+
+# --------------------------------------------------------------------------- torchrun
+_PORT_BUSY_ONE_NODE = (
+    "Port `{port}` is already in use. Accelerate will attempt to launch in a standalone-like mode by finding an open port "
+    "automatically for this session. If this current attempt fails, or for more control in future runs, please specify a different "
+    "port (e.g., `--main_process_port <your_chosen_port>`) in your launch command or Accelerate config file."
+)
+_PORT_BUSY_MULTI_NODE = (
+    "Tried to launch distributed communication on port `{port}`, but another process is utilizing it. Please specify a different "
+    "port (such as using the `--main_process_port` flag or specifying a different `main_process_port` in your config file) and "
+    "rerun your script. To automatically use the next open port (on a single node), you can set this to `0`."
+)
+
+
+def _set_rendezvous(args) -> None:
+    """Fill the attributes ``torch.distributed.run`` reads (``nproc_per_node``, ``nnodes``, ``master_*`` / ``rdzv_endpoint``)."""
+    machines, total = args.num_machines, args.num_processes
+    host, port = args.main_process_ip, args.main_process_port
+    if machines > 1:
+        args.nproc_per_node, args.nnodes, args.node_rank = str(total // machines), str(machines), int(args.machine_rank)
+        if getattr(args, "same_network", False):
+            args.master_addr, args.master_port = str(host), str(port)
+        else:
+            args.rdzv_endpoint = f"{host}:{port}"
+    else:
+        args.nproc_per_node = str(total)
+        args.master_addr = str(host) if host else "127.0.0.1"
+        if port is not None:
+            args.master_port = str(port)
+    probe = 29500 if port is None else port
+    first_node = machines <= 1 or int(args.machine_rank) == 0
+    if first_node and is_port_in_use(probe):
+        if machines > 1:
+            raise ConnectionError(_PORT_BUSY_MULTI_NODE.format(port=probe))
+        args.standalone = True  # torchrun then picks a free port itself
+        warnings.warn(_PORT_BUSY_ONE_NODE.format(port=probe), UserWarning)
 
 
 def prepare_multi_gpu_env(args: argparse.Namespace) -> dict[str, str]:
-    """Sets the torchrun-facing attributes on ``args`` and returns the env of a multi-GPU launch."""
-    num_processes = args.num_processes
-    num_machines = args.num_machines
-    main_process_ip = args.main_process_ip
-    main_process_port = args.main_process_port
-    if num_machines > 1:
-        args.nproc_per_node = str(num_processes // num_machines)
-        args.nnodes = str(num_machines)
-        args.node_rank = int(args.machine_rank)
-        if getattr(args, "same_network", False):
-            args.master_addr = str(main_process_ip)
-            args.master_port = str(main_process_port)
-        else:
-            args.rdzv_endpoint = f"{main_process_ip}:{main_process_port}"
-    else:
-        args.nproc_per_node = str(num_processes)
-        if main_process_port is not None:
-            args.master_port = str(main_process_port)
-        args.master_addr = str(main_process_ip) if main_process_ip else "127.0.0.1"
-    if main_process_port is None:
-        main_process_port = 29500
-    # a busy port on a single node: let torchrun pick one (--standalone) instead of failing later
-    need_port_check = num_machines <= 1 or int(args.machine_rank) == 0
-    if need_port_check and is_port_in_use(main_process_port):
-        if num_machines <= 1:
-            args.standalone = True
-            warnings.warn(f"Port `{main_process_port}` is already in use. Accelerate will attempt to launch in a standalone-like mode by finding an open port automatically for this session. If this current attempt fails, or for more control in future runs, please specify a different port (e.g., `--main_process_port <your_chosen_port>`) in your launch command or Accelerate config file.", UserWarning)
-        else:
-            raise ConnectionError(f"Tried to launch distributed communication on port `{main_process_port}`, but another process is utilizing it. Please specify a different port (such as using the `--main_process_port` flag or specifying a different `main_process_port` in your config file) and rerun your script. To automatically use the next open port (on a single node), you can set this to `0`.")
-    if args.module and args.no_python:
-        raise ValueError("--module and --no_python cannot be used together")
-    elif args.module:
-        args.module = True
-    elif args.no_python:
-        args.no_python = True
+    """Completes ``args`` for ``torch.distributed.run`` and returns the environment of a multi-GPU (DDP / FSDP / Megatron) job."""
+    _set_rendezvous(args)
+    _check_module_flags(args)
+    args.module, args.no_python = bool(args.module), bool(args.no_python)
 
-    current_env = os.environ.copy()
-    if args.debug:
-        current_env["ACCELERATE_DEBUG_MODE"] = "true"
-    gpu_ids = getattr(args, "gpu_ids", "all")
-    if gpu_ids != "all" and args.gpu_ids is not None:
-        current_env["CUDA_VISIBLE_DEVICES"] = gpu_ids
-    current_env["ACCELERATE_MIXED_PRECISION"] = _mixed_precision(args)
-    if str(args.mixed_precision).lower() == "fp8":
-        setup_fp8_env(args, current_env)
-    _dynamo_env(args, current_env)
-
+    env = _common_env(args)
     if args.use_fsdp:
-        current_env["ACCELERATE_USE_FSDP"] = "true"
         if args.fsdp_cpu_ram_efficient_loading and not args.fsdp_sync_module_states:
             raise ValueError("When using `--fsdp_cpu_ram_efficient_loading` set `--fsdp_sync_module_states` to `True`")
-        current_env["FSDP_VERSION"] = str(args.fsdp_version) if hasattr(args, "fsdp_version") else "1"
-        # FSDP1 uses sharding_strategy, FSDP2 reshard_after_forward; both travel when given
-        if getattr(args, "fsdp_sharding_strategy", None) is not None:
-            current_env["FSDP_SHARDING_STRATEGY"] = str(args.fsdp_sharding_strategy)
-        if getattr(args, "fsdp_reshard_after_forward", None) is not None:
-            current_env["FSDP_RESHARD_AFTER_FORWARD"] = str(args.fsdp_reshard_after_forward).lower()
-        current_env["FSDP_OFFLOAD_PARAMS"] = str(args.fsdp_offload_params).lower()
-        current_env["FSDP_MIN_NUM_PARAMS"] = str(args.fsdp_min_num_params)
-        if args.fsdp_auto_wrap_policy is not None:
-            current_env["FSDP_AUTO_WRAP_POLICY"] = str(args.fsdp_auto_wrap_policy)
-        if args.fsdp_transformer_layer_cls_to_wrap is not None:
-            current_env["FSDP_TRANSFORMER_CLS_TO_WRAP"] = str(args.fsdp_transformer_layer_cls_to_wrap)
-        if args.fsdp_backward_prefetch is not None:
-            current_env["FSDP_BACKWARD_PREFETCH"] = str(args.fsdp_backward_prefetch)
-        if args.fsdp_state_dict_type is not None:
-            current_env["FSDP_STATE_DICT_TYPE"] = str(args.fsdp_state_dict_type)
-        current_env["FSDP_FORWARD_PREFETCH"] = str(args.fsdp_forward_prefetch).lower()
-        current_env["FSDP_USE_ORIG_PARAMS"] = str(args.fsdp_use_orig_params).lower()
-        current_env["FSDP_CPU_RAM_EFFICIENT_LOADING"] = str(args.fsdp_cpu_ram_efficient_loading).lower()
-        current_env["FSDP_SYNC_MODULE_STATES"] = str(args.fsdp_sync_module_states).lower()
-        current_env["FSDP_ACTIVATION_CHECKPOINTING"] = str(args.fsdp_activation_checkpointing).lower()
-        if getattr(args, "fsdp_ignored_modules", None) is not None:
-            current_env["FSDP_IGNORED_MODULES"] = str(args.fsdp_ignored_modules)
-
+        env["ACCELERATE_USE_FSDP"] = "true"
+        env["FSDP_VERSION"] = str(getattr(args, "fsdp_version", 1))
+        _apply(_FSDP_RULES, args, env)
     if args.use_megatron_lm:
-        prefix = "MEGATRON_LM_"
-        current_env["ACCELERATE_USE_MEGATRON_LM"] = "true"
-        current_env[prefix + "TP_DEGREE"] = str(args.megatron_lm_tp_degree)
-        current_env[prefix + "PP_DEGREE"] = str(args.megatron_lm_pp_degree)
-        current_env[prefix + "GRADIENT_CLIPPING"] = str(args.megatron_lm_gradient_clipping)
-        if args.megatron_lm_num_micro_batches is not None:
-            current_env[prefix + "NUM_MICRO_BATCHES"] = str(args.megatron_lm_num_micro_batches)
-        if args.megatron_lm_sequence_parallelism is not None:
-            current_env[prefix + "SEQUENCE_PARALLELISM"] = str(args.megatron_lm_sequence_parallelism)
-        if args.megatron_lm_recompute_activations is not None:
-            current_env[prefix + "RECOMPUTE_ACTIVATIONS"] = str(args.megatron_lm_recompute_activations)
-        if args.megatron_lm_use_distributed_optimizer is not None:
-            current_env[prefix + "USE_DISTRIBUTED_OPTIMIZER"] = str(args.megatron_lm_use_distributed_optimizer)
-
-    current_env["OMP_NUM_THREADS"] = str(args.num_cpu_threads_per_process)
+        env["ACCELERATE_USE_MEGATRON_LM"] = "true"
+        _apply(_MEGATRON_RULES, args, env)
+    env["OMP_NUM_THREADS"] = str(args.num_cpu_threads_per_process)
     if args.enable_cpu_affinity:
-        current_env["ACCELERATE_CPU_AFFINITY"] = "1"
-    if not args.use_parallelism_config:
-        return current_env
-    prepare_extend_env_parallelism_config(args, current_env)
-    return current_env
+        env["ACCELERATE_CPU_AFFINITY"] = "1"
+    if args.use_parallelism_config:
+        prepare_extend_env_parallelism_config(args, env)
+    return env
 
 
 def prepare_extend_env_parallelism_config(args: argparse.Namespace, current_env: dict) -> None:
-    """``--parallelism_config_*`` flags -> ``PARALLELISM_CONFIG_*`` variables (in place)."""
-    prefix = "PARALLELISM_CONFIG_"
+    """``--parallelism_config_*`` → ``PARALLELISM_CONFIG_*`` (in place); the cp / sp detail variables only when that axis is used."""
     current_env["ACCELERATE_USE_PARALLELISM_CONFIG"] = "true"
-    current_env[prefix + "DP_REPLICATE_SIZE"] = str(args.parallelism_config_dp_replicate_size)
-    current_env[prefix + "DP_SHARD_SIZE"] = str(args.parallelism_config_dp_shard_size)
-    current_env[prefix + "TP_SIZE"] = str(args.parallelism_config_tp_size)
-    current_env[prefix + "CP_SIZE"] = str(args.parallelism_config_cp_size)
-    current_env[prefix + "CP_BACKEND"] = str(args.parallelism_config_cp_backend)
-    current_env[prefix + "SP_SIZE"] = str(args.parallelism_config_sp_size)
-    current_env[prefix + "SP_BACKEND"] = str(args.parallelism_config_sp_backend)
+    _apply(_PARALLELISM_RULES, args, current_env)
     if args.parallelism_config_cp_size > 1:
-        current_env[prefix + "CP_COMM_STRATEGY"] = str(args.parallelism_config_cp_comm_strategy)
+        _apply(_CP_ONLY_RULES, args, current_env)
     if args.parallelism_config_sp_size > 1:
-        current_env[prefix + "SP_SEQ_LENGTH"] = str(args.parallelism_config_sp_seq_length)
-        current_env[prefix + "SP_SEQ_LENGTH_IS_VARIABLE"] = str(args.parallelism_config_sp_seq_length_is_variable).lower()
-        current_env[prefix + "SP_ATTN_IMPLEMENTATION"] = str(args.parallelism_config_sp_attn_implementation)
+        _apply(_SP_ONLY_RULES, args, current_env)
 
 
 def prepare_deepspeed_cmd_env(args: argparse.Namespace) -> tuple[list[str], dict[str, str]]:
-    """DeepSpeed-configured launch.  DeepSpeed is a config shell here (ZeRO maps onto the native sharded
-    engine), so the job is started with torchrun and the ``ACCELERATE_DEEPSPEED_*`` variables are set
-    exactly as the reference sets them for the plugin to read."""
-    if getattr(args, "deepspeed_multinode_launcher", None) not in (None, *DEEPSPEED_MULTINODE_LAUNCHERS):
-        raise ValueError(f"Unknown multinode launcher {args.deepspeed_multinode_launcher}; choose from {DEEPSPEED_MULTINODE_LAUNCHERS}")
-    current_env = prepare_multi_gpu_env(args)
-    current_env["ACCELERATE_USE_DEEPSPEED"] = "true"
-    prefix = "ACCELERATE_DEEPSPEED_"
-    if args.zero_stage is not None:
-        current_env[prefix + "ZERO_STAGE"] = str(args.zero_stage)
-    if args.gradient_accumulation_steps is not None:
-        current_env["ACCELERATE_GRADIENT_ACCUMULATION_STEPS"] = str(args.gradient_accumulation_steps)
-    if args.gradient_clipping is not None:
-        current_env["ACCELERATE_GRADIENT_CLIPPING"] = str(args.gradient_clipping).lower()
-    if args.offload_optimizer_device is not None:
-        current_env[prefix + "OFFLOAD_OPTIMIZER_DEVICE"] = str(args.offload_optimizer_device).lower()
-    if args.offload_param_device is not None:
-        current_env[prefix + "OFFLOAD_PARAM_DEVICE"] = str(args.offload_param_device).lower()
-    if args.zero3_init_flag is not None:
-        current_env[prefix + "ZERO3_INIT"] = str(args.zero3_init_flag).lower()
-    if args.zero3_save_16bit_model is not None:
-        current_env[prefix + "ZERO3_SAVE_16BIT_MODEL"] = str(args.zero3_save_16bit_model).lower()
-    if args.deepspeed_config_file is not None:
-        current_env[prefix + "CONFIG_FILE"] = str(args.deepspeed_config_file)
-    if getattr(args, "deepspeed_moe_layer_cls_names", None) is not None:
-        current_env[prefix + "MOE_LAYER_CLS_NAMES"] = str(args.deepspeed_moe_layer_cls_names)
-    return [], current_env
+    """A DeepSpeed-configured job.  DeepSpeed is a configuration dialect here (ZeRO stages map onto the native sharded engine),
+    so the job is a torchrun job whose environment additionally carries the ``ACCELERATE_DEEPSPEED_*`` variables the plugin
+    reads.  Returns ``([], env)``: no external launcher command is needed."""
+    launcher = getattr(args, "deepspeed_multinode_launcher", None)
+    if launcher is not None and launcher not in DEEPSPEED_MULTINODE_LAUNCHERS:
+        raise ValueError(f"Unknown multinode launcher {launcher}; choose from {DEEPSPEED_MULTINODE_LAUNCHERS}")
+    env = prepare_multi_gpu_env(args)
+    env["ACCELERATE_USE_DEEPSPEED"] = "true"
+    _apply(_DEEPSPEED_RULES, args, env)
+    return [], env
 
 
 def prepare_tpu(args, current_env, pod: bool = False):
@@ -293,31 +316,33 @@ def prepare_sagemager_args_inputs(sagemaker_config, args):
 
 
 def env_var_path_add(env_var_name: str, path_to_add: str) -> str:
-    """``path_to_add`` appended to the ``:``-separated variable ``env_var_name``."""
-    paths = [p for p in os.environ.get(env_var_name, "").split(":") if len(p) > 0]
-    paths.append(str(path_to_add))
-    return ":".join(paths)
+    """Value of the ``:``-separated variable ``env_var_name`` with ``path_to_add`` appended (empty entries dropped)."""
+    entries = [entry for entry in os.environ.get(env_var_name, "").split(":") if entry]
+    return ":".join(entries + [str(path_to_add)])
 
 
+# --------------------------------------------------------------------------- in-process (forked) workers
 class PrepareForLaunch:
-    """Callable handed to ``torch.multiprocessing.start_processes``: sets the rank variables, then runs ``launcher``."""
+    """The callable ``notebook_launcher`` / ``debug_launcher`` hand to ``torch.multiprocessing.start_processes``: it gives the
+    forked worker its rank variables (and, in debug mode, a gloo group rendezvousing over a file), then runs ``launcher``."""
 
     def __init__(self, launcher, distributed_type="NO", debug: bool = False):
         self.launcher = launcher
         self.distributed_type = DistributedType(distributed_type)
         self.debug = debug
 
+    def _debug_group(self, index: int) -> None:
+        world = int(os.environ["WORLD_SIZE"])
+        store = torch.distributed.FileStore(os.environ["ACCELERATE_DEBUG_RDV_FILE"], world)
+        os.environ["RANK"] = os.environ["LOCAL_RANK"] = str(index)
+        torch.distributed.init_process_group("gloo", rank=index, world_size=world, store=store)
+
     def __call__(self, index, *args):
         if self.debug:
-            world_size = int(os.environ.get("WORLD_SIZE"))
-            rdv_file = os.environ.get("ACCELERATE_DEBUG_RDV_FILE")
-            os.environ["RANK"] = str(index)
-            os.environ["LOCAL_RANK"] = str(index)
-            torch.distributed.init_process_group("gloo", rank=index, store=torch.distributed.FileStore(rdv_file, world_size), world_size=world_size)
+            self._debug_group(index)
         elif self.distributed_type in (DistributedType.MULTI_GPU, DistributedType.MULTI_CPU):
+            per_node, node = int(os.environ.get("NPROC", 1)), int(os.environ.get("NODE_RANK", 0))
             os.environ["LOCAL_RANK"] = str(index)
-            nproc = int(os.environ.get("NPROC", 1))
-            node_rank = int(os.environ.get("NODE_RANK", 0))
-            os.environ["RANK"] = str(nproc * node_rank + index)
-        os.environ["FORK_LAUNCHED"] = str(1)
+            os.environ["RANK"] = str(per_node * node + index)
+        os.environ["FORK_LAUNCHED"] = "1"
         self.launcher(*args)
