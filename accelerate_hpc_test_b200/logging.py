@@ -46,8 +46,8 @@ class MultiProcessAdapter(logging.LoggerAdapter):
             raise RuntimeError(_STATE_MISSING)
         only_main = kwargs.pop("main_process_only", True)
         ordered = kwargs.pop("in_order", False)
-        # report the caller of .info()/.warning(), not this adapter
-        kwargs.setdefault("stacklevel", 2)
+        # report the caller of .info()/.warning(), not this adapter: _emit <- log <- (logging internals, not counted) <- caller
+        kwargs.setdefault("stacklevel", 3)
         if not self.isEnabledFor(level):
             return
         if ordered:
@@ -66,7 +66,7 @@ class MultiProcessAdapter(logging.LoggerAdapter):
         if key in self._warned:
             return
         self._warned.add(key)
-        kwargs.setdefault("stacklevel", 3)
+        kwargs.setdefault("stacklevel", 4)
         self.warning(msg, *args, **kwargs)
 
 

@@ -35,6 +35,13 @@ def _lower(value) -> str:
     return str(value).lower()
 
 
+def _truthy(value) -> bool:
+    """Flags such as ``--fsdp_sync_module_states`` arrive as text ("true" / "false") from the CLI and as bool from YAML."""
+    if isinstance(value, str):
+        return value.strip().lower() in ("1", "true", "yes", "y", "on")
+    return bool(value)
+
+
 class EnvRule:
     """``args.<flag>`` → ``env[<variable>]`` through ``fmt``; skipped when the flag is absent or (``optional``) None."""
 
@@ -268,7 +275,7 @@ def prepare_multi_gpu_env(args: argparse.Namespace) -> dict[str, str]:
 
     env = _common_env(args)
     if args.use_fsdp:
-        if args.fsdp_cpu_ram_efficient_loading and not args.fsdp_sync_module_states:
+        if _truthy(args.fsdp_cpu_ram_efficient_loading) and not _truthy(args.fsdp_sync_module_states):
             raise ValueError("When using `--fsdp_cpu_ram_efficient_loading` set `--fsdp_sync_module_states` to `True`")
         env["ACCELERATE_USE_FSDP"] = "true"
         env["FSDP_VERSION"] = str(getattr(args, "fsdp_version", 1))
