@@ -484,6 +484,7 @@ static constexpr int NOALLOC_MAX_H = 8192;
 static __device__ __align__(256) float g_rmsnorm_bwd_noalloc_scratch[(size_t)NOALLOC_MAX_PARTS * NOALLOC_MAX_H];
 
 static int rmsnorm_noalloc_scratch(float** out) {
+  // written without a lock: two host threads racing on the first call of a device both store the same address
   static float* cached[64] = {nullptr};
   int dev = 0;
   B200_CUDA(cudaGetDevice(&dev));

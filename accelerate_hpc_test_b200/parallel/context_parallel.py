@@ -67,6 +67,11 @@ class CPComm:
         self.world = dist.get_world_size(self.group)
         self.device = torch.device(device)
         self.strategy = strategy
+        # K/V all-gather and dK/dV reduce-scatter run on the peer-memory kernels (TMA pull / NVLS reduction); c10d is only
+        # the CPU oracle path and the fallback for shapes the kernels do not take
+        from .peer_collectives import PeerCollectives
+
+        self.peer = PeerCollectives(self.group, self.device)
 
     def local_positions(self, S_loc: int, device) -> torch.Tensor:
         c = S_loc // 2
@@ -80,20 +85,11 @@ class CPComm:
 
     def all_gather_rows(self, x: torch.Tensor) -> torch.Tensor:
         """``[rows, w] -> [world, rows, w]``"""
-        out = torch.empty((self.world,) + tuple(x.shape), dtype=x.dtype, device=x.device)
-        dist.all_gather_into_tensor(out.view(-1, *x.shape[1:]), x.contiguous(), group=self.group)
-        return out
+        return self.peer.all_gather(x)
 
     def reduce_scatter_rows(self, x: torch.Tensor) -> torch.Tensor:
         """``[world, rows, w] -> [rows, w]`` (sum over ranks of slice ``rank``)"""
-        out = torch.empty(tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
-        if x.is_cuda:
-            dist.reduce_scatter_tensor(out, x.contiguous().view(-1, *x.shape[2:]), group=self.group)
-        else:  # gloo has no reduce_scatter
-            y = x.contiguous()
-            dist.all_reduce(y, group=self.group)
-            out.copy_(y[self.rank])
-        return out
+        return self.peer.reduce_scatter(x)
 
     def shift_labels_across_ranks(self, labels: torch.Tensor) -> torch.Tensor:
         parts = [torch.empty_like(labels) for _ in range(self.world)]

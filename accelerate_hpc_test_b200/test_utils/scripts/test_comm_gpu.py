@@ -247,13 +247,14 @@ def check_collectives(ws, dev, rank, world):
     return res
 
 
-def check_ddp(dev, rank, world):
+def check_ddp(dev, rank, world, tied: bool = False):
     from accelerate_hpc_test_b200 import Accelerator
     from accelerate_hpc_test_b200.models import LlamaConfig, LlamaForCausalLM
     from accelerate_hpc_test_b200.optim import FusedAdamW
     from accelerate_hpc_test_b200.state import AcceleratorState, GradientState, PartialState
 
-    cfg = LlamaConfig.tiny()
+    # tied=True: lm_head and embed_tokens share one Parameter, which then receives two native gradient deliveries per step
+    cfg = LlamaConfig.tiny(tie_word_embeddings=tied)
     torch.manual_seed(0)
     ref = LlamaForCausalLM(cfg, device=dev)
     torch.manual_seed(0)
@@ -281,8 +282,11 @@ def check_ddp(dev, rank, world):
         ref_opt.step()
     torch.cuda.synchronize()
     worst = max(rel(p, q) for p, q in zip(model.module.parameters(), ref.parameters()))
-    assert worst < 2e-2, ("ddp param mismatch", worst)
-    log(f"ddp ok (worst rel err {worst:.2e})")
+    assert worst < 2e-2, ("ddp param mismatch", tied, worst)
+    if tied:
+        assert model.module.lm_head.weight is model.module.model.embed_tokens.weight
+    log(f"ddp ok (tied_embeddings={tied}, worst rel err {worst:.2e})")
+    model.release()
     AcceleratorState._reset_state(True)
     GradientState._reset_state()
 
@@ -545,6 +549,7 @@ def main():
         ws.close()
     if "ddp" in what:
         check_ddp(dev, rank, world)
+        check_ddp(dev, rank, world, tied=True)
     if "fsdp" in what:
         check_fsdp(dev, rank, world, "0")
         check_fsdp(dev, rank, world, "1")
