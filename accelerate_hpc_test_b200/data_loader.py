@@ -1,29 +1,34 @@
-"""Data-loading layer: per-rank sharding, rank-0 dispatch, seedable sampling, mid-epoch skip.
+"""Data-loading layer: what ``Accelerator.prepare`` turns a ``torch.utils.data.DataLoader`` into.
 
-Behavioural parity with reference src/accelerate/data_loader.py: ``SeedableRandomSampler`` :73-107,
-``BatchSamplerShard`` :110-263, ``IterableDatasetShard`` :266-362, ``DataLoaderStateMixin`` :365-405,
-``DataLoaderAdapter`` :408-497, ``DataLoaderShard`` :500-648 (iterates one batch ahead to know
-``end_of_dataloader``), ``DataLoaderDispatcher`` :704-959, ``prepare_data_loader`` :996-1309 (rank
-arithmetic from the device mesh :1109-1145) and the skip helpers :1312-1451.  Written from the
-behaviour up (rounds of ``num_processes`` batches rather than the reference's index bookkeeping);
-``tests/test_data_loader.py`` pins the exact index lists.
+Three jobs:
 
-On CUDA the host->device copy of ``DataLoaderShard`` is issued one batch ahead on a side stream from
-pinned memory (``non_blocking``), so the step never waits for its inputs.
+* **who reads what** — ``BatchSamplerShard`` (map-style data) and ``IterableDatasetShard`` (streams) give each of ``P`` ranks its
+  share of every *round* of ``P`` batches; a ragged last round is dropped, left ragged (``even_batches=False``) or completed with
+  samples recycled from the start of the epoch (``_Refill``), so that every rank takes the same number of equally sized steps;
+  ``DataLoaderDispatcher`` is the other policy: rank 0 reads, everybody receives a slice over the process group;
+* **where the batch lives** — on a CUDA device ``DataLoaderShard`` issues the host→device copy of batch ``i+1`` from pinned memory on
+  a copy stream while step ``i`` computes (``_DeviceStager``); the loader keeps one batch in hand anyway, because it has to know
+  which batch is the last one (``end_of_dataloader`` / ``remainder`` drive ``gather_for_metrics`` and gradient accumulation);
+* **reproducibility** — ``SeedableRandomSampler`` (order is a function of seed + epoch), RNG synchronisation at the start of an
+  epoch, ``skip_first_batches`` for resuming in the middle of one, ``state_dict`` pass-through for torchdata's stateful loader.
+
+Behavioural parity: reference ``src/accelerate/data_loader.py`` — sampler :73-107, batch-sampler shard :110-263, iterable shard
+:266-362, state mixin :365-405, adapter :408-497, shard loader :500-648, dispatcher :704-959, ``prepare_data_loader`` :996-1309
+(mesh arithmetic :1109-1145), skipping :1312-1451.  ``tests/test_data_loader.py`` pins the exact index lists per rank.
 """
 
 from __future__ import annotations
 
-import importlib
+import inspect
 import math
-from contextlib import suppress
-from typing import Callable, Optional, Union
+import os
+from typing import Callable, Iterable, Iterator, Optional
 
 import torch
 from torch.utils.data import BatchSampler, DataLoader, IterableDataset, RandomSampler
 
 from .state import GradientState, PartialState
-from .utils.dataclasses import DistributedType, RNGType
+from .utils.dataclasses import DistributedType
 from .utils.imports import is_torchdata_stateful_dataloader_available
 from .utils.operations import (
     broadcast,
@@ -32,307 +37,416 @@ from .utils.operations import (
     find_batch_size,
     get_data_structure,
     initialize_tensors,
+    recursively_apply,
     send_to_device,
     slice_tensors,
 )
 from .utils.random import synchronize_rng_states
 
-# kwargs copied from the user's DataLoader when it is rebuilt around a sharded sampler
+# every keyword ``DataLoader`` accepts besides the dataset, with its default — read off the installed torch instead of a hand-kept table
 _PYTORCH_DATALOADER_KWARGS = {
-    "batch_size": 1, "shuffle": False, "sampler": None, "batch_sampler": None, "num_workers": 0, "collate_fn": None,
-    "pin_memory": False, "drop_last": False, "timeout": 0, "worker_init_fn": None, "multiprocessing_context": None,
-    "generator": None, "prefetch_factor": None, "persistent_workers": False, "pin_memory_device": "",
+    name: (None if spec.default is inspect.Parameter.empty else spec.default)
+    for name, spec in inspect.signature(DataLoader.__init__).parameters.items()
+    if name not in ("self", "dataset")
 }
-for _extra in ("in_order",):
-    if _extra in DataLoader.__init__.__code__.co_varnames:
-        _PYTORCH_DATALOADER_KWARGS[_extra] = True
+# the ones a rebuilt loader decides for itself
+_REBUILT = frozenset({"batch_size", "shuffle", "sampler", "batch_sampler", "drop_last"})
 
 
+def _inherited_kwargs(dataloader) -> dict:
+    """Construction arguments a rebuilt loader takes over from ``dataloader`` (workers, collate, pinning, ...)."""
+    return {name: getattr(dataloader, name, default) for name, default in _PYTORCH_DATALOADER_KWARGS.items() if name not in _REBUILT}
+
+
+def _cpu_generator() -> torch.Generator:
+    where = torch.get_default_device() if hasattr(torch, "get_default_device") else "cpu"
+    return torch.Generator(device=where)
+
+
+# ------------------------------------------------------------------------------------------------- sampling
 class SeedableRandomSampler(RandomSampler):
-    """``RandomSampler`` whose permutation of epoch ``e`` is a pure function of ``initial_seed + e``,
-    so every rank (and a resumed run) draws the same order without broadcasting RNG state."""
+    """Random order that is a pure function of ``data_seed + epoch``: ranks agree, and a resumed run repeats it, without any
+    RNG state being shipped around.  The epoch advances by itself after a full pass; ``set_epoch`` overrides it."""
 
-    def __init__(self, *args, **kwargs):
-        data_seed = kwargs.pop("data_seed", None)
+    def __init__(self, *args, data_seed: Optional[int] = None, **kwargs):
         super().__init__(*args, **kwargs)
-        self.initial_seed = data_seed if data_seed is not None else torch.random.initial_seed()
+        self.initial_seed = torch.random.initial_seed() if data_seed is None else data_seed
         self.epoch = 0
+
+    def set_epoch(self, epoch: int) -> None:
+        self.epoch = epoch
 
     def __iter__(self):
         if self.generator is None:
-            self.generator = torch.Generator(device=torch.get_default_device() if hasattr(torch, "get_default_device") else "cpu")
-            self.generator.manual_seed(self.initial_seed)
-        self.generator.manual_seed(self.epoch + self.initial_seed)
+            self.generator = _cpu_generator()
+        self.generator.manual_seed(self.initial_seed + self.epoch)
         yield from super().__iter__()
-        self.set_epoch(self.epoch + 1)
+        self.epoch += 1
 
-    def set_epoch(self, epoch: int):
-        self.epoch = epoch
+
+class _Refill:
+    """Samples remembered from the start of an epoch, handed out again (cyclically) to complete a ragged last round."""
+
+    def __init__(self, capacity: int):
+        self.pool: list = []
+        self.capacity = capacity  # how many more samples to remember
+        self.cursor = 0
+
+    def remember(self, samples: Iterable) -> None:
+        if self.capacity > 0:
+            kept = list(samples)[: self.capacity]
+            self.pool.extend(kept)
+            self.capacity -= len(kept)
+
+    def take(self, count: int) -> list:
+        out = []
+        while len(out) < count:
+            out.append(self.pool[self.cursor % len(self.pool)])
+            self.cursor += 1
+        return out
 
 
 class BatchSamplerShard(BatchSampler):
-    """View of a batch sampler for one of ``num_processes`` ranks.
+    """What rank ``process_index`` of ``num_processes`` sees of ``batch_sampler``.
 
-    ``split_batches=False``: batches are dealt out round-robin (rank r gets batches r, r+P, ...).
-    ``split_batches=True``: every batch is cut in P equal slices.
-    ``even_batches=True``: when the data does not divide evenly the tail is completed with
-    samples from the start of the epoch so every rank sees the same number of equally sized batches.
+    Dealing mode (default): batches go round the ranks — rank r gets batches r, r+P, r+2P, ...  Slicing mode
+    (``split_batches=True``): every batch is cut into P equal slices, rank r keeps slice r.  When the data does not fill the last
+    round: ``drop_last`` of the wrapped sampler drops it; otherwise ``even_batches=True`` completes it with samples from the start
+    of the epoch, and ``even_batches=False`` leaves the ranks with what there is (some get a shorter batch or none).
     """
 
-    def __init__(self, batch_sampler: BatchSampler, num_processes: int = 1, process_index: int = 0,
-                 split_batches: bool = False, even_batches: bool = True):
-        if split_batches and batch_sampler.batch_size % num_processes != 0:
-            raise ValueError(
-                f"To use `BatchSamplerShard` in `split_batches` mode, the batch size ({batch_sampler.batch_size}) "
-                f"needs to be a round multiple of the number of processes ({num_processes})."
-            )
+    def __init__(self, batch_sampler: BatchSampler, num_processes: int = 1, process_index: int = 0, split_batches: bool = False,
+                 even_batches: bool = True):
         self.batch_sampler = batch_sampler
-        self.num_processes = num_processes
-        self.process_index = process_index
-        self.split_batches = split_batches
-        self.even_batches = even_batches
+        self.num_processes, self.process_index = num_processes, process_index
+        self.split_batches, self.even_batches = split_batches, even_batches
         self.batch_size = getattr(batch_sampler, "batch_size", None)
         self.drop_last = getattr(batch_sampler, "drop_last", False)
-        if self.batch_size is None and self.even_batches:
+        if split_batches and self.batch_size % num_processes:
             raise ValueError(
-                "You need to use `even_batches=False` when the batch sampler has no batch size. If you "
-                "are not calling this method directly, set `accelerator.even_batches=False` instead."
+                f"To use `BatchSamplerShard` in `split_batches` mode, the batch size ({self.batch_size}) needs to be a round "
+                f"multiple of the number of processes ({num_processes})."
+            )
+        if even_batches and self.batch_size is None:
+            raise ValueError(
+                "You need to use `even_batches=False` when the batch sampler has no batch size. If you are not calling this method "
+                "directly, set `accelerator.even_batches=False` instead."
             )
 
     @property
-    def total_length(self):
+    def total_length(self) -> int:
         return len(self.batch_sampler)
 
-    def __len__(self):
-        n = len(self.batch_sampler)
+    def __len__(self) -> int:
+        batches = len(self.batch_sampler)
         if self.split_batches:
-            return n
-        if n % self.num_processes == 0:
-            return n // self.num_processes
-        full_rounds = n // self.num_processes
-        if self.drop_last:
-            return full_rounds
-        if self.even_batches:
-            return full_rounds + 1
-        return full_rounds + 1 if self.process_index < n % self.num_processes else full_rounds
+            return batches
+        rounds, extra = divmod(batches, self.num_processes)
+        if extra == 0 or self.drop_last:
+            return rounds
+        if self.even_batches or self.process_index < extra:
+            return rounds + 1
+        return rounds
 
     def __iter__(self):
-        return self._iter_with_split() if self.split_batches else self._iter_with_no_split()
+        return self._sliced() if self.split_batches else self._dealt()
 
-    def _is_full(self, batch) -> bool:
-        return self.batch_size is None or len(batch) == self.batch_size
+    def _short(self, batch) -> bool:
+        return self.batch_size is not None and len(batch) < self.batch_size
 
-    def _iter_with_split(self):
-        width = self.batch_sampler.batch_size // self.num_processes
-        lo, hi = width * self.process_index, width * (self.process_index + 1)
-        first = None
-        last = None
+    def _sliced(self):
+        width = self.batch_size // self.num_processes
+        mine = slice(width * self.process_index, width * (self.process_index + 1))
+        refill = _Refill(self.batch_size)
+        tail = None
         for batch in self.batch_sampler:
-            if first is None:
-                first = list(batch)
-            last = batch
-            if len(batch) == self.batch_size:
-                yield batch[lo:hi]
-        if self.drop_last or first is None or len(last) == self.batch_size:
+            refill.remember(batch)
+            if self._short(batch):
+                tail = list(batch)  # only the last batch can be short
+            else:
+                yield batch[mine]
+        if tail is None or self.drop_last:
             return
-        # ragged tail
-        if not self.even_batches:
-            if len(last) > lo:
-                yield last[lo:hi]
-            return
-        filler = list(first)
-        while len(filler) < self.batch_size:
-            filler += filler
-        yield (list(last) + filler)[lo:hi]
+        if self.even_batches:
+            yield (tail + refill.take(self.batch_size - len(tail)))[mine]
+        elif len(tail) > mine.start:
+            yield tail[mine]
 
-    def _iter_with_no_split(self):
-        P, me = self.num_processes, self.process_index
-        head: list = []  # samples of the first P batches, for the wrap-around completion
-        seen_batches = 0
-        pending: list = []  # batches of the round being assembled
+    def _dealt(self):
+        ranks, me = self.num_processes, self.process_index
+        refill = _Refill(0 if self.drop_last or self.batch_size is None else ranks * self.batch_size)
+        hand: list = []  # the round being dealt
         for batch in self.batch_sampler:
-            if not self.drop_last and seen_batches < P:
-                head += list(batch)
-            seen_batches += 1
-            pending.append(batch)
-            if len(pending) == P:
-                if self._is_full(batch):
-                    yield pending[me]
-                    pending = []
-                # else: the short batch ends the epoch; handled below
-        if self.drop_last or seen_batches == 0 or not pending:
+            refill.remember(batch)
+            hand.append(batch)
+            if len(hand) == ranks and not self._short(batch):
+                yield hand[me]
+                hand = []
+        if not hand or self.drop_last:
             return
         if not self.even_batches:
-            if me < len(pending) and len(pending[me]) > 0:
-                yield pending[me]
+            if me < len(hand) and len(hand[me]) > 0:
+                yield hand[me]
             return
-        # complete the round: top up the short batch, then mint new batches, all from `head`
-        while len(head) < P * self.batch_size:
-            head += head
-        cursor = 0
-        completed = [list(b) for b in pending]
-        if len(completed[-1]) < self.batch_size:
-            need = self.batch_size - len(completed[-1])
-            completed[-1] += head[cursor:cursor + need]
-            cursor += need
-        while len(completed) < P:
-            completed.append(head[cursor:cursor + self.batch_size])
-            cursor += self.batch_size
-        yield completed[me]
+        # top the short batch up, then mint the batches the round still lacks, all from the start of the epoch
+        hand = [list(batch) for batch in hand]
+        hand[-1] += refill.take(self.batch_size - len(hand[-1]))
+        while len(hand) < ranks:
+            hand.append(refill.take(self.batch_size))
+        yield hand[me]
 
 
 class IterableDatasetShard(IterableDataset):
-    """Per-rank view of an iterable dataset: buffer one global batch, yield this rank's slice of it."""
+    """Rank ``process_index``'s view of a stream: buffer one *global* batch (``batch_size`` x ranks, or just ``batch_size`` when
+    ``split_batches``), emit this rank's contiguous part of it.  A partial last global batch is dropped or completed from the
+    first one."""
 
     def __init__(self, dataset: IterableDataset, batch_size: int = 1, drop_last: bool = False, num_processes: int = 1,
                  process_index: int = 0, split_batches: bool = False):
-        if split_batches and batch_size > 1 and batch_size % num_processes != 0:
+        if split_batches and batch_size > 1 and batch_size % num_processes:
             raise ValueError(
-                f"To use `IterableDatasetShard` in `split_batches` mode, the batch size ({batch_size}) "
-                f"needs to be a round multiple of the number of processes ({num_processes})."
+                f"To use `IterableDatasetShard` in `split_batches` mode, the batch size ({batch_size}) needs to be a round "
+                f"multiple of the number of processes ({num_processes})."
             )
         self.dataset = dataset
-        self.batch_size = batch_size
-        self.drop_last = drop_last
-        self.num_processes = num_processes
-        self.process_index = process_index
+        self.batch_size, self.drop_last = batch_size, drop_last
+        self.num_processes, self.process_index = num_processes, process_index
         self.split_batches = split_batches
 
-    def set_epoch(self, epoch):
+    def _geometry(self) -> tuple[int, int]:
+        """(samples per global batch, samples of it this rank keeps)"""
+        if self.split_batches:
+            return self.batch_size, self.batch_size // self.num_processes
+        return self.batch_size * self.num_processes, self.batch_size
+
+    def set_epoch(self, epoch: int) -> None:
         self.epoch = epoch
         if hasattr(self.dataset, "set_epoch"):
             self.dataset.set_epoch(epoch)
 
-    def _sizes(self):
-        global_bs = self.batch_size if self.split_batches else self.batch_size * self.num_processes
-        local_bs = self.batch_size // self.num_processes if self.split_batches else self.batch_size
-        return global_bs, local_bs
-
-    def __len__(self):
-        global_bs, local_bs = self._sizes()
-        if self.drop_last:
-            return (len(self.dataset) // global_bs) * local_bs
-        return math.ceil(len(self.dataset) / global_bs) * local_bs
+    def __len__(self) -> int:
+        whole, part = self._geometry()
+        count = len(self.dataset) / whole
+        return (math.floor(count) if self.drop_last else math.ceil(count)) * part
 
     def __iter__(self):
-        if (not hasattr(self.dataset, "set_epoch") and hasattr(self.dataset, "generator")
-                and isinstance(self.dataset.generator, torch.Generator)):
-            self.dataset.generator.manual_seed(getattr(self, "epoch", 0))
-        global_bs, local_bs = self._sizes()
-        mine = range(self.process_index * local_bs, (self.process_index + 1) * local_bs)
-        first_global = None
-        buf = []
-        for element in self.dataset:
-            buf.append(element)
-            if len(buf) == global_bs:
-                for i in mine:
-                    yield buf[i]
-                if first_global is None:
-                    first_global = list(buf)
-                buf = []
-        if not self.drop_last and len(buf) > 0:
-            if first_global is None:
-                first_global = list(buf)
-            while len(buf) < global_bs:
-                buf += first_global
-            for i in mine:
-                yield buf[i]
+        own_generator = getattr(self.dataset, "generator", None)
+        if isinstance(own_generator, torch.Generator) and not hasattr(self.dataset, "set_epoch"):
+            own_generator.manual_seed(getattr(self, "epoch", 0))
+        whole, part = self._geometry()
+        lo = self.process_index * part
+        refill = _Refill(whole)
+        pending: list = []
+        for sample in self.dataset:
+            pending.append(sample)
+            if len(pending) == whole:
+                refill.remember(pending)
+                yield from pending[lo : lo + part]
+                pending = []
+        if pending and not self.drop_last:
+            refill.remember(pending)
+            pending += refill.take(whole - len(pending))
+            yield from pending[lo : lo + part]
 
 
+# ------------------------------------------------------------------------------------------------- sampler plumbing
+def _index_batcher(dataloader):
+    """The object that produces lists of indices: with ``DataLoader(sampler=<a BatchSampler>, batch_size=None)`` that is the sampler."""
+    return dataloader.sampler if isinstance(dataloader.sampler, BatchSampler) else dataloader.batch_sampler
+
+
+def _batcher_layers(dataloader) -> Iterator:
+    """The batch sampler and whatever it wraps (shard / skip wrappers expose the wrapped one as ``.batch_sampler``), outside in."""
+    layer, seen = _index_batcher(dataloader), set()
+    while layer is not None and id(layer) not in seen:
+        seen.add(id(layer))
+        yield layer
+        layer = getattr(layer, "batch_sampler", None)
+
+
+def get_sampler(dataloader):
+    """The index sampler under the batch-sampler wrappers of ``dataloader`` (None for iterable datasets)."""
+    for layer in _batcher_layers(dataloader):
+        found = getattr(layer, "sampler", None)
+        if found is not None:
+            return found
+    return None
+
+
+def _install_sampler(dataloader, sampler) -> None:
+    layers = list(_batcher_layers(dataloader))
+    for depth, layer in enumerate(layers):
+        if depth == 0 or hasattr(layer, "sampler"):
+            layer.sampler = sampler
+
+
+def _announce_epoch(dataloader, epoch: int) -> None:
+    """Tell everything that shuffles by epoch: batch samplers, their index samplers, else the dataset."""
+    told = set()
+    for layer in _batcher_layers(dataloader):
+        for target in (layer, getattr(layer, "sampler", None)):
+            if target is not None and id(target) not in told and hasattr(target, "set_epoch"):
+                told.add(id(target))
+                target.set_epoch(epoch)
+    if not told and hasattr(dataloader.dataset, "set_epoch"):
+        dataloader.dataset.set_epoch(epoch)
+
+
+# ------------------------------------------------------------------------------------------------- loader building blocks
 class DataLoaderStateMixin:
-    """``end_of_dataloader`` / ``remainder`` bookkeeping shared by the prepared dataloaders."""
+    """``end_of_dataloader`` (true while the last batch is being consumed) and ``remainder`` (how many real samples the last
+    global batch holds; -1 when unknown), plus registration with ``GradientState`` for the duration of an iteration."""
 
     def __init_subclass__(cls, **kwargs):
         cls.end_of_dataloader = False
         cls.remainder = -1
 
-    def reset(self):
-        self.end_of_dataloader = False
-        self.remainder = -1
+    def reset(self) -> None:
+        self.end_of_dataloader, self.remainder = False, -1
 
-    def begin(self):
-        """Register with ``GradientState`` and compute how many samples the last batch duplicates."""
+    def begin(self) -> None:
         self.reset()
-        with suppress(Exception):
-            if not self._drop_last:
-                length = getattr(self.dataset, "total_dataset_length", len(self.dataset))
-                self.remainder = length % self.total_batch_size
+        if not self._drop_last:
+            try:
+                samples = getattr(self.dataset, "total_dataset_length", None)
+                self.remainder = (len(self.dataset) if samples is None else samples) % self.total_batch_size
+            except Exception:  # streams without a length, batch samplers without a batch size
+                pass
         self.gradient_state._add_dataloader(self)
 
-    def end(self):
+    def end(self) -> None:
         self.gradient_state._remove_dataloader(self)
 
 
 class DataLoaderAdapter:
-    """Composition over a ``DataLoader`` or ``torchdata.StatefulDataLoader`` with attribute forwarding."""
+    """Owns the real loader (``torch.utils.data.DataLoader`` or torchdata's ``StatefulDataLoader``) and forwards to it.  It also
+    reports that loader's class as its own, so ``isinstance(prepared, DataLoader)`` keeps holding in user code."""
 
     def __init__(self, dataset, use_stateful_dataloader: bool = False, batch_sampler=None, **kwargs):
         self.use_stateful_dataloader = use_stateful_dataloader
+        loader_cls = DataLoader
         if use_stateful_dataloader:
             if not is_torchdata_stateful_dataloader_available():
                 raise ImportError("StatefulDataLoader is not available. Please install torchdata version 0.8.0 or higher to use it.")
-            from torchdata.stateful_dataloader import StatefulDataLoader
+            from torchdata.stateful_dataloader import StatefulDataLoader as loader_cls
+        self.base_dataloader = loader_cls(dataset, batch_sampler=batch_sampler, **kwargs)
+        self._snapshot(adjust=False)
 
-            self.base_dataloader = StatefulDataLoader(dataset, batch_sampler=batch_sampler, **kwargs)
-        else:
-            self.base_dataloader = DataLoader(dataset, batch_sampler=batch_sampler, **kwargs)
-        if hasattr(self.base_dataloader, "state_dict"):
-            self.dl_state_dict = self.base_dataloader.state_dict()
+    __class__ = property(lambda self: self.base_dataloader.__class__)
 
     def __getattr__(self, name):
-        if name == "base_dataloader":
-            raise AttributeError()
+        if name == "base_dataloader":  # not constructed yet (unpickling): do not recurse
+            raise AttributeError(name)
         return getattr(self.base_dataloader, name)
+
+    def __len__(self) -> int:
+        return len(self.base_dataloader)
 
     def state_dict(self):
         return self.dl_state_dict
 
-    def load_state_dict(self, state_dict):
+    def load_state_dict(self, state_dict) -> None:
         self.base_dataloader.load_state_dict(state_dict)
 
-    @property
-    def __class__(self):
-        # so isinstance(prepared_dl, DataLoader) (or StatefulDataLoader) keeps holding
-        return self.base_dataloader.__class__
+    def adjust_state_dict_for_prefetch(self) -> None:
+        """The wrapped loader runs ahead of what has been handed out (one batch in hand per rank): take that back out of the counts."""
+        if PartialState().distributed_type == DistributedType.NO:
+            return
+        ahead = PartialState().num_processes - 1
+        state = self.dl_state_dict
+        for counter in ("_sampler_iter_yielded", "_num_yielded"):
+            if state[counter] > 0:
+                state[counter] -= ahead
+        inner = state["_index_sampler_state"]
+        if inner is not None and inner.get("samples_yielded", 0) > 0:
+            inner["samples_yielded"] -= self.batch_size * ahead
 
-    def __len__(self):
-        return len(self.base_dataloader)
-
-    def adjust_state_dict_for_prefetch(self):
-        """A stateful dataloader has already pulled ``prefetch`` batches we have not yielded: rewind the count."""
-        if PartialState().distributed_type != DistributedType.NO:
-            factor = PartialState().num_processes - 1
-            if self.dl_state_dict["_sampler_iter_yielded"] > 0:
-                self.dl_state_dict["_sampler_iter_yielded"] -= factor
-            if self.dl_state_dict["_num_yielded"] > 0:
-                self.dl_state_dict["_num_yielded"] -= factor
-            if self.dl_state_dict["_index_sampler_state"] is not None:
-                st = self.dl_state_dict["_index_sampler_state"]
-                if "samples_yielded" in st and st["samples_yielded"] > 0:
-                    st["samples_yielded"] -= self.batch_size * factor
-
-    def _update_state_dict(self):
-        if hasattr(self.base_dataloader, "state_dict"):
-            self.dl_state_dict = self.base_dataloader.state_dict()
+    def _snapshot(self, adjust: bool = True) -> None:
+        if not hasattr(self.base_dataloader, "state_dict"):
+            return
+        self.dl_state_dict = self.base_dataloader.state_dict()
+        if adjust:
             self.adjust_state_dict_for_prefetch()
             self.dl_state_dict["_iterator_finished"] = self.end_of_dataloader
 
+    _update_state_dict = _snapshot  # reference-compatible name
+
+
+def _flag_last(iterator: Iterator, before_fetch: Optional[Callable[[], None]] = None, on_fetch: Callable = lambda item: item):
+    """``(item, is_last)`` for every item of ``iterator``, which takes reading one item ahead.  ``before_fetch`` runs before every
+    read-ahead, ``on_fetch`` maps every item the moment it has been read (that is where the device copy is started)."""
+    nothing = object()
+    held = next(iterator, nothing)
+    if held is nothing:
+        return
+    held = on_fetch(held)
+    while True:
+        if before_fetch is not None:
+            before_fetch()
+        ahead = next(iterator, nothing)
+        if ahead is nothing:
+            yield held, True
+            return
+        ahead = on_fetch(ahead)
+        yield held, False
+        held = ahead
+
+
+class _DeviceStager:
+    """Host→device copies one batch ahead of the consumer.
+
+    ``stage`` pins what is not pinned yet and enqueues the copies on a private stream; ``claim`` makes the consumer's stream wait
+    for exactly those copies (an event, no host synchronisation) and hands the tensors over to it (``record_stream``, so the
+    caching allocator does not recycle them under a kernel still reading).  Off CUDA, or when the loader was not asked for
+    non-blocking copies, ``stage`` is a plain synchronous ``send_to_device`` and ``claim`` does nothing.
+    """
+
+    def __init__(self, device, non_blocking: bool):
+        self.device = None if device is None else torch.device(device)
+        self.non_blocking = non_blocking
+        self.overlapped = (
+            non_blocking and self.device is not None and self.device.type == "cuda" and torch.cuda.is_available()
+            and os.environ.get("ACCELERATE_B200_ASYNC_H2D", "1") != "0"
+        )
+        self.stream = torch.cuda.Stream(device=self.device) if self.overlapped else None
+
+    @staticmethod
+    def _pinned(t: torch.Tensor) -> torch.Tensor:
+        return t if t.device.type != "cpu" or t.is_pinned() else t.pin_memory()
+
+    def stage(self, batch):
+        if self.device is None:
+            return batch, None
+        if not self.overlapped:
+            return send_to_device(batch, self.device, non_blocking=self.non_blocking), None
+        batch = recursively_apply(self._pinned, batch)
+        with torch.cuda.stream(self.stream):
+            moved = send_to_device(batch, self.device, non_blocking=True)
+            landed = torch.cuda.Event()
+            landed.record(self.stream)
+        return moved, landed
+
+    def claim(self, staged):
+        moved, landed = staged
+        if landed is not None:
+            consumer = torch.cuda.current_stream(self.device)
+            consumer.wait_event(landed)
+            recursively_apply(lambda t: (t.record_stream(consumer), t)[1] if t.is_cuda else t, moved)
+        return moved
+
 
 class DataLoaderShard(DataLoaderAdapter, DataLoaderStateMixin):
-    """The per-rank dataloader: synchronises RNG at epoch start, moves batches to the device and knows
-    when it is on its last batch (it always holds one batch in hand)."""
+    """The loader every rank iterates on its own share of the data.  At the start of a pass it synchronises the requested RNGs
+    and announces the epoch; batches arrive on ``device``; the last batch is flagged while the loop body still runs on it."""
 
     def __init__(self, dataset, device=None, rng_types=None, synchronized_generator=None, skip_batches: int = 0,
                  use_stateful_dataloader: bool = False, _drop_last: bool = False, _non_blocking: bool = False,
                  torch_device_mesh=None, **kwargs):
         super().__init__(dataset, use_stateful_dataloader=use_stateful_dataloader, **kwargs)
-        self.device = device
-        self.rng_types = rng_types
-        self.synchronized_generator = synchronized_generator
+        self.device, self.rng_types, self.synchronized_generator = device, rng_types, synchronized_generator
         self.skip_batches = skip_batches
+        self._drop_last, self._non_blocking = _drop_last, _non_blocking
         self.gradient_state = GradientState()
-        self._drop_last = _drop_last
-        self._non_blocking = _non_blocking
         self.iteration = 0
 
     def __iter__(self):
@@ -340,259 +454,218 @@ class DataLoaderShard(DataLoaderAdapter, DataLoaderStateMixin):
             synchronize_rng_states(self.rng_types, self.synchronized_generator)
         self.begin()
         self.set_epoch(self.iteration)
-        it = self.base_dataloader.__iter__()
-        try:
-            current = next(it)
-        except StopIteration:
-            self.end()
-            return
-        index = 0
-        while True:
-            if self.device is not None:
-                current = send_to_device(current, self.device, non_blocking=self._non_blocking)
-            self._update_state_dict()
-            try:
-                upcoming = next(it)
-            except StopIteration:
+        stager = _DeviceStager(self.device, self._non_blocking)
+        stream = _flag_last(iter(self.base_dataloader), before_fetch=self._snapshot, on_fetch=stager.stage)
+        for position, (staged, is_last) in enumerate(stream):
+            if is_last:
                 self.end_of_dataloader = True
-                self._update_state_dict()
-                if index >= self.skip_batches:
-                    yield current
-                break
-            if index >= self.skip_batches:
-                yield current
-            index += 1
-            current = upcoming
+                self._snapshot()
+            if position >= self.skip_batches:
+                yield stager.claim(staged)
         self.iteration += 1
         self.end()
 
     def __reduce__(self):
-        args = super().__reduce__()
-        return (DataLoaderShard, *args[1:])
+        return (DataLoaderShard, *super().__reduce__()[1:])
 
-    def set_epoch(self, epoch: int):
-        if self.iteration != epoch:
-            self.iteration = epoch
-        if hasattr(self.batch_sampler, "set_epoch"):
-            self.batch_sampler.set_epoch(epoch)
-        if hasattr(self.batch_sampler, "sampler") and hasattr(self.batch_sampler.sampler, "set_epoch"):
-            self.batch_sampler.sampler.set_epoch(epoch)
-        if (hasattr(self.batch_sampler, "batch_sampler") and hasattr(self.batch_sampler.batch_sampler, "sampler")
-                and hasattr(self.batch_sampler.batch_sampler.sampler, "set_epoch")):
-            self.batch_sampler.batch_sampler.sampler.set_epoch(epoch)
-        elif hasattr(self.dataset, "set_epoch"):
-            self.dataset.set_epoch(epoch)
+    def set_epoch(self, epoch: int) -> None:
+        self.iteration = epoch
+        _announce_epoch(self, epoch)
 
     @property
-    def total_batch_size(self):
-        bs = self.sampler if isinstance(self.sampler, BatchSampler) else self.batch_sampler
-        if getattr(bs, "split_batches", False):
-            return bs.batch_size
-        return bs.batch_size * getattr(bs, "num_processes", 1)
+    def total_batch_size(self) -> int:
+        batcher = _index_batcher(self)
+        per_rank_factor = 1 if getattr(batcher, "split_batches", False) else getattr(batcher, "num_processes", 1)
+        return batcher.batch_size * per_rank_factor
 
     @property
-    def total_dataset_length(self):
-        if hasattr(self.dataset, "total_length"):
-            return self.dataset.total_length
-        return len(self.dataset)
+    def total_dataset_length(self) -> int:
+        return getattr(self.dataset, "total_length", None) or len(self.dataset)
 
     def get_sampler(self):
         return get_sampler(self)
 
-    def set_sampler(self, sampler):
-        sampler_is_batch_sampler = isinstance(self.sampler, BatchSampler)
-        if sampler_is_batch_sampler:
-            self.sampler.sampler = sampler
-        else:
-            self.batch_sampler.sampler = sampler
-            if hasattr(self.batch_sampler, "batch_sampler"):
-                self.batch_sampler.batch_sampler.sampler = sampler
+    def set_sampler(self, sampler) -> None:
+        _install_sampler(self, sampler)
 
 
 class DataLoaderDispatcher(DataLoaderAdapter, DataLoaderStateMixin):
-    """Only rank 0 reads the data: it broadcasts each global batch's structure (pickled) and tensors,
-    and every rank keeps its slice.  Useful for iterable datasets that cannot be sharded."""
+    """Rank 0 is the only reader.  For every global batch it tells the group what is coming (the batch's structure — shapes and
+    dtypes — and whether it is the last), then the tensors are broadcast and every rank keeps its slice.  Meant for streams that
+    cannot be sharded; costs one object broadcast and one tensor broadcast per step."""
 
     def __init__(self, dataset, split_batches: bool = False, skip_batches: int = 0, use_stateful_dataloader: bool = False,
                  _drop_last: bool = False, _non_blocking: bool = False, slice_fn=None, torch_device_mesh=None, **kwargs):
-        shuffle = False
         super().__init__(dataset, use_stateful_dataloader=use_stateful_dataloader, **kwargs)
-        self.split_batches = split_batches
-        self.gradient_state = GradientState()
-        self.state = PartialState()
-        self._drop_last = _drop_last
-        self._non_blocking = _non_blocking
-        self.skip_batches = skip_batches
+        self.split_batches, self.skip_batches = split_batches, skip_batches
+        self._drop_last, self._non_blocking = _drop_last, _non_blocking
+        self.gradient_state, self.state = GradientState(), PartialState()
+        self.slice_fn = slice_fn or slice_tensors
         self.torch_device_mesh = torch_device_mesh
-        self.slice_fn = slice_tensors if slice_fn is None else slice_fn
         self.iteration = 0
-        # with a mesh, ranks that share tp/cp/sp coordinates must receive the same slice
-        self.submesh_tp = self.submesh_dp = self.submesh_fsdp = None
-        if torch_device_mesh is not None:
-            names = torch_device_mesh.mesh_dim_names or ()
-            self.submesh_tp = torch_device_mesh["tp"] if "tp" in names else None
-            self.submesh_dp = torch_device_mesh["dp"] if "dp" in names else None
-            self.submesh_fsdp = torch_device_mesh["fsdp"] if "fsdp" in names else None
-        if self.submesh_tp is not None and (self.submesh_dp or self.submesh_fsdp):
+        axes = () if torch_device_mesh is None else tuple(torch_device_mesh.mesh_dim_names or ())
+        self.submesh_tp, self.submesh_dp, self.submesh_fsdp = (torch_device_mesh[a] if a in axes else None for a in ("tp", "dp", "fsdp"))
+        if self.submesh_tp is not None:
+            # ranks of one tp group would need the same slice: that routing does not exist here (the sharded loader has it)
             raise ValueError("TP + (DP/FSDP) is not yet supported in dispatch mode")
 
-    def _fetch_batches(self, iterator):
-        """(batch or None, batch_info=[structure, stop_iteration]) — rank 0 reads, everybody learns the structure."""
-        batches, batch = None, None
-        if self.state.process_index == 0:
-            if self.submesh_tp is not None:
-                raise ValueError("Dispatch mode with a TP sub-mesh is not supported; use sharded mode")
-            try:
-                if self.split_batches:
-                    self._update_state_dict()
-                    batch = next(iterator)
-                else:
-                    batches = []
-                    for _ in range(self.state.num_processes):
-                        self._update_state_dict()
-                        batches.append(next(iterator))
-                    try:
-                        batch = concatenate(batches, dim=0)
-                    except RuntimeError as e:
-                        raise RuntimeError(
-                            "You can't use batches of different size with `dispatch_batches=True` or when using an `IterableDataset`."
-                            "either pass `dispatch_batches=False` and have each process fetch its own batch "
-                            " or pass `split_batches=True`. By doing so, the main process will fetch a full batch and "
-                            "slice it into `num_processes` batches for each process."
-                        ) from e
-                batch_info = [get_data_structure(batch), False]
-            except StopIteration:
-                batch_info = [None, True]
-        else:
-            batch_info = [None, self._stop_iteration]
-        broadcast_object_list(batch_info)
-        self._stop_iteration = batch_info[1]
-        if self._stop_iteration:
-            # a ragged tail: rank 0 may hold some batches that did not fill the round
-            if not self.split_batches and not self._drop_last:
-                if self.state.process_index == 0 and batches is not None and len(batches) > 0:
-                    batch = concatenate(batches, dim=0)
-                    batch_info = [get_data_structure(batch), False]
-                else:
-                    batch_info = [None, True]
-                broadcast_object_list(batch_info)
-        return batch, batch_info
+    # -- rank 0 ---------------------------------------------------------------------------------------------
+    def _global_batches(self):
+        """Global batches as rank 0 reads them: one loader batch (``split_batches``) or ``num_processes`` of them concatenated; a
+        last incomplete group is kept unless the loader drops its tail."""
+        source = iter(self.base_dataloader)
+        group_size = 1 if self.split_batches else self.state.num_processes
+        while True:
+            group = []
+            for _ in range(group_size):
+                self._snapshot()
+                try:
+                    group.append(next(source))
+                except StopIteration:
+                    break
+            exhausted = len(group) < group_size
+            if group and not (exhausted and self._drop_last):
+                try:
+                    yield group[0] if self.split_batches else concatenate(group, dim=0)
+                except RuntimeError as err:
+                    raise RuntimeError(
+                        "You can't use batches of different size with `dispatch_batches=True` or when using an `IterableDataset`."
+                        "either pass `dispatch_batches=False` and have each process fetch its own batch  or pass `split_batches=True`. "
+                        "By doing so, the main process will fetch a full batch and slice it into `num_processes` batches for each process."
+                    ) from err
+            if exhausted:
+                return
 
+    def _headers(self):
+        """``(batch or None, structure, is_last)`` on every rank, in lock step.  A closing ``structure=None`` header ends an empty pass."""
+        if self.state.process_index == 0:
+            sent = False
+            for batch, is_last in _flag_last(self._global_batches()):
+                broadcast_object_list([get_data_structure(batch), is_last])
+                sent = True
+                yield batch, None, is_last
+            if not sent:
+                broadcast_object_list([None, True])
+            return
+        while True:
+            header = [None, True]
+            broadcast_object_list(header)
+            if header[0] is None:
+                return
+            yield None, header[0], header[1]
+            if header[1]:
+                return
+
+    # -- every rank -----------------------------------------------------------------------------------------
     def __iter__(self):
         self.begin()
         self.set_epoch(self.iteration)
-        main_iterator = None
-        if self.state.process_index == 0:
-            main_iterator = self.base_dataloader.__iter__()
-        stop_iteration = False
-        self._stop_iteration = False
-        first_batch = None
-        next_batch, next_batch_info = self._fetch_batches(main_iterator)
-        batch_index = 0
-        while not stop_iteration:
-            batch, batch_info = next_batch, next_batch_info
-            if self.state.process_index != 0:
-                batch = initialize_tensors(batch_info[0])
-            batch = send_to_device(batch, self.state.device, non_blocking=self._non_blocking)
-            batch = broadcast(batch, from_process=0)
-            if not self._drop_last and first_batch is None:
-                first_batch = self.slice_fn(batch, slice(0, self.state.num_processes), process_index=self.state.process_index,
-                                            num_processes=self.state.num_processes)
+        ranks, me = self.state.num_processes, self.state.process_index
+        opening = None  # first `ranks` samples of the epoch, to complete a last global batch that does not divide
+        for position, (batch, structure, is_last) in enumerate(self._headers()):
             if batch is None:
-                raise ValueError(f"Batch does not contain any data (`{batch}`). At the end of all iterable data available before expected stop iteration.")
-            observed_batch_size = find_batch_size(batch)
-            batch_size = observed_batch_size // self.state.num_processes
-            stop_iteration = self._stop_iteration
-            if not stop_iteration:
-                # peek: is there another global batch?
-                next_batch, next_batch_info = self._fetch_batches(main_iterator)
-                if self._stop_iteration and next_batch_info[0] is None:
-                    stop_iteration = True
-            if not self._drop_last and stop_iteration and observed_batch_size % self.state.num_processes != 0:
-                # complete the last global batch with samples from the first one
-                batch = concatenate([batch, first_batch], dim=0)
-                batch_size += 1
-            data_slice = slice(self.state.process_index * batch_size, (self.state.process_index + 1) * batch_size)
-            batch = self.slice_fn(batch, data_slice, process_index=self.state.process_index, num_processes=self.state.num_processes)
-            if stop_iteration:
+                batch = initialize_tensors(structure)
+            batch = broadcast(send_to_device(batch, self.state.device, non_blocking=self._non_blocking), from_process=0)
+            if opening is None and not self._drop_last:
+                opening = self.slice_fn(batch, slice(0, ranks), process_index=me, num_processes=ranks)
+            observed = find_batch_size(batch)
+            share = observed // ranks
+            if is_last and observed % ranks and not self._drop_last:
+                batch = concatenate([batch, opening], dim=0)
+                share += 1
+            batch = self.slice_fn(batch, slice(me * share, (me + 1) * share), process_index=me, num_processes=ranks)
+            if is_last:
                 self.end_of_dataloader = True
-                self._update_state_dict()
-                self.remainder = observed_batch_size
-            if batch_index >= self.skip_batches:
+                self._snapshot()
+                self.remainder = observed
+            if position >= self.skip_batches:
                 yield batch
-            batch_index += 1
         self.iteration += 1
         self.end()
 
-    def set_epoch(self, epoch: int):
-        if self.iteration != epoch:
-            self.iteration = epoch
-        if hasattr(self.batch_sampler, "sampler") and hasattr(self.batch_sampler.sampler, "set_epoch"):
-            self.batch_sampler.sampler.set_epoch(epoch)
-        elif hasattr(self.dataset, "set_epoch"):
-            self.dataset.set_epoch(epoch)
+    def set_epoch(self, epoch: int) -> None:
+        self.iteration = epoch
+        _announce_epoch(self, epoch)
 
-    def __len__(self):
-        whole_length = len(self.base_dataloader)
+    def __len__(self) -> int:
+        batches = len(self.base_dataloader)
         if self.split_batches:
-            return whole_length
-        if self._drop_last:
-            return whole_length // self.state.num_processes
-        return math.ceil(whole_length / self.state.num_processes)
+            return batches
+        per_rank = batches / self.state.num_processes
+        return math.floor(per_rank) if self._drop_last else math.ceil(per_rank)
 
     def __reduce__(self):
-        args = super().__reduce__()
-        return (DataLoaderDispatcher, *args[1:])
+        return (DataLoaderDispatcher, *super().__reduce__()[1:])
 
     @property
-    def total_batch_size(self):
-        return self.dataset.batch_size if self.split_batches else (self.dataset.batch_size * self.dataset.num_processes)
+    def total_batch_size(self) -> int:
+        inner = self.dataset
+        return inner.batch_size if self.split_batches else inner.batch_size * inner.num_processes
 
     @property
-    def total_dataset_length(self):
+    def total_dataset_length(self) -> int:
         return len(self.dataset)
 
     def get_sampler(self):
         return get_sampler(self)
 
-    def set_sampler(self, sampler):
-        sampler_is_batch_sampler = isinstance(self.sampler, BatchSampler)
-        if sampler_is_batch_sampler:
-            self.sampler.sampler = sampler
-        else:
-            self.batch_sampler.sampler = sampler
-            if hasattr(self.batch_sampler, "batch_sampler"):
-                self.batch_sampler.batch_sampler.sampler = sampler
+    def set_sampler(self, sampler) -> None:
+        _install_sampler(self, sampler)
 
 
-def get_sampler(dataloader):
-    """The index sampler underneath whatever batch-sampler wrappers ``dataloader`` carries."""
-    sampler_is_batch_sampler = isinstance(dataloader.sampler, BatchSampler)
-    if sampler_is_batch_sampler:
-        sampler = getattr(dataloader.sampler, "sampler", None)
-    else:
-        sampler = getattr(dataloader.batch_sampler, "sampler", None)
-    return sampler
-
-
-def _mesh_data_ranks(torch_device_mesh, process_index: int, num_processes: int):
+# ------------------------------------------------------------------------------------------------- prepare
+def _mesh_data_ranks(torch_device_mesh, process_index: int, num_processes: int) -> tuple[int, int]:
     """(index, count) of this rank among the ranks that must read *different* data.
 
-    Ranks that differ only in tp / cp / sp coordinates consume the same batch; dp_replicate x
-    dp_shard ranks consume different ones (reference data_loader.py:1109-1145).
+    Ranks that differ only in their tp / cp / sp coordinate work on the same batch; the dp_replicate x dp_shard grid reads
+    different ones, replicate-major (reference data_loader.py:1109-1145).  A mesh with axes this does not know is left alone.
     """
-    names = tuple(torch_device_mesh.mesh_dim_names or ())
-    shared = 1
-    for axis in ("tp", "cp", "sp"):
-        if axis in names:
-            shared *= torch_device_mesh[axis].size()
-    rep = torch_device_mesh["dp_replicate"].size() if "dp_replicate" in names else 1
-    shard = torch_device_mesh["dp_shard"].size() if "dp_shard" in names else 1
-    rep_rank = torch_device_mesh.get_local_rank("dp_replicate") if "dp_replicate" in names else 0
-    shard_rank = torch_device_mesh.get_local_rank("dp_shard") if "dp_shard" in names else 0
-    if rep * shard * shared != torch_device_mesh.size():
-        return process_index, num_processes  # unknown axes: do not guess
-    return rep_rank * shard + shard_rank, rep * shard
+    axes = tuple(torch_device_mesh.mesh_dim_names or ())
+
+    def extent(axis):
+        return torch_device_mesh[axis].size() if axis in axes else 1
+
+    def coordinate(axis):
+        return torch_device_mesh.get_local_rank(axis) if axis in axes else 0
+
+    same_data = extent("tp") * extent("cp") * extent("sp")
+    readers = extent("dp_replicate") * extent("dp_shard")
+    if same_data * readers != torch_device_mesh.size():
+        return process_index, num_processes
+    return coordinate("dp_replicate") * extent("dp_shard") + coordinate("dp_shard"), readers
+
+
+def _check_splittable(dataloader, num_processes: int) -> None:
+    size = dataloader.batch_size
+    if size is None:
+        size = getattr(dataloader.batch_sampler, "batch_size", None)
+    if size is None:
+        raise ValueError(
+            "In order to use `split_batches==True` you must have a `batch_size` attribute either in the passed `dataloader` or "
+            "`dataloader.batch_sampler` objects, and it has to return a natural number. Your `dataloader.batch_size` is None and "
+            f"`dataloader.batch_sampler` (`{type(dataloader.batch_sampler)}`) does not have the `batch_size` attribute set."
+        )
+    if size > 1 and size % num_processes:
+        raise ValueError(
+            f"To use a `DataLoader` in `split_batches` mode, the batch size ({dataloader.batch_size}) needs to be a round multiple "
+            f"of the number of processes ({num_processes})."
+        )
+
+
+def _as_seedable(sampler: RandomSampler, data_seed) -> SeedableRandomSampler:
+    generator = getattr(sampler, "generator", None) or _cpu_generator()
+    return SeedableRandomSampler(data_source=sampler.data_source, replacement=sampler.replacement, num_samples=sampler._num_samples,
+                                 generator=generator, data_seed=data_seed)
+
+
+def _generator_to_synchronise(sampler):
+    """The generator whose state rank 0 will broadcast at every epoch start, created (randomly seeded) if the sampler has none yet."""
+    if not hasattr(sampler, "generator"):
+        return None
+    if sampler.generator is None:
+        sampler.generator = _cpu_generator()
+        sampler.generator.manual_seed(int(torch.empty((), dtype=torch.int64).random_().item()))
+    return sampler.generator
 
 
 def prepare_data_loader(dataloader: DataLoader, device=None, num_processes: Optional[int] = None, process_index: Optional[int] = None,
@@ -600,176 +673,146 @@ def prepare_data_loader(dataloader: DataLoader, device=None, num_processes: Opti
                         even_batches: bool = True, slice_fn_for_dispatch: Optional[Callable] = None, use_seedable_sampler: bool = False,
                         data_seed: Optional[int] = None, non_blocking: bool = False, use_stateful_dataloader: bool = False,
                         torch_device_mesh=None) -> DataLoader:
-    """Rebuild ``dataloader`` so each rank iterates its share and batches land on ``device``."""
+    """Rebuild ``dataloader`` for this rank: its share of the data (or rank-0 dispatch), batches placed on ``device``.
+
+    ``dispatch_batches=None`` means "dispatch exactly when the dataset is a stream and batches go to the device".  ``split_batches``
+    keeps the global batch size equal to the loader's batch size (each rank gets a slice) instead of multiplying it by the number of
+    ranks.  With a device mesh only the data-parallel axes count as readers.
+    """
+    streaming = isinstance(dataloader.dataset, IterableDataset)
     if dispatch_batches is None:
-        if not put_on_device:
-            dispatch_batches = False
-        else:
-            dispatch_batches = isinstance(dataloader.dataset, IterableDataset)
-    if dispatch_batches and not put_on_device:
+        dispatch_batches = put_on_device and streaming
+    elif dispatch_batches and not put_on_device:
         raise ValueError("Using `dispatch_batches=True` requires `put_on_device=True`.")
     state = PartialState()
-    if num_processes is None:
-        num_processes = state.num_processes
-    if process_index is None:
-        process_index = state.process_index
+    num_processes = state.num_processes if num_processes is None else num_processes
+    process_index = state.process_index if process_index is None else process_index
     if torch_device_mesh is not None:
         process_index, num_processes = _mesh_data_ranks(torch_device_mesh, process_index, num_processes)
-
     if split_batches:
-        if dataloader.batch_size is not None:
-            batch_size_for_check = dataloader.batch_size
-        elif hasattr(dataloader.batch_sampler, "batch_size"):
-            batch_size_for_check = dataloader.batch_sampler.batch_size
-        else:
-            raise ValueError(
-                "In order to use `split_batches==True` you must have a `batch_size` attribute either in the passed "
-                "`dataloader` or `dataloader.batch_sampler` objects, and it has to return a natural number. "
-                f"Your `dataloader.batch_size` is None and `dataloader.batch_sampler` (`{type(dataloader.batch_sampler)}`) does not have the `batch_size` attribute set."
-            )
-        if batch_size_for_check > 1 and batch_size_for_check % num_processes != 0:
-            raise ValueError(
-                f"To use a `DataLoader` in `split_batches` mode, the batch size ({dataloader.batch_size}) "
-                f"needs to be a round multiple of the number of processes ({num_processes})."
-            )
+        _check_splittable(dataloader, num_processes)
 
-    new_dataset = dataloader.dataset
-    new_batch_sampler = dataloader.batch_sampler if not isinstance(new_dataset, IterableDataset) else None
-    sampler_is_batch_sampler = isinstance(dataloader.sampler, BatchSampler)
-    synchronized_generator = None
     sampler = get_sampler(dataloader)
-    if isinstance(sampler, RandomSampler) and use_seedable_sampler:
-        sampler = SeedableRandomSampler(
-            data_source=sampler.data_source, replacement=sampler.replacement, num_samples=sampler._num_samples,
-            generator=getattr(sampler, "generator", torch.Generator(device=torch.get_default_device() if hasattr(torch, "get_default_device") else "cpu")),
-            data_seed=data_seed,
-        )
-    if isinstance(dataloader.sampler, RandomSampler) and state.distributed_type == DistributedType.XLA:
-        pass  # not reachable on this build
+    if use_seedable_sampler and isinstance(sampler, RandomSampler):
+        sampler = _as_seedable(sampler, data_seed)
 
-    if (num_processes != 1 or state.distributed_type == DistributedType.MEGATRON_LM) and not dispatch_batches:
-        if isinstance(new_dataset, IterableDataset):
-            if getattr(dataloader.dataset, "generator", None) is not None:
-                synchronized_generator = dataloader.dataset.generator
-            new_dataset = IterableDatasetShard(new_dataset, batch_size=dataloader.batch_size, drop_last=dataloader.drop_last,
-                                               num_processes=num_processes, process_index=process_index, split_batches=split_batches)
-        else:
-            if not use_seedable_sampler and hasattr(sampler, "generator"):
-                if sampler.generator is None:
-                    sampler.generator = torch.Generator(device=torch.get_default_device() if hasattr(torch, "get_default_device") else "cpu")
-                    seed = int(torch.empty((), dtype=torch.int64).random_().item())
-                    sampler.generator.manual_seed(seed)
-                synchronized_generator = sampler.generator
-            batch_sampler = dataloader.sampler if sampler_is_batch_sampler else dataloader.batch_sampler
-            new_batch_sampler = BatchSamplerShard(batch_sampler, num_processes=num_processes, process_index=process_index,
-                                                  split_batches=split_batches, even_batches=even_batches)
+    dataset = dataloader.dataset
+    batcher = None if streaming else dataloader.batch_sampler
+    batcher_is_sampler = isinstance(dataloader.sampler, BatchSampler)
+    synchronized_generator = None
+    shard_here = not dispatch_batches and (num_processes != 1 or state.distributed_type == DistributedType.MEGATRON_LM)
+    if shard_here and streaming:
+        synchronized_generator = getattr(dataset, "generator", None)
+        dataset = IterableDatasetShard(dataset, batch_size=dataloader.batch_size, drop_last=dataloader.drop_last,
+                                       num_processes=num_processes, process_index=process_index, split_batches=split_batches)
+    elif shard_here:
+        if not use_seedable_sampler:
+            synchronized_generator = _generator_to_synchronise(sampler)
+        batcher = BatchSamplerShard(_index_batcher(dataloader), num_processes=num_processes, process_index=process_index,
+                                    split_batches=split_batches, even_batches=even_batches)
 
-    ignore_kwargs = ["batch_size", "shuffle", "sampler", "batch_sampler", "drop_last"]
-    if rng_types is not None and synchronized_generator is None and "generator" in rng_types:
-        rng_types = [r for r in rng_types if r != "generator"]
-    kwargs = {k: getattr(dataloader, k, _PYTORCH_DATALOADER_KWARGS[k]) for k in _PYTORCH_DATALOADER_KWARGS if k not in ignore_kwargs}
-    if new_batch_sampler is None:
+    if rng_types is not None and synchronized_generator is None:
+        rng_types = [kind for kind in rng_types if kind != "generator"]
+    kwargs = _inherited_kwargs(dataloader)
+    if batcher is None:  # streams: the loader itself batches
         kwargs["drop_last"] = dataloader.drop_last
         kwargs["batch_size"] = dataloader.batch_size // num_processes if split_batches and not dispatch_batches else dataloader.batch_size
+    common = dict(_drop_last=dataloader.drop_last, _non_blocking=non_blocking, use_stateful_dataloader=use_stateful_dataloader)
 
     if dispatch_batches:
-        kwargs.pop("generator")
-        dataloader = DataLoaderDispatcher(new_dataset, split_batches=split_batches, batch_sampler=new_batch_sampler,
-                                          _drop_last=dataloader.drop_last, _non_blocking=non_blocking, slice_fn=slice_fn_for_dispatch,
-                                          use_stateful_dataloader=use_stateful_dataloader, torch_device_mesh=torch_device_mesh, **kwargs)
-    elif sampler_is_batch_sampler:
-        dataloader = DataLoaderShard(new_dataset, device=device if put_on_device else None, sampler=new_batch_sampler,
-                                     batch_size=dataloader.batch_size, rng_types=rng_types, _drop_last=dataloader.drop_last,
-                                     _non_blocking=non_blocking, synchronized_generator=synchronized_generator,
-                                     use_stateful_dataloader=use_stateful_dataloader, **kwargs)
+        kwargs.pop("generator", None)
+        prepared = DataLoaderDispatcher(dataset, split_batches=split_batches, batch_sampler=batcher, slice_fn=slice_fn_for_dispatch,
+                                        torch_device_mesh=torch_device_mesh, **common, **kwargs)
     else:
-        dataloader = DataLoaderShard(new_dataset, device=device if put_on_device else None, batch_sampler=new_batch_sampler,
-                                     rng_types=rng_types, synchronized_generator=synchronized_generator, _drop_last=dataloader.drop_last,
-                                     _non_blocking=non_blocking, use_stateful_dataloader=use_stateful_dataloader, **kwargs)
-    if isinstance(sampler, SeedableRandomSampler) and use_seedable_sampler:
-        dataloader.set_sampler(sampler)
-    return dataloader
+        if batcher_is_sampler:  # DataLoader(sampler=<BatchSampler>, batch_size=None): keep that calling convention
+            placement = {"sampler": batcher, "batch_size": dataloader.batch_size}
+        else:
+            placement = {"batch_sampler": batcher}
+        prepared = DataLoaderShard(dataset, device=device if put_on_device else None, rng_types=rng_types,
+                                   synchronized_generator=synchronized_generator, **placement, **common, **kwargs)
+    if isinstance(sampler, SeedableRandomSampler):
+        prepared.set_sampler(sampler)
+    return prepared
 
 
+# ------------------------------------------------------------------------------------------------- resuming inside an epoch
 class SkipBatchSampler(BatchSampler):
-    """Batch sampler that drops the first ``skip_batches`` batches of another one."""
+    """``batch_sampler`` without its first ``skip_batches`` batches."""
 
     def __init__(self, batch_sampler, skip_batches: int = 0):
-        self.batch_sampler = batch_sampler
-        self.skip_batches = skip_batches
-
-    def __iter__(self):
-        for index, samples in enumerate(self.batch_sampler):
-            if index >= self.skip_batches:
-                yield samples
+        self.batch_sampler, self.skip_batches = batch_sampler, skip_batches
 
     @property
-    def total_length(self):
+    def total_length(self) -> int:
         return len(self.batch_sampler)
 
-    def __len__(self):
+    def __len__(self) -> int:
         return len(self.batch_sampler) - self.skip_batches
+
+    def __iter__(self):
+        produced = iter(self.batch_sampler)
+        for _ in range(self.skip_batches):
+            if next(produced, None) is None:
+                return
+        yield from produced
 
 
 class SkipDataLoader(DataLoaderAdapter, DataLoaderStateMixin):
-    """Dataloader that drops its first ``skip_batches`` batches (for iterable datasets)."""
+    """A loader that reads and discards its first ``skip_batches`` batches — the only way to skip in a stream."""
 
     def __init__(self, dataset, skip_batches: int = 0, use_stateful_dataloader: bool = False, **kwargs):
         super().__init__(dataset, use_stateful_dataloader=use_stateful_dataloader, **kwargs)
         self.skip_batches = skip_batches
         self.gradient_state = GradientState()
+        self._drop_last = kwargs.get("drop_last", False)
+
+    def __len__(self) -> int:
+        return len(self.base_dataloader) - self.skip_batches
 
     def __iter__(self):
         self.begin()
-        for index, batch in enumerate(self.base_dataloader.__iter__()):
-            if index >= self.skip_batches:
-                self._update_state_dict()
-                yield batch
+        for position, batch in enumerate(iter(self.base_dataloader)):
+            if position < self.skip_batches:
+                continue
+            self._snapshot()
+            yield batch
         self.end()
 
-    def __len__(self):
-        return len(self.base_dataloader) - self.skip_batches
-
     def __reduce__(self):
-        args = super().__reduce__()
-        return (SkipDataLoader, *args[1:])
+        return (SkipDataLoader, *super().__reduce__()[1:])
 
 
 def skip_first_batches(dataloader, num_batches: int = 0):
-    """A dataloader equal to ``dataloader`` minus its first ``num_batches`` batches (resume mid-epoch)."""
+    """A loader that continues where ``dataloader`` would be after ``num_batches`` batches, of the same kind (sharded, dispatching
+    or plain).  Map-style data skips at the index level (nothing is read); streams have to be read through."""
     dataset = dataloader.dataset
-    sampler_is_batch_sampler = False
-    if isinstance(dataset, IterableDataset):
-        new_batch_sampler = None
+    streaming = isinstance(dataset, IterableDataset)
+    kwargs = _inherited_kwargs(dataloader)
+    if streaming:
+        kwargs.update(drop_last=dataloader.drop_last, batch_size=dataloader.batch_size)
+        placement = {}
     else:
-        sampler_is_batch_sampler = isinstance(dataloader.sampler, BatchSampler)
-        batch_sampler = dataloader.sampler if sampler_is_batch_sampler else dataloader.batch_sampler
-        new_batch_sampler = SkipBatchSampler(batch_sampler, skip_batches=num_batches)
-    ignore_kwargs = ["batch_size", "shuffle", "sampler", "batch_sampler", "drop_last"]
-    kwargs = {k: getattr(dataloader, k, _PYTORCH_DATALOADER_KWARGS[k]) for k in _PYTORCH_DATALOADER_KWARGS if k not in ignore_kwargs}
-    if new_batch_sampler is None:
-        kwargs["drop_last"] = dataloader.drop_last
-        kwargs["batch_size"] = dataloader.batch_size
-    # the adapters fake ``__class__``; look at the real type
-    is_dispatcher = issubclass(type(dataloader), DataLoaderDispatcher)
-    is_shard = issubclass(type(dataloader), DataLoaderShard)
-    if is_dispatcher:
-        if new_batch_sampler is None:
-            kwargs["skip_batches"] = num_batches
-        kwargs.pop("generator", None)
-        return DataLoaderDispatcher(dataset, split_batches=dataloader.split_batches, batch_sampler=new_batch_sampler,
-                                    _drop_last=dataloader._drop_last, use_stateful_dataloader=dataloader.use_stateful_dataloader, **kwargs)
-    if is_shard:
-        if new_batch_sampler is None:
-            kwargs["skip_batches"] = num_batches
-        elif sampler_is_batch_sampler:
-            kwargs["sampler"] = new_batch_sampler
-            kwargs["batch_size"] = dataloader.batch_size
+        skipping = SkipBatchSampler(_index_batcher(dataloader), skip_batches=num_batches)
+        if isinstance(dataloader.sampler, BatchSampler):
+            placement = {"sampler": skipping, "batch_size": dataloader.batch_size}
         else:
-            kwargs["batch_sampler"] = new_batch_sampler
+            placement = {"batch_sampler": skipping}
+    kind = type(dataloader)  # the adapters report a borrowed __class__; type() sees the real one
+    if issubclass(kind, DataLoaderDispatcher):
+        kwargs.pop("generator", None)
+        if streaming:
+            kwargs["skip_batches"] = num_batches
+        else:
+            placement = {"batch_sampler": skipping}
+        return DataLoaderDispatcher(dataset, split_batches=dataloader.split_batches, _drop_last=dataloader._drop_last,
+                                    use_stateful_dataloader=dataloader.use_stateful_dataloader, **placement, **kwargs)
+    if issubclass(kind, DataLoaderShard):
+        if streaming:
+            kwargs["skip_batches"] = num_batches
         return DataLoaderShard(dataset, device=dataloader.device, rng_types=dataloader.rng_types,
                                synchronized_generator=dataloader.synchronized_generator, _drop_last=dataloader._drop_last,
-                               use_stateful_dataloader=dataloader.use_stateful_dataloader, **kwargs)
-    if new_batch_sampler is None:
+                               _non_blocking=dataloader._non_blocking, use_stateful_dataloader=dataloader.use_stateful_dataloader,
+                               **placement, **kwargs)
+    if streaming:
         return SkipDataLoader(dataset, skip_batches=num_batches, **kwargs)
-    return DataLoader(dataset, batch_sampler=new_batch_sampler, **kwargs)
+    return DataLoader(dataset, batch_sampler=skipping, **kwargs)

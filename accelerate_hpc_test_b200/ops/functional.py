@@ -35,9 +35,13 @@ def _rowmajor2d(t: torch.Tensor) -> torch.Tensor:
     """Return a 2-D view with unit inner stride and a 16-byte aligned row stride (copy only if needed)."""
     assert t.dim() == 2
     if t.stride(1) != 1 or t.stride(0) % 8 != 0 or t.data_ptr() % 16 != 0:
-        t = t.contiguous()
-        if t.stride(0) % 8 != 0:
-            raise _lib.B200KernelError(f"gemm operand row stride {t.stride(0)} must be a multiple of 8 elements")
+        rows, cols = t.shape
+        if cols % 8 == 0:
+            return t.contiguous()
+        # TMA wants 16-byte row pitches: copy into rows padded to 8 elements and hand out the [rows, cols] window
+        padded = torch.empty((rows, (cols + 7) // 8 * 8), dtype=t.dtype, device=t.device)
+        padded[:, :cols].copy_(t)
+        return padded[:, :cols]
     return t
 
 

@@ -233,3 +233,196 @@ def test_prepare_data_loader_shards_for_virtual_ranks():
         outs.append([b.tolist() for b in p])
     assert outs[0] == [[0, 1], [8, 9]] and outs[3] == [[6, 7], [14, 15]]
     assert p.total_batch_size == 8
+
+
+# ------------------------------------------------------------------------------------------------- more of the layer
+class _Stream(IterableDataset):
+    def __init__(self, n):
+        self.n = n
+
+    def __iter__(self):
+        yield from range(self.n)
+
+    def __len__(self):
+        return self.n
+
+
+def test_refill_cycles_over_what_it_remembered():
+    from accelerate_hpc_test_b200.data_loader import _Refill
+
+    r = _Refill(4)
+    r.remember([0, 1, 2])
+    r.remember([3, 4, 5])  # only one more fits
+    assert r.pool == [0, 1, 2, 3]
+    assert r.take(6) == [0, 1, 2, 3, 0, 1] and r.take(1) == [2]
+
+
+def test_flag_last_marks_only_the_last_item_and_calls_back_before_each_read_ahead():
+    from accelerate_hpc_test_b200.data_loader import _flag_last
+
+    reads = []
+    out = list(_flag_last(iter("abc"), before_fetch=lambda: reads.append(1), on_fetch=str.upper))
+    assert out == [("A", False), ("B", False), ("C", True)] and len(reads) == 3
+    assert list(_flag_last(iter(()))) == []
+
+
+def test_get_and_set_sampler_reach_through_the_shard_wrapper():
+    PartialState()
+    base = DataLoader(list(range(12)), batch_size=2, shuffle=True)
+    prepared = prepare_data_loader(base, num_processes=2, process_index=0)
+    assert prepared.get_sampler() is base.sampler  # found under BatchSamplerShard -> BatchSampler
+    new = SeedableRandomSampler(list(range(12)), data_seed=5)
+    prepared.set_sampler(new)
+    assert prepared.get_sampler() is new and prepared.batch_sampler.batch_sampler.sampler is new
+
+
+def test_seedable_sampler_through_prepare_gives_disjoint_shards_that_change_with_the_epoch():
+    PartialState()
+    base = DataLoader(list(range(16)), batch_size=2, shuffle=True)
+    loaders = [prepare_data_loader(base, num_processes=2, process_index=r, use_seedable_sampler=True, data_seed=11) for r in range(2)]
+    epoch0 = [[b.tolist() for b in dl] for dl in loaders]
+    flat = sorted(i for shard in epoch0 for b in shard for i in b)
+    assert flat == list(range(16))  # same permutation on both ranks, dealt without overlap
+    epoch1 = [[b.tolist() for b in dl] for dl in loaders]
+    assert sorted(i for shard in epoch1 for b in shard for i in b) == list(range(16)) and epoch1 != epoch0
+    for dl in loaders:
+        dl.set_epoch(0)
+    assert [[b.tolist() for b in dl] for dl in loaders] == epoch0  # the order is a function of seed + epoch only
+
+
+def test_set_epoch_reaches_the_dataset_when_nothing_else_listens():
+    class Data(_Stream):
+        epoch = None
+
+        def set_epoch(self, e):
+            self.epoch = e
+
+    PartialState()
+    data = Data(8)
+    dl = prepare_data_loader(DataLoader(data, batch_size=2), num_processes=2, process_index=1)
+    dl.set_epoch(3)
+    assert data.epoch == 3 and dl.iteration == 3
+    assert [b.tolist() for b in dl] == [[2, 3], [6, 7]]
+
+
+def test_split_batches_checks():
+    PartialState()
+    with pytest.raises(ValueError, match="round multiple"):
+        prepare_data_loader(DataLoader(list(range(12)), batch_size=3), num_processes=2, process_index=0, split_batches=True)
+    with pytest.raises(ValueError, match="requires `put_on_device=True`"):
+        prepare_data_loader(DataLoader(list(range(12)), batch_size=2), dispatch_batches=True)
+    dl = prepare_data_loader(DataLoader(list(range(12)), batch_size=4), num_processes=2, process_index=1, split_batches=True)
+    assert [b.tolist() for b in dl] == [[2, 3], [6, 7], [10, 11]] and dl.total_batch_size == 4 and len(dl) == 3
+
+
+def test_batch_sampler_passed_as_sampler_keeps_that_convention():
+    PartialState()
+    base = DataLoader(torch.arange(12), sampler=BatchSampler(range(12), 3, False), batch_size=None)
+    dl = prepare_data_loader(base, num_processes=2, process_index=1)
+    assert isinstance(dl.sampler, BatchSamplerShard) and dl.batch_size is None
+    assert [b.tolist() for b in dl] == [[3, 4, 5], [9, 10, 11]]
+    assert [b.tolist() for b in skip_first_batches(dl, 1)] == [[9, 10, 11]]
+
+
+def test_skip_first_batches_on_a_streaming_shard_reads_through():
+    PartialState()
+    dl = prepare_data_loader(DataLoader(_Stream(16), batch_size=2), num_processes=2, process_index=0)
+    assert [b.tolist() for b in dl] == [[0, 1], [4, 5], [8, 9], [12, 13]]
+    resumed = skip_first_batches(dl, 2)
+    assert type(resumed) is DataLoaderShard and resumed.skip_batches == 2
+    assert [b.tolist() for b in resumed] == [[8, 9], [12, 13]]
+    plain = skip_first_batches(DataLoader(_Stream(8), batch_size=2), 3)
+    assert type(plain) is SkipDataLoader and [b.tolist() for b in plain] == [[6, 7]] and len(plain) == 1
+
+
+def test_inherited_kwargs_follow_the_installed_dataloader_signature():
+    from accelerate_hpc_test_b200.data_loader import _PYTORCH_DATALOADER_KWARGS, _inherited_kwargs
+
+    assert {"num_workers", "collate_fn", "pin_memory", "timeout", "generator", "persistent_workers"} <= set(_PYTORCH_DATALOADER_KWARGS)
+    collate = lambda rows: torch.tensor(rows) * 10  # noqa: E731
+    kw = _inherited_kwargs(DataLoader(list(range(4)), batch_size=2, collate_fn=collate))
+    assert kw["collate_fn"] is collate and not {"batch_size", "sampler", "batch_sampler", "shuffle", "drop_last"} & set(kw)
+    PartialState()
+    dl = prepare_data_loader(DataLoader(list(range(8)), batch_size=2, collate_fn=collate), num_processes=2, process_index=1)
+    assert [b.tolist() for b in dl] == [[20, 30], [60, 70]]
+
+
+def test_mesh_data_ranks():
+    from accelerate_hpc_test_b200.data_loader import _mesh_data_ranks
+
+    class Axis:
+        def __init__(self, n):
+            self.n = n
+
+        def size(self):
+            return self.n
+
+    class Mesh:
+        def __init__(self, extents, coords):
+            self.mesh_dim_names, self.extents, self.coords = tuple(extents), extents, coords
+
+        def __getitem__(self, name):
+            return Axis(self.extents[name])
+
+        def get_local_rank(self, name):
+            return self.coords[name]
+
+        def size(self):
+            return math.prod(self.extents.values())
+
+    import math
+
+    # dp_replicate 2 x dp_shard 2 x tp 2: the two tp ranks of a group read the same data; readers are numbered replicate-major
+    mesh = Mesh({"dp_replicate": 2, "dp_shard": 2, "tp": 2}, {"dp_replicate": 1, "dp_shard": 0, "tp": 1})
+    assert _mesh_data_ranks(mesh, 5, 8) == (2, 4)
+    assert _mesh_data_ranks(Mesh({"cp": 4}, {"cp": 3}), 3, 4) == (0, 1)
+    assert _mesh_data_ranks(Mesh({"pp": 2, "dp_shard": 2}, {"pp": 1, "dp_shard": 1}), 3, 4) == (3, 4)  # unknown axis: untouched
+
+
+def _dispatch_ragged():
+    from accelerate_hpc_test_b200.utils.operations import gather
+
+    state = PartialState()
+    # 22 samples, batches of 4 -> loader batches 4,4,4,4,4,2; two ranks => global batches of 8, 8, and a last one of 6 = 3 + 3
+    dl = prepare_data_loader(DataLoader(_Stream(22), batch_size=4), state.device, put_on_device=True, dispatch_batches=True)
+    got, flags = [], []
+    for batch in dl:
+        flags.append(dl.end_of_dataloader)
+        got.append(gather(batch).tolist())
+    assert got == [list(range(8)), list(range(8, 16)), list(range(16, 22))], got
+    assert flags == [False, False, True] and dl.remainder == 6
+    # 21 samples: the last global batch has 5 rows -> completed with the first row of the epoch, 3 rows per rank
+    dl = prepare_data_loader(DataLoader(_Stream(21), batch_size=4), state.device, put_on_device=True, dispatch_batches=True)
+    got = [gather(b).tolist() for b in dl]
+    assert got[-1] == [16, 17, 18, 19, 20, 0] and dl.remainder == 5, got
+    # drop_last on the loader drops the incomplete round as a whole
+    dl = prepare_data_loader(DataLoader(_Stream(22), batch_size=4, drop_last=True), state.device, put_on_device=True, dispatch_batches=True)
+    assert [gather(b).tolist() for b in dl] == [list(range(8)), list(range(8, 16))] and len(dl) == 2
+    # an empty stream ends the pass on every rank without a batch
+    dl = prepare_data_loader(DataLoader(_Stream(0), batch_size=4), state.device, put_on_device=True, dispatch_batches=True)
+    assert list(dl) == []
+    # resuming: skip the first global batch
+    dl = prepare_data_loader(DataLoader(_Stream(22), batch_size=4), state.device, put_on_device=True, dispatch_batches=True)
+    assert [gather(b).tolist() for b in skip_first_batches(dl, 1)] == [list(range(8, 16)), list(range(16, 22))]
+
+
+def test_dispatcher_ragged_tail_two_processes():
+    from accelerate_hpc_test_b200.launchers import debug_launcher
+
+    debug_launcher(_dispatch_ragged, num_processes=2)
+
+
+@pytest.mark.gpu
+def test_overlapped_host_to_device_copies_deliver_the_right_batches():
+    PartialState()
+    data = torch.arange(64 * 1024, dtype=torch.int64).view(64, 1024)
+    dl = prepare_data_loader(DataLoader(data, batch_size=8), device=torch.device("cuda", 0), put_on_device=True, non_blocking=True)
+    seen = []
+    for batch in dl:
+        assert batch.is_cuda
+        # keep the device busy so that the next copy really runs beside compute
+        x = torch.randn(2048, 2048, device="cuda")
+        for _ in range(4):
+            x = x @ x
+        seen.append(batch.sum().item())
+    assert seen == [data[i : i + 8].sum().item() for i in range(0, 64, 8)]
