@@ -1,502 +1,520 @@
-"""Model-surgery utilities for big-model inference: tensor placement, size accounting, device maps,
-checkpoint streaming.
+"""Model surgery for models that do not fit one device: where each tensor lives, how big things are, which device gets what,
+and how a checkpoint is streamed in without ever holding the whole model twice.
 
-Behaviour parity with reference src/accelerate/utils/modeling.py: ``set_module_tensor_to_device``
-:217-424, ``named_module_tensors`` :427-474, ``find_tied_parameters`` :554-606, ``retie_parameters``
-:609-648, ``compute_module_sizes`` :651-702, ``get_max_layer_size`` :705-741, ``get_max_memory``
-:744-852, ``clean_device_map`` :855-877, ``get_balanced_memory`` :918-1049,
-``infer_auto_device_map`` :1278-1583, ``check_device_map`` :1586-1617, ``load_state_dict``
-:1620-1712, ``load_checkpoint_in_model`` :1788-2046, ``get_mixed_precision_context_manager``
-:2049-2089, ``get_grad_scaler`` :2092-2131.  CUDA + CPU + disk only; the greedy packer is written
-from the behaviour (reserve room for the largest un-splittable layer, keep tied weights together,
-optionally look ahead for a module that fits).
+The pieces, bottom up:
+
+* sizes — ``convert_file_size_to_int``, ``dtype_byte_size``, ``compute_module_sizes`` (bytes under every dotted module name),
+  ``get_max_layer_size`` (the largest block that must stay in one piece);
+* placement — ``set_module_tensor_to_device`` replaces one parameter / buffer by a copy elsewhere (or by a checkpoint value) keeping
+  its class, ``requires_grad`` and ties; ``align_module_device`` does it temporarily for a whole module;
+* ties — ``find_tied_parameters`` / ``retie_parameters`` / ``check_tied_parameters_on_same_device``;
+* budgets and maps — ``get_max_memory``, ``get_balanced_memory``, ``infer_auto_device_map`` (greedy packer), ``clean_device_map``,
+  ``check_device_map``;
+* checkpoints — ``load_state_dict`` (safetensors land directly on their target devices), ``shard_checkpoint``,
+  ``load_checkpoint_in_model`` (gpu / cpu / disk per the device map), ``get_state_dict_offloaded_model``.
+
+Behavioural parity: reference ``src/accelerate/utils/modeling.py`` (``set_module_tensor_to_device`` :217-424, ``named_module_tensors``
+:427-474, ties :477-648, sizes :651-741, ``get_max_memory`` :744-852, ``clean_device_map`` :855-877, ``get_balanced_memory`` :918-1049,
+``infer_auto_device_map`` :1278-1583, ``check_device_map`` :1586-1617, ``load_state_dict`` :1620-1712, ``load_checkpoint_in_model``
+:1788-2046, autocast / scaler helpers :2049-2131).  Devices here are CUDA GPUs (integers), ``"cpu"`` and ``"disk"``.
 """
 
 from __future__ import annotations
 
 import contextlib
 import gc
+import itertools
 import json
 import logging
 import os
 import re
+import shutil
+import tempfile
 import warnings
 from collections import OrderedDict, defaultdict
-from typing import Optional, Union
+from typing import Iterator, Optional, Union
 
 import torch
 import torch.nn as nn
 
 from .constants import SAFE_WEIGHTS_NAME, WEIGHTS_NAME
 from .dataclasses import AutocastKwargs, CustomDtype, DistributedType
-from .memory import clear_device_cache
+from .memory import clear_device_cache  # noqa: F401 - re-exported
 from .offload import load_offloaded_weight, offload_weight, save_offload_index
 
 logger = logging.getLogger(__name__)
 
 WEIGHTS_INDEX_NAME = "pytorch_model.bin.index.json"
+_META = torch.device("meta")
+_QUANTIZED_PARAM_CLASSES = ("Int8Params", "FP4Params", "Params4bit")
+_TENSOR_SUBCLASS_PARAMS = ("QTensor", "QBitsTensor", "AffineQuantizedTensor")
 
 
-# ------------------------------------------------------------------------------------ sizes
+# ------------------------------------------------------------------------------------------------- sizes
+_SIZE_PATTERN = re.compile(r"^\s*(\d+(?:\.\d+)?)\s*([KMG])(I?)([Bb])\s*$", re.IGNORECASE)
+
+
 def convert_file_size_to_int(size: Union[int, str]) -> int:
-    """``"5GB"`` -> 5_000_000_000, ``"2MiB"`` -> 2 * 2**20 (bit units end in lowercase ``b``)."""
+    """``"5GB"`` → 5·10⁹, ``"2MiB"`` → 2·2²⁰; a lower-case ``b`` means bits (``"8Gb"`` is one gigabyte).  Integers pass through."""
     if isinstance(size, int):
         return size
-    units = {"GIB": 2**30, "MIB": 2**20, "KIB": 2**10, "GB": 10**9, "MB": 10**6, "KB": 10**3}
-    up = size.upper()
-    for suffix, mult in units.items():
-        if up.endswith(suffix):
-            try:
-                value = int(float(size[: -len(suffix)]) * mult) if "." in size[: -len(suffix)] else int(size[: -len(suffix)]) * mult
-            except ValueError:
-                break
-            return value // 8 if size.endswith("b") else value
-    raise ValueError("`size` is not in a valid format. Use an integer followed by the unit, e.g., '5GB'.")
+    match = _SIZE_PATTERN.match(size)
+    if match is None:
+        raise ValueError("`size` is not in a valid format. Use an integer followed by the unit, e.g., '5GB'.")
+    amount, prefix, binary, unit = match.groups()
+    step = 1024 if binary else 1000
+    scale = step ** ("KMG".index(prefix.upper()) + 1)
+    total = int(float(amount) * scale) if "." in amount else int(amount) * scale
+    return total // 8 if unit == "b" else total
+
+
+_CUSTOM_DTYPE_BYTES = {CustomDtype.INT2: 0.25, CustomDtype.INT4: 0.5, CustomDtype.FP8: 1}
 
 
 def dtype_byte_size(dtype) -> float:
-    """Bytes per element, including the sub-byte ``CustomDtype`` s."""
+    """Bytes per element; booleans count as one bit and the sub-byte ``CustomDtype`` s as what they are."""
     if dtype == torch.bool:
         return 1 / 8
-    if dtype == CustomDtype.INT2:
-        return 1 / 4
-    if dtype == CustomDtype.INT4:
-        return 1 / 2
-    if dtype == CustomDtype.FP8:
-        return 1
-    bit_search = re.search(r"[^\d](\d+)(_.*)?$", str(dtype))
-    if bit_search is None:
+    if dtype in _CUSTOM_DTYPE_BYTES:
+        return _CUSTOM_DTYPE_BYTES[dtype]
+    if isinstance(dtype, torch.dtype):
+        info = torch.finfo(dtype) if (dtype.is_floating_point or dtype.is_complex) else torch.iinfo(dtype)
+        return info.bits // 8 * (2 if dtype.is_complex else 1)
+    digits = re.search(r"(\d+)(?:_\w+)?$", str(dtype))
+    if digits is None:
         raise ValueError(f"`dtype` is not a valid dtype: {dtype}.")
-    return int(bit_search.groups()[0]) // 8
+    return int(digits.group(1)) // 8
+
+
+def _is_integer_like(dtype: torch.dtype) -> bool:
+    """Integer, unsigned and boolean tensors are never cast when a floating dtype is requested."""
+    return not (dtype.is_floating_point or dtype.is_complex)
+
+
+def _as_torch_dtype(dtype):
+    return getattr(torch, dtype.replace("torch.", "")) if isinstance(dtype, str) else dtype
 
 
 def id_tensor_storage(tensor: torch.Tensor):
-    """(device, storage pointer, storage size): equal for tensors that share memory."""
+    """``(device, address, bytes)`` of the storage behind ``tensor``: equal for views of one allocation, ``(dev, 0, 0)`` when the
+    tensor has no accessible storage (meta, some subclasses)."""
     try:
-        storage_ptr = tensor.untyped_storage().data_ptr()
-        storage_size = tensor.untyped_storage().nbytes()
+        storage = tensor.untyped_storage()
+        return tensor.device, storage.data_ptr(), storage.nbytes()
     except Exception:
-        storage_ptr, storage_size = 0, 0
-    return tensor.device, storage_ptr, storage_size
+        return tensor.device, 0, 0
 
 
 def is_peft_model(model) -> bool:
     try:
         from peft import PeftModel
-
-        return isinstance(model, PeftModel)
     except ImportError:
         return False
+    return isinstance(model, PeftModel)
 
 
 def check_device_same(first_device, second_device) -> bool:
-    """``cuda`` == ``cuda:0`` (index defaults to 0); otherwise exact type+index match."""
-    if first_device.type != second_device.type:
-        return False
-    if first_device.type != "cpu" and first_device.index is None:
-        first_device = torch.device(first_device.type, index=0)
-    if second_device.type != "cpu" and second_device.index is None:
-        second_device = torch.device(second_device.type, index=0)
-    return first_device == second_device
+    """Same physical device?  An accelerator device without an index means index 0 (``cuda`` is ``cuda:0``)."""
 
+    def canonical(device):
+        if device.type != "cpu" and device.index is None:
+            return torch.device(device.type, 0)
+        return device
 
-# ------------------------------------------------------------------------------------ tensor placement
-def set_module_tensor_to_device(module: nn.Module, tensor_name: str, device, value: Optional[torch.Tensor] = None, dtype=None,
-                                fp16_statistics=None, tied_params_map=None, non_blocking: bool = False, clear_cache: bool = True):
-    """Re-home one parameter or buffer of ``module`` (``tensor_name`` may be dotted).
-
-    Moving *off* the meta device needs ``value``.  Parameter-ness / ``requires_grad`` are kept, tied
-    parameters are re-used through ``tied_params_map`` ``{data_ptr: {device: tensor}}`` so a shared
-    weight is materialised once per device.
-    """
-    if "." in tensor_name:
-        splits = tensor_name.split(".")
-        for split in splits[:-1]:
-            new_module = getattr(module, split)
-            if new_module is None:
-                raise ValueError(f"{module} has no attribute {split}.")
-            module = new_module
-        tensor_name = splits[-1]
-    if tensor_name not in module._parameters and tensor_name not in module._buffers:
-        raise ValueError(f"{module} does not have a parameter or a buffer named {tensor_name}.")
-    is_buffer = tensor_name in module._buffers
-    old_value = getattr(module, tensor_name)
-
-    # a tied parameter already materialised on the target device: alias it
-    if value is not None and tied_params_map is not None and value.data_ptr() in tied_params_map and device in tied_params_map[value.data_ptr()]:
-        module._parameters[tensor_name] = tied_params_map[value.data_ptr()][device]
-        return
-    elif tied_params_map is not None and old_value.data_ptr() in tied_params_map and device in tied_params_map[old_value.data_ptr()]:
-        module._parameters[tensor_name] = tied_params_map[old_value.data_ptr()][device]
-        return
-
-    if old_value.device == torch.device("meta") and device not in ["meta", torch.device("meta")] and value is None:
-        raise ValueError(f"{tensor_name} is on the meta device, we need a `value` to put in on {device}.")
-    param = module._parameters[tensor_name] if tensor_name in module._parameters else None
-    param_cls = type(param)
-
-    if value is not None:
-        if old_value.shape != value.shape and param_cls.__name__ != "Params4bit":
-            raise ValueError(f'Trying to set a tensor of shape {value.shape} in "{tensor_name}" (which has shape {old_value.shape}), this looks incorrect.')
-        if dtype is None:
-            value = value.to(old_value.dtype, non_blocking=non_blocking)
-        elif not str(value.dtype).startswith(("torch.uint", "torch.int", "torch.bool")):
-            value = value.to(dtype, non_blocking=non_blocking)
-
-    device_quantization = None
-    with torch.no_grad():
-        if isinstance(device, int):
-            device = torch.device("cuda", device)
-        if "cuda" in str(device) and clear_cache and False:
-            clear_device_cache()
-        if value is None:
-            new_value = old_value.to(device, non_blocking=non_blocking)
-            if dtype is not None and device in ["meta", torch.device("meta")]:
-                if not str(old_value.dtype).startswith(("torch.uint", "torch.int", "torch.bool")):
-                    new_value = new_value.to(dtype, non_blocking=non_blocking)
-                if not is_buffer:
-                    module._parameters[tensor_name] = param_cls(new_value, requires_grad=old_value.requires_grad)
-        elif isinstance(value, torch.Tensor):
-            new_value = value.to(device, non_blocking=non_blocking)
-        else:
-            new_value = torch.tensor(value, device=device)
-        if is_buffer:
-            module._buffers[tensor_name] = new_value
-        elif value is not None or not check_device_same(torch.device(device), module._parameters[tensor_name].device):
-            param_cls = type(module._parameters[tensor_name])
-            kwargs = module._parameters[tensor_name].__dict__
-            if param_cls.__name__ in ("Int8Params", "FP4Params", "Params4bit"):
-                if param_cls.__name__ == "Int8Params" and new_value.dtype == torch.float32:
-                    new_value = new_value.to(torch.float16, non_blocking=non_blocking)
-                new_value = param_cls(new_value, requires_grad=old_value.requires_grad, **kwargs).to(device)
-            elif param_cls.__name__ in ("QTensor", "QBitsTensor", "AffineQuantizedTensor"):
-                new_value = torch.nn.Parameter(new_value, requires_grad=old_value.requires_grad).to(device)
-            else:
-                new_value = param_cls(new_value, requires_grad=old_value.requires_grad).to(device, non_blocking=non_blocking)
-            module._parameters[tensor_name] = new_value
-            if fp16_statistics is not None:
-                module._parameters[tensor_name].SCB = fp16_statistics.to(device, non_blocking=non_blocking)
-                del fp16_statistics
-    # remember materialised tied parameters
-    if tied_params_map is not None and old_value.data_ptr() in tied_params_map and device not in tied_params_map[old_value.data_ptr()]:
-        tied_params_map[old_value.data_ptr()][device] = new_value
-    elif value is not None and tied_params_map is not None and value.data_ptr() in tied_params_map and device not in tied_params_map[value.data_ptr()]:
-        tied_params_map[value.data_ptr()][device] = new_value
+    return first_device.type == second_device.type and canonical(first_device) == canonical(second_device)
 
 
 def named_module_tensors(module: nn.Module, include_buffers: bool = True, recurse: bool = False, remove_non_persistent: bool = False):
-    """(name, tensor) for parameters and, optionally, buffers (non-persistent ones can be dropped)."""
+    """``(name, tensor)`` over the parameters, then (optionally) the buffers — all of them or only those saved in a state dict."""
     yield from module.named_parameters(recurse=recurse)
-    if include_buffers:
-        non_persistent_buffers = set()
-        if remove_non_persistent:
-            non_persistent_buffers = get_non_persistent_buffers(module, recurse=recurse)
-        for named_buffer in module.named_buffers(recurse=recurse):
-            name, _ = named_buffer
-            if name not in non_persistent_buffers:
-                yield named_buffer
+    if not include_buffers:
+        return
+    transient = get_non_persistent_buffers(module, recurse=recurse) if remove_non_persistent else ()
+    yield from ((name, buf) for name, buf in module.named_buffers(recurse=recurse) if name not in transient)
 
 
-def get_non_persistent_buffers(module: nn.Module, recurse: bool = False, fqns: bool = False):
-    non_persistent_buffers_set = module._non_persistent_buffers_set
-    if fqns:
-        non_persistent_buffers_set = set(non_persistent_buffers_set)
+def get_non_persistent_buffers(module: nn.Module, recurse: bool = False, fqns: bool = False) -> set:
+    """Names of the buffers ``register_buffer(..., persistent=False)`` created; ``fqns`` qualifies the names of sub-modules."""
+    names = set(module._non_persistent_buffers_set)
     if recurse:
-        for n, m in module.named_modules():
-            if fqns:
-                non_persistent_buffers_set |= {n + "." + b for b in m._non_persistent_buffers_set}
-            else:
-                non_persistent_buffers_set |= m._non_persistent_buffers_set
-    return non_persistent_buffers_set
-
-
-class FindTiedParametersResult(list):
-    """List of groups of tied-parameter names (with a deprecated dict-style ``values`` accessor)."""
-
-    def __init__(self, *args, **kwargs):
-        super().__init__(*args, **kwargs)
-
-    def values(self):
-        warnings.warn("The 'values' method of FindTiedParametersResult is deprecated and will be removed in Accelerate v1.3.0. ", FutureWarning)
-        return sum([x[1:] for x in self], [])
-
-
-def check_tied_parameters_in_config(model: nn.Module) -> bool:
-    """Does the (transformers) config say that some weights are tied?"""
-    has_tied_word_embedding = False
-    has_tied_encoder_decoder = False
-    has_tied_module = False
-    if "PreTrainedModel" in [c.__name__ for c in model.__class__.__mro__]:
-        has_tied_word_embedding = False
-        config = getattr(model, "config", None)
-        if config is not None:
-            try:
-                text = config.get_text_config(decoder=True)
-            except Exception:
-                text = config
-            has_tied_word_embedding = bool(getattr(text, "tie_word_embeddings", False) and model.get_output_embeddings())
-            has_tied_encoder_decoder = bool(getattr(config, "is_encoder_decoder", False) and getattr(config, "tie_encoder_decoder", False))
-        has_tied_module = any(hasattr(module, "_tie_weights") for module in model.modules())
-    elif getattr(getattr(model, "config", None), "tie_word_embeddings", False):
-        has_tied_word_embedding = True
-    return any([has_tied_word_embedding, has_tied_encoder_decoder, has_tied_module])
-
-
-def _get_param_device(param, device_map):
-    if param in device_map:
-        return device_map[param]
-    parent_param = ".".join(param.split(".")[:-1])
-    if parent_param == param:
-        raise ValueError(f"The `device_map` does not contain the module {param}.")
-    return _get_param_device(parent_param, device_map)
-
-
-def check_tied_parameters_on_same_device(tied_params, device_map):
-    """Warn when tied parameters were mapped to different devices (they will be duplicated)."""
-    for tie_param in tied_params:
-        tie_param_devices = {}
-        for param in tie_param:
-            tie_param_devices[param] = _get_param_device(param, device_map)
-        if len(set(tie_param_devices.values())) > 1:
-            logger.warning(f"Tied parameters are on different devices: {tie_param_devices}. Please modify your custom device map or set `device_map='auto'`. ")
-
-
-def find_tied_parameters(model: nn.Module, **kwargs) -> list:
-    """Groups of parameter names that are the same tensor object."""
-    all_named_parameters = dict(model.named_parameters(remove_duplicate=False))
-    no_duplicate_named_parameters = dict(model.named_parameters(remove_duplicate=True))
-    tied_param_names = set(all_named_parameters.keys()) - set(no_duplicate_named_parameters.keys())
-    tied_param_groups = {}
-    for tied_param_name in tied_param_names:
-        tied_param = all_named_parameters[tied_param_name]
-        for param_name, param in no_duplicate_named_parameters.items():
-            if param is tied_param:
-                tied_param_groups.setdefault(param_name, []).append(tied_param_name)
-    return FindTiedParametersResult([sorted([weight] + list(set(tied))) for weight, tied in tied_param_groups.items()])
-
-
-def retie_parameters(model: nn.Module, tied_params):
-    """Make the parameters of each group the same object again (after loading broke the tie)."""
-    for tied_group in tied_params:
-        param_to_tie = None
-        for param_name in tied_group:
-            module = model
-            splits = param_name.split(".")
-            for split in splits[:-1]:
-                module = getattr(module, split)
-            param = getattr(module, splits[-1])
-            if param_to_tie is None and param.device != torch.device("meta"):
-                param_to_tie = param
-                break
-        if param_to_tie is not None:
-            for param_name in tied_group:
-                module = model
-                splits = param_name.split(".")
-                for split in splits[:-1]:
-                    module = getattr(module, split)
-                setattr(module, splits[-1], param_to_tie)
-
-
-def _get_proper_dtype(dtype):
-    if isinstance(dtype, str):
-        dtype = dtype.replace("torch.", "")
-        dtype = getattr(torch, dtype)
-    return dtype
+        for prefix, child in module.named_modules():
+            names.update(f"{prefix}.{b}" if fqns and prefix else b for b in child._non_persistent_buffers_set)
+    return names
 
 
 def compute_module_sizes(model: nn.Module, dtype=None, special_dtypes: Optional[dict] = None, buffers_only: bool = False):
-    """Bytes of every (sub)module name, ``""`` being the whole model."""
-    if dtype is not None:
-        dtype = _get_proper_dtype(dtype)
-        dtype_size = dtype_byte_size(dtype)
-    if special_dtypes is not None:
-        special_dtypes = {key: _get_proper_dtype(dtyp) for key, dtyp in special_dtypes.items()}
-        special_dtypes_size = {key: dtype_byte_size(dtyp) for key, dtyp in special_dtypes.items()}
-    module_sizes = defaultdict(int)
-    module_list = []
-    if not buffers_only:
-        module_list = named_module_tensors(model, recurse=True)
-    else:
-        module_list = model.named_buffers(recurse=True)
-    for name, tensor in module_list:
-        if special_dtypes is not None and name in special_dtypes:
-            size = tensor.numel() * special_dtypes_size[name]
-        elif dtype is None:
-            size = tensor.numel() * dtype_byte_size(tensor.dtype)
-        elif str(tensor.dtype).startswith(("torch.uint", "torch.int", "torch.bool")):
-            size = tensor.numel() * dtype_byte_size(tensor.dtype)
-        else:
-            size = tensor.numel() * min(dtype_size, dtype_byte_size(tensor.dtype))
-        name_parts = name.split(".")
-        for idx in range(len(name_parts) + 1):
-            module_sizes[".".join(name_parts[:idx])] += size
-    return module_sizes
+    """``{dotted name: bytes}`` for every tensor, every module that contains one, and ``""`` (the whole model).
+
+    ``dtype`` is the dtype the floating tensors will be loaded in (a tensor never grows: the smaller of the two counts);
+    ``special_dtypes`` overrides it per tensor name.
+    """
+    target_bytes = None if dtype is None else dtype_byte_size(_as_torch_dtype(dtype))
+    override_bytes = {name: dtype_byte_size(_as_torch_dtype(d)) for name, d in (special_dtypes or {}).items()}
+
+    def bytes_per_element(name, tensor):
+        own = dtype_byte_size(tensor.dtype)
+        if name in override_bytes:
+            return override_bytes[name]
+        if target_bytes is None or _is_integer_like(tensor.dtype):
+            return own
+        return min(own, target_bytes)
+
+    sizes = defaultdict(int)
+    tensors = model.named_buffers(recurse=True) if buffers_only else named_module_tensors(model, recurse=True)
+    for name, tensor in tensors:
+        nbytes = tensor.numel() * bytes_per_element(name, tensor)
+        sizes[""] += nbytes
+        for prefix in itertools.accumulate(name.split("."), lambda a, b: f"{a}.{b}"):
+            sizes[prefix] += nbytes
+    return sizes
 
 
 def compute_module_total_buffer_size(model: nn.Module, dtype=None, special_dtypes=None):
-    module_sizes = compute_module_sizes(model, dtype=dtype, special_dtypes=special_dtypes, buffers_only=True)
-    return module_sizes.get("", 0)
+    return compute_module_sizes(model, dtype=dtype, special_dtypes=special_dtypes, buffers_only=True).get("", 0)
+
+
+def _top_level_entries(model: nn.Module) -> list:
+    """What a packer starts from: the model's own parameters, its children, its own buffers — in that order."""
+    return [*model.named_parameters(recurse=False), *model.named_children(), *model.named_buffers(recurse=False)]
 
 
 def get_max_layer_size(modules: list, module_sizes: dict, no_split_module_classes: list):
-    """(size, names) of the largest module that cannot be split further."""
-    max_size = 0
-    layer_names = []
-    modules_to_treat = modules.copy()
-    while len(modules_to_treat) > 0:
-        module_name, module = modules_to_treat.pop(0)
-        modules_children = list(module.named_children()) if isinstance(module, torch.nn.Module) else []
-        if len(modules_children) == 0 or module.__class__.__name__ in no_split_module_classes:
-            size = module_sizes[module_name]
-            if size > max_size:
-                max_size = size
-                layer_names = [module_name]
-            elif size == max_size:
-                layer_names.append(module_name)
-        else:
-            modules_to_treat = [(f"{module_name}.{n}", v) for n, v in modules_children] + modules_to_treat
-    return max_size, layer_names
+    """``(bytes, [names])`` of the largest piece that cannot be divided: a tensor, a module without children, or a module whose
+    class is in ``no_split_module_classes``.  ``modules`` is a list of ``(name, module or tensor)``; visiting is depth first, in order."""
+    best, holders = 0, []
+    stack = list(reversed(modules))
+    while stack:
+        name, entry = stack.pop()
+        children = list(entry.named_children()) if isinstance(entry, nn.Module) else []
+        if children and type(entry).__name__ not in no_split_module_classes:
+            stack.extend((f"{name}.{child_name}", child) for child_name, child in reversed(children))
+            continue
+        size = module_sizes[name]
+        if size > best:
+            best, holders = size, [name]
+        elif size == best:
+            holders.append(name)
+    return best, holders
 
 
-def get_max_memory(max_memory: Optional[dict] = None):
-    """Per-device byte budget: free CUDA memory per GPU plus available CPU RAM when not given."""
-    import psutil
-
-    if max_memory is None:
-        max_memory = {}
-        if torch.cuda.is_available():
-            for i in range(torch.cuda.device_count()):
-                try:
-                    _ = torch.tensor([0], device=i)
-                    max_memory[i] = torch.cuda.mem_get_info(i)[0]
-                except Exception:
-                    logger.info(f"Device {i} seems unavailable, Proceeding to check subsequent devices.")
-                    continue
-        max_memory["cpu"] = psutil.virtual_memory().available
-        return max_memory
-    for key in max_memory:
-        if isinstance(max_memory[key], str):
-            max_memory[key] = convert_file_size_to_int(max_memory[key])
-    gpu_devices = sorted([k for k in max_memory.keys() if isinstance(k, int)])
-    num_devices = torch.cuda.device_count() if torch.cuda.is_available() else 0
-    for device in gpu_devices:
-        if device >= num_devices or device < 0:
-            logger.warning(f"Device {device} is not available, available devices are {list(range(num_devices))}")
-    all_devices = gpu_devices + [k for k in ["mps", "cpu", "disk"] if k in max_memory.keys()]
-    for k in max_memory.keys():
-        if k not in all_devices:
-            raise ValueError(f"Device {k} is not recognized, available devices are integers(for GPU/XPU), 'mps', 'cpu' and 'disk'")
-    return {k: max_memory[k] for k in all_devices}
+def calculate_maximum_sizes(model: nn.Module):
+    """``(total bytes, (largest undividable layer bytes, its names))`` — what ``accelerate estimate-memory`` prints."""
+    sizes = compute_module_sizes(model)
+    keep_whole = getattr(model, "_no_split_modules", None) or []
+    return sizes[""], get_max_layer_size(_top_level_entries(model), sizes, keep_whole)
 
 
-def clean_device_map(device_map: dict, module_name: str = ""):
-    """Collapse children that all live on one device into their parent entry."""
-    prefix = "" if module_name == "" else f"{module_name}."
-    values = [v for k, v in device_map.items() if k.startswith(prefix)]
-    if len(set(values)) == 1 and len(values) > 1:
-        for k in [k for k in device_map if k.startswith(prefix)]:
-            del device_map[k]
-        device_map[module_name] = values[0]
-    children_modules = [k for k in device_map.keys() if k.startswith(prefix) and len(k) > len(module_name)]
-    idx = len(module_name.split(".")) + 1 if len(module_name) > 0 else 1
-    children = set(".".join(k.split(".")[:idx]) for k in children_modules)
-    for child in children:
-        clean_device_map(device_map, module_name=child)
-    return device_map
+# ------------------------------------------------------------------------------------------------- tensor placement
+def _owner_of(module: nn.Module, dotted: str) -> tuple[nn.Module, str]:
+    """The sub-module that directly holds ``dotted`` and the tensor's own name."""
+    *path, leaf = dotted.split(".")
+    for step in path:
+        child = getattr(module, step)
+        if child is None:
+            raise ValueError(f"{module} has no attribute {step}.")
+        module = child
+    return module, leaf
 
 
-def load_offloaded_weights(model, index, offload_folder):
-    """Load disk-offloaded weights listed in ``index`` into ``model`` on CPU."""
-    if index is None or len(index) == 0:
+def _tied_copy(tied_params_map, tensor, device):
+    """The already materialised copy on ``device`` of a tensor registered in ``tied_params_map`` (else None)."""
+    if tied_params_map is None or tensor is None:
+        return None
+    return tied_params_map.get(tensor.data_ptr(), {}).get(device)
+
+
+def _rewrap_parameter(template: nn.Parameter, data: torch.Tensor, device, requires_grad: bool, non_blocking: bool):
+    """A parameter of ``template``'s class around ``data`` on ``device`` (bitsandbytes / quanto / torchao classes need their own treatment)."""
+    kind = type(template)
+    if kind.__name__ in _QUANTIZED_PARAM_CLASSES:
+        if kind.__name__ == "Int8Params" and data.dtype == torch.float32:
+            data = data.to(torch.float16, non_blocking=non_blocking)  # int8 quantisation starts from half precision
+        return kind(data, requires_grad=requires_grad, **template.__dict__).to(device)
+    if kind.__name__ in _TENSOR_SUBCLASS_PARAMS:
+        return nn.Parameter(data, requires_grad=requires_grad).to(device)
+    return kind(data, requires_grad=requires_grad).to(device, non_blocking=non_blocking)
+
+
+def set_module_tensor_to_device(module: nn.Module, tensor_name: str, device, value: Optional[torch.Tensor] = None, dtype=None,
+                                fp16_statistics=None, tied_params_map=None, non_blocking: bool = False, clear_cache: bool = True):
+    """Put the parameter or buffer ``tensor_name`` (dotted names allowed) of ``module`` on ``device``, optionally with a new ``value``.
+
+    Leaving the meta device needs a ``value``.  The tensor keeps its kind (parameter class, ``requires_grad``, buffer-ness) and, when
+    ``dtype`` is None, its dtype; integer tensors are never cast.  ``tied_params_map`` ``{data_ptr: {device: tensor}}`` makes every
+    member of a tie group resolve to one tensor per device instead of one copy each.
+    """
+    owner, leaf = _owner_of(module, tensor_name)
+    is_parameter, is_buffer = leaf in owner._parameters, leaf in owner._buffers
+    if not (is_parameter or is_buffer):
+        raise ValueError(f"{owner} does not have a parameter or a buffer named {leaf}.")
+    current = getattr(owner, leaf)
+
+    shared = _tied_copy(tied_params_map, value, device)
+    if shared is None:
+        shared = _tied_copy(tied_params_map, current, device)
+    if shared is not None:
+        owner._parameters[leaf] = shared
         return
-    for param_name, metadata in index.items():
-        if "SCB" in param_name:
-            continue
-        fp16_statistics = None
-        if "weight" in param_name and param_name.replace("weight", "SCB") in index.keys():
-            weight_name = param_name.replace("weight", "SCB")
-            fp16_statistics = load_offloaded_weight(os.path.join(offload_folder, f"{weight_name}.dat"), index[weight_name])
-        tensor_file = os.path.join(offload_folder, f"{param_name}.dat")
-        weight = load_offloaded_weight(tensor_file, metadata)
-        set_module_tensor_to_device(model, param_name, "cpu", value=weight, fp16_statistics=fp16_statistics)
+
+    to_meta = device in ("meta", _META)
+    if current.device == _META and value is None and not to_meta:
+        raise ValueError(f"{leaf} is on the meta device, we need a `value` to put in on {device}.")
+    template = owner._parameters[leaf] if is_parameter else None
+    if value is not None:
+        if value.shape != current.shape and type(template).__name__ != "Params4bit":
+            raise ValueError(f'Trying to set a tensor of shape {value.shape} in "{leaf}" (which has shape {current.shape}), this looks incorrect.')
+        if dtype is None:
+            value = value.to(current.dtype, non_blocking=non_blocking)
+        elif not _is_integer_like(value.dtype):
+            value = value.to(dtype, non_blocking=non_blocking)
+    requested = device  # the key callers use in `tied_params_map`
+    if isinstance(device, int):
+        device = torch.device("cuda", device)
+
+    with torch.no_grad():
+        if value is None:
+            placed = current.to(device, non_blocking=non_blocking)
+            if to_meta and dtype is not None:
+                if not _is_integer_like(current.dtype):
+                    placed = placed.to(dtype, non_blocking=non_blocking)
+                if is_parameter:
+                    owner._parameters[leaf] = type(template)(placed, requires_grad=current.requires_grad)
+        elif isinstance(value, torch.Tensor):
+            placed = value.to(device, non_blocking=non_blocking)
+        else:
+            placed = torch.tensor(value, device=device)
+
+        if is_buffer:
+            owner._buffers[leaf] = placed
+        elif value is not None or not check_device_same(torch.device(device), owner._parameters[leaf].device):
+            placed = _rewrap_parameter(owner._parameters[leaf], placed, device, current.requires_grad, non_blocking)
+            owner._parameters[leaf] = placed
+            if fp16_statistics is not None:
+                placed.SCB = fp16_statistics.to(device, non_blocking=non_blocking)
+
+    if tied_params_map is not None:
+        for source in (current, value):
+            copies = tied_params_map.get(source.data_ptr()) if source is not None else None
+            if copies is not None and requested not in copies:
+                copies[requested] = placed
+                break
 
 
-def get_module_leaves(module_sizes):
-    module_children = {}
-    for module in module_sizes:
-        if module == "" or "." not in module:
+def has_offloaded_params(module: nn.Module) -> bool:
+    """Is ``module`` run through an ``AlignDevicesHook`` that keeps its weights somewhere else between forwards?"""
+    from ..hooks import AlignDevicesHook
+
+    hook = getattr(module, "_hf_hook", None)
+    return isinstance(hook, AlignDevicesHook) and hook.offload
+
+
+@contextlib.contextmanager
+def align_module_device(module: nn.Module, execution_device=None):
+    """Within the block, ``module``'s own parameters are on ``execution_device`` (offloaded ones are brought in through their hook);
+    afterwards everything is back where it was."""
+    if has_offloaded_params(module):
+        hook = module._hf_hook
+        saved = hook.execution_device
+        if execution_device is not None:
+            hook.execution_device = execution_device
+        try:
+            hook.pre_forward(module)
+            yield
+        finally:
+            hook.post_forward(module, None)
+            hook.execution_device = saved
+        return
+    if execution_device is None:
+        yield
+        return
+    home = {name: param.device for name, param in module.named_parameters(recurse=False)}
+    try:
+        for name in home:
+            set_module_tensor_to_device(module, name, execution_device)
+        yield
+    finally:
+        for name, device in home.items():
+            set_module_tensor_to_device(module, name, device)
+
+
+# ------------------------------------------------------------------------------------------------- tied parameters
+class FindTiedParametersResult(list):
+    """List of tie groups (each a sorted list of names).  ``values()`` is what the old dict-shaped result offered."""
+
+    def values(self):
+        warnings.warn("The 'values' method of FindTiedParametersResult is deprecated and will be removed in Accelerate v1.3.0. ", FutureWarning)
+        return [name for group in self for name in group[1:]]
+
+
+def find_tied_parameters(model: nn.Module, **kwargs) -> list:
+    """Groups of parameter names bound to one and the same ``nn.Parameter`` object, e.g. ``[["embed.weight", "lm_head.weight"]]``."""
+    names_of = defaultdict(list)
+    for name, param in model.named_parameters(remove_duplicate=False):
+        names_of[id(param)].append(name)
+    return FindTiedParametersResult(sorted(set(names)) for names in names_of.values() if len(names) > 1)
+
+
+def check_tied_parameters_in_config(model: nn.Module) -> bool:
+    """Does the model's (transformers-style) config promise tied weights — so that finding none means ``tie_weights()`` was forgotten?"""
+    config = getattr(model, "config", None)
+    if not any(cls.__name__ == "PreTrainedModel" for cls in type(model).__mro__):
+        return bool(getattr(config, "tie_word_embeddings", False))
+    promises = [any(hasattr(sub, "_tie_weights") for sub in model.modules())]
+    if config is not None:
+        try:
+            text_config = config.get_text_config(decoder=True)
+        except Exception:
+            text_config = config
+        promises.append(bool(getattr(text_config, "tie_word_embeddings", False) and model.get_output_embeddings()))
+        promises.append(bool(getattr(config, "is_encoder_decoder", False) and getattr(config, "tie_encoder_decoder", False)))
+    return any(promises)
+
+
+def _get_param_device(param: str, device_map: dict):
+    """Device of the closest enclosing entry of ``device_map`` (``""`` encloses everything)."""
+    name = param
+    while name and name not in device_map:
+        name = name.rpartition(".")[0]
+    if name not in device_map:
+        raise ValueError(f"The `device_map` does not contain the module {param}.")
+    return device_map[name]
+
+
+def check_tied_parameters_on_same_device(tied_params, device_map) -> None:
+    """Warn about tie groups the device map tears apart: each member would get its own copy."""
+    for group in tied_params:
+        placement = {name: _get_param_device(name, device_map) for name in group}
+        if len(set(placement.values())) > 1:
+            logger.warning(f"Tied parameters are on different devices: {placement}. Please modify your custom device map or set `device_map='auto'`. ")
+
+
+def retie_parameters(model: nn.Module, tied_params) -> None:
+    """Loading gives every name its own tensor; make each group share the first member that holds real data again."""
+    for group in tied_params:
+        holders = [_owner_of(model, name) for name in group]
+        keeper = next((getattr(owner, leaf) for owner, leaf in holders if getattr(owner, leaf).device != _META), None)
+        if keeper is None:
             continue
-        parent = module.rsplit(".", 1)[0]
-        module_children[parent] = module_children.get(parent, 0) + 1
-    return [module for module in module_sizes if module_children.get(module, 0) == 0 and not module.endswith(("weight", "bias"))]
+        for owner, leaf in holders:
+            setattr(owner, leaf, keeper)
+
+
+# ------------------------------------------------------------------------------------------------- budgets
+def get_max_memory(max_memory: Optional[dict] = None) -> dict:
+    """Byte budget per device.  Not given: what is free on every visible GPU plus the available host RAM.  Given: sizes parsed
+    (``"10GiB"``), keys validated and ordered GPUs first, then ``cpu``, then ``disk``."""
+    gpu_count = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if max_memory is None:
+        import psutil
+
+        budget = {}
+        for index in range(gpu_count):
+            try:
+                torch.zeros(1, device=index)  # forces the context; a dead device raises here
+                budget[index] = torch.cuda.mem_get_info(index)[0]
+            except Exception:
+                logger.info(f"Device {index} seems unavailable, Proceeding to check subsequent devices.")
+        budget["cpu"] = psutil.virtual_memory().available
+        return budget
+    parsed = {key: convert_file_size_to_int(amount) if isinstance(amount, str) else amount for key, amount in max_memory.items()}
+    max_memory.update(parsed)  # callers see their strings parsed, as with the reference
+    gpus = sorted(key for key in parsed if isinstance(key, int))
+    named = [key for key in ("mps", "cpu", "disk") if key in parsed]
+    strangers = [key for key in parsed if key not in gpus and key not in named]
+    if strangers:
+        raise ValueError(f"Device {strangers[0]} is not recognized, available devices are integers(for GPU/XPU), 'mps', 'cpu' and 'disk'")
+    for index in gpus:
+        if not 0 <= index < gpu_count:
+            logger.warning(f"Device {index} is not available, available devices are {list(range(gpu_count))}")
+    return {key: parsed[key] for key in gpus + named}
+
+
+def get_module_leaves(module_sizes) -> list:
+    """Names in ``module_sizes`` nothing else in it sits under, weights and biases themselves excluded."""
+    parents = {name.rsplit(".", 1)[0] for name in module_sizes if "." in name}
+    return [name for name in module_sizes if name not in parents and not name.endswith(("weight", "bias"))]
+
+
+def _first_size_per_class(model: nn.Module, module_sizes: dict, class_names) -> dict:
+    """Bytes of the first module of each of ``class_names`` met in ``module_sizes`` order."""
+    wanted, found = set(class_names), {}
+    for name, size in module_sizes.items():
+        if name == "" or len(found) == len(wanted):
+            continue
+        try:
+            kind = type(model.get_submodule(name)).__name__
+        except AttributeError:  # a tensor's name, not a module's
+            continue
+        if kind in wanted:
+            found.setdefault(kind, size)
+    return found
 
 
 def get_balanced_memory(model: nn.Module, max_memory: Optional[dict] = None, no_split_module_classes: Optional[list] = None,
-                        dtype=None, special_dtypes: Optional[dict] = None, low_zero: bool = False):
-    """Budgets that spread ``model`` evenly over the GPUs (``low_zero`` keeps GPU 0 nearly empty)."""
-    user_not_set_max_memory = max_memory is None
+                        dtype=None, special_dtypes: Optional[dict] = None, low_zero: bool = False) -> dict:
+    """Budgets that make the greedy packer spread ``model`` evenly over the GPUs instead of filling GPU 0 first: every GPU but the
+    last is capped at an equal share plus slack (1.25 x the larger of the biggest undividable block and the mean leaf module).
+    ``low_zero`` keeps GPU 0 as empty as the others allow (room for ``generate``'s activations)."""
+    defaults_used = max_memory is None
     max_memory = get_max_memory(max_memory)
-    num_devices = len([d for d in max_memory if torch.device(d).type == "cuda" and max_memory[d] > 0]) if torch.cuda.is_available() else 0
-    if num_devices == 0:
+    gpus = sorted(key for key, room in max_memory.items() if isinstance(key, int) and room > 0) if torch.cuda.is_available() else []
+    if not gpus:
         return max_memory
-    if num_devices == 1:
+    if len(gpus) == 1:
         low_zero = False
-        if user_not_set_max_memory:
-            for key in max_memory.keys():
-                if isinstance(key, int):
-                    max_memory[key] *= 0.9
-                    logger.info(f"We will use 90% of the memory on device {key} for storing the model, and 10% for the buffer to avoid OOM. You can set `max_memory` in to a higher value to use more memory (at your own risk).")
-                    break
-    module_sizes = compute_module_sizes(model, dtype=dtype, special_dtypes=special_dtypes)
-    per_gpu = module_sizes[""] // (num_devices - 1 if low_zero else num_devices)
+        if defaults_used:
+            max_memory[gpus[0]] *= 0.9
+            logger.info(f"We will use 90% of the memory on device {gpus[0]} for storing the model, and 10% for the buffer to avoid OOM. "
+                        "You can set `max_memory` in to a higher value to use more memory (at your own risk).")
+    sizes = compute_module_sizes(model, dtype=dtype, special_dtypes=special_dtypes)
+    share = sizes[""] // (len(gpus) - 1 if low_zero else len(gpus))
+
     if no_split_module_classes is None:
         no_split_module_classes = []
     elif not isinstance(no_split_module_classes, (list, tuple)):
         no_split_module_classes = [no_split_module_classes]
-    if len(no_split_module_classes) > 0:
-        no_split_children = {}
-        for name, size in module_sizes.items():
-            if name == "":
-                continue
-            submodule = model
-            for submodule_name in name.split("."):
-                submodule = getattr(submodule, submodule_name)
-            class_name = submodule.__class__.__name__
-            if class_name in no_split_module_classes and class_name not in no_split_children:
-                no_split_children[class_name] = size
-            if set(no_split_children.keys()) == set(no_split_module_classes):
-                break
-        buffer = max(no_split_children.values()) if len(no_split_children) > 0 else 0
-    else:
-        buffer = 0
-    leaves = get_module_leaves(module_sizes)
-    module_sizes = {n: v for n, v in module_sizes.items() if n not in leaves}
-    leaves = get_module_leaves(module_sizes)
-    mean_leaves = int(sum([module_sizes[n] for n in leaves]) / max(len(leaves), 1))
-    buffer = int(1.25 * max(buffer, mean_leaves))
-    per_gpu += buffer
-    gpus_idx_list = list(sorted(device_id for device_id, device_mem in max_memory.items() if isinstance(device_id, int) and device_mem > 0))
-    for idx in gpus_idx_list[:-1]:
-        max_memory[idx] = min(max_memory[0] if low_zero and idx == 0 else per_gpu, max_memory[idx])
+    undividable = max(_first_size_per_class(model, sizes, no_split_module_classes).values(), default=0)
+    # mean size of the smallest *modules* (drop the tensor-level entries first, then take what is a leaf among the rest)
+    tensor_level = set(get_module_leaves(sizes))
+    module_level = {name: size for name, size in sizes.items() if name not in tensor_level}
+    leaves = get_module_leaves(module_level)
+    mean_leaf = int(sum(module_level[name] for name in leaves) / max(len(leaves), 1))
+    share += int(1.25 * max(undividable, mean_leaf))
+
+    for index in gpus[:-1]:
+        cap = max_memory[0] if (low_zero and index == 0) else share
+        max_memory[index] = min(cap, max_memory[index])
     if low_zero:
-        min_zero = max(0, module_sizes[""] - sum([max_memory[i] for i in range(1, num_devices)]))
-        max_memory[0] = min(min_zero, max_memory[0])
+        overflow = sizes[""] - sum(max_memory[i] for i in range(1, len(gpus)))
+        max_memory[0] = min(max(0, overflow), max_memory[0])
     return max_memory
 
 
-def calculate_maximum_sizes(model: torch.nn.Module):
-    """(total bytes, (largest layer bytes, names))."""
-    sizes = compute_module_sizes(model)
-    no_split_modules = getattr(model, "_no_split_modules", None)
-    if no_split_modules is None:
-        no_split_modules = []
-    modules_to_treat = list(model.named_parameters(recurse=False)) + list(model.named_children()) + list(model.named_buffers(recurse=False))
-    largest_layer = get_max_layer_size(modules_to_treat, sizes, no_split_modules)
-    total_size = sizes[""]
-    return total_size, largest_layer
+def clean_device_map(device_map: dict, module_name: str = "") -> dict:
+    """Replace the entries below a module by one entry for the module wherever they all name the same device; works on
+    ``device_map`` in place, deepest modules first, so whole sub-trees fold up as far as they can."""
+    root = module_name
+
+    def below(prefix):
+        dotted = f"{prefix}." if prefix else ""
+        return [key for key in device_map if key.startswith(dotted)]
+
+    ancestors = set()
+    for key in below(root):
+        parts = key.split(".")
+        ancestors.update(".".join(parts[:depth]) for depth in range(len(root.split(".")) if root else 0, len(parts)))
+    ancestors.add(root)
+    for prefix in sorted(ancestors, key=lambda name: (-(name.count(".") + 1 if name else 0), name)):
+        members = below(prefix)
+        places = {device_map[key] for key in members}
+        if len(members) > 1 and len(places) == 1:
+            for key in members:
+                del device_map[key]
+            device_map[prefix] = places.pop()
+    return device_map
 
 
-# ------------------------------------------------------------------------------------ device map inference
+# ------------------------------------------------------------------------------------------------- device map inference
 def infer_auto_device_map(model: nn.Module, max_memory: Optional[dict] = None, no_split_module_classes: Optional[list] = None,
                           dtype=None, special_dtypes: Optional[dict] = None, verbose: bool = False, clean_result: bool = True,
                           offload_buffers: bool = False, fallback_allocation: bool = False):
@@ -523,7 +541,7 @@ def infer_auto_device_map(model: nn.Module, max_memory: Optional[dict] = None, n
     tied_parameters = find_tied_parameters(model)
     if check_tied_parameters_in_config(model) and len(tied_parameters) == 0:
         logger.warn("The model weights are not tied. Please use the `tie_weights` method before using the `infer_auto_device` function.")
-    modules_to_treat = (list(model.named_parameters(recurse=False)) + list(model.named_children()) + list(model.named_buffers(recurse=False)))
+    modules_to_treat = _top_level_entries(model)
     max_layer_size, max_layer_names = get_max_layer_size(modules_to_treat, module_sizes, no_split_module_classes)
 
     device_map: "OrderedDict[str, Union[int, str]]" = OrderedDict()
@@ -654,322 +672,293 @@ def infer_auto_device_map(model: nn.Module, max_memory: Optional[dict] = None, n
     return device_map
 
 
-def check_device_map(model: nn.Module, device_map: dict):
-    """Every parameter must be covered by an entry of ``device_map``."""
-    all_module_names = dict(model.named_modules())
-    invalid_keys = [k for k in device_map if k != "" and k not in all_module_names and k not in dict(named_module_tensors(model, recurse=True))]
-    if invalid_keys:
-        warnings.warn(f"The following device_map keys do not match any submodules in the model: {invalid_keys}", UserWarning)
-    all_model_tensors = [name for name, _ in model.state_dict().items()]
-    for module_name in device_map.keys():
-        if module_name == "":
-            all_model_tensors.clear()
-            break
-        all_model_tensors = [name for name in all_model_tensors if not name == module_name and not name.startswith(module_name + ".")]
-    if len(all_model_tensors) > 0:
-        non_covered_params = ", ".join(all_model_tensors)
-        raise ValueError(f"The device_map provided does not give any device for the following parameters: {non_covered_params}")
+def check_device_map(model: nn.Module, device_map: dict) -> None:
+    """Raise when some tensor of the state dict has no entry above it in ``device_map``; warn about entries that name nothing."""
+    known = set(dict(model.named_modules())) | {name for name, _ in named_module_tensors(model, recurse=True)}
+    strangers = [key for key in device_map if key != "" and key not in known]
+    if strangers:
+        warnings.warn(f"The following device_map keys do not match any submodules in the model: {strangers}", UserWarning)
+    if "" in device_map:
+        return
+
+    def covered(tensor_name):
+        return any(tensor_name == key or tensor_name.startswith(f"{key}.") for key in device_map)
+
+    orphans = [name for name in model.state_dict() if not covered(name)]
+    if orphans:
+        raise ValueError(f"The device_map provided does not give any device for the following parameters: {', '.join(orphans)}")
 
 
-# ------------------------------------------------------------------------------------ checkpoint IO
+# ------------------------------------------------------------------------------------------------- checkpoint IO
+def _torch_device_name(device) -> str:
+    return f"cuda:{device}" if isinstance(device, int) else device
+
+
+def _require_pt_safetensors(checkpoint_file, metadata) -> None:
+    if metadata is None:
+        logger.warning(f"The safetensors archive passed at {checkpoint_file} does not contain metadata. Make sure to save your model "
+                       "with the `save_pretrained` method. Defaulting to 'pt' metadata.")
+        return
+    fmt = metadata.get("format")
+    if fmt not in ("pt", "tf", "flax"):
+        raise OSError(f"The safetensors archive passed at {checkpoint_file} does not contain the valid metadata. Make sure you save "
+                      "your model with the `save_pretrained` method.")
+    if fmt != "pt":
+        raise ValueError(f"The checkpoint passed was saved with {fmt}, we need a the pt format.")
+
+
 def load_state_dict(checkpoint_file, device_map=None):
-    """Load a (safetensors or torch) checkpoint file; with a ``device_map`` safetensors go straight to their devices."""
-    if str(checkpoint_file).endswith(".safetensors"):
-        from safetensors import safe_open
-        from safetensors.torch import load_file as safe_load_file
+    """Read one checkpoint file.  ``torch.save`` files come back on CPU.  Safetensors files are read tensor by tensor onto the device
+    ``device_map`` assigns to each (``disk`` and unassigned weights go to CPU), so GPU weights never make a stop in host memory."""
+    if not str(checkpoint_file).endswith(".safetensors"):
+        return torch.load(checkpoint_file, map_location=torch.device("cpu"), weights_only=True)
+    from safetensors import safe_open
+    from safetensors.torch import load_file
 
-        with safe_open(checkpoint_file, framework="pt") as f:
-            metadata = f.metadata()
-            weight_names = f.keys()
-        if metadata is None:
-            logger.warning(f"The safetensors archive passed at {checkpoint_file} does not contain metadata. Make sure to save your model with the `save_pretrained` method. Defaulting to 'pt' metadata.")
-            metadata = {"format": "pt"}
-        if metadata.get("format") not in ["pt", "tf", "flax"]:
-            raise OSError(f"The safetensors archive passed at {checkpoint_file} does not contain the valid metadata. Make sure you save your model with the `save_pretrained` method.")
-        elif metadata["format"] != "pt":
-            raise ValueError(f"The checkpoint passed was saved with {metadata['format']}, we need a the pt format.")
-        if device_map is None:
-            return safe_load_file(checkpoint_file)
-        if len(set(device_map.values())) == 1:
-            device = list(device_map.values())[0]
-            target_device = device if device != "disk" else "cpu"
-            if isinstance(target_device, int):
-                target_device = f"cuda:{target_device}"
-            return safe_load_file(checkpoint_file, device=target_device)
-        devices = list(set(device_map.values()) - {"disk"})
-        if "cpu" not in devices:
-            devices.append("cpu")
-        device_weights = {device: [] for device in devices}
-        for module_name, device in device_map.items():
-            if device in devices:
-                device_weights[device].extend([k for k in weight_names if k == module_name or k.startswith(module_name + ".")])
-        device_weights["cpu"].extend([k for k in weight_names if k not in sum(device_weights.values(), [])])
-        tensors = {}
-        for device in devices:
-            target_device = f"cuda:{device}" if isinstance(device, int) else device
-            with safe_open(checkpoint_file, framework="pt", device=target_device) as f:
-                for key in device_weights[device]:
-                    tensors[key] = f.get_tensor(key)
-        return tensors
-    return torch.load(checkpoint_file, map_location=torch.device("cpu"), weights_only=True)
+    with safe_open(checkpoint_file, framework="pt") as archive:
+        _require_pt_safetensors(checkpoint_file, archive.metadata())
+        stored = list(archive.keys())
+    if device_map is None:
+        return load_file(checkpoint_file)
+    targets = set(device_map.values())
+    if len(targets) == 1:
+        (only,) = targets
+        return load_file(checkpoint_file, device=_torch_device_name("cpu" if only == "disk" else only))
+
+    def destination(weight_name):
+        for entry, device in device_map.items():
+            if weight_name == entry or weight_name.startswith(f"{entry}."):
+                return "cpu" if device == "disk" else device
+        return "cpu"
+
+    per_device = defaultdict(list)
+    for weight_name in stored:
+        per_device[destination(weight_name)].append(weight_name)
+    tensors = {}
+    for device, names in per_device.items():
+        with safe_open(checkpoint_file, framework="pt", device=_torch_device_name(device)) as archive:
+            tensors.update((name, archive.get_tensor(name)) for name in names)
+    return tensors
 
 
-def get_state_dict_offloaded_model(model: nn.Module):
-    """State dict (on CPU) of a model whose weights are offloaded behind ``AlignDevicesHook`` s."""
-    state_dict = {}
-    placeholders = set()
-    for name, module in model.named_modules():
-        if name == "":
+def load_offloaded_weights(model, index, offload_folder) -> None:
+    """Bring the weights listed in an offload ``index`` (``offload_weight`` files in ``offload_folder``) back into ``model`` on CPU;
+    int8 weights pick up their ``SCB`` statistics on the way."""
+    for name, entry in (index or {}).items():
+        if "SCB" in name:
+            continue
+        statistics = None
+        companion = name.replace("weight", "SCB")
+        if "weight" in name and companion in index:
+            statistics = load_offloaded_weight(os.path.join(offload_folder, f"{companion}.dat"), index[companion])
+        weight = load_offloaded_weight(os.path.join(offload_folder, f"{name}.dat"), entry)
+        set_module_tensor_to_device(model, name, "cpu", value=weight, fp16_statistics=statistics)
+
+
+def get_state_dict_offloaded_model(model: nn.Module) -> dict:
+    """CPU state dict of a model whose weights live behind offload hooks, gathered one sub-module at a time."""
+    gathered, still_meta = {}, set()
+    for prefix, sub in model.named_modules():
+        if prefix == "":
             continue
         try:
-            with align_module_device(module, "cpu"):
-                module_state_dict = module.state_dict()
+            with align_module_device(sub, "cpu"):
+                local = sub.state_dict()
         except MemoryError:
             raise MemoryError("Offloaded module must fit in CPU memory to call save_model!") from None
-        for key in module_state_dict:
-            if module_state_dict[key].device == torch.device("meta"):
-                placeholders.add(name + f".{key}")
-                continue
-            params = module_state_dict[key]
-            state_dict[name + f".{key}"] = params.to("cpu")
-    for key in placeholders.copy():
-        if key in state_dict:
-            placeholders.remove(key)
-    if placeholders:
-        logger.warning(f"The following tensors were not saved because they were still on meta device: {placeholders}")
-    return state_dict
+        for key, tensor in local.items():
+            full = f"{prefix}.{key}"
+            if tensor.device == _META:
+                still_meta.add(full)
+            else:
+                gathered[full] = tensor.to("cpu")
+    still_meta -= set(gathered)
+    if still_meta:
+        logger.warning(f"The following tensors were not saved because they were still on meta device: {still_meta}")
+    return gathered
 
 
-def get_state_dict_from_offload(module: nn.Module, module_name: str, state_dict: dict, device_to_put_offload="cpu"):
-    root = module_name[: module_name.rfind(".")]
+def get_state_dict_from_offload(module: nn.Module, module_name: str, state_dict: dict, device_to_put_offload="cpu") -> dict:
+    """Fill the entries of ``state_dict`` that belong to the offloaded ``module`` (``module_name`` is one of its tensors' names)."""
+    prefix = module_name[: module_name.rfind(".")]
     with align_module_device(module, device_to_put_offload):
-        for m_key, params in module.state_dict().items():
-            if (root + f".{m_key}") in state_dict:
-                state_dict[root + f".{m_key}"] = params
+        for key, tensor in module.state_dict().items():
+            if f"{prefix}.{key}" in state_dict:
+                state_dict[f"{prefix}.{key}"] = tensor
     return state_dict
 
 
 def shard_checkpoint(state_dict: dict, max_shard_size: Union[int, str] = "10GB", weights_name: str = WEIGHTS_NAME):
-    """Split ``state_dict`` into shards of at most ``max_shard_size`` (HF naming ``name-0000X-of-0000Y.ext``).
+    """Cut ``state_dict`` into files of at most ``max_shard_size`` (one oversized tensor still gets a file of its own).  Tensors that
+    share storage stay in one file.  Returns ``({file name: tensors}, index)``; a single file keeps ``weights_name`` and has no index,
+    several are named ``stem-0000i-of-0000n.ext`` and the index maps every tensor to its file."""
+    limit = convert_file_size_to_int(max_shard_size)
+    shards: list = [{}]
+    filled = total = 0
+    home_of_storage = {}
+    for key, tensor in state_dict.items():
+        if isinstance(tensor, str):
+            continue
+        storage = id_tensor_storage(tensor)
+        if storage[1] != 0 and storage in home_of_storage:
+            shards[home_of_storage[storage]][key] = tensor
+            continue
+        nbytes = tensor.numel() * dtype_byte_size(tensor.dtype)
+        if shards[-1] and filled + nbytes > limit:
+            shards.append({})
+            filled = 0
+        shards[-1][key] = tensor
+        home_of_storage[storage] = len(shards) - 1
+        filled += nbytes
+        total += nbytes
+    if len(shards) == 1:
+        return {weights_name: shards[0]}, None
+    stem, extension = os.path.splitext(weights_name)
+    files, weight_map = {}, {}
+    for number, shard in enumerate(shards, start=1):
+        file_name = f"{stem}-{number:05d}-of-{len(shards):05d}{extension}"
+        files[file_name] = shard
+        weight_map.update(dict.fromkeys(shard, file_name))
+    return files, {"metadata": {"total_size": int(total)}, "weight_map": weight_map}
 
-    Returns ``({filename: shard}, index-or-None)``.
-    """
-    max_shard_size = convert_file_size_to_int(max_shard_size)
-    sharded = [{}]
-    last_block_size = 0
-    total_size = 0
-    storage_id_to_block = {}
-    for key, weight in state_dict.items():
-        if isinstance(weight, str):
-            continue
-        storage_id = id_tensor_storage(weight)
-        if storage_id in storage_id_to_block and storage_id[1] != 0:
-            sharded[storage_id_to_block[storage_id]][key] = weight
-            continue
-        weight_size = weight.numel() * dtype_byte_size(weight.dtype)
-        if last_block_size + weight_size > max_shard_size and len(sharded[-1]) > 0:
-            sharded.append({})
-            last_block_size = 0
-        sharded[-1][key] = weight
-        last_block_size += weight_size
-        total_size += weight_size
-        storage_id_to_block[storage_id] = len(sharded) - 1
-    if len(sharded) == 1:
-        return {weights_name: sharded[0]}, None
-    weight_map = {}
-    shards = {}
-    for idx, shard in enumerate(sharded):
-        shard_file = weights_name.replace(".bin", f"-{idx + 1:05d}-of-{len(sharded):05d}.bin")
-        shard_file = shard_file.replace(".safetensors", f"-{idx + 1:05d}-of-{len(sharded):05d}.safetensors")
-        shards[shard_file] = shard
-        for key in shard.keys():
-            weight_map[key] = shard_file
-    index = {"metadata": {"total_size": int(total_size)}, "weight_map": weight_map}
-    return shards, index
+
+def _checkpoint_files(checkpoint) -> list:
+    """Files to read for ``checkpoint``: a weights file, an index (``*.index.json``), or a folder holding either."""
+    index_file = None
+    if os.path.isfile(checkpoint):
+        if not str(checkpoint).endswith(".json"):
+            return [checkpoint]
+        index_file = checkpoint
+    elif os.path.isdir(checkpoint):
+        present = os.listdir(checkpoint)
+        for whole in (WEIGHTS_NAME, SAFE_WEIGHTS_NAME):
+            if whole in present:
+                return [os.path.join(checkpoint, whole)]
+        indexes = [name for name in present if name.endswith(".index.json")]
+        if not indexes:
+            raise ValueError(f"{checkpoint} is not a folder containing a `.index.json` file or a {WEIGHTS_NAME} or a {SAFE_WEIGHTS_NAME} file")
+        if len(indexes) > 1:
+            raise ValueError(f"{checkpoint} containing more than one `.index.json` file, delete the irrelevant ones.")
+        index_file = os.path.join(checkpoint, indexes[0])
+    else:
+        raise ValueError("`checkpoint` should be the path to a file containing a whole state dict, or the index of a sharded checkpoint, "
+                         f"or a folder containing a sharded checkpoint or the whole state dict, but got {checkpoint}.")
+    with open(index_file) as handle:
+        index = json.load(handle)
+    files = sorted(set(index.get("weight_map", index).values()))
+    return [os.path.join(os.path.dirname(index_file), name) for name in files]
+
+
+def _device_entry_for(tensor_name: str, device_map: dict):
+    try:
+        return _get_param_device(tensor_name, device_map)
+    except ValueError:
+        raise ValueError(f"{tensor_name} doesn't have any device set.") from None
+
+
+def _stays_fp32(param_name: str, keep_in_fp32_modules) -> bool:
+    """fp16 loading keeps the modules named in ``keep_in_fp32_modules`` (matched as a path component, or the full name) in fp32."""
+    return any(key == param_name or (key in param_name and f"{key}." in param_name) for key in keep_in_fp32_modules or ())
 
 
 def load_checkpoint_in_model(model: nn.Module, checkpoint, device_map: Optional[dict] = None, offload_folder=None, dtype=None,
                              offload_state_dict: bool = False, offload_buffers: bool = False, keep_in_fp32_modules: list = None,
                              offload_8bit_bnb: bool = False, strict: bool = False, full_state_dict: bool = True,
-                             broadcast_from_rank0: bool = False):
-    """Stream a (possibly sharded) checkpoint into ``model`` honouring ``device_map`` (gpu / cpu / disk)."""
-    tied_params = find_tied_parameters(model)
-    if check_tied_parameters_in_config(model) and len(tied_params) == 0:
+                             broadcast_from_rank0: bool = False) -> None:
+    """Stream ``checkpoint`` (file, index or folder; sharded or not) into ``model``, one file at a time.
+
+    With a ``device_map`` every weight goes where its closest enclosing entry says: a GPU or the CPU (set in place), or ``"disk"``
+    (written to ``offload_folder`` as a memory-mappable file, the model keeps a meta tensor).  ``offload_state_dict`` parks the CPU
+    weights on disk while the other files are read, to bound host memory.  Without a map the files are loaded the ordinary way — or,
+    with ``broadcast_from_rank0`` and a sharded engine, through ``load_full_state_dict`` (rank 0 reads, the shards are scattered).
+    Tied weights are tied again at the end.
+    """
+    tied = find_tied_parameters(model)
+    if not tied and check_tied_parameters_in_config(model):
         logger.warning("The model weights are not tied. Please use the `tie_weights` method before using the `infer_auto_device` function.")
+    spills_to_disk = device_map is not None and "disk" in device_map.values()
     if device_map is not None:
-        check_tied_parameters_on_same_device(tied_params, device_map)
-    if offload_folder is None and device_map is not None and "disk" in device_map.values():
-        raise ValueError("At least one of the model submodule will be offloaded to disk, please pass along an `offload_folder`.")
-    elif offload_folder is not None and device_map is not None and "disk" in device_map.values():
+        check_tied_parameters_on_same_device(tied, device_map)
+    if spills_to_disk:
+        if offload_folder is None:
+            raise ValueError("At least one of the model submodule will be offloaded to disk, please pass along an `offload_folder`.")
         os.makedirs(offload_folder, exist_ok=True)
-    if isinstance(dtype, str):
-        dtype = dtype.replace("torch.", "")
-        dtype = getattr(torch, dtype)
+    dtype = _as_torch_dtype(dtype)
+    files = _checkpoint_files(checkpoint)
 
-    checkpoint_files = None
-    index_filename = None
-    if os.path.isfile(checkpoint):
-        if str(checkpoint).endswith(".json"):
-            index_filename = checkpoint
-        else:
-            checkpoint_files = [checkpoint]
-    elif os.path.isdir(checkpoint):
-        potential_state_bin = [f for f in os.listdir(checkpoint) if f == WEIGHTS_NAME]
-        potential_state_safetensor = [f for f in os.listdir(checkpoint) if f == SAFE_WEIGHTS_NAME]
-        if len(potential_state_bin) == 1:
-            checkpoint_files = [os.path.join(checkpoint, potential_state_bin[0])]
-        elif len(potential_state_safetensor) == 1:
-            checkpoint_files = [os.path.join(checkpoint, potential_state_safetensor[0])]
-        else:
-            potential_index = [f for f in os.listdir(checkpoint) if f.endswith(".index.json")]
-            if len(potential_index) == 0:
-                raise ValueError(f"{checkpoint} is not a folder containing a `.index.json` file or a {WEIGHTS_NAME} or a {SAFE_WEIGHTS_NAME} file")
-            elif len(potential_index) == 1:
-                index_filename = os.path.join(checkpoint, potential_index[0])
-            else:
-                raise ValueError(f"{checkpoint} containing more than one `.index.json` file, delete the irrelevant ones.")
-    else:
-        raise ValueError(f"`checkpoint` should be the path to a file containing a whole state dict, or the index of a sharded checkpoint, or a folder containing a sharded checkpoint or the whole state dict, but got {checkpoint}.")
-    if index_filename is not None:
-        checkpoint_folder = os.path.split(index_filename)[0]
-        with open(index_filename) as f:
-            index = json.loads(f.read())
-        if "weight_map" in index:
-            index = index["weight_map"]
-        checkpoint_files = sorted(list(set(index.values())))
-        checkpoint_files = [os.path.join(checkpoint_folder, f) for f in checkpoint_files]
+    expected = set(model.state_dict())
+    buffers = {name for name, _ in model.named_buffers()}
+    real_devices = {t.device for t in model.state_dict().values() if isinstance(t, torch.Tensor)} - {_META}
+    disk_index: dict = {}
+    parked_index: dict = {}
+    parked_folder = tempfile.mkdtemp() if offload_state_dict else None
+    unexpected = set()
 
-    offload_index = {}
-    if offload_state_dict:
-        import tempfile
-
-        state_dict_folder = tempfile.mkdtemp()
-        state_dict_index = {}
-    unexpected_keys = set()
-    model_keys = set(model.state_dict().keys())
-    buffer_names = [name for name, _ in model.named_buffers()]
-    model_devices = {t.device for t in model.state_dict().values() if isinstance(t, torch.Tensor)}
-    model_physical_devices = model_devices - {torch.device("meta")}
-    for checkpoint_file in checkpoint_files:
+    for file in files:
+        weights = load_state_dict(file, device_map=device_map)
+        unexpected.update(name for name in weights if name not in expected and "SCB" not in name)
         if device_map is None:
-            # plain load (optionally rank-0 broadcast into a sharded engine)
-            loaded_checkpoint = load_state_dict(checkpoint_file, device_map=None)
-            if hasattr(model, "load_full_state_dict") and broadcast_from_rank0:
-                model.load_full_state_dict(loaded_checkpoint)
+            if broadcast_from_rank0 and hasattr(model, "load_full_state_dict"):
+                model.load_full_state_dict(weights)
             else:
-                target = list(model_physical_devices)[0] if len(model_physical_devices) == 1 else None
-                if target is not None:
-                    loaded_checkpoint = {k: v.to(target) for k, v in loaded_checkpoint.items()}
-                model.load_state_dict(loaded_checkpoint, strict=strict)
-            unexpected_keys.update(set(loaded_checkpoint.keys()) - model_keys)
-            del loaded_checkpoint
-            gc.collect()
-            continue
-        loaded_checkpoint = load_state_dict(checkpoint_file, device_map=device_map)
-        for param_name, param in loaded_checkpoint.items():
-            if "SCB" in param_name:
-                continue
-            if param_name not in model_keys:
-                unexpected_keys.add(param_name)
-                if not strict:
+                if len(real_devices) == 1:
+                    (where,) = real_devices
+                    weights = {name: tensor.to(where) for name, tensor in weights.items()}
+                model.load_state_dict(weights, strict=strict)
+        else:
+            for name, tensor in weights.items():
+                if "SCB" in name or (name not in expected and not strict):
                     continue
-            module_name = param_name
-            while len(module_name) > 0 and module_name not in device_map:
-                module_name = ".".join(module_name.split(".")[:-1])
-            if module_name == "" and "" not in device_map:
-                raise ValueError(f"{param_name} doesn't have any device set.")
-            param_device = device_map[module_name]
-            new_dtype = dtype
-            if dtype is not None and torch.is_floating_point(param):
-                if keep_in_fp32_modules is not None and dtype == torch.float16:
-                    proceed = False
-                    for key in keep_in_fp32_modules:
-                        if ((key in param_name) and (key + "." in param_name)) or key == param_name:
-                            proceed = True
-                            break
-                    if proceed:
-                        new_dtype = torch.float32
-            if "weight" in param_name and param_name.replace("weight", "SCB") in loaded_checkpoint.keys():
-                fp16_statistics = loaded_checkpoint[param_name.replace("weight", "SCB")] if param.dtype == torch.int8 else None
-            else:
-                fp16_statistics = None
-            if param_device == "disk":
-                if offload_buffers or param_name not in buffer_names:
-                    if new_dtype is None:
-                        new_dtype = param.dtype
-                    set_module_tensor_to_device(model, param_name, "meta", dtype=new_dtype)
-                    offload_weight(param.to(new_dtype) if torch.is_floating_point(param) else param, param_name, offload_folder, index=offload_index)
-            elif param_device == "cpu" and offload_state_dict:
-                if new_dtype is None:
-                    new_dtype = param.dtype
-                set_module_tensor_to_device(model, param_name, "meta", dtype=new_dtype)
-                offload_weight(param, param_name, state_dict_folder, index=state_dict_index)
-            else:
-                set_module_tensor_to_device(model, param_name, param_device, value=param, dtype=new_dtype, fp16_statistics=fp16_statistics)
-        del loaded_checkpoint
+                target = _device_entry_for(name, device_map)
+                wanted = dtype
+                if dtype == torch.float16 and torch.is_floating_point(tensor) and _stays_fp32(name, keep_in_fp32_modules):
+                    wanted = torch.float32
+                statistics = None
+                if tensor.dtype == torch.int8 and "weight" in name:
+                    statistics = weights.get(name.replace("weight", "SCB"))
+                if target == "disk":
+                    if offload_buffers or name not in buffers:
+                        stored_dtype = wanted or tensor.dtype
+                        set_module_tensor_to_device(model, name, "meta", dtype=stored_dtype)
+                        offload_weight(tensor.to(stored_dtype) if torch.is_floating_point(tensor) else tensor, name, offload_folder, index=disk_index)
+                elif target == "cpu" and offload_state_dict:
+                    set_module_tensor_to_device(model, name, "meta", dtype=wanted or tensor.dtype)
+                    offload_weight(tensor, name, parked_folder, index=parked_index)
+                else:
+                    set_module_tensor_to_device(model, name, target, value=tensor, dtype=wanted, fp16_statistics=statistics)
+        del weights
         gc.collect()
-    if not strict and len(unexpected_keys) > 0:
-        logger.warning(f"Some weights of the model checkpoint at {checkpoint} were not used when initializing {model.__class__.__name__}: {unexpected_keys}. This may or may not be an issue - make sure that the checkpoint does not have unnecessary parameters, or that the model definition correctly corresponds to the checkpoint.")
-    save_offload_index(offload_index, offload_folder)
-    if offload_state_dict:
-        import shutil
 
-        load_offloaded_weights(model, state_dict_index, state_dict_folder)
-        shutil.rmtree(state_dict_folder)
-    retie_parameters(model, tied_params)
+    if unexpected and not strict:
+        logger.warning(f"Some weights of the model checkpoint at {checkpoint} were not used when initializing {type(model).__name__}: "
+                       f"{unexpected}. This may or may not be an issue - make sure that the checkpoint does not have unnecessary "
+                       "parameters, or that the model definition correctly corresponds to the checkpoint.")
+    save_offload_index(disk_index, offload_folder)
+    if parked_folder is not None:
+        load_offloaded_weights(model, parked_index, parked_folder)
+        shutil.rmtree(parked_folder)
+    retie_parameters(model, tied)
 
 
-# ------------------------------------------------------------------------------------ contexts
+# ------------------------------------------------------------------------------------------------- autocast / scaler
 def get_mixed_precision_context_manager(native_amp: bool = False, autocast_kwargs: AutocastKwargs = None):
-    """``torch.autocast`` for the active mixed-precision mode (nullcontext when none)."""
+    """The ``torch.autocast`` context for the active mixed-precision mode; a no-op context when AMP is off.  (The native bf16 engine
+    does not need it — its kernels take bf16 in and accumulate in fp32 — this is for arbitrary ``nn.Module`` s.)"""
+    if not native_amp:
+        return contextlib.nullcontext()
     from ..state import AcceleratorState
 
     state = AcceleratorState()
-    autocast_kwargs = {} if autocast_kwargs is None else autocast_kwargs.to_kwargs()
-    if not native_amp:
-        return contextlib.nullcontext()
-    device_type = "cuda" if state.device.type == "cuda" else "cpu"
-    if state.mixed_precision == "fp16":
-        return torch.autocast(device_type=device_type, dtype=torch.float16 if device_type == "cuda" else torch.bfloat16, **autocast_kwargs)
-    if state.mixed_precision in ("bf16", "fp8"):
-        return torch.autocast(device_type=device_type, dtype=torch.bfloat16, **autocast_kwargs)
-    return torch.autocast(device_type=device_type, **autocast_kwargs)
+    options = autocast_kwargs.to_kwargs() if autocast_kwargs is not None else {}
+    on_gpu = state.device.type == "cuda"
+    device_type = "cuda" if on_gpu else "cpu"
+    low_precision = {"fp16": torch.float16 if on_gpu else torch.bfloat16, "bf16": torch.bfloat16, "fp8": torch.bfloat16}
+    if state.mixed_precision in low_precision:
+        options = {"dtype": low_precision[state.mixed_precision], **options}
+    return torch.autocast(device_type=device_type, **options)
 
 
 def get_grad_scaler(distributed_type: DistributedType = None, **kwargs):
-    """A ``torch.amp.GradScaler`` for the current device type (sharded engines need no special scaler)."""
-    device = "cuda" if torch.cuda.is_available() else "cpu"
-    return torch.amp.GradScaler(device, **kwargs)
-
-
-def has_offloaded_params(module: nn.Module) -> bool:
-    from ..hooks import AlignDevicesHook
-
-    return hasattr(module, "_hf_hook") and isinstance(module._hf_hook, AlignDevicesHook) and module._hf_hook.offload
-
-
-@contextlib.contextmanager
-def align_module_device(module: nn.Module, execution_device=None):
-    """Inside the block the module's (possibly offloaded) parameters live on ``execution_device``."""
-    if has_offloaded_params(module):
-        if execution_device is not None:
-            original_device = module._hf_hook.execution_device
-            module._hf_hook.execution_device = execution_device
-        try:
-            module._hf_hook.pre_forward(module)
-            yield
-        finally:
-            module._hf_hook.post_forward(module, None)
-            if execution_device is not None:
-                module._hf_hook.execution_device = original_device
-    elif execution_device is not None:
-        devices = {name: param.device for name, param in module.named_parameters(recurse=False)}
-        try:
-            for name in devices:
-                set_module_tensor_to_device(module, name, execution_device)
-            yield
-        finally:
-            for name, device in devices.items():
-                set_module_tensor_to_device(module, name, device)
-    else:
-        yield
+    """Loss scaler for fp16.  One kind serves every engine here: sharded gradients are unscaled shard by shard and the inf check is
+    all-reduced by the engine itself."""
+    return torch.amp.GradScaler("cuda" if torch.cuda.is_available() else "cpu", **kwargs)
