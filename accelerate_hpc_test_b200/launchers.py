@@ -1,107 +1,102 @@
-"""In-process launchers: ``notebook_launcher`` and ``debug_launcher``.
+"""Launching a distributed job from inside a running Python process.
 
-Parity with reference src/accelerate/launchers.py:41-309.  ``notebook_launcher`` forks ``num_processes``
-workers through torchelastic (so ``max_restarts`` / ``monitor_interval`` / rendezvous options work as
-with ``torchrun``); ``debug_launcher`` forks a CPU-only gloo job that rendezvous through a temp file —
-the "cluster on a laptop" every distributed unit test of this repo runs on.
+``notebook_launcher`` is for notebooks: it forks one worker per GPU out of the current interpreter through torchelastic, so restarts,
+monitoring and rendezvous options behave as with ``torchrun``.  Forking only works while CUDA has not been touched, so the launcher
+first checks everything that would make the children die on their first CUDA call (``_preflight``).  ``debug_launcher`` forks a CPU-only
+gloo job that rendezvous through a temporary file — the "cluster on a laptop" all multi-process unit tests of this repository run on.
+Behavioural parity: reference ``src/accelerate/launchers.py:41-309`` (TPU branches excluded).
 """
 
 from __future__ import annotations
 
 import os
-import sys
 import tempfile
 
 import torch
 
-from .state import AcceleratorState, PartialState
+from .state import AcceleratorState
 from .utils.environment import are_libraries_initialized, patch_environment
 from .utils.launch import PrepareForLaunch
 from .utils.other import get_free_port, is_port_in_use
+
+_CUDA_FORK_ERROR = "Cannot re-initialize CUDA in forked subprocess"
+
+
+def _preflight() -> None:
+    """Refuse to fork when the parent already holds state the children cannot share."""
+    if AcceleratorState._shared_state:
+        raise ValueError("To launch a multi-GPU training from your notebook, the `Accelerator` should only be initialized inside your "
+                         "training function. Restart your notebook and make sure no cells initializes an `Accelerator`.")
+    if torch.cuda.is_available() and torch.cuda.is_initialized():
+        raise ValueError("To launch a multi-GPU training from your notebook, you need to avoid running any instruction using `torch.cuda` "
+                         "in any cell. Restart your notebook and make sure no cells use any CUDA function.")
+    touched = are_libraries_initialized("bitsandbytes")
+    if touched:
+        raise RuntimeError("Could not start distributed process. Libraries known to initialize CUDA upon import have been imported "
+                           f"already: {touched}. Please keep these imports inside your training function.")
+
+
+def _resolve_port(use_port) -> str:
+    if int(use_port) == 0:
+        return str(get_free_port())
+    if is_port_in_use(int(use_port)):
+        raise ConnectionError(f"Port {use_port} is already in use; pass another `use_port` (or 0 for a free one).")
+    return str(use_port)
 
 
 def notebook_launcher(function, args=(), num_processes=None, mixed_precision="no", use_port="29500", master_addr="127.0.0.1",
                       node_rank=0, num_nodes=1, rdzv_backend="static", rdzv_endpoint="", rdzv_conf=None, rdzv_id="none",
                       max_restarts=0, monitor_interval=0.1, log_line_prefix_template=None):
-    """Run ``function(*args)`` on ``num_processes`` GPUs (forked from the current process), or in-process
-    when only one device is requested/available."""
-    in_colab = "google.colab" in sys.modules
-    in_kaggle = "KAGGLE_KERNEL_RUN_TYPE" in os.environ
+    """Run ``function(*args)`` on ``num_processes`` devices of this machine (default: every visible GPU).  With one process the
+    function simply runs here; with more, workers are forked and the call returns when all of them have finished."""
+    gpus_here = torch.cuda.is_available()
     if num_processes is None:
-        num_processes = torch.cuda.device_count() if torch.cuda.is_available() else 1
-    if num_processes is not None and int(num_processes) > 1:
-        from torch.distributed.launcher.api import LaunchConfig, elastic_launch
-        from torch.multiprocessing.spawn import ProcessRaisedException
-
-        if len(AcceleratorState._shared_state) > 0:
-            raise ValueError(
-                "To launch a multi-GPU training from your notebook, the `Accelerator` should only be initialized "
-                "inside your training function. Restart your notebook and make sure no cells initializes an `Accelerator`."
-            )
-        if torch.cuda.is_available() and torch.cuda.is_initialized():
-            raise ValueError(
-                "To launch a multi-GPU training from your notebook, you need to avoid running any instruction "
-                "using `torch.cuda` in any cell. Restart your notebook and make sure no cells use any CUDA function."
-            )
-        problematic_imports = are_libraries_initialized("bitsandbytes")
-        if len(problematic_imports) > 0:
-            raise RuntimeError(
-                "Could not start distributed process. Libraries known to initialize CUDA upon import have been imported "
-                f"already: {problematic_imports}. Please keep these imports inside your training function."
-            )
-        if use_port == "0" or int(use_port) == 0:
-            use_port = str(get_free_port())
-        elif is_port_in_use(int(use_port)):
-            raise ConnectionError(f"Port {use_port} is already in use; pass another `use_port` (or 0 for a free one).")
-        patched_env = dict(nproc=num_processes, node_rank=node_rank, world_size=num_nodes * num_processes,
-                           master_addr=master_addr, master_port=use_port, mixed_precision=mixed_precision)
-        with patch_environment(**patched_env):
-            os.environ["ACCELERATE_MIXED_PRECISION"] = str(mixed_precision)
-            use_cpu = not torch.cuda.is_available()
-            if use_cpu:
-                os.environ["ACCELERATE_USE_CPU"] = "yes"
-            launcher = PrepareForLaunch(function, distributed_type="MULTI_CPU" if use_cpu else "MULTI_GPU")
-            print(f"Launching training on {num_processes} {'CPUs' if use_cpu else 'GPUs'}.")
-            try:
-                if rdzv_conf is None:
-                    rdzv_conf = {}
-                if rdzv_backend == "static":
-                    rdzv_conf["rank"] = node_rank
-                    if not rdzv_endpoint:
-                        rdzv_endpoint = f"{master_addr}:{use_port}"
-                launch_config_kwargs = dict(
-                    min_nodes=num_nodes, max_nodes=num_nodes, nproc_per_node=num_processes, run_id=rdzv_id, rdzv_endpoint=rdzv_endpoint,
-                    rdzv_backend=rdzv_backend, rdzv_configs=rdzv_conf, max_restarts=max_restarts, monitor_interval=monitor_interval,
-                    start_method="fork",
-                )
-                if log_line_prefix_template is not None:
-                    launch_config_kwargs["log_line_prefix_template"] = log_line_prefix_template
-                elastic_launch(config=LaunchConfig(**launch_config_kwargs), entrypoint=function)(*args)
-            except ProcessRaisedException as e:
-                if "Cannot re-initialize CUDA in forked subprocess" in e.args[0]:
-                    raise RuntimeError(
-                        "CUDA has been initialized before the `notebook_launcher` could create a forked subprocess. "
-                        "This likely stems from an outside import causing issues once the `notebook_launcher()` is called. "
-                        "Please review your imports and test them when running the `notebook_launcher()` to identify "
-                        "which one is problematic and causing CUDA to be initialized."
-                    ) from e
-                raise RuntimeError(f"An issue was found when launching the training: {e}") from e
-            finally:
-                os.environ.pop("ACCELERATE_USE_CPU", None) if use_cpu else None
-    else:
-        if torch.cuda.is_available():
-            print("Launching training on one GPU.")
-        else:
-            print("Launching training on CPU.")
+        num_processes = torch.cuda.device_count() if gpus_here else 1
+    num_processes = int(num_processes)
+    if num_processes <= 1:
+        print("Launching training on one GPU." if gpus_here else "Launching training on CPU.")
         function(*args)
+        return
+
+    from torch.distributed.launcher.api import LaunchConfig, elastic_launch
+    from torch.multiprocessing.spawn import ProcessRaisedException
+
+    _preflight()
+    port = _resolve_port(use_port)
+    rdzv_conf = dict(rdzv_conf or {})
+    if rdzv_backend == "static":
+        rdzv_conf["rank"] = node_rank
+        rdzv_endpoint = rdzv_endpoint or f"{master_addr}:{port}"
+    config = dict(min_nodes=num_nodes, max_nodes=num_nodes, nproc_per_node=num_processes, run_id=rdzv_id, rdzv_endpoint=rdzv_endpoint,
+                  rdzv_backend=rdzv_backend, rdzv_configs=rdzv_conf, max_restarts=max_restarts, monitor_interval=monitor_interval,
+                  start_method="fork")
+    if log_line_prefix_template is not None:
+        config["log_line_prefix_template"] = log_line_prefix_template
+
+    worker_env = dict(nproc=num_processes, node_rank=node_rank, world_size=num_nodes * num_processes, master_addr=master_addr,
+                      master_port=port, mixed_precision=mixed_precision, accelerate_mixed_precision=mixed_precision)
+    if not gpus_here:
+        worker_env["accelerate_use_cpu"] = "yes"
+    with patch_environment(**worker_env):
+        # validates the mixed-precision / device choice in the parent, before anything is forked
+        PrepareForLaunch(function, distributed_type="MULTI_GPU" if gpus_here else "MULTI_CPU")
+        print(f"Launching training on {num_processes} {'GPUs' if gpus_here else 'CPUs'}.")
+        try:
+            elastic_launch(config=LaunchConfig(**config), entrypoint=function)(*args)
+        except ProcessRaisedException as failure:
+            if _CUDA_FORK_ERROR in failure.args[0]:
+                raise RuntimeError("CUDA has been initialized before the `notebook_launcher` could create a forked subprocess. This "
+                                   "likely stems from an outside import causing issues once the `notebook_launcher()` is called. Please "
+                                   "review your imports and test them when running the `notebook_launcher()` to identify which one is "
+                                   "problematic and causing CUDA to be initialized.") from failure
+            raise RuntimeError(f"An issue was found when launching the training: {failure}") from failure
 
 
 def debug_launcher(function, args=(), num_processes=2):
-    """Run ``function(*args)`` on ``num_processes`` CPU processes over gloo with a file rendezvous."""
+    """Run ``function(*args)`` on ``num_processes`` forked CPU processes that form a gloo group (file rendezvous, nothing on the network)."""
     from torch.multiprocessing import start_processes
 
-    with tempfile.NamedTemporaryFile() as tmp_file:
+    with tempfile.NamedTemporaryFile() as rendezvous:
         with patch_environment(world_size=num_processes, master_addr="127.0.0.1", master_port="29500", accelerate_mixed_precision="no",
-                               accelerate_debug_rdv_file=tmp_file.name, accelerate_use_cpu="yes"):
-            launcher = PrepareForLaunch(function, debug=True)
-            start_processes(launcher, args=args, nprocs=num_processes, start_method="fork")
+                               accelerate_debug_rdv_file=rendezvous.name, accelerate_use_cpu="yes"):
+            start_processes(PrepareForLaunch(function, debug=True), args=args, nprocs=num_processes, start_method="fork")

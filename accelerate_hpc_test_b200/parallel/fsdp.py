@@ -355,12 +355,16 @@ class B200ShardedModule(nn.Module):
             self.rs_world = self.ws.world
             self.rs_rank = self.ws.rank
             self._nvls_rs = self.ws.has_multicast and os.environ.get("ACCELERATE_B200_FSDP_NVLS_RS", "1") != "0"
+            # a shard group of one (pure tensor / context parallelism, dp_shard=1): the shard IS the parameter — nothing to gather,
+            # nothing to reduce; the engine only keeps the fp32 master / moments and updates the bf16 copy in place
+            self._solo = self.world == 1 and self.rs_world == 1 and os.environ.get("ACCELERATE_B200_FSDP_SOLO", "1") != "0"
         else:
             self.ws = None
             self.comm_stream = None
             self.rs_stream = None
             self._ag_peers = None
             self._nvls_rs = False
+            self._solo = False
             self.rs_world = self.world * (torch.distributed.get_world_size(self.replicate_group) if self.replicate_group is not None else 1)
         meta_init = any(p.device.type == "meta" for u in self._units for p in u.params)
         src = torch.distributed.get_global_rank(self.group, 0)
@@ -458,6 +462,9 @@ class B200ShardedModule(nn.Module):
         the next GEMMs when ``carry``), the rest is pulled on the comm stream."""
         if u.full is not None:
             return
+        if self._solo:
+            u.full, u.full_idx, u.ag_event = u.shard, None, None  # same layout when world == 1: the parameters view the shard
+            return
         idx = u.fpool.take()
         u.full_idx = idx
         u.full = u.fpool.bufs[idx][1][: u.padded]
@@ -550,12 +557,13 @@ class B200ShardedModule(nn.Module):
             if s.job is not None:
                 s.job.pending = False
         ev = None
-        if self._poison:
-            u.full.fill_(float("nan"))  # debug: anything that still reads the released buffer turns into NaN
-        if self.use_symm:
-            ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream(self.device))
-        u.fpool.give(u.full_idx, ev)
+        if u.full_idx is not None:
+            if self._poison:
+                u.full.fill_(float("nan"))  # debug: anything that still reads the released buffer turns into NaN
+            if self.use_symm:
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(self.device))
+            u.fpool.give(u.full_idx, ev)
         u.full = None
         u.ag_event = None
         u.unsharded = False
@@ -755,6 +763,17 @@ class B200ShardedModule(nn.Module):
             if not fused and u.grad_shard is None:
                 u.grad_shard = torch.empty(u.shard_numel, dtype=torch.float32, device=self.device)
             h = self._adam_hyper() if fused else dict(lr=0.0, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0)
+            if self._solo:
+                # nobody to reduce with: the flat gradient buffer already is the gradient shard (same layout at world 1)
+                with torch.cuda.stream(self.rs_stream):
+                    if fused:
+                        F.adamw_flat_(u.master, u.exp_avg, u.exp_avg_sq, u.grad, u.shard, step=self.step_count + 1, **h)
+                    else:
+                        F.scale_cast(u.grad, u.grad_shard, 1.0)
+                    u.rs_event = torch.cuda.Event()
+                    u.rs_event.record(self.rs_stream)
+                u.updated_in_backward = fused
+                return
             with torch.cuda.stream(self.rs_stream):
                 for i in range(0, len(u.segs), SEGS_PER_LAUNCH):
                     part = u.segs[i : i + SEGS_PER_LAUNCH]

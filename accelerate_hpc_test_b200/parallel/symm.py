@@ -74,7 +74,8 @@ class SymmetricWorkspace:
         self._opened = []
         self._symm_tensor = None
         self.backend = "ipc"
-        if os.environ.get("ACCELERATE_B200_SYMM_BACKEND", "auto") != "ipc" and self._try_vmm_multicast(group, device):
+        # a group of one has no peers to map and no switch to reduce in: plain device memory through the IPC path
+        if os.environ.get("ACCELERATE_B200_SYMM_BACKEND", "auto") != "ipc" and self.world > 1 and self._try_vmm_multicast(group, device):
             self.backend = "vmm"
         else:
             self._alloc_ipc(group, device, lib)

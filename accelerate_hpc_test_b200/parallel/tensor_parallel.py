@@ -51,6 +51,9 @@ class TPComm:
         self.fused = fused and self.cuda
         self.hidden = hidden
         self.max_tokens = max_tokens
+        # ACCELERATE_B200_TP_KEEP_GATHERED=0 trades the per-layer copy of the gathered input (tokens x hidden x 2 bytes per
+        # column-parallel layer) for a second gather in backward
+        self.keep_gathered = os.environ.get("ACCELERATE_B200_TP_KEEP_GATHERED", "1") != "0"
         if self.cuda:
             from .symm import SymmetricWorkspace
 
@@ -65,6 +68,12 @@ class TPComm:
             self.ch_a2a = (self.ws.new_channel(), self.ws.new_channel())
             self.flip_ag = 0
             self.flip_rs = 0
+
+    def private_copy(self, gathered: torch.Tensor) -> torch.Tensor:
+        """A copy of gathered rows that outlives the rotating gather buffer (a no-op when nothing was gathered into one)."""
+        if self.world == 1 or not self.cuda:
+            return gathered
+        return gathered.clone()
 
     # ------------------------------------------------------------------ un-fused primitives
     def all_gather_rows(self, x: torch.Tensor) -> torch.Tensor:
@@ -172,8 +181,11 @@ class _ColumnParallelFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, comm: TPComm):
-        y, _ = comm.ag_gemm(x, weight)
-        ctx.save_for_backward(x, weight)
+        y, x_full = comm.ag_gemm(x, weight)
+        # the gathered activations sit in a rotating symmetric buffer: a private copy (one D2D pass) is cheaper than the
+        # stage + barrier + peer pulls of gathering them again for the weight gradient
+        ctx.kept_full = comm.keep_gathered and weight.requires_grad
+        ctx.save_for_backward(comm.private_copy(x_full) if ctx.kept_full else x, weight)
         ctx.comm = comm
         return y
 
@@ -185,7 +197,7 @@ class _ColumnParallelFn(torch.autograd.Function):
         dx = comm.gemm_rs(dy, weight, b_mn_major=True) if ctx.needs_input_grad[0] else None
         dw = None
         if ctx.needs_input_grad[1]:
-            x_full = comm.all_gather_rows(x)
+            x_full = x if ctx.kept_full else comm.all_gather_rows(x)
             dw = F.deliver_weight_grad(weight, lambda out, acc: F.gemm(dy, x_full, a_mn_major=True, b_mn_major=True, out=out, accumulate=acc))
         return dx, dw, None
 

@@ -32,11 +32,30 @@ def record(row, name, ours_ms, baseline, baseline_ms, flops=0.0, link_bytes=0.0,
     roof_ms = max(flops / (PEAK_TFLOPS * 1e9), link_bytes / (NVLINK_GBS * 1e6), hbm_bytes / (HBM_GBS * 1e6))
     RESULTS.append(dict(row=row, op=name, ours_ms=round(ours_ms, 4), baseline=baseline, baseline_ms=round(baseline_ms, 4),
                         speedup_vs_baseline=round(baseline_ms / ours_ms, 3), roofline_ms=round(roof_ms, 4),
-                        roofline_fraction=round(roof_ms / ours_ms, 3)))
+                        roofline_fraction=round(roof_ms / ours_ms, 3), clocks=getattr(ours_ms, "clocks", None),
+                        baseline_clocks=getattr(baseline_ms, "clocks", None)))
+
+
+class Ms(float):
+    """Milliseconds that remember the clocks / throttle reasons sampled while they were measured (this rank's GPU)."""
+
+    def __new__(cls, value, clocks=None):
+        self = super().__new__(cls, value)
+        self.clocks = clocks
+        return self
+
+
+_PROBE = None
 
 
 def timed(fn, iters=10, warm=3):
-    """ms per call: CUDA events on the launching stream, max over ranks."""
+    """ms per call: CUDA events on the launching stream, max over ranks; NVML clock samples while the calls are in flight."""
+    global _PROBE
+    if _PROBE is None:
+        from accelerate_hpc_test_b200.utils.diagnostics import ClockProbe
+
+        _PROBE = ClockProbe()
+    _PROBE.reset()
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
@@ -45,11 +64,12 @@ def timed(fn, iters=10, warm=3):
     s.record()
     for _ in range(iters):
         fn()
+        _PROBE.sample()
     e.record()
     torch.cuda.synchronize()
     t = torch.tensor([s.elapsed_time(e) / iters], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return t.item()
+    return Ms(t.item(), _PROBE.summary())
 
 
 def rel(a, b):
@@ -155,27 +175,23 @@ def check_collectives(ws, dev, rank, world):
     assert torch.equal(tbuf, tref), "allreduce_tma"
     log("allreduce_tma ok")
     chs2 = (ws.new_channel(), ws.new_channel(), ws.new_channel())
-    for name, fn in (("ours_allreduce", lambda: ws.allreduce_(off, n, torch.bfloat16, 1.0 / world, ch_a, ch_d, ctas=64)),
-                     ("ours_allreduce_tma", lambda: ws.allreduce_tma_(off, n, 1.0 / world, chs2)),
-                     ("nccl_allreduce", lambda: dist.all_reduce(nccl_buf))):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        dist.barrier()
-        s, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        for _ in range(5):
-            fn()
-        e2.record()
-        torch.cuda.synchronize()
-        t = torch.tensor([s.elapsed_time(e2) / 5], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        busbw = 2 * (world - 1) / world * n * 2 / (t.item() * 1e-3) / 1e9
-        res[name] = (t.item(), busbw)
-        log(f"{name}: {t.item():.3f} ms, bus bw {busbw:.1f} GB/s ({n * 2 / 2**20:.0f} MiB)")
+    candidates = [("ours_allreduce", lambda: ws.allreduce_(off, n, torch.bfloat16, 1.0 / world, ch_a, ch_d, ctas=64)),
+                  ("ours_allreduce_tma", lambda: ws.allreduce_tma_(off, n, 1.0 / world, chs2)),
+                  ("nccl_allreduce", lambda: dist.all_reduce(nccl_buf))]
+    if ws.has_multicast:
+        ch_n = (ws.new_channel(), ws.new_channel())
+        candidates.insert(2, ("ours_allreduce_nvls", lambda: ws.allreduce_nvls_(off, n, 1.0 / world, ch_n[0], ch_n[1])))
+    for name, fn in candidates:
+        t = timed(fn, iters=5)
+        busbw = 2 * (world - 1) / world * n * 2 / (t * 1e-3) / 1e9
+        res[name] = (t, busbw)
+        log(f"{name}: {t:.3f} ms, bus bw {busbw:.1f} GB/s ({n * 2 / 2**20:.0f} MiB), clocks {t.clocks}")
     record("W7", "all-reduce 512 MiB bf16, scale fused (TMA: reduce own slice + pull the rest)", res["ours_allreduce_tma"][0], "ncclAllReduce",
            res["nccl_allreduce"][0],
            link_bytes=2 * (world - 1) / world * n * 2)
+    if "ours_allreduce_nvls" in res:
+        record("W7", "all-reduce 512 MiB bf16, scale fused (NVLS: multimem.ld_reduce own slice, multimem.st to all)", res["ours_allreduce_nvls"][0],
+               "ncclAllReduce", res["nccl_allreduce"][0], link_bytes=2 * (world - 1) / world * n * 2)
     # all-gather of one Llama-3-8B decoder layer (436 MB gathered) vs NCCL
     layer_elems = 218_112_000 // (world * 8) * (world * 8)
     sh = layer_elems // world
@@ -187,34 +203,12 @@ def check_collectives(ws, dev, rank, world):
     dist.barrier()
     for ctas in (16, 32, 64, 148):
         for name, fn in ((f"ours_allgather_ctas{ctas}", lambda: ws.allgather_pull(soff, sh * 2, full, ctas=ctas)),):
-            for _ in range(3):
-                fn()
-            torch.cuda.synchronize()
-            dist.barrier()
-            s, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            s.record()
-            for _ in range(5):
-                fn()
-            e2.record()
-            torch.cuda.synchronize()
-            t = torch.tensor([s.elapsed_time(e2) / 5], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            log(f"{name}: {t.item():.3f} ms, ingress {(world - 1) / world * layer_elems * 2 / (t.item() * 1e-3) / 1e9:.1f} GB/s")
-    for _ in range(3):
-        dist.all_gather_into_tensor(full2, shard)
-    torch.cuda.synchronize()
-    dist.barrier()
-    s, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    s.record()
-    for _ in range(5):
-        dist.all_gather_into_tensor(full2, shard)
-    e2.record()
-    torch.cuda.synchronize()
-    t = torch.tensor([s.elapsed_time(e2) / 5], device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    log(f"nccl_allgather: {t.item():.3f} ms, ingress {(world - 1) / world * layer_elems * 2 / (t.item() * 1e-3) / 1e9:.1f} GB/s")
+            t = timed(fn, iters=5)
+            log(f"{name}: {t:.3f} ms, ingress {(world - 1) / world * layer_elems * 2 / (t * 1e-3) / 1e9:.1f} GB/s")
+    t_nccl_ag = timed(lambda: dist.all_gather_into_tensor(full2, shard), iters=5)
+    log(f"nccl_allgather: {t_nccl_ag:.3f} ms, ingress {(world - 1) / world * layer_elems * 2 / (t_nccl_ag * 1e-3) / 1e9:.1f} GB/s")
     t_ag = timed(lambda: ws.allgather_pull(soff, sh * 2, full, ctas=148), iters=5)
-    record("W9", "all-gather of one Llama-3-8B layer (436 MB, TMA bulk pull, 148 CTAs)", t_ag, "ncclAllGather", t.item(),
+    record("W9", "all-gather of one Llama-3-8B layer (436 MB, TMA bulk pull, 148 CTAs)", t_ag, "ncclAllGather", t_nccl_ag,
            link_bytes=(world - 1) / world * layer_elems * 2)
     # ---- W8: reduce-scatter + AdamW on one layer's gradients vs NCCL reduce-scatter + our flat AdamW kernel
     nsh = sh
@@ -396,20 +390,8 @@ def check_tp(dev, rank, world):
     tms = {}
     for name, fn in (("fused_ag_gemm", lambda: big.ag_gemm(x, w)), ("nccl_ag_then_cublas", nccl_ag_gemm), ("gemm_only", lambda: F.gemm(xf, w)),
                      ("fused_gemm_rs", lambda: big.gemm_rs(xr, wr)), ("cublas_then_nccl_rs", nccl_gemm_rs), ("gemm_only_rs_shape", lambda: F.gemm(xr, wr))):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        dist.barrier()
-        s, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        for _ in range(10):
-            fn()
-        e2.record()
-        torch.cuda.synchronize()
-        tt = torch.tensor([s.elapsed_time(e2) / 10], device=dev)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        log(f"tp {name}: {tt.item():.3f} ms")
-        tms[name] = tt.item()
+        tms[name] = timed(fn, iters=10)
+        log(f"tp {name}: {tms[name]:.3f} ms")
     record("W10", f"all-gather -> GEMM (x [{T // world}x{H}] per rank, W [{28672 // world}x{H}])", tms["fused_ag_gemm"],
            "ncclAllGather + cuBLASLt", tms["nccl_ag_then_cublas"], flops=2.0 * T * (28672 // world) * H,
            link_bytes=(world - 1) / world * T * H * 2)
@@ -462,19 +444,8 @@ def check_seq(dev, rank, world):
     xb = torch.randn(Bq * Sl, sum(wd), device=dev).to(torch.bfloat16)
     for name, fn in (("exchange_kernel", lambda: comm.exchange(xb, 0, Bq, Sl, wd)),
                      ("nccl_all_to_all+permutes", lambda: comm._exchange_reference(xb, 0, Bq, Sl, wd))):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        dist.barrier()
-        s, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s.record()
-        for _ in range(10):
-            fn()
-        e2.record()
-        torch.cuda.synchronize()
-        tt = torch.tensor([s.elapsed_time(e2) / 10], device=dev)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        log(f"ulysses {name}: {tt.item():.3f} ms ({xb.numel() * 2 * (world - 1) / world / tt.item() / 1e6:.0f} GB/s ingress)")
+        tt = timed(fn, iters=10)
+        log(f"ulysses {name}: {tt:.3f} ms ({xb.numel() * 2 * (world - 1) / world / tt / 1e6:.0f} GB/s ingress), clocks {tt.clocks}")
     log("ulysses exchange ok")
     # W12 / W13: QKV projection fused with the sequence->head all-to-all (also the dgrad of the output projection)
     from accelerate_hpc_test_b200.ops import functional as F

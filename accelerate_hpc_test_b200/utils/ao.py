@@ -1,36 +1,41 @@
-"""torchao float8 adapter (reference src/accelerate/utils/ao.py:32-143); optional library back-end."""
+"""Adapter for the optional ``torchao`` float8 training back-end (``ACCELERATE_FP8_BACKEND=AO``).
 
-from functools import partial
+The native fp8 path of this framework is the MXFP8 block-scaled tcgen05 GEMM in ``parallel/precision.py``; this module is for users who
+ask for torchao explicitly.  torchao swaps ``nn.Linear`` for ``Float8Linear``; by convention the first and the last linear of a network
+(input embedding projection / output head) stay in high precision, and so does any layer whose dimensions the fp8 GEMMs cannot tile.
+Behavioural parity: reference ``src/accelerate/utils/ao.py:32-143``.
+"""
+
+from __future__ import annotations
+
 from typing import Callable, Optional
 
 import torch
 
 from .imports import is_torchao_available
 
+_FP8_TILE = 16  # fp8 tensor-core GEMMs want every matrix dimension to be a multiple of 16
+
 
 def find_first_last_linear_layers(model: torch.nn.Module):
-    """Names of the first and last ``nn.Linear`` in definition order."""
-    first_linear, last_linear = None, None
-    for name, module in model.named_modules():
-        if isinstance(module, torch.nn.Linear):
-            if first_linear is None:
-                first_linear = name
-            last_linear = name
-    return first_linear, last_linear
+    """``(first, last)`` qualified names of the ``nn.Linear`` layers in registration order (both None when there is none)."""
+    linears = [name for name, module in model.named_modules() if isinstance(module, torch.nn.Linear)]
+    return (linears[0], linears[-1]) if linears else (None, None)
 
 
 def filter_linear_layers(module, fqn: str, layers_to_filter: list) -> bool:
-    """True for linears that can run in float8: dims multiples of 16 and not in ``layers_to_filter``."""
-    if isinstance(module, torch.nn.Linear):
-        if module.in_features % 16 != 0 or module.out_features % 16 != 0:
-            return False
+    """Should ``module`` (named ``fqn``) be converted?  No for the excluded names and for linears with a dimension off the fp8 tile."""
     if fqn in layers_to_filter:
         return False
+    if isinstance(module, torch.nn.Linear):
+        return module.in_features % _FP8_TILE == 0 and module.out_features % _FP8_TILE == 0
     return True
 
 
 def filter_first_and_last_linear_layers(module, fqn: str) -> bool:
-    raise NotImplementedError("use `functools.partial(filter_linear_layers, layers_to_filter=[first, last])`")
+    """Marker for "the default filter": the first and last linear are only known once a model is given, so ``convert_model_to_fp8_ao``
+    resolves this name to ``filter_linear_layers`` bound to that model's first and last linear."""
+    raise NotImplementedError("resolved by `convert_model_to_fp8_ao`; call `filter_linear_layers(module, fqn, [first, last])` directly")
 
 
 def has_ao_layers(model: torch.nn.Module) -> bool:
@@ -38,16 +43,20 @@ def has_ao_layers(model: torch.nn.Module) -> bool:
         return False
     from torchao.float8.float8_linear import Float8Linear
 
-    return any(isinstance(m, Float8Linear) for m in model.modules())
+    return any(isinstance(module, Float8Linear) for module in model.modules())
 
 
 def convert_model_to_fp8_ao(model: torch.nn.Module, config=None, module_filter_func: Optional[Callable] = filter_first_and_last_linear_layers):
-    """``torchao.float8.convert_to_float8_training`` skipping the first/last linear by default."""
+    """In-place ``torchao.float8.convert_to_float8_training``.  ``module_filter_func(module, fqn) -> bool`` picks the layers; the
+    default keeps the first and the last linear (and badly shaped ones) in high precision."""
     if not is_torchao_available():
         raise ImportError("torchao is not installed; the native MXFP8 path (`ACCELERATE_FP8_BACKEND=NATIVE`) needs no extra package.")
     from torchao.float8 import convert_to_float8_training
 
-    first_linear, last_linear = find_first_last_linear_layers(model)
-    if module_filter_func is None or module_filter_func is filter_first_and_last_linear_layers:
-        module_filter_func = partial(filter_linear_layers, layers_to_filter=[first_linear, last_linear])
+    if module_filter_func in (None, filter_first_and_last_linear_layers):
+        keep_precise = list(find_first_last_linear_layers(model))
+
+        def module_filter_func(module, fqn):
+            return filter_linear_layers(module, fqn, keep_precise)
+
     convert_to_float8_training(model, module_filter_fn=module_filter_func, config=config)

@@ -304,3 +304,71 @@ class ClockRecord:
 
 def sample_clocks(gpu_index: Optional[int] = None) -> ClockRecord:
     return ClockRecord(gpu_index)
+
+
+class ClockProbe:
+    """Instantaneous SM clock / power / throttle-reason samples through NVML, for timed regions much shorter than the 200 ms
+    period ``ClockRecord`` polls at (micro-benchmarks of single kernels).  ``sample()`` costs a few microseconds of host time and
+    nothing on the device: call it while the measured work is in flight (after the closing event has been recorded, before the
+    synchronize), then put ``summary()`` next to the number::
+
+        probe = ClockProbe()
+        for _ in range(iters):
+            start.record(); fn(); stop.record(); probe.sample(); torch.cuda.synchronize()
+        row["clocks"] = probe.summary()
+    """
+
+    _REASON_BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+
+    def __init__(self, gpu_index: Optional[int] = None):
+        self._nvml = None
+        self._handle = None
+        self._samples: list = []
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            idx = gpu_index
+            if idx is None:
+                idx = torch.cuda.current_device() if _cuda() else 0
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+                if vis:
+                    try:
+                        idx = int(vis.split(",")[idx])
+                    except (ValueError, IndexError):
+                        pass
+            self._handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self._max = pynvml.nvmlDeviceGetMaxClockInfo(self._handle, pynvml.NVML_CLOCK_SM)
+            self._nvml = pynvml
+        except Exception:  # noqa: BLE001 - no NVML on this host
+            self._nvml = None
+
+    def sample(self) -> None:
+        if self._nvml is None:
+            return
+        n = self._nvml
+        try:
+            mhz = n.nvmlDeviceGetClockInfo(self._handle, n.NVML_CLOCK_SM)
+            watts = n.nvmlDeviceGetPowerUsage(self._handle) / 1000.0
+            try:
+                mask = n.nvmlDeviceGetCurrentClocksEventReasons(self._handle)
+            except AttributeError:
+                mask = n.nvmlDeviceGetCurrentClocksThrottleReasons(self._handle)
+            self._samples.append((mhz, watts, mask))
+        except Exception:  # noqa: BLE001
+            pass
+
+    def reset(self) -> None:
+        self._samples = []
+
+    def summary(self) -> dict:
+        import statistics
+
+        if self._nvml is None or not self._samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"], "samples": 0}
+        mask = 0
+        for _, _, m in self._samples:
+            mask |= m
+        return {"sm_mhz": statistics.median(s[0] for s in self._samples), "sm_max_mhz": self._max,
+                "power_w_max": round(max(s[1] for s in self._samples), 1), "samples": len(self._samples),
+                "reasons": sorted(name for name, bit in self._REASON_BITS.items() if mask & bit)}

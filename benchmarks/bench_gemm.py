@@ -9,7 +9,28 @@ import torch
 from accelerate_hpc_test_b200.ops import functional as F
 
 
+class Ms(float):
+    """Milliseconds that remember the clock record of the run they came from."""
+
+    def __new__(cls, value, clocks=None):
+        self = super().__new__(cls, value)
+        self.clocks = clocks
+        return self
+
+
+_PROBE = None
+LAST_CLOCKS = None  # clocks / throttle reasons sampled while the kernels of the last timeit() call were in flight
+
+
 def timeit(fn, iters=10, warm=3):
+    """Median ms over ``iters`` calls: CUDA events on the launching stream, L2 flushed (256 MiB memset) before every call, NVML
+    clock samples taken while each call is in flight (``LAST_CLOCKS``)."""
+    global _PROBE, LAST_CLOCKS
+    from accelerate_hpc_test_b200.utils.diagnostics import ClockProbe
+
+    if _PROBE is None:
+        _PROBE = ClockProbe()
+    _PROBE.reset()
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
     for _ in range(warm):
         fn()
@@ -21,10 +42,12 @@ def timeit(fn, iters=10, warm=3):
         s.record()
         fn()
         e.record()
+        _PROBE.sample()
         torch.cuda.synchronize()
         ts.append(s.elapsed_time(e))
     ts.sort()
-    return ts[len(ts) // 2]
+    LAST_CLOCKS = _PROBE.summary()
+    return Ms(ts[len(ts) // 2], LAST_CLOCKS)
 
 
 def main():
@@ -41,9 +64,10 @@ def main():
             ("dgrad", lambda: F.gemm(dy, w, b_mn_major=True), lambda: dy @ w),
             ("wgrad", lambda: F.gemm(dy, x, a_mn_major=True, b_mn_major=True), lambda: dy.t() @ x),
         ]:
-            t_o, t_r = timeit(ours), timeit(ref)
-            rows.append(dict(shape=name, kind=kind, M=M, N=N, K=K, ours_ms=t_o, cublas_ms=t_r,
-                             ours_tflops=fl / t_o / 1e9, cublas_tflops=fl / t_r / 1e9))
+            t_r = timeit(ref)
+            t_o = timeit(ours)
+            rows.append(dict(shape=name, kind=kind, M=M, N=N, K=K, ours_ms=float(t_o), cublas_ms=float(t_r),
+                             ours_tflops=fl / t_o / 1e9, cublas_tflops=fl / t_r / 1e9, clocks=t_o.clocks, cublas_clocks=t_r.clocks))
             print(json.dumps(rows[-1]), flush=True)
     os.makedirs("gpurun_out", exist_ok=True)
     json.dump(rows, open("gpurun_out/bench_gemm.json", "w"), indent=1)

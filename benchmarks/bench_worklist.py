@@ -31,7 +31,7 @@ def add(row, name, ours_ms, base_ms, base_name, work, unit, peak):
     achieved = work / ours_ms / 1e9  # TFLOP/s or TB/s
     rows.append(dict(row=row, op=name, ours_ms=round(ours_ms, 4), baseline=base_name, baseline_ms=round(base_ms, 4),
                      speedup_vs_baseline=round(base_ms / ours_ms, 3), achieved=round(achieved, 2), unit=unit,
-                     roofline_fraction=round(achieved / peak, 3)))
+                     roofline_fraction=round(achieved / peak, 3), clocks=getattr(ours_ms, "clocks", None), baseline_clocks=getattr(base_ms, "clocks", None)))
     print(json.dumps(rows[-1]), flush=True)
 
 

@@ -18,13 +18,19 @@ def main():
     if int(os.environ.get("WORLD_SIZE", 1)) > 1:
         plugin = FullyShardedDataParallelPlugin(fsdp_version=2, auto_wrap_policy="transformer_based_wrap",
                                                 transformer_cls_names_to_wrap=["LlamaDecoderLayer"])
-    acc = Accelerator(mixed_precision="bf16", fsdp_plugin=plugin)
+    pc = None
+    tp = int(os.environ.get("TP", 1))
+    if tp > 1:  # TP=2 torchrun ... : tp x dp_shard mesh, to see what tensor parallelism adds on the host side
+        from accelerate_hpc_test_b200.parallelism_config import ParallelismConfig
+
+        pc = ParallelismConfig(tp_size=tp, dp_shard_size=int(os.environ["WORLD_SIZE"]) // tp)
+    acc = Accelerator(mixed_precision="bf16", fsdp_plugin=plugin, parallelism_config=pc)
     cfg = LlamaConfig.llama3_8b(num_hidden_layers=int(os.environ.get("LAYERS", 32)))
     torch.manual_seed(0)
     model = LlamaForCausalLM(cfg, dtype=torch.bfloat16, device=acc.device)
     opt = FusedAdamW(model.parameters(), lr=3e-5, weight_decay=0.01)
     model, opt = acc.prepare(model, opt)
-    ids = torch.randint(0, cfg.vocab_size, (2, 2048), device=acc.device)
+    ids = torch.randint(0, cfg.vocab_size, (2 * tp, 2048), device=acc.device)  # same tokens per GPU as the dp runs
 
     def step():
         opt.zero_grad()
