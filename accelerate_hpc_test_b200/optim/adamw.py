@@ -75,6 +75,38 @@ class FusedAdamW(torch.optim.Optimizer):
             self._bwd_hooks.append(p.register_post_accumulate_grad_hook(self._on_grad_ready))
         self._bwd_mode = "active" if mode == "1" else "probing"
 
+    def enable_update_after_reduce(self, stream, sync_gradients_fn=None, mode: Optional[str] = None) -> bool:
+        """The same fusion under a data-parallel engine (``parallel/ddp.py``): a gradient is final once its bucket has been
+        all-reduced, so the engine calls ``update_reduced`` for the bucket's parameters right behind the all-reduce, on its
+        communication ``stream`` — the update of bucket *i* then overlaps the backward GEMMs that produce bucket *i+1*.
+        Same ``mode`` / probing rules as ``enable_update_in_backward``.  Returns whether the fusion was armed."""
+        mode = mode or os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto")
+        if mode == "0" or self._bwd_hooks or self._bwd_stream is not None:
+            return False
+        self._sync_fn = sync_gradients_fn
+        self._bwd_stream = stream
+        self._group_of = {p: g for g in self.param_groups for p in g["params"]}
+        self._bwd_mode = "active" if mode == "1" else "probing"
+        return True
+
+    @torch.no_grad()
+    def update_reduced(self, p: torch.Tensor, reduced_grad: torch.Tensor) -> bool:
+        """Engine hook: ``reduced_grad`` (a view of the reduced bucket) is final.  Must be called with the engine's stream current,
+        after the all-reduce was enqueued on it.  True when the parameter was updated (its gradient is then spent)."""
+        if self._bwd_mode == "probing":
+            self._bwd_fired[p] = self._bwd_fired.get(p, 0) + 1
+            return False
+        if self._bwd_mode != "active" or p not in self._group_of:
+            return False
+        if self._sync_fn is not None and not self._sync_fn():
+            return False
+        if p in self._bwd_updated:
+            raise RuntimeError("a parameter's bucket was reduced twice in one step (several synchronised backward passes per step): "
+                               "set ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD=0.")
+        self._update_one(p, reduced_grad, self._group_of[p])
+        self._bwd_updated.add(p)
+        return True
+
     def _note_grad_consumer(self, what: str):
         self._saw_grad_consumer = True
         if self._bwd_mode == "active" and self._bwd_updated:

@@ -279,7 +279,10 @@ def check_ddp(dev, rank, world, tied: bool = False):
     assert worst < 2e-2, ("ddp param mismatch", tied, worst)
     if tied:
         assert model.module.lm_head.weight is model.module.model.embed_tokens.weight
-    log(f"ddp ok (tied_embeddings={tied}, worst rel err {worst:.2e})")
+    mode = opt.optimizer._bwd_mode
+    if os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto") == "auto":
+        assert mode == "active", mode  # steps 2 and 3 updated every bucket right behind its all-reduce
+    log(f"ddp ok (tied_embeddings={tied}, worst rel err {worst:.2e}, update behind the all-reduce: {mode})")
     model.release()
     AcceleratorState._reset_state(True)
     GradientState._reset_state()
