@@ -1,256 +1,247 @@
-"""Environment / capability probing (L1 of SURVEY.md §1).
+"""What the process can learn from its environment: flags in ``os.environ``, the GPUs and driver underneath, MPI rank variables, the
+NUMA node a GPU hangs off — plus the context managers tests and launchers use to edit ``os.environ`` and put it back.
 
-Behavioural parity with reference src/accelerate/utils/environment.py (flag parsing :59-91,
-``patch_environment`` / ``clear_environment`` / ``purge_accelerate_environment`` :341-471, MPI rank
-discovery :263-280, NUMA affinity :283-338, old-driver P2P guard :197-222) — written for a CUDA-only
-B200 node, so the multi-vendor ladders are gone.
+Behavioural parity: reference ``src/accelerate/utils/environment.py`` (flag parsing :59-91, driver P2P guard :197-222, MPI rank discovery
+:263-280, NUMA affinity :283-338, ``clear_environment`` / ``patch_environment`` / ``purge_accelerate_environment`` :341-471).  Written for
+CUDA nodes only: the reference's per-vendor ladders have no counterpart here.
 """
 
 from __future__ import annotations
 
+import functools
 import logging
-import math
 import os
 import platform
+import shutil
 import subprocess
 import sys
 from contextlib import contextmanager
-from dataclasses import dataclass, field
-from functools import lru_cache, wraps
-from shutil import which
-from typing import Optional
+from dataclasses import dataclass
+from typing import Iterable, Optional
 
 import torch
 from packaging.version import parse
 
 logger = logging.getLogger(__name__)
 
-_TRUE = {"1", "true", "t", "yes", "y", "on"}
-_FALSE = {"0", "false", "f", "no", "n", "off"}
+_TRUTH = {**dict.fromkeys(("1", "true", "t", "yes", "y", "on"), True), **dict.fromkeys(("0", "false", "f", "no", "n", "off"), False)}
+_ENV_FILE_BREAKERS = frozenset(";\n<> ")
 
 
-def convert_dict_to_env_variables(current_env: dict) -> list[str]:
-    """``{"A": "1"}`` -> ``["A=1\\n"]`` skipping entries that would break a shell env file."""
-    forbidden = [";", "\n", "<", ">", " "]
-    out = []
-    for key, value in current_env.items():
-        if all(c not in (key + value) for c in forbidden) and len(key) >= 1 and len(value) >= 1:
-            out.append(f"{key}={value}\n")
-        else:
-            logger.warning(f"WARNING: Skipping {key}={value} as it contains forbidden characters or missing values.")
-    return out
-
-
+# ------------------------------------------------------------------------------------------------- flags
 def str_to_bool(value, to_bool: bool = False):
-    """'yes'/'true'/'1'... -> 1 (or True), 'no'/'false'/'0'... -> 0 (or False); anything else raises."""
-    v = str(value).lower()
-    if v in _TRUE:
-        return True if to_bool else 1
-    if v in _FALSE:
-        return False if to_bool else 0
-    raise ValueError(f"invalid truth value {value}")
+    """The usual spellings of yes and no (case-insensitive) as 1 / 0 — or True / False with ``to_bool``; anything else raises."""
+    try:
+        verdict = _TRUTH[str(value).lower()]
+    except KeyError:
+        raise ValueError(f"invalid truth value {value}") from None
+    return verdict if to_bool else int(verdict)
 
 
-def get_int_from_env(env_keys, default):
-    """First non-negative int found among ``env_keys``, else ``default``."""
-    for e in env_keys:
-        val = int(os.environ.get(e, -1))
-        if val >= 0:
-            return val
-    return default
-
-
-def parse_flag_from_env(key, default=False):
-    return str_to_bool(os.environ.get(key, str(default))) == 1
+def parse_flag_from_env(key, default=False) -> bool:
+    return bool(str_to_bool(os.environ.get(key, str(default))))
 
 
 def parse_choice_from_env(key, default="no"):
     return os.environ.get(key, str(default))
 
 
+def get_int_from_env(env_keys: Iterable[str], default):
+    """The first of ``env_keys`` that holds a non-negative integer, else ``default``."""
+    for key in env_keys:
+        found = int(os.environ.get(key, -1))
+        if found >= 0:
+            return found
+    return default
+
+
+def convert_dict_to_env_variables(current_env: dict) -> list[str]:
+    """``KEY=value`` lines for an env file; pairs that are empty or contain characters a shell would choke on are skipped (and logged)."""
+    lines = []
+    for key, value in current_env.items():
+        if key and value and not _ENV_FILE_BREAKERS & set(key + value):
+            lines.append(f"{key}={value}\n")
+        else:
+            logger.warning(f"WARNING: Skipping {key}={value} as it contains forbidden characters or missing values.")
+    return lines
+
+
 def are_libraries_initialized(*library_names: str) -> list[str]:
-    return [lib for lib in library_names if lib in sys.modules.keys()]
+    """Which of the named libraries have been imported already (some initialise CUDA on import, which forbids forking)."""
+    return [name for name in library_names if name in sys.modules]
 
 
-def _nvidia_smi():
-    if platform.system() == "Windows":
-        command = which("nvidia-smi")
-        if command is None:
-            command = f"{os.environ['systemdrive']}\\Program Files\\NVIDIA Corporation\\NVSMI\\nvidia-smi.exe"
-    else:
-        command = "nvidia-smi"
-    return command
+# ------------------------------------------------------------------------------------------------- GPUs underneath
+def _nvidia_smi() -> str:
+    if platform.system() != "Windows":
+        return "nvidia-smi"
+    return shutil.which("nvidia-smi") or f"{os.environ['systemdrive']}\\Program Files\\NVIDIA Corporation\\NVSMI\\nvidia-smi.exe"
+
+
+def _query_gpus(fields: str) -> list[list[str]]:
+    """One list of fields per GPU, from ``nvidia-smi`` — which, unlike ``torch.cuda``, does not create a CUDA context."""
+    text = subprocess.check_output([_nvidia_smi(), f"--query-gpu={fields}", "--format=csv,noheader"], universal_newlines=True)
+    return [[cell.strip() for cell in line.split(",")] for line in text.strip().splitlines()]
 
 
 def get_gpu_info():
-    """``(list of GPU names, count)`` without initialising CUDA."""
-    output = subprocess.check_output([_nvidia_smi(), "--query-gpu=count,name", "--format=csv,noheader"], universal_newlines=True)
-    output = output.strip()
-    gpus = output.split(os.linesep)
-    gpu_count = len(gpus)
-    gpu_names = [gpu.split(",")[1].strip() for gpu in gpus]
-    return gpu_names, gpu_count
+    """``([name of every GPU], how many)``."""
+    rows = _query_gpus("count,name")
+    return [row[1] for row in rows], len(rows)
 
 
-def get_driver_version():
-    output = subprocess.check_output([_nvidia_smi(), "--query-gpu=driver_version", "--format=csv,noheader"], universal_newlines=True)
-    return output.strip().split(os.linesep)[0]
+def get_driver_version() -> str:
+    return _query_gpus("driver_version")[0][0]
 
 
 def check_cuda_p2p_ib_support() -> bool:
-    """False for consumer Ada boards on drivers that mis-handle P2P/IB; always True on B200."""
+    """False only for multi-GPU RTX 40 boxes on drivers older than 550.40.07, whose peer-to-peer / InfiniBand paths hang; the caller
+    then disables them for NCCL.  Any probing failure counts as "supported"."""
     try:
-        device_names, device_count = get_gpu_info()
-        unsupported = {"RTX 40"}
-        if device_count > 1 and any(d in name for d in unsupported for name in device_names):
-            if parse(get_driver_version()) < parse("550.40.07"):
-                return False
+        names, count = get_gpu_info()
+        if count > 1 and any("RTX 40" in name for name in names):
+            return parse(get_driver_version()) >= parse("550.40.07")
     except Exception:
         pass
     return True
 
 
-@lru_cache
+def _compute_capability() -> tuple:
+    try:
+        return tuple(torch.cuda.get_device_capability())
+    except Exception:
+        return (0, 0)
+
+
+@functools.lru_cache
 def check_cuda_fp8_capability() -> bool:
-    """fp8 tensor cores need compute capability >= 8.9 (B200 is 10.0)."""
-    try:
-        return torch.cuda.get_device_capability() >= (8, 9)
-    except Exception:
-        return False
+    """fp8 tensor cores exist from compute capability 8.9 on (B200 is 10.0)."""
+    return _compute_capability() >= (8, 9)
 
 
-@lru_cache
+@functools.lru_cache
 def check_blackwell() -> bool:
-    """True when the current device has tcgen05 / MXFP8 block-scaled tensor cores (sm_100+)."""
-    try:
-        return torch.cuda.get_device_capability()[0] >= 10
-    except Exception:
-        return False
+    """tcgen05 tensor cores with tensor memory and block-scaled MXFP8 operands: sm_100 and later."""
+    return _compute_capability() >= (10, 0)
 
 
+def get_current_device_type():
+    """``(device type, distributed type)`` this process would use — reference utils/environment.py:101-130 minus the other vendors."""
+    return ("cuda", "MULTI_GPU") if torch.cuda.is_available() else ("cpu", "MULTI_CPU")
+
+
+# ------------------------------------------------------------------------------------------------- MPI launches
 @dataclass
 class CPUInformation:
-    """Rank / world-size facts of an mpirun-launched CPU job, read from the MPI flavours' env vars."""
+    """Who this process is in a job started by ``mpirun`` rather than ``torchrun``."""
 
-    rank: int = field(default=0)
-    world_size: int = field(default=1)
-    local_rank: int = field(default=0)
-    local_world_size: int = field(default=1)
+    rank: int = 0
+    world_size: int = 1
+    local_rank: int = 0
+    local_world_size: int = 1
+
+
+# torchrun's name first, then Intel MPI / MPICH, Open MPI, MVAPICH2
+_MPI_VARIABLES = {
+    "rank": ("RANK", "PMI_RANK", "OMPI_COMM_WORLD_RANK", "MV2_COMM_WORLD_RANK"),
+    "world_size": ("WORLD_SIZE", "PMI_SIZE", "OMPI_COMM_WORLD_SIZE", "MV2_COMM_WORLD_SIZE"),
+    "local_rank": ("LOCAL_RANK", "MPI_LOCALRANKID", "OMPI_COMM_WORLD_LOCAL_RANK", "MV2_COMM_WORLD_LOCAL_RANK"),
+    "local_world_size": ("LOCAL_WORLD_SIZE", "MPI_LOCALNRANKS", "OMPI_COMM_WORLD_LOCAL_SIZE", "MV2_COMM_WORLD_LOCAL_SIZE"),
+}
 
 
 def get_cpu_distributed_information() -> CPUInformation:
-    info = {
-        "rank": get_int_from_env(["RANK", "PMI_RANK", "OMPI_COMM_WORLD_RANK", "MV2_COMM_WORLD_RANK"], 0),
-        "world_size": get_int_from_env(["WORLD_SIZE", "PMI_SIZE", "OMPI_COMM_WORLD_SIZE", "MV2_COMM_WORLD_SIZE"], 1),
-        "local_rank": get_int_from_env(["LOCAL_RANK", "MPI_LOCALRANKID", "OMPI_COMM_WORLD_LOCAL_RANK", "MV2_COMM_WORLD_LOCAL_RANK"], 0),
-        "local_world_size": get_int_from_env(["LOCAL_WORLD_SIZE", "MPI_LOCALNRANKS", "OMPI_COMM_WORLD_LOCAL_SIZE", "MV2_COMM_WORLD_LOCAL_SIZE"], 1),
-    }
-    return CPUInformation(**info)
+    fallback = CPUInformation()
+    return CPUInformation(**{name: get_int_from_env(keys, getattr(fallback, name)) for name, keys in _MPI_VARIABLES.items()})
 
 
+# ------------------------------------------------------------------------------------------------- NUMA
 def override_numa_affinity(local_process_index: int, verbose: Optional[bool] = None) -> None:
-    """Pin this process to the CPU cores of the NUMA node its GPU hangs off (needs pynvml)."""
-    if verbose is None:
-        verbose = parse_flag_from_env("ACCELERATE_DEBUG_MODE", False)
+    """Restrict this process to the CPU cores NVML reports as closest to GPU ``local_process_index``, so that pinned-memory copies
+    and kernel launches do not cross the socket interconnect.  A no-op without CUDA or without ``pynvml``."""
     if not torch.cuda.is_available():
         return
     try:
-        import pynvml as nvml
+        import pynvml
     except ImportError:
         return
-    nvml.nvmlInit()
-    num_elements = math.ceil(os.cpu_count() / 64)
-    handle = nvml.nvmlDeviceGetHandleByIndex(local_process_index)
-    affinity_string = ""
-    for j in nvml.nvmlDeviceGetCpuAffinity(handle, num_elements):
-        affinity_string = f"{j:064b}{affinity_string}"
-    affinity_list = [int(x) for x in affinity_string]
-    affinity_list.reverse()
-    affinity_to_set = [i for i, e in enumerate(affinity_list) if e != 0]
-    os.sched_setaffinity(0, affinity_to_set)
+    if verbose is None:
+        verbose = parse_flag_from_env("ACCELERATE_DEBUG_MODE", False)
+    pynvml.nvmlInit()
+    words = -(-os.cpu_count() // 64)  # NVML hands the mask back in 64-bit words, least significant first
+    mask = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local_process_index), words)
+    cores = [64 * word + bit for word, bits in enumerate(mask) for bit in range(64) if bits >> bit & 1]
+    os.sched_setaffinity(0, cores)
     if verbose:
-        cpu_cores = os.sched_getaffinity(0)
-        logger.info(f"Assigning {len(cpu_cores)} cpu cores to process {local_process_index}: {cpu_cores}")
+        now = os.sched_getaffinity(0)
+        logger.info(f"Assigning {len(now)} cpu cores to process {local_process_index}: {now}")
 
 
-@lru_cache
+@functools.lru_cache
 def set_numa_affinity(local_process_index: int, verbose: Optional[bool] = None) -> None:
+    """``override_numa_affinity`` once per (process, GPU)."""
     override_numa_affinity(local_process_index=local_process_index, verbose=verbose)
+
+
+# ------------------------------------------------------------------------------------------------- editing os.environ and putting it back
+@contextmanager
+def _environment_restored(only_prefix: str = ""):
+    """On exit every variable starting with ``only_prefix`` has the value it had on entry (variables born inside are removed)."""
+    before = {key: value for key, value in os.environ.items() if key.startswith(only_prefix)}
+    try:
+        yield
+    finally:
+        for key in [key for key in os.environ if key.startswith(only_prefix) and key not in before]:
+            del os.environ[key]
+        os.environ.update(before)
 
 
 @contextmanager
 def clear_environment():
-    """Empty ``os.environ`` inside the block and restore it afterwards (same dict object)."""
-    _old = os.environ.copy()
-    os.environ.clear()
-    try:
-        yield
-    finally:
+    """An empty ``os.environ`` (the same mapping object, emptied) for the duration of the block."""
+    with _environment_restored():
         os.environ.clear()
-        os.environ.update(_old)
+        yield
 
 
 @contextmanager
 def patch_environment(**kwargs):
-    """Temporarily set (upper-cased) env vars; previous values come back on exit."""
-    existing = {}
-    for key, value in kwargs.items():
-        key = key.upper()
-        if key in os.environ:
-            existing[key] = os.environ[key]
-        os.environ[key] = str(value)
+    """Set the given variables (names upper-cased, values stringified) for the duration of the block; other variables changed inside
+    the block keep their new values."""
+    names = [name.upper() for name in kwargs]
+    before = {name: os.environ.get(name) for name in names}
+    os.environ.update({name: str(value) for name, value in zip(names, kwargs.values())})
     try:
         yield
     finally:
-        for key in kwargs:
-            key = key.upper()
-            if key in existing:
-                os.environ[key] = existing[key]
+        for name, old in before.items():
+            if old is None:
+                os.environ.pop(name, None)
             else:
-                os.environ.pop(key, None)
+                os.environ[name] = old
 
 
 def purge_accelerate_environment(func_or_cls):
-    """Decorator (function or TestCase class): ``ACCELERATE_*`` variables set inside do not leak out."""
-    prefix = "ACCELERATE_"
+    """Decorator for a test function, or a test class (its ``test*`` methods): ``ACCELERATE_*`` variables set while it runs do not
+    leak into the tests after it."""
+    marker = "_accelerate_is_purged_environment_wrapped"
 
-    @contextmanager
-    def env_var_context():
-        existing = {k: v for k, v in os.environ.items() if k.startswith(prefix)}
-        try:
-            yield
-        finally:
-            for k in [k for k in os.environ if k.startswith(prefix)]:
-                if k in existing:
-                    os.environ[k] = existing[k]
-                else:
-                    os.environ.pop(k, None)
-            for k, v in existing.items():
-                os.environ[k] = v
+    def guarded(func):
+        if getattr(func, marker, False):
+            return func
 
-    def wrap_function(func):
-        @wraps(func)
-        def wrapper(*args, **kwargs):
-            with env_var_context():
+        @functools.wraps(func)
+        def run(*args, **kwargs):
+            with _environment_restored("ACCELERATE_"):
                 return func(*args, **kwargs)
 
-        wrapper._accelerate_is_purged_environment_wrapped = True
-        return wrapper
+        setattr(run, marker, True)
+        return run
 
     if not isinstance(func_or_cls, type):
-        return wrap_function(func_or_cls)
-    cls = func_or_cls
-    for name in dir(cls):
-        attr = getattr(cls, name, None)
-        if name.startswith("test") and callable(attr) and not getattr(attr, "_accelerate_is_purged_environment_wrapped", False):
-            setattr(cls, name, wrap_function(attr))
-    return cls
-
-
-def get_current_device_type():
-    """``(device_type, distributed_type)`` of the accelerator this process would use (reference utils/environment.py:101-130)."""
-    import torch
-
-    if torch.cuda.is_available():
-        return "cuda", "MULTI_GPU"
-    return "cpu", "MULTI_CPU"
+        return guarded(func_or_cls)
+    for name in dir(func_or_cls):
+        member = getattr(func_or_cls, name, None)
+        if name.startswith("test") and callable(member):
+            setattr(func_or_cls, name, guarded(member))
+    return func_or_cls

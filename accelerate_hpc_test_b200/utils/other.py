@@ -16,9 +16,8 @@ import platform
 import re
 import socket
 from contextlib import contextmanager
-from functools import partial, reduce
+from functools import reduce
 from types import MethodType
-from typing import Callable, OrderedDict
 
 import numpy as np
 import torch
@@ -45,68 +44,66 @@ def clear_environment_for_defaults():
         os.environ.update(saved)
 
 
+def _optimized_module_type():
+    dynamo = getattr(torch, "_dynamo", None)
+    return dynamo.eval_frame.OptimizedModule if dynamo is not None else ()
+
+
 def is_compiled_module(module: torch.nn.Module) -> bool:
-    return hasattr(torch, "_dynamo") and isinstance(module, torch._dynamo.eval_frame.OptimizedModule)
+    """Is ``module`` what ``torch.compile(model)`` returned?"""
+    return isinstance(module, _optimized_module_type())
 
 
 def has_compiled_regions(module: torch.nn.Module) -> bool:
-    if not hasattr(torch, "_dynamo"):
-        return False
-    if module._modules:
-        for submodule in module.modules():
-            if isinstance(submodule, torch._dynamo.eval_frame.OptimizedModule):
-                return True
-    return False
+    """Does ``module`` contain compiled sub-modules (the result of ``compile_regions``)?"""
+    kind = _optimized_module_type()
+    return bool(kind) and bool(module._modules) and any(isinstance(sub, kind) for sub in module.modules())
 
 
 def is_repeated_blocks(module: torch.nn.Module) -> bool:
-    return isinstance(module, torch.nn.ModuleList) and all(isinstance(m, module[0].__class__) for m in module)
+    """A ``ModuleList`` whose members all have the class of the first — a stack of decoder layers, typically."""
+    return isinstance(module, torch.nn.ModuleList) and all(isinstance(member, type(module[0])) for member in module)
 
 
 def has_repeated_blocks(module: torch.nn.Module) -> bool:
-    if module._modules:
-        for submodule in module.modules():
-            if is_repeated_blocks(submodule):
-                return True
-    return False
+    return bool(module._modules) and any(is_repeated_blocks(sub) for sub in module.modules())
 
 
 def compile_regions(module: torch.nn.Module, **compile_kwargs) -> torch.nn.Module:
-    """Compile repeated blocks (ModuleLists of one class) separately and the rest as a whole.
-
-    Available for user modules that want it; the framework's own hot path does not use torch.compile.
-    """
-    new_module = _compile_regions(module, **compile_kwargs)
-    if "_orig_mod" not in new_module.__dict__:
-        new_module.__dict__["_orig_mod"] = module
-    return new_module
+    """Regional compilation for user models: every member of a stack of identical blocks is compiled on its own (the compiler's
+    cache makes the 2nd..Nth nearly free), everything else as one piece.  The original stays reachable as ``_orig_mod``.  (This
+    framework's own hot path is hand-written kernels; nothing here depends on ``torch.compile``.)"""
+    compiled = _compile_regions(module, **compile_kwargs)
+    compiled.__dict__.setdefault("_orig_mod", module)
+    return compiled
 
 
 def _compile_regions(module: torch.nn.Module, **compile_kwargs) -> torch.nn.Module:
     if is_repeated_blocks(module):
-        new_module = torch.nn.ModuleList()
-        for submodule in module:
-            new_module.append(torch.compile(submodule, **compile_kwargs))
-    elif has_repeated_blocks(module):
-        new_module = module.__class__.__new__(module.__class__)
-        new_module.__dict__.update(module.__dict__)
-        new_module._modules = {}
-        for name, submodule in module.named_children():
-            new_module.add_module(name, _compile_regions(submodule, **compile_kwargs))
-    else:
-        new_module = torch.compile(module, **compile_kwargs)
-    return new_module
+        return torch.nn.ModuleList(torch.compile(block, **compile_kwargs) for block in module)
+    if not has_repeated_blocks(module):
+        return torch.compile(module, **compile_kwargs)
+    # a shell of the same class sharing the attributes, with every child replaced by its regionally compiled version
+    shell = type(module).__new__(type(module))
+    shell.__dict__.update(module.__dict__)
+    shell._modules = {}
+    for name, child in module.named_children():
+        shell.add_module(name, _compile_regions(child, **compile_kwargs))
+    return shell
 
 
-def compile_regions_deepspeed(module: torch.nn.Module, **compile_kwargs):
+def compile_regions_deepspeed(module: torch.nn.Module, **compile_kwargs) -> None:
+    """In-place variant (``nn.Module.compile``) for engines that hold on to the module objects."""
     if is_repeated_blocks(module):
-        for submodule in module:
-            submodule.compile(**compile_kwargs)
+        targets = list(module)
     elif has_repeated_blocks(module):
         for child in module.children():
             compile_regions_deepspeed(child, **compile_kwargs)
+        return
     else:
-        module.compile(**compile_kwargs)
+        targets = [module]
+    for target in targets:
+        target.compile(**compile_kwargs)
 
 
 def model_has_dtensor(model: torch.nn.Module) -> bool:
@@ -122,52 +119,52 @@ def _parallel_wrapper_types():
     return (torch.nn.parallel.DistributedDataParallel, torch.nn.DataParallel, B200DataParallel, B200ShardedModule)
 
 
-def extract_model_from_parallel(model, keep_fp32_wrapper: bool = True, keep_torch_compile: bool = True, recursive: bool = False):
-    """Strip the distributed wrappers (torch DDP, native DDP / sharded engines, torch.compile) off ``model``."""
-    options = _parallel_wrapper_types()
-    is_compiled = is_compiled_module(model)
-    has_compiled = has_compiled_regions(model)
-    compiled_model = None
-    if is_compiled:
-        compiled_model = model
-        model = model._orig_mod
-    elif has_compiled:
-        compiled_model = model
-        model = model.__dict__["_orig_mod"]
-    while isinstance(model, options):
+def _peel(model, wrappers):
+    while isinstance(model, wrappers):
         model = model.module
-    if recursive:
-        def _recursive_unwrap(module):
-            if hasattr(module, "module") and isinstance(module, options):
-                unwrapped = _recursive_unwrap(module.module)
-            else:
-                unwrapped = module
-            for name, child in unwrapped.named_children():
-                setattr(unwrapped, name, _recursive_unwrap(child))
-            return unwrapped
-
-        model = _recursive_unwrap(model)
-    if not keep_fp32_wrapper:
-        forward = model.forward
-        original_forward = model.__dict__.pop("_original_forward", None)
-        if original_forward is not None:
-            while hasattr(forward, "__wrapped__"):
-                forward = forward.__wrapped__
-                if forward == original_forward:
-                    break
-            model.forward = MethodType(forward, model)
-        if getattr(model, "_converted_to_transformer_engine", False):
-            from .transformer_engine import convert_model
-
-            convert_model(model, to_transformer_engine=False)
-    if keep_torch_compile and compiled_model is not None:
-        if is_compiled:
-            compiled_model._orig_mod = model
-            model = compiled_model
-        elif has_compiled:
-            compiled_model.__dict__["_orig_mod"] = model
-            model = compiled_model
     return model
+
+
+def _peel_everywhere(module, wrappers):
+    module = _peel(module, wrappers)
+    for name, child in module.named_children():
+        setattr(module, name, _peel_everywhere(child, wrappers))
+    return module
+
+
+def _restore_plain_forward(model) -> None:
+    """Undo what ``prepare`` did to ``model.forward`` (autocast / fp32-output decorators, TransformerEngine layers)."""
+    original = model.__dict__.pop("_original_forward", None)
+    if original is not None:
+        forward = model.forward
+        while hasattr(forward, "__wrapped__") and forward != original:
+            forward = forward.__wrapped__
+        model.forward = MethodType(forward, model)
+    if getattr(model, "_converted_to_transformer_engine", False):
+        from .transformer_engine import convert_model
+
+        convert_model(model, to_transformer_engine=False)
+
+
+def extract_model_from_parallel(model, keep_fp32_wrapper: bool = True, keep_torch_compile: bool = True, recursive: bool = False):
+    """The user's module back out of the wrappers ``prepare`` put around it: torch DDP / DataParallel, the native data-parallel and
+    sharded engines, ``torch.compile`` (kept on top unless ``keep_torch_compile=False``).  ``recursive`` also unwraps wrapped
+    sub-modules; ``keep_fp32_wrapper=False`` additionally restores the undecorated ``forward``."""
+    wrappers = _parallel_wrapper_types()
+    compiled_outer = model if (is_compiled_module(model) or has_compiled_regions(model)) else None
+    whole_model_compiled = compiled_outer is not None and is_compiled_module(model)
+    if compiled_outer is not None:
+        model = model._orig_mod if whole_model_compiled else model.__dict__["_orig_mod"]
+    model = _peel_everywhere(model, wrappers) if recursive else _peel(model, wrappers)
+    if not keep_fp32_wrapper:
+        _restore_plain_forward(model)
+    if compiled_outer is None or not keep_torch_compile:
+        return model
+    if whole_model_compiled:
+        compiled_outer._orig_mod = model
+    else:
+        compiled_outer.__dict__["_orig_mod"] = model
+    return compiled_outer
 
 
 def wait_for_everyone():
@@ -201,20 +198,20 @@ def clean_state_dict_for_safetensors(state_dict: dict):
 
 
 def save(obj, f, save_on_each_node: bool = False, safe_serialization: bool = False):
-    """Write ``obj`` to ``f`` once per job (or once per node): torch.save, or safetensors for state dicts."""
+    """Write ``obj`` to ``f`` from one process only — the job's main process, or each node's with ``save_on_each_node`` (node-local
+    disks).  ``safe_serialization`` writes safetensors (state dicts are de-aliased first), otherwise ``torch.save``."""
+    state = PartialState()
+    writer = state.is_local_main_process if save_on_each_node else state.is_main_process
+    if safe_serialization and isinstance(obj, dict):
+        obj = clean_state_dict_for_safetensors(obj)
+    if not writer:
+        return
     if safe_serialization:
         from safetensors.torch import save_file
 
-        save_func = partial(save_file, metadata={"format": "pt"})
-        if isinstance(obj, (OrderedDict, dict)):
-            obj = clean_state_dict_for_safetensors(obj)
+        save_file(obj, f, metadata={"format": "pt"})
     else:
-        save_func = torch.save
-    state = PartialState()
-    if state.is_main_process and not save_on_each_node:
-        save_func(obj, f)
-    elif state.is_local_main_process and save_on_each_node:
-        save_func(obj, f)
+        torch.save(obj, f)
 
 
 # numpy globals that legacy RNG-state pickles reference; allowed under weights_only=True
@@ -249,12 +246,11 @@ def load(f, map_location=None, **kwargs):
 
 
 def get_pretty_name(obj) -> str:
-    if not hasattr(obj, "__qualname__") and not hasattr(obj, "__name__"):
-        obj = getattr(obj, "__class__", obj)
-    if hasattr(obj, "__qualname__"):
-        return obj.__qualname__
-    if hasattr(obj, "__name__"):
-        return obj.__name__
+    """Qualified name of a function / class, or of the class of an instance."""
+    for candidate in (obj, type(obj)):
+        for attribute in ("__qualname__", "__name__"):
+            if hasattr(candidate, attribute):
+                return getattr(candidate, attribute)
     return str(obj)
 
 
@@ -283,11 +279,13 @@ def get_free_port() -> int:
 
 
 def convert_bytes(size) -> str:
-    for unit in ["bytes", "KB", "MB", "GB", "TB"]:
-        if size < 1024.0:
-            return f"{round(size, 2)} {unit}"
+    """``1536`` -> ``"1.5 KB"`` (binary steps, decimal names, as the reference prints them)."""
+    units = ("bytes", "KB", "MB", "GB", "TB", "PB")
+    step = 0
+    while size >= 1024.0 and step < len(units) - 1:
         size /= 1024.0
-    return f"{round(size, 2)} PB"
+        step += 1
+    return f"{round(size, 2)} {units[step]}"
 
 
 def check_os_kernel():
