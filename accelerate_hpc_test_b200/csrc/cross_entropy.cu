@@ -19,7 +19,8 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restric
   __nv_bfloat16* z = logits + row * ld;
   const long long label = labels[row];
   const bool valid = (label != ignore_index) && label >= 0 && label < V;
-  const int nvec = V >> 3;  // V % 8 == 0 enforced by host
+  const int nvec = V >> 3;       // whole 16-byte vectors of the row (the row pitch `ld` is a multiple of 8 elements)
+  const int tail0 = nvec << 3;   // the last V % 8 elements (odd vocabularies, e.g. 50257) are handled one per thread
   const uint4* zv = reinterpret_cast<const uint4*>(z);
 
   float mx = -INFINITY, sum = 0.f;
@@ -33,6 +34,14 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restric
     }
     sum += __expf(a.x - mx) + __expf(a.y - mx) + __expf(b.x - mx) + __expf(b.y - mx) + __expf(c.x - mx) +
            __expf(c.y - mx) + __expf(d.x - mx) + __expf(d.y - mx);
+  }
+  if ((int)threadIdx.x < V - tail0) {
+    const float a = __bfloat162float(z[tail0 + threadIdx.x]);
+    if (a > mx) {
+      sum *= __expf(mx - a);
+      mx = a;
+    }
+    sum += __expf(a - mx);
   }
   const float gmx = block_max(mx, red);
   sum *= (mx == -INFINITY) ? 0.f : __expf(mx - gmx);
@@ -68,6 +77,12 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const long long* __restric
     o.x = f2_to_bf2(f[0], f[1]); o.y = f2_to_bf2(f[2], f[3]);
     o.z = f2_to_bf2(f[4], f[5]); o.w = f2_to_bf2(f[6], f[7]);
     st_v4(zo + i, o);
+  }
+  if ((int)threadIdx.x < V - tail0) {
+    const int idx = tail0 + threadIdx.x;
+    float f = __expf(__bfloat162float(z[idx]) - lse) * g;
+    if (valid && idx == label) f -= g;
+    z[idx] = __float2bfloat16(f);
   }
 }
 
@@ -106,7 +121,7 @@ using namespace b200;
 B200_API int b200_ce_fwd_bwd(void* logits, const void* labels, void* loss_rows, void* lse_rows,
                              long long T, long long ld, int V, const void* inv_count, float scale,
                              long long ignore_index, int write_grad, void* stream) {
-  if (V % 8 || ld % 8) return B200_ERR_BAD_ARG;
+  if (ld % 8 || V > ld) return B200_ERR_BAD_ARG;
   if (T == 0) return 0;
   ce_fwd_bwd_kernel<<<(unsigned)T, 1024, 0, (cudaStream_t)stream>>>(
       (__nv_bfloat16*)logits, (const long long*)labels, (float*)loss_rows, (float*)lse_rows, ld, V,

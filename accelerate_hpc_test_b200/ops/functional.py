@@ -517,7 +517,11 @@ class _FusedLinearCEFn(torch.autograd.Function):
         first = True
         for t0 in range(0, T, chunk_tokens):
             t1 = min(T, t0 + chunk_tokens)
-            logits = gemm(h2[t0:t1], weight)  # [tc, V] bf16
+            if V % 8:
+                # odd vocabularies (GPT-2's 50257): rows on a 16-byte pitch so that TMA and the vector loads stay aligned
+                logits = gemm(h2[t0:t1], weight, out=torch.empty((t1 - t0, (V + 7) // 8 * 8), dtype=h2.dtype, device=h2.device)[:, :V])
+            else:
+                logits = gemm(h2[t0:t1], weight)  # [tc, V] bf16
             rows = cross_entropy_chunk_(logits, lab[t0:t1], inv, 1.0, ignore_index, write_grad=need_grad)
             loss_rows.append(rows)
             if need_grad:

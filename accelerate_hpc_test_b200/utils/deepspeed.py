@@ -18,85 +18,90 @@ from .dataclasses import DeepSpeedPlugin
 
 
 def get_active_deepspeed_plugin(state):
+    """The plugin in force: the only one, or — when several were registered by name — the one marked ``selected``."""
     if state.distributed_type.value != "DEEPSPEED":
-        raise ValueError("Couldn't retrieve the active `DeepSpeedPlugin` as none were enabled. Please make sure that either `Accelerator` is configured for `deepspeed` or make sure that the desired `DeepSpeedPlugin` has been enabled (`AcceleratorState().select_deepspeed_plugin(name)`) before calling this function.")
-    if not isinstance(state.deepspeed_plugins, dict):
-        return state.deepspeed_plugins
-    return next(plugin for plugin in state.deepspeed_plugins.values() if plugin.selected)
+        raise ValueError("Couldn't retrieve the active `DeepSpeedPlugin` as none were enabled. Please make sure that either `Accelerator` "
+                         "is configured for `deepspeed` or make sure that the desired `DeepSpeedPlugin` has been enabled "
+                         "(`AcceleratorState().select_deepspeed_plugin(name)`) before calling this function.")
+    plugins = state.deepspeed_plugins
+    if isinstance(plugins, dict):
+        return next(plugin for plugin in plugins.values() if plugin.selected)
+    return plugins
+
+
+_MISSING = object()
 
 
 class HfDeepSpeedConfig:
-    """Dictionary-path access to a DeepSpeed config (dict, JSON path or base64 JSON)."""
+    """A DeepSpeed configuration with dotted-path access (``cfg.get_value("zero_optimization.stage")``).  Accepts a dict (copied), the
+    path of a JSON file, or the JSON text base64-encoded (how launchers pass it through an environment variable)."""
 
     def __init__(self, config_file_or_dict):
-        if isinstance(config_file_or_dict, dict):
-            config = deepcopy(config_file_or_dict)
-        elif os.path.exists(config_file_or_dict):
-            with open(config_file_or_dict, encoding="utf-8") as f:
-                config = json.load(f)
-        else:
-            try:
-                import base64
-
-                config = json.loads(base64.urlsafe_b64decode(config_file_or_dict).decode("utf-8"))
-            except (UnicodeDecodeError, AttributeError, ValueError):
-                raise ValueError(f"Expected a string path to an existing deepspeed config, or a dictionary, or a base64 encoded string. Received: {config_file_or_dict}")
-        self.config = config
+        self.config = self._read(config_file_or_dict)
         self.set_stage_and_offload()
 
-    def set_stage_and_offload(self):
-        self._stage = self.get_value("zero_optimization.stage", -1)
-        self._offload = False
-        if self.is_zero2() or self.is_zero3():
-            offload_devices_valid = {"cpu", "nvme"}
-            offload_devices = {self.get_value("zero_optimization.offload_optimizer.device"), self.get_value("zero_optimization.offload_param.device")}
-            if len(offload_devices & offload_devices_valid) > 0:
-                self._offload = True
+    @staticmethod
+    def _read(source) -> dict:
+        if isinstance(source, dict):
+            return deepcopy(source)
+        if os.path.exists(source):
+            with open(source, encoding="utf-8") as handle:
+                return json.load(handle)
+        try:
+            import base64
 
-    def find_config_node(self, ds_key_long):
-        config = self.config
-        nodes = ds_key_long.split(".")
-        ds_key = nodes.pop()
-        for node in nodes:
-            config = config.get(node)
-            if config is None:
-                return None, ds_key
-        return config, ds_key
+            return json.loads(base64.urlsafe_b64decode(source).decode("utf-8"))
+        except (UnicodeDecodeError, AttributeError, ValueError):
+            raise ValueError("Expected a string path to an existing deepspeed config, or a dictionary, or a base64 encoded string. "
+                             f"Received: {source}") from None
+
+    def _walk(self, dotted: str):
+        """``(the dict that holds the last key, the last key)`` — the dict is None when the path breaks off earlier."""
+        *parents, leaf = dotted.split(".")
+        node = self.config
+        for key in parents:
+            node = node.get(key) if isinstance(node, dict) else None
+            if node is None:
+                break
+        return node, leaf
+
+    find_config_node = _walk  # reference name
 
     def get_value(self, ds_key_long, default=None):
-        config, ds_key = self.find_config_node(ds_key_long)
-        if config is None:
-            return default
-        return config.get(ds_key, default)
+        holder, leaf = self._walk(ds_key_long)
+        return default if holder is None else holder.get(leaf, default)
 
     def del_config_sub_tree(self, ds_key_long, must_exist=False):
-        config = self.config
-        nodes = ds_key_long.split(".")
-        for node in nodes:
-            parent_config = config
-            config = config.get(node)
-            if config is None:
-                if must_exist:
-                    raise ValueError(f"Can't find {ds_key_long} entry in the config: {self.config}")
-                return
-        if parent_config is not None:
-            parent_config.pop(node)
+        """Remove the entry at ``ds_key_long`` (and everything below it)."""
+        holder, leaf = self._walk(ds_key_long)
+        if holder is None or holder.get(leaf) is None:
+            if must_exist:
+                raise ValueError(f"Can't find {ds_key_long} entry in the config: {self.config}")
+            return
+        del holder[leaf]
 
-    def is_true(self, ds_key_long):
-        value = self.get_value(ds_key_long)
-        return False if value is None else bool(value)
+    def is_true(self, ds_key_long) -> bool:
+        """Present and truthy (an absent key is neither true nor false)."""
+        value = self.get_value(ds_key_long, _MISSING)
+        return value is not _MISSING and value is not None and bool(value)
 
-    def is_false(self, ds_key_long):
-        value = self.get_value(ds_key_long)
-        return False if value is None else not bool(value)
+    def is_false(self, ds_key_long) -> bool:
+        """Present and falsy."""
+        value = self.get_value(ds_key_long, _MISSING)
+        return value is not _MISSING and value is not None and not bool(value)
 
-    def is_zero2(self):
+    def set_stage_and_offload(self) -> None:
+        self._stage = self.get_value("zero_optimization.stage", -1)
+        targets = {self.get_value(f"zero_optimization.{what}.device") for what in ("offload_optimizer", "offload_param")}
+        self._offload = self._stage in (2, 3) and bool(targets & {"cpu", "nvme"})
+
+    def is_zero2(self) -> bool:
         return self._stage == 2
 
-    def is_zero3(self):
+    def is_zero3(self) -> bool:
         return self._stage == 3
 
-    def is_offload(self):
+    def is_offload(self) -> bool:
         return self._offload
 
 

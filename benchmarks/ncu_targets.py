@@ -114,12 +114,17 @@ def ops():
     yield "reduce-scatter + adamw (1 rank)", rs_adamw
 
 
-for name, fn in ops():
+# TARGETS=tc: tensor-core kernels only; TARGETS=mem: the bandwidth-bound and comm kernels; default: all (a full-set report
+# of all of them with sources imported is ~85 MB — more than one gpurun call brings back)
+which = os.environ.get("TARGETS", "all")
+TC = ("gemm", "flash", "mxfp8", "lm head")
+selected = [(n_, f_) for n_, f_ in ops() if which == "all" or (which == "tc") == n_.startswith(TC)]
+for name, fn in selected:
     for _ in range(2):
         fn()
 torch.cuda.synchronize()
 torch.cuda.profiler.start()
-for name, fn in ops():
+for name, fn in selected:
     fn()
 torch.cuda.synchronize()
 torch.cuda.profiler.stop()

@@ -1,0 +1,114 @@
+"""Adapters for optional libraries (DeepSpeed config objects, bitsandbytes plumbing, torchao / TransformerEngine guards): the parts that
+run without those libraries installed."""
+
+import base64
+import json
+
+import pytest
+import torch
+import torch.nn as nn
+
+from accelerate_hpc_test_b200.utils import ao, bnb, transformer_engine
+from accelerate_hpc_test_b200.utils.deepspeed import DummyOptim, DummyScheduler, HfDeepSpeedConfig, map_pytorch_optim_to_deepspeed
+from accelerate_hpc_test_b200.utils.imports import is_torchao_available, is_transformer_engine_available
+
+ZERO3 = {"zero_optimization": {"stage": 3, "offload_param": {"device": "cpu"}, "overlap_comm": True, "contiguous_gradients": False},
+         "bf16": {"enabled": True}, "train_batch_size": "auto"}
+
+
+def test_deepspeed_config_sources(tmp_path):
+    from_dict = HfDeepSpeedConfig(ZERO3)
+    assert from_dict.config == ZERO3 and from_dict.config is not ZERO3
+    path = tmp_path / "ds.json"
+    path.write_text(json.dumps(ZERO3))
+    assert HfDeepSpeedConfig(str(path)).config == ZERO3
+    encoded = base64.urlsafe_b64encode(json.dumps(ZERO3).encode()).decode()
+    assert HfDeepSpeedConfig(encoded).config == ZERO3
+    with pytest.raises(ValueError, match="Expected a string path"):
+        HfDeepSpeedConfig("definitely-not-a-config")
+
+
+def test_deepspeed_config_paths_and_flags():
+    cfg = HfDeepSpeedConfig(ZERO3)
+    assert cfg.get_value("zero_optimization.stage") == 3 and cfg.get_value("zero_optimization.nothing", 7) == 7
+    assert cfg.get_value("no.such.path") is None and cfg.get_value("train_batch_size") == "auto"
+    assert cfg.is_zero3() and not cfg.is_zero2() and cfg.is_offload()
+    assert cfg.is_true("zero_optimization.overlap_comm") and not cfg.is_false("zero_optimization.overlap_comm")
+    assert cfg.is_false("zero_optimization.contiguous_gradients") and not cfg.is_true("zero_optimization.contiguous_gradients")
+    assert not cfg.is_true("zero_optimization.absent") and not cfg.is_false("zero_optimization.absent")
+    holder, leaf = cfg.find_config_node("zero_optimization.offload_param.device")
+    assert holder == {"device": "cpu"} and leaf == "device"
+    cfg.del_config_sub_tree("zero_optimization.offload_param")
+    assert "offload_param" not in cfg.config["zero_optimization"]
+    cfg.del_config_sub_tree("zero_optimization.offload_param")  # absent: fine unless it must exist
+    with pytest.raises(ValueError, match="Can't find"):
+        cfg.del_config_sub_tree("zero_optimization.offload_param", must_exist=True)
+    cfg.set_stage_and_offload()
+    assert not cfg.is_offload()
+    stage2 = HfDeepSpeedConfig({"zero_optimization": {"stage": 2, "offload_optimizer": {"device": "nvme"}}})
+    assert stage2.is_zero2() and stage2.is_offload()
+    assert not HfDeepSpeedConfig({"zero_optimization": {"stage": 1, "offload_optimizer": {"device": "cpu"}}}).is_offload()
+
+
+def test_dummy_optimizer_and_scheduler_materialize():
+    layer = nn.Linear(4, 4)
+    placeholder = DummyOptim(layer.parameters(), lr=0.5, weight_decay=0.1, betas=(0.8, 0.9), unknown=1)
+    opt = placeholder.materialize()
+    group = opt.param_groups[0]
+    assert group["lr"] == 0.5 and group["weight_decay"] == 0.1 and tuple(group["betas"]) == (0.8, 0.9)
+    sched = DummyScheduler(opt, total_num_steps=10, warmup_num_steps=2).materialize(opt)
+    rates = []
+    for _ in range(10):
+        rates.append(opt.param_groups[0]["lr"])
+        opt.step()
+        sched.step()
+    assert rates[0] == 0.0 and rates[1] == 0.25 and rates[2] == 0.5 and rates[-1] < rates[3]
+    custom = DummyScheduler(opt, lr_scheduler_callable=lambda o: torch.optim.lr_scheduler.ConstantLR(o, factor=1.0)).materialize(opt)
+    assert isinstance(custom, torch.optim.lr_scheduler.ConstantLR)
+    mapped = map_pytorch_optim_to_deepspeed(torch.optim.AdamW(layer.parameters(), lr=0.25, weight_decay=0.0))
+    assert type(mapped).__name__ == "FusedAdamW" and mapped.param_groups[0]["lr"] == 0.25
+
+
+class Tiny(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.embed = nn.Embedding(8, 16)
+        self.body = nn.Sequential(nn.Linear(16, 32), nn.Linear(32, 16), nn.Linear(16, 10))
+        self.lm_head = nn.Linear(16, 8, bias=False)
+
+
+def test_bnb_exclusion_rules():
+    model = Tiny()
+    assert bnb.get_keys_to_not_convert(model) == ["lm_head"]
+    model.lm_head.weight = model.embed.weight
+    assert bnb.get_keys_to_not_convert(model) == ["embed", "lm_head"]
+    assert bnb._excluded("model.lm_head.proj", ["lm_head"]) and bnb._excluded("lm_head", ["lm_head"])
+    assert not bnb._excluded("model.lm_headless", ["lm_head"])
+    assert not bnb.has_4bit_bnb_layers(model)
+    cfg = bnb.BnbQuantizationConfig(load_in_8bit=True)
+    with pytest.raises(ImportError, match="not compatible with 8bit"):
+        bnb.load_and_quantize_model(model, cfg)
+
+
+def test_ao_filters():
+    model = Tiny()
+    assert ao.find_first_last_linear_layers(model) == ("body.0", "lm_head")
+    assert ao.find_first_last_linear_layers(nn.ReLU()) == (None, None)
+    assert ao.filter_linear_layers(model.body[1], "body.1", ["body.0", "lm_head"])
+    assert not ao.filter_linear_layers(model.body[0], "body.0", ["body.0", "lm_head"])
+    assert not ao.filter_linear_layers(model.body[2], "body.2", [])  # 10 output features: off the fp8 tile
+    assert ao.filter_linear_layers(nn.ReLU(), "act", [])
+    assert not ao.has_ao_layers(model) or is_torchao_available()
+    if not is_torchao_available():
+        with pytest.raises(ImportError, match="torchao is not installed"):
+            ao.convert_model_to_fp8_ao(model)
+
+
+def test_transformer_engine_guards():
+    model = Tiny()
+    assert not transformer_engine.has_transformer_engine_layers(model) or is_transformer_engine_available()
+    if not is_transformer_engine_available():
+        with pytest.raises(ImportError, match="transformer_engine"):
+            transformer_engine.convert_model(model)
+        with pytest.raises(ImportError, match="transformer_engine"):
+            transformer_engine.apply_fp8_autowrap(model, None)
