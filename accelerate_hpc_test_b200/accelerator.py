@@ -113,6 +113,22 @@ def _is_scheduler(x):
     return isinstance(x, LRScheduler)
 
 
+_UNSET = object()
+
+
+def _forwarded(owner: str, attribute: str, settable: bool = False, default=_UNSET):
+    """Property that reads (and optionally writes) ``self.<owner>.<attribute>``."""
+
+    def read(self):
+        target = getattr(self, owner)
+        return getattr(target, attribute) if default is _UNSET else getattr(target, attribute, default)
+
+    def write(self, value):
+        setattr(getattr(self, owner), attribute, value)
+
+    return property(read, write if settable else None)
+
+
 class Accelerator:
     """Creates the distributed state and wraps training objects.
 
@@ -337,93 +353,34 @@ class Accelerator:
     def deepspeed_plugin(self):
         return self.state.deepspeed_plugin
 
-    @property
-    def use_distributed(self):
-        return self.state.use_distributed
+    # read-only views of the process state, the dataloader configuration and the project configuration
+    use_distributed = _forwarded("state", "use_distributed")
+    distributed_type = _forwarded("state", "distributed_type")
+    num_processes = _forwarded("state", "num_processes")
+    process_index = _forwarded("state", "process_index")
+    local_process_index = _forwarded("state", "local_process_index")
+    device = _forwarded("state", "device")
+    is_main_process = _forwarded("state", "is_main_process")
+    is_local_main_process = _forwarded("state", "is_local_main_process")
+    mixed_precision = _forwarded("state", "mixed_precision")
+    is_fsdp2 = _forwarded("state", "is_fsdp2")
+    split_batches = _forwarded("dataloader_config", "split_batches")
+    dispatch_batches = _forwarded("dataloader_config", "dispatch_batches")
+    even_batches = _forwarded("dataloader_config", "even_batches", settable=True)
+    use_seedable_sampler = _forwarded("dataloader_config", "use_seedable_sampler")
+    non_blocking = _forwarded("dataloader_config", "non_blocking")
+    use_stateful_dataloader = _forwarded("dataloader_config", "use_stateful_dataloader", default=False)
+    project_dir = _forwarded("project_configuration", "project_dir")
+    logging_dir = _forwarded("project_configuration", "logging_dir")
+    save_iteration = _forwarded("project_configuration", "iteration")
 
     @property
     def multi_device(self):
         return self.use_distributed and self.distributed_type in (DistributedType.MULTI_GPU, DistributedType.MULTI_CPU)
 
     @property
-    def distributed_type(self):
-        return self.state.distributed_type
-
-    @property
-    def num_processes(self):
-        return self.state.num_processes
-
-    @property
-    def process_index(self):
-        return self.state.process_index
-
-    @property
-    def local_process_index(self):
-        return self.state.local_process_index
-
-    @property
-    def device(self):
-        return self.state.device
-
-    @property
-    def split_batches(self):
-        return self.dataloader_config.split_batches
-
-    @property
-    def dispatch_batches(self):
-        return self.dataloader_config.dispatch_batches
-
-    @property
-    def even_batches(self):
-        return self.dataloader_config.even_batches
-
-    @even_batches.setter
-    def even_batches(self, value: bool):
-        self.dataloader_config.even_batches = value
-
-    @property
-    def use_seedable_sampler(self):
-        return self.dataloader_config.use_seedable_sampler
-
-    @property
-    def non_blocking(self):
-        return self.dataloader_config.non_blocking
-
-    @property
-    def use_stateful_dataloader(self):
-        return getattr(self.dataloader_config, "use_stateful_dataloader", False)
-
-    @property
-    def project_dir(self):
-        return self.project_configuration.project_dir
-
-    @property
-    def logging_dir(self):
-        return self.project_configuration.logging_dir
-
-    @property
-    def save_iteration(self):
-        return self.project_configuration.iteration
-
-    @property
-    def is_main_process(self):
-        return self.state.is_main_process
-
-    @property
-    def is_local_main_process(self):
-        return self.state.is_local_main_process
-
-    @property
     def is_last_process(self):
         return self.process_index == self.num_processes - 1
-
-    @property
-    def mixed_precision(self):
-        return self.state.mixed_precision
-
-    @property
-    def is_fsdp2(self):
-        return self.state.is_fsdp2
 
     @property
     def is_composable_parallelism_enabled(self):
@@ -1185,140 +1142,132 @@ class Accelerator:
 
     def register_for_checkpointing(self, *objects):
         """Track extra objects (with ``state_dict`` / ``load_state_dict``) in ``save_state`` / ``load_state``."""
-        invalid_objects = []
-        for obj in objects:
-            if not hasattr(obj, "state_dict") or not hasattr(obj, "load_state_dict"):
-                invalid_objects.append(obj)
-        if len(invalid_objects) > 0:
-            err = "All `objects` must include a `state_dict` and `load_state_dict` function to be stored. The following inputs are invalid:"
-            for index, obj in enumerate(invalid_objects):
-                err += f"\n\t- Item at index {index}, `{get_pretty_name(obj)}`"
-            raise ValueError(err)
+        rejected = [obj for obj in objects if not (hasattr(obj, "state_dict") and hasattr(obj, "load_state_dict"))]
+        if rejected:
+            listing = "".join(f"\n\t- Item at index {i}, `{get_pretty_name(obj)}`" for i, obj in enumerate(rejected))
+            raise ValueError("All `objects` must include a `state_dict` and `load_state_dict` function to be stored. The following inputs "
+                             f"are invalid:{listing}")
         self._custom_objects.extend(objects)
 
     # ================================================================== save_state / load_state
+    @staticmethod
+    def _checkpoint_number(folder: str) -> int:
+        """``.../checkpoint_12`` -> 12 (the last run of digits of the last path component)."""
+        return int(re.findall(r"(\d+)", os.path.basename(os.path.normpath(folder)))[-1])
+
+    def _numbered_checkpoints(self) -> list:
+        """Existing ``<project_dir>/checkpoints/*`` folders, oldest first."""
+        root = os.path.join(self.project_dir, "checkpoints")
+        return sorted((os.path.join(root, name) for name in os.listdir(root)), key=self._checkpoint_number)
+
+    def _claim_checkpoint_dir(self, output_dir: Optional[str]) -> str:
+        """Where this ``save_state`` writes.  Under automatic naming: ``checkpoints/checkpoint_<iteration>``, after the oldest
+        checkpoints were removed to respect ``total_limit``."""
+        cfg = self.project_configuration
+        if not cfg.automatic_checkpoint_naming:
+            os.makedirs(output_dir, exist_ok=True)
+            return output_dir
+        os.makedirs(os.path.join(self.project_dir, "checkpoints"), exist_ok=True)
+        existing = self._numbered_checkpoints()
+        surplus = 0 if cfg.total_limit is None else len(existing) + 1 - cfg.total_limit
+        if surplus > 0 and self.is_main_process:
+            logger.warning(f"Deleting {surplus} checkpoints to make room for new checkpoint.")
+            for folder in existing[:surplus]:
+                shutil.rmtree(folder, ignore_errors=True)
+        target = os.path.join(self.project_dir, "checkpoints", f"checkpoint_{self.save_iteration}")
+        if os.path.exists(target):
+            raise ValueError(f"Checkpoint directory {target} ({self.save_iteration}) already exists. Please manually override "
+                             "`self.save_iteration` with what iteration to start with.")
+        self.wait_for_everyone()
+        os.makedirs(target, exist_ok=True)
+        return target
+
+    def _sharded_optimizer_io(self, opt, index: int, folder: str, save: bool) -> bool:
+        """Optimizers whose state is sharded go through their engine (native) or DCP (torch FSDP2).  True when handled."""
+        from .utils.fsdp_utils import load_fsdp_optimizer, save_fsdp_optimizer
+
+        engine = getattr(opt, "_engine", None)
+        method = "save_sharded_optimizer" if save else "load_sharded_optimizer"
+        if engine is not None and hasattr(engine, method):
+            getattr(engine, method)(opt, folder, index, self.state.fsdp_plugin)
+            return True
+        torch_fsdp2 = [m for m in self._models if getattr(m, "_b200_torch_fsdp2", False)]
+        if torch_fsdp2:
+            (save_fsdp_optimizer if save else load_fsdp_optimizer)(self.state.fsdp_plugin, self, opt, torch_fsdp2[0], folder, index)
+            return True
+        return False
+
+    @staticmethod
+    def _is_sharded_model(model) -> bool:
+        return hasattr(model, "save_sharded_state") or getattr(model, "_b200_torch_fsdp2", False)
+
     def save_state(self, output_dir: Optional[str] = None, safe_serialization: bool = True, **save_model_func_kwargs):
         """Checkpoint everything ``prepare`` saw (plus registered objects and RNG state) under ``output_dir``."""
-        if self.project_configuration.automatic_checkpoint_naming:
-            output_dir = os.path.join(self.project_dir, "checkpoints")
-        os.makedirs(output_dir, exist_ok=True)
-        if self.project_configuration.automatic_checkpoint_naming:
-            folders = [os.path.join(output_dir, folder) for folder in os.listdir(output_dir)]
-            if self.project_configuration.total_limit is not None and (len(folders) + 1 > self.project_configuration.total_limit) and self.is_main_process:
-                def _inner(folder):
-                    return list(map(int, re.findall(r"[\/]?([0-9]+)(?=[^\/]*$)", folder)))[0]
+        from .utils.fsdp_utils import save_fsdp_model
 
-                folders.sort(key=_inner)
-                logger.warning(f"Deleting {len(folders) + 1 - self.project_configuration.total_limit} checkpoints to make room for new checkpoint.")
-                for folder in folders[: len(folders) + 1 - self.project_configuration.total_limit]:
-                    shutil.rmtree(folder, ignore_errors=True)
-            output_dir = os.path.join(output_dir, f"checkpoint_{self.save_iteration}")
-            if os.path.exists(output_dir):
-                raise ValueError(f"Checkpoint directory {output_dir} ({self.save_iteration}) already exists. Please manually override `self.save_iteration` with what iteration to start with.")
-            self.wait_for_everyone()
-        os.makedirs(output_dir, exist_ok=True)
+        output_dir = self._claim_checkpoint_dir(output_dir)
         logger.info(f"Saving current state to {output_dir}")
-
         weights = []
-        sharded_models = []
-        from .utils.fsdp_utils import load_fsdp_model, load_fsdp_optimizer, save_fsdp_model, save_fsdp_optimizer  # noqa: F401
-
-        torch_fsdp2 = [m for m in self._models if getattr(m, "_b200_torch_fsdp2", False)]
         for i, model in enumerate(self._models):
-            if hasattr(model, "save_sharded_state") or getattr(model, "_b200_torch_fsdp2", False):
+            if self._is_sharded_model(model):
                 save_fsdp_model(self.state.fsdp_plugin, self, model, output_dir, i)
-                sharded_models.append(i)
                 logger.info(f"Sharded model saved to output dir {output_dir}")
             else:
                 weights.append(self.get_state_dict(model, unwrap=False))
-        optimizers = []
-        for i, opt in enumerate(self._optimizers):
-            engine = getattr(opt, "_engine", None)
-            if engine is not None and hasattr(engine, "save_sharded_optimizer"):
-                engine.save_sharded_optimizer(opt, output_dir, i, self.state.fsdp_plugin)
-                logger.info(f"Sharded optimizer state saved to output dir {output_dir}")
-            elif torch_fsdp2:
-                save_fsdp_optimizer(self.state.fsdp_plugin, self, opt, torch_fsdp2[0], output_dir, i)
-            else:
-                optimizers.append(opt)
-        schedulers = []
-        for scheduler in self._schedulers:
-            schedulers.append(scheduler)
-        dataloaders = self._dataloaders
+        plain_optimizers = [opt for i, opt in enumerate(self._optimizers) if not self._sharded_optimizer_io(opt, i, output_dir, save=True)]
         for hook in self._save_model_state_pre_hook.values():
             hook(self._models, weights, output_dir)
-        save_location = save_accelerator_state(
-            output_dir, weights, optimizers, schedulers, dataloaders, self.state.process_index, self.step, self.scaler,
-            save_on_each_node=self.project_configuration.save_on_each_node, safe_serialization=safe_serialization,
-        )
+        per_node = self.project_configuration.save_on_each_node
+        save_location = save_accelerator_state(output_dir, weights, plain_optimizers, list(self._schedulers), self._dataloaders,
+                                               self.state.process_index, self.step, self.scaler, save_on_each_node=per_node,
+                                               safe_serialization=safe_serialization)
         for i, obj in enumerate(self._custom_objects):
-            save_custom_state(obj, output_dir, i, save_on_each_node=self.project_configuration.save_on_each_node)
+            save_custom_state(obj, output_dir, i, save_on_each_node=per_node)
         self.project_configuration.iteration += 1
         return save_location
 
-    def load_state(self, input_dir: Optional[str] = None, load_kwargs: Optional[dict] = None, **load_model_func_kwargs):
-        """Restore what :meth:`save_state` wrote (latest ``checkpoint_N`` under automatic naming)."""
+    def _find_checkpoint_dir(self, input_dir: Optional[str]) -> str:
         if input_dir is not None:
             input_dir = os.path.expanduser(input_dir)
             if not os.path.isdir(input_dir):
                 raise ValueError(f"Tried to find {input_dir} but folder does not exist")
-        elif self.project_configuration.automatic_checkpoint_naming:
-            input_dir = os.path.join(self.project_dir, "checkpoints")
-            folders = [os.path.join(input_dir, folder) for folder in os.listdir(input_dir)]
-
-            def _inner(folder):
-                return list(map(int, re.findall(r"[\/]?([0-9]+)(?=[^\/]*$)", folder)))[0]
-
-            folders.sort(key=_inner)
-            input_dir = folders[-1]
-        else:
+            return input_dir
+        if not self.project_configuration.automatic_checkpoint_naming:
             raise ValueError("No input_dir provided and automatic checkpoint naming is disabled.")
+        return self._numbered_checkpoints()[-1]
+
+    def load_state(self, input_dir: Optional[str] = None, load_kwargs: Optional[dict] = None, **load_model_func_kwargs):
+        """Restore what :meth:`save_state` wrote (latest ``checkpoint_N`` under automatic naming)."""
+        from .utils.fsdp_utils import load_fsdp_model
+
+        input_dir = self._find_checkpoint_dir(input_dir)
         logger.info(f"Loading states from {input_dir}")
-
-        models = []
-        from .utils.fsdp_utils import load_fsdp_model, load_fsdp_optimizer
-
-        torch_fsdp2 = [m for m in self._models if getattr(m, "_b200_torch_fsdp2", False)]
+        plain_models = []
         for i, model in enumerate(self._models):
-            if hasattr(model, "load_sharded_state") or getattr(model, "_b200_torch_fsdp2", False):
+            if self._is_sharded_model(model) or hasattr(model, "load_sharded_state"):
                 load_fsdp_model(self.state.fsdp_plugin, self, model, input_dir, i)
                 logger.info(f"Sharded model loaded from input dir {input_dir}")
             else:
-                models.append(model)
-        optimizers = []
-        for i, opt in enumerate(self._optimizers):
-            engine = getattr(opt, "_engine", None)
-            if engine is not None and hasattr(engine, "load_sharded_optimizer"):
-                engine.load_sharded_optimizer(opt, input_dir, i, self.state.fsdp_plugin)
-            elif torch_fsdp2:
-                load_fsdp_optimizer(self.state.fsdp_plugin, self, opt, torch_fsdp2[0], input_dir, i)
-            else:
-                optimizers.append(opt)
-        schedulers = list(self._schedulers)
-        dataloaders = self._dataloaders
+                plain_models.append(model)
+        plain_optimizers = [opt for i, opt in enumerate(self._optimizers) if not self._sharded_optimizer_io(opt, i, input_dir, save=False)]
         for hook in self._load_model_state_pre_hook.values():
-            hook(models, input_dir)
+            hook(plain_models, input_dir)
         map_location = load_model_func_kwargs.pop("map_location", None)
         if map_location is None:
-            if self.num_processes > 1 and self.multi_device and self.distributed_type != DistributedType.MULTI_CPU:
-                map_location = "on_device"
-            else:
-                map_location = "cpu"
-        override_attributes = load_accelerator_state(
-            input_dir, models, optimizers, schedulers, dataloaders, self.state.process_index, self.scaler, map_location,
-            load_kwargs, **load_model_func_kwargs,
-        )
-        if "step" in override_attributes:
-            self.step = override_attributes["step"]
-        custom_checkpoints = [f for f in os.listdir(input_dir) if re.search(r"^custom_checkpoint_\d+\.pkl$", f) is not None]
-        if len(custom_checkpoints) != len(self._custom_objects):
-            err = f"Number of custom checkpoints in folder {input_dir} does not match the number of registered objects:"
-            err += f"\n\tFound checkpoints: {len(custom_checkpoints)}"
-            err += f"\n\tRegistered objects: {len(self._custom_objects)}\n"
-            err += "Please make sure to only load checkpoints from folders that were created with the same set of registered objects,"
-            err += "or avoid using `custom_checkpoint` in the filename for files in that same directory and load them in manually."
-            raise RuntimeError(err)
-        logger.info(f"Loading in {len(custom_checkpoints)} custom states")
+            on_gpus = self.num_processes > 1 and self.multi_device and self.distributed_type != DistributedType.MULTI_CPU
+            map_location = "on_device" if on_gpus else "cpu"
+        restored = load_accelerator_state(input_dir, plain_models, plain_optimizers, list(self._schedulers), self._dataloaders,
+                                          self.state.process_index, self.scaler, map_location, load_kwargs, **load_model_func_kwargs)
+        self.step = restored.get("step", self.step)
+        found = sum(1 for name in os.listdir(input_dir) if re.fullmatch(r"custom_checkpoint_\d+\.pkl", name))
+        if found != len(self._custom_objects):
+            raise RuntimeError(
+                f"Number of custom checkpoints in folder {input_dir} does not match the number of registered objects:"
+                f"\n\tFound checkpoints: {found}\n\tRegistered objects: {len(self._custom_objects)}\n"
+                "Please make sure to only load checkpoints from folders that were created with the same set of registered objects,"
+                "or avoid using `custom_checkpoint` in the filename for files in that same directory and load them in manually."
+            )
+        logger.info(f"Loading in {found} custom states")
         for index, obj in enumerate(self._custom_objects):
             load_custom_state(obj, input_dir, index)
 
