@@ -315,6 +315,27 @@ add_inplace_bf16_kernel(__nv_bfloat16* __restrict__ y, const __nv_bfloat16* __re
   }
 }
 
+// out (+)= in * (*scale): the scale lives on the device (an upstream gradient, a clip coefficient), so no host sync
+__global__ void __launch_bounds__(256)
+scale_by_scalar_bf16_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, long long nvec,
+                            const float* __restrict__ scale, int accumulate) {
+  const float s = *scale;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
+       i += (long long)gridDim.x * blockDim.x) {
+    const uint4 v = ld_nc_v4(reinterpret_cast<const uint4*>(in) + i);
+    float2 b0 = bf2_to_f2(v.x), b1 = bf2_to_f2(v.y), b2 = bf2_to_f2(v.z), b3 = bf2_to_f2(v.w);
+    b0.x *= s; b0.y *= s; b1.x *= s; b1.y *= s; b2.x *= s; b2.y *= s; b3.x *= s; b3.y *= s;
+    if (accumulate) {
+      const uint4 u = ld_v4(reinterpret_cast<const uint4*>(out) + i);
+      const float2 a0 = bf2_to_f2(u.x), a1 = bf2_to_f2(u.y), a2 = bf2_to_f2(u.z), a3 = bf2_to_f2(u.w);
+      b0.x += a0.x; b0.y += a0.y; b1.x += a1.x; b1.y += a1.y; b2.x += a2.x; b2.y += a2.y; b3.x += a3.x; b3.y += a3.y;
+    }
+    uint4 o;
+    o.x = f2_to_bf2(b0.x, b0.y); o.y = f2_to_bf2(b1.x, b1.y); o.z = f2_to_bf2(b2.x, b2.y); o.w = f2_to_bf2(b3.x, b3.y);
+    st_v4(reinterpret_cast<uint4*>(out) + i, o);
+  }
+}
+
 int num_sms();
 
 }  // namespace b200
@@ -442,6 +463,16 @@ B200_API int b200_scale_cast(const void* in, void* out, long long n, float scale
     case 3: scale_cast_kernel<__nv_bfloat16, __nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, scale); break;
     default: return B200_ERR_BAD_ARG;
   }
+  b200_count_launch();
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+B200_API int b200_scale_by_scalar_bf16(const void* in, void* out, long long n, const void* scale, int accumulate, void* stream) {
+  if (n % 8 || scale == nullptr || (reinterpret_cast<uintptr_t>(in) & 15) || (reinterpret_cast<uintptr_t>(out) & 15)) return B200_ERR_BAD_ARG;
+  if (n == 0) return 0;
+  scale_by_scalar_bf16_kernel<<<ew_grid(n / 8), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, n / 8,
+                                                                               (const float*)scale, accumulate);
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;

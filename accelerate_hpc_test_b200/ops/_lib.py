@@ -56,6 +56,7 @@ _SIGNATURES = {
     "b200_embedding_bwd": [P, P, P, L, I, L, P],
     "b200_scale_cast": [P, P, L, F, I, P],
     "b200_add_inplace_bf16": [P, P, L, P],
+    "b200_scale_by_scalar_bf16": [P, P, L, P, I, P],
     "b200_adamw_flat": [P, P, P, P, P, L, I, F, F, F, F, F, I, F, P, P, P],
     "b200_adamw_multi": [P, I, L, I, F, F, F, F, F, I, F, P, P, P],
     "b200_sumsq": [P, L, I, P, P],

@@ -492,6 +492,20 @@ def cross_entropy_chunk_(logits: torch.Tensor, labels: torch.Tensor, inv_count: 
     return loss_rows
 
 
+def _scale_by_device_scalar(src: torch.Tensor, dst: torch.Tensor, scale: torch.Tensor, accumulate: bool) -> torch.Tensor:
+    """``dst (+)= src * scale`` with ``scale`` a 0-dim fp32 tensor on the same device (never read by the host)."""
+    fast = (_on_gpu(src) and src.dtype == BF16 and dst.dtype == BF16 and src.is_contiguous() and dst.is_contiguous()
+            and src.numel() % 8 == 0 and src.data_ptr() % 16 == 0 and dst.data_ptr() % 16 == 0 and scale.dtype == torch.float32)
+    if not fast:
+        s = scale.to(src.dtype)
+        if accumulate:
+            return dst.add_(src * s)
+        return src.mul_(s) if dst is src else torch.mul(src, s, out=dst)
+    lib = _lib.require_gpu_lib()
+    check(lib.b200_scale_by_scalar_bf16(ptr(src), ptr(dst), src.numel(), ptr(scale.reshape(1)), int(accumulate), cur_stream()), "scale_by_scalar")
+    return dst
+
+
 class _FusedLinearCEFn(torch.autograd.Function):
     """mean CE(h W^T, labels) without ever holding full logits: per token-chunk GEMM -> CE(+grad in
     place) -> dgrad / wgrad GEMMs.  Gradients are produced in forward and scaled in backward."""
@@ -546,17 +560,12 @@ class _FusedLinearCEFn(torch.autograd.Function):
     def backward(ctx, dloss):
         dh, dw = ctx.saved_tensors
         g = dloss.to(torch.float32)
-        # upstream scale (1/GA from Accelerator.backward, loss scaling): one cheap pass
-        dh = dh.mul_(g.to(dh.dtype)) if ctx.needs_input_grad[0] else None
+        # upstream scale (1/GA from Accelerator.backward, loss scaling): one pass, the scale is read on the device
+        dh = _scale_by_device_scalar(dh, dh, g, False) if ctx.needs_input_grad[0] else None
         if ctx.needs_input_grad[1]:
-            gw = g.to(dw.dtype)
 
             def compute(out, acc):
-                if out is None:
-                    return dw.mul_(gw)
-                if acc:
-                    return out.add_(dw * gw)
-                return torch.mul(dw, gw, out=out)
+                return _scale_by_device_scalar(dw, dw if out is None else out, g, acc and out is not None)
 
             dw = deliver_weight_grad(ctx.weight, compute)
         else:

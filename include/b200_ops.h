@@ -133,6 +133,8 @@ int b200_embedding_fwd(const void* ids, const void* table, void* out, long long 
 int b200_embedding_bwd(const void* ids, const void* dout, void* dtable, long long T, int H, long long vocab, void* stream);
 int b200_scale_cast(const void* in, void* out, long long n, float scale, int kind, void* stream); /* 0 f32->bf16 1 bf16->f32 2 f32 3 bf16 */
 int b200_add_inplace_bf16(void* y, const void* a, long long n, void* stream);
+/* out (+)= in * (*scale), bf16, n % 8 == 0, 16-byte aligned pointers; `scale` is a device fp32 scalar (no host sync) */
+int b200_scale_by_scalar_bf16(const void* in, void* out, long long n, const void* scale, int accumulate, void* stream);
 
 /* ---- K8: cross-entropy over a logits chunk, forward + in-place gradient (csrc/cross_entropy.cu) */
 int b200_ce_fwd_bwd(void* logits, const void* labels, void* loss_rows, void* lse_rows, long long T, long long ld, int V,
