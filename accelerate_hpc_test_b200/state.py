@@ -379,6 +379,19 @@ class PartialState:
         raise AttributeError(f"'PartialState' object has no attribute '{name}'")
 
 
+def _from_partial_state(name: str, call: bool = False):
+    """Class attribute of ``AcceleratorState`` that defers to the ``PartialState`` singleton: a read-only property, or (``call``)
+    a method with the same signature."""
+    if not call:
+        return property(lambda self: getattr(PartialState(), name))
+
+    def method(self, *args, **kwargs):
+        return getattr(PartialState(), name)(*args, **kwargs)
+
+    method.__name__ = name
+    return method
+
+
 class AcceleratorState:
     """Everything in ``PartialState`` plus the training configuration: mixed precision, plugins,
     ``ParallelismConfig`` and the device mesh (reference src/accelerate/state.py:863-1240)."""
@@ -481,54 +494,22 @@ class AcceleratorState:
         if reset_partial_state:
             PartialState._reset_state()
 
-    # passthroughs -----------------------------------------------------------------------------
-    def destroy_process_group(self, group=None):
-        PartialState().destroy_process_group(group)
-
-    @property
-    def fork_launched(self):
-        return PartialState().fork_launched
-
-    @property
-    def use_distributed(self):
-        return PartialState().use_distributed
+    # everything about the process group itself is answered by PartialState ---------------------------------
+    fork_launched = _from_partial_state("fork_launched")
+    use_distributed = _from_partial_state("use_distributed")
+    is_last_process = _from_partial_state("is_last_process")
+    is_main_process = _from_partial_state("is_main_process")
+    is_local_main_process = _from_partial_state("is_local_main_process")
+    destroy_process_group = _from_partial_state("destroy_process_group", call=True)
+    wait_for_everyone = _from_partial_state("wait_for_everyone", call=True)
+    split_between_processes = _from_partial_state("split_between_processes", call=True)  # these three return context managers
+    main_process_first = _from_partial_state("main_process_first", call=True)
+    local_main_process_first = _from_partial_state("local_main_process_first", call=True)
+    print = _from_partial_state("print", call=True)
 
     @property
     def is_fsdp2(self) -> bool:
         return self.distributed_type == DistributedType.FSDP and self.fsdp_plugin is not None and self.fsdp_plugin.fsdp_version == 2
-
-    @property
-    def is_last_process(self) -> bool:
-        return PartialState().is_last_process
-
-    @property
-    def is_main_process(self) -> bool:
-        return PartialState().is_main_process
-
-    @property
-    def is_local_main_process(self) -> bool:
-        return PartialState().is_local_main_process
-
-    def wait_for_everyone(self):
-        PartialState().wait_for_everyone()
-
-    @contextmanager
-    def split_between_processes(self, inputs, apply_padding: bool = False):
-        with PartialState().split_between_processes(inputs, apply_padding=apply_padding) as inputs:
-            yield inputs
-
-    @contextmanager
-    def main_process_first(self):
-        with PartialState().main_process_first():
-            yield
-
-    @contextmanager
-    def local_main_process_first(self):
-        with PartialState().local_main_process_first():
-            yield
-
-    def print(self, *args, **kwargs):
-        PartialState().print(*args, **kwargs)
 
     # DeepSpeed plugin registry ----------------------------------------------------------------
     @property
@@ -555,6 +536,10 @@ class AcceleratorState:
         raise AttributeError(f"'AcceleratorState' object has no attribute '{name}'")
 
 
+def _plugin_setting(key: str, default):
+    return property(lambda self: self.plugin_kwargs.get(key, default))
+
+
 class GradientState:
     """Gradient-accumulation bookkeeping shared by the Accelerator, optimizers, schedulers and dataloaders.
 
@@ -577,45 +562,34 @@ class GradientState:
         if gradient_accumulation_plugin is not None and self.plugin_kwargs != gradient_accumulation_plugin.to_kwargs():
             self.plugin_kwargs = gradient_accumulation_plugin.to_kwargs()
 
-    @property
-    def num_steps(self) -> int:
-        return self.plugin_kwargs.get("num_steps", 1)
-
-    @property
-    def adjust_scheduler(self) -> bool:
-        return self.plugin_kwargs.get("adjust_scheduler", False)
-
-    @property
-    def sync_with_dataloader(self) -> bool:
-        return self.plugin_kwargs.get("sync_with_dataloader", True)
-
-    @property
-    def sync_each_batch(self) -> bool:
-        return self.plugin_kwargs.get("sync_each_batch", False)
+    # the plugin's settings, with the defaults that apply when no plugin was given
+    num_steps = _plugin_setting("num_steps", 1)
+    adjust_scheduler = _plugin_setting("adjust_scheduler", False)
+    sync_with_dataloader = _plugin_setting("sync_with_dataloader", True)
+    sync_each_batch = _plugin_setting("sync_each_batch", False)
 
     @property
     def initialized(self) -> bool:
-        return GradientState._shared_state != {}
+        return bool(GradientState._shared_state)
+
+    @property
+    def in_dataloader(self) -> bool:
+        return self.active_dataloader is not None
 
     @property
     def end_of_dataloader(self) -> bool:
-        if not self.in_dataloader:
-            return False
-        return self.active_dataloader.end_of_dataloader
+        """Is the innermost active dataloader handing out its last batch?  False outside of any dataloader."""
+        return self.in_dataloader and self.active_dataloader.end_of_dataloader
 
     @property
     def remainder(self) -> int:
-        if not self.in_dataloader:
-            return -1
-        return self.active_dataloader.remainder
+        """Real samples in the last global batch of the active dataloader (-1: unknown or not iterating)."""
+        return self.active_dataloader.remainder if self.in_dataloader else -1
 
     def __repr__(self):
-        return (
-            f"Sync Gradients: {self.sync_gradients}\n"
-            f"At end of current dataloader: {self.end_of_dataloader}\n"
-            f"Extra samples added: {self.remainder}\n"
-            f"Gradient accumulation plugin: {self.plugin_kwargs}\n"
-        )
+        facts = {"Sync Gradients": self.sync_gradients, "At end of current dataloader": self.end_of_dataloader,
+                 "Extra samples added": self.remainder, "Gradient accumulation plugin": self.plugin_kwargs}
+        return "".join(f"{label}: {value}\n" for label, value in facts.items())
 
     @property
     def is_xla_gradients_synced(self):
@@ -642,10 +616,6 @@ class GradientState:
                     break
         last = refs[-1]
         self.active_dataloader = last() if last is not None else None
-
-    @property
-    def in_dataloader(self) -> bool:
-        return self.active_dataloader is not None
 
     @staticmethod
     def _reset_state():

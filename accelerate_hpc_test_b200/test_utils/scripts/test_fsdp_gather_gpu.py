@@ -16,7 +16,7 @@ import torch.distributed as dist
 from accelerate_hpc_test_b200.ops import functional as F
 from accelerate_hpc_test_b200.ops._lib import check, cur_stream, ptr
 from accelerate_hpc_test_b200.parallel.symm import SymmetricWorkspace
-from accelerate_hpc_test_b200.utils.diagnostics import sample_clocks
+from accelerate_hpc_test_b200.utils.diagnostics import ClockProbe
 
 
 def log(*a):
@@ -29,6 +29,27 @@ def rel(a, b):
     return ((a - b).norm() / b.norm().clamp(min=1e-12)).item()
 
 
+_PROBE = None
+
+
+class sample_clocks:
+    """NVML clock / power / throttle samples taken while the timed launches of the block are in flight (the kernels are far
+    shorter than the 200 ms period nvidia-smi polls at)."""
+
+    def __enter__(self):
+        global _PROBE
+        if _PROBE is None:
+            _PROBE = ClockProbe()
+        _PROBE.reset()
+        return self
+
+    def __exit__(self, *exc):
+        return False
+
+    def summary(self):
+        return _PROBE.summary()
+
+
 def timed(fn, iters=10, warm=3):
     for _ in range(warm):
         fn()
@@ -38,6 +59,8 @@ def timed(fn, iters=10, warm=3):
     s.record()
     for _ in range(iters):
         fn()
+        if _PROBE is not None:
+            _PROBE.sample()
     e.record()
     torch.cuda.synchronize()
     t = torch.tensor([s.elapsed_time(e) / iters], device="cuda")
