@@ -100,6 +100,9 @@ class B200DataParallel(nn.Module):
         algo = os.environ.get("ACCELERATE_B200_ALLREDUCE", "auto")
         if algo == "auto":
             algo = "nvls" if self.world >= 4 else "tma"
+        # CTAs of the in-switch all-reduce: it runs beside the backward GEMMs, so it should hold as few SM slots as still fill the links
+        self._ar_ctas = int(os.environ.get("ACCELERATE_B200_DDP_AR_CTAS", "16"))
+        self._tma_ctas = int(os.environ.get("ACCELERATE_B200_DDP_TMA_CTAS", "148"))
         self._tma_allreduce = algo in ("tma", "nvls")
         self._nvls_allreduce = algo == "nvls"
         self._buckets: list[_Bucket] = []
@@ -215,10 +218,10 @@ class B200DataParallel(nn.Module):
         with torch.cuda.stream(self.comm_stream):
             if b.dtype == torch.bfloat16 and self.ws.has_multicast and self._nvls_allreduce:
                 # the NVSwitch sums the 8 copies and multicasts the result: one pass over the bucket, no shared-memory staging
-                self.ws.allreduce_nvls_(b.offset_bytes, b.padded, 1.0 / self.world, b.ch_arrive, b.ch_done, stream=self.comm_stream)
+                self.ws.allreduce_nvls_(b.offset_bytes, b.padded, 1.0 / self.world, b.ch_arrive, b.ch_done, ctas=self._ar_ctas, stream=self.comm_stream)
             elif b.dtype == torch.bfloat16 and self._tma_allreduce:
                 # TMA engine end to end (reduce my slice from all peers, then pull the other slices): ~1.5x the LSU kernel
-                self.ws.allreduce_tma_(b.offset_bytes, b.padded, 1.0 / self.world, (b.ch_arrive, b.ch_mid, b.ch_done), stream=self.comm_stream)
+                self.ws.allreduce_tma_(b.offset_bytes, b.padded, 1.0 / self.world, (b.ch_arrive, b.ch_mid, b.ch_done), ctas=self._tma_ctas, stream=self.comm_stream)
             else:
                 self.ws.allreduce_(b.offset_bytes, b.padded, b.dtype, 1.0 / self.world, b.ch_arrive, b.ch_done, stream=self.comm_stream)
             b.updated = False
