@@ -2,6 +2,7 @@
 // squared-gradient-norm reduction and the clip coefficient, all stream-ordered with no host sync.
 // the reference calls torch.optim.AdamW (multi-tensor ATen) and
 // torch.nn.utils.clip_grad_norm_ (reference src/accelerate/accelerator.py:2918-2979).
+#include <cstdlib>
 #include "common.cuh"
 
 namespace b200 {
@@ -182,6 +183,20 @@ static inline int flat_grid(long long n) {
   return (int)(g < cap ? (g > 0 ? g : 1) : cap);
 }
 
+// The update usually runs on a side stream beside the backward GEMMs (optimizer in backward): how many CTAs per SM it may take
+// is a trade between its own bandwidth and the SM slots / issue cycles it takes from them.  ACCELERATE_B200_ADAMW_CTAS_PER_SM.
+static inline int adamw_grid(long long n) {
+  static int per_sm = 0;
+  if (per_sm == 0) {
+    const char* e = getenv("ACCELERATE_B200_ADAMW_CTAS_PER_SM");
+    per_sm = e ? atoi(e) : 4;  // 1 GPU, 8B model: 212.5 / 209.9 / 215.3 / 230.9 ms per step with 8 / 4 / 2 / 1
+    if (per_sm < 1 || per_sm > 8) per_sm = 8;
+  }
+  long long g = (n / 4 + 255) / 256;
+  long long cap = (long long)num_sms() * per_sm;
+  return (int)(g < cap ? (g > 0 ? g : 1) : cap);
+}
+
 B200_API int b200_adamw_flat(void* master, void* m, void* v, const void* grad, void* shadow_bf16,
                              long long n, int grad_is_bf16, float lr, float beta1, float beta2, float eps,
                              float weight_decay, int step, float grad_scale, const void* clip_coef,
@@ -191,11 +206,11 @@ B200_API int b200_adamw_flat(void* master, void* m, void* v, const void* grad, v
              1.f - powf(beta2, (float)step), grad_scale};
   cudaStream_t st = (cudaStream_t)stream;
   if (grad_is_bf16)
-    adamw_flat_kernel<__nv_bfloat16><<<flat_grid(n), 256, 0, st>>>(
+    adamw_flat_kernel<__nv_bfloat16><<<adamw_grid(n), 256, 0, st>>>(
         (float*)master, (float*)m, (float*)v, (const __nv_bfloat16*)grad, (__nv_bfloat16*)shadow_bf16, n, a,
         (const float*)clip_coef, (const float*)found_inf);
   else
-    adamw_flat_kernel<float><<<flat_grid(n), 256, 0, st>>>((float*)master, (float*)m, (float*)v,
+    adamw_flat_kernel<float><<<adamw_grid(n), 256, 0, st>>>((float*)master, (float*)m, (float*)v,
                                                            (const float*)grad, (__nv_bfloat16*)shadow_bf16,
                                                            n, a, (const float*)clip_coef,
                                                            (const float*)found_inf);

@@ -58,6 +58,7 @@ def parse_args():
     ap.add_argument("--model", default=os.environ.get("BENCH_MODEL", "llama3-8b"), choices=list(MODELS))
     ap.add_argument("--seq-len", type=int, default=2048)
     ap.add_argument("--micro-batch", type=int, default=int(os.environ.get("BENCH_MICRO_BATCH", 2)))
+    ap.add_argument("--sweep", default="", help="diagnostic: engine_attribute=v1,v2,... re-times the step with each value (e.g. rs_ctas=32,64)")
     ap.add_argument("--parallelism", default="auto",
                     help="auto | ddp | fsdp | tpN | spN | cpN  (tp/sp/cp: N ranks per model-parallel group, the rest is dp_shard)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp8"], help="fp8: native e4m3 linear layers (ours arm)")
@@ -216,6 +217,20 @@ def run(args, build_fn):
     if info.get("exposed_comm") is not None and world > 1:
         exposed = info["exposed_comm"](step_device, dev_batches)
 
+    sweep = None
+    if args.sweep and info.get("engine") is not None:
+        # diagnostic (not part of the headline): re-time the same step with another CTA budget for the collective that runs
+        # beside backward, on this very box and model instance — "attr=v1,v2,..."
+        attr, _, values = args.sweep.partition("=")
+        engine, sweep = info["engine"], {"attribute": attr, "ms_per_step": {}}
+        original = getattr(engine, attr)
+        for v in [int(x) for x in values.split(",") if x]:
+            setattr(engine, attr, v)
+            for i in range(2):
+                step_device(dev_batches[i % n_host])
+            sweep["ms_per_step"][str(v)] = round(timed_loop(lambda i: step_device(dev_batches[i % n_host]), args.steps, world) / args.steps, 2)
+        setattr(engine, attr, original)
+
     if rank == 0:
         out = {
             "metric": "Llama-3-8B training tokens/s (whole job)" if args.model == "llama3-8b" else f"{args.model} training tokens/s",
@@ -234,6 +249,8 @@ def run(args, build_fn):
             "tflops_per_gpu": info.get("flops_per_token", 0) * value / world / 1e12 if info.get("flops_per_token") else None,
             "peak_mem_gb": torch.cuda.max_memory_allocated() / 2**30,
         }
+        if sweep is not None:
+            out["cta_sweep"] = sweep
         print(json.dumps(out), flush=True)
     if world > 1:
         torch.distributed.destroy_process_group()
@@ -321,7 +338,7 @@ def build_ours(args, cfg, rank, world, local):
 
     info = {"parallelism": names.get(par, f"{mp_kind}={mp} x fsdp2 dp_shard={world // mp}"), "exposed_comm": exposed_comm,
             "launch_count": _lib.launch_count, "flops_per_token": lcfg.flops_per_token(args.seq_len),
-            "model_parallel_size": mp, "shard_batch": shard_batch}
+            "model_parallel_size": mp, "shard_batch": shard_batch, "engine": model}
     return step_device, step_e2e, info
 
 
