@@ -348,8 +348,9 @@ class B200ShardedModule(nn.Module):
             self.ag_ctas = int(os.environ.get("ACCELERATE_B200_AG_CTAS", "148"))
             # the reduce-scatter (+AdamW) runs beside the backward GEMMs and each rank owns 1/world of a layer: it gets just enough
             # CTAs to finish under the next layer's backward and leaves the other SM slots to the GEMMs.  Measured ms/step:
-            # 2 GPUs 218.1 / 218.8 / 223.0 / 226.9 with 148 / 96 / 64 / 48 CTAs; 4 GPUs 216.6 / 206.9 / 216.8 with 148 / 64 / 32
-            self.rs_ctas = int(os.environ.get("ACCELERATE_B200_RS_CTAS", "0")) or max(32, min(148, 256 // max(1, self.ws.world)))
+            # 2 GPUs 218.1 / 218.8 / 223.0 / 226.9 with 148 / 96 / 64 / 48 CTAs; 4 GPUs 216.6 / 206.9 / 216.8 with 148 / 64 / 32;
+            # 8 GPUs (one box, one model instance) 213.1 / 211.7 / 205.9 / 206.4 / 208.2 with 148 / 96 / 64 / 48 / 32
+            self.rs_ctas = int(os.environ.get("ACCELERATE_B200_RS_CTAS", "0")) or (128 if self.ws.world <= 2 else 64)
             self.ch_step = self.ws.new_channel()
             # all-gathers stay inside the shard group; reductions span shard x replicate (hybrid sharding)
             ws_ranks = torch.distributed.get_process_group_ranks(self._ws_group)
