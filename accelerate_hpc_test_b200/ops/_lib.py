@@ -149,18 +149,31 @@ def check(rc: int, what: str = "") -> None:
         raise B200KernelError(f"{what or 'b200 kernel'} failed with code {rc}: {msg}")
 
 
+_cuda_checked = False
+
+
 def require_gpu_lib():
     """Return the library or raise loudly: used by ops when handed CUDA tensors."""
-    if not torch.cuda.is_available():
-        raise B200KernelError("CUDA tensors passed to a b200 op but no CUDA device is available")
-    return get_lib()
+    global _cuda_checked
+    if not _cuda_checked:  # once: is_available() re-reads the environment on every call and this sits on every op's path
+        if not torch.cuda.is_available():
+            raise B200KernelError("CUDA tensors passed to a b200 op but no CUDA device is available")
+        _cuda_checked = True
+    return _lib if _lib is not None else get_lib()
 
 
 def ptr(t) -> c_void_p:
     return c_void_p(0) if t is None else c_void_p(t.data_ptr())
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def cur_stream() -> c_void_p:
+    """Handle of torch's current stream on the current device.  Called once per kernel launch: the raw accessor skips the
+    ``torch.cuda.Stream`` object (and the device-index / availability checks) that ``torch.cuda.current_stream()`` builds."""
+    if _raw_stream is not None:
+        return c_void_p(_raw_stream(torch._C._cuda_getDevice()))
     return c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
