@@ -191,6 +191,9 @@ class Accelerator:
             if not isinstance(deepspeed_plugins, DeepSpeedPlugin):
                 raise TypeError("`deepspeed_plugin` must be a DeepSpeedPlugin or a dict of them")
             deepspeed_plugins = {"default": deepspeed_plugins}
+        # kept even when the job does not run in DeepSpeed mode (one process, CPU): `prepare` still reads optimizer / scheduler
+        # settings for `DummyOptim` / `DummyScheduler` from it
+        self._requested_deepspeed_plugins = deepspeed_plugins
         if deepspeed_plugins is not None:
             for plugin in deepspeed_plugins.values():
                 if not isinstance(plugin, DeepSpeedPlugin):
@@ -642,6 +645,7 @@ class Accelerator:
             if self.is_fsdp2 and n_models > 1:
                 raise ValueError("Only one model is supported when using FSDP2")
 
+        args = self._materialize_placeholders(args)
         # already-prepared objects pass through untouched (idempotence)
         result = []
         models_this_call = []
@@ -684,6 +688,43 @@ class Accelerator:
                 except Exception:
                     pass
         return tuple(result) if len(result) > 1 else result[0]
+
+    def _materialize_placeholders(self, args) -> tuple:
+        """Scripts written for a DeepSpeed config pass ``DummyOptim`` / ``DummyScheduler`` where the config file describes the
+        optimizer and the schedule.  Here such a configuration runs on the native engines, so the placeholders become real
+        objects: the optimizer from the placeholder's own arguments overlaid with the config's ``optimizer.params``, the
+        scheduler bound to that optimizer (``scheduler.params`` of the config: ``total_num_steps`` / ``warmup_num_steps``)."""
+        from .utils.deepspeed import DummyOptim, DummyScheduler
+
+        if not any(isinstance(obj, (DummyOptim, DummyScheduler)) for obj in args):
+            return args
+        plugin = self.deepspeed_plugin  # None unless the job runs in DeepSpeed mode ...
+        if plugin is None and self._requested_deepspeed_plugins:
+            plugin = next(iter(self._requested_deepspeed_plugins.values()))  # ... but a requested configuration still applies
+
+        def setting(path, fallback):
+            value = plugin.get_value(path) if plugin is not None else None
+            return fallback if value in (None, "auto") else value
+
+        optimizer = None
+        out = list(args)
+        for i, obj in enumerate(out):
+            if isinstance(obj, DummyOptim):
+                obj.lr = setting("optimizer.params.lr", obj.lr)
+                obj.weight_decay = setting("optimizer.params.weight_decay", obj.weight_decay)
+                for key in ("betas", "eps"):
+                    if setting(f"optimizer.params.{key}", None) is not None:
+                        obj.kwargs[key] = tuple(setting(f"optimizer.params.{key}", None)) if key == "betas" else setting(f"optimizer.params.{key}", None)
+                out[i] = optimizer = obj.materialize()
+        for i, obj in enumerate(out):
+            if isinstance(obj, DummyScheduler):
+                target = optimizer if optimizer is not None else obj.optimizer
+                if isinstance(target, DummyOptim):
+                    raise ValueError("A `DummyScheduler` needs its optimizer (a real one, or a `DummyOptim` passed to the same `prepare` call).")
+                obj.total_num_steps = setting("scheduler.params.total_num_steps", obj.total_num_steps)
+                obj.warmup_num_steps = setting("scheduler.params.warmup_num_steps", obj.warmup_num_steps)
+                out[i] = obj.materialize(target)
+        return tuple(out)
 
     def _mixed_precision_dtype(self):
         return {"fp16": torch.float16, "bf16": torch.bfloat16, "fp8": torch.bfloat16}.get(self.mixed_precision)
@@ -949,8 +990,10 @@ class Accelerator:
     def backward(self, loss, **kwargs):
         """``loss / gradient_accumulation_steps`` then backward (through the GradScaler for fp16)."""
         learning_rate = kwargs.pop("learning_rate", None)
-        if self.distributed_type != DistributedType.DEEPSPEED or True:
-            loss = loss / self.gradient_accumulation_steps if self.gradient_accumulation_steps != 1 else loss
+        # (a DeepSpeed-style configuration runs on the native engines here, so the loss is divided for it too — the reference
+        # leaves that to DeepSpeed's own engine)
+        if self.gradient_accumulation_steps != 1:
+            loss = loss / self.gradient_accumulation_steps
         if learning_rate is not None and self.has_lomo_optimizer:
             self.lomo_backward(loss, learning_rate)
         elif self.scaler is not None:

@@ -661,7 +661,7 @@ def infer_auto_device_map(model: nn.Module, max_memory: Optional[dict] = None, n
         device_map = clean_device_map(device_map)
     non_gpu_buffer_size = buffers_on_device.get("cpu", 0) + buffers_on_device.get("disk", 0)
     if non_gpu_buffer_size > 0 and not offload_buffers and len(gpus) > 0:
-        is_buffer_fit_any_gpu = any(max_memory[g] - used[g] >= non_gpu_buffer_size for g in gpus if used[g] > 0 or True)
+        is_buffer_fit_any_gpu = any(max_memory[g] - used[g] >= non_gpu_buffer_size for g in gpus)
         if len(gpus) > 0 and not is_buffer_fit_any_gpu:
             warnings.warn(
                 f"Current model requires {non_gpu_buffer_size} bytes of buffer for offloaded layers, which seems does "

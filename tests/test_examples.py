@@ -42,7 +42,7 @@ def _run_inproc(script, *args):
             runpy.run_path(path, run_name="__main__")
     finally:
         sys.argv, sys.path[:] = old_argv, old_path
-        for mod in ("_common", "nlp_example"):
+        for mod in ("_common", "nlp_example", "cv_example"):
             sys.modules.pop(mod, None)
     return buf.getvalue()
 
@@ -68,7 +68,54 @@ def test_by_feature_single_process(script, extra):
     assert "epoch 0" in _run_inproc(script, *SMALL, *extra)
 
 
-@pytest.mark.parametrize("script,extra", [("by_feature/local_sgd.py", ["--local_sgd_steps", "2"]), ("by_feature/multi_process_metrics.py", [])])
+def test_more_by_feature_examples_single_process():
+    out = _run_inproc("by_feature/cross_validation.py", *SMALL, "--num_folds", "2")
+    assert "fold 1 epoch 0" in out and "average of 2 folds on the test set" in out and "'eval_samples': 41" in out
+    assert "epoch 0" in _run_inproc("by_feature/schedule_free.py", *SMALL)
+    out = _run_inproc("by_feature/deepspeed_with_config_support.py", *SMALL,
+                      "--deepspeed_config", os.path.join(EX, "deepspeed_config_templates", "zero_stage3_config.json"))
+    assert "optimizer: FusedAdamW, ZeRO stage 3" in out and "epoch 0" in out
+    out = _run_inproc("by_feature/gradient_accumulation_for_autoregressive_models.py", "--cpu", "--model", "tiny", "--train_size", "20",
+                      "--eval_size", "8", "--max_length", "24", "--gradient_accumulation_steps", "2")
+    assert "perplexity" in out
+    out = _run_inproc("by_feature/megatron_lm_gpt_pretraining.py", "--cpu", "--model", "tiny", "--block_size", "16", "--train_size", "16",
+                      "--eval_size", "8", "--max_train_steps", "3")
+    assert "steps: 3" in out
+
+
+def test_cv_examples(tmp_path):
+    small = ["--cpu", "--train_size", "128", "--eval_size", "37", "--image_size", "16", "--num_epochs", "1"]
+    assert "'eval_samples': 37" in _run_inproc("cv_example.py", *small)
+    ck = str(tmp_path / "cv")
+    _run_inproc("complete_cv_example.py", *small, "--checkpointing_steps", "1", "--output_dir", ck, "--with_tracking",
+                "--project_dir", str(tmp_path / "logs"))
+    assert sorted(os.listdir(ck)) == ["step_1", "step_2"]
+    out = _run_inproc("complete_cv_example.py", *small, "--resume_from_checkpoint", os.path.join(ck, "step_1"))
+    assert "Resumed from checkpoint" in out and "epoch 0" in out
+
+
+def test_deepspeed_templates_and_slurm_scripts_are_well_formed():
+    import json
+
+    from accelerate_hpc_test_b200.utils import DeepSpeedPlugin
+
+    folder = os.path.join(EX, "deepspeed_config_templates")
+    stages = {}
+    for name in sorted(os.listdir(folder)):
+        cfg = json.load(open(os.path.join(folder, name)))
+        plugin = DeepSpeedPlugin(hf_ds_config=os.path.join(folder, name))
+        stages[name] = plugin.get_value("zero_optimization.stage")
+        assert plugin.is_auto("train_micro_batch_size_per_gpu") and cfg["optimizer"]["type"] == "AdamW"
+    assert stages == {"zero_stage1_config.json": 1, "zero_stage2_config.json": 2, "zero_stage2_offload_config.json": 2,
+                      "zero_stage3_config.json": 3, "zero_stage3_offload_config.json": 3}
+    for name in os.listdir(os.path.join(EX, "slurm")):
+        if name.endswith(".sh"):
+            assert subprocess.run(["bash", "-n", os.path.join(EX, "slurm", name)]).returncode == 0, name
+
+
+@pytest.mark.parametrize("script,extra", [("by_feature/local_sgd.py", ["--local_sgd_steps", "2"]), ("by_feature/multi_process_metrics.py", []),
+                                          ("by_feature/ddp_comm_hook.py", ["--ddp_comm_hook", "bf16"]),
+                                          ("by_feature/fsdp_with_peak_mem_tracking.py", ["--use_fsdp"])])
 def test_by_feature_two_processes(script, extra):
     assert "'eval_samples': 41" in _launch(2, script, *SMALL, *extra)
 

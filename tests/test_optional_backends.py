@@ -112,3 +112,26 @@ def test_transformer_engine_guards():
             transformer_engine.convert_model(model)
         with pytest.raises(ImportError, match="transformer_engine"):
             transformer_engine.apply_fp8_autowrap(model, None)
+
+
+def test_prepare_turns_deepspeed_placeholders_into_real_objects():
+    from accelerate_hpc_test_b200 import Accelerator
+    from accelerate_hpc_test_b200.scheduler import AcceleratedScheduler
+
+    acc = Accelerator(cpu=True)
+    model = nn.Linear(4, 4)
+    opt = DummyOptim(model.parameters(), lr=0.25, weight_decay=0.0)
+    sched = DummyScheduler(opt, total_num_steps=8, warmup_num_steps=2)
+    model, opt, sched = acc.prepare(model, opt, sched)
+    assert type(opt.optimizer).__name__ == "FusedAdamW" and isinstance(sched, AcceleratedScheduler)
+    seen = []
+    for _ in range(4):
+        loss = model(torch.ones(2, 4)).sum()
+        acc.backward(loss)
+        seen.append(opt.param_groups[0]["lr"])
+        opt.step()
+        sched.step()
+        opt.zero_grad()
+    assert seen[0] == 0.0 and seen[1] == 0.125 and seen[2] == 0.25 and seen[3] < 0.25  # warm-up then linear decay
+    with pytest.raises(ValueError, match="needs its optimizer"):
+        acc.prepare(DummyScheduler(DummyOptim(model.parameters())))
