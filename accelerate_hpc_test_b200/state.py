@@ -434,7 +434,9 @@ class AcceleratorState:
 
         cp_or_sp = parallelism_config is not None and (parallelism_config.cp_enabled or parallelism_config.sp_enabled)
         if self.distributed_type in (DistributedType.MULTI_GPU, DistributedType.MULTI_CPU):
-            if (parse_flag_from_env("ACCELERATE_USE_DEEPSPEED") or deepspeed_plugin is not None) and not cpu:
+            # (the reference refuses DeepSpeed on CPU; here a ZeRO configuration runs on the native sharded engine, whose gloo
+            # path works on CPU too — that is how the DeepSpeed-style scripts are tested without GPUs)
+            if parse_flag_from_env("ACCELERATE_USE_DEEPSPEED") or deepspeed_plugin is not None:
                 self.distributed_type = DistributedType.DEEPSPEED
                 if not isinstance(deepspeed_plugin, dict) and deepspeed_plugin is not None:
                     deepspeed_plugin = {"default": deepspeed_plugin}
