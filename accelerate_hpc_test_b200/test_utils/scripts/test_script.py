@@ -1,68 +1,62 @@
-"""End-to-end sanity script run by ``accelerate test`` and the launcher tests (reference
-src/accelerate/test_utils/scripts/test_script.py:827-905): process control, RNG sync, dataloader
-sharding against a baseline, ``split_between_processes``, single-vs-distributed training parity, triggers."""
+"""The end-to-end sanity program behind ``accelerate test``: run it under any launcher and configuration and it walks through what a
+training script relies on — which rank executes what, RNG synchronisation, dataloader sharding (per-rank and rank-0 dispatch) against
+the unsharded data, ``split_between_processes``, training that matches a single-process baseline, the cross-rank breakpoint trigger.
+Behaviour of reference ``src/accelerate/test_utils/scripts/test_script.py:827-905``.
 
+    accelerate launch --num_processes 2 --cpu -m accelerate_hpc_test_b200.test_utils.scripts.test_script
+"""
+
+import contextlib
 import io
 import math
-from contextlib import redirect_stdout
 
 import torch
 from torch.utils.data import DataLoader
 
 from accelerate_hpc_test_b200 import Accelerator
-from accelerate_hpc_test_b200.data_loader import SeedableRandomSampler, prepare_data_loader
+from accelerate_hpc_test_b200.data_loader import prepare_data_loader
 from accelerate_hpc_test_b200.state import AcceleratorState, GradientState, PartialState
 from accelerate_hpc_test_b200.test_utils.training import RegressionDataset, RegressionModel
-from accelerate_hpc_test_b200.utils import DistributedType, gather, set_seed, synchronize_rng_states
+from accelerate_hpc_test_b200.utils import DataLoaderConfiguration, DistributedType, gather, set_seed, synchronize_rng_states
 
 
-def print_main(state):
-    print(f"Printing from the main process {state.process_index}")
+def announce(title):
+    if PartialState().local_process_index == 0:
+        print(f"\n**{title}**")
 
 
-def print_local_main(state):
-    print(f"Printing from the local main process {state.local_process_index}")
+def same_on_every_rank(tensor) -> bool:
+    everyone = gather(tensor[None].clone().to(PartialState().device)).cpu()
+    return bool((everyone == everyone[0]).all())
 
 
-def print_last(state):
-    print(f"Printing from the last process {state.process_index}")
+are_the_same_tensors = same_on_every_rank  # name used by other scripts
 
 
-def print_on(state, process_idx):
-    print(f"Printing from process {process_idx}: {state.process_index}")
+# ------------------------------------------------------------------------------------------------- who runs what
+def _captured(call) -> str:
+    sink = io.StringIO()
+    with contextlib.redirect_stdout(sink):
+        call()
+    return sink.getvalue().strip()
 
 
 def process_execution_check():
     accelerator = Accelerator()
-    num_processes = accelerator.num_processes
-    f = io.StringIO()
+    me, world = accelerator.process_index, accelerator.num_processes
     with accelerator.main_process_first():
-        with redirect_stdout(f):
-            pass
+        pass
     accelerator.wait_for_everyone()
-    f = io.StringIO()
-    with redirect_stdout(f):
-        accelerator.on_main_process(print_main)(accelerator.state)
-    result = f.getvalue().rstrip()
-    if accelerator.is_main_process:
-        assert result == "Printing from the main process 0", f"{result} != Printing from the main process 0"
-    else:
-        assert f.getvalue().rstrip() == "", f'{result} != ""'
-    f = io.StringIO()
-    with redirect_stdout(f):
-        accelerator.on_last_process(print_last)(accelerator.state)
-    if accelerator.is_last_process:
-        assert f.getvalue().rstrip() == f"Printing from the last process {num_processes - 1}"
-    else:
-        assert f.getvalue().rstrip() == ""
-    for process_idx in range(num_processes):
-        f = io.StringIO()
-        with redirect_stdout(f):
-            accelerator.on_process(print_on, process_index=process_idx)(accelerator.state, process_idx)
-        if accelerator.process_index == process_idx:
-            assert f.getvalue().rstrip() == f"Printing from process {process_idx}: {accelerator.process_index}"
-        else:
-            assert f.getvalue().rstrip() == ""
+    cases = [
+        (accelerator.on_main_process, {}, accelerator.is_main_process, "main"),
+        (accelerator.on_local_main_process, {}, accelerator.is_local_main_process, "local main"),
+        (accelerator.on_last_process, {}, accelerator.is_last_process, "last"),
+    ] + [(accelerator.on_process, {"process_index": rank}, me == rank, f"number {rank}") for rank in range(world)]
+    for decorator, options, mine, who in cases:
+        text = f"the {who} process speaking: {me}"
+        wrapped = decorator(lambda: print(text), **options) if options else decorator(lambda: print(text))
+        said = _captured(wrapped)
+        assert said == (text if mine else ""), f"rank {me}, decorator for the {who} process printed {said!r}"
 
 
 def init_state_check():
@@ -72,140 +66,120 @@ def init_state_check():
         print(state)
 
 
+# ------------------------------------------------------------------------------------------------- randomness
 def rng_sync_check():
     state = AcceleratorState()
     synchronize_rng_states(["torch"])
-    assert are_the_same_tensors(torch.get_rng_state()), "RNG states improperly synchronized on CPU."
+    assert same_on_every_rank(torch.get_rng_state()), "RNG states improperly synchronized on CPU."
     if state.distributed_type == DistributedType.MULTI_GPU:
         synchronize_rng_states(["cuda"])
-        assert are_the_same_tensors(torch.cuda.get_rng_state()), "RNG states improperly synchronized on GPU."
+        assert same_on_every_rank(torch.cuda.get_rng_state()), "RNG states improperly synchronized on GPU."
     generator = torch.Generator()
     synchronize_rng_states(["generator"], generator=generator)
-    assert are_the_same_tensors(generator.get_state()), "RNG states improperly synchronized in generator."
+    assert same_on_every_rank(generator.get_state()), "RNG states improperly synchronized in generator."
     if state.local_process_index == 0:
         print("All rng are properly synched.")
 
 
-def are_the_same_tensors(tensor):
-    state = AcceleratorState()
-    tensor = tensor[None].clone().to(state.device)
-    tensors = gather(tensor).cpu()
-    tensor = tensor[0].cpu()
-    for i in range(tensors.shape[0]):
-        if not torch.equal(tensors[i], tensor):
-            return False
-    return True
+# ------------------------------------------------------------------------------------------------- dataloaders
+def _everything_the_ranks_saw(loader):
+    return torch.cat([gather(batch) for batch in loader]).cpu()
 
 
 def dl_preparation_check():
     state = AcceleratorState()
-    length = 32 * state.num_processes
+    samples = 32 * state.num_processes
     for split_batches in (False, True):
         for shuffle in (False, True):
-            dl = DataLoader(range(length), batch_size=8 * (state.num_processes if split_batches else 1), shuffle=shuffle)
-            dl = prepare_data_loader(dl, state.device, state.num_processes, state.process_index, put_on_device=True, split_batches=split_batches)
-            result = []
-            for batch in dl:
-                result.append(gather(batch))
-            result = torch.cat(result)
-            assert torch.equal(result.cpu().sort().values if shuffle else result.cpu(), torch.arange(0, length).long()), "Wrong dataloader sharding."
+            batch_size = 8 * (state.num_processes if split_batches else 1)
+            loader = prepare_data_loader(DataLoader(range(samples), batch_size=batch_size, shuffle=shuffle), state.device, state.num_processes,
+                                         state.process_index, put_on_device=True, split_batches=split_batches)
+            seen = _everything_the_ranks_saw(loader)
+            expected = torch.arange(samples)
+            assert torch.equal(seen.sort().values if shuffle else seen, expected), "Wrong dataloader sharding."
     if state.process_index == 0:
         print("Non-shuffled and shuffled dataloaders passing.")
 
 
 def central_dl_preparation_check():
     state = AcceleratorState()
-    length = 32 * state.num_processes
+    samples = 32 * state.num_processes
     for split_batches in (False, True):
-        dl = DataLoader(range(length), batch_size=8 * (state.num_processes if split_batches else 1))
-        dl = prepare_data_loader(dl, state.device, state.num_processes, state.process_index, put_on_device=True, dispatch_batches=True,
-                                 split_batches=split_batches)
-        result = []
-        for batch in dl:
-            result.append(gather(batch))
-        result = torch.cat(result)
-        assert torch.equal(result.cpu(), torch.arange(0, length).long()), "Wrong central dataloader."
+        batch_size = 8 * (state.num_processes if split_batches else 1)
+        loader = prepare_data_loader(DataLoader(range(samples), batch_size=batch_size), state.device, state.num_processes, state.process_index,
+                                     put_on_device=True, dispatch_batches=True, split_batches=split_batches)
+        assert torch.equal(_everything_the_ranks_saw(loader), torch.arange(samples)), "Wrong central dataloader."
     if state.process_index == 0:
         print("Central (dispatch) dataloaders passing.")
 
 
+# ------------------------------------------------------------------------------------------------- training
+def _fit(model, optimizer, loader, backward, epochs=3):
+    for _ in range(epochs):
+        for batch in loader:
+            model.zero_grad()
+            backward(torch.nn.functional.mse_loss(model(batch["x"]), batch["y"]))
+            optimizer.step()
+
+
 def mock_training(length, batch_size, generator, use_seedable_sampler=False):
+    """The baseline: plain PyTorch on one process over the whole batch."""
     set_seed(42)
     generator.manual_seed(42)
-    train_set = RegressionDataset(length=length, seed=42)
-    train_dl = DataLoader(train_set, batch_size=batch_size, shuffle=True, generator=generator)
+    data = RegressionDataset(length=length, seed=42)
     model = RegressionModel()
-    optimizer = torch.optim.SGD(model.parameters(), lr=0.1)
-    for epoch in range(3):
-        for batch in train_dl:
-            model.zero_grad()
-            output = model(batch["x"])
-            loss = torch.nn.functional.mse_loss(output, batch["y"])
-            loss.backward()
-            optimizer.step()
-    return train_set, model
+    _fit(model, torch.optim.SGD(model.parameters(), lr=0.1), DataLoader(data, batch_size=batch_size, shuffle=True, generator=generator),
+         lambda loss: loss.backward())
+    return data, model
 
 
 def training_check(use_seedable_sampler=False):
     state = AcceleratorState()
+    world = state.num_processes
     generator = torch.Generator()
-    batch_size = 8
-    length = batch_size * 4 * state.num_processes
-    train_set, old_model = mock_training(length, batch_size * state.num_processes, generator, use_seedable_sampler)
-    assert are_the_same_tensors(old_model.a), "Did not obtain the same model on both processes."
-    assert are_the_same_tensors(old_model.b), "Did not obtain the same model on both processes."
-    from accelerate_hpc_test_b200.utils import DataLoaderConfiguration
-
+    per_rank = 8
+    data, baseline = mock_training(per_rank * 4 * world, per_rank * world, generator, use_seedable_sampler)
+    assert same_on_every_rank(baseline.a) and same_on_every_rank(baseline.b), "Did not obtain the same model on both processes."
     for split_batches in (False, True):
         AcceleratorState._reset_state(True)
         GradientState._reset_state()
         accelerator = Accelerator(dataloader_config=DataLoaderConfiguration(split_batches=split_batches))
-        train_dl = DataLoader(train_set, batch_size=batch_size * (state.num_processes if split_batches else 1), shuffle=True, generator=generator)
+        loader = DataLoader(data, batch_size=per_rank * (world if split_batches else 1), shuffle=True, generator=generator)
         model = RegressionModel()
-        optimizer = torch.optim.SGD(model.parameters(), lr=0.1 if split_batches else 0.1)
-        train_dl, model, optimizer = accelerator.prepare(train_dl, model, optimizer)
+        optimizer = torch.optim.SGD(model.parameters(), lr=0.1)
+        loader, model, optimizer = accelerator.prepare(loader, model, optimizer)
         set_seed(42)
         generator.manual_seed(42)
-        for epoch in range(3):
-            for batch in train_dl:
-                model.zero_grad()
-                output = model(batch["x"])
-                loss = torch.nn.functional.mse_loss(output, batch["y"])
-                accelerator.backward(loss)
-                optimizer.step()
-        model = accelerator.unwrap_model(model).cpu()
-        assert torch.allclose(old_model.a, model.a, atol=1e-4), f"Did not obtain the same model on CPU or distributed training ({old_model.a} vs {model.a})."
-        assert torch.allclose(old_model.b, model.b, atol=1e-4), f"Did not obtain the same model on CPU or distributed training ({old_model.b} vs {model.b})."
+        _fit(model, optimizer, loader, accelerator.backward)
+        trained = accelerator.unwrap_model(model).cpu()
+        for name in ("a", "b"):
+            want, got = getattr(baseline, name), getattr(trained, name)
+            assert torch.allclose(want, got, atol=1e-4), f"Did not obtain the same model on CPU or distributed training ({want} vs {got})."
         accelerator.print(f"Training yielded the same results on one CPU or distributed setup with {'batch split' if split_batches else 'no batch split'}.")
 
 
+# ------------------------------------------------------------------------------------------------- splitting work
 def test_split_between_processes_list():
     state = AcceleratorState()
-    data = list(range(0, 2 * state.num_processes))
-    with state.split_between_processes(data) as results:
-        assert len(results) == 2, f"Each process did not have two items. Process index: {state.process_index}; Length: {len(results)}"
-    data = list(range(0, (3 * state.num_processes) - 1))
-    with state.split_between_processes(data, apply_padding=True) as results:
+    world, me = state.num_processes, state.process_index
+    with state.split_between_processes(list(range(2 * world))) as mine:
+        assert len(mine) == 2, f"Each process did not have two items. Process index: {me}; Length: {len(mine)}"
+    uneven = list(range(3 * world - 1))
+    with state.split_between_processes(uneven, apply_padding=True) as mine:
         if state.is_last_process:
-            num_samples_per_device = math.ceil(len(data) / state.num_processes)
-            assert len(results) == num_samples_per_device, f"Last process did not get the extra item(s). Process index: {state.process_index}; Length: {len(results)}"
+            assert len(mine) == math.ceil(len(uneven) / world), f"Last process did not get the extra item(s). Process index: {me}; Length: {len(mine)}"
     state.wait_for_everyone()
 
 
 def test_split_between_processes_nested_dict():
     state = AcceleratorState()
-    a = [1, 2, 3, 4, 5, 6, 7, 8]
-    b = ["a", "b", "c", "d", "e", "f", "g", "h"]
-    c = torch.tensor([1, 2, 3, 4, 5, 6, 7, 8])
-    if state.num_processes in (1, 2, 4):
-        data = {"a": a, "b": b, "c": c}
-        data_copy = dict(data)
-        with state.split_between_processes(data) as results:
-            per = 8 // state.num_processes
-            lo = state.process_index * per
-            assert results["a"] == data_copy["a"][lo : lo + per]
-            assert results["b"] == data_copy["b"][lo : lo + per]
-            assert torch.allclose(results["c"], data_copy["c"][lo : lo + per])
+    world, me = state.num_processes, state.process_index
+    if 8 % world == 0:
+        whole = {"a": list(range(1, 9)), "b": list("abcdefgh"), "c": torch.arange(1, 9)}
+        share = 8 // world
+        window = slice(me * share, (me + 1) * share)
+        with state.split_between_processes(dict(whole)) as mine:
+            assert mine["a"] == whole["a"][window] and mine["b"] == whole["b"][window] and torch.equal(mine["c"], whole["c"][window])
     state.wait_for_everyone()
 
 
@@ -214,51 +188,39 @@ def test_trigger():
     assert accelerator.check_trigger() is False
     if accelerator.is_main_process:
         accelerator.set_trigger()
+    # one rank raised the flag: every rank sees it, once
     assert accelerator.check_trigger() is True
     assert accelerator.check_trigger() is False
 
 
 def test_reinstantiated_state():
+    """After a state reset an Accelerator built earlier must fail with a message that says so, not with a bare AttributeError."""
     AcceleratorState._reset_state()
-    simple_model = torch.nn.Linear(1, 1)
     accelerator = Accelerator()
     try:
-        accelerator.prepare(simple_model)
-    except AttributeError as e:
-        assert "`AcceleratorState` object has no attribute" in str(e)
-    else:
-        pass
+        accelerator.prepare(torch.nn.Linear(1, 1))
+    except AttributeError as error:
+        assert "`AcceleratorState` object has no attribute" in str(error)
 
 
 def main():
     accelerator = Accelerator()
     state = accelerator.state
-    if state.local_process_index == 0:
-        print("**Initialization**")
+    announce("Initialization")
     init_state_check()
     state.wait_for_everyone()
-    if state.local_process_index == 0:
-        print("\n**Test process execution**")
-    process_execution_check()
-    if state.local_process_index == 0:
-        print("\n**Test split between processes as a list**")
-    test_split_between_processes_list()
-    if state.local_process_index == 0:
-        print("\n**Test split between processes as a dict**")
-    test_split_between_processes_nested_dict()
-    if state.local_process_index == 0:
-        print("\n**Test random number generator synchronization**")
-    rng_sync_check()
-    if state.local_process_index == 0:
-        print("\n**DataLoader integration test**")
-    dl_preparation_check()
-    central_dl_preparation_check()
-    if state.local_process_index == 0:
-        print("\n**Training integration test**")
-    training_check()
-    if state.local_process_index == 0:
-        print("\n**Breakpoint trigger test**")
-    test_trigger()
+    for title, checks in (
+        ("Test process execution", (process_execution_check,)),
+        ("Test split between processes as a list", (test_split_between_processes_list,)),
+        ("Test split between processes as a dict", (test_split_between_processes_nested_dict,)),
+        ("Test random number generator synchronization", (rng_sync_check,)),
+        ("DataLoader integration test", (dl_preparation_check, central_dl_preparation_check)),
+        ("Training integration test", (training_check,)),
+        ("Breakpoint trigger test", (test_trigger,)),
+    ):
+        announce(title)
+        for check in checks:
+            check()
     PartialState().wait_for_everyone()
     if PartialState().is_main_process:
         print("test_script: all passed")
