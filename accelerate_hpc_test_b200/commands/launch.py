@@ -152,6 +152,11 @@ def launch_command_parser(subparsers=None):
     megatron_lm_args.add_argument("--megatron_lm_recompute_activations", default=None, type=str, help="Decides Whether (true|false) to enable Selective Activation Recomputation.")
     megatron_lm_args.add_argument("--megatron_lm_use_distributed_optimizer", default=None, type=str, help="Decides Whether (true|false) to use distributed optimizer which shards optimizer state and gradients across Data Pralellel (DP) ranks.")
     megatron_lm_args.add_argument("--megatron_lm_gradient_clipping", default=1.0, type=float, help="Megatron-LM's gradient clipping value based on global L2 Norm (0 to disable).")
+    # the long tail of Megatron-LM switches: carried into the plugin (and its `megatron_lm_default_args`) for configuration
+    # compatibility; the degrees among them (context / expert parallel sizes) feed `ParallelismConfig`
+    tail = "(useful only when `use_megatron_lm` flag is passed)."
+    for flag, kind, default, what in _MEGATRON_TAIL:
+        megatron_lm_args.add_argument(f"--megatron_lm_{flag}", default=default, type=kind, help=f"{what} {tail}")
 
     fp8_args = parser.add_argument_group("FP8 Arguments", "Arguments related to FP8 training (native MXFP8 block scaling on B200, or TransformerEngine / torchao / MS-AMP)")
     fp8_args.add_argument("--fp8_backend", type=str, choices=["native", "ao", "te", "msamp"], help="Choose a backend to train with FP8")
@@ -261,6 +266,34 @@ def tpu_launcher(args):
 def sagemaker_launcher(sagemaker_config, args):
     raise NotImplementedError("SageMaker launch is out of scope for the B200 build")
 
+
+def _truthy_flag(text) -> bool:
+    return str(text).lower() in ("1", "true", "yes", "y", "on")
+
+
+# (flag, type, default, help) of the less common Megatron-LM options; "true|false" strings are parsed by the plugin
+_MEGATRON_TAIL = (
+    ("use_custom_fsdp", _truthy_flag, False, "Whether to use Megatron's own FSDP."),
+    ("no_load_optim", _truthy_flag, False, "Do not load the optimizer state from a checkpoint."),
+    ("no_save_optim", _truthy_flag, False, "Do not save the optimizer state in checkpoints."),
+    ("eod_mask_loss", _truthy_flag, False, "Mask the loss on end-of-document tokens."),
+    ("optimizer_cpu_offload", _truthy_flag, False, "Keep optimizer state in host memory."),
+    ("use_precision_aware_optimizer", _truthy_flag, False, "Use the precision-aware optimizer."),
+    ("overlap_cpu_optimizer_d2h_h2d", _truthy_flag, False, "Overlap the host<->device copies of an offloaded optimizer with compute."),
+    ("decoder_last_pipeline_num_layers", int, None, "Number of decoder layers on the last pipeline stage."),
+    ("recompute_granularity", str, None, "Activation recompute granularity (full, selective)."),
+    ("recompute_method", str, None, "Activation recompute method (uniform, block)."),
+    ("recompute_num_layers", int, None, "Number of layers whose activations are recomputed."),
+    ("attention_backend", str, None, "Decides Whether (true|false) to enable attention backend."),
+    ("expert_model_parallel_size", int, None, "Expert model parallel size."),
+    ("expert_tensor_parallel_size", int, None, "Expert tensor parallel size."),
+    ("context_parallel_size", int, None, "Context parallel size."),
+    ("attention_dropout", float, None, "Attention dropout."),
+    ("hidden_dropout", float, None, "Hidden dropout."),
+    ("attention_softmax_in_fp32", str, None, "Decides Whether (true|false) to run the attention softmax in fp32."),
+    ("calculate_per_token_loss", str, None, "Decides Whether (true|false) to average the loss per token."),
+    ("use_rotary_position_embeddings", str, None, "Decides Whether (true|false) to use rotary position embeddings."),
+)
 
 _SECTION_PREFIX = {"fsdp_config": "fsdp", "fp8_config": "fp8", "parallelism_config": "parallelism_config", "megatron_lm_config": "megatron_lm"}
 _STRATEGY_FLAGS = ("multi_gpu", "tpu", "use_deepspeed", "use_fsdp", "use_megatron_lm")

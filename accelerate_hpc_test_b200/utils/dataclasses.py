@@ -1014,6 +1014,16 @@ class MegatronLMPlugin:
             self.expert_model_parallel_size = int(os.environ.get(p + "EXPERT_MODEL_PARALLEL_SIZE", 1))
         if self.expert_tensor_parallel_size is None:
             self.expert_tensor_parallel_size = int(os.environ.get(p + "EXPERT_TENSOR_PARALLEL_SIZE", 1))
+        # the long tail: booleans, strings and numbers the launcher exports as MEGATRON_LM_<FIELD>
+        tail = {"use_custom_fsdp": bool, "no_load_optim": bool, "eod_mask_loss": bool, "no_save_optim": bool, "optimizer_cpu_offload": bool,
+                "use_precision_aware_optimizer": bool, "attention_backend": bool, "attention_softmax_in_fp32": bool,
+                "calculate_per_token_loss": bool, "use_rotary_position_embeddings": bool, "decoder_last_pipeline_num_layers": int,
+                "recompute_num_layers": int, "recompute_granularity": str, "recompute_method": str, "attention_dropout": float,
+                "hidden_dropout": float}
+        for name, kind in tail.items():
+            raw = os.environ.get(p + name.upper())
+            if getattr(self, name, None) is None and raw is not None:
+                setattr(self, name, (str_to_bool(raw) == 1) if kind is bool else kind(raw))
         if self.pp_degree > 1 or self.use_distributed_optimizer:
             self.DDP_impl = "local"
         else:

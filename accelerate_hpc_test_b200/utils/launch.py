@@ -89,6 +89,13 @@ _MEGATRON_RULES = (
     EnvRule("megatron_lm_sequence_parallelism", "MEGATRON_LM_SEQUENCE_PARALLELISM", optional=True),
     EnvRule("megatron_lm_recompute_activations", "MEGATRON_LM_RECOMPUTE_ACTIVATIONS", optional=True),
     EnvRule("megatron_lm_use_distributed_optimizer", "MEGATRON_LM_USE_DISTRIBUTED_OPTIMIZER", optional=True),
+) + tuple(
+    EnvRule(f"megatron_lm_{name}", f"MEGATRON_LM_{name.upper()}", optional=True)
+    for name in ("use_custom_fsdp", "no_load_optim", "no_save_optim", "eod_mask_loss", "optimizer_cpu_offload", "use_precision_aware_optimizer",
+                 "overlap_cpu_optimizer_d2h_h2d", "decoder_last_pipeline_num_layers", "recompute_granularity", "recompute_method",
+                 "recompute_num_layers", "attention_backend", "expert_model_parallel_size", "expert_tensor_parallel_size",
+                 "context_parallel_size", "attention_dropout", "hidden_dropout", "attention_softmax_in_fp32", "calculate_per_token_loss",
+                 "use_rotary_position_embeddings")
 )
 
 _PARALLELISM_RULES = (

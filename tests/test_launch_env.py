@@ -226,3 +226,26 @@ def test_validate_reports_defaults_and_contradictions(caplog):
     args, cfg, from_cfg = _validate_launch_command(args)
     assert cfg is None and from_cfg is False and args.num_processes == 1 and args.num_machines == 1 and args.mixed_precision == "no"
     assert args.machine_rank == 0 and args.num_cpu_threads_per_process >= 1
+
+
+def test_megatron_tail_flags_reach_the_plugin_through_the_environment():
+    from accelerate_hpc_test_b200.commands.launch import launch_command_parser
+    from accelerate_hpc_test_b200.utils import MegatronLMPlugin
+    from accelerate_hpc_test_b200.utils.environment import patch_environment
+    from accelerate_hpc_test_b200.utils.launch import prepare_multi_gpu_env
+
+    args = launch_command_parser().parse_args([
+        "--use_megatron_lm", "--num_processes", "8", "--num_machines", "1", "--main_process_port", "29999", "--megatron_lm_tp_degree", "2", "--megatron_lm_context_parallel_size", "2",
+        "--megatron_lm_recompute_granularity", "selective", "--megatron_lm_attention_dropout", "0.1", "--megatron_lm_eod_mask_loss", "true",
+        "--megatron_lm_use_rotary_position_embeddings", "true", "--megatron_lm_recompute_num_layers", "4", "train.py"])
+    args, _, _ = _validate_launch_command(args)
+    assert args.megatron_lm_eod_mask_loss is True and args.megatron_lm_no_save_optim is False and args.megatron_lm_hidden_dropout is None
+    env = prepare_multi_gpu_env(args)
+    assert env["ACCELERATE_USE_MEGATRON_LM"] == "true" and env["MEGATRON_LM_TP_DEGREE"] == "2" and env["MEGATRON_LM_CONTEXT_PARALLEL_SIZE"] == "2"
+    assert env["MEGATRON_LM_RECOMPUTE_GRANULARITY"] == "selective" and env["MEGATRON_LM_ATTENTION_DROPOUT"] == "0.1"
+    assert env["MEGATRON_LM_EOD_MASK_LOSS"] == "True" and "MEGATRON_LM_HIDDEN_DROPOUT" not in env
+    with patch_environment(**{k: v for k, v in env.items() if k.startswith("MEGATRON_LM_")}):
+        plugin = MegatronLMPlugin()
+    assert plugin.tp_degree == 2 and plugin.context_parallel_size == 2 and plugin.recompute_granularity == "selective"
+    assert plugin.attention_dropout == 0.1 and plugin.eod_mask_loss is True and plugin.use_rotary_position_embeddings is True
+    assert plugin.recompute_num_layers == 4 and plugin.hidden_dropout is None
