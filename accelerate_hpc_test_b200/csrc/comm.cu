@@ -642,18 +642,22 @@ struct ExSegs {
   ExSeg s[3];
   int n;
 };
-static constexpr int EX_CHUNK = 4096;
-static constexpr int EX_STAGES = 6;
-static constexpr int EX_AHEAD = 4;
-static constexpr int EX_SMEM = EX_CHUNK * EX_STAGES + 128 + 128;
+// One thread per CTA drives the copies, so throughput = bytes in flight / round-trip time.  The ring is EX_RING bytes whatever the
+// row segments look like: CHUNK is the largest segment (rounded up to 512 B .. 4 KB), the ring holds EX_RING / CHUNK stages and all but
+// two of them are in flight — with the 1 KB segments of sp=8 that is 22 copies per CTA instead of 4, and several CTAs share an SM.
+static constexpr int EX_RING = 24576;
+static constexpr int EX_SMEM = EX_RING + 512 + 128;
 
+template <int EX_CHUNK>
 __global__ void __launch_bounds__(32)
 seq_head_exchange_kernel(Peers peers, int rank, int world, long long src_off, uint8_t* __restrict__ out, int mode, int B,
                          int S_loc, long long src_pitch, long long dst_pitch, ExSegs segs, int ch_arrive, int ch_done,
                          uint32_t epoch, uint32_t* __restrict__ counter) {
   extern __shared__ uint8_t ex_smem_raw[];
   uint8_t* ring = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ex_smem_raw) + 127) & ~(uintptr_t)127);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + EX_CHUNK * EX_STAGES);
+  constexpr int EX_STAGES = EX_RING / EX_CHUNK;
+  constexpr int EX_AHEAD = EX_STAGES - 2;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + EX_RING);
   if (blockIdx.x == 0) signal_all(peers, rank, world, ch_arrive, epoch);  // my source matrix is complete (stream order)
   wait_all(peers, rank, world, ch_arrive, epoch);
   if (threadIdx.x == 0) {
@@ -939,15 +943,26 @@ B200_API int b200_seq_head_exchange(const void* const* peer_ptrs, int rank, int 
     sg.s[i] = ExSeg{segs[3 * i], segs[3 * i + 1], segs[3 * i + 2]};
     if ((sg.s[i].src_base | sg.s[i].dst_base | sg.s[i].bytes) % 16 || sg.s[i].bytes <= 0) return B200_ERR_BAD_ARG;
   }
-  if (ctas <= 0) ctas = 148;
+  if (ctas <= 0) ctas = 3 * 148;  // 32 threads and 25 KB each: three per SM still leave a persistent GEMM CTA its shared memory
+  long long widest = 0;
+  for (int i = 0; i < nseg; ++i) widest = sg.s[i].bytes > widest ? sg.s[i].bytes : widest;
   static bool attr = false;
   if (!attr) {
-    B200_CUDA(cudaFuncSetAttribute(seq_head_exchange_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, EX_SMEM));
+    B200_CUDA(cudaFuncSetAttribute(seq_head_exchange_kernel<4096>, cudaFuncAttributeMaxDynamicSharedMemorySize, EX_SMEM));
+    B200_CUDA(cudaFuncSetAttribute(seq_head_exchange_kernel<2048>, cudaFuncAttributeMaxDynamicSharedMemorySize, EX_SMEM));
+    B200_CUDA(cudaFuncSetAttribute(seq_head_exchange_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, EX_SMEM));
+    B200_CUDA(cudaFuncSetAttribute(seq_head_exchange_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, EX_SMEM));
     attr = true;
   }
-  seq_head_exchange_kernel<<<ctas, 32, EX_SMEM, (cudaStream_t)stream>>>(P, rank, world, src_off, (uint8_t*)out, mode, B, S_loc,
-                                                                        src_pitch, dst_pitch, sg, ch_arrive, ch_done, epoch,
-                                                                        (uint32_t*)counter);
+#define B200_EXCHANGE(CHUNK)                                                                                                    \
+  seq_head_exchange_kernel<CHUNK><<<ctas, 32, EX_SMEM, (cudaStream_t)stream>>>(P, rank, world, src_off, (uint8_t*)out, mode, B, \
+                                                                               S_loc, src_pitch, dst_pitch, sg, ch_arrive,      \
+                                                                               ch_done, epoch, (uint32_t*)counter)
+  if (widest <= 512) B200_EXCHANGE(512);
+  else if (widest <= 1024) B200_EXCHANGE(1024);
+  else if (widest <= 2048) B200_EXCHANGE(2048);
+  else B200_EXCHANGE(4096);
+#undef B200_EXCHANGE
   b200_count_launch();
   B200_CHECK_LAUNCH();
   return 0;

@@ -67,6 +67,8 @@ class SPComm:
         self._max_bytes = int(nbytes * 1.25)
         self._ch_arrive = self.ws.new_channel()
         self._ch_done = self.ws.new_channel()
+        # CTAs of the head<->sequence exchange kernel (0: the library's default, three per SM)
+        self._exchange_ctas = int(os.environ.get("ACCELERATE_B200_EXCHANGE_CTAS", "0"))
 
     def _native(self, x2d: torch.Tensor) -> bool:
         return x2d.is_cuda and self.world > 1 and hasattr(self, "_ws_cls")
@@ -108,7 +110,7 @@ class SPComm:
         _lib.check(
             self.ws.lib.b200_seq_head_exchange(self.ws.peer_array, self.rank, w, self._src_off, _lib.ptr(out), mode, B, S_loc,
                                                cols_in * es, cols_out * es, arr, len(widths), self._ch_arrive, self._ch_done, e,
-                                               self.ws.counter_ptr(self._ch_arrive), 148, _lib.cur_stream()),
+                                               self.ws.counter_ptr(self._ch_arrive), self._exchange_ctas, _lib.cur_stream()),
             "seq_head_exchange",
         )
         return out

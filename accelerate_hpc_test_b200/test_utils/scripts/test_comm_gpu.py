@@ -449,6 +449,12 @@ def check_seq(dev, rank, world):
                      ("nccl_all_to_all+permutes", lambda: comm._exchange_reference(xb, 0, Bq, Sl, wd))):
         tt = timed(fn, iters=10)
         log(f"ulysses {name}: {tt:.3f} ms ({xb.numel() * 2 * (world - 1) / world / tt / 1e6:.0f} GB/s ingress), clocks {tt.clocks}")
+    # the same bytes in the other direction (attention output -> sequence shards), where rows are cut into `world` pieces
+    yb = comm.exchange(xb, 0, Bq, Sl, wd)
+    for name, fn in (("exchange_kernel head->seq", lambda: comm.exchange(yb, 1, Bq, Sl, wd)),
+                     ("nccl_all_to_all+permutes head->seq", lambda: comm._exchange_reference(yb, 1, Bq, Sl, wd))):
+        tt = timed(fn, iters=10)
+        log(f"ulysses {name}: {tt:.3f} ms ({xb.numel() * 2 * (world - 1) / world / tt / 1e6:.0f} GB/s ingress)")
     log("ulysses exchange ok")
     # W12 / W13: QKV projection fused with the sequence->head all-to-all (also the dgrad of the output projection)
     from accelerate_hpc_test_b200.ops import functional as F
