@@ -39,6 +39,7 @@ class FusedAdamW(torch.optim.Optimizer):
         self._bwd_updated = set()       # params already updated during this step's backward
         self._saw_grad_consumer = False  # clip / found_inf / grad_scale used: gradients are needed after backward
         self._sync_fn = None
+        self._probe_clean_steps = 0
 
     # -- hooks used by Accelerator.clip_grad_norm_ / GradScaler integration --------------------
     def set_clip_coef(self, coef: Optional[torch.Tensor]):
@@ -81,7 +82,7 @@ class FusedAdamW(torch.optim.Optimizer):
         communication ``stream`` — the update of bucket *i* then overlaps the backward GEMMs that produce bucket *i+1*.
         Same ``mode`` / probing rules as ``enable_update_in_backward``.  Returns whether the fusion was armed."""
         mode = mode or os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto")
-        if mode == "0" or self._bwd_hooks or self._bwd_stream is not None:
+        if mode == "0" or self._bwd_hooks or self._bwd_mode != "off":
             return False
         self._sync_fn = sync_gradients_fn
         self._bwd_stream = stream
@@ -182,12 +183,19 @@ class FusedAdamW(torch.optim.Optimizer):
                 self._update_one(p, p.grad, group)
         if self._bwd_updated:
             # the next forward reads the parameters the side stream has just written
-            torch.cuda.current_stream().wait_stream(self._bwd_stream)
+            if self._bwd_stream is not None:
+                torch.cuda.current_stream().wait_stream(self._bwd_stream)
             self._bwd_updated.clear()
         if self._bwd_mode == "probing":
-            ok = (not self._saw_grad_consumer and self.grad_scale == 1.0 and self._bwd_fired
-                  and all(n == 1 for n in self._bwd_fired.values()))
-            self._bwd_mode = "active" if ok else "off"
+            # switch on after two steps in a row that each followed exactly one backward and needed no gradient afterwards; a
+            # loop that accumulates by hand (several backward passes per step) keeps the ordinary update
+            clean = (not self._saw_grad_consumer and self.grad_scale == 1.0 and bool(self._bwd_fired)
+                     and all(n == 1 for n in self._bwd_fired.values()))
+            self._probe_clean_steps = self._probe_clean_steps + 1 if clean else 0
+            if self._saw_grad_consumer or self.grad_scale != 1.0:
+                self._bwd_mode = "off"
+            elif self._probe_clean_steps >= 2:
+                self._bwd_mode = "active"
             self._bwd_fired.clear()
         self._clip_coef = None
         return loss

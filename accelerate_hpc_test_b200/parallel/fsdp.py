@@ -260,6 +260,8 @@ class B200ShardedModule(nn.Module):
         self._shard_params = {}        # id(original param) -> shard-shaped nn.Parameter (generic optimizers)
         self._clip_requested_this_step = False
         self._saw_clip = False
+        self._synced_backwards = 0     # synchronised backward passes since the last optimizer step
+        self._clean_steps = 0          # consecutive optimizer steps that followed exactly one synchronised backward
         self._clip_coef = None
         self._callback_queued = False
         self._units: list[_Unit] = []
@@ -727,6 +729,14 @@ class B200ShardedModule(nn.Module):
 
     def _finish_backward(self):
         self._callback_queued = False
+        if self.requires_gradient_sync:
+            self._synced_backwards += 1
+            if self._fused and self._hyper_ok and self._synced_backwards > 1:
+                raise RuntimeError(
+                    "a second synchronised backward pass ran before optimizer.step(), but the fused reduce-scatter + AdamW already "
+                    "applied the first one's gradients. Accumulate under `accelerator.accumulate(model)` / `no_sync`, or set "
+                    "ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD=0."
+                )
         if self._order and not self._order_locked:
             self._order_locked = True
         for u in self._units:
@@ -916,8 +926,12 @@ class B200ShardedModule(nn.Module):
                 self.comm_stream.wait_stream(self.rs_stream)
                 torch.cuda.current_stream(self.device).wait_stream(self.rs_stream)
         self._clip_coef = None
-        # first step ran in the safe mode; switch to the fused update if nobody asked for the gradients
-        if self._fused_allowed and not self._fused and not self._saw_clip and os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto") == "auto":
+        # the first steps run in the safe mode; the fused update is switched on once two optimizer steps in a row each followed
+        # exactly one synchronised backward (a loop that accumulates by hand steps after several) and nobody asked for the gradients
+        self._clean_steps = self._clean_steps + 1 if self._synced_backwards == 1 else 0
+        self._synced_backwards = 0
+        if (self._fused_allowed and not self._fused and not self._saw_clip and self._clean_steps >= 2
+                and os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto") == "auto"):
             self._fused = True
             for u in self._units:
                 u.grad_shard = None

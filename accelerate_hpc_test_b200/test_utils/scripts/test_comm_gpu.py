@@ -259,7 +259,7 @@ def check_ddp(dev, rank, world, tied: bool = False):
     assert type(model).__name__ == "B200DataParallel", type(model)
     ref_opt = FusedAdamW(ref.parameters(), lr=1e-3, weight_decay=0.0)
     g = torch.Generator().manual_seed(5)
-    for step in range(3):
+    for step in range(4):
         ids_all = torch.randint(0, cfg.vocab_size, (world * 2, 128), generator=g).to(dev)
         ids = ids_all[rank * 2 : rank * 2 + 2]
         opt.zero_grad()
@@ -281,7 +281,7 @@ def check_ddp(dev, rank, world, tied: bool = False):
         assert model.module.lm_head.weight is model.module.model.embed_tokens.weight
     mode = opt.optimizer._bwd_mode
     if os.environ.get("ACCELERATE_B200_FUSED_OPTIM_IN_BACKWARD", "auto") == "auto":
-        assert mode == "active", mode  # steps 2 and 3 updated every bucket right behind its all-reduce
+        assert mode == "active", mode  # steps 3 and 4 updated every bucket right behind its all-reduce
     log(f"ddp ok (tied_embeddings={tied}, worst rel err {worst:.2e}, update behind the all-reduce: {mode})")
     model.release()
     AcceleratorState._reset_state(True)

@@ -244,3 +244,61 @@ def test_zero_grad_set_to_none_argument():
     assert model.weight.grad is not None and model.weight.grad.abs().sum() == 0
     opt.zero_grad()
     assert model.weight.grad is None
+
+
+def test_fused_adamw_switches_to_updates_behind_the_reduction_only_after_two_clean_steps():
+    """The engine-driven fusion (DDP: update a bucket right behind its all-reduce) is armed by probing: two optimizer steps in a row
+    that each followed exactly one reduction of every parameter.  A loop that accumulates by hand never gets there."""
+    import torch
+
+    from accelerate_hpc_test_b200.optim import FusedAdamW
+
+    def fresh():
+        torch.manual_seed(0)
+        p = torch.nn.Parameter(torch.randn(16))
+        opt = FusedAdamW([p], lr=0.1, weight_decay=0.0)
+        assert opt.enable_update_after_reduce(stream=None, mode="auto") and opt._bwd_mode == "probing"
+        assert not opt.enable_update_after_reduce(stream=None)  # armed once
+        return p, opt
+
+    def backward(p, opt, reductions=1):
+        p.grad = torch.ones_like(p)
+        done = [opt.update_reduced(p, p.grad) for _ in range(reductions)]
+        if all(done):
+            p.grad = None  # spent, as the engine does
+        return all(done)
+
+    # one backward per step: probing, probing -> active from the third step on
+    p, opt = fresh()
+    reference = torch.nn.Parameter(p.detach().clone())
+    ref_opt = FusedAdamW([reference], lr=0.1, weight_decay=0.0)
+    modes = []
+    for _ in range(4):
+        updated = backward(p, opt)
+        opt.step()
+        modes.append((opt._bwd_mode, updated))
+        reference.grad = torch.ones_like(reference)
+        ref_opt.step()
+    assert modes == [("probing", False), ("active", False), ("active", True), ("active", True)]
+    assert torch.allclose(p, reference, atol=1e-6)  # the same update, only earlier
+    # step() at micro-batch 0, then after every second backward (the `step % accumulation == 0` idiom): never armed
+    p, opt = fresh()
+    pattern = [1, 2, 2, 2]
+    for reductions in pattern:
+        assert backward(p, opt, reductions) is False
+        opt.step()
+    assert opt._bwd_mode == "probing" and opt._probe_clean_steps == 0
+    # asking for clipping during probing switches the fusion off for good
+    p, opt = fresh()
+    backward(p, opt)
+    opt.set_clip_coef(torch.ones(1))
+    opt.step()
+    assert opt._bwd_mode == "off"
+    # once active, a second reduction before step() is an error rather than a silent double update
+    p, opt = fresh()
+    for _ in range(2):
+        backward(p, opt)
+        opt.step()
+    assert backward(p, opt) is True
+    with pytest.raises(RuntimeError, match="reduced twice"):
+        opt.update_reduced(p, torch.ones_like(p))
