@@ -1121,3 +1121,93 @@ def add_model_config_to_megatron_parser(model_type: str):
         return wrapper
 
     return add_model_config_parser_helper
+
+
+@dataclass(frozen=True)
+class _MegatronModelSpec:
+    """How one model family's config spells the quantities Megatron needs, and which sequence length governs it."""
+
+    model_type_name: str                 # Megatron's name of the family: bert / gpt / t5
+    layers: str                          # config attribute names ...
+    hidden: str
+    heads: str
+    positions: str
+    seq_field: Optional[str]             # plugin field that overrides `seq_length` (None: encoder/decoder lengths are kept apart)
+    pretraining: Optional[bool] = True   # None: decided by the class name (masked-LM head = pre-training)
+    extras: tuple = ()                   # (megatron key, source) pairs; source is a config attribute or a literal in a 1-tuple
+    default_positions: int = 1024
+
+
+_MEGATRON_MODEL_SPECS = {
+    "megatron-bert": _MegatronModelSpec("bert", "num_hidden_layers", "hidden_size", "num_attention_heads", "max_position_embeddings",
+                                        "encoder_seq_length", pretraining=None, extras=(("num_labels", "num_labels"),)),
+    "bert": _MegatronModelSpec("bert", "num_hidden_layers", "hidden_size", "num_attention_heads", "max_position_embeddings",
+                               "encoder_seq_length", pretraining=None, extras=(("num_labels", "num_labels"),)),
+    "gpt2": _MegatronModelSpec("gpt", "n_layer", "n_embd", "n_head", "n_positions", "decoder_seq_length",
+                               extras=(("tokenizer_type", ("GPT2BPETokenizer",)),)),
+    "t5": _MegatronModelSpec("t5", "num_layers", "d_model", "num_heads", "n_positions", None),
+    "llama": _MegatronModelSpec("gpt", "num_hidden_layers", "hidden_size", "num_attention_heads", "max_position_embeddings",
+                                "decoder_seq_length",
+                                extras=(("tokenizer_type", ("Llama2Tokenizer",)), ("num_query_groups", "num_key_value_heads"),
+                                        ("ffn_hidden_size", "intermediate_size"), ("norm_epsilon", "rms_norm_eps"),
+                                        ("rotary_base", "rope_theta"), ("swiglu", (True,)), ("normalization", ("RMSNorm",)),
+                                        ("position_embedding_type", ("rope",)), ("untie_embeddings_and_output_weights", (True,)))),
+}
+
+
+def _describe_for_megatron(spec: _MegatronModelSpec, plugin, model, batch_data) -> None:
+    """Fill ``plugin.megatron_lm_default_args`` (and the plugin's sequence lengths) from ``model.config`` according to ``spec``."""
+    config = model.config
+    out = plugin.megatron_lm_default_args
+    positions = getattr(config, spec.positions, None) or spec.default_positions
+
+    def length_from(batch_key, fallback):
+        if batch_data is not None and batch_key in batch_data:
+            return batch_data[batch_key].shape[1]
+        return fallback
+
+    if spec.seq_field is None:
+        # encoder-decoder: the two lengths stay separate
+        if plugin.encoder_seq_length is None:
+            plugin.encoder_seq_length = length_from("input_ids", positions)
+        if plugin.decoder_seq_length is None:
+            plugin.decoder_seq_length = length_from("labels", positions)
+        out["encoder_seq_length"], out["decoder_seq_length"] = plugin.encoder_seq_length, plugin.decoder_seq_length
+    else:
+        specific = getattr(plugin, spec.seq_field)
+        if specific is not None:
+            if plugin.seq_length is not None and plugin.seq_length != specific:
+                warnings.warn(f"Both `seq_length` and `{spec.seq_field}` are set. Using `{spec.seq_field}`.")
+            plugin.seq_length = specific
+        elif plugin.seq_length is None:
+            plugin.seq_length = length_from("input_ids", positions)
+        out["seq_length"] = plugin.seq_length
+    pretraining = spec.pretraining
+    if pretraining is None:
+        pretraining = "maskedlm" in type(model).__name__.lower()
+    out.update(model_type_name=spec.model_type_name, num_layers=getattr(config, spec.layers), hidden_size=getattr(config, spec.hidden),
+               num_attention_heads=getattr(config, spec.heads), max_position_embeddings=positions, pretraining_flag=pretraining,
+               orig_vocab_size=config.vocab_size, model_return_dict=getattr(config, "return_dict", True))
+    if spec.model_type_name == "gpt":
+        out["return_logits"] = plugin.return_logits
+    for key, source in spec.extras:
+        if isinstance(source, tuple):
+            out[key] = source[0]
+        elif getattr(config, source, None) is not None:
+            out[key] = getattr(config, source)
+
+
+def _register_megatron_parsers() -> None:
+    for model_type, spec in _MEGATRON_MODEL_SPECS.items():
+        def parser(megatron_lm_plugin, model, batch_data, _spec=spec):
+            _describe_for_megatron(_spec, megatron_lm_plugin, model, batch_data)
+
+        parser.__name__ = f"parse_{model_type.replace('-', '_')}_config"
+        add_model_config_to_megatron_parser(model_type)(parser)
+
+
+_register_megatron_parsers()
+parse_bert_config = MODEL_CONFIGS_TO_MEGATRON_PARSERS["megatron-bert"]
+parse_gpt2_config = MODEL_CONFIGS_TO_MEGATRON_PARSERS["gpt2"]
+parse_t5_config = MODEL_CONFIGS_TO_MEGATRON_PARSERS["t5"]
+parse_llama_config = MODEL_CONFIGS_TO_MEGATRON_PARSERS["llama"]

@@ -42,3 +42,61 @@ def test_engine_step_equals_manual_accumulation():
     ev = engine(input_ids=ids)
     assert torch.isfinite(ev) and engine.log_eval_results()
     assert avg_losses_across_data_parallel_group([torch.tensor(2.0)]).item() == 2.0
+
+
+def test_model_configs_are_translated_into_megatron_arguments():
+    import types
+
+    import pytest
+
+    from accelerate_hpc_test_b200.models import LlamaConfig, LlamaForCausalLM
+    from accelerate_hpc_test_b200.utils import MegatronLMPlugin
+    from accelerate_hpc_test_b200.utils.dataclasses import MODEL_CONFIGS_TO_MEGATRON_PARSERS
+
+    assert {"megatron-bert", "bert", "gpt2", "t5", "llama"} <= set(MODEL_CONFIGS_TO_MEGATRON_PARSERS)
+
+    class GPT2LMHeadModel:
+        config = types.SimpleNamespace(n_layer=12, n_embd=768, n_head=12, n_positions=1024, vocab_size=50257, return_dict=True)
+
+    plugin = MegatronLMPlugin()
+    MODEL_CONFIGS_TO_MEGATRON_PARSERS["gpt2"](plugin, GPT2LMHeadModel(), {"input_ids": torch.zeros(4, 512, dtype=torch.long)})
+    args = plugin.megatron_lm_default_args
+    assert args["model_type_name"] == "gpt" and args["num_layers"] == 12 and args["hidden_size"] == 768 and args["seq_length"] == 512
+    assert args["tokenizer_type"] == "GPT2BPETokenizer" and args["pretraining_flag"] is True and args["orig_vocab_size"] == 50257
+    # an explicit decoder length wins over the batch, and over a differing generic one (with a warning)
+    plugin = MegatronLMPlugin(seq_length=256, decoder_seq_length=128)
+    with pytest.warns(UserWarning, match="Using `decoder_seq_length`"):
+        MODEL_CONFIGS_TO_MEGATRON_PARSERS["gpt2"](plugin, GPT2LMHeadModel(), None)
+    assert plugin.seq_length == 128
+
+    class BertForMaskedLM:
+        config = types.SimpleNamespace(num_hidden_layers=2, hidden_size=64, num_attention_heads=4, max_position_embeddings=128,
+                                       num_labels=2, vocab_size=1000, return_dict=True)
+
+    class BertForSequenceClassification(BertForMaskedLM):
+        pass
+
+    plugin = MegatronLMPlugin()
+    MODEL_CONFIGS_TO_MEGATRON_PARSERS["megatron-bert"](plugin, BertForMaskedLM(), None)
+    assert plugin.megatron_lm_default_args["pretraining_flag"] is True and plugin.seq_length == 128  # falls back to the position table
+    plugin = MegatronLMPlugin()
+    MODEL_CONFIGS_TO_MEGATRON_PARSERS["bert"](plugin, BertForSequenceClassification(), None)
+    assert plugin.megatron_lm_default_args["pretraining_flag"] is False and plugin.megatron_lm_default_args["num_labels"] == 2
+
+    class T5ForConditionalGeneration:
+        config = types.SimpleNamespace(num_layers=6, d_model=512, num_heads=8, vocab_size=32128, return_dict=True)
+
+    plugin = MegatronLMPlugin()
+    batch = {"input_ids": torch.zeros(2, 96, dtype=torch.long), "labels": torch.zeros(2, 24, dtype=torch.long)}
+    MODEL_CONFIGS_TO_MEGATRON_PARSERS["t5"](plugin, T5ForConditionalGeneration(), batch)
+    args = plugin.megatron_lm_default_args
+    assert (args["encoder_seq_length"], args["decoder_seq_length"], args["max_position_embeddings"]) == (96, 24, 1024)
+
+    # the native Llama: grouped-query attention, SwiGLU width and RoPE base come along
+    cfg = LlamaConfig.tiny(head_dim=32, hidden_size=64, intermediate_size=128, vocab_size=128, num_attention_heads=4, num_key_value_heads=2)
+    model = LlamaForCausalLM(cfg, dtype=torch.float32)
+    plugin = MegatronLMPlugin()
+    MODEL_CONFIGS_TO_MEGATRON_PARSERS["llama"](plugin, model, {"input_ids": torch.zeros(2, 48, dtype=torch.long)})
+    args = plugin.megatron_lm_default_args
+    assert args["model_type_name"] == "gpt" and args["num_query_groups"] == 2 and args["ffn_hidden_size"] == 128 and args["swiglu"] is True
+    assert args["seq_length"] == 48 and args["normalization"] == "RMSNorm"
