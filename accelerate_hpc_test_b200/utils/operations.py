@@ -42,48 +42,69 @@ def is_namedtuple(data) -> bool:
 
 
 def honor_type(obj, generator):
-    """Rebuild a list / tuple / namedtuple of the same type as ``obj`` from ``generator``."""
-    if is_namedtuple(obj):
-        return type(obj)(*list(generator))
-    return type(obj)(generator)
+    """A sequence of ``obj``'s own type (list, tuple, namedtuple) holding the items of ``generator``."""
+    items = list(generator)
+    return type(obj)(*items) if is_namedtuple(obj) else type(obj)(items)
+
+
+# The framework's batches, metrics and states are *trees*: lists / tuples / namedtuples / mappings nested to any depth with tensors
+# (and arbitrary other objects) at the leaves.  Everything below is written on two primitives: rebuild a tree with its leaves mapped,
+# and walk the leaves in order.
+def _map_leaves(tree, on_leaf: Callable, skip_keys=()):
+    if isinstance(tree, (list, tuple)):
+        return honor_type(tree, (_map_leaves(item, on_leaf, skip_keys) for item in tree))
+    if isinstance(tree, Mapping):
+        return type(tree)({key: value if key in skip_keys else _map_leaves(value, on_leaf, skip_keys) for key, value in tree.items()})
+    return on_leaf(tree)
+
+
+def _leaves(tree):
+    if isinstance(tree, (list, tuple)):
+        for item in tree:
+            yield from _leaves(item)
+    elif isinstance(tree, Mapping):
+        for value in tree.values():
+            yield from _leaves(value)
+    else:
+        yield tree
 
 
 def recursively_apply(func, data, *args, test_type=is_torch_tensor, error_on_other_type=False, **kwargs):
-    """Apply ``func`` to every leaf of ``data`` (nested list/tuple/dict) that passes ``test_type``."""
-    if isinstance(data, (tuple, list)):
-        return honor_type(data, (recursively_apply(func, o, *args, test_type=test_type, error_on_other_type=error_on_other_type, **kwargs) for o in data))
-    if isinstance(data, Mapping):
-        return type(data)({k: recursively_apply(func, v, *args, test_type=test_type, error_on_other_type=error_on_other_type, **kwargs) for k, v in data.items()})
-    if test_type(data):
-        return func(data, *args, **kwargs)
-    if error_on_other_type:
-        raise TypeError(
-            f"Unsupported types ({type(data)}) passed to `{func.__name__}`. Only nested list/tuple/dicts of "
-            f"objects that are valid for `{test_type.__name__}` should be passed."
-        )
-    return data
+    """``data`` with ``func(leaf, *args, **kwargs)`` in place of every leaf that passes ``test_type``; other leaves are kept, or
+    rejected with ``error_on_other_type``."""
+
+    def on_leaf(leaf):
+        if test_type(leaf):
+            return func(leaf, *args, **kwargs)
+        if error_on_other_type:
+            raise TypeError(f"Unsupported types ({type(leaf)}) passed to `{func.__name__}`. Only nested list/tuple/dicts of objects that "
+                            f"are valid for `{test_type.__name__}` should be passed.")
+        return leaf
+
+    return _map_leaves(data, on_leaf)
 
 
 def send_to_device(tensor, device, non_blocking: bool = False, skip_keys=None):
-    """Move every tensor of a nested structure to ``device`` (objects with ``.to`` are moved whole)."""
-    if is_torch_tensor(tensor) or hasattr(tensor, "to"):
+    """The tree with everything that has a ``.to`` moved to ``device`` (a whole ``BatchEncoding``-like container moves itself);
+    mapping entries named in ``skip_keys`` stay where they are."""
+    if isinstance(skip_keys, str):
+        skip_keys = [skip_keys]
+
+    def move(leaf):
+        if not hasattr(leaf, "to"):
+            return leaf
         try:
-            return tensor.to(device, non_blocking=non_blocking)
-        except TypeError:  # .to() without non_blocking
-            return tensor.to(device)
-    if isinstance(tensor, (tuple, list)):
-        return honor_type(tensor, (send_to_device(t, device, non_blocking=non_blocking, skip_keys=skip_keys) for t in tensor))
-    if isinstance(tensor, Mapping):
-        if isinstance(skip_keys, str):
-            skip_keys = [skip_keys]
-        elif skip_keys is None:
-            skip_keys = []
-        return type(tensor)({k: t if k in skip_keys else send_to_device(t, device, non_blocking=non_blocking, skip_keys=skip_keys) for k, t in tensor.items()})
-    return tensor
+            return leaf.to(device, non_blocking=non_blocking)
+        except TypeError:  # a `.to` that does not know `non_blocking`
+            return leaf.to(device)
+
+    if not isinstance(tensor, (list, tuple, Mapping)) or hasattr(tensor, "to"):
+        return move(tensor)
+    return _map_leaves(tensor, move, tuple(skip_keys or ()))
 
 
 def get_data_structure(data):
-    """Same nesting as ``data`` with every tensor replaced by its ``TensorInformation``."""
+    """The same tree with a ``TensorInformation`` (shape, dtype) in place of every tensor — what rank 0 announces before a broadcast."""
     return recursively_apply(lambda t: TensorInformation(shape=t.shape, dtype=t.dtype), data)
 
 
@@ -92,25 +113,22 @@ def get_shape(data):
 
 
 def initialize_tensors(data_structure):
-    """Inverse of ``get_data_structure``: empty tensors of the recorded shapes/dtypes."""
-    return recursively_apply(lambda ti: torch.empty(*ti.shape, dtype=ti.dtype), data_structure, test_type=is_tensor_information)
+    """Inverse of ``get_data_structure``: uninitialised tensors of the announced shapes and dtypes."""
+    return recursively_apply(lambda info: torch.empty(*info.shape, dtype=info.dtype), data_structure, test_type=is_tensor_information)
 
 
 def find_batch_size(data):
-    """Batch size (dim 0 of the first tensor found) of a nested batch."""
-    if isinstance(data, (tuple, list, Mapping)) and len(data) == 0:
+    """Dim 0 of the first leaf of a batch tree; that leaf has to be a tensor."""
+    if isinstance(data, (list, tuple, Mapping)) and len(data) == 0:
         raise ValueError(f"Cannot find the batch size from empty {type(data)}.")
-    if isinstance(data, (tuple, list)):
-        return find_batch_size(data[0])
-    if isinstance(data, Mapping):
-        for k in data.keys():
-            return find_batch_size(data[k])
-    if not isinstance(data, torch.Tensor):
-        raise TypeError(f"Can only find the batch size of tensors but got {type(data)}.")
-    return data.shape[0]
+    first = next(_leaves(data), None)
+    if not isinstance(first, torch.Tensor):
+        raise TypeError(f"Can only find the batch size of tensors but got {type(first)}.")
+    return first.shape[0]
 
 
 def ignorant_find_batch_size(data):
+    """``find_batch_size`` or None."""
     try:
         return find_batch_size(data)
     except (ValueError, TypeError):
@@ -118,14 +136,13 @@ def ignorant_find_batch_size(data):
 
 
 def listify(data):
-    """Tensors -> python lists, recursively."""
-    def _to_list(t):
-        t = t.detach().cpu()
-        if t.dtype == torch.bfloat16:
-            t = t.to(torch.float32)
-        return t.tolist()
+    """Tensors → nested Python lists (bf16 through fp32: ``tolist`` does not know bf16 on every build)."""
 
-    return recursively_apply(_to_list, data)
+    def to_list(t):
+        t = t.detach().cpu()
+        return (t.float() if t.dtype == torch.bfloat16 else t).tolist()
+
+    return recursively_apply(to_list, data)
 
 
 # ------------------------------------------------------------------------------- debug verification
@@ -172,20 +189,8 @@ def chained_operation(function):
 
 
 def find_device(data):
-    """Device of the first tensor found in a nested structure (None if there is none)."""
-    if isinstance(data, Mapping):
-        for obj in data.values():
-            device = find_device(obj)
-            if device is not None:
-                return device
-    elif isinstance(data, (tuple, list)):
-        for obj in data:
-            device = find_device(obj)
-            if device is not None:
-                return device
-    elif isinstance(data, torch.Tensor):
-        return data.device
-    return None
+    """Device of the first tensor in the tree (None when it holds none)."""
+    return next((leaf.device for leaf in _leaves(data) if isinstance(leaf, torch.Tensor)), None)
 
 
 # ------------------------------------------------------------------------------- gather
@@ -276,13 +281,14 @@ def slice_tensors(data, tensor_slice, process_index=None, num_processes=None):
 
 
 def concatenate(data, dim: int = 0):
-    """Concatenate a list of identically nested structures leaf by leaf."""
-    if isinstance(data[0], (tuple, list)):
-        return honor_type(data[0], (concatenate([d[i] for d in data], dim=dim) for i in range(len(data[0]))))
-    if isinstance(data[0], Mapping):
-        return type(data[0])({k: concatenate([d[k] for d in data], dim=dim) for k in data[0].keys()})
-    if not isinstance(data[0], torch.Tensor):
-        raise TypeError(f"Can only concatenate tensors but got {type(data[0])}")
+    """``data`` is a list of identically shaped trees: one tree whose leaves are the concatenations along ``dim``."""
+    head = data[0]
+    if isinstance(head, (list, tuple)):
+        return honor_type(head, (concatenate([tree[i] for tree in data], dim=dim) for i in range(len(head))))
+    if isinstance(head, Mapping):
+        return type(head)({key: concatenate([tree[key] for tree in data], dim=dim) for key in head})
+    if not isinstance(head, torch.Tensor):
+        raise TypeError(f"Can only concatenate tensors but got {type(head)}")
     return torch.cat(data, dim=dim)
 
 
@@ -298,21 +304,17 @@ def pad_across_processes(tensor, dim: int = 0, pad_index: int = 0, pad_first: bo
         if getattr(t, "is_nested", False):
             warnings.warn("Cannot pad nested tensors without more information. Leaving unprocessed.", CannotPadNestedTensorWarning)
             return t
-        if dim >= len(t.shape) or dim < -len(t.shape):
+        if not -t.ndim <= dim < t.ndim:
             return t
-        if dim < 0:
-            dim += len(t.shape)
-        size = torch.tensor(t.shape, device=t.device)[None]
-        sizes = gather(size).cpu()
-        max_size = max(s[dim] for s in sizes)
-        if max_size == t.shape[dim]:
+        dim %= t.ndim
+        # the whole shape goes round, not just `dim`: in debug mode a rank whose tensor has another number of dimensions is caught here
+        longest = int(gather(torch.tensor(t.shape, device=t.device)[None])[:, dim].max())
+        if longest == t.shape[dim]:
             return t
-        new_size = list(t.shape)
-        new_size[dim] = int(max_size)
-        out = t.new_zeros(tuple(new_size)) + pad_index
-        idx = tuple(slice(max_size - t.shape[dim], max_size) if i == dim else slice(None) for i in range(len(new_size))) if pad_first else \
-            tuple(slice(0, t.shape[dim]) if i == dim else slice(None) for i in range(len(new_size)))
-        out[idx] = t
+        shape = list(t.shape)
+        shape[dim] = longest
+        out = t.new_full(shape, pad_index)
+        out.narrow(dim, longest - t.shape[dim] if pad_first else 0, t.shape[dim]).copy_(t)
         return out
 
     return recursively_apply(_pad_one, tensor, error_on_other_type=True, dim=dim, pad_index=pad_index, pad_first=pad_first)
@@ -322,22 +324,10 @@ def pad_input_tensors(tensor, batch_size: int, num_processes: int, dim: int = 0)
     """Pad the batch dim with copies of the last row so it divides evenly over ``num_processes``."""
 
     def _pad_one(t, batch_size, num_processes, dim=0):
-        remainder = batch_size // num_processes
-        last = batch_size - remainder * num_processes
-        if batch_size // num_processes == 0:
-            to_pad = num_processes - batch_size
-        else:
-            to_pad = num_processes - (batch_size // num_processes)
-        if last != 0:
-            to_pad = num_processes - last
-        else:
+        short_by = -batch_size % num_processes
+        if short_by == 0:
             return t
-        new_size = list(t.shape)
-        new_size[0] = batch_size + to_pad
-        out = t.new_zeros(tuple(new_size))
-        out[: t.shape[0]] = t
-        out[t.shape[0]:] = t[-1:]
-        return out
+        return torch.cat([t, t[-1:].expand(short_by, *t.shape[1:])], dim=0)
 
     return recursively_apply(_pad_one, tensor, error_on_other_type=True, batch_size=batch_size, num_processes=num_processes, dim=dim)
 

@@ -254,3 +254,53 @@ def test_version_predicates():
     assert compare_versions(parse("2.1.0"), "==", "2.1") and compare_versions(parse("2.1.0"), "!=", "2.2")
     with pytest.raises(ValueError, match="operation"):
         compare_versions("torch", "~=", "2.0")
+
+
+def test_tree_helpers_keep_container_types_and_order():
+    import collections
+
+    import torch
+
+    from accelerate_hpc_test_b200.utils.operations import (concatenate, find_batch_size, find_device, get_data_structure, honor_type,
+                                                          ignorant_find_batch_size, initialize_tensors, listify, pad_input_tensors,
+                                                          recursively_apply, send_to_device, slice_tensors)
+
+    Point = collections.namedtuple("Point", "x y")
+    tree = {"a": [torch.ones(2, 3), Point(torch.zeros(2), "label")], "b": (torch.arange(4).view(2, 2),), "c": 7}
+    doubled = recursively_apply(lambda t: t * 2, tree)
+    assert isinstance(doubled["a"][1], Point) and doubled["a"][1].y == "label" and doubled["c"] == 7 and isinstance(doubled["b"], tuple)
+    assert doubled["a"][0].sum() == 12 and list(doubled) == ["a", "b", "c"]
+    with pytest.raises(TypeError, match="Unsupported types"):
+        recursively_apply(lambda t: t, tree, error_on_other_type=True)
+    assert honor_type(Point(1, 2), iter([3, 4])) == Point(3, 4) and honor_type([0], iter((1, 2))) == [1, 2]
+    assert find_batch_size(tree) == 2 and find_device(tree) == torch.device("cpu") and find_device({"x": [1, "s"]}) is None
+    with pytest.raises(ValueError):
+        find_batch_size([])
+    with pytest.raises(TypeError):
+        find_batch_size({"x": "text"})
+    assert ignorant_find_batch_size("text") is None
+    # structure round trip
+    blueprint = get_data_structure(tree)
+    rebuilt = initialize_tensors(blueprint)
+    assert rebuilt["a"][0].shape == (2, 3) and rebuilt["b"][0].dtype == torch.int64 and rebuilt["c"] == 7
+    # skip_keys and objects that move themselves
+    class Movable:
+        def __init__(self):
+            self.where = None
+
+        def to(self, device):
+            self.where = device
+            return self
+
+    moved = send_to_device({"keep": torch.ones(1), "skip": torch.ones(1), "obj": Movable()}, "meta", skip_keys="skip")
+    assert moved["keep"].device.type == "meta" and moved["skip"].device.type == "cpu" and moved["obj"].where == "meta"
+    assert listify({"v": torch.tensor([1.5, 2.5], dtype=torch.bfloat16)}) == {"v": [1.5, 2.5]}
+    assert slice_tensors({"v": torch.arange(6)}, slice(1, 3))["v"].tolist() == [1, 2]
+    parts = [{"v": torch.ones(1, 2), "w": (torch.zeros(1),)}, {"v": torch.ones(3, 2), "w": (torch.zeros(2),)}]
+    joined = concatenate(parts)
+    assert joined["v"].shape == (4, 2) and joined["w"][0].shape == (3,)
+    with pytest.raises(TypeError):
+        concatenate([{"v": 1}, {"v": 2}])
+    padded = pad_input_tensors({"v": torch.arange(10).view(5, 2)}, batch_size=5, num_processes=4)
+    assert padded["v"].shape == (8, 2) and padded["v"][5:].tolist() == [[8, 9]] * 3  # the last row repeated
+    assert pad_input_tensors(torch.ones(8, 1), 8, 4).shape == (8, 1)
