@@ -1,5 +1,9 @@
-"""Distributed checks of the collective helpers; run under any launcher (reference
-src/accelerate/test_utils/scripts/test_ops.py:37-148)."""
+"""Launched checks of the tensor-tree collectives (``gather``, ``gather_object``, ``broadcast``, ``pad_across_processes``, ``reduce``,
+``copy_tensor_to_devices``) and of the debug-mode shape verification; works on any number of processes, including one.
+Behaviour of reference ``src/accelerate/test_utils/scripts/test_ops.py:37-148``.
+
+    accelerate launch --num_processes 2 --cpu -m accelerate_hpc_test_b200.test_utils.scripts.test_ops
+"""
 
 import torch
 
@@ -15,86 +19,79 @@ from accelerate_hpc_test_b200.utils.operations import (
 )
 
 
-def create_tensor(state):
-    return (torch.arange(state.num_processes) + 1.0 + (state.num_processes * state.process_index)).to(state.device)
+def ramp(state):
+    """Rank r holds ``[r*P + 1, ..., r*P + P]``: gathered in rank order the values read 1 .. P*P."""
+    world = state.num_processes
+    return (torch.arange(world) + 1.0 + world * state.process_index).to(state.device)
+
+
+def every_rank_sum(world):
+    return sum(torch.arange(world) + 1.0 + world * rank for rank in range(world))
 
 
 def test_gather(state):
-    tensor = create_tensor(state)
-    gathered = gather(tensor)
-    assert gathered.tolist() == list(range(1, state.num_processes**2 + 1))
+    assert gather(ramp(state)).tolist() == list(range(1, state.num_processes**2 + 1))
 
 
 def test_gather_object(state):
-    obj = [state.process_index]
-    gathered = gather_object(obj)
-    assert len(gathered) == state.num_processes and gathered == list(range(state.num_processes))
+    assert gather_object([state.process_index]) == list(range(state.num_processes))
 
 
 def test_gather_non_contiguous(state):
-    tensor = torch.arange(12, device=state.device).view(4, 3).t()
-    assert not tensor.is_contiguous()
-    out = gather(tensor)
-    assert out.shape[0] == 3 * state.num_processes
+    view = torch.arange(12, device=state.device).view(4, 3).t()
+    assert not view.is_contiguous()
+    assert gather(view).shape[0] == 3 * state.num_processes  # made contiguous on the way, not refused
 
 
 def test_broadcast(state):
-    tensor = create_tensor(state)
-    out = broadcast(tensor)
-    assert out.shape == torch.Size([state.num_processes]) and out.tolist() == list(range(1, state.num_processes + 1))
+    out = broadcast(ramp(state))
+    assert out.tolist() == list(range(1, state.num_processes + 1))  # everybody now holds rank 0's values
 
 
 def test_pad_across_processes(state):
-    if state.is_main_process:
-        tensor = torch.arange(state.num_processes + 1).to(state.device)
-    else:
-        tensor = torch.arange(state.num_processes).to(state.device)
-    padded = pad_across_processes(tensor)
-    assert padded.shape == torch.Size([state.num_processes + 1])
+    world = state.num_processes
+    mine = torch.arange(world + 1 if state.is_main_process else world).to(state.device)  # rank 0 is one longer
+    assert pad_across_processes(mine).shape == (world + 1,)
     if not state.is_main_process:
-        assert padded.tolist() == list(range(0, state.num_processes)) + [0]
-    first = pad_across_processes(tensor, pad_first=True, pad_index=-1)
-    if not state.is_main_process:
-        assert first.tolist() == [-1] + list(range(0, state.num_processes))
+        assert pad_across_processes(mine).tolist() == [*range(world), 0]
+        assert pad_across_processes(mine, pad_first=True, pad_index=-1).tolist() == [-1, *range(world)]
 
 
 def test_reduce_sum(state):
-    tensor = create_tensor(state)
-    out = reduce(tensor, "sum")
-    n = state.num_processes
-    expected = sum(torch.arange(n) + 1.0 + n * r for r in range(n))
-    assert torch.allclose(out.cpu(), expected), (out, expected)
+    assert torch.allclose(reduce(ramp(state), "sum").cpu(), every_rank_sum(state.num_processes))
 
 
 def test_reduce_mean(state):
-    tensor = create_tensor(state)
-    out = reduce(tensor, "mean")
-    n = state.num_processes
-    expected = sum(torch.arange(n) + 1.0 + n * r for r in range(n)) / n
-    assert torch.allclose(out.cpu(), expected)
+    world = state.num_processes
+    assert torch.allclose(reduce(ramp(state), "mean").cpu(), every_rank_sum(world) / world)
 
 
 def test_op_checker(state):
+    """In debug mode the collectives compare operand shapes across ranks first and raise instead of hanging."""
     if state.num_processes < 2:
         return
     state.debug = True
-    if state.process_index == 0:
-        data = {"tensor": torch.tensor([[0.0, 1, 2, 3, 4]]).to(state.device)}
-    else:
-        data = {"tensor": torch.tensor([[[0.0, 1, 2, 3, 4, 5]]]).to(state.device)}
-    for fn in (lambda: gather(data), lambda: broadcast(data), lambda: reduce(data), lambda: pad_across_processes(data, dim=0)):
-        try:
-            fn()
+    try:
+        width = 5 if state.process_index == 0 else 6
+        shape = (1, width) if state.process_index == 0 else (1, 1, width)
+        data = {"tensor": torch.arange(width, dtype=torch.float32).reshape(shape).to(state.device)}
+        for call in (lambda: gather(data), lambda: broadcast(data), lambda: reduce(data), lambda: pad_across_processes(data, dim=0)):
+            try:
+                call()
+            except DistributedOperationException:
+                continue
             raise AssertionError("shape mismatch went unnoticed in debug mode")
-        except DistributedOperationException:
-            pass
-    state.debug = False
+    finally:
+        state.debug = False
 
 
 def test_copy_tensor_to_devices(state):
-    tensor = torch.tensor([1, 2, 3], dtype=torch.int).to(state.device) if state.is_main_process else None
-    out = copy_tensor_to_devices(tensor)
-    assert torch.allclose(out.cpu(), torch.tensor([1, 2, 3], dtype=torch.int))
+    only_on_main = torch.tensor([1, 2, 3], dtype=torch.int).to(state.device) if state.is_main_process else None
+    assert copy_tensor_to_devices(only_on_main).cpu().tolist() == [1, 2, 3]
+
+
+CHECKS = (test_gather, test_gather_object, test_gather_non_contiguous, test_broadcast, test_pad_across_processes, test_reduce_sum,
+          test_reduce_mean, test_op_checker, test_copy_tensor_to_devices)
 
 
 def _mp_fn(index):
@@ -104,10 +101,9 @@ def _mp_fn(index):
 def main():
     state = PartialState()
     state.print(f"State: {state}")
-    for fn in (test_gather, test_gather_object, test_gather_non_contiguous, test_broadcast, test_pad_across_processes,
-               test_reduce_sum, test_reduce_mean, test_op_checker, test_copy_tensor_to_devices):
-        state.print(f"running {fn.__name__}")
-        fn(state)
+    for check in CHECKS:
+        state.print(f"running {check.__name__}")
+        check(state)
     state.wait_for_everyone()
     state.print("test_ops: all passed")
 
