@@ -33,7 +33,7 @@ def _run_inproc(script, *args):
     for st in (AcceleratorState, GradientState, PartialState):
         st._reset_state(True) if st is AcceleratorState else st._reset_state()
     path = os.path.join(EX, script)
-    old_argv, old_path = sys.argv, list(sys.path)
+    old_argv, old_path, old_env = sys.argv, list(sys.path), dict(os.environ)
     sys.argv = [path, *args]
     sys.path.insert(0, os.path.dirname(path))  # what `python script.py` does
     buf = io.StringIO()
@@ -42,6 +42,8 @@ def _run_inproc(script, *args):
             runpy.run_path(path, run_name="__main__")
     finally:
         sys.argv, sys.path[:] = old_argv, old_path
+        os.environ.clear()
+        os.environ.update(old_env)  # e.g. ACCELERATE_USE_DEEPSPEED, which an Accelerator with a DeepSpeed plugin exports
         for mod in ("_common", "nlp_example", "cv_example"):
             sys.modules.pop(mod, None)
     return buf.getvalue()
