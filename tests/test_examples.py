@@ -74,6 +74,8 @@ def test_more_by_feature_examples_single_process():
     out = _run_inproc("by_feature/cross_validation.py", *SMALL, "--num_folds", "2")
     assert "fold 1 epoch 0" in out and "average of 2 folds on the test set" in out and "'eval_samples': 41" in out
     assert "epoch 0" in _run_inproc("by_feature/schedule_free.py", *SMALL)
+    out = _run_inproc("by_feature/fsdp_with_peak_mem_tracking.py", *SMALL, "--use_fsdp")  # (two ranks: test_launched_scripts' memory script)
+    assert "train: device memory used" in out and "epoch 0" in out
     out = _run_inproc("by_feature/deepspeed_with_config_support.py", *SMALL,
                       "--deepspeed_config", os.path.join(EX, "deepspeed_config_templates", "zero_stage3_config.json"))
     assert "optimizer: FusedAdamW, ZeRO stage 3" in out and "epoch 0" in out
@@ -116,8 +118,7 @@ def test_deepspeed_templates_and_slurm_scripts_are_well_formed():
 
 
 @pytest.mark.parametrize("script,extra", [("by_feature/local_sgd.py", ["--local_sgd_steps", "2"]), ("by_feature/multi_process_metrics.py", []),
-                                          ("by_feature/ddp_comm_hook.py", ["--ddp_comm_hook", "bf16"]),
-                                          ("by_feature/fsdp_with_peak_mem_tracking.py", ["--use_fsdp"])])
+                                          ("by_feature/ddp_comm_hook.py", ["--ddp_comm_hook", "bf16"])])
 def test_by_feature_two_processes(script, extra):
     assert "'eval_samples': 41" in _launch(2, script, *SMALL, *extra)
 
