@@ -668,17 +668,26 @@ class Accelerator:
                 result.append(obj)
         # optimizers learn about the engines that own their parameters (sharded update, fused clip)
         for _, engine_model in models_this_call:
+            remap = getattr(engine_model, "_b200_param_remap", None)
+            if remap:
+                # the model's parameters were replaced by `prepare` (torch FSDP2 fallback: same repair the reference makes after
+                # fully_shard, accelerator.py:1690-1744; a transformers Llama adopted as the native model): re-point the optimizers.
+                # A replacement of None means "folded into another parameter"; nothing is listed twice.
+                for opt in optimizers_this_call or self._optimizers:
+                    listed = set()
+                    for group in opt.optimizer.param_groups:
+                        fresh = []
+                        for q in group["params"]:
+                            new_q = remap.get(id(q), q)
+                            if new_q is not None and id(new_q) not in listed:
+                                listed.add(id(new_q))
+                                fresh.append(new_q)
+                        group["params"] = fresh
+                    opt.optimizer.state.clear()
             engine = engine_model if hasattr(engine_model, "bind_optimizer") else None
             if engine is not None:
                 for opt in optimizers_this_call or self._optimizers:
                     engine.bind_optimizer(opt)
-            remap = getattr(engine_model, "_b200_param_remap", None)
-            if remap:
-                # torch FSDP2 fallback: same repair the reference makes after fully_shard (accelerator.py:1690-1744)
-                for opt in optimizers_this_call or self._optimizers:
-                    for group in opt.optimizer.param_groups:
-                        group["params"] = [remap.get(id(q), q) for q in group["params"]]
-                    opt.optimizer.state.clear()
         # schedulers last: they need the prepared optimizers
         result = [self.prepare_scheduler(o) if (_is_scheduler(o) and not getattr(o, "_is_accelerate_prepared", False)) else o for o in result]
         for item in result:
@@ -764,11 +773,16 @@ class Accelerator:
             model = model.to(self.device)
 
         if not evaluation_mode:
-            if self.distributed_type == DistributedType.MULTI_GPU or (self.distributed_type == DistributedType.MULTI_CPU):
+            pc = self.parallelism_config
+            model_parallel = pc is not None and (pc.tp_enabled or pc.sp_enabled or pc.cp_enabled)
+            if model_parallel or self.distributed_type in (DistributedType.FSDP, DistributedType.DEEPSPEED, DistributedType.MEGATRON_LM):
+                # tensor / sequence / context parallelism always runs inside the sharded engine, also without a sharding plugin
+                # (dp_shard = 1: a shard group of one, no gather or reduce kernels): ranks of one model-parallel group hold
+                # different weight shards, so a data-parallel all-reduce over all ranks would be wrong
+                model = self._wrap_sharded(model)
+            elif self.distributed_type in (DistributedType.MULTI_GPU, DistributedType.MULTI_CPU):
                 if any(p.requires_grad for p in model.parameters()):
                     model = self._wrap_data_parallel(model)
-            elif self.distributed_type in (DistributedType.FSDP, DistributedType.DEEPSPEED, DistributedType.MEGATRON_LM):
-                model = self._wrap_sharded(model)
         # activation checkpointing can be requested through the FSDP plugin even on one process
         plugin = self.state.fsdp_plugin
         if plugin is not None and plugin.activation_checkpointing and self.distributed_type == DistributedType.NO:
@@ -816,6 +830,33 @@ class Accelerator:
             self.ddp_handler.register_comm_hook(model)
         return model
 
+    def _adopt_for_native_parallelism(self, model):
+        """Tensor / sequence / context parallelism are implemented on the native Llama.  A ``transformers`` Llama (recognised by
+        its config) is therefore rebuilt as the native model with the same weights — where the reference accepts a
+        ``tp_plan="auto"`` transformers model.  The optimizer, created on the transformers parameters, is re-pointed in
+        ``prepare`` through ``_b200_param_remap`` (fused projections take the group of their first part)."""
+        from .models.llama import LlamaForCausalLM
+
+        if isinstance(model, LlamaForCausalLM) or getattr(getattr(model, "config", None), "model_type", None) != "llama":
+            return model
+        on_gpu = self.device.type == "cuda"
+        native = LlamaForCausalLM.from_transformers(model, dtype=torch.bfloat16 if on_gpu else None, device=self.device)
+        theirs = dict(model.named_parameters())
+        remap = {id(p): None for p in theirs.values()}  # None: folded into a fused native parameter, dropped from the optimizer
+        representative = {}
+        for name, _ in native.named_parameters():
+            representative[name] = name.replace("qkv_proj", "q_proj").replace("gate_up_proj", "gate_proj")
+        mine = dict(native.named_parameters())
+        for name, param in mine.items():
+            source = theirs.get(representative[name])
+            if source is not None:
+                remap[id(source)] = param
+        native._b200_param_remap = remap
+        logger.warning("a transformers Llama was rebuilt as the native Llama (same weights) so that tensor / sequence / context "
+                       "parallelism can run on the fused kernels; use `accelerator.unwrap_model(model).hf_state_dict()` to export "
+                       "weights under transformers' names", main_process_only=True)
+        return native
+
     def _wrap_sharded(self, model):
         from .parallel.fsdp import B200ShardedModule
 
@@ -828,6 +869,8 @@ class Accelerator:
             plugin.set_mixed_precision(self.mixed_precision)
         pc = self.parallelism_config
         mesh = self.torch_device_mesh
+        if pc is not None and (pc.tp_enabled or pc.sp_enabled or pc.cp_enabled):
+            model = self._adopt_for_native_parallelism(model)
         if pc is not None and pc.tp_enabled:
             from .parallel.tensor_parallel import apply_tensor_parallel
 

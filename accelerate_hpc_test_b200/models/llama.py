@@ -398,6 +398,44 @@ class LlamaForCausalLM(nn.Module):
             out[pre + "post_attention_layernorm.weight"] = l.post_attention_layernorm.weight
         return {k: v.detach() for k, v in out.items()}
 
+    @classmethod
+    def from_transformers(cls, hf_model, dtype: Optional[torch.dtype] = None, device=None) -> "LlamaForCausalLM":
+        """The native counterpart of a ``transformers`` ``LlamaForCausalLM`` (recognised by its config, not by import), with its
+        weights: what ``Accelerator.prepare`` builds when tensor / sequence / context parallelism is asked for a transformers Llama.
+        Refuses variants the native kernels do not implement (attention / MLP biases, scaled RoPE, sliding windows)."""
+        hc = hf_model.config
+        if getattr(hc, "model_type", None) != "llama":
+            raise NotImplementedError(f"only Llama-architecture models can be adopted, got model_type={getattr(hc, 'model_type', None)!r}")
+        unsupported = []
+        if getattr(hc, "attention_bias", False) or getattr(hc, "mlp_bias", False):
+            unsupported.append("attention_bias / mlp_bias")
+        scaling = getattr(hc, "rope_scaling", None) or getattr(hc, "rope_parameters", None)
+        if isinstance(scaling, dict) and scaling.get("rope_type", scaling.get("type", "default")) not in ("default", None):
+            unsupported.append(f"rope scaling {scaling.get('rope_type', scaling.get('type'))!r}")
+        if getattr(hc, "sliding_window", None):
+            unsupported.append("sliding_window")
+        if unsupported:
+            raise NotImplementedError("the native Llama does not implement: " + ", ".join(unsupported))
+        head_dim = getattr(hc, "head_dim", None) or hc.hidden_size // hc.num_attention_heads
+        theta = getattr(hc, "rope_theta", None)
+        if theta is None and isinstance(scaling, dict):
+            theta = scaling.get("rope_theta")
+        cfg = LlamaConfig(vocab_size=hc.vocab_size, hidden_size=hc.hidden_size, intermediate_size=hc.intermediate_size,
+                          num_hidden_layers=hc.num_hidden_layers, num_attention_heads=hc.num_attention_heads,
+                          num_key_value_heads=getattr(hc, "num_key_value_heads", None) or hc.num_attention_heads, head_dim=head_dim,
+                          rope_theta=float(theta or 10000.0), rms_norm_eps=hc.rms_norm_eps,
+                          max_position_embeddings=hc.max_position_embeddings, tie_word_embeddings=bool(getattr(hc, "tie_word_embeddings", False)))
+        first = next(hf_model.parameters())
+        native = cls(cfg, dtype=dtype or first.dtype, device=device if device is not None else first.device)
+        sd = dict(hf_model.state_dict())
+        if cfg.tie_word_embeddings:
+            sd.pop("lm_head.weight", None)
+        native.load_hf_state_dict(sd)
+        if cfg.tie_word_embeddings:
+            native.tie_weights()
+        native.train(hf_model.training)
+        return native
+
     @torch.no_grad()
     def load_hf_state_dict(self, sd: dict):
         mine = self.hf_state_dict()

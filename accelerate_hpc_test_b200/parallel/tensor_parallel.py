@@ -324,6 +324,7 @@ def apply_tensor_parallel(model: nn.Module, tp_mesh, tp_config=None, max_tokens:
     D = cfg.head_dim
     nq, nk = cfg.num_attention_heads * D, cfg.num_key_value_heads * D
     I = cfg.intermediate_size
+    before = {name: param for name, param in model.named_parameters()}
     for layer in model.model.layers:
         attn, mlp = layer.self_attn, layer.mlp
         w = attn.qkv_proj.weight.data
@@ -343,6 +344,16 @@ def apply_tensor_parallel(model: nn.Module, tp_mesh, tp_config=None, max_tokens:
         _mark_replicated(p, comm)
     model.model.tp_comm = comm
     model.tp_comm = comm
+    # the sharded linears hold new Parameter objects: tell `Accelerator.prepare` how to re-point optimizers created before
+    # (chained behind an earlier replacement, e.g. a transformers model adopted as the native one)
+    after = dict(model.named_parameters())
+    replaced = {id(old): after[name] for name, old in before.items() if name in after and after[name] is not old}
+    earlier = getattr(model, "_b200_param_remap", None)
+    if earlier:
+        model._b200_param_remap = {key: (replaced.get(id(new), new) if new is not None else None) for key, new in earlier.items()}
+        model._b200_param_remap.update({key: new for key, new in replaced.items() if key not in model._b200_param_remap})
+    else:
+        model._b200_param_remap = replaced
     return model
 
 
