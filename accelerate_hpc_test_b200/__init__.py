@@ -9,7 +9,7 @@ reference's surface; the hot path underneath is hand-written sm_100a CUDA (``ops
 native parallel engines over peer-mapped NVLink memory (``parallel/``).
 """
 
-__version__ = "0.1.0"
+__version__ = "0.2.0"
 
 from .accelerator import Accelerator
 from .data_loader import skip_first_batches

@@ -136,7 +136,7 @@ def __getattr__(name):
                      "get_mixed_precision_context_manager has_offloaded_params id_tensor_storage infer_auto_device_map is_peft_model "
                      "load_checkpoint_in_model load_offloaded_weights load_state_dict named_module_tensors retie_parameters "
                      "set_module_tensor_to_device shard_checkpoint get_state_dict_offloaded_model get_grad_scaler clean_device_map "
-                     "align_module_device get_state_dict_from_offload calculate_maximum_sizes").split(),
+                     "align_module_device get_state_dict_from_offload calculate_maximum_sizes fallback_allocate get_module_size_with_ties").split(),
         "offload": "OffloadedWeightsLoader PrefixedDataset extract_submodules_state_dict load_offloaded_weight offload_state_dict offload_weight save_offload_index".split(),
         "fsdp_utils": ("disable_fsdp_ram_efficient_loading enable_fsdp_ram_efficient_loading ensure_weights_retied fsdp2_apply_ac "
                        "fsdp2_load_full_state_dict fsdp2_prepare_model fsdp2_switch_optimizer_parameters get_fsdp2_grad_scaler "

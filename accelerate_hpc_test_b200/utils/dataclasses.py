@@ -1136,6 +1136,36 @@ class _MegatronModelSpec:
     pretraining: Optional[bool] = True   # None: decided by the class name (masked-LM head = pre-training)
     extras: tuple = ()                   # (megatron key, source) pairs; source is a config attribute or a literal in a 1-tuple
     default_positions: int = 1024
+    config_seq: Optional[str] = None     # config attribute that, when present, beats the plugin's family-specific length
+    derive: Optional[Callable] = None    # config -> dict of entries that are computed rather than read
+
+
+# GLM-4.5 mixture-of-experts (reference utils/dataclasses.py:2940-3021): a GPT-family decoder with grouped-query attention, half-rotary
+# RoPE, sigmoid-scored routing with an expert bias, and shared experts of the routed experts' width.
+_GLM4_MOE_EXTRAS = (
+    ("tokenizer_type", ("HuggingFaceTokenizer",)), ("kv_channels", "head_dim"), ("original_model_type", "model_type"),
+    ("position_embedding_type", ("rope",)), ("rope_type", ("rope",)), ("rotary_base", "rope_theta"),
+    ("rotary-percent", (0.5,)), ("rotary_percent", "partial_rotary_factor"),
+    ("qk_layernorm", "use_qk_norm"), ("add_bias_linear", (False,)), ("add_qkv_bias", (True,)),
+    ("group_query_attention", (True,)), ("num_query_groups", "num_key_value_heads"), ("ffn_hidden_size", "intermediate_size"),
+    ("normalization", ("RMSNorm",)), ("norm_epsilon", (1e-3,)), ("swiglu", (True,)), ("use_flash_attn", (True,)),
+    ("moe_ffn_hidden_size", "moe_intermediate_size"), ("moe_shared_expert_intermediate_size", "moe_intermediate_size"),
+    ("moe_router_pre_softmax", (True,)), ("moe_router_score_function", ("sigmoid",)), ("moe_router_enable_expert_bias", (True,)),
+    ("moe_router_bias_update_rate", (0,)), ("moe_router_load_balancing_type", ("seq_aux_loss",)),
+    ("moe_token_dispatcher_type", ("alltoall",)), ("moe_router_topk", "num_experts_per_tok"),
+    ("moe_router_topk_scaling_factor", "routed_scaling_factor"), ("num_experts", "n_routed_experts"),
+    ("moe_grouped_gemm", (True,)), ("moe_router_dtype", ("fp32",)), ("moe_permute_fusion", (True,)), ("moe_aux_loss_coeff", (0,)),
+    ("eos_token_id", "eos_token_id"), ("bf16", "bf16"),
+)
+
+
+def _glm4_moe_derived(config) -> dict:
+    dense = int(getattr(config, "first_k_dense_replace", 0))
+    out = {"moe_layer_freq": [0] * dense + [1] * (config.num_hidden_layers - dense),
+           "untie_embeddings_and_output_weights": not getattr(config, "tie_word_embeddings", False)}
+    if getattr(config, "fp8_param", False):
+        out.update({key: getattr(config, key) for key in ("fp8", "fp8_param", "fp8_param_gather", "fp8_recipe")})
+    return out
 
 
 _MEGATRON_MODEL_SPECS = {
@@ -1152,6 +1182,9 @@ _MEGATRON_MODEL_SPECS = {
                                         ("ffn_hidden_size", "intermediate_size"), ("norm_epsilon", "rms_norm_eps"),
                                         ("rotary_base", "rope_theta"), ("swiglu", (True,)), ("normalization", ("RMSNorm",)),
                                         ("position_embedding_type", ("rope",)), ("untie_embeddings_and_output_weights", (True,)))),
+    "glm4_moe": _MegatronModelSpec("gpt", "num_hidden_layers", "hidden_size", "num_attention_heads", "max_position_embeddings",
+                                   "decoder_seq_length", pretraining=False, config_seq="max_sequence_length",
+                                   extras=_GLM4_MOE_EXTRAS, derive=_glm4_moe_derived),
 }
 
 
@@ -1175,7 +1208,12 @@ def _describe_for_megatron(spec: _MegatronModelSpec, plugin, model, batch_data) 
         out["encoder_seq_length"], out["decoder_seq_length"] = plugin.encoder_seq_length, plugin.decoder_seq_length
     else:
         specific = getattr(plugin, spec.seq_field)
-        if specific is not None:
+        from_config = getattr(config, spec.config_seq, None) if spec.config_seq else None
+        if spec.config_seq is not None:
+            # this family settles the length once: plugin value, else the config's own, else the family field, the batch, the positions
+            if plugin.seq_length is None:
+                plugin.seq_length = from_config or specific or length_from("input_ids", positions)
+        elif specific is not None:
             if plugin.seq_length is not None and plugin.seq_length != specific:
                 warnings.warn(f"Both `seq_length` and `{spec.seq_field}` are set. Using `{spec.seq_field}`.")
             plugin.seq_length = specific
@@ -1195,6 +1233,8 @@ def _describe_for_megatron(spec: _MegatronModelSpec, plugin, model, batch_data) 
             out[key] = source[0]
         elif getattr(config, source, None) is not None:
             out[key] = getattr(config, source)
+    if spec.derive is not None:
+        out.update(spec.derive(config))
 
 
 def _register_megatron_parsers() -> None:
@@ -1211,3 +1251,4 @@ parse_bert_config = MODEL_CONFIGS_TO_MEGATRON_PARSERS["megatron-bert"]
 parse_gpt2_config = MODEL_CONFIGS_TO_MEGATRON_PARSERS["gpt2"]
 parse_t5_config = MODEL_CONFIGS_TO_MEGATRON_PARSERS["t5"]
 parse_llama_config = MODEL_CONFIGS_TO_MEGATRON_PARSERS["llama"]
+parse_glm4_moe_config = MODEL_CONFIGS_TO_MEGATRON_PARSERS["glm4_moe"]

@@ -204,6 +204,87 @@ def calculate_maximum_sizes(model: nn.Module):
     return sizes[""], get_max_layer_size(_top_level_entries(model), sizes, keep_whole)
 
 
+def _holds(owner: str, tensor_name: str) -> bool:
+    """Whether ``tensor_name`` lives at or below ``owner`` ("1" holds "1.weight" but not "10.weight")."""
+    return tensor_name == owner or tensor_name.startswith(owner + ".")
+
+
+def _entries_below(name: str, entry) -> list:
+    """``entry`` taken apart one level: its own parameters, then its children, under their full names."""
+    if not isinstance(entry, nn.Module):
+        return []
+    return [(f"{name}.{n}", v) for n, v in [*entry.named_parameters(recurse=False), *entry.named_children()]]
+
+
+def get_module_size_with_ties(tied_params: list, module_size: int, module_sizes: dict, modules_to_treat: list):
+    """Bytes needed to place a module *together with* the entries of ``modules_to_treat`` that hold the parameters tied to it
+    (``tied_params``: names outside the module).  A tied parameter shares storage with one already counted in ``module_size``, so
+    each is charged its holder minus itself.  Returns ``(bytes, holder names, holders)``, holders in first-seen order
+    (reference utils/modeling.py:1134-1167)."""
+    names, holders, total = [], [], module_size
+    for tied in tied_params:
+        holder = next(((n, m) for n, m in modules_to_treat if _holds(n, tied)), None)
+        if holder is None:
+            raise ValueError(f"tied parameter {tied!r} is not below any of the entries still to be placed")
+        if holder[0] not in names:
+            names.append(holder[0])
+            holders.append(holder[1])
+            total += module_sizes[holder[0]]
+        total -= module_sizes[tied]
+    return total, names, holders
+
+
+def _open_ancestors(modules: list, name: str) -> list:
+    """``modules`` with every ancestor of ``name`` taken apart, outermost first, so that ``name`` is an entry of its own."""
+    opened = list(modules)
+    steps = name.split(".")
+    for depth in range(1, len(steps)):
+        ancestor = ".".join(steps[:depth])
+        at = next((i for i, (n, _) in enumerate(opened) if n == ancestor), None)
+        if at is not None:
+            opened[at : at + 1] = _entries_below(*opened[at])
+    return opened
+
+
+def fallback_allocate(modules: list, module_sizes: dict, size_limit, no_split_module_classes: Optional[list] = None,
+                      tied_parameters: Optional[list] = None):
+    """The first piece of ``modules`` that still fits ``size_limit`` — used by the device-map packer to fill the room a device has
+    left when the module whose turn it is does not fit and cannot be divided.
+
+    ``modules`` is searched in order; an entry that is too big is taken apart (unless its class is in ``no_split_module_classes``)
+    and its pieces are searched before the entries after it.  "Fits" counts the entries that would have to come along because a
+    parameter inside the piece is tied to one inside them.  Returns ``(name, piece, rest)``; ``rest`` is ``modules`` with the piece's
+    ancestors taken apart and the piece removed.  ``(None, None, modules)`` when nothing fits (reference utils/modeling.py:1170-1275).
+    """
+    try:
+        limit = convert_file_size_to_int(size_limit)
+    except ValueError:
+        return None, None, modules
+    keep_whole = set(no_split_module_classes or [])
+    groups = tied_parameters or []
+
+    def needed(name: str) -> int:
+        crossing = [g for g in groups if any(_holds(name, p) for p in g) and not all(_holds(name, p) for p in g)]
+        outside = [p for g in crossing for p in g if not _holds(name, p)]
+        if not outside:
+            return module_sizes[name]
+        others = [(n, m) for n, m in _open_ancestors(modules, name) if n != name]
+        try:
+            return get_module_size_with_ties(outside, module_sizes[name], module_sizes, others)[0]
+        except ValueError:  # the tied partner was placed already: nothing more to bring
+            return module_sizes[name]
+
+    queue = list(modules)
+    while queue:
+        name, piece = queue.pop(0)
+        if needed(name) <= limit:
+            rest = [(n, m) for n, m in _open_ancestors(modules, name) if n != name]
+            return name, piece, rest
+        if isinstance(piece, nn.Module) and type(piece).__name__ not in keep_whole and any(True for _ in piece.children()):
+            queue = _entries_below(name, piece) + queue
+    return None, None, modules
+
+
 # ------------------------------------------------------------------------------------------------- tensor placement
 def _owner_of(module: nn.Module, dotted: str) -> tuple[nn.Module, str]:
     """The sub-module that directly holds ``dotted`` and the tensor's own name."""
@@ -581,21 +662,16 @@ def infer_auto_device_map(model: nn.Module, max_memory: Optional[dict] = None, n
         module_size = module_sizes[name]
         # tied partners not yet placed must come along
         partners = [p for p in tied_group_of(name) if not any(p == k or p.startswith(k + ".") for k in device_map)]
-        partner_modules = []
-        for p in partners:
-            for cand_name, cand in modules_to_treat:
-                if p == cand_name or p.startswith(cand_name + "."):
-                    if (cand_name, cand) not in partner_modules:
-                        partner_modules.append((cand_name, cand))
-        total_size = module_size + sum(module_sizes[n] for n, _ in partner_modules)
+        placeable = [p for p in partners if any(_holds(n, p) for n, _ in modules_to_treat)]
+        total_size, partner_names, partner_entries = get_module_size_with_ties(placeable, module_size, module_sizes, modules_to_treat)
+        partner_modules = list(zip(partner_names, partner_entries))
         device = devices[dev_idx]
         cap = budget(dev_idx)
         if cap is None or used[device] + total_size <= cap:
             device_map[name] = device
-            used[device] += module_size
+            used[device] += total_size
             for n, m in partner_modules:
                 device_map[n] = device
-                used[device] += module_sizes[n]
                 modules_to_treat.remove((n, m))
             if isinstance(module, nn.Module):
                 buffers_on_device[device] += compute_module_total_buffer_size(module, dtype=dtype, special_dtypes=special_dtypes)
@@ -624,30 +700,12 @@ def infer_auto_device_map(model: nn.Module, max_memory: Optional[dict] = None, n
             max_layer_size, max_layer_names = get_max_layer_size(
                 [(n, m) for n, m in modules_to_treat if isinstance(m, torch.nn.Module)], module_sizes, no_split_module_classes)
             continue
-        # cannot split: optionally fill the remaining room with a later module that fits
-        if fallback_allocation and cap is not None:
-            placed = False
-            queue = list(modules_to_treat)
-            while queue:
-                cn, cm = queue.pop(0)
-                csize = module_sizes[cn]
-                if used[device] + csize <= cap and not tied_group_of(cn):
-                    device_map[cn] = device
-                    used[device] += csize
-                    # remove it (or the ancestor chain it was expanded from) from the work list
-                    if (cn, cm) in modules_to_treat:
-                        modules_to_treat.remove((cn, cm))
-                        placed = True
-                        break
-                    continue
-                if isinstance(cm, nn.Module) and cm.__class__.__name__ not in no_split_module_classes and (cn, cm) in modules_to_treat:
-                    sub = children_of(cn, cm)
-                    if sub and any(module_sizes[s] + used[device] <= cap for s, _ in sub):
-                        i = modules_to_treat.index((cn, cm))
-                        modules_to_treat = modules_to_treat[:i] + sub + modules_to_treat[i + 1:]
-                        queue = sub + queue
-            if placed:
-                modules_to_treat.insert(0, (name, module))
+        # cannot split: optionally fill the room this device has left with a later piece that fits, then come back to this module
+        if fallback_allocation and cap is not None and cap - used[device] > 0:
+            pick_name, pick, rest = fallback_allocate(modules_to_treat, module_sizes, cap - used[device], no_split_module_classes,
+                                                      tied_parameters)
+            if pick is not None:
+                modules_to_treat = [(pick_name, pick), (name, module)] + rest
                 continue
         if verbose:
             print(f"Not enough space on {device} to put {name} (space available {None if cap is None else cap - used[device]}, module size {total_size}).")

@@ -100,3 +100,43 @@ def test_model_configs_are_translated_into_megatron_arguments():
     args = plugin.megatron_lm_default_args
     assert args["model_type_name"] == "gpt" and args["num_query_groups"] == 2 and args["ffn_hidden_size"] == 128 and args["swiglu"] is True
     assert args["seq_length"] == 48 and args["normalization"] == "RMSNorm"
+
+
+def test_glm4_moe_config_is_translated_with_its_routing_and_layer_layout():
+    import types
+
+    from accelerate_hpc_test_b200.utils import MegatronLMPlugin
+    from accelerate_hpc_test_b200.utils.dataclasses import MODEL_CONFIGS_TO_MEGATRON_PARSERS, parse_glm4_moe_config
+
+    assert MODEL_CONFIGS_TO_MEGATRON_PARSERS["glm4_moe"] is parse_glm4_moe_config
+
+    class Glm4MoeForCausalLM:
+        config = types.SimpleNamespace(
+            model_type="glm4_moe", num_hidden_layers=6, hidden_size=256, num_attention_heads=8, num_key_value_heads=2, head_dim=32,
+            vocab_size=4096, max_position_embeddings=8192, intermediate_size=512, moe_intermediate_size=128, n_routed_experts=16,
+            num_experts_per_tok=4, routed_scaling_factor=2.5, first_k_dense_replace=1, use_qk_norm=False, rope_theta=1e6,
+            partial_rotary_factor=0.5, eos_token_id=2, bf16=True, tie_word_embeddings=False, return_dict=True)
+
+    plugin = MegatronLMPlugin()
+    parse_glm4_moe_config(plugin, Glm4MoeForCausalLM(), {"input_ids": torch.zeros(2, 640, dtype=torch.long)})
+    a = plugin.megatron_lm_default_args
+    assert a["model_type_name"] == "gpt" and a["pretraining_flag"] is False and a["original_model_type"] == "glm4_moe"
+    assert a["seq_length"] == 640 == plugin.seq_length                       # no config length, no plugin length: the batch decides
+    assert a["moe_layer_freq"] == [0, 1, 1, 1, 1, 1] and a["num_experts"] == 16 and a["moe_router_topk"] == 4
+    assert a["moe_ffn_hidden_size"] == a["moe_shared_expert_intermediate_size"] == 128 and a["ffn_hidden_size"] == 512
+    assert a["moe_router_score_function"] == "sigmoid" and a["moe_router_topk_scaling_factor"] == 2.5 and a["moe_grouped_gemm"] is True
+    assert a["num_query_groups"] == 2 and a["kv_channels"] == 32 and a["qk_layernorm"] is False and a["add_qkv_bias"] is True
+    assert a["rotary_percent"] == 0.5 and a["rotary_base"] == 1e6 and a["norm_epsilon"] == 1e-3
+    assert a["untie_embeddings_and_output_weights"] is True and a["tokenizer_type"] == "HuggingFaceTokenizer" and "fp8" not in a
+
+    # the config's own maximum wins over the family field; an explicit plugin length wins over both; fp8 parameters ride along
+    class WithLength(Glm4MoeForCausalLM):
+        config = types.SimpleNamespace(**{**vars(Glm4MoeForCausalLM.config), "max_sequence_length": 2048, "fp8_param": True,
+                                          "fp8": "hybrid", "fp8_param_gather": True, "fp8_recipe": "mxfp8"})
+
+    plugin = MegatronLMPlugin(decoder_seq_length=1024)
+    parse_glm4_moe_config(plugin, WithLength(), None)
+    assert plugin.seq_length == 2048 and plugin.megatron_lm_default_args["fp8_recipe"] == "mxfp8"
+    plugin = MegatronLMPlugin(seq_length=512)
+    parse_glm4_moe_config(plugin, WithLength(), None)
+    assert plugin.seq_length == 512

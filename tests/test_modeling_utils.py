@@ -3,6 +3,7 @@ tests/test_modeling_utils.py, on CPU / meta / disk)."""
 
 import json
 import os
+from collections import OrderedDict
 
 import pytest
 import torch
@@ -376,3 +377,91 @@ def test_infer_auto_device_map_spills_in_order_and_reserves_the_largest_layer():
     # room for `first` plus the reserve for the largest layer, not for `second`: the rest goes to disk, in definition order
     tight = infer_auto_device_map(model, max_memory={"cpu": sizes["first"] * 2 + 8}, no_split_module_classes=["Block"])
     assert tight["first"] == "cpu" and tight["second"] == "disk" and tight["head"] == "disk"
+
+
+# ------------------------------------------------------------------------------------------------- ties and fallback placement
+def _stack_of_linears(n, tie=False):
+    import torch.nn as nn
+
+    stack = nn.ModuleList([nn.Linear(10, 10) for _ in range(n)])
+    if tie:
+        for i in range(1, n):
+            stack[i].weight = stack[0].weight
+    return stack
+
+
+def test_size_with_ties_charges_each_holder_once_and_not_the_shared_tensor():
+    from accelerate_hpc_test_b200.utils.modeling import compute_module_sizes, find_tied_parameters, get_module_size_with_ties
+
+    # twelve layers so that "1" is a string prefix of "10" and "11" without holding their tensors
+    stack = _stack_of_linears(12, tie=True)
+    sizes = compute_module_sizes(stack)
+    group = sorted(find_tied_parameters(stack)[0])
+    assert len(group) == 12
+    pending = list(stack.named_children())[1:]
+    outside = [p for p in group if p != "0.weight"]
+    total, names, holders = get_module_size_with_ties(outside, sizes["0"], sizes, pending)
+    assert total == sizes["0"] + 11 * sizes["0.bias"]          # the shared weight is paid for once
+    assert names == [p.rsplit(".", 1)[0] for p in outside] and holders == [stack[int(n)] for n in names]
+    # nothing tied: the size comes back unchanged
+    assert get_module_size_with_ties([], 123, sizes, pending) == (123, [], [])
+    # two tied tensors below one holder: the holder is charged once
+    import torch.nn as nn
+
+    pair = nn.Sequential(nn.Linear(10, 10), nn.Sequential(nn.Linear(10, 10), nn.Linear(10, 10)))
+    pair[1][0].weight = pair[0].weight
+    pair[1][1].weight = pair[0].weight
+    sizes = compute_module_sizes(pair)
+    total, names, _ = get_module_size_with_ties(["1.0.weight", "1.1.weight"], sizes["0"], sizes, [("1", pair[1])])
+    assert names == ["1"] and total == sizes["0"] + 2 * sizes["1.0.bias"]
+
+
+def test_fallback_allocate_finds_the_first_piece_that_fits_and_opens_its_ancestors():
+    import torch.nn as nn
+
+    from accelerate_hpc_test_b200.utils.modeling import compute_module_sizes, fallback_allocate
+
+    model = nn.Sequential(OrderedDict(big=nn.Sequential(OrderedDict(a=nn.Linear(100, 100), b=nn.Linear(4, 4))), tail=nn.Linear(50, 50)))
+    sizes = compute_module_sizes(model)
+    entries = list(model.named_children())
+    # nothing as large as `big` fits, its second child does; `big` is replaced by its remaining pieces in what is left
+    name, piece, rest = fallback_allocate(entries, sizes, sizes["big.b"])
+    assert name == "big.b" and piece is model.big.b and [n for n, _ in rest] == ["big.a", "tail"]
+    # with `big` un-splittable the search moves on to `tail`
+    name, piece, rest = fallback_allocate(entries, sizes, sizes["tail"], no_split_module_classes=["Sequential"])
+    assert name == "tail" and [n for n, _ in rest] == ["big"]
+    # nothing fits / a limit that is not a size: the list comes back untouched
+    assert fallback_allocate(entries, sizes, 8) == (None, None, entries)
+    assert fallback_allocate(entries, sizes, "a lot") == (None, None, entries)
+    # sizes given the way `max_memory` spells them
+    assert fallback_allocate(entries, sizes, "11KB", no_split_module_classes=["Sequential"])[0] == "tail"
+    assert fallback_allocate(entries, sizes, "11KB")[0] == "big.b"
+    # a piece tied to something outside it only fits if its partner's holder fits too
+    model.tail2 = nn.Linear(4, 4)
+    model.tail2.weight = model.big.b.weight
+    sizes = compute_module_sizes(model)
+    entries = list(model.named_children())
+    ties = [["big.b.weight", "tail2.weight"]]
+    assert fallback_allocate(entries, sizes, sizes["big.b"], tied_parameters=ties)[0] is None
+    name, _, rest = fallback_allocate(entries, sizes, sizes["big.b"] + sizes["tail2.bias"], tied_parameters=ties)
+    assert name == "big.b" and [n for n, _ in rest] == ["big.a", "tail", "tail2"]
+
+
+def test_device_map_with_fallback_fills_the_first_device_instead_of_leaving_it_empty():
+    import torch.nn as nn
+
+    from accelerate_hpc_test_b200.utils.modeling import compute_module_sizes, infer_auto_device_map
+
+    model = nn.Sequential(OrderedDict(wide=nn.Linear(200, 200), narrow=nn.Linear(10, 10), other=nn.Linear(200, 200)))
+    sizes = compute_module_sizes(model)
+    # device 0 must keep room for the largest layer, so `wide` itself cannot go there
+    budget = {0: sizes["wide"] + sizes["narrow"] + 10, 1: 10 * sizes[""]}
+    plain = infer_auto_device_map(model, max_memory=budget)
+    assert 0 not in plain.values()
+    filled = infer_auto_device_map(model, max_memory=budget, fallback_allocation=True)
+    assert filled == {"narrow": 0, "wide": 1, "other": 1}
+    # tied pieces stay together under fallback as well
+    model.twin = nn.Linear(10, 10)
+    model.twin.weight = model.narrow.weight
+    filled = infer_auto_device_map(model, max_memory={0: budget[0] + sizes["narrow.bias"], 1: budget[1]}, fallback_allocation=True)
+    assert filled["narrow"] == filled["twin"] == 0 and filled["wide"] == 1
