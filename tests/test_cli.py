@@ -152,3 +152,51 @@ def test_accelerate_test_script_two_cpu_processes(tmp_path):
                           "accelerate_hpc_test_b200.test_utils.scripts.test_script"], capture_output=True, text=True, env=ENV, cwd=ROOT, timeout=900)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "test_script: all passed" in out.stdout
+
+
+# ------------------------------------------------------------------------------------------------- config files on disk
+CONFIGS = os.path.join(ROOT, "tests", "test_configs")
+_VINTAGES = sorted(name for name in os.listdir(CONFIGS) if name.endswith(".yaml") and name != "invalid_keys.yaml")
+
+
+@pytest.mark.parametrize("name", _VINTAGES)
+def test_config_files_of_every_vintage_load_and_launch(name):
+    """Every file `accelerate config` ever wrote still loads, and merges into a launch command line without complaint."""
+    path = os.path.join(CONFIGS, name)
+    cfg = load_config_from_file(path)
+    assert isinstance(cfg, ClusterConfig)
+    raw = yaml.safe_load(open(path))
+    assert cfg.num_processes == raw["num_processes"] and str(cfg.distributed_type).endswith(str(raw["distributed_type"]))
+    # keys a vintage did not know come out as today's defaults
+    assert cfg.debug is bool(raw.get("debug", False)) and cfg.use_cpu is bool(raw.get("use_cpu", False))
+    args, defaults, _ = _validate_launch_command(launch_command_parser().parse_args(["--config_file", path, "train.py"]))
+    assert defaults is not None and args.num_processes == raw["num_processes"] and args.mixed_precision == raw.get("mixed_precision", "no")
+    assert args.use_fsdp == (raw["distributed_type"] == "FSDP") and args.use_deepspeed == (raw["distributed_type"] == "DEEPSPEED")
+    assert args.use_megatron_lm == (raw["distributed_type"] == "MEGATRON_LM")
+
+
+def test_config_sections_reach_the_launch_arguments():
+    parse = lambda name, *extra: _validate_launch_command(
+        launch_command_parser().parse_args(["--config_file", os.path.join(CONFIGS, name), *extra, "train.py"]))[0]
+    fsdp1 = parse("latest_fsdp1.yaml")
+    assert fsdp1.fsdp_sharding_strategy == "SHARD_GRAD_OP" and fsdp1.fsdp_transformer_layer_cls_to_wrap == "LlamaDecoderLayer"
+    assert fsdp1.fsdp_activation_checkpointing is True
+    nd = parse("latest_fsdp2_nd.yaml")
+    assert nd.fsdp_version == 2 and nd.use_parallelism_config and (nd.parallelism_config_dp_shard_size, nd.parallelism_config_tp_size) == (4, 2)
+    zero3 = parse("latest_deepspeed.yaml")
+    assert zero3.zero_stage == 3 and zero3.gradient_accumulation_steps == 4 and zero3.zero3_init_flag is True
+    megatron = parse("latest_megatron.yaml")
+    assert (megatron.megatron_lm_tp_degree, megatron.megatron_lm_pp_degree, megatron.megatron_lm_num_micro_batches) == (2, 2, 2)
+    assert megatron.megatron_lm_sequence_parallelism is True and megatron.megatron_lm_use_distributed_optimizer is True
+    mpi = load_config_from_file(os.path.join(CONFIGS, "v0_28_mpi.yaml"))
+    assert mpi.mpirun_config == {"mpirun_hostfile": "/etc/cluster/hosts"} and mpi.num_machines == 2 and mpi.main_process_port == 29511
+    fp8 = load_config_from_file(os.path.join(CONFIGS, "v0_34_fp8.yaml"))
+    assert fp8.mixed_precision == "fp8" and fp8.fp8_config["backend"] == "TE" and fp8.fp8_config["fp8_format"] == "HYBRID"
+    # sections that do not belong to the distributed type stay inert; a flag typed on the command line beats the file
+    inert = parse("validate_launch_cmd.yaml", "--num_processes", "2", "--cpu")
+    assert inert.debug is True and inert.num_processes == 2 and not inert.use_fsdp and not inert.use_deepspeed
+
+
+def test_config_file_with_unknown_keys_names_them():
+    with pytest.raises(ValueError, match=r"unknown keys \(\['nproc', 'shard_everything'\]\)"):
+        load_config_from_file(os.path.join(CONFIGS, "invalid_keys.yaml"))
