@@ -30,6 +30,7 @@ style:
 
 docs:
 	$(PYTHON) tools/gen_api_reference.py
+	$(PYTHON) tools/gen_cli_reference.py
 
 # shingle overlap of every same-named file with the reference tree (needs /root/reference)
 overlap:
