@@ -9,7 +9,9 @@ script also answers "what does the native engine buy over torch's FSDP2 on this 
     python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 benchmarks/fsdp2_parity.py --model llama3-1b --steps 20
 
 Every arm starts from the same seed, sees the same per-rank batches and uses AdamW with the same hyper-parameters; the optimizer of the
-Accelerate arm is created *before* ``prepare`` (the order FSDP2 makes possible and the reference's benchmark stresses).
+Accelerate arm is created *before* ``prepare`` (the order FSDP2 makes possible and the reference's benchmark stresses).  On GPUs both
+arms keep fp32 sharded parameters and optimizer state and compute in bf16 (torch: fp32 model + ``MixedPrecisionPolicy(bf16)``; native
+engine: bf16 model + fp32 master shards).
 """
 
 import argparse
@@ -81,6 +83,10 @@ def arm_torch(args, device, dtype):
     from torch.distributed.fsdp import MixedPrecisionPolicy, fully_shard
 
     model, cfg = build(args, device, dtype)
+    # the usual FSDP2 mixed-precision set-up: sharded parameters, optimizer state and update in fp32, compute and reduction in bf16.
+    # It is also what the native engine does with a bf16 model (fp32 master shards + moments), so both arms round at the same places;
+    # starting from the bf16-initialised weights keeps the two arms' initial values identical.
+    model = model.float()
     policy = MixedPrecisionPolicy(param_dtype=dtype, reduce_dtype=dtype) if dtype != torch.float32 else MixedPrecisionPolicy()
     for layer in model.model.layers:
         fully_shard(layer, mp_policy=policy)
