@@ -1036,25 +1036,35 @@ class B200ShardedModule(nn.Module):
 
     @torch.no_grad()
     def load_full_state_dict(self, sd: dict, strict: bool = True):
-        """Every rank passes the same full dict (or only rank 0 passes values and the others ``None`` entries are filled by a
-        broadcast — ``cpu_ram_efficient_loading``)."""
+        """Every rank passes the same full dict — or only rank 0 passes values, the others an empty dict, and every tensor rank 0
+        holds is broadcast (``cpu_ram_efficient_loading``, ``load_checkpoint_in_model(..., broadcast_from_rank0=True)``).  ``sd`` may
+        hold only part of the model (one file of a sharded checkpoint) when ``strict`` is off: what it does not name stays as it is."""
         have = torch.tensor([1 if sd else 0], device=self.device)
         counts = [torch.zeros_like(have) for _ in range(self.world)]
         torch.distributed.all_gather(counts, have, group=self.group)
-        bcast = any(int(c) == 0 for c in counts)
+        bcast = any(int(c) == 0 for c in counts) and any(int(c) for c in counts)
         src = torch.distributed.get_global_rank(self.group, 0)
+        if bcast:
+            names = [sorted(sd)] if self.rank == 0 else [None]
+            torch.distributed.broadcast_object_list(names, src=src, group=self.group)
+            present = set(names[0])
+        else:
+            present = set(sd)
+        missing = [s.name for u in self._units for s in u.segs if s.name not in present]
+        if missing and strict:
+            raise KeyError(f"missing key {missing[0]!r} in state dict ({len(missing)} missing in all)")
         for u in self._units:
+            touched = False
             for s in u.segs:
+                if s.name not in present:
+                    continue
+                touched = True
                 if bcast:
                     full = torch.empty(s.numel, dtype=torch.float32, device=self.device)
                     if self.rank == 0:
                         full.copy_(sd[s.name].reshape(-1).float())
                     torch.distributed.broadcast(full, src=src, group=self.group)
                 else:
-                    if s.name not in sd:
-                        if strict:
-                            raise KeyError(f"missing key {s.name!r} in state dict")
-                        continue
                     full = sd[s.name].reshape(-1)
                 lo = self.rank * s.piece
                 n = max(0, min(s.piece, s.numel - lo))
@@ -1062,11 +1072,19 @@ class B200ShardedModule(nn.Module):
                 dst.zero_()
                 if n > 0:
                     dst[:n].copy_(full[lo : lo + n].to(self.device, torch.float32))
-            u.shard.copy_(u.master)
-        if sd:
-            for n, b in self.module.named_buffers():
-                if n in sd:
-                    b.copy_(sd[n])
+            if touched:
+                u.shard.copy_(u.master)
+        for n, b in self.module.named_buffers():
+            if n not in present:
+                continue
+            if bcast:
+                value = b.detach().clone()
+                if self.rank == 0:
+                    value.copy_(sd[n])
+                torch.distributed.broadcast(value, src=src, group=self.group)
+                b.copy_(value)
+            else:
+                b.copy_(sd[n])
         self._sync_after_external_update()
 
     def load_state_dict(self, sd, strict: bool = True):

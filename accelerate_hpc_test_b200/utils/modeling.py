@@ -919,6 +919,34 @@ def _stays_fp32(param_name: str, keep_in_fp32_modules) -> bool:
     return any(key == param_name or (key in param_name and f"{key}." in param_name) for key in keep_in_fp32_modules or ())
 
 
+def _receive_from_rank0(model: nn.Module, weights: dict) -> None:
+    """``broadcast_from_rank0``: rank 0 holds ``weights`` (one checkpoint file), every other rank an empty dict.  The names rank 0
+    has for this model are announced, then each tensor is broadcast and copied into the model — into the local shard when the
+    target is a ``DTensor`` (torch ``fully_shard``), whole otherwise (plain modules, the module inside a DDP wrapper).  The reference
+    gets this from ``set_model_state_dict(..., broadcast_from_rank0=True)`` (utils/modeling.py:1934-1953)."""
+    import torch.distributed as dist
+
+    targets = model.state_dict()
+    announced = [[name for name in weights if name in targets]] if dist.get_rank() == 0 else [None]
+    dist.broadcast_object_list(announced, src=0)
+    with torch.no_grad():
+        for name in announced[0]:
+            target = targets[name]
+            sharded = hasattr(target, "device_mesh") and hasattr(target, "placements")
+            local = target.to_local() if sharded else target
+            staging_device = local.device if local.device.type != "meta" else torch.device("cpu")
+            full = torch.empty(tuple(target.shape), dtype=target.dtype, device=staging_device)
+            if dist.get_rank() == 0:
+                full.copy_(weights[name])
+            dist.broadcast(full, src=0)
+            if sharded:
+                from torch.distributed.tensor import distribute_tensor
+
+                local.copy_(distribute_tensor(full, target.device_mesh, target.placements).to_local())
+            else:
+                target.copy_(full)
+
+
 def load_checkpoint_in_model(model: nn.Module, checkpoint, device_map: Optional[dict] = None, offload_folder=None, dtype=None,
                              offload_state_dict: bool = False, offload_buffers: bool = False, keep_in_fp32_modules: list = None,
                              offload_8bit_bnb: bool = False, strict: bool = False, full_state_dict: bool = True,
@@ -928,7 +956,8 @@ def load_checkpoint_in_model(model: nn.Module, checkpoint, device_map: Optional[
     With a ``device_map`` every weight goes where its closest enclosing entry says: a GPU or the CPU (set in place), or ``"disk"``
     (written to ``offload_folder`` as a memory-mappable file, the model keeps a meta tensor).  ``offload_state_dict`` parks the CPU
     weights on disk while the other files are read, to bound host memory.  Without a map the files are loaded the ordinary way — or,
-    with ``broadcast_from_rank0`` and a sharded engine, through ``load_full_state_dict`` (rank 0 reads, the shards are scattered).
+    with ``broadcast_from_rank0`` in a distributed run, only rank 0 reads each file and the tensors are broadcast: into the native
+    sharded engine through ``load_full_state_dict``, into ``DTensor`` parameters shard by shard, into plain modules whole.
     Tied weights are tied again at the end.
     """
     tied = find_tied_parameters(model)
@@ -952,12 +981,18 @@ def load_checkpoint_in_model(model: nn.Module, checkpoint, device_map: Optional[
     parked_folder = tempfile.mkdtemp() if offload_state_dict else None
     unexpected = set()
 
+    from_rank0 = broadcast_from_rank0 and device_map is None and torch.distributed.is_available() and torch.distributed.is_initialized()
+    reader = not from_rank0 or torch.distributed.get_rank() == 0
+
     for file in files:
-        weights = load_state_dict(file, device_map=device_map)
+        weights = load_state_dict(file, device_map=device_map) if reader else {}
         unexpected.update(name for name in weights if name not in expected and "SCB" not in name)
         if device_map is None:
-            if broadcast_from_rank0 and hasattr(model, "load_full_state_dict"):
-                model.load_full_state_dict(weights)
+            if hasattr(model, "load_full_state_dict"):
+                # native sharded engine: one file may hold part of the model; with `broadcast_from_rank0` only rank 0 has values
+                model.load_full_state_dict(weights, strict=False)
+            elif from_rank0:
+                _receive_from_rank0(model, weights)
             else:
                 if len(real_devices) == 1:
                     (where,) = real_devices
