@@ -645,6 +645,8 @@ class Accelerator:
             if self.is_fsdp2 and n_models > 1:
                 raise ValueError("Only one model is supported when using FSDP2")
 
+        if self.distributed_type == DistributedType.DEEPSPEED and self.deepspeed_plugin is not None:
+            self._resolve_deepspeed_config(args)
         args = self._materialize_placeholders(args)
         # already-prepared objects pass through untouched (idempotence)
         result = []
@@ -697,6 +699,121 @@ class Accelerator:
                 except Exception:
                     pass
         return tuple(result) if len(result) > 1 else result[0]
+
+    def _resolve_deepspeed_config(self, args) -> None:
+        """Fill the ``"auto"`` entries of the active DeepSpeed-style configuration from what ``prepare`` was handed, and refuse
+        combinations that say the same thing twice.  What the reference does at the top of ``_prepare_deepspeed``
+        (accelerator.py:2132-2330) before building DeepSpeed's engine; here the resolved configuration drives the native engines:
+
+        * micro batch size from the dataloaders (smallest or largest, ``is_train_batch_min``), ``train_batch_size`` from it;
+        * gradient accumulation: the configuration's value wins over the ``Accelerator`` argument (with a warning);
+        * bucket sizes that depend on the model's hidden size; optimizer / scheduler parameters from ``DummyOptim`` / ``DummyScheduler``;
+        * an optimizer (scheduler) described in the configuration *and* built in code, or a placeholder without a description, is an error;
+        * a numeric ``gradient_clipping`` is applied at every optimizer step (``backward`` does it on synchronising steps).
+        """
+        from .utils.deepspeed import DummyOptim, DummyScheduler
+
+        plugin = self.deepspeed_plugin
+        config = plugin.deepspeed_config
+        loaders = [obj for obj in args if _is_dataloader(obj)]
+        if plugin.is_auto("train_micro_batch_size_per_gpu"):
+            if not loaders:
+                raise ValueError(
+                    "When using DeepSpeed, `accelerate.prepare()` requires you to pass at least one of training or evaluation dataloaders "
+                    "with `batch_size` attribute returning an integer value "
+                    "or alternatively set an integer value in `train_micro_batch_size_per_gpu` in the deepspeed config file "
+                    "or assign integer value to `AcceleratorState().deepspeed_plugin.deepspeed_config['train_micro_batch_size_per_gpu']`.")
+            sizes = [getattr(dl, "batch_size", None) if getattr(dl, "batch_size", None) is not None
+                     else getattr(getattr(dl, "batch_sampler", None), "batch_size", None) for dl in loaders]
+            if any(size is None for size in sizes):
+                raise ValueError(
+                    "At least one of the dataloaders passed to `accelerate.prepare()` has `None` as batch size. "
+                    "Please set an integer value in `train_micro_batch_size_per_gpu` in the deepspeed config file "
+                    "or assign integer value to `AcceleratorState().deepspeed_plugin.deepspeed_config['train_micro_batch_size_per_gpu']`.")
+            if self.split_batches:
+                sizes = [size // self.num_processes for size in sizes]
+            micro_batch = min(sizes) if plugin.is_train_batch_min else max(sizes)
+            if len(sizes) > 1:
+                logger.info(f"Since you passed both train and evaluation dataloader, `is_train_batch_min` (here {plugin.is_train_batch_min} "
+                            f"will decide the `train_batch_size` ({micro_batch}).")
+        else:
+            micro_batch = plugin.get_value("train_micro_batch_size_per_gpu")
+
+        plugin.fill_match("gradient_accumulation_steps", must_match=False, gradient_accumulation_steps=self.gradient_accumulation_steps)
+        stated_steps = plugin.get_value("gradient_accumulation_steps")
+        if stated_steps != self.gradient_accumulation_steps:
+            logger.warning(f"Gradient accumulation steps mismatch: GradientAccumulationPlugin has {self.gradient_accumulation_steps}, "
+                           f"DeepSpeed config has {stated_steps}. Using DeepSpeed's value.")
+            self.gradient_accumulation_steps = stated_steps
+
+        known = {"gradient_clipping": 1.0, "zero_optimization.stage3_gather_16bit_weights_on_model_save": False}
+        if micro_batch is not None:
+            pc = self.parallelism_config
+            sequence_ranks = pc.sp_size if (pc is not None and pc.sp_enabled) else 1
+            known["train_micro_batch_size_per_gpu"] = micro_batch
+            known["train_batch_size"] = micro_batch * stated_steps * self.num_processes // sequence_ranks
+
+        model = next((obj for obj in args if _is_module(obj)), None)
+        optimizer = next((obj for obj in args if isinstance(obj, DummyOptim) or _is_optimizer(obj)), None)
+        scheduler = next((obj for obj in args if isinstance(obj, DummyScheduler) or _is_scheduler(obj)), None)
+        if optimizer is not None:
+            placeholder = isinstance(optimizer, DummyOptim)
+            if "optimizer" in config and not placeholder:
+                raise ValueError("You cannot specify an optimizer in the config file and in the code at the same time. "
+                                 "Please remove the optimizer from the config file or create `accelerate.utils.DummyOptim` in the code.")
+            if "optimizer" not in config and placeholder:
+                raise ValueError("You cannot create a `DummyOptim` without specifying an optimizer in the config file.")
+            if not placeholder:
+                config["zero_allow_untested_optimizer"] = True
+        if scheduler is not None:
+            placeholder = isinstance(scheduler, DummyScheduler)
+            if "scheduler" in config and not placeholder:
+                raise ValueError("You cannot specify a scheduler in the config file and in the code at the same time. "
+                                 "Please remove the scheduler from the config file or create `accelerate.utils.DummyScheduler` in the code.")
+            if "scheduler" not in config and placeholder and scheduler.lr_scheduler_callable is None:
+                raise ValueError("Either specify a scheduler in the config file or "
+                                 "pass in the `lr_scheduler_callable` parameter when using `accelerate.utils.DummyScheduler`.")
+        if isinstance(optimizer, DummyOptim) and scheduler is not None and not isinstance(scheduler, DummyScheduler):
+            raise ValueError("You can only specify `accelerate.utils.DummyScheduler` in the code when using `accelerate.utils.DummyOptim`.")
+
+        if model is not None:
+            plugin.set_moe_leaf_modules(model)
+            by_hidden_size = ("zero_optimization.reduce_bucket_size", "zero_optimization.stage3_prefetch_bucket_size",
+                              "zero_optimization.stage3_param_persistence_threshold")
+            open_entries = [path for path in by_hidden_size if plugin.is_auto(path)]
+            if open_entries:
+                why = ("therefore it's not possible to automatically fill out the following `auto` entries "
+                       f"in the DeepSpeed config file: {open_entries}. You can fix that by replacing "
+                       "`auto` values for these keys with an integer value of your choice.")
+                model_config = getattr(model, "config", None)
+                if model_config is None:
+                    raise ValueError("Can't find `model.config` entry, " + why)
+                if hasattr(model_config, "hidden_size"):
+                    hidden = model_config.hidden_size
+                elif hasattr(model_config, "hidden_sizes"):
+                    hidden = max(model_config.hidden_sizes)
+                else:
+                    raise ValueError("Can find neither `model.config.hidden_size` nor `model.config.hidden_sizes`, " + why)
+                known.update({by_hidden_size[0]: hidden * hidden, by_hidden_size[1]: int(0.9 * hidden * hidden), by_hidden_size[2]: 10 * hidden})
+            if isinstance(optimizer, DummyOptim):
+                known.update({"optimizer.params.lr": optimizer.lr, "optimizer.params.weight_decay": optimizer.weight_decay})
+            if isinstance(scheduler, DummyScheduler) and scheduler.lr_scheduler_callable is None:
+                peak = getattr(scheduler.optimizer, "lr", None)
+                if peak is None:
+                    peak = getattr(scheduler.optimizer, "defaults", {}).get("lr")
+                known.update({"scheduler.params.warmup_min_lr": 0, "scheduler.params.warmup_max_lr": peak,
+                              "scheduler.params.warmup_num_steps": scheduler.warmup_num_steps})
+                if scheduler.total_num_steps is not None:
+                    ranks = self.num_processes if not self.split_batches else 1
+                    known["scheduler.params.total_num_steps"] = -(-scheduler.total_num_steps // ranks)
+            plugin.deepspeed_config_process(must_match=False, **known)
+        else:
+            # no model in this call (dataloaders prepared on their own): fill what can be filled, leave the rest for the call that has it
+            for path, value in known.items():
+                if plugin.is_auto(path):
+                    plugin.fill_match(path, must_match=False, **{path: value})
+        clip = plugin.get_value("gradient_clipping")
+        self._config_clip_norm = float(clip) if isinstance(clip, (int, float)) and not isinstance(clip, bool) and clip > 0 else None
 
     def _materialize_placeholders(self, args) -> tuple:
         """Scripts written for a DeepSpeed config pass ``DummyOptim`` / ``DummyScheduler`` where the config file describes the
@@ -1043,6 +1160,9 @@ class Accelerator:
             self.scaler.scale(loss).backward(**kwargs)
         else:
             loss.backward(**kwargs)
+        if getattr(self, "_config_clip_norm", None) is not None and self.sync_gradients:
+            # `gradient_clipping` of a DeepSpeed-style configuration: DeepSpeed's engine clips at every step boundary on its own
+            self._clip_from_config()
 
     def set_trigger(self):
         """Raise the cross-rank flag (e.g. "stop training") checked by :meth:`check_trigger`."""
@@ -1070,8 +1190,21 @@ class Accelerator:
                     opt = opt.optimizer
                 self.scaler.unscale_(opt)
 
+    def _clip_from_config(self):
+        limit, self._config_clip_norm = self._config_clip_norm, None  # (so that the call below really clips)
+        try:
+            for model in self._models:
+                params = [p for p in model.parameters() if p.requires_grad]
+                if params:
+                    self._last_config_clip_norm = self.clip_grad_norm_(params, limit)
+        finally:
+            self._config_clip_norm = limit
+
     def clip_grad_norm_(self, parameters, max_norm, norm_type=2):
         """Clip to ``max_norm`` and return the total norm (a device tensor; no host sync on the native path)."""
+        if getattr(self, "_config_clip_norm", None) is not None:
+            # the configuration already clipped this step's gradients (reference: under DeepSpeed this call only reports the norm)
+            return getattr(self, "_last_config_clip_norm", None)
         parameters = [p for p in parameters]
         for model in self._models:
             if hasattr(model, "clip_grad_norm_") and not isinstance(model, torch.nn.parallel.DistributedDataParallel):

@@ -100,6 +100,7 @@ class PartialState:
             raise ValueError(f"Your assigned backend {original_backend} is not available, please use {backend}")
         self.backend = backend
         self.distributed_type = distributed_type
+        self._launch_distributed_type = distributed_type  # what the launch gave us, before any engine plugin promotes it
         self._symm_workspace = None
 
         if distributed_type == DistributedType.NO:
@@ -433,6 +434,8 @@ class AcceleratorState:
         self.megatron_lm_plugin = None
 
         cp_or_sp = parallelism_config is not None and (parallelism_config.cp_enabled or parallelism_config.sp_enabled)
+        # start from the launch's own type: an earlier AcceleratorState (reset since) may have left its promotion on PartialState
+        self.distributed_type = PartialState._shared_state.get("_launch_distributed_type", self.distributed_type)
         if self.distributed_type in (DistributedType.MULTI_GPU, DistributedType.MULTI_CPU):
             # (the reference refuses DeepSpeed on CPU; here a ZeRO configuration runs on the native sharded engine, whose gloo
             # path works on CPU too — that is how the DeepSpeed-style scripts are tested without GPUs)
@@ -442,7 +445,14 @@ class AcceleratorState:
                     deepspeed_plugin = {"default": deepspeed_plugin}
                 self.deepspeed_plugins = deepspeed_plugin
                 if deepspeed_plugin:
-                    next(iter(deepspeed_plugin.values())).select(_from_accelerator_state=True)
+                    chosen = next(iter(deepspeed_plugin.values()))
+                    # a configuration that states its own precision decides when none was asked for (the native engines need
+                    # to know it; the reference leaves precision to DeepSpeed's engine and reads it back from the config)
+                    if self._mixed_precision == "no" and chosen.stated_precision() is not None:
+                        self._mixed_precision = chosen.stated_precision()
+                    for plugin in deepspeed_plugin.values():
+                        plugin.set_mixed_precision(self._mixed_precision)
+                    chosen.select(_from_accelerator_state=True)
             elif parse_flag_from_env("ACCELERATE_USE_FSDP") or fsdp_plugin is not None or (parallelism_config is not None and parallelism_config.cp_enabled):
                 if parallelism_config is not None and parallelism_config.cp_enabled and fsdp_plugin is None:
                     from .utils.dataclasses import FullyShardedDataParallelPlugin

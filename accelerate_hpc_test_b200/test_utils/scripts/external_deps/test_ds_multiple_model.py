@@ -22,6 +22,8 @@ def tiny_llama(device, seed):
 def main():
     plugins = {"student": DeepSpeedPlugin(zero_stage=2, gradient_accumulation_steps=1),
                "teacher": DeepSpeedPlugin(zero_stage=3, gradient_accumulation_steps=1)}
+    for plugin in plugins.values():  # no dataloader is prepared below, so the batch size is stated instead of left on "auto"
+        plugin.deepspeed_config["train_micro_batch_size_per_gpu"] = 2
     accelerator = Accelerator(deepspeed_plugins=plugins)
     state = AcceleratorState()
     if accelerator.num_processes < 2:

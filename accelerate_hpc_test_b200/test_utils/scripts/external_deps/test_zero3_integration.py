@@ -28,12 +28,24 @@ def main():
     names = sorted(model.state_dict())
     before = {k: v.detach().float().cpu().clone() for k, v in model.state_dict().items()}
     optimizer = torch.optim.AdamW(model.parameters(), lr=1e-2)
-    model, optimizer = accelerator.prepare(model, optimizer)
+    if accelerator.distributed_type == DistributedType.DEEPSPEED:
+        try:
+            accelerator.prepare(model, optimizer)
+        except ValueError as error:  # `auto` batch sizes need a dataloader to be read from, as under DeepSpeed
+            assert "requires you to pass at least one of training or evaluation dataloaders" in str(error)
+        else:
+            raise AssertionError("`auto` batch sizes were accepted without a dataloader")
+    g = torch.Generator().manual_seed(accelerator.process_index)
+    data = [torch.randint(0, cfg.vocab_size, (32,), generator=g) for _ in range(6)]
+    loader = torch.utils.data.DataLoader(data, batch_size=2)
+    model, optimizer, loader = accelerator.prepare(model, optimizer, loader)
+    resolved = plugin.deepspeed_config
+    if accelerator.distributed_type == DistributedType.DEEPSPEED:
+        assert resolved["train_micro_batch_size_per_gpu"] == 2 and resolved["train_batch_size"] == 2 * accelerator.num_processes
     if accelerator.num_processes > 1:
         assert type(model).__name__ == "B200ShardedModule", type(model).__name__  # stage 3 == parameters sharded
     losses = []
-    for step in range(3):
-        ids = torch.randint(0, cfg.vocab_size, (2, 32), generator=torch.Generator().manual_seed(step * 7 + accelerator.process_index)).to(accelerator.device)
+    for ids in loader:
         loss = model(input_ids=ids, labels=ids).loss
         accelerator.backward(loss)
         optimizer.step()

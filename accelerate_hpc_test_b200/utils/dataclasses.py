@@ -19,6 +19,7 @@ import functools
 import logging
 import os
 import warnings
+from contextlib import contextmanager
 from dataclasses import dataclass, field, fields, is_dataclass
 from datetime import timedelta
 from typing import Any, Callable, Iterable, Literal, Optional, Union
@@ -470,6 +471,46 @@ class TorchDynamoPlugin(KwargsHandler):
 
 
 # =============================================================================== DeepSpeed (config shell)
+_DS_FIELD_PATHS = {  # plugin attribute -> dotted path of the same setting in a DeepSpeed config
+    "gradient_accumulation_steps": "gradient_accumulation_steps",
+    "gradient_clipping": "gradient_clipping",
+    "zero_stage": "zero_optimization.stage",
+    "offload_optimizer_device": "zero_optimization.offload_optimizer.device",
+    "offload_param_device": "zero_optimization.offload_param.device",
+    "offload_param_nvme_path": "zero_optimization.offload_param.nvme_path",
+    "offload_optimizer_nvme_path": "zero_optimization.offload_optimizer.nvme_path",
+    "zero3_save_16bit_model": "zero_optimization.stage3_gather_16bit_weights_on_model_save",
+}
+
+
+def _int_or_auto(text):
+    return int(text) if str(text).isdigit() else text
+
+
+def _float_or_auto(text):
+    return text if text == "auto" else float(text)
+
+
+_DS_ENV_DEFAULTS = (  # (attribute, environment variable, parser, default) for the fields the launcher exports
+    ("gradient_accumulation_steps", "ACCELERATE_GRADIENT_ACCUMULATION_STEPS", _int_or_auto, "auto"),
+    ("gradient_clipping", "ACCELERATE_GRADIENT_CLIPPING", _float_or_auto, "auto"),
+    ("zero_stage", "ACCELERATE_DEEPSPEED_ZERO_STAGE", int, 2),
+    ("offload_optimizer_device", "ACCELERATE_DEEPSPEED_OFFLOAD_OPTIMIZER_DEVICE", str, "none"),
+    ("offload_param_device", "ACCELERATE_DEEPSPEED_OFFLOAD_PARAM_DEVICE", str, "none"),
+    ("offload_optimizer_nvme_path", "ACCELERATE_DEEPSPEED_OFFLOAD_OPTIMIZER_NVME_PATH", str, "none"),
+    ("offload_param_nvme_path", "ACCELERATE_DEEPSPEED_OFFLOAD_PARAM_NVME_PATH", str, "none"),
+    ("zero3_save_16bit_model", "ACCELERATE_DEEPSPEED_ZERO3_SAVE_16BIT_MODEL", lambda text: str(text).lower() == "true", "false"),
+    ("enable_msamp", "ACCELERATE_FP8_BACKEND", lambda text: text == "MSAMP", None),
+    ("msamp_opt_level", "ACCELERATE_FP8_OPT_LEVEL", str, "O1"),
+)
+_DS_SHADOWED_BY_CONFIG_FILE = (
+    "ACCELERATE_GRADIENT_ACCUMULATION_STEPS", "ACCELERATE_GRADIENT_CLIPPING", "ACCELERATE_DEEPSPEED_ZERO_STAGE",
+    "ACCELERATE_DEEPSPEED_OFFLOAD_OPTIMIZER_DEVICE", "ACCELERATE_DEEPSPEED_OFFLOAD_PARAM_DEVICE",
+    "ACCELERATE_DEEPSPEED_OFFLOAD_PARAM_NVME_PATH", "ACCELERATE_DEEPSPEED_OFFLOAD_OPTIMIZER_NVME_PATH",
+    "ACCELERATE_DEEPSPEED_ZERO3_SAVE_16BIT_MODEL", "ACCELERATE_MIXED_PRECISION",
+)
+
+
 @dataclass
 class DeepSpeedPlugin:
     """DeepSpeed configuration shell.
@@ -497,104 +538,226 @@ class DeepSpeedPlugin:
     msamp_opt_level: Optional[Literal["O1", "O2"]] = None
 
     def __post_init__(self):
-        p = "ACCELERATE_DEEPSPEED_"
-        if self.gradient_accumulation_steps is None:
-            gas = os.environ.get("ACCELERATE_GRADIENT_ACCUMULATION_STEPS", "auto")
-            self.gradient_accumulation_steps = int(gas) if gas.isdigit() else gas
-        if self.gradient_clipping is None:
-            gc = os.environ.get("ACCELERATE_GRADIENT_CLIPPING", "auto")
-            self.gradient_clipping = gc if gc == "auto" else float(gc)
-        if self.zero_stage is None:
-            self.zero_stage = int(os.environ.get(p + "ZERO_STAGE", 2))
-        if self.offload_optimizer_device is None:
-            self.offload_optimizer_device = os.environ.get(p + "OFFLOAD_OPTIMIZER_DEVICE", "none")
-        if self.offload_param_device is None:
-            self.offload_param_device = os.environ.get(p + "OFFLOAD_PARAM_DEVICE", "none")
-        if self.offload_optimizer_nvme_path is None:
-            self.offload_optimizer_nvme_path = os.environ.get(p + "OFFLOAD_OPTIMIZER_NVME_PATH", "none")
-        if self.offload_param_nvme_path is None:
-            self.offload_param_nvme_path = os.environ.get(p + "OFFLOAD_PARAM_NVME_PATH", "none")
-        if self.zero3_save_16bit_model is None:
-            self.zero3_save_16bit_model = os.environ.get(p + "ZERO3_SAVE_16BIT_MODEL", "false").lower() == "true"
+        for attribute, variable, parse, default in _DS_ENV_DEFAULTS:
+            if getattr(self, attribute) is None:
+                setattr(self, attribute, parse(os.environ.get(variable, default)))
+        source = self.hf_ds_config
+        if source is None:
+            source = os.environ.get("ACCELERATE_DEEPSPEED_CONFIG_FILE", "none")
+        if isinstance(source, str) and source == "none":
+            self._compose_config()
+        else:
+            self._adopt_config(source)
+        self.deepspeed_config = self.hf_ds_config.config
+        self.deepspeed_config["steps_per_print"] = float("inf")
         if self.zero3_init_flag is None:
-            self.zero3_init_flag = str_to_bool(os.environ.get(p + "ZERO3_INIT", str(self.zero_stage == 3))) == 1
-        if self.enable_msamp is None:
-            self.enable_msamp = os.environ.get(p + "ENABLE_MSAMP", "false").lower() == "true"
-        if self.msamp_opt_level is None:
-            self.msamp_opt_level = os.environ.get(p + "MSAMP_OPT_LEVEL", "O1")
-        self.deepspeed_config = self._build_config()
-        self.selected = False
+            self.zero3_init_flag = str_to_bool(os.environ.get("ACCELERATE_DEEPSPEED_ZERO3_INIT", str(self.hf_ds_config.is_zero3()))) == 1
+        if self.zero3_init_flag and not self.hf_ds_config.is_zero3():
+            warnings.warn("DeepSpeed Zero3 Init flag is only applicable for ZeRO Stage 3. Setting it to False.")
+            self.zero3_init_flag = False
+        self._selected = False
+        self.dschf = None
+        if self.enable_msamp and "msamp" not in self.deepspeed_config:
+            if self.zero_stage == 3:
+                raise NotImplementedError("MS-AMP is not supported for ZeRO Stage 3. Please use ZeRO Stage 0, 1, or 2 instead.")
+            if self.msamp_opt_level not in ("O1", "O2"):
+                raise ValueError("Invalid optimization level for MS-AMP. Please use one of ['O1' or'O2'].")
+            self.deepspeed_config["msamp"] = {"enabled": True, "opt_level": self.msamp_opt_level}
 
-    def _build_config(self) -> dict:
-        if isinstance(self.hf_ds_config, dict):
-            return copy.deepcopy(self.hf_ds_config)
-        if isinstance(self.hf_ds_config, str) and os.path.exists(self.hf_ds_config):
-            import json
+    # ------------------------------------------------------------------ where the configuration comes from
+    def _compose_config(self) -> None:
+        """No file: the configuration is written from the plugin's own fields."""
+        from .deepspeed import HfDeepSpeedConfig
 
-            with open(self.hf_ds_config) as f:
-                return json.load(f)
-        cfg = {
+        def nvme(device, path):
+            return path if device == "nvme" else None
+
+        config = {
             "train_batch_size": "auto",
             "train_micro_batch_size_per_gpu": "auto",
             "gradient_accumulation_steps": self.gradient_accumulation_steps,
             "zero_optimization": {
                 "stage": self.zero_stage,
-                "offload_optimizer": {"device": self.offload_optimizer_device, "nvme_path": self.offload_optimizer_nvme_path},
-                "offload_param": {"device": self.offload_param_device, "nvme_path": self.offload_param_nvme_path},
+                "offload_optimizer": {"device": self.offload_optimizer_device,
+                                      "nvme_path": nvme(self.offload_optimizer_device, self.offload_optimizer_nvme_path)},
+                "offload_param": {"device": self.offload_param_device, "nvme_path": nvme(self.offload_param_device, self.offload_param_nvme_path)},
                 "stage3_gather_16bit_weights_on_model_save": self.zero3_save_16bit_model,
             },
-            "steps_per_print": float("inf"),
         }
         if self.gradient_clipping:
-            cfg["gradient_clipping"] = self.gradient_clipping
-        return cfg
+            config["gradient_clipping"] = self.gradient_clipping
+        self.hf_ds_config = HfDeepSpeedConfig(config)
 
+    def _adopt_config(self, source) -> None:
+        """A file / dict / encoded config rules: its ``auto`` entries are filled from the plugin's fields, and the fields then take
+        every value the config states, so ``plugin.zero_stage`` and ``config["zero_optimization"]["stage"]`` cannot disagree."""
+        from .deepspeed import HfDeepSpeedConfig
+
+        self.hf_ds_config = source if isinstance(source, HfDeepSpeedConfig) else HfDeepSpeedConfig(source)
+        config = self.hf_ds_config.config
+        config.setdefault("gradient_accumulation_steps", 1)
+        if "zero_optimization" not in config:
+            raise ValueError("Please specify the ZeRO optimization config in the DeepSpeed config.")
+        self._deepspeed_config_checks()
+        stated = {path: getattr(self, attribute) for attribute, path in _DS_FIELD_PATHS.items() if getattr(self, attribute) is not None}
+        for path in stated:
+            self.fill_match(path, must_match=False, **stated)
+        self.hf_ds_config.set_stage_and_offload()
+        for attribute, path in _DS_FIELD_PATHS.items():
+            value = self.hf_ds_config.get_value(path)
+            if value is not None and value != "auto":
+                setattr(self, attribute, value)
+
+    def _deepspeed_config_checks(self) -> None:
+        """With a DeepSpeed config file, the same settings must not also come from the accelerate config (the launcher lists the
+        ones it found in ``ACCELERATE_CONFIG_DS_FIELDS``)."""
+        shadowed = [name.replace("ACCELERATE_", "").replace("DEEPSPEED_", "").lower() for name in _DS_SHADOWED_BY_CONFIG_FILE]
+        given = os.environ.get("ACCELERATE_CONFIG_DS_FIELDS", "").split(",")
+        if any(name in shadowed for name in given):
+            raise ValueError(
+                f"When using `deepspeed_config_file`, the following accelerate config variables will be ignored: {shadowed}.\n"
+                "Please specify them appropriately in the DeepSpeed config file.\n"
+                "If you are using an accelerate config file, remove others config variables mentioned in the above specified list.\n"
+                "The easiest method is to create a new config following the questionnaire via `accelerate config`.\n"
+                "It will only ask for the necessary config variables when using `deepspeed_config_file`."
+            )
+
+    # ------------------------------------------------------------------ reading and filling
     def fill_match(self, ds_key_long, mismatches=None, must_match=True, **kwargs):
-        """Resolve an ``"auto"`` entry of the config from ``kwargs`` (same contract as the reference)."""
+        """An ``"auto"`` entry takes the value ``kwargs`` has under the same dotted name (an error if it has none); a stated entry is
+        compared with it when ``must_match`` and a difference is appended to ``mismatches``."""
         mismatches = [] if mismatches is None else mismatches
-        config, ds_key = self._find_node(ds_key_long)
-        if config is None or ds_key not in config:
+        holder, leaf = self.hf_ds_config.find_config_node(ds_key_long)
+        if holder is None:
             return
-        if config.get(ds_key) == "auto":
-            if ds_key_long in kwargs:
-                config[ds_key] = kwargs[ds_key_long]
-                return
-            raise ValueError(f"`{ds_key_long}` not found in kwargs; pass it or replace `auto` in the DeepSpeed config.")
-        if not must_match:
+        if holder.get(leaf) == "auto":
+            if ds_key_long not in kwargs:
+                raise ValueError(f"`{ds_key_long}` not found in kwargs. Please specify `{ds_key_long}` without `auto` (set to correct value) "
+                                 "in the DeepSpeed config file or pass it in kwargs.")
+            holder[leaf] = kwargs[ds_key_long]
             return
-        ds_val = config.get(ds_key)
-        if ds_val is not None and ds_key_long in kwargs and ds_val != kwargs[ds_key_long]:
-            mismatches.append(f"- ds {ds_key_long}={ds_val} vs arg {ds_key_long}={kwargs[ds_key_long]}")
+        if must_match and holder.get(leaf) is not None and ds_key_long in kwargs and holder[leaf] != kwargs[ds_key_long]:
+            mismatches.append(f"- ds {ds_key_long}={holder[leaf]} vs arg {ds_key_long}={kwargs[ds_key_long]}")
 
-    def _find_node(self, ds_key_long):
-        config = self.deepspeed_config
-        nodes = ds_key_long.split(".")
-        ds_key = nodes.pop()
-        for node in nodes:
-            config = config.get(node)
-            if config is None:
-                return None, ds_key
-        return config, ds_key
+    def deepspeed_config_process(self, prefix="", mismatches=None, config=None, must_match=True, **kwargs):
+        """``fill_match`` for every leaf of the configuration; raises once, at the top level, listing every mismatch."""
+        top = mismatches is None
+        mismatches = [] if mismatches is None else mismatches
+        config = self.deepspeed_config if config is None else config
+        for key, value in config.items():
+            if isinstance(value, dict):
+                self.deepspeed_config_process(prefix=f"{prefix}{key}.", mismatches=mismatches, config=value, must_match=must_match, **kwargs)
+            else:
+                self.fill_match(prefix + key, mismatches, must_match=must_match, **kwargs)
+        if mismatches and (top or prefix == ""):
+            listing = "\n".join(mismatches)
+            raise ValueError("Please correct the following DeepSpeed config values that mismatch kwargs "
+                             f" values:\n{listing}\nThe easiest method is to set these DeepSpeed config values to 'auto'.")
 
     def get_value(self, ds_key_long, default=None):
-        config, ds_key = self._find_node(ds_key_long)
-        if config is None:
-            return default
-        return config.get(ds_key, default)
+        return self.hf_ds_config.get_value(ds_key_long, default)
 
-    def is_auto(self, ds_key_long):
-        return self.get_value(ds_key_long) == "auto"
+    def is_auto(self, ds_key_long) -> bool:
+        return self.hf_ds_config.get_value(ds_key_long) == "auto"
+
+    def stated_precision(self) -> Optional[str]:
+        """``"fp16"`` / ``"bf16"`` when the configuration itself switches one of them on, else ``None``."""
+        for name in ("fp16", "bf16"):
+            if str(self.deepspeed_config.get(name, {}).get("enabled", False)).lower() == "true":
+                return name
+        return None
+
+    def set_mixed_precision(self, mixed_precision) -> None:
+        """Write the precision into the ``fp16`` / ``bf16`` sections (filling ``auto``); a section that enables the *other* 16-bit
+        type contradicts ``mixed_precision`` and is an error."""
+        config = self.deepspeed_config
+        wanted = {"fp16.enabled": mixed_precision == "fp16", "bf16.enabled": mixed_precision in ("bf16", "fp8")}  # fp8 rides on bf16 autocast
+        if mixed_precision != "no":  # checked first, so that a refused call leaves the configuration as it was
+            other = "bf16" if mixed_precision == "fp16" else "fp16"
+            if str(config.get(other, {}).get("enabled", "False")).lower() == "true":
+                raise ValueError(f"`--mixed_precision` arg cannot be set to `{mixed_precision}` when `{other}` is set in the DeepSpeed config file.")
+        if mixed_precision == "fp16":
+            config.setdefault("fp16", {"enabled": True, "auto_cast": True})
+        elif mixed_precision in ("bf16", "fp8"):
+            config.setdefault("bf16", {"enabled": True})
+        if mixed_precision == "fp8" and self.enable_msamp:
+            config.setdefault("msamp", {"enabled": True, "opt_level": self.msamp_opt_level})
+        for section in ("fp16", "bf16"):
+            config.setdefault(section, {"enabled": False})
+        self.fill_match("fp16.enabled", must_match=False, **wanted)
+        self.fill_match("bf16.enabled", must_match=False, **wanted)
+
+    def set_deepspeed_weakref(self) -> None:
+        """The reference parks a resolved copy of the config where ``transformers`` finds it, so that ``from_pretrained`` builds ZeRO-3
+        models partitioned.  There is no DeepSpeed here to partition for — big models are built under ``init_empty_weights`` and
+        sharded by the native engine — so the resolved copy (``auto`` batch entries set to 1) is only kept on the plugin, ``dschf``."""
+        from .deepspeed import HfDeepSpeedConfig
+
+        resolved = copy.deepcopy(self.deepspeed_config)
+        for key in ("gradient_accumulation_steps", "train_micro_batch_size_per_gpu"):
+            if resolved.get(key, "auto") == "auto":
+                resolved[key] = 1
+        if resolved.get("train_batch_size") == "auto":
+            del resolved["train_batch_size"]
+        self.dschf = HfDeepSpeedConfig(resolved)
 
     def is_zero3_init_enabled(self):
         return self.zero3_init_flag
 
+    @contextmanager
+    def zero3_init_context_manager(self, enable=False):
+        """Temporarily switch ``zero3_init_flag`` (e.g. off, to build an auxiliary model whole)."""
+        before = self.zero3_init_flag
+        if before == enable:
+            yield
+            return
+        self.zero3_init_flag = enable
+        self.set_deepspeed_weakref()
+        try:
+            yield
+        finally:
+            self.zero3_init_flag = before
+            self.set_deepspeed_weakref()
+
+    def set_moe_leaf_modules(self, model):
+        """Mixture-of-experts blocks named in ``transformer_moe_cls_names`` must not be gathered expert by expert (which experts run
+        depends on the data, so ranks would disagree on the order of gathers): every instance is marked ``_z3_leaf`` and the
+        sharded engine keeps a marked module in one unit.  Returns the classes found."""
+        if self.transformer_moe_cls_names is None:
+            self.transformer_moe_cls_names = os.environ.get("ACCELERATE_DEEPSPEED_MOE_LAYER_CLS_NAMES", None)
+        if self.transformer_moe_cls_names is None:
+            return []
+        found = []
+        for name in self.transformer_moe_cls_names.split(","):
+            cls = get_module_class_from_name(model, name.strip())
+            if cls is None:
+                raise Exception(f"Could not find a transformer layer class called '{name.strip()}' to wrap in the model.")
+            found.append(cls)
+        for module in model.modules():
+            if isinstance(module, tuple(found)):
+                module._z3_leaf = True
+        return found
+
+    # ------------------------------------------------------------------ selection among several plugins
     def select(self, _from_accelerator_state: bool = False):
         if not _from_accelerator_state:
-            raise ValueError("A `DeepSpeedPlugin` is selected through `AcceleratorState().select_deepspeed_plugin(name)`.")
-        self.selected = True
+            raise ValueError("A `DeepSpeedPlugin` object must be enabled manually by calling `AcceleratorState().enable_deepspeed_plugin(plugin_key)`.")
+        self.set_deepspeed_weakref()
+        self._selected = True
 
     def _unselect(self):
-        self.selected = False
+        self._selected = False
+
+    def _set_selected(self, value: bool):
+        self._selected = value
+
+    @property
+    def selected(self) -> bool:
+        return self._selected
+
+    @selected.setter
+    def selected(self, value):
+        raise NotImplementedError("'enabled' can only be set through calling 'AcceleratorState().enable_deepspeed_plugin(key)'.")
 
     def to_fsdp_plugin(self) -> "FullyShardedDataParallelPlugin":
         """The native-engine equivalent of this ZeRO configuration."""
