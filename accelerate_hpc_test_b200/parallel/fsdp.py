@@ -293,8 +293,14 @@ class B200ShardedModule(nn.Module):
         self._uses = uses
         if plugin.activation_checkpointing:
             apply_activation_checkpointing(self.module, plugin)
+        # a module marked `_z3_leaf` (DeepSpeedPlugin.set_moe_leaf_modules: mixture-of-experts blocks, whose experts run in a
+        # data-dependent order) is one unit whatever the policy says, and nothing inside it becomes a unit of its own
+        inside_leaf = {id(m) for marked in self.module.modules() if getattr(marked, "_z3_leaf", False)
+                       for m in marked.modules() if m is not marked}
         for fqn, sub in get_module_children_bottom_up(self.module, return_fqns=True):
-            if sub is self.module or not plugin.should_wrap(sub):
+            if sub is self.module or id(sub) in inside_leaf:
+                continue
+            if not (getattr(sub, "_z3_leaf", False) or plugin.should_wrap(sub)):
                 continue
             ps = [p for p in sub.parameters() if id(p) not in claimed and id(p) not in ignored and p.requires_grad]
             if not ps:

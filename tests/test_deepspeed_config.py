@@ -231,5 +231,34 @@ def _prepare_resolves():
     assert acc.deepspeed_plugin.deepspeed_config["gradient_clipping"] == 1.0          # `auto` clipping means 1.0, as under DeepSpeed
 
 
+def _moe_blocks_stay_whole():
+    from accelerate_hpc_test_b200 import Accelerator
+    from accelerate_hpc_test_b200.utils import FullyShardedDataParallelPlugin
+
+    class Experts(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.experts = nn.ModuleList(nn.Linear(8, 8) for _ in range(3))
+
+        def forward(self, x):
+            return self.experts[int(x.sum() > 0)](x)           # which expert runs depends on the data
+
+    model = nn.Sequential(nn.Linear(8, 8), Experts(), nn.Linear(8, 8))
+    plugin = DeepSpeedPlugin(zero_stage=3, transformer_moe_cls_names="Experts")
+    assert plugin.set_moe_leaf_modules(model) == [Experts]
+    acc = Accelerator(fsdp_plugin=FullyShardedDataParallelPlugin(fsdp_version=2, auto_wrap_policy="transformer_based_wrap",
+                                                                 transformer_cls_names_to_wrap=["Linear"]))
+    engine = acc.prepare(model)
+    units = [u.name for u in engine._units]
+    assert "1" in units and not any(name.startswith("1.experts") for name in units), units
+    assert {"0", "2"} <= set(units)
+    x = torch.randn(4, 8) + (1.0 if acc.process_index else -1.0)      # the two ranks take different experts
+    engine(x).sum().backward()
+
+
+def test_marked_moe_blocks_are_single_units_two_processes():
+    debug_launcher(_moe_blocks_stay_whole, num_processes=2)
+
+
 def test_prepare_resolves_the_configuration_two_processes():
     debug_launcher(_prepare_resolves, num_processes=2)
