@@ -35,6 +35,7 @@ from __future__ import annotations
 import contextlib
 import ctypes
 import os
+import re
 from typing import Optional
 
 import torch
@@ -282,7 +283,11 @@ class B200ShardedModule(nn.Module):
         plugin = self.plugin
         claimed = set()
         ignored = set()
-        if plugin.ignored_modules is not None and not isinstance(plugin.ignored_modules, str):
+        if isinstance(plugin.ignored_modules, str):
+            # a string is a regular expression on module names (FSDP_IGNORED_MODULES); what it names stays whole on every rank
+            pattern = re.compile(plugin.ignored_modules)
+            plugin.ignored_modules = [m for name, m in self.module.named_modules() if pattern.fullmatch(name)]
+        if plugin.ignored_modules is not None:
             for m in plugin.ignored_modules:
                 ignored.update(id(p) for p in m.parameters())
         names = {id(p): n for n, p in self.module.named_parameters()}

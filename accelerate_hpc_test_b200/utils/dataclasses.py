@@ -857,7 +857,10 @@ class FullyShardedDataParallelPlugin:
                 self.reshard_after_forward = self.sharding_strategy
         if isinstance(self.reshard_after_forward, str):
             if self.fsdp_version == 2:
-                self.reshard_after_forward = str_to_bool(self.reshard_after_forward.lower(), to_bool=True)
+                try:
+                    self.reshard_after_forward = str_to_bool(self.reshard_after_forward.lower(), to_bool=True)
+                except ValueError:
+                    pass  # not a truth value (an FSDP1 strategy name, say): reported below with the field's name
             else:
                 self.reshard_after_forward = self.reshard_after_forward.upper()
         if self.fsdp_version == 2 and not isinstance(self.reshard_after_forward, bool):
