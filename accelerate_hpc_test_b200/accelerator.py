@@ -93,6 +93,23 @@ _even_batches = object()
 _use_seedable_sampler = object()
 
 
+def _remap_after_sharding(before: dict, after: dict, model) -> dict:
+    """``id(old parameter) -> new parameter`` by name, for re-pointing optimizers after ``fully_shard`` replaced the parameters.
+    A name that is gone afterwards cannot be mapped: with tied embeddings that is the expected casualty (the tie was broken or
+    collapsed by the wrapping) and the message says what to do; otherwise it is a bug worth a loud ``KeyError``
+    (reference accelerator.py:1690-1744)."""
+    missing = [name for name in before if name not in after]
+    if missing:
+        tied = bool(getattr(getattr(model, "config", None), "tie_word_embeddings", False))
+        if tied:
+            raise ValueError(
+                f"FSDP2 mapping failed: {missing} cannot be found after wrapping. The model uses tied embeddings "
+                "(`tie_word_embeddings = True`), which the optimizer re-pointing cannot follow. Create the optimizer after "
+                "`prepare(model)`, or load the model with `tie_word_embeddings = False`.")
+        raise KeyError(f"Parameters missing after FSDP2 wrapping: {missing}")
+    return {id(parameter): after[name] for name, parameter in before.items()}
+
+
 def _is_module(x):
     return isinstance(x, torch.nn.Module)
 
@@ -1079,8 +1096,7 @@ class Accelerator:
                 fully_shard(sub, **kw)
         fully_shard(model, **kw)
         # fully_shard replaced every Parameter by a DTensor one: optimizers built on the old objects are re-pointed in prepare()
-        after = dict(model.named_parameters())
-        model._b200_param_remap = {id(before[n]): after[n] for n in before if n in after}
+        model._b200_param_remap = _remap_after_sharding(before, dict(model.named_parameters()), model)
         model._b200_torch_fsdp2 = True
         return model
 

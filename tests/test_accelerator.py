@@ -310,3 +310,21 @@ def test_parallelism_config_validation():
         ParallelismConfig(dp_replicate_size=2, tp_size=2)
     with patch_environment(parallelism_config_dp_shard_size="2", parallelism_config_cp_size="2"):
         assert ParallelismConfig().dp_shard_cp_dim_names == ["dp_shard", "cp"]
+
+
+def test_optimizer_remap_after_sharding_reports_what_it_cannot_map():
+    import types
+
+    from accelerate_hpc_test_b200.accelerator import _remap_after_sharding
+
+    a, b, c = (torch.nn.Parameter(torch.zeros(1)) for _ in range(3))
+    new_a, new_b = (torch.nn.Parameter(torch.ones(1)) for _ in range(2))
+    model = types.SimpleNamespace(config=types.SimpleNamespace(tie_word_embeddings=False))
+    assert _remap_after_sharding({"x": a, "y": b}, {"x": new_a, "y": new_b}, model) == {id(a): new_a, id(b): new_b}
+    with pytest.raises(KeyError, match="Parameters missing after FSDP2 wrapping") as raised:
+        _remap_after_sharding({"x": a, "y": b, "some_other.weight": c}, {"x": new_a, "y": new_b}, model)
+    assert "some_other.weight" in str(raised.value)
+    model.config.tie_word_embeddings = True
+    with pytest.raises(ValueError, match="FSDP2 mapping failed") as raised:
+        _remap_after_sharding({"model.embed_tokens.weight": a, "lm_head.weight": c}, {"model.embed_tokens.weight": new_a}, model)
+    assert "tied embeddings" in str(raised.value) and "lm_head.weight" in str(raised.value) and "tie_word_embeddings = False" in str(raised.value)
