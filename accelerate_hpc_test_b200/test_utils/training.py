@@ -54,3 +54,25 @@ def mocked_dataloaders(accelerator, batch_size: int = 16):
         return DataLoader(data, shuffle=shuffle, collate_fn=pad_collate, batch_size=batch_size)
 
     return loader(64, 0, True), loader(32, 1, False)
+
+
+def mocked_dataloaders_for_autoregressive_models(accelerator, batch_size: int = 16):
+    """Train / eval dataloaders for a causal language model: fixed-length token sequences whose labels are the inputs themselves
+    (the model shifts them), padded positions masked out of the loss.  Synthetic and reproducible — the reference tokenises the MRPC
+    sentence pairs with a hub tokenizer, which cannot be fetched here."""
+
+    def loader(count, seed, shuffle, length=32, vocab=1000):
+        g = torch.Generator().manual_seed(seed)
+        rows = []
+        for _ in range(count):
+            used = int(torch.randint(length // 2, length + 1, (1,), generator=g))
+            ids = torch.zeros(length, dtype=torch.long)
+            ids[:used] = torch.randint(1, vocab, (used,), generator=g)
+            mask = (torch.arange(length) < used).long()
+            labels = ids.clone()
+            labels[used:] = -100
+            rows.append({"input_ids": ids, "attention_mask": mask, "labels": labels})
+        collate = lambda batch: {key: torch.stack([row[key] for row in batch]) for key in batch[0]}  # noqa: E731
+        return DataLoader(rows, shuffle=shuffle, collate_fn=collate, batch_size=batch_size)
+
+    return loader(64, 0, True), loader(32, 1, False)

