@@ -160,4 +160,12 @@ def __getattr__(name):
         if name in names:
             m = importlib.import_module(f"{__name__}.{mod}")
             return getattr(m, name)
+    # the Megatron helpers carry a prefix here that they do not have in their module (reference utils/__init__.py:269-273)
+    if name.startswith("megatron_lm_") and name[len("megatron_lm_"):] in ("initialize", "prepare_data_loader", "prepare_model_optimizer_scheduler",
+                                                                         "prepare_optimizer", "prepare_scheduler"):
+        return getattr(importlib.import_module(f"{__name__}.megatron_lm"), name[len("megatron_lm_"):])
+    if name == "ParallelismConfig":
+        return importlib.import_module(__name__.rsplit(".", 1)[0] + ".parallelism_config").ParallelismConfig
+    if name == "install_xla":
+        return importlib.import_module(f"{__name__}.torch_xla").install_xla
     raise AttributeError(f"module {__name__!r} has no attribute {name!r}")

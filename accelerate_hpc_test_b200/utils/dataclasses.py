@@ -1089,6 +1089,13 @@ class TorchTensorParallelConfig:
 
 
 # =============================================================================== Megatron-LM (config shell)
+_MEGATRON_LOGGING_SWITCHES = (
+    "log_params_norm", "log_num_zeros_in_grad", "log_throughput", "log_progress", "log_timers_to_tensorboard",
+    "log_batch_size_to_tensorboard", "log_learning_rate_to_tensorboard", "log_loss_scale_to_tensorboard", "log_validation_ppl_to_tensorboard",
+    "log_memory_to_tensorboard", "log_world_size_to_tensorboard",
+)
+
+
 @dataclass
 class MegatronLMPlugin:
     """Megatron-LM option bag.  Megatron itself is not a dependency: tp/cp/sp degrees are mapped
@@ -1207,6 +1214,65 @@ class MegatronLMPlugin:
         }
         if self.other_megatron_args:
             self.megatron_lm_default_args.update(self.other_megatron_args)
+
+    # ------------------------------------------------------------------ what a prepared job records on the plugin
+    def set_network_size_args(self, model, batch_data=None):
+        """Translate ``model.config`` into Megatron's argument names with the parser registered for its ``model_type``."""
+        kind = model.config.model_type.lower()
+        parser = next((fn for name, fn in MODEL_CONFIGS_TO_MEGATRON_PARSERS.items() if name in kind), None)
+        if parser is None:
+            raise ValueError(f"Accelerate Megatron-LM integration not supports {kind} model. You can add your own model config parser.")
+        parser(self, model, batch_data)
+
+    def set_mixed_precision(self, mixed_precision):
+        if mixed_precision == "fp16":
+            self.megatron_lm_default_args["fp16"] = True
+        elif mixed_precision == "bf16":
+            self.megatron_lm_default_args["bf16"] = True
+            self.DDP_impl = "local"
+            self.megatron_lm_default_args["DDP_impl"] = self.DDP_impl
+
+    def set_training_args(self, micro_batch_size, dp_degree):
+        """The batch geometry: global batch = data-parallel ranks x micro batch x micro batches per step."""
+        self.data_parallel_size = dp_degree
+        self.micro_batch_size = micro_batch_size
+        self.global_batch_size = dp_degree * micro_batch_size * self.num_micro_batches
+        self.megatron_lm_default_args.update(data_parallel_size=dp_degree, micro_batch_size=micro_batch_size,
+                                             global_batch_size=self.global_batch_size)
+
+    def set_optimizer_type(self, optimizer):
+        """Record the update rule under Megatron's names (``adam`` / ``sgd`` and their hyper-parameters)."""
+        name = type(optimizer).__name__.lower()
+        args, defaults = self.megatron_lm_default_args, optimizer.defaults
+        if "adam" in name:
+            args.update(optimizer="adam", adam_beta1=defaults["betas"][0], adam_beta2=defaults["betas"][1], adam_eps=defaults["eps"])
+        elif "sgd" in name:
+            args.update(optimizer="sgd", sgd_momentum=defaults["momentum"])
+        else:
+            raise ValueError(f"Optimizer {name} is not supported by Megatron-LM")
+        args.update(lr=defaults["lr"], weight_decay=defaults["weight_decay"])
+
+    def set_scheduler_args(self, scheduler):
+        """Iteration counts from a dummy scheduler's step counts (which are per process: divided by the data-parallel size)."""
+        ranks = self.megatron_lm_default_args["data_parallel_size"]
+        if self.train_iters is None:
+            self.train_iters = scheduler.total_num_steps // ranks
+            if self.train_samples is not None:
+                self.train_samples = None
+                warnings.warn("Ignoring `train_samples` as `train_iters` based on scheduler is being used for training.")
+        if self.lr_warmup_iters is None:
+            self.lr_warmup_iters = scheduler.warmup_num_steps // ranks
+            if self.lr_warmup_samples is not None:
+                warnings.warn("Ignoring `lr_warmup_samples` as `lr_warmup_iters` based on scheduler is being used for training.")
+            self.lr_warmup_samples = 0
+        for key in ("train_iters", "lr_warmup_iters", "train_samples", "lr_warmup_samples", "lr_decay_iters", "lr_decay_samples",
+                    "lr_warmup_fraction", "lr_decay_style", "weight_decay_incr_style", "start_weight_decay", "end_weight_decay", "min_lr"):
+            self.megatron_lm_default_args[key] = getattr(self, key)
+
+    def set_tensorboard_logging_options(self):
+        """Switch on every ``log_*`` option Megatron's tensorboard writer knows (the list is fixed here: Megatron is not imported)."""
+        for key in _MEGATRON_LOGGING_SWITCHES:
+            self.megatron_lm_default_args[key] = True
 
     def to_parallelism_kwargs(self) -> dict:
         """tp / cp sizes for ``ParallelismConfig`` (pipeline training has no native engine: pp must be 1)."""

@@ -286,3 +286,118 @@ def gather_across_data_parallel_groups(tensor):
     from .operations import gather
 
     return gather(tensor)
+
+
+# --------------------------------------------------------------------------------------- function-style API
+# The reference's ``Accelerator._prepare_megatron_lm`` is a sequence of five helpers (reference utils/megatron_lm.py: ``initialize``
+# :97-170, ``prepare_data_loader`` :235-352, ``prepare_model_optimizer_scheduler`` :173-232, ``prepare_optimizer`` :375-381,
+# ``prepare_scheduler`` :409-412) that scripts also call directly.  Here they do the same jobs on the native engines.
+def initialize(accelerator, extra_args_provider=None, args_defaults=None):
+    """Resolve the plugin's settings into one argument namespace (what Megatron's ``initialize_megatron`` produces), seed every
+    generator from it and keep it on the plugin as ``megatron_args``.  ``args_defaults`` override the plugin's defaults;
+    ``extra_args_provider`` may add ``argparse`` arguments, which are read from the command line."""
+    import argparse
+
+    from .random import set_seed
+
+    plugin = accelerator.state.megatron_lm_plugin
+    if plugin is None:
+        raise ValueError("`initialize` needs an Accelerator created with a `MegatronLMPlugin` (or launched with `--use_megatron_lm`).")
+    settings = dict(plugin.megatron_lm_default_args)
+    settings.update(args_defaults or {})
+    if extra_args_provider is not None:
+        parser = extra_args_provider(argparse.ArgumentParser(allow_abbrev=False))
+        extra, _ = parser.parse_known_args()
+        settings.update({k: v for k, v in vars(extra).items() if v is not None})
+    settings.setdefault("seed", 1234)
+    settings.update(rank=accelerator.process_index, world_size=accelerator.num_processes, local_rank=accelerator.local_process_index,
+                    tensor_model_parallel_size=plugin.tp_degree, pipeline_model_parallel_size=plugin.pp_degree,
+                    context_parallel_size=plugin.context_parallel_size)
+    args = argparse.Namespace(**settings)
+    set_seed(args.seed)
+    plugin.megatron_args = args
+    return args
+
+
+def prepare_data_loader(accelerator, dataloader):
+    """An ordinary ``DataLoader`` is sharded over the data-parallel ranks only (ranks of one tensor / context parallel group read the
+    same batches); with ``num_micro_batches`` it yields *whole-step* batches — ``MegatronEngine`` cuts them into micro-batches.
+    ``MegatronLMDummyDataLoader`` (Megatron's own indexed-dataset pipeline) is not part of this build."""
+    if isinstance(dataloader, MegatronLMDummyDataLoader):
+        dataloader.set_megatron_data_args()
+    plugin = accelerator.state.megatron_lm_plugin
+    micro_batches = int(getattr(plugin, "num_micro_batches", 1) or 1)
+    if micro_batches > 1 and getattr(dataloader, "batch_size", None) is not None and not getattr(dataloader, "_is_accelerate_prepared", False):
+        from torch.utils.data import DataLoader
+
+        rebuilt = {k: getattr(dataloader, k) for k in ("num_workers", "collate_fn", "pin_memory", "drop_last", "timeout", "worker_init_fn")}
+        sampler = dataloader.sampler
+        shuffle = type(sampler).__name__ == "RandomSampler"
+        dataloader = DataLoader(dataloader.dataset, batch_size=dataloader.batch_size * micro_batches, shuffle=shuffle, **rebuilt)
+    return accelerator.prepare_data_loader(dataloader)
+
+
+def prepare_optimizer(accelerator, model):
+    """The optimizer Megatron would build from its arguments: the fused AdamW (or SGD) over ``model``'s parameters, hyper-parameters
+    from the plugin's resolved arguments (``set_optimizer_type`` records them when the script created an optimizer itself)."""
+    from ..optim import FusedAdamW
+
+    plugin = accelerator.state.megatron_lm_plugin
+    args = plugin.megatron_lm_default_args
+    params = [p for p in model.parameters() if p.requires_grad]
+    if args.get("optimizer", "adam") == "sgd":
+        return torch.optim.SGD(params, lr=args.get("lr", 1e-3), momentum=args.get("sgd_momentum", 0.0), weight_decay=args.get("weight_decay", 0.0))
+    return FusedAdamW(params, lr=args.get("lr", 1e-3), betas=(args.get("adam_beta1", 0.9), args.get("adam_beta2", 0.999)),
+                      eps=args.get("adam_eps", 1e-8), weight_decay=args.get("weight_decay", 0.01))
+
+
+def prepare_scheduler(accelerator, optimizer, scheduler):
+    """A real scheduler passes through; a ``MegatronLMDummyScheduler`` becomes the warm-up + decay schedule its step counts (and the
+    plugin's ``lr_decay_style`` / ``min_lr``) describe."""
+    import math
+
+    if not isinstance(scheduler, MegatronLMDummyScheduler):
+        return scheduler
+    plugin = accelerator.state.megatron_lm_plugin
+    inner = getattr(optimizer, "optimizer", optimizer)
+    total, warm = scheduler.total_num_steps, scheduler.warmup_num_steps or 0
+    style = getattr(plugin, "lr_decay_style", "linear") or "linear"
+    peak = inner.param_groups[0]["lr"]
+    floor = (getattr(plugin, "min_lr", 0) or 0) / peak if peak else 0.0
+
+    def factor(step):
+        if warm and step < warm:
+            return step / max(1, warm)
+        if not total or style == "constant":
+            return 1.0
+        progress = min(1.0, (step - warm) / max(1, total - warm))
+        shape = 0.5 * (1.0 + math.cos(math.pi * progress)) if style == "cosine" else 1.0 - progress
+        return floor + (1.0 - floor) * shape
+
+    return torch.optim.lr_scheduler.LambdaLR(inner, factor)
+
+
+def prepare_model_optimizer_scheduler(accelerator):
+    """Model, optimizer and scheduler from the plugin alone, for scripts that let Megatron build everything: the model comes from
+    ``custom_prepare_model_function(accelerator)`` or ``custom_model_provider_function()`` (this build has no Megatron model zoo to
+    fall back on), the optimizer and schedule from the resolved arguments."""
+    plugin = accelerator.state.megatron_lm_plugin
+    if plugin.custom_prepare_model_function is not None:
+        if plugin.custom_model_provider_function is None:
+            raise ValueError("You must provide a `custom_model_provider_function` when using a `custom_prepare_model_function`.")
+        model = plugin.custom_prepare_model_function(accelerator)
+    elif plugin.custom_model_provider_function is not None:
+        model = plugin.custom_model_provider_function()
+    else:
+        raise NotImplementedError("Building Megatron's own bert / gpt / t5 models needs Megatron-LM, which is not part of this build: pass a "
+                                  "model to `prepare`, or set `custom_model_provider_function` on the `MegatronLMPlugin`.")
+    model = accelerator.prepare_model(model)
+    optimizer = accelerator.prepare_optimizer(prepare_optimizer(accelerator, model))
+    if hasattr(model, "bind_optimizer"):
+        model.bind_optimizer(optimizer)
+    args = plugin.megatron_lm_default_args
+    schedule = None
+    if args.get("train_iters"):
+        schedule = MegatronLMDummyScheduler(optimizer, total_num_steps=args["train_iters"], warmup_num_steps=args.get("lr_warmup_iters") or 0)
+        schedule = accelerator.prepare_scheduler(prepare_scheduler(accelerator, optimizer, schedule))
+    return model, optimizer, schedule

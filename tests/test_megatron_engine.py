@@ -140,3 +140,109 @@ def test_glm4_moe_config_is_translated_with_its_routing_and_layer_layout():
     plugin = MegatronLMPlugin(seq_length=512)
     parse_glm4_moe_config(plugin, WithLength(), None)
     assert plugin.seq_length == 512
+
+
+def test_plugin_records_batch_geometry_optimizer_and_schedule():
+    import types
+
+    import pytest
+
+    from accelerate_hpc_test_b200.utils import MegatronLMDummyScheduler, MegatronLMPlugin
+
+    plugin = MegatronLMPlugin(num_micro_batches=4, train_samples=1000, lr_warmup_samples=10)
+    plugin.set_training_args(micro_batch_size=2, dp_degree=8)
+    assert plugin.global_batch_size == 64 and plugin.megatron_lm_default_args["micro_batch_size"] == 2
+    layer = torch.nn.Linear(2, 2)
+    plugin.set_optimizer_type(torch.optim.AdamW(layer.parameters(), lr=3e-4, betas=(0.9, 0.95), eps=1e-6, weight_decay=0.1))
+    args = plugin.megatron_lm_default_args
+    assert (args["optimizer"], args["adam_beta2"], args["adam_eps"], args["lr"], args["weight_decay"]) == ("adam", 0.95, 1e-6, 3e-4, 0.1)
+    plugin.set_optimizer_type(torch.optim.SGD(layer.parameters(), lr=0.1, momentum=0.9))
+    assert args["optimizer"] == "sgd" and args["sgd_momentum"] == 0.9
+    with pytest.raises(ValueError, match="rmsprop is not supported by Megatron-LM"):
+        plugin.set_optimizer_type(torch.optim.RMSprop(layer.parameters()))
+    with pytest.warns(UserWarning) as caught:
+        plugin.set_scheduler_args(MegatronLMDummyScheduler(None, total_num_steps=800, warmup_num_steps=80))
+    assert {"train_samples", "lr_warmup_samples"} <= {word for w in caught for word in ("train_samples", "lr_warmup_samples") if word in str(w.message)}
+    assert (plugin.train_iters, plugin.lr_warmup_iters, plugin.train_samples, plugin.lr_warmup_samples) == (100, 10, None, 0)
+    assert args["train_iters"] == 100 and args["lr_decay_style"] == "linear" and args["min_lr"] == 0
+    plugin.set_mixed_precision("bf16")
+    assert args["bf16"] is True and args["DDP_impl"] == "local"
+    plugin.set_tensorboard_logging_options()
+    assert args["log_timers_to_tensorboard"] is True and args["log_validation_ppl_to_tensorboard"] is True
+    model = types.SimpleNamespace(config=types.SimpleNamespace(model_type="mamba"))
+    with pytest.raises(ValueError, match="not supports mamba model"):
+        plugin.set_network_size_args(model)
+    cfg = LlamaConfig.tiny(head_dim=32, hidden_size=64, intermediate_size=128, vocab_size=128)
+    plugin.set_network_size_args(LlamaForCausalLM(cfg, dtype=torch.float32), {"input_ids": torch.zeros(2, 24, dtype=torch.long)})
+    assert args["hidden_size"] == 64 and args["seq_length"] == 24 and args["model_type_name"] == "gpt"
+
+
+def _function_style_api():
+    from torch.utils.data import DataLoader
+
+    from accelerate_hpc_test_b200.utils import (MegatronLMDummyDataLoader, MegatronLMDummyScheduler, MegatronLMPlugin, megatron_lm_initialize,
+                                                megatron_lm_prepare_data_loader, megatron_lm_prepare_model_optimizer_scheduler,
+                                                megatron_lm_prepare_optimizer, megatron_lm_prepare_scheduler)
+
+    cfg = LlamaConfig.tiny(head_dim=32, hidden_size=64, intermediate_size=128, vocab_size=128, num_hidden_layers=2)
+
+    def provider():
+        torch.manual_seed(0)
+        return LlamaForCausalLM(cfg, dtype=torch.float32)
+
+    plugin = MegatronLMPlugin(num_micro_batches=2, lr_decay_style="cosine", min_lr=1e-4, custom_model_provider_function=provider,
+                              other_megatron_args={"seed": 77})
+    acc = Accelerator(megatron_lm_plugin=plugin)
+    assert acc.distributed_type.value == "MEGATRON_LM"
+    args = megatron_lm_initialize(acc, args_defaults={"lr": 1e-2, "weight_decay": 0.0})
+    assert args.seed == 77 and args.world_size == 2 and args.rank == acc.process_index and plugin.megatron_args is args
+    assert args.tensor_model_parallel_size == 1 and args.lr == 1e-2
+    first = torch.rand(1)
+    megatron_lm_initialize(acc)
+    assert torch.equal(torch.rand(1), first)                      # seeded from the arguments, the same on every call and rank
+
+    data = [{"input_ids": torch.randint(0, 128, (16,), generator=torch.Generator().manual_seed(i))} for i in range(32)]
+    collate = lambda rows: {"input_ids": torch.stack([r["input_ids"] for r in rows])}  # noqa: E731
+    loader = megatron_lm_prepare_data_loader(acc, DataLoader(data, batch_size=2, collate_fn=collate))
+    batch = next(iter(loader))
+    assert batch["input_ids"].shape == (4, 16)                    # whole-step batches: micro batch x num_micro_batches
+    assert len(loader) == 32 // 4 // 2                            # ... sharded over the two data-parallel ranks
+    try:
+        megatron_lm_prepare_data_loader(acc, MegatronLMDummyDataLoader(data_path="corpus"))
+    except NotImplementedError as error:
+        assert "Megatron-LM data pipelines are not part of this build" in str(error)
+    else:
+        raise AssertionError("the indexed-dataset pipeline must be refused")
+
+    plugin.megatron_lm_default_args.update(lr=1e-2, weight_decay=0.0, train_iters=10, lr_warmup_iters=2)
+    model, optimizer, scheduler = megatron_lm_prepare_model_optimizer_scheduler(acc)
+    assert type(optimizer.optimizer).__name__ == "FusedAdamW" and optimizer.optimizer.param_groups[0]["lr"] == 0.0     # warm-up starts at zero
+    rates = []
+    for _ in range(5):
+        out = model(input_ids=batch["input_ids"], labels=batch["input_ids"])
+        acc.backward(out.loss)
+        optimizer.step()
+        scheduler.step()
+        optimizer.zero_grad()
+        rates.append(optimizer.optimizer.param_groups[0]["lr"])
+    assert max(rates) == 1e-2 and rates[-1] < 1e-2 and min(rates[1:]) >= 1e-4        # warm-up, cosine decay, never below min_lr
+    # the pieces on their own
+    bare = megatron_lm_prepare_optimizer(acc, provider())
+    assert bare.param_groups[0]["lr"] == 1e-2 and bare.param_groups[0]["weight_decay"] == 0.0
+    real = torch.optim.lr_scheduler.ConstantLR(bare, factor=1.0)
+    assert megatron_lm_prepare_scheduler(acc, bare, real) is real
+    built = megatron_lm_prepare_scheduler(acc, bare, MegatronLMDummyScheduler(bare, total_num_steps=4, warmup_num_steps=0))
+    assert isinstance(built, torch.optim.lr_scheduler.LambdaLR)
+    plugin.custom_model_provider_function = None
+    try:
+        megatron_lm_prepare_model_optimizer_scheduler(acc)
+    except NotImplementedError as error:
+        assert "custom_model_provider_function" in str(error)
+    else:
+        raise AssertionError("without a provider there is no model to build")
+
+
+def test_function_style_api_two_processes():
+    from accelerate_hpc_test_b200 import debug_launcher
+
+    debug_launcher(_function_style_api, num_processes=2)
