@@ -664,6 +664,8 @@ class Accelerator:
 
         if self.distributed_type == DistributedType.DEEPSPEED and self.deepspeed_plugin is not None:
             self._resolve_deepspeed_config(args)
+        if self.distributed_type == DistributedType.MEGATRON_LM and self.state.megatron_lm_plugin is not None:
+            self._record_megatron_arguments(args)
         args = self._materialize_placeholders(args)
         # already-prepared objects pass through untouched (idempotence)
         result = []
@@ -716,6 +718,39 @@ class Accelerator:
                 except Exception:
                     pass
         return tuple(result) if len(result) > 1 else result[0]
+
+    def _record_megatron_arguments(self, args) -> None:
+        """Under a ``MegatronLMPlugin`` the objects handed to ``prepare`` are described in Megatron's argument names on the plugin
+        (``megatron_lm_default_args``): network size from the model's config, batch geometry from the dataloader, the optimizer's
+        rule and the dummy scheduler's step counts — what the reference's ``_prepare_megatron_lm`` (accelerator.py:2478-2579)
+        collects before it initialises Megatron.  The native engines do not read them; scripts and ``MegatronEngine`` users do."""
+        from .utils.megatron_lm import MegatronLMDummyScheduler
+
+        plugin = self.state.megatron_lm_plugin
+        model = next((obj for obj in args if _is_module(obj)), None)
+        loader = next((obj for obj in args if _is_dataloader(obj)), None)
+        optimizer = next((obj for obj in args if _is_optimizer(obj)), None)
+        scheduler = next((obj for obj in args if isinstance(obj, MegatronLMDummyScheduler)), None)
+        pc = self.parallelism_config
+        model_parallel = pc.non_data_parallel_size if pc is not None else max(1, (plugin.tp_degree or 1) * (plugin.context_parallel_size or 1))
+        micro_batch = None
+        if loader is not None:
+            micro_batch = getattr(loader, "batch_size", None) or getattr(getattr(loader, "batch_sampler", None), "batch_size", None)
+        if micro_batch is not None:
+            plugin.set_training_args(micro_batch, max(1, self.num_processes // model_parallel))
+        if model is not None and getattr(getattr(model, "config", None), "model_type", None):
+            try:
+                plugin.set_network_size_args(model, None)
+            except ValueError as error:
+                logger.warning(f"{error} (the model trains all the same; only the Megatron-style description of it is missing)")
+        plugin.set_mixed_precision(self.mixed_precision)
+        if optimizer is not None:
+            try:
+                plugin.set_optimizer_type(optimizer)
+            except ValueError as error:
+                logger.warning(str(error))
+        if scheduler is not None and "data_parallel_size" in plugin.megatron_lm_default_args:
+            plugin.set_scheduler_args(scheduler)
 
     def _resolve_deepspeed_config(self, args) -> None:
         """Fill the ``"auto"`` entries of the active DeepSpeed-style configuration from what ``prepare`` was handed, and refuse

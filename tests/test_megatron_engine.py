@@ -246,3 +246,30 @@ def test_function_style_api_two_processes():
     from accelerate_hpc_test_b200 import debug_launcher
 
     debug_launcher(_function_style_api, num_processes=2)
+
+
+def _prepare_describes_the_job():
+    from torch.utils.data import DataLoader
+
+    from accelerate_hpc_test_b200.utils import MegatronLMPlugin
+
+    plugin = MegatronLMPlugin(num_micro_batches=2)
+    acc = Accelerator(megatron_lm_plugin=plugin)
+    cfg = LlamaConfig.tiny(head_dim=32, hidden_size=64, intermediate_size=128, vocab_size=128, num_hidden_layers=2)
+    model = LlamaForCausalLM(cfg, dtype=torch.float32)
+    optimizer = torch.optim.AdamW(model.parameters(), lr=2e-3, betas=(0.9, 0.98), weight_decay=0.05)
+    data = [torch.randint(0, 128, (16,)) for _ in range(16)]
+    model, optimizer, loader = acc.prepare(model, optimizer, DataLoader(data, batch_size=4))
+    described = plugin.megatron_lm_default_args
+    assert (described["micro_batch_size"], described["data_parallel_size"], described["global_batch_size"]) == (4, 2, 16)
+    assert (described["num_layers"], described["hidden_size"], described["model_type_name"]) == (2, 64, "gpt")
+    assert (described["optimizer"], described["lr"], described["adam_beta2"], described["weight_decay"]) == ("adam", 2e-3, 0.98, 0.05)
+    ids = next(iter(loader))
+    acc.backward(model(input_ids=ids, labels=ids).loss)
+    optimizer.step()
+
+
+def test_prepare_records_the_megatron_description_two_processes():
+    from accelerate_hpc_test_b200 import debug_launcher
+
+    debug_launcher(_prepare_describes_the_job, num_processes=2)
