@@ -153,6 +153,40 @@ class BertForSequenceClassification(nn.Module):
         return SequenceClassifierOutput(loss=loss, logits=logits)
 
 
+    # ------------------------------------------------------------------ pipeline-parallel inference
+    def pipeline_blocks(self):
+        """The model as an ordered list of blocks for ``prepare_pippy``: embeddings, one block per encoder layer, pooler +
+        classifier.  ``(hidden states, key mask)`` travel between blocks; the mask goes as a float tensor (1 = attend) so that
+        it can cross a process boundary like any activation."""
+        from ..inference import Block
+
+        core = self.bert
+
+        def embed(input_ids, attention_mask=None, token_type_ids=None, **_):
+            B, S = input_ids.shape
+            positions = torch.arange(S, device=input_ids.device)[None]
+            if token_type_ids is None:
+                token_type_ids = torch.zeros_like(input_ids)
+            x = core.word_embeddings(input_ids) + core.position_embeddings(positions) + core.token_type_embeddings(token_type_ids)
+            keep = torch.ones(B, S, device=x.device) if attention_mask is None else attention_mask.to(x.device)
+            return core.drop(core.emb_norm(x)), keep.to(x.dtype)
+
+        def encoder(layer):
+            def run(x, keep):
+                return layer(x, keep[:, None, None, :] > 0.5), keep
+
+            return run
+
+        def head(x, keep):
+            pooled = torch.tanh(core.pooler(x[:, 0]))
+            return (self.classifier(self.dropout(pooled)),)
+
+        blocks = [Block("bert.word_embeddings", embed, [core.word_embeddings, core.position_embeddings, core.token_type_embeddings, core.emb_norm])]
+        blocks += [Block(f"bert.layers.{i}", encoder(layer), layer) for i, layer in enumerate(core.layers)]
+        blocks.append(Block("bert.pooler", head, [core.pooler, self.classifier]))
+        return blocks
+
+
 def synthetic_mrpc(n: int, vocab_size: int = 28996, max_len: int = 128, seed: int = 0):
     """MRPC-shaped synthetic sentence pairs: variable lengths, ``[CLS] a [SEP] b [SEP]``, binary labels.
 

@@ -164,3 +164,47 @@ def test_complete_example_covers_feature(feature, monkeypatch):
         if call and call not in text:
             missing.append(ln)
     assert not missing, missing
+
+
+def test_example_side_files_are_well_formed():
+    """Launcher configurations, the ZeRO configuration and the helper module shipped next to the examples load and mean what their
+    READMEs say."""
+    import importlib.util
+
+    from accelerate_hpc_test_b200.commands.launch import _validate_launch_command, launch_command_parser
+    from accelerate_hpc_test_b200.models import LlamaConfig
+    from accelerate_hpc_test_b200.utils import DeepSpeedPlugin
+
+    def merged(path):
+        return _validate_launch_command(launch_command_parser().parse_args(["--config_file", os.path.join(ROOT, "examples", path), "train.py"]))[0]
+
+    cp = merged("torch_native_parallelism/configs/cp.yaml")
+    assert cp.use_fsdp and cp.parallelism_config_cp_size == 4 and cp.num_processes == 4
+    hsdp = merged("torch_native_parallelism/configs/tp_hsdp.yaml")
+    assert (hsdp.parallelism_config_dp_replicate_size, hsdp.parallelism_config_dp_shard_size, hsdp.parallelism_config_tp_size) == (2, 2, 2)
+    sp = merged("alst_ulysses_sequence_parallelism/sp_alst.accelerate_config.yml")
+    assert sp.parallelism_config_sp_size == 8 and sp.num_processes == 8 and sp.mixed_precision == "bf16"
+    zero3 = DeepSpeedPlugin(hf_ds_config=os.path.join(ROOT, "examples", "alst_ulysses_sequence_parallelism", "sp_alst.ds_config.json"))
+    assert zero3.zero_stage == 3 and zero3.stated_precision() == "bf16"
+    assert os.access(os.path.join(ROOT, "examples", "alst_ulysses_sequence_parallelism", "sp_alst.sh"), os.X_OK)
+
+    spec = importlib.util.spec_from_file_location("nd_utils", os.path.join(ROOT, "examples", "torch_native_parallelism", "utils.py"))
+    helpers = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(helpers)
+    config = LlamaConfig.llama3_8b()
+    flops = helpers.get_model_flops_per_token(config, 2048)
+    matmul_weights = config.num_parameters() - config.vocab_size * config.hidden_size          # the embedding table does no matmul
+    assert 6 * matmul_weights < flops < 6.4 * matmul_weights                                   # 6N plus a few percent of attention
+    tracker = helpers.PerformanceTracker(warmup_steps=2, flops_per_token=flops, device="cpu")
+    for _ in range(5):
+        tracker.step(4096)
+    measured = tracker.metrics()
+    assert measured["steps"] == 3 and measured["total_tokens"] == 3 * 4096 and measured["tflops_per_device"] > 0
+    batch = helpers.collate(helpers.synthetic_tokens(3, 16, 100))
+    assert batch["input_ids"].shape == (3, 16) and batch["labels"] is not batch["input_ids"]
+
+
+def test_config_template_reporter_runs():
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "config_yaml_templates", "run_me.py")], cwd=ROOT,
+                         env=dict(os.environ, ACCELERATE_USE_CPU="true"), capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0 and "Accelerator state from the current environment" in res.stdout, res.stdout + res.stderr[-2000:]

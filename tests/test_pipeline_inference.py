@@ -81,3 +81,31 @@ def _llama_pipeline():
 
 def test_native_llama_two_stages():
     debug_launcher(_llama_pipeline, num_processes=2)
+
+
+def _bert_pipeline():
+    from accelerate_hpc_test_b200 import PartialState
+    from accelerate_hpc_test_b200.inference import prepare_pippy
+    from accelerate_hpc_test_b200.models.bert import BertConfig, BertForSequenceClassification
+
+    state = PartialState()
+    cfg = BertConfig(vocab_size=200, hidden_size=32, num_hidden_layers=4, num_attention_heads=4, intermediate_size=64, max_position_embeddings=64)
+    torch.manual_seed(0)
+    model = BertForSequenceClassification(cfg).eval()
+    g = torch.Generator().manual_seed(5)
+    ids = torch.randint(0, 200, (4, 10), generator=g)
+    mask = torch.ones(4, 10, dtype=torch.long)
+    mask[1, 6:] = 0
+    mask[3, 3:] = 0
+    types = torch.randint(0, 2, (4, 10), generator=g)
+    with torch.no_grad():
+        want = model(ids, attention_mask=mask, token_type_ids=types).logits
+    piped = prepare_pippy(model, num_chunks=2, gather_output=True)
+    out = piped(input_ids=ids, attention_mask=mask, token_type_ids=types) if state.is_main_process else piped()
+    assert torch.allclose(out, want, atol=1e-5), (state.process_index, (out - want).abs().max())
+    lo, hi = model.pippy_stage.lo, model.pippy_stage.hi
+    assert hi - lo >= 1 and (lo == 0) == state.is_main_process     # embeddings on the first stage, classifier on the last
+
+
+def test_native_bert_two_stages_with_padding_mask():
+    debug_launcher(_bert_pipeline, num_processes=2)
