@@ -71,6 +71,8 @@ class _Linear(nn.Module):
 
 
 class BertLayer(nn.Module):
+    """Post-norm encoder block: fused QKV projection, scaled-dot-product attention with a key padding mask, GELU feed-forward."""
+
     def __init__(self, c: BertConfig, dtype):
         super().__init__()
         self.c = c
@@ -95,6 +97,8 @@ class BertLayer(nn.Module):
 
 
 class BertModel(nn.Module):
+    """Word + position + token-type embeddings, the encoder stack and the ``[CLS]`` pooler."""
+
     def __init__(self, c: BertConfig, dtype=torch.float32):
         super().__init__()
         self.word_embeddings = nn.Embedding(c.vocab_size, c.hidden_size, dtype=dtype)
@@ -121,6 +125,8 @@ class BertModel(nn.Module):
 
 
 class BertForSequenceClassification(nn.Module):
+    """BERT encoder with a classification head on the pooled ``[CLS]`` state (the MRPC-style example workload)."""
+
     _no_split_modules = ["BertLayer"]
 
     def __init__(self, config: BertConfig, dtype=torch.float32):

@@ -110,6 +110,8 @@ class B200Linear(nn.Module):
 
 
 class B200RMSNorm(nn.Module):
+    """RMSNorm with the residual add fused in: ``forward(x, residual) -> (normed, new_residual)`` on the sm_100a kernel."""
+
     def __init__(self, hidden_size: int, eps: float = 1e-5, dtype=torch.bfloat16, device=None):
         super().__init__()
         self.weight = nn.Parameter(torch.ones(hidden_size, dtype=dtype, device=device))
@@ -122,6 +124,8 @@ class B200RMSNorm(nn.Module):
 
 
 class LlamaAttention(nn.Module):
+    """Grouped-query causal self-attention: one fused QKV projection, RoPE + flash attention as one op (Ulysses / context-parallel variants when those axes are on), output projection."""
+
     def __init__(self, cfg: LlamaConfig, dtype, device=None):
         super().__init__()
         self.cfg = cfg
@@ -156,6 +160,8 @@ class LlamaAttention(nn.Module):
 
 
 class LlamaMLP(nn.Module):
+    """Gated MLP: one fused gate/up projection, SwiGLU kernel, down projection."""
+
     def __init__(self, cfg: LlamaConfig, dtype, device=None):
         super().__init__()
         self.gate_up_proj = B200Linear(cfg.hidden_size, 2 * cfg.intermediate_size, dtype=dtype, device=device)
@@ -166,6 +172,8 @@ class LlamaMLP(nn.Module):
 
 
 class LlamaDecoderLayer(nn.Module):
+    """Pre-norm decoder block (attention, MLP) that passes the un-normalised residual stream along with the activations."""
+
     def __init__(self, cfg: LlamaConfig, layer_idx: int, dtype, device=None):
         super().__init__()
         self.layer_idx = layer_idx
@@ -183,6 +191,8 @@ class LlamaDecoderLayer(nn.Module):
 
 
 class LlamaModel(nn.Module):
+    """Token embedding, the stack of decoder layers and the final norm; activations are ``[tokens, hidden]`` throughout."""
+
     def __init__(self, cfg: LlamaConfig, dtype=torch.bfloat16, device=None):
         super().__init__()
         self.cfg = cfg

@@ -220,6 +220,8 @@ def _seg_table(rows):
 
 
 class B200ShardedModule(nn.Module):
+    """The sharded engine: wraps ``module``, keeps this rank's dim-0 shard of every parameter (fp32 master + compute copy) in peer-mapped memory, gathers a unit's parameters just before it runs, and reduce-scatters — with ``FusedAdamW``, also updates — its gradients as soon as they are complete."""
+
     def __init__(self, module: nn.Module, plugin, device, shard_group=None, replicate_group=None, gradient_state=None,
                  shard_group_is_world: bool = True, dp_group=None):
         super().__init__()
