@@ -22,7 +22,6 @@ from __future__ import annotations
 import contextlib
 import functools
 import json
-import math
 import os
 import re
 import shutil
@@ -43,7 +42,15 @@ from .optimizer import AcceleratedOptimizer
 from .parallelism_config import ParallelismConfig
 from .scheduler import AcceleratedScheduler
 from .state import AcceleratorState, GradientState, PartialState
-from .utils.constants import FSDP_MODEL_NAME, OPTIMIZER_NAME, PROFILE_PATTERN_NAME, SAFE_WEIGHTS_INDEX_NAME, SAFE_WEIGHTS_NAME, SAFE_WEIGHTS_PATTERN_NAME, WEIGHTS_INDEX_NAME, WEIGHTS_NAME, WEIGHTS_PATTERN_NAME
+from .utils.constants import (
+    PROFILE_PATTERN_NAME,
+    SAFE_WEIGHTS_INDEX_NAME,
+    SAFE_WEIGHTS_NAME,
+    SAFE_WEIGHTS_PATTERN_NAME,
+    WEIGHTS_INDEX_NAME,
+    WEIGHTS_NAME,
+    WEIGHTS_PATTERN_NAME,
+)
 from .utils.dataclasses import (
     AORecipeKwargs,
     AutocastKwargs,
@@ -59,31 +66,19 @@ from .utils.dataclasses import (
     GradScalerKwargs,
     InitProcessGroupKwargs,
     KwargsHandler,
-    LoggerType,
     MegatronLMPlugin,
     MSAMPRecipeKwargs,
     PrecisionType,
     ProfileKwargs,
     ProjectConfiguration,
-    RNGType,
     TERecipeKwargs,
     TorchDynamoPlugin,
     TorchTensorParallelPlugin,
 )
-from .utils.environment import parse_choice_from_env, parse_flag_from_env, str_to_bool
-from .utils.memory import clear_device_cache, release_memory
-from .utils.operations import (
-    broadcast,
-    convert_outputs_to_fp32,
-    gather,
-    gather_object,
-    pad_across_processes,
-    recursively_apply,
-    reduce,
-    send_to_device,
-)
+from .utils.environment import parse_choice_from_env, parse_flag_from_env
+from .utils.memory import release_memory
+from .utils.operations import convert_outputs_to_fp32, gather, gather_object, pad_across_processes, recursively_apply, reduce
 from .utils.other import check_os_kernel, clean_state_dict_for_safetensors, compile_regions, extract_model_from_parallel, is_compiled_module, save, wait_for_everyone
-from .utils.random import set_seed
 
 logger = get_logger(__name__)
 

@@ -13,21 +13,11 @@ from pathlib import Path
 
 import numpy as np
 import torch
-from safetensors.torch import load_file, load_model
+from safetensors.torch import load_model
 
 from .logging import get_logger
 from .state import PartialState
-from .utils.constants import (
-    MODEL_NAME,
-    OPTIMIZER_NAME,
-    RNG_STATE_NAME,
-    SAFE_MODEL_NAME,
-    SAFE_WEIGHTS_NAME,
-    SAMPLER_NAME,
-    SCALER_NAME,
-    SCHEDULER_NAME,
-    WEIGHTS_NAME,
-)
+from .utils.constants import MODEL_NAME, OPTIMIZER_NAME, RNG_STATE_NAME, SAFE_MODEL_NAME, SAMPLER_NAME, SCALER_NAME, SCHEDULER_NAME
 from .utils.other import get_pretty_name, load, save
 
 logger = get_logger(__name__)

@@ -11,7 +11,6 @@ not part of the B200 build.
 from __future__ import annotations
 
 import argparse
-import importlib
 import logging
 import os
 import subprocess
@@ -20,10 +19,10 @@ from pathlib import Path
 
 import torch
 
-from ..utils.constants import DEEPSPEED_MULTINODE_LAUNCHERS, TORCH_DYNAMO_MODES
-from ..utils.dataclasses import ComputeEnvironment, DistributedType, DynamoBackend, PrecisionType
-from ..utils.environment import check_cuda_p2p_ib_support, convert_dict_to_env_variables, patch_environment, str_to_bool
-from ..utils.launch import _filter_args, env_var_path_add, prepare_deepspeed_cmd_env, prepare_multi_gpu_env, prepare_simple_launcher_cmd_env
+from ..utils.constants import TORCH_DYNAMO_MODES
+from ..utils.dataclasses import ComputeEnvironment, DistributedType, DynamoBackend
+from ..utils.environment import check_cuda_p2p_ib_support, patch_environment, str_to_bool
+from ..utils.launch import _filter_args, prepare_deepspeed_cmd_env, prepare_multi_gpu_env, prepare_simple_launcher_cmd_env
 from .config.config_args import default_config_file, load_config_from_file
 from .utils import CustomArgumentParser, CustomHelpFormatter
 

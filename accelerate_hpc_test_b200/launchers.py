@@ -9,7 +9,6 @@ Behavioural parity: reference ``src/accelerate/launchers.py:41-309`` (TPU branch
 
 from __future__ import annotations
 
-import os
 import tempfile
 
 import torch

@@ -9,7 +9,6 @@ model family is the framework-level oracle workload, not a hot path.
 
 from __future__ import annotations
 
-import math
 from dataclasses import dataclass
 from typing import Optional
 

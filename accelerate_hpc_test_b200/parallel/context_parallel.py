@@ -19,7 +19,6 @@ from __future__ import annotations
 
 import math
 from contextlib import contextmanager
-from typing import Optional
 
 import torch
 import torch.distributed as dist

@@ -18,7 +18,6 @@ Buckets are filled in reverse parameter order (≈ the order backward produces g
 from __future__ import annotations
 
 import contextlib
-import weakref
 from typing import Optional
 
 import os

@@ -22,7 +22,6 @@ from __future__ import annotations
 import ctypes
 import itertools
 import os
-from typing import Optional
 
 import torch
 

@@ -23,7 +23,6 @@ from __future__ import annotations
 import ctypes
 import math
 import os
-from typing import Optional
 
 import torch
 import torch.distributed as dist

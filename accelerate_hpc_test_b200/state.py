@@ -13,13 +13,11 @@ facts; ``_reset_state`` empties them for tests (:338-346).  What is different he
 from __future__ import annotations
 
 import logging
-import math
 import os
 import threading
-import warnings
 import weakref
 from contextlib import contextmanager
-from functools import partial, wraps
+from functools import partial
 from typing import Any, Callable, Optional
 
 import torch

@@ -7,7 +7,6 @@ Every check compares against torch.distributed (NCCL) or a single-process replay
 import json
 import os
 import sys
-import time
 
 import torch
 import torch.distributed as dist

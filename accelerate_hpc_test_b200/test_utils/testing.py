@@ -23,7 +23,7 @@ import torch
 
 from ..state import AcceleratorState, GradientState, PartialState
 from ..utils import imports as _imp
-from ..utils.versions import compare_versions, is_torch_version
+from ..utils.versions import is_torch_version
 
 
 def get_backend():

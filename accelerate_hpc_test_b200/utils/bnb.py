@@ -11,7 +11,6 @@ from __future__ import annotations
 
 import logging
 from copy import deepcopy
-from typing import Optional
 
 import torch
 import torch.nn as nn

@@ -20,7 +20,7 @@ import logging
 import os
 import warnings
 from contextlib import contextmanager
-from dataclasses import dataclass, field, fields, is_dataclass
+from dataclasses import dataclass, field, fields
 from datetime import timedelta
 from typing import Any, Callable, Iterable, Literal, Optional, Union
 

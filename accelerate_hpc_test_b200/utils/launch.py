@@ -17,7 +17,7 @@ import subprocess
 import sys
 import warnings
 from shutil import which
-from typing import Callable, Optional
+from typing import Callable
 
 import torch
 

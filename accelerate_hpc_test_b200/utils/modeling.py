@@ -32,7 +32,7 @@ import shutil
 import tempfile
 import warnings
 from collections import OrderedDict, defaultdict
-from typing import Iterator, Optional, Union
+from typing import Optional, Union
 
 import torch
 import torch.nn as nn

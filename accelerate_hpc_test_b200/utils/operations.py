@@ -15,7 +15,7 @@ from __future__ import annotations
 import pickle
 import warnings
 from collections.abc import Mapping
-from contextlib import contextmanager, nullcontext
+from contextlib import contextmanager
 from functools import update_wrapper, wraps
 from typing import Any, Callable
 

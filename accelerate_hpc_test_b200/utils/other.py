@@ -9,7 +9,6 @@ Reference parity: src/accelerate/utils/other.py — ``extract_model_from_paralle
 
 from __future__ import annotations
 
-import collections
 import logging
 import os
 import platform
@@ -24,10 +23,6 @@ import torch
 from packaging.version import Version
 
 from ._lazy_state import PartialState
-from .constants import FSDP_PYTORCH_VERSION
-from .dataclasses import DistributedType
-from .imports import is_safetensors_available
-from .versions import is_torch_version
 
 logger = logging.getLogger(__name__)
 

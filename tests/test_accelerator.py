@@ -9,16 +9,14 @@ import pytest
 import torch
 from torch.utils.data import DataLoader, TensorDataset
 
-from accelerate_hpc_test_b200 import Accelerator, AcceleratorState, GradientState, PartialState
+from accelerate_hpc_test_b200 import Accelerator, AcceleratorState, PartialState
 from accelerate_hpc_test_b200.data_loader import DataLoaderShard
 from accelerate_hpc_test_b200.optimizer import AcceleratedOptimizer
 from accelerate_hpc_test_b200.scheduler import AcceleratedScheduler
 from accelerate_hpc_test_b200.test_utils.training import RegressionDataset, RegressionModel
 from accelerate_hpc_test_b200.utils import (
-    DataLoaderConfiguration,
     DistributedType,
     GradientAccumulationPlugin,
-    KwargsHandler,
     ProjectConfiguration,
     patch_environment,
     set_seed,

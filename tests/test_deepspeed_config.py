@@ -3,7 +3,6 @@ entries are filled, which combinations are refused, and what ``prepare`` resolve
 tests/deepspeed/test_deepspeed.py (plugin / autofill / assertion tests), without DeepSpeed itself."""
 
 import json
-import os
 
 import pytest
 import torch

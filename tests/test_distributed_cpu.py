@@ -1,7 +1,6 @@
 """2-process CPU (gloo) runs of the in-package distributed scripts through ``debug_launcher`` — the
 reference's "cluster on a laptop" pattern (reference tests/test_cpu.py:21-27, tests/test_grad_sync.py)."""
 
-import pytest
 import torch
 
 from accelerate_hpc_test_b200.launchers import debug_launcher

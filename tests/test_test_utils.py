@@ -1,10 +1,8 @@
 """test_utils helpers (reference src/accelerate/test_utils/testing.py, examples.py; tests/test_examples.py)."""
 
-import os
 import textwrap
 import unittest
 
-import pytest
 
 from accelerate_hpc_test_b200.test_utils.examples import compare_against_test
 from accelerate_hpc_test_b200.test_utils.testing import (AccelerateTestCase, assert_exception, capture_call_output, get_launch_command,
