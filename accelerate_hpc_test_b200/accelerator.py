@@ -1094,7 +1094,7 @@ class Accelerator:
         bf16 = first is not None and (first.dtype == torch.bfloat16 or (pol is not None and getattr(pol, "param_dtype", None) == torch.bfloat16))
         if not bf16:
             return f"{first.dtype if first is not None else 'no'} parameters without a bf16 mixed-precision policy"
-        if getattr(plugin, "cpu_offload", False) and getattr(getattr(plugin, "cpu_offload", None), "offload_params", True):
+        if getattr(plugin, "offloads_parameters", False):
             return "CPU offload of parameters"
         return ""
 
@@ -1108,7 +1108,7 @@ class Accelerator:
             kw["mp_policy"] = pol if isinstance(pol, MixedPrecisionPolicy) else MixedPrecisionPolicy(
                 param_dtype=getattr(pol, "param_dtype", None), reduce_dtype=getattr(pol, "reduce_dtype", None),
                 output_dtype=getattr(pol, "output_dtype", None))
-        if getattr(plugin, "cpu_offload", False):
+        if getattr(plugin, "offloads_parameters", False):
             kw["offload_policy"] = CPUOffloadPolicy()
         if mesh is not None:
             names = mesh.mesh_dim_names or ()

@@ -319,7 +319,8 @@ def load_checkpoint_and_dispatch(model: nn.Module, checkpoint: Union[str, os.Pat
 
 
 # =========================================================================== storage-dtype casting
-_CASTABLE = (nn.Linear, nn.Conv1d, nn.Conv2d, nn.Conv3d, nn.ConvTranspose1d, nn.ConvTranspose2d, nn.ConvTranspose3d)
+SUPPORTED_PYTORCH_LAYERS_FOR_UPCASTING = (nn.Conv1d, nn.Conv2d, nn.Conv3d, nn.ConvTranspose1d, nn.ConvTranspose2d, nn.ConvTranspose3d, nn.Linear)
+_CASTABLE = SUPPORTED_PYTORCH_LAYERS_FOR_UPCASTING
 _DEFAULT_SKIP_CAST_PATTERNS = ("pos_embed", "patch_embed", "norm", "^proj_in$", "^proj_out$")
 
 

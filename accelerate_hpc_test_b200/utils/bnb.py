@@ -125,6 +125,59 @@ def _auto_device_map(model, cfg: BnbQuantizationConfig, strategy: str, no_split_
     return infer_auto_device_map(model, max_memory=max_memory, **sizing)
 
 
+def get_quantized_model_device_map(model, bnb_quantization_config: BnbQuantizationConfig, device_map=None, max_memory=None,
+                                   no_split_module_classes=None):
+    """The device map a quantised ``model`` will be loaded with: the current GPU when none is asked for, an inferred one for
+    ``"auto"`` / ``"balanced"`` / ``"balanced_low_0"`` / ``"sequential"`` (sized with the quantised bytes), or the given dict — checked:
+    a 4-bit layer cannot live on cpu / disk (its entries must be in ``skip_modules``), an 8-bit one can and is quantised on the way."""
+    cfg = bnb_quantization_config
+    if device_map is None:
+        if not torch.cuda.is_available():
+            raise RuntimeError("No GPU found. A GPU is needed for quantization.")
+        device_map = {"": torch.cuda.current_device()}
+        logger.info("The device_map was not initialized.Setting device_map to `{'':torch.cuda.current_device()}`.")
+    if isinstance(device_map, str):
+        device_map = _auto_device_map(model, cfg, device_map, no_split_module_classes, max_memory)
+    if isinstance(device_map, dict):
+        left_whole = set((cfg.skip_modules or []) + (cfg.keep_in_fp32_modules or []))
+        offloaded = [key for key, where in device_map.items() if key not in left_whole and where in ("cpu", "disk")]
+        if offloaded and cfg.load_in_4bit:
+            raise ValueError(
+                "Some modules are dispatched on the CPU or the disk. Make sure you have enough GPU RAM to fit the quantized model. "
+                "If you want to dispatch the model on the CPU or the disk while keeping these modules in `torch_dtype`, you need to "
+                f"pass a custom `device_map` to `load_and_quantize_model` (offloaded here: {offloaded}).")
+        if offloaded:
+            logger.info("Some modules are are offloaded to the CPU or the disk. Note that these modules will be converted to 8-bit")
+    return device_map
+
+
+def get_parameter_device(parameter: torch.nn.Module):
+    """Device of a module's first parameter."""
+    return next(parameter.parameters()).device
+
+
+def quantize_and_offload_8bit(model, param, param_name, new_dtype, offload_folder, offload_index, fp16_statistics):
+    """Store an 8-bit weight that will live on cpu / disk: quantise it by passing it through GPU 0 once (unless the checkpoint
+    already holds int8 data with its ``SCB`` statistics), write the int8 data and the statistics to ``offload_folder``, and leave a
+    meta tensor in the model."""
+    from .modeling import _owner_of, set_module_tensor_to_device
+    from .offload import offload_weight
+
+    statistics_name = param_name.replace("weight", "SCB")
+    if fp16_statistics is None:
+        set_module_tensor_to_device(model, param_name, 0, dtype=new_dtype, value=param)
+        owner, leaf = _owner_of(model, param_name)
+        quantised = owner._parameters[leaf]
+        quantised.requires_grad = False
+        offload_weight(quantised, param_name, offload_folder, index=offload_index)
+        if hasattr(quantised, "SCB"):
+            offload_weight(quantised.SCB, statistics_name, offload_folder, index=offload_index)
+    else:
+        offload_weight(param, param_name, offload_folder, index=offload_index)
+        offload_weight(fp16_statistics, statistics_name, offload_folder, index=offload_index)
+    set_module_tensor_to_device(model, param_name, "meta", dtype=new_dtype, value=torch.empty(*param.size()))
+
+
 def load_and_quantize_model(model: torch.nn.Module, bnb_quantization_config: BnbQuantizationConfig, weights_location=None, device_map=None,
                             no_split_module_classes=None, max_memory=None, offload_folder=None, offload_state_dict: bool = False):
     """Quantise ``model`` with bitsandbytes.  The intended use: ``model`` was built under ``init_empty_weights`` and
@@ -154,10 +207,7 @@ def load_and_quantize_model(model: torch.nn.Module, bnb_quantization_config: Bnb
         raise RuntimeError(f"`weights_location` needs to be the folder path containing the weights of the model, but we found {weights_location} ")
     with init_empty_weights():
         model, _ = replace_with_bnb_layers(model, cfg, modules_to_not_convert=exclusions)
-    if isinstance(device_map, str):
-        device_map = _auto_device_map(model, cfg, device_map, no_split_module_classes, max_memory)
-    elif device_map is None:
-        device_map = {"": torch.cuda.current_device()}
+    device_map = get_quantized_model_device_map(model, cfg, device_map, max_memory=max_memory, no_split_module_classes=no_split_module_classes)
     load_checkpoint_in_model(model, weights_location, device_map, dtype=cfg.torch_dtype, offload_folder=offload_folder,
                              offload_state_dict=offload_state_dict, keep_in_fp32_modules=cfg.keep_in_fp32_modules,
                              offload_8bit_bnb=cfg.load_in_8bit and offload_folder is not None)

@@ -16,6 +16,11 @@ FSDP_PYTORCH_VERSION = "2.1.0"
 ELASTIC_LOG_LINE_PREFIX_TEMPLATE_PYTORCH_VERSION = "2.2.0"
 XPU_PROFILING_AVAILABLE_PYTORCH_VERSION = "2.4.0"
 MITA_PROFILING_AVAILABLE_PYTORCH_VERSION = "2.1.0"
+DTENSOR_PYTORCH_VERSION = "2.5.0"
+BETA_TP_AVAILABLE_PYTORCH_VERSION = "2.3.0"
+BETA_TP_AVAILABLE_TRANSFORMERS_VERSION = "4.52.0"
+BETA_CP_AVAILABLE_PYTORCH_VERSION = "2.6.0"
+BETA_SP_AVAILABLE_DEEPSPEED_VERSION = "0.18.2"  # the reference's Ulysses needs DeepSpeed from this version on; here it needs none
 
 # ---- what save_state / load_state / save_model call their files
 MODEL_NAME = "pytorch_model"
@@ -54,3 +59,20 @@ TORCH_LAUNCH_PARAMS = (
     "nproc_per_node nnodes node_rank master_addr master_port rdzv_backend rdzv_endpoint rdzv_id rdzv_conf standalone max_restarts "
     "monitor_interval start_method role module m no_python run_path log_dir r redirects t tee"
 ).split()
+
+# ---- SageMaker images the reference's launcher would ask for (kept so that configuration files naming them still load; this build
+# launches on local B200 nodes only)
+SAGEMAKER_PYTORCH_VERSION = "1.10.2"
+SAGEMAKER_PYTHON_VERSION = "py38"
+SAGEMAKER_TRANSFORMERS_VERSION = "4.17.0"
+SAGEMAKER_PARALLEL_EC2_INSTANCES = ["ml.p3.16xlarge", "ml.p3dn.24xlarge", "ml.p4dn.24xlarge"]
+
+
+def __getattr__(name):
+    """``SUPPORTED_PYTORCH_LAYERS_FOR_UPCASTING``: the layer classes whose weights layerwise casting stores small and computes big.
+    Built on first use so that this module stays importable without torch."""
+    if name == "SUPPORTED_PYTORCH_LAYERS_FOR_UPCASTING":
+        from torch import nn
+
+        return (nn.Conv1d, nn.Conv2d, nn.Conv3d, nn.ConvTranspose1d, nn.ConvTranspose2d, nn.ConvTranspose3d, nn.Linear)
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")

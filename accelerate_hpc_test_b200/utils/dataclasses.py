@@ -97,10 +97,18 @@ class SageMakerDistributedType(str, enum.Enum):
 class FP8BackendType(str, enum.Enum):
     """fp8 implementation. ``NATIVE`` = this framework's own MXFP8 block-scaled path."""
 
+    NO = "NO"
     NATIVE = "NATIVE"
     TE = "TE"
     MSAMP = "MSAMP"
     AO = "AO"
+
+
+# value sets of the fp8 recipe fields, for annotations and validation
+Backend = Literal["MSAMP", "TE"]
+OptLevel = Literal["O1", "O2"]
+FP8Format = Literal["HYBRID", "E4M3", "E5M2"]
+AmaxComputeAlgorithm = Literal["max", "most_recent"]
 
 
 class ComputeEnvironment(str, enum.Enum):
@@ -1003,6 +1011,42 @@ class FullyShardedDataParallelPlugin:
                 output_dtype=getattr(mixed_precision, "output_dtype", None),
             )
 
+    def set_cpu_offload(self):
+        """``cpu_offload`` as torch's policy object (what ``fully_shard`` / ``FullyShardedDataParallel`` take); booleans are what the
+        native engine reads (``True`` sends the job to the torch fall-back, which receives the policy object)."""
+        if not isinstance(self.cpu_offload, bool):
+            return
+        if self.fsdp_version == 2:
+            from torch.distributed.fsdp import CPUOffloadPolicy, OffloadPolicy
+
+            self.cpu_offload = CPUOffloadPolicy() if self.cpu_offload else OffloadPolicy()
+        else:
+            from torch.distributed.fsdp import CPUOffload
+
+            self.cpu_offload = CPUOffload(offload_params=self.cpu_offload)
+
+    def validate_cpu_offload(self):
+        if self.fsdp_version == 2:
+            from torch.distributed.fsdp import OffloadPolicy
+
+            if not isinstance(self.cpu_offload, OffloadPolicy):
+                raise ValueError(f"`cpu_offload` must be an instance of `torch.distributed.fsdp.OffloadPolicy` in FSDP2, got {self.cpu_offload}")
+        else:
+            from torch.distributed.fsdp import CPUOffload
+
+            if not isinstance(self.cpu_offload, CPUOffload):
+                raise ValueError(f"`cpu_offload` must be an instance of `torch.distributed.fsdp.CPUOffload` in FSDP1, got {self.cpu_offload}")
+
+    @property
+    def offloads_parameters(self) -> bool:
+        """Whether parameters live on the CPU between uses, whichever way ``cpu_offload`` is spelled (bool or torch policy object)."""
+        value = self.cpu_offload
+        if isinstance(value, bool) or value is None:
+            return bool(value)
+        if hasattr(value, "offload_params"):
+            return bool(value.offload_params)
+        return type(value).__name__ == "CPUOffloadPolicy"
+
     def validate_mixed_precision_policy(self):
         pol = self.mixed_precision_policy
         if pol is not None and not isinstance(pol, MixedPrecisionPolicy):
@@ -1146,6 +1190,7 @@ class MegatronLMPlugin:
     custom_loss_function: Optional[Callable] = None
     other_megatron_args: Optional[dict] = None
     use_custom_fsdp: bool = None
+    overlap_cpu_optimizer_d2h_h2d: bool = None
     no_load_optim: bool = None
     eod_mask_loss: bool = None
     no_save_optim: bool = None
@@ -1188,7 +1233,7 @@ class MegatronLMPlugin:
         if self.expert_tensor_parallel_size is None:
             self.expert_tensor_parallel_size = int(os.environ.get(p + "EXPERT_TENSOR_PARALLEL_SIZE", 1))
         # the long tail: booleans, strings and numbers the launcher exports as MEGATRON_LM_<FIELD>
-        tail = {"use_custom_fsdp": bool, "no_load_optim": bool, "eod_mask_loss": bool, "no_save_optim": bool, "optimizer_cpu_offload": bool,
+        tail = {"use_custom_fsdp": bool, "overlap_cpu_optimizer_d2h_h2d": bool, "no_load_optim": bool, "eod_mask_loss": bool, "no_save_optim": bool, "optimizer_cpu_offload": bool,
                 "use_precision_aware_optimizer": bool, "attention_backend": bool, "attention_softmax_in_fp32": bool,
                 "calculate_per_token_loss": bool, "use_rotary_position_embeddings": bool, "decoder_last_pipeline_num_layers": int,
                 "recompute_num_layers": int, "recompute_granularity": str, "recompute_method": str, "attention_dropout": float,

@@ -283,3 +283,16 @@ def fsdp2_canonicalize_names(named_params: dict) -> dict:
             name = name[len("_orig_mod.") :]
         clean[name] = value
     return clean
+
+
+def get_parameters_from_modules(modules, model, device) -> set:
+    """The parameters of ``modules`` — a list of modules, or a regular expression matched against the module names of ``model`` (the
+    matches are moved to ``device`` first): what a sharding engine must leave whole when they are "ignored modules"."""
+    import re
+
+    if modules is None:
+        return set()
+    if isinstance(modules, str):
+        pattern = re.compile(modules)
+        modules = [module.to(device) for name, module in model.named_modules() if pattern.fullmatch(name)]
+    return {parameter for module in modules for parameter in module.parameters()}

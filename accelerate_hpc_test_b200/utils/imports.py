@@ -333,3 +333,12 @@ def is_bitsandbytes_multi_backend_available():
     import bitsandbytes as bnb
 
     return "multi_backend" in getattr(bnb, "features", set())
+
+
+def is_numpy_available(min_version: str = "1.25.0") -> bool:
+    """numpy is a hard dependency; the question is whether it is at least ``min_version``."""
+    import importlib.metadata
+
+    from packaging.version import parse
+
+    return parse(importlib.metadata.version("numpy")) >= parse(min_version)

@@ -307,6 +307,7 @@ def _tied_copy(tied_params_map, tensor, device):
 def _rewrap_parameter(template: nn.Parameter, data: torch.Tensor, device, requires_grad: bool, non_blocking: bool):
     """A parameter of ``template``'s class around ``data`` on ``device`` (bitsandbytes / quanto / torchao classes need their own treatment)."""
     kind = type(template)
+    requires_grad = requires_grad and (data.is_floating_point() or data.is_complex())  # integer storage (pre-quantised weights) cannot
     if kind.__name__ in _QUANTIZED_PARAM_CLASSES:
         if kind.__name__ == "Int8Params" and data.dtype == torch.float32:
             data = data.to(torch.float16, non_blocking=non_blocking)  # int8 quantisation starts from half precision
@@ -1012,9 +1013,19 @@ def load_checkpoint_in_model(model: nn.Module, checkpoint, device_map: Optional[
                 if target == "disk":
                     if offload_buffers or name not in buffers:
                         stored_dtype = wanted or tensor.dtype
+                        if offload_8bit_bnb:
+                            from .bnb import quantize_and_offload_8bit
+
+                            quantize_and_offload_8bit(model, tensor, name, stored_dtype, offload_folder, disk_index, statistics)
+                            continue
                         set_module_tensor_to_device(model, name, "meta", dtype=stored_dtype)
                         offload_weight(tensor.to(stored_dtype) if torch.is_floating_point(tensor) else tensor, name, offload_folder, index=disk_index)
                 elif target == "cpu" and offload_state_dict:
+                    if offload_8bit_bnb:
+                        from .bnb import quantize_and_offload_8bit
+
+                        quantize_and_offload_8bit(model, tensor, name, wanted or tensor.dtype, parked_folder, parked_index, statistics)
+                        continue
                     set_module_tensor_to_device(model, name, "meta", dtype=wanted or tensor.dtype)
                     offload_weight(tensor, name, parked_folder, index=parked_index)
                 else:

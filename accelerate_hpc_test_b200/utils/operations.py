@@ -33,8 +33,8 @@ def is_torch_tensor(tensor) -> bool:
     return isinstance(tensor, torch.Tensor)
 
 
-def is_tensor_information(x) -> bool:
-    return isinstance(x, TensorInformation)
+def is_tensor_information(tensor_info) -> bool:
+    return isinstance(tensor_info, TensorInformation)
 
 
 def is_namedtuple(data) -> bool:
@@ -273,6 +273,26 @@ def copy_tensor_to_devices(tensor=None) -> torch.Tensor:
         tensor = tensor.to(state.device)
     torch.distributed.broadcast(tensor, src=src)
     return tensor
+
+
+# dtype codes for announcing a tensor that only one rank holds (shape and code travel in one integer vector)
+TENSOR_TYPE_TO_INT = {dtype: code for code, dtype in enumerate(
+    (torch.float, torch.double, torch.half, torch.bfloat16, torch.uint8, torch.int8, torch.int16, torch.int32, torch.int64, torch.bool), start=1)}
+TENSOR_INT_TO_DTYPE = {code: dtype for dtype, code in TENSOR_TYPE_TO_INT.items()}
+
+
+def gather_tensor_shape(tensor):
+    """``(shape, dtype code)`` of a tensor that exists on one rank only, known to every rank afterwards: the holder writes its
+    dimensions followed by the dtype code into a zero vector, a sum over ranks spreads it, the non-zero entries are the answer.
+    (Dimensions of size zero cannot be told from padding — as in the reference, utils/operations.py:496-518.)"""
+    state = PartialState()
+    announced = torch.zeros(64, dtype=torch.int64, device=state.device)
+    if tensor is not None:
+        fields = [*tensor.shape, TENSOR_TYPE_TO_INT[tensor.dtype]]
+        announced[: len(fields)] = torch.tensor(fields, dtype=torch.int64)
+    announced = reduce(announced, reduction="sum")
+    filled = announced[announced.nonzero()].flatten()
+    return filled[:-1], int(filled[-1])
 
 
 # ------------------------------------------------------------------------------- slicing / padding

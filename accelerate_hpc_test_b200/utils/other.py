@@ -209,7 +209,6 @@ def save(obj, f, save_on_each_node: bool = False, safe_serialization: bool = Fal
         torch.save(obj, f)
 
 
-# numpy globals that legacy RNG-state pickles reference; allowed under weights_only=True
 def _numpy_safe_globals():
     out = [np.dtype, np.ndarray]
     core = getattr(np, "_core", None) or getattr(np, "core")
@@ -223,6 +222,10 @@ def _numpy_safe_globals():
     return out
 
 
+# numpy globals that RNG-state pickles reference; allowed while `load` unpickles under weights_only=True
+TORCH_SAFE_GLOBALS = _numpy_safe_globals()
+
+
 def load(f, map_location=None, **kwargs):
     """``torch.load`` with ``weights_only=True`` by default and numpy reconstruction allowed."""
     if "weights_only" not in kwargs:
@@ -231,7 +234,7 @@ def load(f, map_location=None, **kwargs):
     try:
         if kwargs["weights_only"]:
             old = torch.serialization.get_safe_globals()
-            torch.serialization.add_safe_globals(_numpy_safe_globals())
+            torch.serialization.add_safe_globals(TORCH_SAFE_GLOBALS)
         return torch.load(f, map_location=map_location, **kwargs)
     finally:
         if old is not None:

@@ -199,3 +199,27 @@ def _ignored_by_regex():
 
 def test_ignored_modules_by_regular_expression_two_processes():
     debug_launcher(_ignored_by_regex, num_processes=2)
+
+
+def test_cpu_offload_as_bool_or_torch_policy():
+    from torch.distributed.fsdp import CPUOffload, CPUOffloadPolicy, OffloadPolicy
+
+    off = FullyShardedDataParallelPlugin(fsdp_version=2, cpu_offload=False)
+    assert off.offloads_parameters is False
+    off.set_cpu_offload()
+    assert type(off.cpu_offload) is OffloadPolicy and off.offloads_parameters is False     # the policy object of "no offload" is not an offload
+    off.validate_cpu_offload()
+    on = FullyShardedDataParallelPlugin(fsdp_version=2, cpu_offload=True)
+    on.set_cpu_offload()
+    assert isinstance(on.cpu_offload, CPUOffloadPolicy) and on.offloads_parameters is True
+    on.set_cpu_offload()                                                                    # already a policy: left alone
+    first = FullyShardedDataParallelPlugin(fsdp_version=1, cpu_offload=True)
+    first.set_cpu_offload()
+    assert isinstance(first.cpu_offload, CPUOffload) and first.offloads_parameters is True
+    first.validate_cpu_offload()
+    wrong = FullyShardedDataParallelPlugin(fsdp_version=2, cpu_offload=True)
+    with pytest.raises(ValueError, match="must be an instance of `torch.distributed.fsdp.OffloadPolicy` in FSDP2"):
+        wrong.validate_cpu_offload()
+    wrong = FullyShardedDataParallelPlugin(fsdp_version=1, cpu_offload=False)
+    with pytest.raises(ValueError, match="must be an instance of `torch.distributed.fsdp.CPUOffload` in FSDP1"):
+        wrong.validate_cpu_offload()

@@ -135,3 +135,48 @@ def test_prepare_turns_deepspeed_placeholders_into_real_objects():
     assert seen[0] == 0.0 and seen[1] == 0.125 and seen[2] == 0.25 and seen[3] < 0.25  # warm-up then linear decay
     with pytest.raises(ValueError, match="needs its optimizer"):
         acc.prepare(DummyScheduler(DummyOptim(model.parameters())))
+
+
+def test_quantised_device_maps_and_8bit_offload(tmp_path, monkeypatch):
+    import numpy as np
+
+    from accelerate_hpc_test_b200.utils import modeling
+
+    model = Tiny()
+    cfg = bnb.BnbQuantizationConfig(load_in_4bit=True, skip_modules=["lm_head"], keep_in_fp32_modules=[])
+    # a dict is checked: 4-bit layers may not be offloaded unless they are left un-quantised
+    assert bnb.get_quantized_model_device_map(model, cfg, {"embed": 0, "body": 0, "lm_head": "cpu"}) == {"embed": 0, "body": 0, "lm_head": "cpu"}
+    with pytest.raises(ValueError, match="dispatched on the CPU or the disk"):
+        bnb.get_quantized_model_device_map(model, cfg, {"embed": 0, "body": "disk", "lm_head": 0})
+    eight = bnb.BnbQuantizationConfig(load_in_8bit=True, skip_modules=["lm_head"], keep_in_fp32_modules=[])
+    assert bnb.get_quantized_model_device_map(model, eight, {"embed": 0, "body": "cpu", "lm_head": 0})["body"] == "cpu"
+    with pytest.raises(ValueError, match="please choose 'auto', 'balanced', 'balanced_low_0' or 'sequential'"):
+        bnb.get_quantized_model_device_map(model, eight, "everywhere")
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="A GPU is needed for quantization"):
+            bnb.get_quantized_model_device_map(model, eight)
+    assert bnb.get_parameter_device(model.body) == torch.device("cpu")
+
+    # already-quantised checkpoint weights (int8 data + SCB statistics) go to the offload folder as they are, the model keeps a meta tensor
+    index = {}
+    weight = torch.randint(-127, 127, (32, 16), dtype=torch.int8)
+    scb = torch.rand(32)
+    bnb.quantize_and_offload_8bit(model, weight, "body.0.weight", torch.int8, str(tmp_path), index, scb)
+    assert set(index) == {"body.0.weight", "body.0.SCB"} and model.body[0].weight.device.type == "meta"
+    stored = np.memmap(tmp_path / "body.0.weight.dat", dtype=np.int8, mode="r", shape=(32, 16))
+    assert np.array_equal(np.asarray(stored), weight.numpy())
+    # a float weight is quantised by a pass through GPU 0 first: the placement helper is what does it
+    seen = []
+
+    def fake_place(module, name, device, value=None, dtype=None, **kwargs):
+        seen.append((name, device))
+        if device == 0:
+            owner, leaf = modeling._owner_of(module, name)
+            quantised = torch.nn.Parameter(torch.zeros(value.shape, dtype=torch.int8), requires_grad=False)
+            quantised.SCB = torch.ones(value.shape[0])
+            owner._parameters[leaf] = quantised
+
+    monkeypatch.setattr(modeling, "set_module_tensor_to_device", fake_place)
+    index = {}
+    bnb.quantize_and_offload_8bit(model, torch.randn(16, 32), "body.1.weight", torch.float16, str(tmp_path), index, None)
+    assert seen == [("body.1.weight", 0), ("body.1.weight", "meta")] and set(index) == {"body.1.weight", "body.1.SCB"}

@@ -35,3 +35,53 @@ def test_losses_match_the_reference(tmp_path, nproc):
         assert abs(a - b) <= 1e-6 * max(1.0, abs(a)), (i, a, b)
     assert abs(ref["lr"] - ours["lr"]) < 1e-12
     assert abs(ref["checksum"] - ours["checksum"]) <= 1e-6 * abs(ref["checksum"])
+
+
+_SURFACE_PROBE = r"""
+import importlib, inspect, json, sys
+pkg = sys.argv[1]
+
+def norm(flag):
+    return "--" + flag[2:].replace("-", "_") if flag.startswith("--") else flag
+
+def flags(parser):
+    found = set()
+    for action in parser._actions:
+        found.update(norm(s) for s in action.option_strings)
+        if not action.option_strings:
+            found.add("<" + action.dest + ">")
+    return sorted(found)
+
+out = {"cli": {}}
+for module, factory in [("launch", "launch_command_parser"), ("estimate", "estimate_command_parser"), ("merge", "merge_command_parser"),
+                        ("to_fsdp2", "to_fsdp2_command_parser"), ("test", "test_command_parser"), ("env", "env_command_parser")]:
+    out["cli"][module] = flags(getattr(importlib.import_module(f"{pkg}.commands.{module}"), factory)())
+top = importlib.import_module(pkg)
+accelerator = top.Accelerator
+out["accelerator_public"] = sorted(n for n in dir(accelerator) if not n.startswith("_"))
+out["accelerator_init"] = list(inspect.signature(accelerator.__init__).parameters)
+out["partial_state_public"] = sorted(n for n in dir(top.PartialState) if not n.startswith("_"))
+print(json.dumps(out))
+"""
+
+
+def _surface(pkg):
+    extra = REF if pkg == "accelerate" else ROOT
+    env = dict(os.environ, PYTHONPATH=extra + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    r = subprocess.run([sys.executable, "-c", _SURFACE_PROBE, pkg], env=env, cwd="/tmp", capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def test_public_surface_covers_the_reference():
+    """Every command-line flag, every public attribute of ``Accelerator`` / ``PartialState`` and every constructor argument the
+    reference offers is offered here (more is allowed: native-engine switches)."""
+    ref, ours = _surface("accelerate"), _surface("accelerate_hpc_test_b200")
+    for command, wanted in ref["cli"].items():
+        assert set(wanted) <= set(ours["cli"][command]), (command, sorted(set(wanted) - set(ours["cli"][command])))
+    assert set(ref["accelerator_init"]) <= set(ours["accelerator_init"]), sorted(set(ref["accelerator_init"]) - set(ours["accelerator_init"]))
+    # back ends this build does not have (TPU / XLA, IPEX, MS-AMP internals) are the only public names allowed to be absent
+    not_here = {name for name in set(ref["accelerator_public"]) - set(ours["accelerator_public"])}
+    assert not_here <= {"deepspeed_engine_wrapped"}, sorted(not_here)
+    gone = set(ref["partial_state_public"]) - set(ours["partial_state_public"])
+    assert gone <= {"use_ipex"}, sorted(gone)
