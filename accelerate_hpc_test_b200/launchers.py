@@ -13,12 +13,17 @@ import tempfile
 
 import torch
 
-from .state import AcceleratorState
+from .state import AcceleratorState, PartialState
 from .utils.environment import are_libraries_initialized, patch_environment
 from .utils.launch import PrepareForLaunch
 from .utils.other import get_free_port, is_port_in_use
 
 _CUDA_FORK_ERROR = "Cannot re-initialize CUDA in forked subprocess"
+
+
+def test_launch():
+    """Verify a ``PartialState`` can be initialised (the smallest thing a launcher can be asked to run)."""
+    _ = PartialState()
 
 
 def _preflight() -> None:

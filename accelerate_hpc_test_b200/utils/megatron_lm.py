@@ -12,8 +12,16 @@ class MegatronLMDummyDataLoader:
     def __init__(self, **dataset_kwargs):
         self.dataset_args = dict(dataset_kwargs)
 
+    _UNAVAILABLE = "Megatron-LM data pipelines are not part of this build; use a torch DataLoader with `Accelerator.prepare`."
+
     def set_megatron_data_args(self):
-        raise NotImplementedError("Megatron-LM data pipelines are not part of this build; use a torch DataLoader with `Accelerator.prepare`.")
+        raise NotImplementedError(self._UNAVAILABLE)
+
+    def get_train_valid_test_datasets_provider(self, accelerator):
+        raise NotImplementedError(self._UNAVAILABLE)
+
+    def build_train_valid_test_data_iterators(self, accelerator):
+        raise NotImplementedError(self._UNAVAILABLE)
 
 
 class MegatronLMDummyScheduler:
@@ -147,6 +155,25 @@ class T5TrainStep(AbstractTrainStep):
         if accelerator is not None:
             self.bind(accelerator)
 
+    # Megatron's masks are boolean "do NOT attend here" tensors of shape [batch, queries, keys]
+    @staticmethod
+    def attn_mask_postprocess(attention_mask):
+        """Self-attention mask from a ``[batch, seq]`` keep-mask: position (i, j) is blocked unless both tokens are real."""
+        both_real = attention_mask.unsqueeze(1) * attention_mask.unsqueeze(2)
+        return both_real < 0.5
+
+    @staticmethod
+    def get_decoder_mask(seq_length, device):
+        """Causal mask ``[1, seq, seq]``: everything above the diagonal is blocked."""
+        return torch.ones((1, seq_length, seq_length), device=device).tril() < 0.5
+
+    @staticmethod
+    def get_enc_dec_mask(attention_mask, dec_seq_length, device):
+        """Cross-attention mask ``[batch, decoder positions, encoder positions]``: padded encoder tokens are blocked for every query."""
+        batch = attention_mask.shape[0]
+        keys_real = torch.ones((batch, dec_seq_length, 1), device=device) * attention_mask.unsqueeze(1)
+        return keys_real < 0.5
+
 
 class MegatronEngine(torch.nn.Module):
     """``engine(**batch)`` = one full optimisation step over ``num_micro_batches`` slices of the batch.
@@ -180,6 +207,19 @@ class MegatronEngine(torch.nn.Module):
         self.total_loss_dict = {}
         self.eval_total_loss_dict = {}
         self.iteration = 0
+
+    def get_module_config(self):
+        """The wrapped model's configuration with the training hooks Megatron's schedules look for: a loss-scaling function (identity
+        here: bf16 needs none, fp16 scaling is the Accelerator's), the gradient-synchronisation switch of the native engine, and the
+        micro-batch count."""
+        import types
+
+        config = getattr(self.module, "config", None) or getattr(getattr(self.module, "module", None), "config", None)
+        described = types.SimpleNamespace(**(vars(config) if config is not None and hasattr(config, "__dict__") else {}))
+        described.grad_scale_func = lambda loss: loss
+        described.no_sync_func = getattr(self.module, "no_sync", None)
+        described.num_micro_batches = self.num_micro_batches
+        return described
 
     def get_batch_data_iterator(self, batch_data):
         """Split ``batch_data`` into ``num_micro_batches`` equal slices along dim 0 (reference :1008-1031)."""
@@ -401,3 +441,22 @@ def prepare_model_optimizer_scheduler(accelerator):
         schedule = MegatronLMDummyScheduler(optimizer, total_num_steps=args["train_iters"], warmup_num_steps=args.get("lr_warmup_iters") or 0)
         schedule = accelerator.prepare_scheduler(prepare_scheduler(accelerator, optimizer, schedule))
     return model, optimizer, schedule
+
+
+def model_provider_func(pre_process=True, post_process=True, add_encoder=True, add_decoder=True):
+    """Megatron's model provider builds its own bert / gpt / t5 implementations; they are not part of this build (the native models are
+    in ``accelerate_hpc_test_b200.models``).  Set ``custom_model_provider_function`` on the ``MegatronLMPlugin`` instead."""
+    raise NotImplementedError("Megatron-LM's model zoo is not part of this build: set `custom_model_provider_function` on the "
+                              "`MegatronLMPlugin`, or pass a model to `Accelerator.prepare`.")
+
+
+def finish_mpu_init():
+    """Megatron finishes its model-parallel set-up here (process groups, seeds).  The process groups of this build come from
+    ``ParallelismConfig``'s device mesh at ``Accelerator`` construction, so what remains is the seeding — from the arguments that
+    ``initialize`` resolved, if it ran."""
+    from ..state import AcceleratorState
+    from .random import set_seed
+
+    plugin = AcceleratorState().megatron_lm_plugin if AcceleratorState._shared_state else None
+    args = getattr(plugin, "megatron_args", None)
+    set_seed(getattr(args, "seed", 1234))

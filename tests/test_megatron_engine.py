@@ -273,3 +273,36 @@ def test_prepare_records_the_megatron_description_two_processes():
     from accelerate_hpc_test_b200 import debug_launcher
 
     debug_launcher(_prepare_describes_the_job, num_processes=2)
+
+
+def test_t5_masks_engine_config_and_unavailable_pieces():
+    import pytest
+
+    from accelerate_hpc_test_b200.utils.megatron_lm import MegatronLMDummyDataLoader, T5TrainStep, finish_mpu_init, model_provider_func
+
+    keep = torch.tensor([[1, 1, 0], [1, 1, 1]])
+    blocked = T5TrainStep.attn_mask_postprocess(keep)
+    assert blocked.dtype == torch.bool and blocked[0].int().tolist() == [[0, 0, 1], [0, 0, 1], [1, 1, 1]] and not blocked[1].any()
+    assert T5TrainStep.get_decoder_mask(3, "cpu")[0].int().tolist() == [[0, 1, 1], [0, 0, 1], [0, 0, 0]]
+    cross = T5TrainStep.get_enc_dec_mask(keep, dec_seq_length=2, device="cpu")
+    assert cross.shape == (2, 2, 3) and cross[0].int().tolist() == [[0, 0, 1], [0, 0, 1]] and not cross[1].any()
+
+    cfg = LlamaConfig.tiny(head_dim=32, hidden_size=64, intermediate_size=128, vocab_size=128, num_hidden_layers=1)
+    model = LlamaForCausalLM(cfg, dtype=torch.float32)
+    engine = MegatronEngine(Accelerator(cpu=True), model, MegatronLMOptimizerWrapper(FusedAdamW(model.parameters(), lr=1e-3)))
+    engine.num_micro_batches = 3
+    described = engine.get_module_config()
+    assert described.hidden_size == 64 and described.num_micro_batches == 3 and described.grad_scale_func(2.0) == 2.0
+
+    loader = MegatronLMDummyDataLoader(data_path="corpus", seq_length=128)
+    assert loader.dataset_args == {"data_path": "corpus", "seq_length": 128}
+    for call in (loader.set_megatron_data_args, lambda: loader.get_train_valid_test_datasets_provider(None),
+                 lambda: loader.build_train_valid_test_data_iterators(None)):
+        with pytest.raises(NotImplementedError, match="not part of this build"):
+            call()
+    with pytest.raises(NotImplementedError, match="custom_model_provider_function"):
+        model_provider_func()
+    finish_mpu_init()
+    first = torch.rand(1)
+    finish_mpu_init()
+    assert torch.equal(torch.rand(1), first)
