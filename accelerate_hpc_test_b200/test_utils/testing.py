@@ -209,7 +209,7 @@ def are_the_same_tensors(tensor):
     state = AcceleratorState()
     t = tensor[None].clone().to(state.device)
     gathered = gather(t).cpu()
-    t0 = tensor[0].cpu()
+    t0 = t[0].cpu()
     return all(torch.equal(gathered[i], t0) for i in range(gathered.shape[0]))
 
 

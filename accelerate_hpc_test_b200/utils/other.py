@@ -267,7 +267,7 @@ def is_port_in_use(port: int = None) -> bool:
     if port is None:
         port = 29500
     with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
-        return s.connect_ex(("localhost", port)) == 0
+        return s.connect_ex(("127.0.0.1", port)) == 0
 
 
 def get_free_port() -> int:

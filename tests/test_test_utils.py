@@ -94,3 +94,14 @@ def test_autoregressive_mocked_dataloaders_mask_padding_out_of_the_loss():
     assert padded.any() and torch.all(batch["labels"][padded] == -100) and torch.equal(batch["labels"][~padded], batch["input_ids"][~padded])
     again = next(iter(mocked_dataloaders_for_autoregressive_models(None, batch_size=8)[1]))
     assert torch.equal(again["input_ids"], batch["input_ids"])          # reproducible
+
+
+def test_are_the_same_tensors_compares_whole_tensors():
+    import torch
+
+    from accelerate_hpc_test_b200 import Accelerator
+    from accelerate_hpc_test_b200.test_utils import are_the_same_tensors
+
+    Accelerator(cpu=True)
+    assert are_the_same_tensors(torch.arange(6.0).view(2, 3))          # one process: trivially the same, whatever the shape
+    assert are_the_same_tensors(torch.tensor(3.0))
