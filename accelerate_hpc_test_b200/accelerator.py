@@ -437,7 +437,14 @@ class Accelerator:
 
     @property
     def context_parallel_rank(self) -> int:
-        raise NotImplementedError("Context parallelism is currently not supported in Accelerate.")
+        """This process's position in its context-parallel group (the reference raises here: its context parallelism is torch's
+        and gives no rank; the native one has a mesh axis like the others)."""
+        return self._mesh_rank("cp", "Context parallelism")
+
+    @property
+    def sequence_parallel_rank(self) -> int:
+        """This process's position in its Ulysses sequence-parallel group."""
+        return self._mesh_rank("sp", "Sequence parallelism")
 
     @property
     def data_parallel_rank(self) -> int:

@@ -131,3 +131,33 @@ def test_mesh_on_four_cpu_processes():
     from accelerate_hpc_test_b200.launchers import debug_launcher
 
     debug_launcher(_mesh_job, num_processes=4)
+
+
+def _mesh_ranks():
+    import pytest
+
+    from accelerate_hpc_test_b200 import Accelerator
+    from accelerate_hpc_test_b200.parallelism_config import ParallelismConfig
+    from accelerate_hpc_test_b200.state import AcceleratorState
+
+    acc = Accelerator(parallelism_config=ParallelismConfig(cp_size=2))
+    assert acc.context_parallel_rank == acc.process_index and acc.parallelism_config.cp_enabled
+    with pytest.raises(RuntimeError, match="Tensor parallelism is not enabled"):
+        acc.tensor_parallel_rank
+    with pytest.raises(RuntimeError, match="Sequence parallelism is not enabled"):
+        acc.sequence_parallel_rank
+    with pytest.raises(NotImplementedError, match="Pipeline parallelism"):
+        acc.pipeline_parallel_rank
+    assert acc.should_save_model == (acc.process_index == 0)        # the second cp rank holds a replica of what the first saves
+    AcceleratorState._reset_state(reset_partial_state=False)
+    acc = Accelerator(parallelism_config=ParallelismConfig(sp_size=2))
+    assert acc.sequence_parallel_rank == acc.process_index
+    AcceleratorState._reset_state(reset_partial_state=False)
+    acc = Accelerator(parallelism_config=ParallelismConfig(tp_size=2))
+    assert acc.tensor_parallel_rank == acc.process_index and acc.should_save_model
+
+
+def test_rank_properties_follow_the_mesh_two_processes():
+    from accelerate_hpc_test_b200 import debug_launcher
+
+    debug_launcher(_mesh_ranks, num_processes=2)
