@@ -34,18 +34,6 @@ def move_to_device(state, device):
     return state
 
 
-class _StepWitness:
-    """Wraps ``optimizer.step`` so that we can tell afterwards whether the GradScaler actually called it."""
-
-    def __init__(self, step):
-        self._step = step
-        self.called = False
-
-    def __call__(self, *args, **kwargs):
-        self.called = True
-        return self._step(*args, **kwargs)
-
-
 def patch_optimizer_step(accelerated_optimizer: "AcceleratedOptimizer", method):
     """Reference-compatible helper: a ``step`` that records on ``accelerated_optimizer`` that it ran."""
 
