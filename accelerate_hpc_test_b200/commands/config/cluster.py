@@ -332,10 +332,6 @@ _MANY = (DistributedType.MULTI_GPU, DistributedType.MULTI_CPU, DistributedType.F
          DistributedType.MEGATRON_LM)
 
 
-def _device_word(f: Flow) -> str:
-    return "CPU" if f.is_kind(DistributedType.MULTI_CPU) else "GPU"
-
-
 RESOURCES = [
     Ask("top.num_processes", "How many processes should be used for distributed training (one per device)?", "int", 1,
         when=lambda f: f.is_kind(*_MANY)),

@@ -1408,13 +1408,6 @@ def merge_sharded_checkpoint(checkpoint_dir: str) -> dict:
     return dict(model)
 
 
-def _numel(shape) -> int:
-    n = 1
-    for s in shape:
-        n *= int(s)
-    return n
-
-
 def _flatten(x):
     if isinstance(x, torch.Tensor):
         yield x
