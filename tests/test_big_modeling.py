@@ -254,3 +254,29 @@ def test_shard_checkpoint_and_load_checkpoint_in_model(tmp_path):
     model.eval()
     out = load_checkpoint_and_dispatch(fresh2, str(tmp_path), device_map=dm, offload_folder=str(tmp_path / "off2")).eval()(x)
     assert torch.allclose(out, model(x), atol=1e-6)
+
+
+def test_context_parallel_hooks_force_causal_attention_without_a_mask():
+    from accelerate_hpc_test_b200.big_modeling import _attach_context_parallel_hooks
+
+    seen = {}
+
+    class Attention(nn.Module):
+        def forward(self, x, attention_mask=None, is_causal=False):
+            seen.update(mask=attention_mask, causal=is_causal)
+            return x
+
+    class Layer(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.self_attn = Attention()
+            self.other = Attention()
+
+    layer = Layer()
+    assert _attach_context_parallel_hooks(layer) is None
+    layer.self_attn(torch.zeros(1), attention_mask=torch.ones(1, 4))
+    assert seen == {"mask": None, "causal": True}
+    layer.self_attn(torch.zeros(1))                                     # no mask passed: the call is left alone
+    assert seen == {"mask": None, "causal": False}
+    layer.other(torch.zeros(1), attention_mask=torch.ones(1, 4))        # only `*.self_attn` modules are touched
+    assert seen["mask"] is not None and seen["causal"] is False
