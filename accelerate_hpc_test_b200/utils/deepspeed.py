@@ -147,19 +147,36 @@ class DummyScheduler:
 
 
 class DeepSpeedEngineWrapper:
-    """Kept for API parity: ``backward`` on the wrapped engine-like object."""
+    """``backward`` through an engine-like object.  An object with its own ``backward`` / ``step`` (DeepSpeed's contract: the engine
+    scales, accumulates and, at an accumulation boundary, steps) is driven that way; a native engine or plain module has neither,
+    and the loss is simply differentiated — the optimizer step stays with the prepared optimizer."""
 
     def __init__(self, engine):
         self.engine = engine
 
     def backward(self, loss, sync_gradients=True, **kwargs):
-        loss.backward(**kwargs)
+        engine_backward = getattr(self.engine, "backward", None)
+        if not callable(engine_backward):
+            loss.backward(**kwargs)
+            return
+        boundary = getattr(self.engine, "set_gradient_accumulation_boundary", None)
+        if callable(boundary):
+            boundary(is_boundary=sync_gradients)
+        engine_backward(loss, **kwargs)
+        if sync_gradients and callable(getattr(self.engine, "step", None)):
+            self.engine.step()
 
     def get_global_grad_norm(self):
-        return getattr(self.engine, "_last_grad_norm", None)
+        """The gradient norm the engine computed at its last step (a float), or None when it has none to report."""
+        report = getattr(self.engine, "get_global_grad_norm", None)
+        norm = report() if callable(report) else getattr(self.engine, "_last_grad_norm", None)
+        return norm.item() if hasattr(norm, "item") else norm
 
 
 class DeepSpeedOptimizerWrapper:
+    """Under DeepSpeed the engine owns the update and this wrapper's ``step`` / ``zero_grad`` do nothing; on the native engines the
+    optimizer is real, so they call through.  ``step_was_skipped`` reports an fp16 overflow either way."""
+
     def __init__(self, optimizer):
         self.optimizer = optimizer
 
@@ -171,7 +188,7 @@ class DeepSpeedOptimizerWrapper:
 
     @property
     def step_was_skipped(self):
-        return getattr(self.optimizer, "step_was_skipped", False)
+        return bool(getattr(self.optimizer, "step_was_skipped", getattr(self.optimizer, "overflow", False)))
 
 
 class DeepSpeedSchedulerWrapper:
