@@ -200,3 +200,48 @@ def test_config_sections_reach_the_launch_arguments():
 def test_config_file_with_unknown_keys_names_them():
     with pytest.raises(ValueError, match=r"unknown keys \(\['nproc', 'shard_everything'\]\)"):
         load_config_from_file(os.path.join(CONFIGS, "invalid_keys.yaml"))
+
+
+# ------------------------------------------------------------------------------------------------- every sub-command, end to end
+def _cli(*argv, **kwargs):
+    return subprocess.run([sys.executable, "-m", "accelerate_hpc_test_b200.commands.accelerate_cli", *argv], cwd=ROOT, env=ENV,
+                          capture_output=True, text=True, timeout=300, **kwargs)
+
+
+def test_cli_env_estimate_and_help(tmp_path):
+    top = _cli()
+    assert top.returncode == 1 and "accelerate <command> [<args>]" in top.stdout          # no sub-command: help, non-zero
+    for command in ("config", "launch", "env", "test", "estimate-memory", "merge-weights", "to-fsdp2", "tpu-config"):
+        assert command in top.stdout, command
+    config_file = tmp_path / "cfg.yaml"
+    assert _cli("config", "default", "--config_file", str(config_file), "--mixed_precision", "bf16").returncode == 0
+    env = _cli("env", "--config_file", str(config_file))
+    assert env.returncode == 0 and "Copy-and-paste the text below" in env.stdout and "PyTorch version" in env.stdout
+    assert "`Accelerate` config passed:" in env.stdout and "mixed_precision: bf16" in env.stdout
+    estimate = _cli("estimate-memory", "llama3-1b", "--dtypes", "float32", "int4")
+    assert estimate.returncode == 0 and "Largest Layer" in estimate.stdout and "int4" in estimate.stdout and "float32" in estimate.stdout
+    unknown = _cli("estimate-memory", "no-such-model")
+    assert unknown.returncode != 0
+    assert _cli("tpu-config").returncode != 0
+
+
+def test_cli_config_update_and_to_fsdp2(tmp_path):
+    old = tmp_path / "old.yaml"
+    old.write_text(yaml.safe_dump({"compute_environment": "LOCAL_MACHINE", "distributed_type": "FSDP", "mixed_precision": "bf16", "num_processes": 2,
+                                   "fsdp_config": {"fsdp_sharding_strategy": "FULL_SHARD", "fsdp_backward_prefetch": "BACKWARD_PRE",
+                                                   "fsdp_auto_wrap_policy": "TRANSFORMER_BASED_WRAP", "fsdp_use_orig_params": True,
+                                                   "fsdp_transformer_layer_cls_to_wrap": "LlamaDecoderLayer"}}))
+    updated = _cli("config", "update", "--config_file", str(old))
+    assert updated.returncode == 0 and "Sucessfully updated the configuration file" in updated.stdout
+    refreshed = yaml.safe_load(old.read_text())
+    assert refreshed["debug"] is False and refreshed["use_cpu"] is False and refreshed["num_processes"] == 2      # today's keys were added
+    new = tmp_path / "new.yaml"
+    converted = _cli("to-fsdp2", "--config_file", str(old), "--output_file", str(new))
+    assert converted.returncode == 0, converted.stderr[-2000:]
+    section = yaml.safe_load(new.read_text())["fsdp_config"]
+    assert section["fsdp_version"] == 2 and section["fsdp_reshard_after_forward"] is True
+    assert "fsdp_backward_prefetch" not in section and "fsdp_use_orig_params" not in section and "fsdp_sharding_strategy" not in section
+    assert section["fsdp_transformer_layer_cls_to_wrap"] == "LlamaDecoderLayer"
+    refused = _cli("to-fsdp2", "--config_file", str(old), "--output_file", str(new))
+    assert refused.returncode != 0                                                                               # never overwrites silently
+    assert _cli("to-fsdp2", "--config_file", str(old), "--output_file", str(new), "--overwrite").returncode == 0
