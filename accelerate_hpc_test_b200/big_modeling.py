@@ -321,7 +321,6 @@ def load_checkpoint_and_dispatch(model: nn.Module, checkpoint: Union[str, os.Pat
 # =========================================================================== storage-dtype casting
 SUPPORTED_PYTORCH_LAYERS_FOR_UPCASTING = (nn.Conv1d, nn.Conv2d, nn.Conv3d, nn.ConvTranspose1d, nn.ConvTranspose2d, nn.ConvTranspose3d, nn.Linear)
 _CASTABLE = SUPPORTED_PYTORCH_LAYERS_FOR_UPCASTING
-_DEFAULT_SKIP_CAST_PATTERNS = ("pos_embed", "patch_embed", "norm", "^proj_in$", "^proj_out$")
 
 
 def attach_layerwise_casting_hooks(module: nn.Module, storage_dtype: torch.dtype, compute_dtype: torch.dtype,
@@ -329,8 +328,9 @@ def attach_layerwise_casting_hooks(module: nn.Module, storage_dtype: torch.dtype
                                    non_blocking: bool = False) -> None:
     """Linear / convolution layers keep their weights in ``storage_dtype`` and are cast to ``compute_dtype`` only while they
     run.  A sub-tree is left alone when its class is in ``skip_modules_classes`` or its path matches one of the regular
-    expressions in ``skip_modules_pattern``."""
-    patterns = skip_modules_pattern
+    expressions in ``skip_modules_pattern`` (one expression or several).  Only those layer kinds are ever touched — embeddings and
+    normalisation layers keep their dtype even when nothing is skipped (the reference casts the module as a whole in that case)."""
+    patterns = (skip_modules_pattern,) if isinstance(skip_modules_pattern, str) else skip_modules_pattern
 
     def excluded(mod, path) -> bool:
         if skip_modules_classes is not None and isinstance(mod, skip_modules_classes):

@@ -280,3 +280,36 @@ def test_context_parallel_hooks_force_causal_attention_without_a_mask():
     assert seen == {"mask": None, "causal": False}
     layer.other(torch.zeros(1), attention_mask=torch.ones(1, 4))        # only `*.self_attn` modules are touched
     assert seen["mask"] is not None and seen["causal"] is False
+
+
+def test_layerwise_casting_stores_small_and_computes_big():
+    from accelerate_hpc_test_b200.big_modeling import attach_layerwise_casting_hooks
+
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.embed = nn.Embedding(10, 8)
+            self.proj = nn.Linear(8, 8)
+            self.norm = nn.LayerNorm(8)
+            self.head = nn.Linear(8, 4)
+
+        def forward(self, ids):
+            return self.head(self.norm(self.proj(self.embed(ids))))
+
+    torch.manual_seed(0)
+    net = Net()
+    reference = net(torch.arange(6))
+    attach_layerwise_casting_hooks(net, storage_dtype=torch.bfloat16, compute_dtype=torch.float32, skip_modules_pattern=["head"])
+    # linear layers rest in the storage dtype; the skipped head, the embedding and the norm are untouched
+    assert net.proj.weight.dtype == torch.bfloat16 and net.head.weight.dtype == torch.float32
+    assert net.embed.weight.dtype == torch.float32 and net.norm.weight.dtype == torch.float32
+    out = net(torch.arange(6))
+    assert out.dtype == torch.float32 and net.proj.weight.dtype == torch.bfloat16        # computed big, back to small afterwards
+    assert torch.allclose(out, reference, atol=5e-2) and not torch.equal(out, reference)  # only the rounding of the stored weights differs
+    single = Net()
+    attach_layerwise_casting_hooks(single, torch.bfloat16, torch.float32, skip_modules_pattern="^head$")       # one expression as a string
+    assert single.proj.weight.dtype == torch.bfloat16 and single.head.weight.dtype == torch.float32
+    # whole classes can be skipped too
+    other = Net()
+    attach_layerwise_casting_hooks(other, torch.bfloat16, torch.float32, skip_modules_classes=(nn.Linear,))
+    assert other.proj.weight.dtype == torch.float32
