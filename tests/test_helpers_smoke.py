@@ -202,3 +202,89 @@ def test_deepspeed_wrappers_and_megatron_mapping():
     assert pc.tp_size == 2 and pc.cp_size == 1
     with pytest.raises(NotImplementedError, match="pp_degree must be 1"):
         megatron_plugin_to_parallelism_config(MegatronLMPlugin(pp_degree=2))
+
+
+def test_estimate_helpers():
+    from accelerate_hpc_test_b200.commands import estimate
+
+    gb = 2**30
+    assert estimate.estimate_training_usage(4 * gb, "float32") == {"model": 4 * gb, "optimizer": 8 * gb, "gradients": 4 * gb, "step": 16 * gb}
+    mixed = estimate.estimate_training_usage(4 * gb, "bfloat16")
+    assert mixed == {"model": 4 * gb, "optimizer": 8 * gb, "gradients": 6 * gb, "step": 8 * gb}
+    assert set(estimate.estimate_training_usage(gb, "int8").values()) == {-1}
+    table = estimate.create_ascii_table(["dtype", "Total Size"], [["float32", "1.0 GB"], ["int4", "128.0 MB"]], "Memory Usage for loading `m`")
+    lines = table.splitlines()
+    assert lines[0].startswith("┌") and lines[-1].startswith("└") and len({len(line) for line in lines}) == 1       # a rectangle
+    assert "Memory Usage for loading `m`" in lines[1] and "float32" in table and "128.0 MB" in table
+    empty = estimate.create_empty_model("llama3-1b")
+    assert next(empty.parameters()).device.type == "meta"
+    with pytest.raises(OSError, match="neither a built-in config"):
+        estimate.create_empty_model("somebody/some-model")
+
+
+def test_offloaded_weights_come_back(tmp_path):
+    from accelerate_hpc_test_b200.big_modeling import cpu_offload
+    from accelerate_hpc_test_b200.utils import modeling
+    from accelerate_hpc_test_b200.utils.offload import offload_weight, save_offload_index
+
+    torch.manual_seed(0)
+    source = nn.Sequential(nn.Linear(4, 4), nn.Linear(4, 2))
+    index = {}
+    for name, tensor in source.state_dict().items():
+        offload_weight(tensor, name, str(tmp_path), index=index)
+    save_offload_index(index, str(tmp_path))
+    target = nn.Sequential(nn.Linear(4, 4), nn.Linear(4, 2))
+    modeling.load_offloaded_weights(target, index, str(tmp_path))
+    assert all(torch.equal(a, b) for a, b in zip(source.state_dict().values(), target.state_dict().values()))
+    # a model whose weights sit behind offload hooks: one sub-module's entries are filled in
+    hooked = cpu_offload(nn.Sequential(nn.Linear(4, 4), nn.Linear(4, 2)), execution_device="cpu")
+    wanted = {"1.weight": None, "1.bias": None, "0.weight": None}
+    filled = modeling.get_state_dict_from_offload(hooked[1], "1.weight", wanted)
+    assert filled["1.weight"].shape == (2, 4) and filled["1.bias"].shape == (2,) and filled["0.weight"] is None
+    whole = modeling.get_state_dict_offloaded_model(hooked)
+    assert set(whole) == {"0.weight", "0.bias", "1.weight", "1.bias"} and all(t.device.type == "cpu" for t in whole.values())
+
+
+def test_rng_synchronisation_single_process_and_state_descriptor():
+    import threading
+
+    from accelerate_hpc_test_b200 import Accelerator
+    from accelerate_hpc_test_b200.state import ThreadLocalSharedDict
+    from accelerate_hpc_test_b200.utils import RNGType, synchronize_rng_state, synchronize_rng_states
+
+    Accelerator(cpu=True)
+    torch.manual_seed(5)
+    expected = torch.rand(2)
+    torch.manual_seed(5)
+    synchronize_rng_state(RNGType.TORCH)                                # one process: the state is "broadcast" to itself
+    synchronize_rng_states(["torch"])
+    assert torch.equal(torch.rand(2), expected)
+    generator = torch.Generator().manual_seed(9)
+    synchronize_rng_state(RNGType.GENERATOR, generator=generator)
+    assert torch.equal(torch.rand(2, generator=generator), torch.rand(2, generator=torch.Generator().manual_seed(9)))
+
+    class Holder:
+        shared = ThreadLocalSharedDict()
+
+    Holder.shared["main"] = 1
+    seen = {}
+
+    def other_thread():
+        seen["keys"] = list(Holder().shared)                            # a fresh thread starts with its own, empty dict
+        Holder().shared["worker"] = 2
+
+    worker = threading.Thread(target=other_thread)
+    worker.start()
+    worker.join()
+    assert seen["keys"] == [] and list(Holder.shared) == ["main"]
+
+
+def test_generate_device_map_spreads_blocks_evenly():
+    from accelerate_hpc_test_b200.inference import generate_device_map
+
+    model = nn.Sequential(*[nn.Linear(16, 16) for _ in range(4)])
+    one = generate_device_map(model, num_processes=1)
+    assert set(one.values()) <= {0, "cpu"} and len(set(one.values())) == 1
+    two = generate_device_map(model, num_processes=2)
+    placed = [two[name] for name in ("0", "1", "2", "3")]
+    assert placed == sorted(placed) and placed[0] != placed[-1]         # contiguous halves on two devices
