@@ -260,3 +260,38 @@ def test_accelerator_get_tracker_unwrap_and_blank(tmp_path):
     with pytest.raises(ValueError):
         acc.get_tracker("wandb")
     acc.end_training()
+
+
+def test_trackio_and_swanlab_adapters(monkeypatch):
+    Accelerator(cpu=True)
+    seen = []
+    fake_module(monkeypatch, "trackio", init=lambda **k: (seen.append(("init", (), k)), Recorder(seen))[1])
+    t = tracking.TrackioTracker("proj", space_id="me/space")
+    t.start()
+    t.store_init_configuration({"lr": 1e-3})
+    t.log({"loss": 0.5}, step=3)                     # trackio keeps its own step counter: the step is not forwarded
+    t.finish()
+    assert [c[0] for c in seen] == ["init", "config.update", "log", "finish"]
+    assert seen[0][2] == {"project": "proj", "space_id": "me/space"} and seen[2][1] == ({"loss": 0.5},) and seen[2][2] == {}
+    assert t.tracker is not None and tracking.TrackioTracker.name == "trackio" and not tracking.TrackioTracker.requires_logging_directory
+
+    seen.clear()
+    class Config(dict):
+        def update(self, values, **k):
+            super().update(values)
+            seen.append(("config.update", (values,), k))
+
+    swan_config = Config()
+    fake_module(monkeypatch, "swanlab", init=lambda **k: (seen.append(("init", (), k)), Recorder(seen))[1], config=swan_config,
+                Image=lambda x: ("img", x))
+    s = tracking.SwanLabTracker("proj", mode="offline")
+    s.start()
+    assert swan_config["FRAMEWORK"] == "accelerate" and seen[0][2] == {"project": "proj", "mode": "offline"}
+    s.store_init_configuration({"epochs": 3})
+    assert swan_config["epochs"] == 3 and seen[1][2] == {"allow_val_change": True}
+    s.log({"acc": 0.9}, step=7)
+    s.log_images({"samples": ["a", "b"]}, step=7)
+    s.finish()
+    assert seen[2] == ("log", ({"acc": 0.9},), {"step": 7})
+    assert seen[3][1][0] == {"samples": [("img", "a"), ("img", "b")]} and seen[3][2] == {"step": 7}
+    assert seen[-1][0] == "finish"
