@@ -180,3 +180,76 @@ def test_quantised_device_maps_and_8bit_offload(tmp_path, monkeypatch):
     index = {}
     bnb.quantize_and_offload_8bit(model, torch.randn(16, 32), "body.1.weight", torch.float16, str(tmp_path), index, None)
     assert seen == [("body.1.weight", 0), ("body.1.weight", "meta")] and set(index) == {"body.1.weight", "body.1.SCB"}
+
+
+def test_transformer_engine_adapter_through_a_stand_in(monkeypatch):
+    import contextlib
+    import enum
+    import sys
+    import types
+
+    entered = []
+
+    class TELinear(nn.Linear):
+        def __init__(self, i, o, bias=True, params_dtype=torch.float32):
+            super().__init__(i, o, bias=bias, dtype=params_dtype)
+
+    class TELayerNorm(nn.LayerNorm):
+        def __init__(self, width, eps=1e-5, params_dtype=torch.float32):
+            super().__init__(width, eps=eps, dtype=params_dtype)
+
+    class TETransformerLayer(nn.Module):
+        pass
+
+    @contextlib.contextmanager
+    def fp8_autocast(enabled, fp8_recipe):
+        entered.append((enabled, fp8_recipe))
+        yield
+
+    class Format(enum.Enum):
+        E4M3 = 1
+        HYBRID = 2
+
+    pytorch = types.ModuleType("transformer_engine.pytorch")
+    pytorch.Linear, pytorch.LayerNorm, pytorch.TransformerLayer, pytorch.fp8_autocast = TELinear, TELayerNorm, TETransformerLayer, fp8_autocast
+    recipe = types.ModuleType("transformer_engine.common.recipe")
+    recipe.Format = Format
+    recipe.DelayedScaling = lambda **k: ("delayed", k)
+    recipe.MXFP8BlockScaling = lambda **k: ("mxfp8", k)
+    common = types.ModuleType("transformer_engine.common")
+    common.recipe = recipe
+    root = types.ModuleType("transformer_engine")
+    root.pytorch, root.common = pytorch, common
+    for name, module in {"transformer_engine": root, "transformer_engine.pytorch": pytorch, "transformer_engine.common": common,
+                         "transformer_engine.common.recipe": recipe}.items():
+        monkeypatch.setitem(sys.modules, name, module)
+    monkeypatch.setattr(transformer_engine, "is_transformer_engine_available", lambda: True)
+
+    torch.manual_seed(0)
+    model = nn.Sequential(nn.Linear(32, 64), nn.LayerNorm(64), nn.Sequential(nn.Linear(64, 16, bias=False)), nn.Linear(16, 10))
+    x = torch.randn(3, 32)
+    before = model(x)
+    transformer_engine.convert_model(model)
+    assert isinstance(model[0], TELinear) and isinstance(model[1], TELayerNorm) and isinstance(model[2][0], TELinear)
+    assert model[2][0].bias is None and type(model[3]) is nn.Linear          # 10 outputs: off the fp8 tile, left as it is
+    assert torch.equal(model(x), before) and transformer_engine.has_transformer_engine_layers(model)     # weights came along
+    transformer_engine.convert_model(model, to_transformer_engine=False)
+    assert type(model[0]) is nn.Linear and type(model[1]) is nn.LayerNorm and torch.equal(model(x), before)
+    assert not transformer_engine.has_transformer_engine_layers(model)
+
+    from accelerate_hpc_test_b200.utils import TERecipeKwargs
+
+    wrapped = transformer_engine.apply_fp8_autowrap(model, TERecipeKwargs(fp8_format="E4M3", amax_history_len=16, use_autocast_during_eval=False))
+    wrapped.train()
+    wrapped(x)
+    wrapped.eval()
+    wrapped(x)
+    assert [flag for flag, _ in entered] == [True, False]                    # on while training, off in eval unless asked
+    kind, options = entered[0][1]
+    assert kind == "delayed" and options["fp8_format"] is Format.E4M3 and options["amax_history_len"] == 16     # only what differs from TE's defaults
+    entered.clear()
+    block = transformer_engine.apply_fp8_autowrap(nn.Linear(16, 16), TERecipeKwargs(fp8_format="E4M3", use_mxfp8_block_scaling=True,
+                                                                                    use_autocast_during_eval=True))
+    block.eval()
+    block(torch.randn(2, 16))
+    assert entered[0][0] is True and entered[0][1][0] == "mxfp8" and entered[0][1][1]["fp8_format"] is Format.E4M3
