@@ -253,3 +253,44 @@ def test_transformer_engine_adapter_through_a_stand_in(monkeypatch):
     block.eval()
     block(torch.randn(2, 16))
     assert entered[0][0] is True and entered[0][1][0] == "mxfp8" and entered[0][1][1]["fp8_format"] is Format.E4M3
+
+
+def test_torchao_adapter_through_a_stand_in(monkeypatch):
+    import sys
+    import types
+
+    class Float8Linear(nn.Linear):
+        pass
+
+    converted = {}
+
+    def convert_to_float8_training(model, module_filter_fn=None, config=None):
+        converted["config"] = config
+        converted["names"] = []
+        for name, module in list(model.named_modules()):
+            if isinstance(module, nn.Linear) and module_filter_fn(module, name):
+                converted["names"].append(name)
+                owner = model.get_submodule(name.rpartition(".")[0]) if "." in name else model
+                setattr(owner, name.rpartition(".")[2], Float8Linear(module.in_features, module.out_features, bias=module.bias is not None))
+
+    float8 = types.ModuleType("torchao.float8")
+    float8.convert_to_float8_training = convert_to_float8_training
+    float8_linear = types.ModuleType("torchao.float8.float8_linear")
+    float8_linear.Float8Linear = Float8Linear
+    float8.float8_linear = float8_linear
+    root = types.ModuleType("torchao")
+    root.float8 = float8
+    for name, module in {"torchao": root, "torchao.float8": float8, "torchao.float8.float8_linear": float8_linear}.items():
+        monkeypatch.setitem(sys.modules, name, module)
+    monkeypatch.setattr(ao, "is_torchao_available", lambda: True)
+
+    model = nn.Sequential(nn.Linear(16, 32), nn.Linear(32, 32), nn.Linear(32, 24), nn.Linear(32, 32), nn.Linear(32, 16))
+    ao.convert_model_to_fp8_ao(model, config="recipe")
+    # the first and the last linear stay precise, so does the one whose width is off the fp8 tile
+    assert converted == {"config": "recipe", "names": ["1", "3"]} and ao.has_ao_layers(model)
+    assert type(model[0]) is nn.Linear and type(model[2]) is nn.Linear and type(model[4]) is nn.Linear
+    custom = nn.Sequential(nn.Linear(16, 16), nn.Linear(16, 16))
+    ao.convert_model_to_fp8_ao(custom, module_filter_func=lambda module, fqn: fqn == "0")
+    assert converted["names"] == ["0"]
+    with pytest.raises(NotImplementedError, match="resolved by `convert_model_to_fp8_ao`"):
+        ao.filter_first_and_last_linear_layers(custom[0], "0")
