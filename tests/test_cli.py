@@ -203,13 +203,41 @@ def test_config_file_with_unknown_keys_names_them():
 
 
 # ------------------------------------------------------------------------------------------------- every sub-command, end to end
-def _cli(*argv, **kwargs):
-    return subprocess.run([sys.executable, "-m", "accelerate_hpc_test_b200.commands.accelerate_cli", *argv], cwd=ROOT, env=ENV,
-                          capture_output=True, text=True, timeout=300, **kwargs)
+class _Ran:
+    def __init__(self, returncode, stdout):
+        self.returncode, self.stdout, self.stderr = returncode, stdout, ""
+
+
+def _cli(*argv):
+    """Run ``accelerate <argv>`` in this process through the real parser and handler (a fresh interpreter per call costs seconds)."""
+    import contextlib
+    import io
+
+    from accelerate_hpc_test_b200.commands.accelerate_cli import build_parser
+
+    captured = io.StringIO()
+    code = 0
+    with contextlib.redirect_stdout(captured), contextlib.redirect_stderr(captured):
+        try:
+            parser = build_parser()
+            args = parser.parse_args(list(argv))
+            handler = getattr(args, "func", None)
+            if handler is None:
+                parser.print_help()
+                code = 1
+            else:
+                handler(args)
+        except SystemExit as stop:
+            code = stop.code if isinstance(stop.code, int) else (0 if stop.code is None else 1)
+        except Exception as error:  # noqa: BLE001 - a command that raises is a command that failed
+            print(f"{type(error).__name__}: {error}")
+            code = 1
+    return _Ran(code, captured.getvalue())
 
 
 def test_cli_env_estimate_and_help(tmp_path):
-    top = _cli()
+    top = subprocess.run([sys.executable, "-m", "accelerate_hpc_test_b200.commands.accelerate_cli"], cwd=ROOT, env=ENV, capture_output=True,
+                         text=True, timeout=300)                                             # once for real: the module entry point
     assert top.returncode == 1 and "accelerate <command> [<args>]" in top.stdout          # no sub-command: help, non-zero
     for command in ("config", "launch", "env", "test", "estimate-memory", "merge-weights", "to-fsdp2", "tpu-config"):
         assert command in top.stdout, command
@@ -237,7 +265,7 @@ def test_cli_config_update_and_to_fsdp2(tmp_path):
     assert refreshed["debug"] is False and refreshed["use_cpu"] is False and refreshed["num_processes"] == 2      # today's keys were added
     new = tmp_path / "new.yaml"
     converted = _cli("to-fsdp2", "--config_file", str(old), "--output_file", str(new))
-    assert converted.returncode == 0, converted.stderr[-2000:]
+    assert converted.returncode == 0, converted.stdout[-2000:]
     section = yaml.safe_load(new.read_text())["fsdp_config"]
     assert section["fsdp_version"] == 2 and section["fsdp_reshard_after_forward"] is True
     assert "fsdp_backward_prefetch" not in section and "fsdp_use_orig_params" not in section and "fsdp_sharding_strategy" not in section
