@@ -317,6 +317,9 @@ def prepare_deepspeed_cmd_env(args: argparse.Namespace) -> tuple[list[str], dict
         raise ValueError(f"Unknown multinode launcher {launcher}; choose from {DEEPSPEED_MULTINODE_LAUNCHERS}")
     env = prepare_multi_gpu_env(args)
     env["ACCELERATE_USE_DEEPSPEED"] = "true"
+    # which DeepSpeed settings came from the accelerate config file: next to a `deepspeed_config_file` the plugin refuses the ones
+    # that file is supposed to state itself
+    env["ACCELERATE_CONFIG_DS_FIELDS"] = str(getattr(args, "deepspeed_fields_from_accelerate_config", "") or "").lower()
     _apply(_DEEPSPEED_RULES, args, env)
     return [], env
 

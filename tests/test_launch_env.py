@@ -173,6 +173,9 @@ def test_deepspeed_flags_are_a_config_dialect():
     assert cmd == [] and env["ACCELERATE_USE_DEEPSPEED"] == "true" and env["ACCELERATE_DEEPSPEED_ZERO_STAGE"] == "3"
     assert env["ACCELERATE_GRADIENT_ACCUMULATION_STEPS"] == "2" and env["ACCELERATE_DEEPSPEED_OFFLOAD_PARAM_DEVICE"] == "cpu"
     assert env["ACCELERATE_DEEPSPEED_ZERO3_INIT"] == "true" and "ACCELERATE_DEEPSPEED_CONFIG_FILE" not in env
+    assert env["ACCELERATE_CONFIG_DS_FIELDS"] == ""                          # nothing came from an accelerate config file
+    args.deepspeed_fields_from_accelerate_config = "deepspeed_config_file,Zero3_Init_Flag"
+    assert prepare_deepspeed_cmd_env(args)[1]["ACCELERATE_CONFIG_DS_FIELDS"] == "deepspeed_config_file,zero3_init_flag"
     args.deepspeed_multinode_launcher = "carrier_pigeon"
     with pytest.raises(ValueError, match="Unknown multinode launcher"):
         prepare_deepspeed_cmd_env(args)
