@@ -73,3 +73,45 @@ def test_packaging_declares_the_reference_console_scripts_and_the_package_versio
         module_name, func = target.split(":")
         module = importlib.import_module(f"accelerate_hpc_test_b200.{module_name}")
         assert callable(getattr(module, func))
+
+
+def test_built_library_contains_the_blackwell_instructions_it_claims():
+    """``cuobjdump -sass`` on the built kernel library (no GPU needed): the GEMM and attention kernels issue tcgen05 MMAs fed by TMA
+    tensor loads with accumulators read back from tensor memory, the NVLS collectives reduce inside the switch (``multimem.ld_reduce``),
+    the peer-memory copy kernels move data with bulk asynchronous copies.  A refactor that silently falls back to ``mma.sync`` or to
+    plain loads fails here, before any GPU time is spent."""
+    import shutil
+
+    import pytest
+
+    lib = os.path.join(ROOT, "accelerate_hpc_test_b200", "lib", "libb200.so")
+    if not os.path.exists(lib) or shutil.which("cuobjdump") is None:
+        pytest.skip("needs the built kernel library and cuobjdump")
+    listing = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sass_evidence.py")], cwd=ROOT, capture_output=True, text=True,
+                             timeout=600)
+    assert listing.returncode == 0, listing.stderr[-2000:]
+    per_kernel = {}
+    for line in listing.stdout.splitlines():
+        name, _, evidence = line.partition(": ")
+        per_kernel[name.strip()] = evidence
+
+    def kernels(fragment):
+        found = {name: evidence for name, evidence in per_kernel.items() if fragment in name}
+        assert found, f"no kernel named *{fragment}* in the library"
+        return found
+
+    for name, evidence in kernels("gemm2_kernel").items():                      # the 2-CTA tcgen05 GEMM family
+        assert ("UTCHMMA" in evidence or "UTCQMMA" in evidence) and "UTMALDG" in evidence and "LDTM" in evidence, (name, evidence)  # bf16 / fp8
+        assert ".2CTA" in evidence, (name, "cta_group::2 expected")
+        assert " HMMA" not in " " + evidence, (name, "legacy mma.sync in a tcgen05 kernel")
+    for fragment in ("flash_fwd_kernel", "flash_bwd_kernel"):
+        for name, evidence in kernels(fragment).items():
+            if "prep" in name:
+                continue
+            assert "UTCHMMA" in evidence and "UTMALDG" in evidence and "MUFU.EX2" in evidence, (name, evidence)
+    for fragment in ("allreduce_nvls_kernel", "reduce_scatter_adamw_nvls_kernel"):
+        for name, evidence in kernels(fragment).items():
+            assert "LDGMC.E.HPADD.BF16x8" in evidence, (name, evidence)            # multimem.ld_reduce: the NVSwitch adds
+    for fragment in ("allgather_pull_kernel", "seq_head_exchange_kernel"):
+        for name, evidence in kernels(fragment).items():
+            assert "UBLKCP" in evidence and "SYNCS" in evidence, (name, evidence)      # cp.async.bulk completed through mbarriers
