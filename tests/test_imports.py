@@ -28,9 +28,9 @@ def _imported_by(statement: str) -> set:
 
 @pytest.mark.parametrize("statement", [
     "import accelerate_hpc_test_b200",
-    "from accelerate_hpc_test_b200 import Accelerator, ParallelismConfig, notebook_launcher, init_empty_weights",
-    "import accelerate_hpc_test_b200.commands.accelerate_cli",
-    "import accelerate_hpc_test_b200.tracking, accelerate_hpc_test_b200.utils",
+    # the user-facing names, the CLI, the trackers and the utilities in one interpreter (each start costs seconds)
+    "from accelerate_hpc_test_b200 import Accelerator, ParallelismConfig, notebook_launcher, init_empty_weights; "
+    "import accelerate_hpc_test_b200.commands.accelerate_cli, accelerate_hpc_test_b200.tracking, accelerate_hpc_test_b200.utils",
 ])
 def test_optional_packages_are_not_imported(statement):
     dragged_in = _imported_by(statement) & OPTIONAL
